@@ -329,8 +329,8 @@ def config_c1(out_dir: str, width: int = 800, height: int = 800, samples: int = 
         SceneObject(OBJ_SPHERE, id=5, material=3, centerIdx=9, radius=1.5),
         SceneObject(OBJ_SPHERE, id=6, material=4, centerIdx=10, radius=0.75),
     ]
-    sc.pointLights = [PointLight((6.0, 10.0, 6.0), (14000, 14000, 14000)),
-                      PointLight((-7.0, 10.0, 3.0), (9000, 8000, 7000))]
+    sc.pointLights = [PointLight((6.0, 10.0, 6.0), (24000, 24000, 24000)),
+                      PointLight((-7.0, 10.0, 3.0), (16000, 14000, 12000))]
     sc.cameras = [Camera(id=1, imageName="c1.png", width=width, height=height, numSamples=samples,
                          position=(0.5, 5.0, 13.0), gazePoint=(0.0, 1.0, 0.0), up=(0, 1, 0),
                          nearDistance=1.0, fovy=45.0, isLookAt=True)]
@@ -341,7 +341,7 @@ def config_c1(out_dir: str, width: int = 800, height: int = 800, samples: int = 
 
 def _terrain_scene(out_dir: str, name: str, seed: int, n: int, width: int, height: int, samples: int,
                    lights: int) -> str:
-    pos, tris = terrain_mesh(n, seed)
+    pos, tris = terrain_mesh(n, seed, amp=1.5)
     write_ply(os.path.join(out_dir, f"{name}_terrain.ply"), pos, tris)
     sc = Scene(maxRecursionDepth=0, backgroundColor=(10, 20, 40), ambient=(20, 20, 20))
     sc.materials = [_plain(1, (0.6, 0.55, 0.4), (0.25, 0.25, 0.25), 30.0)]
@@ -351,8 +351,8 @@ def _terrain_scene(out_dir: str, name: str, seed: int, n: int, width: int, heigh
         sc.pointLights.append(PointLight((-9.0, 7.0, -2.0), (9000, 10000, 12000)))
     aspect = width / height
     sc.cameras = [Camera(id=1, imageName=f"{name}.png", width=width, height=height, numSamples=samples,
-                         position=(0.0, 9.0, 17.0), gaze=(0.0, -0.5, -1.0), up=(0, 1, 0),
-                         nearPlane=(-0.5 * aspect, 0.5 * aspect, -0.5, 0.5), nearDistance=1.0)]
+                         position=(0.0, 12.0, 19.0), gaze=(0.0, -0.68, -1.0), up=(0, 1, 0),
+                         nearPlane=(-0.42 * aspect, 0.42 * aspect, -0.42, 0.42), nearDistance=1.0)]
     path = os.path.join(out_dir, f"{name}.rtscene")
     write_rtscene(sc, path)
     return path
@@ -409,7 +409,7 @@ def config_c3(out_dir: str, width: int = 1024, height: int = 1024, samples: int 
     Mi = mat_translate((-1.0 + j(), 3.2, 0.2 + j())) @ mat_rotate((0.3, 1.0, 0.2), 25.0) @ mat_scale((0.9, 0.7, 0.9))
     objs.append(SceneObject(OBJ_MESH, id=14, material=7, smooth=False, plyPath="c3_ico.ply", transform=colmajor(Mi)))
     sc.objects = objs
-    sc.pointLights = [PointLight((0.0, 9.0, 2.0), (2600, 2600, 2600)), PointLight((-3.0, 6.0, 4.0), (1200, 1100, 1000))]
+    sc.pointLights = [PointLight((0.0, 9.0, 2.0), (6000, 6000, 6000)), PointLight((-3.0, 6.0, 4.0), (2600, 2400, 2200))]
     sc.cameras = [Camera(id=1, imageName="c3.png", width=width, height=height, numSamples=samples,
                          position=(0.0, 4.0, 14.5), gazePoint=(0.0, 3.0, 0.0), up=(0, 1, 0),
                          nearDistance=1.0, fovy=40.0, isLookAt=True)]
