@@ -1,0 +1,200 @@
+/*
+ * rtcuda.h — C ABI of the B200-native render module ("CRTCuda").
+ *
+ * Drop-in boundary for MyRayTracer's render loop: it replaces the body of
+ *   Renderer.render(scene:cameraIndex:progressRow:) -> [Vec3]
+ *       (Sources/RayTracer/Extensions/Object+Extension.swift:52-379)
+ * and the RGBA8 conversion that follows it
+ *       (Sources/RayTracer/RayTracer.swift:186-195),
+ * fed by the arrays of RTContext (Sources/RayTracer/Models/RTContext.swift:74-92).
+ *
+ * Conventions copied from the reference's only native module, CPly
+ * (Sources/CPly/include/PLYReaderWrapper.h:18-69, Sources/CPly/wrapper.cpp:17-56):
+ * pure C, <stdint.h> only, opaque handle, create() returns NULL on failure and
+ * never throws, destroy(NULL) is safe, every call tolerates a NULL handle,
+ * caller-owned output buffers, borrowed input pointers (valid for the duration
+ * of the call only), enums cross as int.  Status: 0 = ok, negative = error;
+ * rt_last_error() returns a thread-local message.
+ *
+ * All vectors are FP64 as in the reference (Vec3 = SIMD3<Double>,
+ * RTContext.swift:13-16); matrices are column-major like simd_double4x4.
+ */
+#ifndef RTCUDA_H
+#define RTCUDA_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_ABI_VERSION 1
+
+/* status codes; -10/-20/-21 mirror the reference's NSError codes (RayTracer.swift:121-123,142-154) */
+enum {
+    RT_OK = 0,
+    RT_ERR_INVALID = -1,       /* bad argument / inconsistent description */
+    RT_ERR_CUDA = -2,          /* CUDA runtime failure (message in rt_last_error) */
+    RT_ERR_UNSUPPORTED = -3,   /* feature outside the implemented path (fails loudly, never falls back) */
+    RT_ERR_CANCELLED = -4,     /* progress callback asked to stop */
+    RT_ERR_BAD_CAMERA = -10,   /* "Invalid camera index" */
+    RT_ERR_NO_SCENE = -20,     /* "No scene loaded. Can't render." */
+    RT_ERR_NO_RENDERER = -21   /* "Renderer not initialized." */
+};
+
+/* Material.type strings of the reference ("mirror", "dielectric", "conductor", anything else);
+ * Object+Extension.swift:189,207,252 */
+enum { RT_MAT_PLAIN = 0, RT_MAT_MIRROR = 1, RT_MAT_DIELECTRIC = 2, RT_MAT_CONDUCTOR = 3 };
+
+/* GeometryType raw values, Accelearion/BVH.swift:33-38 */
+enum { RT_GEO_MESH = 0, RT_GEO_TRIANGLE = 1, RT_GEO_SPHERE = 2, RT_GEO_PLANE = 3 };
+
+/* HitKind (ParsingKit): .none/.triangle/.sphere/.plane */
+enum { RT_HIT_NONE = 0, RT_HIT_TRIANGLE = 1, RT_HIT_SPHERE = 2, RT_HIT_PLANE = 3 };
+
+/* ParsingKit Material fields read by trace (Object+Extension.swift:105-274) */
+typedef struct rt_material {
+    int32_t type;
+    int32_t reserved;
+    double ambient[3], diffuse[3], specular[3], mirror[3], absorption[3];
+    double phong, ior, absorptionIndex, roughness;
+} rt_material;
+
+typedef struct rt_point_light { double position[3], intensity[3]; } rt_point_light;       /* :118-140 */
+typedef struct rt_area_light { double position[3], normal[3], size, radiance[3]; } rt_area_light; /* :145-186 */
+typedef struct rt_sphere { double center[3], radius; } rt_sphere;                         /* RTContext.swift:513-527 */
+typedef struct rt_plane { double center[3], normal[3]; } rt_plane;                         /* RTContext.swift:530-538 */
+
+/* PrimitiveInfo (BVH.swift:42-64) minus bounds/centroid, which are recomputed */
+typedef struct rt_prim {
+    int32_t type;            /* RT_GEO_TRIANGLE / SPHERE / PLANE */
+    int32_t smooth;          /* ShadingMode: 0 flat, 1 smooth */
+    int64_t primitiveIndex;  /* into triangles / spheres / planes */
+    int64_t materialID;
+} rt_prim;
+
+/* BLAS.prims (RTContext.swift:34-42): a contiguous range of rt_scene_desc.prims.
+ * The reference's own BVH nodes are NOT passed: the module builds its GPU layout itself. */
+typedef struct rt_blas { int64_t firstPrim, primCount; } rt_blas;
+
+/* Instance (RTContext.swift:43-61) */
+typedef struct rt_instance {
+    int32_t blas;                 /* index into rt_scene_desc.blas */
+    int32_t hasMaterialOverride;  /* materialOverride != nil */
+    int64_t materialOverride;
+    double localToWorld[16], worldToLocal[16];
+    double normalMatrix[9];       /* simd_double3x3, column-major */
+    double worldBounds[6];        /* minP, maxP (Instance.worldBounds) */
+    double instanceMotion[3];
+} rt_instance;
+
+/* Flattened RTContext + the Scene fields trace reads (Object+Extension.swift:88,97,102,116) */
+typedef struct rt_scene_desc {
+    uint32_t abiVersion;          /* RT_ABI_VERSION */
+    uint32_t reserved;
+    int64_t nTriangles;
+    const double* triVertices;    /* nTriangles*9: v0,v1,v2 (Triangle.v0/v1/v2) */
+    const double* triNormals;     /* nTriangles*9: n0,n1,n2 */
+    const double* triMotionBlur;  /* nTriangles*3 or NULL (all zero) */
+    int64_t nSpheres;  const rt_sphere* spheres;
+    int64_t nPlanes;   const rt_plane* planes;
+    int64_t nPrims;    const rt_prim* prims;
+    int64_t nBlas;     const rt_blas* blas;
+    int64_t nInstances; const rt_instance* instances;
+    int64_t nMaterials; const rt_material* materials;
+    int64_t nPointLights; const rt_point_light* pointLights;
+    int64_t nAreaLights;  const rt_area_light* areaLights;
+    double ambient[3];            /* scene.lights.ambient */
+    double background[3];         /* scene.backgroundColor */
+    double intersectionTestEpsilon, shadowRayEpsilon;
+    int32_t maxRecursionDepth;
+    int32_t reserved2;
+} rt_scene_desc;
+
+/* ParsingKit Camera fields read by render/makeCameraBasis (Object+Extension.swift:58-63,385-425) */
+typedef struct rt_camera {
+    int32_t width, height;        /* imageResolution */
+    int32_t numSamples;
+    int32_t isLookAt;             /* type?.lowercased() == "lookat" */
+    int32_t hasFovy;
+    int32_t reserved;
+    double position[3], gaze[3], gazePoint[3], up[3];
+    double nearPlane[4];          /* l, r, b, t */
+    double nearDistance, fovy;
+    double apertureSize, focusDistance;
+} rt_camera;
+
+/* progress: rows finished so far (multiples of the 8-row chunk of Object+Extension.swift:75);
+ * return non-zero to cancel (RayTracer.swift:178-180) */
+typedef int (*rt_progress_fn)(int32_t rowsDone, int32_t rowsTotal, void* user);
+
+typedef struct rt_render_params {
+    /* 8-row chunks c with c % shardCount == shardIndex are rendered; other rows are left untouched.
+     * shardCount <= 1 renders the whole frame.  (Multi-process sharding: one rank per GPU.) */
+    int32_t shardIndex, shardCount;
+    int32_t collectCounters;      /* 1: also fill rt_stats box/primitive test counts (slower kernel variant) */
+    int32_t reserved;
+    rt_progress_fn progress;      /* may be NULL */
+    void* progressUser;
+} rt_render_params;
+
+/* identity of one primary ray's closest hit (the reference's Hit has no primitive id) */
+typedef struct rt_hit_id {
+    int32_t inst;                 /* instance index, -1 = miss */
+    int32_t kind;                 /* RT_HIT_* */
+    int64_t prim;                 /* primitiveIndex within its kind's array, -1 = miss */
+    double t;
+} rt_hit_id;
+
+/* RenderStats (Models/RenderStats.swift:8-23) plus the ray counts the reference never fills (RayTracer.swift:168) */
+typedef struct rt_stats {
+    int64_t meshes, triangles, spheres, planes;
+    int64_t rays;                 /* raysPrimary + raysShadow + raysSecondary */
+    int64_t milliseconds;         /* wall clock of the call, like RenderStats.milliseconds */
+    int64_t raysPrimary, raysShadow, raysSecondary;
+    double deviceMs;              /* CUDA-event time of the render kernels */
+    int64_t kernelLaunches;       /* kernels launched by this call */
+    /* only with collectCounters: */
+    int64_t boxTests, triTests, sphereTests, planeTests, instEntries, maxStack;
+} rt_stats;
+
+typedef struct rt_scene_info {
+    int64_t triangles, spheres, planes, instances, blasCount;
+    int64_t blasNodes, tlasNodes, maxLeafSize, maxDepth;
+    int64_t deviceBytes;
+    double buildMs, uploadMs;
+    int32_t device;
+    int32_t reserved;
+} rt_scene_info;
+
+typedef struct rt_scene rt_scene_t;
+
+int32_t rt_abi_version(void);
+int32_t rt_device_count(void);
+const char* rt_last_error(void);
+
+/* Build the GPU acceleration structures from the flattened context and upload them to `device`.
+ * Replaces what Renderer.init(ctx:) keeps (Object+Extension.swift:13-19).  NULL on failure. */
+rt_scene_t* rt_scene_create(const rt_scene_desc* desc, int32_t device);
+void rt_scene_destroy(rt_scene_t* scene);
+int32_t rt_scene_get_info(const rt_scene_t* scene, rt_scene_info* out);
+
+/* Render one camera.  Blocking.  Host buffers, all optional except one of rgbaOut/linearOut:
+ *   rgbaOut   width*height*4 bytes, row 0 = top (RayTracer.swift:186-195)
+ *   linearOut width*height*3 doubles, the [Vec3] Renderer.render returns (0..255 scale)
+ *   idsOut    width*height*n*n records, n = floor(sqrt(max(1,numSamples)))
+ * Device->host copies are part of the call. */
+int32_t rt_render(rt_scene_t* scene, const rt_camera* camera, const rt_render_params* params, uint8_t* rgbaOut,
+                  double* linearOut, rt_hit_id* idsOut, rt_stats* statsOut);
+
+/* Same, but outputs stay in DEVICE memory owned by the caller (pointers valid on the scene's device)
+ * and the launch is enqueued on `cudaStream` (a cudaStream_t, NULL = default stream) without
+ * synchronising; statsOut->deviceMs and ray counts are filled by rt_render_finish(). */
+int32_t rt_render_device(rt_scene_t* scene, const rt_camera* camera, const rt_render_params* params,
+                         void* dRgbaOut, void* dLinearOut, void* dIdsOut, void* cudaStream);
+int32_t rt_render_finish(rt_scene_t* scene, rt_stats* statsOut);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTCUDA_H */

@@ -1,0 +1,44 @@
+/*
+ * rtcuda_host.h — C surface of the C++ host-side mirror (myraytracer_b200/host):
+ * RayTracerEngine (Sources/RayTracer/RayTracer.swift:25-205) over the render module of rtcuda.h.
+ * Exists because the Swift toolchain is absent: Python tests and bench.py drive the mirror
+ * through these calls exactly as Swift code would drive RayTracerEngine.
+ */
+#ifndef RTCUDA_HOST_H
+#define RTCUDA_HOST_H
+
+#include "rtcuda.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rth_engine rth_engine_t;    /* RayTracerEngine */
+typedef struct rth_context rth_context_t;  /* Scene + RTContext(scene:) without a renderer (no GPU needed) */
+
+const char* rth_last_error(void);
+
+/* RayTracerEngine.init(from:) — RayTracer.swift:30-49.  Never NULL unless out of memory: like the
+ * reference, a scene that fails to decode leaves an empty engine (rth_engine_ready() == 0). */
+rth_engine_t* rth_engine_create(const char* sceneUrl, int32_t device);
+void rth_engine_destroy(rth_engine_t* engine);
+int32_t rth_engine_ready(const rth_engine_t* engine);
+int32_t rth_engine_camera_count(const rth_engine_t* engine);
+int32_t rth_engine_camera(const rth_engine_t* engine, int32_t cameraIndex, rt_camera* out);
+rt_scene_t* rth_engine_scene(const rth_engine_t* engine);
+int32_t rth_engine_describe(const rth_engine_t* engine, rt_scene_desc* out);
+int32_t rth_engine_instance_object_ids(const rth_engine_t* engine, int32_t* out, int64_t capacity);
+
+/* RayTracerEngine.render(format:cameraIndex:progress:) — RayTracer.swift:115-131; error codes
+ * -20 / -21 / -10 as the reference's NSErrors (:142-154). */
+int32_t rth_engine_render(rth_engine_t* engine, int32_t cameraIndex, const rt_render_params* params, uint8_t* rgbaOut,
+                          double* linearOut, rt_hit_id* idsOut, rt_stats* statsOut);
+
+rth_context_t* rth_context_create(const char* sceneUrl);
+void rth_context_destroy(rth_context_t* ctx);
+int32_t rth_context_describe(const rth_context_t* ctx, rt_scene_desc* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTCUDA_HOST_H */

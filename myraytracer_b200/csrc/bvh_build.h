@@ -1,0 +1,49 @@
+// bvh_build.h — host-side builder of the GPU BLAS layout (gpu_layout.h).
+//
+// Takes over the role of the reference's BVHBuilder for meshes
+// (Accelearion/BVH.swift:78-250, called from RTContext.swift:430-435) but is a
+// different tree: binned SAH with a leaf-cost termination and up to 4
+// triangles per leaf, children boxes stored in the parent, FP32 boxes relative
+// to the BLAS centre, padded + rounded outward (conservative), triangles
+// re-ordered into leaf order.  Closest-hit results do not depend on the tree
+// (SURVEY.md §7.3-4): only equal-t ties may resolve differently.
+#pragma once
+#include <cstdint>
+#include <vector>
+
+#include "gpu_layout.h"
+
+namespace rtg {
+
+struct BlasBuildInput {
+    const double* triVertices;      // global array, 9 doubles per triangle
+    const int64_t* triIndices;      // triangles of this BLAS (global indices), in prim order
+    int64_t count;
+    double motionBlur[3];           // box growth for Triangle.motionBlur (RTContext.swift:283-289)
+    int threads;                    // 0 = hardware concurrency
+};
+
+struct BlasBuildOutput {
+    std::vector<GNode> nodes;       // inner nodes, node 0 = root when rootRef == 0
+    std::vector<GTri> tris;         // leaf order (when !f64)
+    std::vector<GTriD> trisD;       // leaf order (when f64)
+    bool f64 = false;
+    int32_t rootRef = kEmptyRef;
+    double rootLo[3], rootHi[3];    // exact FP64 bounds (incl. motion blur growth)
+    double centre[3];
+    double pad = 0;                 // absolute padding applied to every FP32 box
+    int maxDepth = 0;
+    int maxLeaf = 0;
+};
+
+void buildBlas(const BlasBuildInput& in, BlasBuildOutput& out);
+
+// TLAS over instance world bounds (FP64, one instance per leaf).
+struct TlasBuildOutput {
+    std::vector<TNode> nodes;
+    int32_t rootRef = kEmptyRef;
+    int maxDepth = 0;
+};
+void buildTlas(const double* worldBounds /* n*6 */, int64_t n, TlasBuildOutput& out);
+
+}  // namespace rtg

@@ -1,0 +1,119 @@
+// gpu_layout.h — device-side data layout of the render module (shared by the
+// host builder and the CUDA kernels).
+//
+// Replaces the reference's runtime layout: 96-B FP64 AoS
+// BVHNode + primIdx -> 160-B PrimitiveInfo -> >=320-B Triangle
+// (Accelearion/BVH.swift:16-64, Models/RTContext.swift:34-92) with
+//   * GNode      64 B : one inner BLAS node holding BOTH children's FP32 boxes
+//                       (4 x 16-B vector loads, one 64-B aligned segment);
+//                       boxes are relative to the BLAS centre, padded and rounded
+//                       outward so the FP32 slab test is conservative;
+//   * GTri       48 B : float-exact vertices in BVH leaf order (no primIdx hop),
+//                       original triangle index in v0.w;  GTriD 80 B for meshes
+//                       whose vertices are not float-exact;
+//   * TNode     112 B : TLAS inner node, FP64 boxes = Instance.worldBounds unions
+//                       (the TLAS is tiny; FP64 keeps the reference's culling exact);
+//   * GInstance       : FP64 world<->local matrices, exact local root box, kind.
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define RT_ALIGN(n) __align__(n)
+#else
+#define RT_ALIGN(n) alignas(n)
+#endif
+
+namespace rtg {
+
+// Child reference: >= 0 inner node index (relative to the BLAS / TLAS node array);
+// < 0 leaf: ~ref = (first << 3) | (count - 1), count in 1..8; kEmptyRef = no child.
+static const int32_t kEmptyRef = 0x7fffffff;
+static const int kMaxLeaf = 4;
+
+struct RT_ALIGN(16) GNode {
+    // q0 = lo0.x lo0.y lo0.z hi0.x | q1 = hi0.y hi0.z lo1.x lo1.y | q2 = lo1.z hi1.x hi1.y hi1.z
+    float q0[4], q1[4], q2[4];
+    int32_t child0, child1, pad0, pad1;
+};
+
+struct RT_ALIGN(16) GTri {   // float-exact vertices (PLY meshes: Helpers/PLYReader.swift:85-101)
+    float v0[3]; int32_t triIndex;
+    float v1[3]; int32_t pad1;
+    float v2[3]; int32_t pad2;
+};
+
+struct RT_ALIGN(16) GTriD {  // FP64 vertices
+    double v0[3], v1[3], v2[3];
+    int64_t triIndex;
+};
+
+struct RT_ALIGN(16) TNode {
+    double lo0[3], hi0[3], lo1[3], hi1[3];
+    int32_t child0, child1, pad0, pad1;  // leaf: ~ref = instance index (one instance per leaf)
+};
+
+enum InstKind : int32_t { INST_MESH = 0, INST_SPHERE = 2, INST_PLANE = 3, INST_TRI = 1 };
+
+struct RT_ALIGN(16) GInstance {
+    double w2l[12];        // rows 0..2 of worldToLocal, column-major 3x4: w2l[c*3+r], c = 0..3
+    double l2w[12];        // same for localToWorld
+    double nmat[9];        // normalMatrix, column-major
+    double rootLo[3], rootHi[3];  // exact local-space bounds (= the reference's BLAS root node box)
+    double centre[3];      // BLAS box centre the FP32 node boxes are relative to
+    double motion[3];      // instanceMotion
+    double prim[8];        // analytic payload: sphere c.xyz,r | plane c.xyz,n.xyz | unused for meshes
+    int64_t matId;         // hit.mat value (materialOverride ?? primitive materialID)
+    int64_t primIndex;     // analytic: primitiveIndex; mesh: unused
+    int32_t kind;          // InstKind
+    int32_t identity;      // 1: worldToLocal is exactly the identity (skip the transform)
+    int32_t flipNormal;    // det(localToWorld 3x3) < 0  (RTContext.swift:691-698)
+    int32_t smooth;        // mesh shading mode
+    int32_t nodeBase;      // first GNode of this BLAS in the global node array
+    int32_t triBase;       // first GTri/GTriD slot of this BLAS
+    int32_t triF64;        // 1: GTriD array, 0: GTri array
+    int32_t rootRef;       // child reference of the BLAS root (inner node 0 or a leaf)
+    int32_t hasMotion;     // instanceMotion != 0 or mesh motion blur != 0
+    int32_t pad[3];
+    double meshMotion[3];  // Triangle.motionBlur of this mesh
+    double pad2;
+};
+
+struct GMaterial {
+    double ambient[3], diffuse[3], specular[3], mirror[3], absorption[3];
+    double phong, ior, absorptionIndex, roughness;
+    int32_t type, hasAbsorption;
+};
+
+struct GPointLight { double position[3], intensity[3]; };
+
+// Everything the kernels read, passed by value as a kernel parameter.
+struct DeviceScene {
+    const GNode* nodes;
+    const GTri* tris;
+    const GTriD* trisD;
+    const double* triNormals;      // original triangle index * 9
+    const double* triVertsD;       // original triangle index * 9 (FP64 v0,v1,v2; hit point / flat normal)
+    const TNode* tlas;
+    const GInstance* instances;
+    const GMaterial* materials;
+    const GPointLight* pointLights;
+    int32_t tlasRootRef;
+    int32_t nInstances, nMaterials, nPointLights;
+    int32_t maxDepth;
+    int32_t pad;
+    double ambient[3], background[3];
+    double eps, shadowEps;
+};
+
+struct CameraParams {
+    double eye[3], u[3], v[3], w[3];
+    double q00[3], m[3];          // q00 = m + u*l + v*t ; m = eye - w*nd
+    double du, dv;
+    double aperture, focus;
+    int32_t width, height, samples, n;  // n = floor(sqrt(samples))
+    int32_t dof;
+    int32_t shardIndex, shardCount;
+    int32_t pad;
+};
+
+}  // namespace rtg

@@ -1,0 +1,305 @@
+// rt_api.cu — implementation of the C ABI declared in include/rtcuda.h.
+//
+// rt_scene_create : flattened RTContext (Models/RTContext.swift:74-92) -> GPU layout
+//                   (replaces BVHBuilder for meshes, Accelearion/BVH.swift:78-250, and buildTLAS,
+//                   RTContext.swift:459-474, with the builders of bvh_build.cpp)
+// rt_render       : Renderer.render (Extensions/Object+Extension.swift:52-379) + RGBA8 conversion
+//                   (RayTracer.swift:186-195); camera set-up = makeCameraBasis (:382-427) on the host.
+// There is no CPU fallback: without a CUDA device every entry point fails with RT_ERR_CUDA.
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/rtcuda.h"
+#include "bvh_build.h"
+#include "rt_kernels.h"
+
+using namespace rtg;
+
+namespace {
+
+thread_local std::string g_err;
+int fail(int code, const std::string& msg) { g_err = msg; return code; }
+
+#define CK(call)                                                                                       \
+    do {                                                                                               \
+        cudaError_t e_ = (call);                                                                       \
+        if (e_ != cudaSuccess) {                                                                       \
+            g_err = std::string(#call) + ": " + cudaGetErrorString(e_);                                \
+            return RT_ERR_CUDA;                                                                        \
+        }                                                                                              \
+    } while (0)
+
+template <class T>
+int upload(const std::vector<T>& v, T** d, int64_t& bytes) {
+    *d = nullptr;
+    size_t n = v.size() * sizeof(T);
+    CK(cudaMalloc((void**)d, n ? n : 16));
+    if (n) CK(cudaMemcpy(*d, v.data(), n, cudaMemcpyHostToDevice));
+    bytes += (int64_t)n;
+    return RT_OK;
+}
+
+double nowMs() {
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+bool isIdentity34(const double* m16) {
+    for (int c = 0; c < 4; c++)
+        for (int r = 0; r < 4; r++)
+            if (m16[c * 4 + r] != ((c == r) ? 1.0 : 0.0)) return false;
+    return true;
+}
+
+}  // namespace
+
+struct rt_scene {
+    int device = 0;
+    DeviceScene ds{};
+    rt_scene_info info{};
+    int64_t meshes = 0;
+    // device allocations
+    GNode* dNodes = nullptr; GTri* dTris = nullptr; GTriD* dTrisD = nullptr; double* dNormals = nullptr;
+    TNode* dTlas = nullptr; GInstance* dInst = nullptr; GMaterial* dMat = nullptr; GPointLight* dLights = nullptr;
+    // render state (re-used across calls)
+    int* dTileCounter = nullptr; unsigned long long* dCounters = nullptr;
+    double* dPathStack = nullptr; size_t pathStackBytes = 0;
+    uint8_t* dRgba = nullptr; size_t rgbaBytes = 0;
+    double* dLinear = nullptr; size_t linearBytes = 0;
+    HitId* dIds = nullptr; size_t idsBytes = 0;
+    unsigned long long* hCounters = nullptr;  // pinned
+    cudaEvent_t evStart = nullptr, evStop = nullptr;
+    int blocks = 0, blocksCounters = 0;
+    bool pending = false; bool pendingCounters = false;
+    cudaStream_t pendingStream = nullptr;
+    int64_t launches = 0;
+};
+
+extern "C" {
+
+int32_t rt_abi_version(void) { return RT_ABI_VERSION; }
+
+int32_t rt_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+const char* rt_last_error(void) { return g_err.c_str(); }
+
+static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
+    if (!d) return fail(RT_ERR_INVALID, "null scene description");
+    if (d->abiVersion != RT_ABI_VERSION) return fail(RT_ERR_INVALID, "rt_scene_desc.abiVersion mismatch");
+    if (d->nMaterials < 1 || !d->materials) return fail(RT_ERR_INVALID, "at least one material is required");
+    if (d->nAreaLights > 0)
+        return fail(RT_ERR_UNSUPPORTED, "area lights are not implemented on the GPU path yet (SURVEY.md §8f row 3)");
+    if (d->triMotionBlur)
+        for (int64_t i = 0; i < d->nTriangles * 3; i++)
+            if (d->triMotionBlur[i] != 0.0) return fail(RT_ERR_UNSUPPORTED, "motion blur is not implemented on the GPU path yet");
+    int ndev = 0;
+    CK(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail(RT_ERR_INVALID, "invalid CUDA device index");
+    CK(cudaSetDevice(device));
+    sc->device = device;
+    const double t0 = nowMs();
+
+    // ---- BLAS build (one per rt_blas, shared by instances)
+    struct BlasInfo {
+        int kind = INST_MESH; int64_t prim = 0; int64_t matId = 0; int smooth = 0;
+        int32_t nodeBase = 0, triBase = 0, rootRef = kEmptyRef; int f64 = 0;
+        double lo[3], hi[3], centre[3];
+    };
+    std::vector<BlasInfo> blasInfo((size_t)d->nBlas);
+    std::vector<GNode> nodes;
+    std::vector<GTri> tris;
+    std::vector<GTriD> trisD;
+    int64_t maxDepth = 0, maxLeaf = 0;
+    for (int64_t b = 0; b < d->nBlas; b++) {
+        const rt_blas& bl = d->blas[b];
+        BlasInfo& bi = blasInfo[b];
+        if (bl.primCount < 1 || bl.firstPrim < 0 || bl.firstPrim + bl.primCount > d->nPrims)
+            return fail(RT_ERR_INVALID, "rt_blas range outside prims");
+        const rt_prim* pr = d->prims + bl.firstPrim;
+        bi.matId = pr[0].materialID;
+        bi.smooth = pr[0].smooth;
+        if (bl.primCount == 1 && pr[0].type == RT_GEO_SPHERE) {
+            if (pr[0].primitiveIndex < 0 || pr[0].primitiveIndex >= d->nSpheres) return fail(RT_ERR_INVALID, "sphere index out of range");
+            const rt_sphere& s = d->spheres[pr[0].primitiveIndex];
+            bi.kind = INST_SPHERE; bi.prim = pr[0].primitiveIndex;
+            for (int a = 0; a < 3; a++) { bi.lo[a] = s.center[a] - s.radius; bi.hi[a] = s.center[a] + s.radius; bi.centre[a] = s.center[a]; }
+            continue;
+        }
+        if (bl.primCount == 1 && pr[0].type == RT_GEO_PLANE) {
+            if (pr[0].primitiveIndex < 0 || pr[0].primitiveIndex >= d->nPlanes) return fail(RT_ERR_INVALID, "plane index out of range");
+            bi.kind = INST_PLANE; bi.prim = pr[0].primitiveIndex;
+            for (int a = 0; a < 3; a++) { bi.lo[a] = -1e5; bi.hi[a] = 1e5; bi.centre[a] = 0; }  // RTContext.swift:172-174
+            continue;
+        }
+        std::vector<int64_t> idx((size_t)bl.primCount);
+        for (int64_t k = 0; k < bl.primCount; k++) {
+            if (pr[k].type != RT_GEO_TRIANGLE) return fail(RT_ERR_UNSUPPORTED, "a multi-primitive BLAS must hold triangles only");
+            if (pr[k].primitiveIndex < 0 || pr[k].primitiveIndex >= d->nTriangles) return fail(RT_ERR_INVALID, "triangle index out of range");
+            if (pr[k].materialID != bi.matId || pr[k].smooth != bi.smooth)
+                return fail(RT_ERR_UNSUPPORTED, "per-triangle material / shading mode inside one BLAS");
+            idx[k] = pr[k].primitiveIndex;
+        }
+        BlasBuildInput in{};
+        in.triVertices = d->triVertices; in.triIndices = idx.data(); in.count = bl.primCount; in.threads = 0;
+        BlasBuildOutput out;
+        buildBlas(in, out);
+        if (out.maxDepth > renderStackCapacity() - 2) return fail(RT_ERR_UNSUPPORTED, "BLAS deeper than the traversal stack");
+        bi.kind = bl.primCount == 1 ? INST_TRI : INST_MESH;
+        bi.prim = pr[0].primitiveIndex;
+        bi.f64 = out.f64 ? 1 : 0;
+        bi.nodeBase = (int32_t)nodes.size();
+        bi.triBase = (int32_t)(out.f64 ? trisD.size() : tris.size());
+        bi.rootRef = out.rootRef;
+        std::memcpy(bi.lo, out.rootLo, 24); std::memcpy(bi.hi, out.rootHi, 24); std::memcpy(bi.centre, out.centre, 24);
+        nodes.insert(nodes.end(), out.nodes.begin(), out.nodes.end());
+        if (out.f64) trisD.insert(trisD.end(), out.trisD.begin(), out.trisD.end());
+        else tris.insert(tris.end(), out.tris.begin(), out.tris.end());
+        if (out.maxDepth > maxDepth) maxDepth = out.maxDepth;
+        if (out.maxLeaf > maxLeaf) maxLeaf = out.maxLeaf;
+        if (bi.kind == INST_MESH) sc->meshes++;
+    }
+
+    // ---- instances
+    std::vector<GInstance> inst((size_t)d->nInstances);
+    std::vector<double> wb((size_t)d->nInstances * 6);
+    for (int64_t i = 0; i < d->nInstances; i++) {
+        const rt_instance& in = d->instances[i];
+        if (in.blas < 0 || in.blas >= d->nBlas) return fail(RT_ERR_INVALID, "rt_instance.blas out of range");
+        if (in.instanceMotion[0] != 0 || in.instanceMotion[1] != 0 || in.instanceMotion[2] != 0)
+            return fail(RT_ERR_UNSUPPORTED, "instance motion blur is not implemented on the GPU path yet");
+        const BlasInfo& bi = blasInfo[in.blas];
+        GInstance& g = inst[i];
+        std::memset(&g, 0, sizeof g);
+        for (int c = 0; c < 4; c++)
+            for (int r = 0; r < 3; r++) { g.w2l[c * 3 + r] = in.worldToLocal[c * 4 + r]; g.l2w[c * 3 + r] = in.localToWorld[c * 4 + r]; }
+        std::memcpy(g.nmat, in.normalMatrix, sizeof g.nmat);
+        std::memcpy(g.rootLo, bi.lo, 24); std::memcpy(g.rootHi, bi.hi, 24); std::memcpy(g.centre, bi.centre, 24);
+        g.kind = bi.kind;
+        g.identity = (isIdentity34(in.worldToLocal) && isIdentity34(in.localToWorld)) ? 1 : 0;
+        // simd_determinant of the upper 3x3 (RTContext.swift:691-698), same expansion as the oracle
+        const double* m = in.localToWorld;
+        const double c0[3] = {m[0], m[1], m[2]}, c1[3] = {m[4], m[5], m[6]}, c2[3] = {m[8], m[9], m[10]};
+        const double cx = c1[1] * c2[2] - c1[2] * c2[1], cy = c1[2] * c2[0] - c1[0] * c2[2], cz = c1[0] * c2[1] - c1[1] * c2[0];
+        g.flipNormal = ((c0[0] * cx + c0[1] * cy) + c0[2] * cz) < 0.0 ? 1 : 0;
+        g.smooth = bi.smooth;
+        g.nodeBase = bi.nodeBase; g.triBase = bi.triBase; g.triF64 = bi.f64; g.rootRef = bi.rootRef;
+        g.matId = in.hasMaterialOverride ? in.materialOverride : bi.matId;  // RTContext.swift:704
+        g.primIndex = bi.prim;
+        if (bi.kind == INST_SPHERE) { const rt_sphere& s = d->spheres[bi.prim]; g.prim[0] = s.center[0]; g.prim[1] = s.center[1]; g.prim[2] = s.center[2]; g.prim[3] = s.radius; }
+        if (bi.kind == INST_PLANE) { const rt_plane& p = d->planes[bi.prim]; for (int a = 0; a < 3; a++) { g.prim[a] = p.center[a]; g.prim[3 + a] = p.normal[a]; } }
+        std::memcpy(&wb[i * 6], in.worldBounds, 48);
+    }
+    TlasBuildOutput tl;
+    buildTlas(wb.data(), d->nInstances, tl);
+    if (tl.maxDepth > 38) return fail(RT_ERR_UNSUPPORTED, "TLAS deeper than the TLAS stack");
+
+    // ---- materials / lights
+    std::vector<GMaterial> mats((size_t)d->nMaterials);
+    for (int64_t i = 0; i < d->nMaterials; i++) {
+        const rt_material& m = d->materials[i];
+        GMaterial& g = mats[i];
+        std::memcpy(g.ambient, m.ambient, 24); std::memcpy(g.diffuse, m.diffuse, 24); std::memcpy(g.specular, m.specular, 24);
+        std::memcpy(g.mirror, m.mirror, 24); std::memcpy(g.absorption, m.absorption, 24);
+        g.phong = m.phong; g.ior = m.ior; g.absorptionIndex = m.absorptionIndex; g.roughness = m.roughness;
+        g.type = (m.type >= RT_MAT_MIRROR && m.type <= RT_MAT_CONDUCTOR) ? m.type : RT_MAT_PLAIN;
+        g.hasAbsorption = (m.absorption[0] != 0 || m.absorption[1] != 0 || m.absorption[2] != 0) ? 1 : 0;
+    }
+    std::vector<GPointLight> lights((size_t)d->nPointLights);
+    for (int64_t i = 0; i < d->nPointLights; i++) {
+        std::memcpy(lights[i].position, d->pointLights[i].position, 24);
+        std::memcpy(lights[i].intensity, d->pointLights[i].intensity, 24);
+    }
+    std::vector<double> normals;
+    if (d->nTriangles > 0) {
+        if (!d->triVertices || !d->triNormals) return fail(RT_ERR_INVALID, "triangle arrays missing");
+        normals.assign(d->triNormals, d->triNormals + d->nTriangles * 9);
+    }
+    const double t1 = nowMs();
+
+    // ---- upload
+    int64_t bytes = 0;
+    int rc;
+    if ((rc = upload(nodes, &sc->dNodes, bytes))) return rc;
+    if ((rc = upload(tris, &sc->dTris, bytes))) return rc;
+    if ((rc = upload(trisD, &sc->dTrisD, bytes))) return rc;
+    if ((rc = upload(normals, &sc->dNormals, bytes))) return rc;
+    if ((rc = upload(tl.nodes, &sc->dTlas, bytes))) return rc;
+    if ((rc = upload(inst, &sc->dInst, bytes))) return rc;
+    if ((rc = upload(mats, &sc->dMat, bytes))) return rc;
+    if ((rc = upload(lights, &sc->dLights, bytes))) return rc;
+    CK(cudaMalloc((void**)&sc->dTileCounter, 64));
+    CK(cudaMalloc((void**)&sc->dCounters, 16 * sizeof(unsigned long long)));
+    CK(cudaMallocHost((void**)&sc->hCounters, 16 * sizeof(unsigned long long)));
+    CK(cudaEventCreate(&sc->evStart));
+    CK(cudaEventCreate(&sc->evStop));
+    CK(cudaDeviceSynchronize());
+    const double t2 = nowMs();
+
+    DeviceScene& S = sc->ds;
+    S.nodes = sc->dNodes; S.tris = sc->dTris; S.trisD = sc->dTrisD; S.triNormals = sc->dNormals; S.triVertsD = nullptr;
+    S.tlas = sc->dTlas; S.instances = sc->dInst; S.materials = sc->dMat; S.pointLights = sc->dLights;
+    S.tlasRootRef = tl.rootRef;
+    S.nInstances = (int32_t)d->nInstances; S.nMaterials = (int32_t)d->nMaterials; S.nPointLights = (int32_t)d->nPointLights;
+    S.maxDepth = d->maxRecursionDepth;
+    std::memcpy(S.ambient, d->ambient, 24); std::memcpy(S.background, d->background, 24);
+    S.eps = d->intersectionTestEpsilon; S.shadowEps = d->shadowRayEpsilon;
+
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    int bps = 0;
+    CK(renderOccupancy(&bps, false));
+    sc->blocks = prop.multiProcessorCount * (bps > 0 ? bps : 1);
+    CK(renderOccupancy(&bps, true));
+    sc->blocksCounters = prop.multiProcessorCount * (bps > 0 ? bps : 1);
+
+    rt_scene_info& I = sc->info;
+    I.triangles = d->nTriangles; I.spheres = d->nSpheres; I.planes = d->nPlanes; I.instances = d->nInstances; I.blasCount = d->nBlas;
+    I.blasNodes = (int64_t)nodes.size(); I.tlasNodes = (int64_t)tl.nodes.size(); I.maxLeafSize = maxLeaf; I.maxDepth = maxDepth;
+    I.deviceBytes = bytes; I.buildMs = t1 - t0; I.uploadMs = t2 - t1; I.device = device;
+    return RT_OK;
+}
+
+void rt_scene_destroy(rt_scene_t* sc) {
+    if (!sc) return;
+    cudaSetDevice(sc->device);
+    cudaFree(sc->dNodes); cudaFree(sc->dTris); cudaFree(sc->dTrisD); cudaFree(sc->dNormals); cudaFree(sc->dTlas);
+    cudaFree(sc->dInst); cudaFree(sc->dMat); cudaFree(sc->dLights); cudaFree(sc->dTileCounter); cudaFree(sc->dCounters);
+    cudaFree(sc->dPathStack); cudaFree(sc->dRgba); cudaFree(sc->dLinear); cudaFree(sc->dIds);
+    if (sc->hCounters) cudaFreeHost(sc->hCounters);
+    if (sc->evStart) cudaEventDestroy(sc->evStart);
+    if (sc->evStop) cudaEventDestroy(sc->evStop);
+    delete sc;
+}
+
+rt_scene_t* rt_scene_create(const rt_scene_desc* desc, int32_t device) {
+    rt_scene* sc = nullptr;
+    try {
+        sc = new rt_scene();
+        int rc = createImpl(desc, device, sc);
+        if (rc != RT_OK) { rt_scene_destroy(sc); return nullptr; }
+        return sc;
+    } catch (const std::exception& e) {
+        g_err = e.what();
+    } catch (...) {
+        g_err = "unknown exception";
+    }
+    if (sc) rt_scene_destroy(sc);
+    return nullptr;
+}
+
+int32_t rt_scene_get_info(const rt_scene_t* sc, rt_scene_info* out) {
+    if (!sc || !out) return fail(RT_ERR_NO_SCENE, "No scene loaded. Can't render.");
+    *out = sc->info;
+    return RT_OK;
+}
+
+}  // extern "C"
+
+#include "rt_api_render.inl"

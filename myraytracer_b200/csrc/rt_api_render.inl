@@ -1,0 +1,170 @@
+// rt_api_render.inl — render entry points (included by rt_api.cu).
+
+namespace {
+
+struct H3 { double x, y, z; };
+inline H3 h3(const double* p) { return {p[0], p[1], p[2]}; }
+inline H3 operator-(H3 a, H3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+inline H3 operator+(H3 a, H3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+inline H3 operator*(H3 a, double s) { return {a.x * s, a.y * s, a.z * s}; }
+inline H3 neg(H3 a) { return {-a.x, -a.y, -a.z}; }
+inline double hdot(H3 a, H3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+inline H3 hcross(H3 a, H3 b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+inline H3 hnorm(H3 a) { return a * (1.0 / std::sqrt(hdot(a, a))); }
+inline void put(double* d, H3 v) { d[0] = v.x; d[1] = v.y; d[2] = v.z; }
+
+// makeCameraBasis (Object+Extension.swift:382-427) + du, dv, m, q00 (:67-70)
+int buildCamera(const rt_camera* c, const rt_render_params* prm, CameraParams& cp) {
+    std::memset(&cp, 0, sizeof cp);
+    const int W = c->width > 1 ? c->width : 1, H = c->height > 1 ? c->height : 1;  // max(1, ...) :62-63
+    const double aspect = (double)W / (double)H;
+    const H3 e = h3(c->position);
+    const double nd = c->nearDistance;
+    double l, r, b, t;
+    H3 w, u, v;
+    if (c->isLookAt) {
+        const H3 gazeNorm = hnorm(h3(c->gazePoint) - h3(c->position));
+        w = neg(gazeNorm);
+        const H3 upNorm = hnorm(h3(c->up));
+        u = hnorm(hcross(upNorm, w));
+        v = hnorm(hcross(w, u));
+        if (c->hasFovy) {
+            const double fovYRad = (c->fovy * M_PI) / (2.0 * 180.0);
+            t = nd * std::tan(fovYRad);
+        } else {
+            t = nd * 0.5;
+        }
+        b = -t; r = t * aspect; l = -r;
+    } else {
+        l = c->nearPlane[0]; r = c->nearPlane[1]; b = c->nearPlane[2]; t = c->nearPlane[3];
+        const H3 gazeNorm = hnorm(h3(c->gaze));
+        w = neg(gazeNorm);
+        const H3 upNorm = hnorm(h3(c->up));
+        u = hnorm(hcross(upNorm, w));
+        v = hnorm(hcross(w, u));
+    }
+    const H3 m = e - w * nd;
+    const H3 q00 = (m + u * l) + v * t;
+    put(cp.eye, e); put(cp.u, u); put(cp.v, v); put(cp.w, w); put(cp.q00, q00); put(cp.m, m);
+    cp.du = (r - l) / (double)W;
+    cp.dv = (t - b) / (double)H;
+    cp.aperture = c->apertureSize; cp.focus = c->focusDistance;
+    cp.dof = (c->apertureSize > 0 && c->focusDistance > 0) ? 1 : 0;
+    cp.width = W; cp.height = H;
+    cp.samples = c->numSamples > 1 ? c->numSamples : 1;
+    cp.n = (int)std::sqrt((double)cp.samples);
+    cp.shardIndex = 0; cp.shardCount = 1;
+    if (prm && prm->shardCount > 1) {
+        if (prm->shardIndex < 0 || prm->shardIndex >= prm->shardCount) return fail(RT_ERR_INVALID, "shardIndex outside [0, shardCount)");
+        cp.shardIndex = prm->shardIndex; cp.shardCount = prm->shardCount;
+    }
+    return RT_OK;
+}
+
+template <class T>
+int ensure(T** p, size_t* have, size_t need) {
+    if (*have >= need && *p) return RT_OK;
+    if (*p) cudaFree(*p);
+    *p = nullptr; *have = 0;
+    CK(cudaMalloc((void**)p, need));
+    *have = need;
+    return RT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_render_params* params, void* dRgbaOut,
+                         void* dLinearOut, void* dIdsOut, void* cudaStream) {
+    if (!sc) return fail(RT_ERR_NO_SCENE, "No scene loaded. Can't render.");
+    if (!camera) return fail(RT_ERR_BAD_CAMERA, "Invalid camera index");
+    if (sc->pending) return fail(RT_ERR_INVALID, "a render is already in flight on this scene (call rt_render_finish)");
+    CK(cudaSetDevice(sc->device));
+    CameraParams cp;
+    int rc = buildCamera(camera, params, cp);
+    if (rc) return rc;
+    const bool counters = params && params->collectCounters;
+    const int blocks = counters ? sc->blocksCounters : sc->blocks;
+    cudaStream_t st = (cudaStream_t)cudaStream;
+
+    const size_t threads = (size_t)blocks * renderBlockSize();
+    const size_t need = (size_t)(sc->ds.maxDepth + 1) * kPathFields * threads * sizeof(double);
+    if ((rc = ensure(&sc->dPathStack, &sc->pathStackBytes, need))) return rc;
+
+    RenderTargets rt{};
+    rt.rgba = (uint8_t*)dRgbaOut; rt.linear = (double*)dLinearOut; rt.ids = (HitId*)dIdsOut;
+    rt.pathStack = sc->dPathStack; rt.tileCounter = sc->dTileCounter; rt.counters = sc->dCounters;
+    CK(cudaEventRecord(sc->evStart, st));
+    CK(cudaMemsetAsync(sc->dTileCounter, 0, 64, st));
+    CK(cudaMemsetAsync(sc->dCounters, 0, 16 * sizeof(unsigned long long), st));
+    CK(launchRender(sc->ds, cp, rt, blocks, counters, st));
+    CK(cudaMemcpyAsync(sc->hCounters, sc->dCounters, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    CK(cudaEventRecord(sc->evStop, st));
+    sc->pending = true; sc->pendingCounters = counters; sc->pendingStream = st;
+    sc->launches = 1;
+    return RT_OK;
+}
+
+int32_t rt_render_finish(rt_scene_t* sc, rt_stats* st) {
+    if (!sc) return fail(RT_ERR_NO_SCENE, "No scene loaded. Can't render.");
+    if (!sc->pending) return fail(RT_ERR_INVALID, "no render in flight");
+    CK(cudaSetDevice(sc->device));
+    sc->pending = false;
+    CK(cudaEventSynchronize(sc->evStop));
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, sc->evStart, sc->evStop));
+    if (st) {
+        std::memset(st, 0, sizeof *st);
+        st->meshes = sc->meshes; st->triangles = sc->info.triangles; st->spheres = sc->info.spheres; st->planes = sc->info.planes;
+        st->raysPrimary = (int64_t)sc->hCounters[0]; st->raysShadow = (int64_t)sc->hCounters[1];
+        st->raysSecondary = (int64_t)sc->hCounters[2];
+        st->rays = st->raysPrimary + st->raysShadow + st->raysSecondary;
+        st->deviceMs = ms;
+        st->kernelLaunches = sc->launches;
+        if (sc->pendingCounters) {
+            st->boxTests = (int64_t)sc->hCounters[3]; st->triTests = (int64_t)sc->hCounters[4];
+            st->sphereTests = (int64_t)sc->hCounters[5]; st->planeTests = (int64_t)sc->hCounters[6];
+            st->instEntries = (int64_t)sc->hCounters[7]; st->maxStack = (int64_t)sc->hCounters[8];
+        }
+    }
+    return RT_OK;
+}
+
+int32_t rt_render(rt_scene_t* sc, const rt_camera* camera, const rt_render_params* params, uint8_t* rgbaOut,
+                  double* linearOut, rt_hit_id* idsOut, rt_stats* statsOut) {
+    if (!sc) return fail(RT_ERR_NO_SCENE, "No scene loaded. Can't render.");
+    if (!camera) return fail(RT_ERR_BAD_CAMERA, "Invalid camera index");
+    if (!rgbaOut && !linearOut) return fail(RT_ERR_INVALID, "one of rgbaOut / linearOut is required");
+    const double w0 = nowMs();
+    CK(cudaSetDevice(sc->device));
+    const size_t W = camera->width > 1 ? camera->width : 1, H = camera->height > 1 ? camera->height : 1;
+    const int samples = camera->numSamples > 1 ? camera->numSamples : 1;
+    const size_t n = (size_t)std::sqrt((double)samples);
+    int rc;
+    if (rgbaOut && (rc = ensure(&sc->dRgba, &sc->rgbaBytes, W * H * 4))) return rc;
+    if (linearOut && (rc = ensure(&sc->dLinear, &sc->linearBytes, W * H * 3 * sizeof(double)))) return rc;
+    if (idsOut && (rc = ensure(&sc->dIds, &sc->idsBytes, W * H * n * n * sizeof(HitId)))) return rc;
+    // rows outside this rank's shard are defined as zero in the host buffers
+    const bool sharded = params && params->shardCount > 1;
+    if (sharded) {
+        if (rgbaOut) CK(cudaMemsetAsync(sc->dRgba, 0, W * H * 4, 0));
+        if (linearOut) CK(cudaMemsetAsync(sc->dLinear, 0, W * H * 3 * sizeof(double), 0));
+        if (idsOut) CK(cudaMemsetAsync(sc->dIds, 0, W * H * n * n * sizeof(HitId), 0));
+    }
+    if (params && params->progress && params->progress(0, (int32_t)H, params->progressUser)) return fail(RT_ERR_CANCELLED, "cancelled");
+    rc = rt_render_device(sc, camera, params, rgbaOut ? sc->dRgba : nullptr, linearOut ? sc->dLinear : nullptr,
+                          idsOut ? sc->dIds : nullptr, nullptr);
+    if (rc) return rc;
+    if (rgbaOut) CK(cudaMemcpyAsync(rgbaOut, sc->dRgba, W * H * 4, cudaMemcpyDeviceToHost, 0));
+    if (linearOut) CK(cudaMemcpyAsync(linearOut, sc->dLinear, W * H * 3 * sizeof(double), cudaMemcpyDeviceToHost, 0));
+    if (idsOut) CK(cudaMemcpyAsync(idsOut, sc->dIds, W * H * n * n * sizeof(HitId), cudaMemcpyDeviceToHost, 0));
+    rc = rt_render_finish(sc, statsOut);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(0));
+    if (statsOut) statsOut->milliseconds = (int64_t)(nowMs() - w0);
+    if (params && params->progress) params->progress((int32_t)H, (int32_t)H, params->progressUser);
+    return RT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,33 @@
+// rt_kernels.h — host-visible interface of rt_kernels.cu.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "gpu_layout.h"
+
+namespace rtg {
+
+struct HitId {  // same layout as rt_hit_id (include/rtcuda.h)
+    int32_t inst, kind;
+    int64_t prim;
+    double t;
+};
+
+struct RenderTargets {
+    uint8_t* rgba;                 // W*H*4 or null
+    double* linear;                // W*H*3 or null
+    HitId* ids;                    // W*H*n*n or null
+    double* pathStack;             // (maxDepth+1) * PATH_FIELDS * totalThreads doubles
+    int* tileCounter;              // zeroed before launch
+    unsigned long long* counters;  // 16 x u64, zeroed before launch
+};
+
+static const int kPathFields = 11;
+
+cudaError_t launchRender(const DeviceScene& S, const CameraParams& cam, const RenderTargets& out, int blocks, bool counters,
+                         cudaStream_t stream);
+int renderBlockSize();
+int renderStackCapacity();
+cudaError_t renderOccupancy(int* blocksPerSm, bool counters);
+
+}  // namespace rtg

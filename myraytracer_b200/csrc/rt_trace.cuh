@@ -1,0 +1,135 @@
+// rt_trace.cuh — TLAS walk, instance entry, hit resolution (device).
+// See rt_traverse.cuh for the reference lines each piece replaces.
+#pragma once
+#include "rt_traverse.cuh"
+
+namespace rtg {
+
+#define RT_TLAS_STACK 40
+
+// world -> local ray (RTContext.swift:657-669); instanceMotion is rejected at scene creation.
+__device__ __forceinline__ void toLocal(const GInstance& I, V3 o, V3 d, V3& oL, V3& dL) {
+    if (I.identity) { oL = o; dL = d; }
+    else { oL = xfmPoint(I.w2l, o); dL = xfmVector(I.w2l, d); }
+}
+
+// Closest-hit / any-hit test of one instance.  tLow = max(eps, tMin); hit.t = current closest t or tMax.
+template <bool ANYHIT, bool COUNT>
+__device__ __forceinline__ bool enterInstance(const DeviceScene& S, int idx, V3 o, V3 d, double eps, double tMin,
+                                              HitRec& hit, int32_t* sstack, Counters& C) {
+    const GInstance& I = S.instances[idx];
+    V3 oL, dL;
+    toLocal(I, o, d, oL, dL);
+    if (COUNT) C.inst++;
+    const double tLow = dmax(eps, tMin);
+    const int kind = I.kind;
+    if (kind == INST_MESH) return traverseBlas<ANYHIT, COUNT>(S, I, idx, oL, dL, eps, tLow, hit, sstack, C);
+
+    // analytic primitive: the reference's 1-primitive BLAS root test, then the primitive (bit-exact FP64)
+    V3 inv = mk(1.0 / dL.x, 1.0 / dL.y, 1.0 / dL.z);
+    if (COUNT) C.box++;
+    if (!hitAABBExact(I.rootLo, I.rootHi, oL, inv, eps)) return false;
+    double t, u = 0, v = 0;
+    if (kind == INST_SPHERE) {
+        if (COUNT) C.sphere++;
+        // closest: second root if t < eps (RTContext.swift:522); shadow: if t < max(eps,tMin) (:860)
+        if (!sphereT(I.prim, oL, dL, eps, ANYHIT ? tLow : eps, t)) return false;
+    } else if (kind == INST_PLANE) {
+        if (COUNT) C.plane++;
+        if (!planeT(I.prim, oL, dL, eps, t)) return false;
+    } else {
+        if (COUNT) C.tri++;
+        V3 v0, v1, v2;
+        loadTri(S, I, I.triBase, v0, v1, v2);
+        if (!mtTest(v0, v1, v2, oL, dL, eps, t, u, v)) return false;
+    }
+    if (ANYHIT) return (t > tLow && t < hit.t);
+    if (t <= tLow || t >= hit.t) return false;
+    hit.t = t; hit.u = u; hit.v = v; hit.inst = idx; hit.slot = I.triBase;
+    return false;
+}
+
+// TLAS walk (FP64 boxes = unions of Instance.worldBounds, widened interval; near child first).
+template <bool ANYHIT, bool COUNT>
+__device__ __forceinline__ bool traceScene(const DeviceScene& S, V3 o, V3 d, double tMin, HitRec& hit, int32_t* sstack,
+                                           Counters& C) {
+    const double eps = S.eps;
+    int32_t cur = S.tlasRootRef;
+    if (cur == kEmptyRef) return false;
+    if (cur < 0) return enterInstance<ANYHIT, COUNT>(S, ~cur, o, d, eps, tMin, hit, sstack, C);
+    const V3 ia = refinedInv(d);
+    const double tLow = dmax(eps, tMin);
+    int32_t tstack[RT_TLAS_STACK];
+    int sp = 0;
+    for (;;) {
+        if (cur >= 0) {
+            const TNode& n = S.tlas[cur];
+            double n0, f0, n1, f1;
+            slabApprox(n.lo0, n.hi0, o, ia, n0, f0);
+            slabApprox(n.lo1, n.hi1, o, ia, n1, f1);
+            if (COUNT) C.box += 2;
+            // reference: enter iff tmax >= max(tmin, eps) (no culling against hit.t in the box test,
+            // RTContext.swift:632-640); culling against hit.t cannot change the closest hit.
+            bool h0 = !(n0 > f0) && !(f0 < tLow) && !(n0 > hit.t);
+            bool h1 = !(n1 > f1) && !(f1 < tLow) && !(n1 > hit.t);
+            int32_t c0 = n.child0, c1 = n.child1;
+            if (h0 && h1) {
+                if (!ANYHIT && n1 < n0) { int32_t t = c0; c0 = c1; c1 = t; }
+                if (sp < RT_TLAS_STACK) tstack[sp++] = c1;
+                cur = c0;
+                continue;
+            } else if (h0) { cur = c0; continue; }
+            else if (h1) { cur = c1; continue; }
+        } else {
+            if (enterInstance<ANYHIT, COUNT>(S, ~cur, o, d, eps, tMin, hit, sstack, C)) return true;
+        }
+        if (sp == 0) return false;
+        cur = tstack[--sp];
+    }
+}
+
+struct Surface {
+    V3 p, n;          // world-space hit point and geometric normal (Hit.p, Hit.n)
+    int64_t mat;      // Hit.mat
+    int64_t prim;     // primitiveIndex of the hit primitive
+    int32_t kind;     // RT_HIT_*
+};
+
+// Hit.p / Hit.n / Hit.mat exactly as committed at RTContext.swift:496-509,524-526,535-537
+// and mapped to world space at :679-704.
+__device__ __forceinline__ void resolveHit(const DeviceScene& S, const HitRec& hit, V3 o, V3 d, Surface& s) {
+    const GInstance& I = S.instances[hit.inst];
+    V3 pL, nL;
+    const int kind = I.kind;
+    if (kind == INST_MESH || kind == INST_TRI) {
+        V3 v0, v1, v2;
+        loadTri(S, I, hit.slot, v0, v1, v2);
+        int64_t triIndex = I.triF64 ? S.trisD[hit.slot].triIndex : (int64_t)S.tris[hit.slot].triIndex;
+        V3 e1 = v1 - v0, e2 = v2 - v0;
+        const double u = hit.u, v = hit.v;
+        if (I.smooth) {
+            const double* nn = S.triNormals + triIndex * 9;
+            const double w = 1.0 - u - v;
+            nL = normalize((w * ld3(nn) + u * ld3(nn + 3)) + v * ld3(nn + 6));
+        } else {
+            nL = normalize(cross(e1, e2));
+        }
+        pL = (v0 + u * e1) + v * e2;
+        s.kind = 1;  // RT_HIT_TRIANGLE
+        s.prim = triIndex;
+    } else {
+        V3 oL, dL;
+        toLocal(I, o, d, oL, dL);
+        pL = oL + dL * hit.t;
+        if (kind == INST_SPHERE) { nL = normalize(pL - ld3(I.prim)); s.kind = 2; }
+        else { nL = normalize(ld3(I.prim + 3)); s.kind = 3; }
+        s.prim = I.primIndex;
+    }
+    s.p = I.identity ? pL : xfmPoint(I.l2w, pL);
+    V3 wn = normalize(mul3(I.nmat, nL));
+    if (I.flipNormal) wn = -wn;
+    s.n = wn;
+    s.mat = I.matId;
+}
+
+}  // namespace rtg

@@ -1,0 +1,229 @@
+// rt_traverse.cuh — two-level traversal and primitive tests on the device.
+//
+// Replaces, for the GPU layout of gpu_layout.h:
+//   intersectTLAS / intersectBLAS     Models/RTContext.swift:619-720, 544-610
+//   occludedTLAS / occludedBLAS       Models/RTContext.swift:724-829
+//   intersectTriangle/Sphere/Plane    Models/RTContext.swift:479-538
+//   tri/sphere/planeShadowHit         Models/RTContext.swift:832-870
+//   hitAABB                           Models/RTContext.swift:557-565
+// Precision policy: primitive tests and the world->local ray are
+// FP64 in the reference's exact operation order (bit-identical t, u, v);
+// BLAS box tests are FP32 against boxes padded/rounded outward, evaluated from
+// a ray origin advanced to the BLAS in FP64 — conservative, so no hit the
+// reference finds is culled; TLAS boxes are FP64 with a widened interval.
+#pragma once
+#include "gpu_layout.h"
+#include "rt_math.cuh"
+
+namespace rtg {
+
+#ifndef RT_BLOCK
+#define RT_BLOCK 128
+#endif
+#ifndef RT_STACK
+#define RT_STACK 64   // same capacity as the reference's fixed stacks (RTContext.swift:550,626)
+#endif
+
+struct Counters {
+    unsigned long long box, tri, sphere, plane, inst;
+    int maxStack;
+};
+
+struct HitRec {
+    double t, u, v;   // u, v: barycentrics of a triangle hit
+    int32_t inst;     // -1 = miss
+    int32_t slot;     // triangle slot (leaf order) within the global GTri/GTriD array
+};
+
+// FP64 slab test of the reference, bit-exact (used for analytic instances' 1-primitive BLAS root):
+// returns true iff tmax >= max(tmin, eps).
+__device__ __forceinline__ bool hitAABBExact(const double* lo, const double* hi, V3 o, V3 inv, double eps) {
+    double t1x = (lo[0] - o.x) * inv.x, t1y = (lo[1] - o.y) * inv.y, t1z = (lo[2] - o.z) * inv.z;
+    double t2x = (hi[0] - o.x) * inv.x, t2y = (hi[1] - o.y) * inv.y, t2z = (hi[2] - o.z) * inv.z;
+    double tmin = dmax(dmax(dmin(t1x, t2x), dmin(t1y, t2y)), dmin(t1z, t2z));
+    double mx = dmax(t1x, t2x), my = dmax(t1y, t2y), mz = dmax(t1z, t2z);
+    double tmax = dmin(mx, dmin(my, mz));
+    return tmax >= dmax(tmin, eps);
+}
+
+// Widened FP64 slab interval using an approximate reciprocal (relative error ~1e-13, see refinedInv):
+// [tn, tf] contains the exact interval.  NaN lanes (0*inf) drop out through fmin/fmax.
+__device__ __forceinline__ void slabApprox(const double* lo, const double* hi, V3 o, V3 ia, double& tn, double& tf) {
+    double t1x = (lo[0] - o.x) * ia.x, t1y = (lo[1] - o.y) * ia.y, t1z = (lo[2] - o.z) * ia.z;
+    double t2x = (hi[0] - o.x) * ia.x, t2y = (hi[1] - o.y) * ia.y, t2z = (hi[2] - o.z) * ia.z;
+    tn = fmax(fmax(fmin(t1x, t2x), fmin(t1y, t2y)), fmin(t1z, t2z));
+    tf = fmin(fmin(fmax(t1x, t2x), fmax(t1y, t2y)), fmax(t1z, t2z));
+    const double k = 1.0e-9;
+    tn = tn - fabs(tn) * k;
+    tf = tf + fabs(tf) * k;
+}
+
+// 1/d to ~1e-13 relative without an FP64 division: FP32 reciprocal + one Newton step.
+__device__ __forceinline__ double refinedInv1(double d) {
+    double r = (double)(1.0f / (float)d);
+    double r2 = r * (2.0 - d * r);
+    return (isfinite(r) && r != 0.0) ? r2 : r;
+}
+__device__ __forceinline__ V3 refinedInv(V3 d) { return mk(refinedInv1(d.x), refinedInv1(d.y), refinedInv1(d.z)); }
+
+// Moeller-Trumbore in the reference's operation order (RTContext.swift:479-494 / :832-847).
+// The divisions-free early outs reject exactly the cases the reference rejects:
+//   sign(num) != sign(det)      -> u (or v) < 0
+//   |num| > |det| (1 + 1e-15)   -> u > 1 (or u + v > 1)
+// so invDet = 1/det is only evaluated for (near-)hits.  Returns true with t,u,v when
+// u, v pass; the caller applies the t window.
+__device__ __forceinline__ bool mtTest(V3 v0, V3 v1, V3 v2, V3 org, V3 dir, double eps, double& t, double& u, double& v) {
+    V3 e1 = v1 - v0, e2 = v2 - v0;
+    V3 pvec = cross(dir, e2);
+    double det = dot(e1, pvec);
+    double adet = fabs(det);
+    if (adet < eps) return false;
+    V3 tvec = org - v0;
+    double nu = dot(tvec, pvec);
+    const double tiny = 1e-290, big = 1e290;
+    bool safe = adet < big;
+    double lim = adet * (1.0 + 1e-15);
+    if (safe && fabs(nu) > tiny) {
+        if ((nu < 0.0) != (det < 0.0)) return false;
+        if (fabs(nu) > lim) return false;
+    }
+    V3 q = cross(tvec, e1);
+    double nv = dot(dir, q);
+    if (safe && fabs(nv) > tiny) {
+        if ((nv < 0.0) != (det < 0.0)) return false;
+        if (fabs(nu) + fabs(nv) > lim * (1.0 + 1e-15) && fabs(nu) > tiny) return false;
+    }
+    double invDet = 1.0 / det;
+    u = nu * invDet;
+    if (u < 0.0 || u > 1.0) return false;
+    v = nv * invDet;
+    if (v < 0.0 || u + v > 1.0) return false;
+    t = dot(e2, q) * invDet;
+    return true;
+}
+
+// RTContext.swift:512-523 (closest) and :851-861 (shadow: second-root rule uses max(eps,tMin))
+__device__ __forceinline__ bool sphereT(const double* sp, V3 o, V3 d, double eps, double rootLimit, double& t) {
+    V3 oc = o - ld3(sp);
+    double a = dot(d, d);
+    double b = 2.0 * dot(oc, d);
+    double c = dot(oc, oc) - sp[3] * sp[3];
+    double disc = b * b - 4 * a * c;
+    if (disc < 0) return false;
+    double sd = sqrt(disc);
+    t = (-b - sd) / (2 * a);
+    if (t < rootLimit) t = (-b + sd) / (2 * a);
+    return true;
+}
+
+// RTContext.swift:530-534 / :865-869
+__device__ __forceinline__ bool planeT(const double* pl, V3 o, V3 d, double eps, double& t) {
+    V3 n = ld3(pl + 3);
+    double denom = dot(n, d);
+    if (fabs(denom) < eps) return false;
+    t = dot(ld3(pl) - o, n) / denom;
+    return true;
+}
+
+__device__ __forceinline__ void loadTri(const DeviceScene& S, const GInstance& I, int slot, V3& v0, V3& v1, V3& v2) {
+    if (I.triF64) {
+        const GTriD* p = S.trisD + slot;
+        v0 = ld3(p->v0); v1 = ld3(p->v1); v2 = ld3(p->v2);
+    } else {
+        const float4* p = reinterpret_cast<const float4*>(S.tris + slot);
+        float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+        v0 = mk((double)a.x, (double)a.y, (double)a.z);
+        v1 = mk((double)b.x, (double)b.y, (double)b.z);
+        v2 = mk((double)c.x, (double)c.y, (double)c.z);
+    }
+}
+
+// One BLAS (mesh instance) traversal.  ANYHIT: return true at the first accepted primitive.
+// oL/dL: local-space FP64 ray (bit-identical to the reference's).  tLow = max(eps, tMin).
+// hit.t is the current closest t (closest) or tMax (any-hit); updated on accept.
+template <bool ANYHIT, bool COUNT>
+__device__ __forceinline__ bool traverseBlas(const DeviceScene& S, const GInstance& I, int instIdx, V3 oL, V3 dL, double eps,
+                                             double tLow, HitRec& hit, int32_t* sstack, Counters& C) {
+    // Advance the origin to the BLAS in FP64 so that its FP32 copy is accurate relative to the
+    // box size: t0 = entry distance into the (exact) root box, from a widened FP64 slab test.
+    V3 ia = refinedInv(dL);
+    V3 oc = oL - ld3(I.centre);
+    double lo[3] = {I.rootLo[0] - I.centre[0], I.rootLo[1] - I.centre[1], I.rootLo[2] - I.centre[2]};
+    double hi[3] = {I.rootHi[0] - I.centre[0], I.rootHi[1] - I.centre[1], I.rootHi[2] - I.centre[2]};
+    double tn, tf;
+    slabApprox(lo, hi, oc, ia, tn, tf);
+    if (COUNT) C.box++;
+    if (tn > tf || tf < tLow || tn > hit.t) return false;  // widened interval: conservative (NaN -> keep)
+    double t0 = tn > 0.0 ? tn : 0.0;
+    if (!(t0 < 1e300)) t0 = 0.0;
+    V3 o2 = oc + dL * t0;
+    const float ox = (float)o2.x, oy = (float)o2.y, oz = (float)o2.z;
+    const float ix = 1.0f / (float)dL.x, iy = 1.0f / (float)dL.y, iz = 1.0f / (float)dL.z;
+    float tminF = __double2float_rd(tLow - t0);
+    float tmaxF = __double2float_ru(hit.t - t0);
+
+    const GNode* nodes = S.nodes + I.nodeBase;
+    int sp = 0;
+    int32_t cur = I.rootRef;
+    const int tid = threadIdx.x;
+    for (;;) {
+        while ((uint32_t)cur < 0x7fffffffu) {  // inner node
+            const float4* np = reinterpret_cast<const float4*>(nodes + cur);
+            const float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2);
+            const int4 ch = __ldg(reinterpret_cast<const int4*>(np + 3));
+            if (COUNT) C.box += 2;
+            // child 0: lo = q0.xyz, hi = (q0.w, q1.x, q1.y); child 1: lo = (q1.z, q1.w, q2.x), hi = q2.yzw
+            float a0 = (q0.x - ox) * ix, b0 = (q0.w - ox) * ix;
+            float a1 = (q0.y - oy) * iy, b1 = (q1.x - oy) * iy;
+            float a2 = (q0.z - oz) * iz, b2 = (q1.y - oz) * iz;
+            float n0 = fmaxf(fmaxf(fminf(a0, b0), fminf(a1, b1)), fmaxf(fminf(a2, b2), tminF));
+            float f0 = fminf(fminf(fmaxf(a0, b0), fmaxf(a1, b1)), fminf(fmaxf(a2, b2), tmaxF));
+            float c0 = (q1.z - ox) * ix, d0 = (q2.y - ox) * ix;
+            float c1 = (q1.w - oy) * iy, d1 = (q2.z - oy) * iy;
+            float c2 = (q2.x - oz) * iz, d2 = (q2.w - oz) * iz;
+            float n1 = fmaxf(fmaxf(fminf(c0, d0), fminf(c1, d1)), fmaxf(fminf(c2, d2), tminF));
+            float f1 = fminf(fminf(fmaxf(c0, d0), fmaxf(c1, d1)), fminf(fmaxf(c2, d2), tmaxF));
+            // the padding of the stored boxes covers every FP32 rounding here
+            const bool h0 = n0 <= f0, h1 = n1 <= f1;
+            if (h0 && h1) {
+                int32_t nearC = ch.x, farC = ch.y;
+                if (!ANYHIT && n1 < n0) { nearC = ch.y; farC = ch.x; }
+                sstack[sp * RT_BLOCK + tid] = farC;
+                sp++;
+                if (COUNT && sp > C.maxStack) C.maxStack = sp;
+                cur = nearC;
+            } else if (h0) {
+                cur = ch.x;
+            } else if (h1) {
+                cur = ch.y;
+            } else {
+                if (sp == 0) return false;
+                sp--;
+                cur = sstack[sp * RT_BLOCK + tid];
+            }
+        }
+        if (cur != kEmptyRef) {  // leaf
+            const uint32_t ref = ~(uint32_t)cur;
+            const int first = I.triBase + (int)(ref >> 3), count = (int)(ref & 7u) + 1;
+            for (int k = 0; k < count; k++) {
+                V3 v0, v1, v2;
+                loadTri(S, I, first + k, v0, v1, v2);
+                if (COUNT) C.tri++;
+                double t, u, v;
+                if (!mtTest(v0, v1, v2, oL, dL, eps, t, u, v)) continue;
+                if (ANYHIT) {
+                    if (t > tLow && t < hit.t) return true;
+                } else {
+                    if (t <= tLow || t >= hit.t) continue;
+                    hit.t = t; hit.u = u; hit.v = v; hit.inst = instIdx; hit.slot = first + k;
+                    tmaxF = __double2float_ru(t - t0);
+                }
+            }
+        }
+        if (sp == 0) return false;
+        sp--;
+        cur = sstack[sp * RT_BLOCK + tid];
+    }
+}
+
+}  // namespace rtg

@@ -1,0 +1,174 @@
+"""Python face of the host mirror: RayTracerEngine / RenderStats over the C ABI.
+
+Mirrors the reference's public entry points (Sources/RayTracer/RayTracer.swift:25-205):
+``RayTracerEngine(from: url)``, ``render(format:cameraIndex:progress:)``, ``inspect``.
+All work happens in librtcuda.so (C++ host mirror -> C ABI -> CUDA); this module only marshals.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Callable, Optional
+
+import numpy as np
+
+from . import capi
+
+
+class RenderError(RuntimeError):
+    """NSError(domain:code:) of the reference (RayTracer.swift:121-123,142-154)."""
+
+    def __init__(self, code: int, message: str):
+        super().__init__(f"[{code}] {message}")
+        self.code = code
+        self.message = message
+
+
+@dataclass
+class RenderResult:
+    rgba: np.ndarray                  # (H, W, 4) uint8, row 0 = top
+    stats: dict                       # RenderStats + ray split + deviceMs
+    linear: Optional[np.ndarray] = None   # (H, W, 3) float64: the [Vec3] Renderer.render returns
+    ids: Optional[np.ndarray] = None      # (H, W, n*n) HIT_ID_DTYPE
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class RayTracerEngine:
+    def __init__(self, url: str, device: int = 0):
+        self._lib = capi.load()
+        self._h = self._lib.rth_engine_create(url.encode(), device)
+        if not self._h:
+            raise MemoryError(self._lib.rth_last_error().decode())
+        self.load_error = "" if self.ready else self._lib.rth_last_error().decode()
+
+    @property
+    def ready(self) -> bool:
+        return bool(self._h) and self._lib.rth_engine_ready(self._h) == 1
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.rth_engine_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # -- introspection ----------------------------------------------------
+    def camera_count(self) -> int:
+        return self._lib.rth_engine_camera_count(self._h)
+
+    def camera(self, index: int = 0) -> capi.rt_camera:
+        cam = capi.rt_camera()
+        rc = self._lib.rth_engine_camera(self._h, index, C.byref(cam))
+        if rc != 0:
+            raise RenderError(rc, self._lib.rth_last_error().decode())
+        return cam
+
+    def scene_handle(self):
+        """rt_scene_t* of the underlying Renderer (for direct rt_render_device calls)."""
+        return self._lib.rth_engine_scene(self._h)
+
+    def scene_info(self) -> dict:
+        info = capi.rt_scene_info()
+        if self._lib.rt_scene_get_info(self.scene_handle(), C.byref(info)) != 0:
+            raise RenderError(-21, self._lib.rt_last_error().decode())
+        return info.as_dict()
+
+    def describe(self) -> capi.rt_scene_desc:
+        d = capi.rt_scene_desc()
+        rc = self._lib.rth_engine_describe(self._h, C.byref(d))
+        if rc != 0:
+            raise RenderError(rc, self._lib.rth_last_error().decode())
+        return d
+
+    def instance_object_ids(self) -> np.ndarray:
+        n = self._lib.rth_engine_instance_object_ids(self._h, None, 0)
+        out = np.zeros(max(n, 0), np.int32)
+        self._lib.rth_engine_instance_object_ids(self._h, _ptr(out), n)
+        return out
+
+    # -- render -----------------------------------------------------------
+    def render(self, camera_index: int = 0, want_linear: bool = False, want_ids: bool = False,
+               shard_index: int = 0, shard_count: int = 1, counters: bool = False,
+               progress: Optional[Callable[[int, int], bool]] = None) -> RenderResult:
+        if not self._h or self._lib.rth_engine_camera_count(self._h) == 0 and not self.ready:
+            pass  # let the C side produce the reference's error codes
+        cam = None
+        try:
+            cam = self.camera(camera_index)
+        except RenderError:
+            cam = None
+        W = max(1, cam.width) if cam else 1
+        H = max(1, cam.height) if cam else 1
+        n = int(np.floor(np.sqrt(max(1, cam.numSamples)))) if cam else 1
+        rgba = np.zeros((H, W, 4), np.uint8)
+        linear = np.zeros((H, W, 3), np.float64) if want_linear else None
+        ids = np.zeros((H, W, n * n), capi.HIT_ID_DTYPE) if want_ids else None
+        prm = capi.rt_render_params()
+        prm.shardIndex, prm.shardCount, prm.collectCounters = shard_index, shard_count, 1 if counters else 0
+        cb = None
+        if progress is not None:
+            cb = capi.rt_progress_fn(lambda done, total, _u: 0 if progress(done, total) else 1)
+            prm.progress = cb
+        st = capi.rt_stats()
+        rc = self._lib.rth_engine_render(self._h, camera_index, C.byref(prm), _ptr(rgba), _ptr(linear), _ptr(ids), C.byref(st))
+        if rc != 0:
+            raise RenderError(rc, self._lib.rth_last_error().decode())
+        return RenderResult(rgba=rgba, stats=st.as_dict(), linear=linear, ids=ids)
+
+
+class FlatContext:
+    """Scene + RTContext(scene:) of the host mirror without a renderer (runs without a GPU)."""
+
+    def __init__(self, url: str):
+        self._lib = capi.load()
+        self._h = self._lib.rth_context_create(url.encode())
+        if not self._h:
+            raise RuntimeError(self._lib.rth_last_error().decode())
+        self.desc = capi.rt_scene_desc()
+        self._lib.rth_context_describe(self._h, C.byref(self.desc))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.rth_context_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def triangles(self):
+        n = self.desc.nTriangles
+        if n == 0:
+            return np.zeros((0, 3, 3)), np.zeros((0, 3, 3))
+        v = np.ctypeslib.as_array(self.desc.triVertices, shape=(n, 3, 3)).copy()
+        nr = np.ctypeslib.as_array(self.desc.triNormals, shape=(n, 3, 3)).copy()
+        return v, nr
+
+    def instances(self):
+        n = self.desc.nInstances
+        out = dict(l2w=np.zeros((n, 16)), w2l=np.zeros((n, 16)), nmat=np.zeros((n, 9)), bounds=np.zeros((n, 6)),
+                   blas=np.zeros(n, np.int64), mat=np.zeros(n, np.int64))
+        for i in range(n):
+            I = self.desc.instances[i]
+            out["l2w"][i] = list(I.localToWorld)
+            out["w2l"][i] = list(I.worldToLocal)
+            out["nmat"][i] = list(I.normalMatrix)
+            out["bounds"][i] = list(I.worldBounds)
+            out["blas"][i] = I.blas
+            out["mat"][i] = I.materialOverride
+        return out
