@@ -156,6 +156,7 @@ typedef struct rt_stats {
     int64_t kernelLaunches;       /* kernels launched by this call */
     /* only with collectCounters: */
     int64_t boxTests, triTests, sphereTests, planeTests, instEntries, maxStack;
+    int64_t smoothHits;           /* closest hits resolved on smooth-shaded triangles (3 normals fetched) */
 } rt_stats;
 
 typedef struct rt_scene_info {

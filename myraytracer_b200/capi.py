@@ -94,7 +94,8 @@ class rt_stats(C.Structure):
     _fields_ = [(n, C.c_int64) for n in ("meshes", "triangles", "spheres", "planes", "rays", "milliseconds",
                                          "raysPrimary", "raysShadow", "raysSecondary")]
     _fields_ += [("deviceMs", C.c_double), ("kernelLaunches", C.c_int64)]
-    _fields_ += [(n, C.c_int64) for n in ("boxTests", "triTests", "sphereTests", "planeTests", "instEntries", "maxStack")]
+    _fields_ += [(n, C.c_int64) for n in ("boxTests", "triTests", "sphereTests", "planeTests", "instEntries", "maxStack",
+                                         "smoothHits")]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

@@ -126,6 +126,7 @@ int32_t rt_render_finish(rt_scene_t* sc, rt_stats* st) {
             st->boxTests = (int64_t)sc->hCounters[3]; st->triTests = (int64_t)sc->hCounters[4];
             st->sphereTests = (int64_t)sc->hCounters[5]; st->planeTests = (int64_t)sc->hCounters[6];
             st->instEntries = (int64_t)sc->hCounters[7]; st->maxStack = (int64_t)sc->hCounters[8];
+            st->smoothHits = (int64_t)sc->hCounters[9];
         }
     }
     return RT_OK;

@@ -99,7 +99,7 @@ __global__ void __launch_bounds__(RT_BLOCK) renderKernel(DeviceScene S, CameraPa
     const size_t stride = (size_t)gridDim.x * blockDim.x;
 
     Counters C;
-    C.box = C.tri = C.sphere = C.plane = C.inst = 0; C.maxStack = 0;
+    C.box = C.tri = C.sphere = C.plane = C.inst = C.smooth = 0; C.maxStack = 0;
     unsigned long long nPrimary = 0, nShadow = 0, nSecondary = 0;
 
     const int W = cam.width, H = cam.height;
@@ -174,6 +174,7 @@ __global__ void __launch_bounds__(RT_BLOCK) renderKernel(DeviceScene S, CameraPa
                     traceScene<false, COUNT>(S, cur.o, cur.d, primary ? tMinPrimary : 0.0, hit, sstack, C);
                     Surface sf;
                     if (hit.inst >= 0) resolveHit(S, hit, cur.o, cur.d, sf);
+                    if (COUNT && hit.inst >= 0 && sf.kind == 1 && S.instances[hit.inst].smooth) C.smooth++;
                     if (primary && out.ids) {
                         HitId& h = out.ids[((size_t)j * W + i) * (size_t)(n * n) + (size_t)(sy * n + sx)];
                         h.inst = hit.inst;
@@ -325,6 +326,7 @@ __global__ void __launch_bounds__(RT_BLOCK) renderKernel(DeviceScene S, CameraPa
             C.sphere += __shfl_down_sync(0xffffffffu, C.sphere, off);
             C.plane += __shfl_down_sync(0xffffffffu, C.plane, off);
             C.inst += __shfl_down_sync(0xffffffffu, C.inst, off);
+            C.smooth += __shfl_down_sync(0xffffffffu, C.smooth, off);
             int m = __shfl_down_sync(0xffffffffu, C.maxStack, off);
             if (m > C.maxStack) C.maxStack = m;
         }
@@ -340,6 +342,7 @@ __global__ void __launch_bounds__(RT_BLOCK) renderKernel(DeviceScene S, CameraPa
             atomicAdd(&out.counters[6], C.plane);
             atomicAdd(&out.counters[7], C.inst);
             atomicMax(&out.counters[8], (unsigned long long)C.maxStack);
+            atomicAdd(&out.counters[9], C.smooth);
         }
     }
 }

@@ -25,7 +25,7 @@ namespace rtg {
 #endif
 
 struct Counters {
-    unsigned long long box, tri, sphere, plane, inst;
+    unsigned long long box, tri, sphere, plane, inst, smooth;
     int maxStack;
 };
 

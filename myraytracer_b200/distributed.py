@@ -1,0 +1,117 @@
+"""Tile-sharded rendering of one frame across the GPUs of a box: one process per GPU.
+
+The reference parallelises a frame over 8-row chunks pulled by a CPU thread pool and merges them by plain
+row copies (Extensions/Object+Extension.swift:75-82, 285-376).  Every pixel depends only on (i, j), the
+camera and the read-only scene (per-pixel PCG32 seed, :294), so the same unit shards across GPUs with no
+data-path collective: chunk c belongs to rank c % world (interleaved for load balance), the scene/BVH is
+replicated, and the only exchange is the final gather of the RGBA8 rows to rank 0 over NVLink.
+
+torch is plumbing here (device buffers, streams, torch.distributed/NCCL); the render itself is the CUDA
+kernel behind the C ABI (rt_render_device).  The chunk bookkeeping (`owned_chunks`, `pack_chunks`,
+`gather_chunks`) is backend-agnostic so the world_size>1 path is tested on CPU with gloo.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+CHUNK_ROWS = 8  # Object+Extension.swift:75
+
+
+def n_chunks(height: int) -> int:
+    return (height + CHUNK_ROWS - 1) // CHUNK_ROWS
+
+
+def owned_chunks(height: int, rank: int, world: int) -> range:
+    """Chunks rendered by `rank` (same rule as rt_render_params.shardIndex/shardCount)."""
+    return range(rank, n_chunks(height), max(1, world))
+
+
+def max_owned(height: int, world: int) -> int:
+    return (n_chunks(height) + world - 1) // max(1, world)
+
+
+def pack_chunks(fb: torch.Tensor, rank: int, world: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """fb: (n_chunks*8, W, 4) uint8 padded framebuffer -> (max_owned, 8*W*4) contiguous rows of this rank."""
+    nc = fb.shape[0] // CHUNK_ROWS
+    rows = fb.view(nc, -1)[rank::world]
+    mo = (nc + world - 1) // world
+    if out is None:
+        out = torch.zeros((mo, rows.shape[1]), dtype=fb.dtype, device=fb.device)
+    out[: rows.shape[0]].copy_(rows)
+    return out
+
+
+def unpack_chunks(fb: torch.Tensor, packed: torch.Tensor, rank: int, world: int) -> None:
+    nc = fb.shape[0] // CHUNK_ROWS
+    view = fb.view(nc, -1)[rank::world]
+    view.copy_(packed[: view.shape[0]])
+
+
+def gather_chunks(fb: torch.Tensor, rank: int, world: int, send: Optional[torch.Tensor] = None,
+                  recv: Optional[list] = None, group=None) -> None:
+    """Gather every rank's chunks into rank 0's `fb` (in place).  Other ranks' `fb` is left unchanged."""
+    if world <= 1:
+        return
+    send = pack_chunks(fb, rank, world, send)
+    if rank == 0:
+        if recv is None:
+            recv = [torch.empty_like(send) for _ in range(world)]
+        dist.gather(send, gather_list=recv, dst=0, group=group)
+        for r in range(1, world):
+            unpack_chunks(fb, recv[r], r, world)
+    else:
+        dist.gather(send, gather_list=None, dst=0, group=group)
+
+
+class ShardedRenderer:
+    """RayTracerEngine on this rank's GPU + the framebuffer gather.  rank/world default to the
+    torch.distributed group (or 0/1 when it is not initialised)."""
+
+    def __init__(self, scene_url: str, device: int = 0, rank: Optional[int] = None, world: Optional[int] = None,
+                 camera_index: int = 0):
+        from .engine import RayTracerEngine
+        if rank is None:
+            rank = dist.get_rank() if dist.is_initialized() else 0
+        if world is None:
+            world = dist.get_world_size() if dist.is_initialized() else 1
+        self.rank, self.world, self.device, self.camera_index = rank, world, device, camera_index
+        self.engine = RayTracerEngine(scene_url, device=device)
+        if not self.engine.ready:
+            raise RuntimeError("engine not ready: " + self.engine.load_error)
+        cam = self.engine.camera(camera_index)
+        self.width, self.height = max(1, cam.width), max(1, cam.height)
+        dev = torch.device("cuda", device)
+        hp = n_chunks(self.height) * CHUNK_ROWS
+        self.fb = torch.zeros((hp, self.width, 4), dtype=torch.uint8, device=dev)  # padded to whole chunks
+        self.send = self.recv = None
+        if world > 1:
+            self.send = torch.zeros((max_owned(self.height, world), CHUNK_ROWS * self.width * 4), dtype=torch.uint8, device=dev)
+            if rank == 0:
+                self.recv = [torch.empty_like(self.send) for _ in range(world)]
+        self.host = torch.empty((self.height, self.width, 4), dtype=torch.uint8, pin_memory=True) if rank == 0 else None
+
+    def enqueue(self, counters: bool = False) -> None:
+        """Kernel for this rank's chunks + gather to rank 0, on torch's current stream; no host sync."""
+        st = torch.cuda.current_stream(self.device).cuda_stream
+        self.engine.render_device(self.camera_index, d_rgba=self.fb.data_ptr(), stream=st, shard_index=self.rank,
+                                  shard_count=self.world, counters=counters)
+        gather_chunks(self.fb, self.rank, self.world, self.send, self.recv)
+
+    def finish(self) -> dict:
+        return self.engine.finish()
+
+    def render(self):
+        """One frame end to end: returns (rank 0: (H, W, 4) uint8 numpy view of pinned host memory, stats)."""
+        self.enqueue()
+        if self.rank == 0:
+            self.host.copy_(self.fb[: self.height], non_blocking=True)
+        stats = self.finish()
+        torch.cuda.current_stream(self.device).synchronize()
+        return (self.host.numpy() if self.rank == 0 else None), stats
+
+    @property
+    def d2h_bytes(self) -> int:
+        return self.height * self.width * 4 if self.rank == 0 else 0

@@ -129,6 +129,27 @@ class RayTracerEngine:
         return RenderResult(rgba=rgba, stats=st.as_dict(), linear=linear, ids=ids)
 
 
+    def render_device(self, camera_index: int = 0, d_rgba: int = 0, d_linear: int = 0, d_ids: int = 0, stream: int = 0,
+                      shard_index: int = 0, shard_count: int = 1, counters: bool = False) -> None:
+        """rt_render_device: enqueue one frame on `stream` with caller-owned DEVICE buffers (raw pointers,
+        e.g. torch.Tensor.data_ptr()); does not synchronise.  Pair with finish()."""
+        cam = self.camera(camera_index)
+        prm = capi.rt_render_params()
+        prm.shardIndex, prm.shardCount, prm.collectCounters = shard_index, shard_count, 1 if counters else 0
+        rc = self._lib.rt_render_device(self.scene_handle(), C.byref(cam), C.byref(prm), d_rgba or None, d_linear or None,
+                                        d_ids or None, stream or None)
+        if rc != 0:
+            raise RenderError(rc, self._lib.rt_last_error().decode())
+
+    def finish(self) -> dict:
+        """rt_render_finish: wait for the frame enqueued by render_device; returns the stats dict."""
+        st = capi.rt_stats()
+        rc = self._lib.rt_render_finish(self.scene_handle(), C.byref(st))
+        if rc != 0:
+            raise RenderError(rc, self._lib.rt_last_error().decode())
+        return st.as_dict()
+
+
 class FlatContext:
     """Scene + RTContext(scene:) of the host mirror without a renderer (runs without a GPU)."""
 
