@@ -210,7 +210,7 @@ def run_ours(args):
 
     t0 = time.time()
     path = make_scene(args.config, rank)
-    R = ShardedRenderer(path, device=local, rank=rank, world=world)
+    R = ShardedRenderer(path, device=local, rank=rank, world=world, variant=args.variant)
     info = R.engine.scene_info()
     W, H = R.width, R.height
     log(f"[rank {rank}] scene ready in {time.time() - t0:.1f}s: {info}")
@@ -295,7 +295,7 @@ def run_ours(args):
             "data": "synthetic",
             "config": {"workload": BENCH_CONFIGS[args.config][2], "width": W, "height": H, "triangles": info["triangles"],
                        "rays_per_frame": int(rays), "rays_primary": int(rp), "rays_shadow": int(rs),
-                       "rays_secondary": int(rays - rp - rs), "parallelism": f"tiles{world}",
+                       "rays_secondary": int(rays - rp - rs), "parallelism": f"tiles{world}", "kernel_variant": args.variant,
                        "l2": "256 MB buffer written between timed iterations (L2 flush); scene working set "
                              f"{info['deviceBytes'] / 1e6:.0f} MB"},
             "wall_ms_per_step": wall * 1e3 / args.steps, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
@@ -325,6 +325,7 @@ def main():
     ap.add_argument("--config", choices=sorted(BENCH_CONFIGS), default="c4")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--variant", type=int, default=0, help="rt_render_params.kernelVariant (0 = automatic; A/B runs)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         log("note: timing rules ask for >= 3 warm-up steps")

@@ -133,7 +133,9 @@ typedef struct rt_render_params {
      * shardCount <= 1 renders the whole frame.  (Multi-process sharding: one rank per GPU.) */
     int32_t shardIndex, shardCount;
     int32_t collectCounters;      /* 1: also fill rt_stats box/primitive test counts (slower kernel variant) */
-    int32_t reserved;
+    int32_t kernelVariant;        /* 0 = automatic.  For measurements only: 1 = fast kernel (lane = (pixel, sample), warp
+                                   * packets at depth 0; the default when no material is glossy; RT_ERR_UNSUPPORTED on
+                                   * a scene with roughness != 0), 2 = general kernel (lane = pixel, sequential RNG). */
     rt_progress_fn progress;      /* may be NULL */
     void* progressUser;
 } rt_render_params;

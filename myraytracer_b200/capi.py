@@ -10,7 +10,8 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "librtcuda.so")
+# RTCUDA_LIB: developer override to A/B kernel build variants (always a CUDA build of this same source)
+LIB_PATH = os.environ.get("RTCUDA_LIB") or os.path.join(HERE, "librtcuda.so")
 
 RT_ABI_VERSION = 1
 RT_OK, RT_ERR_INVALID, RT_ERR_CUDA, RT_ERR_UNSUPPORTED, RT_ERR_CANCELLED = 0, -1, -2, -3, -4
@@ -87,7 +88,7 @@ rt_progress_fn = C.CFUNCTYPE(C.c_int, C.c_int32, C.c_int32, C.c_void_p)
 
 class rt_render_params(C.Structure):
     _fields_ = [("shardIndex", C.c_int32), ("shardCount", C.c_int32), ("collectCounters", C.c_int32),
-                ("reserved", C.c_int32), ("progress", rt_progress_fn), ("progressUser", C.c_void_p)]
+                ("kernelVariant", C.c_int32), ("progress", rt_progress_fn), ("progressUser", C.c_void_p)]
 
 
 class rt_stats(C.Structure):

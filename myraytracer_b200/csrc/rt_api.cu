@@ -72,7 +72,9 @@ struct rt_scene {
     HitId* dIds = nullptr; size_t idsBytes = 0;
     unsigned long long* hCounters = nullptr;  // pinned
     cudaEvent_t evStart = nullptr, evStop = nullptr;
-    int blocks = 0, blocksCounters = 0;
+    int blocks[KV_COUNT][2] = {};      // [variant][counters]
+    bool glossy = false;               // some material has roughness != 0: RNG draws inside trace
+    int pendingVariant = 0;
     bool pending = false; bool pendingCounters = false;
     cudaStream_t pendingStream = nullptr;
     int64_t launches = 0;
@@ -210,6 +212,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
         g.phong = m.phong; g.ior = m.ior; g.absorptionIndex = m.absorptionIndex; g.roughness = m.roughness;
         g.type = (m.type >= RT_MAT_MIRROR && m.type <= RT_MAT_CONDUCTOR) ? m.type : RT_MAT_PLAIN;
         g.hasAbsorption = (m.absorption[0] != 0 || m.absorption[1] != 0 || m.absorption[2] != 0) ? 1 : 0;
+        if (g.type != RT_MAT_PLAIN && m.roughness != 0) sc->glossy = true;
     }
     std::vector<GPointLight> lights((size_t)d->nPointLights);
     for (int64_t i = 0; i < d->nPointLights; i++) {
@@ -253,11 +256,12 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
 
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, device));
-    int bps = 0;
-    CK(renderOccupancy(&bps, false));
-    sc->blocks = prop.multiProcessorCount * (bps > 0 ? bps : 1);
-    CK(renderOccupancy(&bps, true));
-    sc->blocksCounters = prop.multiProcessorCount * (bps > 0 ? bps : 1);
+    for (int v = 0; v < KV_COUNT; v++)
+        for (int c = 0; c < 2; c++) {
+            int bps = 0;
+            CK(renderOccupancy(v, &bps, c != 0));
+            sc->blocks[v][c] = prop.multiProcessorCount * (bps > 0 ? bps : 1);
+        }
 
     rt_scene_info& I = sc->info;
     I.triangles = d->nTriangles; I.spheres = d->nSpheres; I.planes = d->nPlanes; I.instances = d->nInstances; I.blasCount = d->nBlas;

@@ -85,7 +85,14 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     int rc = buildCamera(camera, params, cp);
     if (rc) return rc;
     const bool counters = params && params->collectCounters;
-    const int blocks = counters ? sc->blocksCounters : sc->blocks;
+    int variant = sc->glossy ? KV_GENERAL : KV_FAST;
+    if (params && params->kernelVariant != 0) {
+        if (params->kernelVariant < 1 || params->kernelVariant > KV_COUNT) return fail(RT_ERR_INVALID, "kernelVariant outside 0..2");
+        variant = params->kernelVariant - 1;
+        if (sc->glossy && variant == KV_FAST)
+            return fail(RT_ERR_UNSUPPORTED, "the fast kernel needs roughness == 0 on every material (RNG skip-ahead)");
+    }
+    const int blocks = sc->blocks[variant][counters ? 1 : 0];
     cudaStream_t st = (cudaStream_t)cudaStream;
 
     const size_t threads = (size_t)blocks * renderBlockSize();
@@ -98,7 +105,7 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     CK(cudaEventRecord(sc->evStart, st));
     CK(cudaMemsetAsync(sc->dTileCounter, 0, 64, st));
     CK(cudaMemsetAsync(sc->dCounters, 0, 16 * sizeof(unsigned long long), st));
-    CK(launchRender(sc->ds, cp, rt, blocks, counters, st));
+    CK(launchRender(variant, sc->ds, cp, rt, blocks, counters, st));
     CK(cudaMemcpyAsync(sc->hCounters, sc->dCounters, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
     CK(cudaEventRecord(sc->evStop, st));
     sc->pending = true; sc->pendingCounters = counters; sc->pendingStream = st;

@@ -1,0 +1,31 @@
+// rt_kernel_variant.cu — one render kernel per object file (build time): -DRT_V_FAST=1 compiles
+// renderKernelFast, -DRT_V_FAST=0 renderKernelGeneral; rt_kernels.cu dispatches.   COMPILE WITH -fmad=false.
+#include "rt_render_kernel.cuh"
+
+#ifndef RT_V_FAST
+#error "define RT_V_FAST"
+#endif
+
+namespace rtg {
+
+#if RT_V_FAST
+#define RT_KERNEL renderKernelFast
+#define RT_NAME(x) x##Fast
+#else
+#define RT_KERNEL renderKernelGeneral
+#define RT_NAME(x) x##General
+#endif
+
+cudaError_t RT_NAME(launchVariant)(const DeviceScene& S, const CameraParams& cam, const RenderTargets& out, int blocks,
+                                   bool counters, cudaStream_t stream) {
+    if (counters) RT_KERNEL<true><<<blocks, RT_BLOCK, 0, stream>>>(S, cam, out);
+    else RT_KERNEL<false><<<blocks, RT_BLOCK, 0, stream>>>(S, cam, out);
+    return cudaGetLastError();
+}
+
+cudaError_t RT_NAME(occupancyVariant)(int* blocksPerSm, bool counters) {
+    if (counters) return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocksPerSm, RT_KERNEL<true>, RT_BLOCK, 0);
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocksPerSm, RT_KERNEL<false>, RT_BLOCK, 0);
+}
+
+}  // namespace rtg

@@ -24,10 +24,20 @@ struct RenderTargets {
 
 static const int kPathFields = 11;
 
-cudaError_t launchRender(const DeviceScene& S, const CameraParams& cam, const RenderTargets& out, int blocks, bool counters,
-                         cudaStream_t stream);
+#ifndef RT_BLOCK
+#define RT_BLOCK 128
+#endif
+#ifndef RT_STACK
+#define RT_STACK 64   // same capacity as the reference's fixed stacks (RTContext.swift:550,626)
+#endif
+
+// kernel variants (rt_kernels.cu); values match rt_render_params.kernelVariant - 1
+enum KernelVariant { KV_FAST = 0, KV_GENERAL = 1, KV_COUNT = 2 };
+
+cudaError_t launchRender(int variant, const DeviceScene& S, const CameraParams& cam, const RenderTargets& out, int blocks,
+                         bool counters, cudaStream_t stream);
 int renderBlockSize();
 int renderStackCapacity();
-cudaError_t renderOccupancy(int* blocksPerSm, bool counters);
+cudaError_t renderOccupancy(int variant, int* blocksPerSm, bool counters);
 
 }  // namespace rtg

@@ -70,6 +70,17 @@ struct PCG32 {
         next();
     }
     __device__ __forceinline__ double nextFloat() { return (double)next() * 2.3283064365386963e-10; }
+    // skip `delta` draws in O(log delta): the LCG state after k steps is A^k*s + (A^k-1)/(A-1)*inc
+    __device__ __forceinline__ void advance(uint64_t delta) {
+        uint64_t curMult = 6364136223846793005ULL, curPlus = inc, accMult = 1, accPlus = 0;
+        while (delta > 0) {
+            if (delta & 1) { accMult *= curMult; accPlus = accPlus * curMult + curPlus; }
+            curPlus = (curMult + 1) * curPlus;
+            curMult *= curMult;
+            delta >>= 1;
+        }
+        state = accMult * state + accPlus;
+    }
 };
 
 }  // namespace rtg

@@ -1,0 +1,218 @@
+// rt_packet.cuh — warp-packet traversal: the 32 rays of a warp walk the TLAS/BLAS together.
+//
+// Same queries as rt_traverse.cuh / rt_trace.cuh (intersectTLAS/BLAS, occludedTLAS/BLAS,
+// Models/RTContext.swift:544-829) for COHERENT ray bundles: the 32 lanes of a warp hold the samples
+// of one or two neighbouring pixels (primary rays) or their shadow rays towards one light, so their
+// BVH paths overlap almost completely.  Instead of 32 private stacks and 32 divergent node fetches
+// (measured: 16 of 32 lanes active in the while-while loop), the warp keeps ONE stack of
+// (node, lane-mask) entries in shared memory, fetches each node once (a warp-uniform, broadcast
+// load) and every lane tests its own ray against it; control flow is decided by ballots only, so
+// the warp never diverges inside the traversal.  A lane whose ray misses a box is simply cleared
+// from the mask that travels with the node.
+// The per-lane arithmetic (conservative FP32 slab test, exact FP64 Moeller-Trumbore in the
+// reference's operation order) is unchanged, so results are identical to the per-lane path except
+// for the visiting order, which only matters at equal-t ties.
+//
+// Every function here must be entered by all 32 lanes of a converged warp.
+#pragma once
+#include "rt_trace.cuh"
+
+namespace rtg {
+
+#define RT_FULL 0xffffffffu
+#ifndef RT_WSTACK
+#define RT_WSTACK 64    // BLAS entries per warp (tree depth is checked against RT_STACK at build time)
+#endif
+#define RT_WTSTACK 40   // TLAS entries per warp
+#define RT_WARP_STACK_INT2 (RT_WSTACK + RT_WTSTACK)
+
+// Packet walk of one mesh BLAS.  inMask (warp-uniform): lanes whose ray takes part.
+// anyhit: run-time, warp-uniform (one copy of the loop for closest-hit and shadow packets).
+// Returns (any-hit only) the warp-uniform mask of lanes found occluded.
+template <bool COUNT>
+__device__ __forceinline__ uint32_t packetBlas(const DeviceScene& S, const GInstance& I, int instIdx, V3 oL, V3 dL,
+                                               double eps, double tLow, HitRec& hit, bool anyhit, uint32_t inMask,
+                                               int2* wstack, Counters& C) {
+    const uint32_t bit = 1u << (threadIdx.x & 31);
+    // per-lane root test + origin advance, exactly as traverseBlas
+    V3 ia = refinedInv(dL);
+    V3 oc = oL - ld3(I.centre);
+    double lo[3] = {I.rootLo[0] - I.centre[0], I.rootLo[1] - I.centre[1], I.rootLo[2] - I.centre[2]};
+    double hi[3] = {I.rootHi[0] - I.centre[0], I.rootHi[1] - I.centre[1], I.rootHi[2] - I.centre[2]};
+    double tn, tf;
+    slabApprox(lo, hi, oc, ia, tn, tf);
+    const bool in = (inMask & bit) != 0;
+    if (COUNT && in) C.box++;
+    const bool alive = in && !(tn > tf || tf < tLow || tn > hit.t);
+    uint32_t live = __ballot_sync(RT_FULL, alive);
+    if (!live) return 0u;
+    double t0 = tn > 0.0 ? tn : 0.0;
+    if (!(t0 < 1e300)) t0 = 0.0;
+    V3 o2 = oc + dL * t0;
+    const float ox = (float)o2.x, oy = (float)o2.y, oz = (float)o2.z;
+    const float ix = fminf(fmaxf(1.0f / (float)dL.x, -1e30f), 1e30f);
+    const float iy = fminf(fmaxf(1.0f / (float)dL.y, -1e30f), 1e30f);
+    const float iz = fminf(fmaxf(1.0f / (float)dL.z, -1e30f), 1e30f);
+    const float nx = -(ox * ix), ny = -(oy * iy), nz = -(oz * iz);
+    const float tminF = __double2float_rd(tLow - t0);
+    float tmaxF = __double2float_ru(hit.t - t0);
+
+    const GNode* nodes = S.nodes + I.nodeBase;
+    uint32_t occluded = 0u;
+    int sp = 0;
+    int32_t cur = I.rootRef;
+    uint32_t curMask = live;
+
+#define RT_PACKET_POP()                                  \
+    for (;;) {                                           \
+        if (sp == 0) return occluded;                    \
+        --sp;                                            \
+        const int2 e_ = wstack[sp];                      \
+        cur = e_.x;                                      \
+        curMask = (uint32_t)e_.y & live;                 \
+        if (curMask) break;                              \
+    }
+
+    for (;;) {
+        while ((uint32_t)cur < 0x7fffffffu) {  // inner node, fetched once for the warp
+            const float4* np = reinterpret_cast<const float4*>(nodes + cur);
+            const float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2);
+            const int4 ch = __ldg(reinterpret_cast<const int4*>(np + 3));
+            const bool inl = (curMask & bit) != 0;
+            if (COUNT && inl) C.box += 2;
+            float a0 = __fmaf_rn(q0.x, ix, nx), b0 = __fmaf_rn(q0.w, ix, nx);
+            float a1 = __fmaf_rn(q0.y, iy, ny), b1 = __fmaf_rn(q1.x, iy, ny);
+            float a2 = __fmaf_rn(q0.z, iz, nz), b2 = __fmaf_rn(q1.y, iz, nz);
+            float n0 = fmaxf(fmaxf(fminf(a0, b0), fminf(a1, b1)), fmaxf(fminf(a2, b2), tminF));
+            float f0 = fminf(fminf(fmaxf(a0, b0), fmaxf(a1, b1)), fminf(fmaxf(a2, b2), tmaxF));
+            float c0 = __fmaf_rn(q1.z, ix, nx), d0 = __fmaf_rn(q2.y, ix, nx);
+            float c1 = __fmaf_rn(q1.w, iy, ny), d1 = __fmaf_rn(q2.z, iy, ny);
+            float c2 = __fmaf_rn(q2.x, iz, nz), d2 = __fmaf_rn(q2.w, iz, nz);
+            float n1 = fmaxf(fmaxf(fminf(c0, d0), fminf(c1, d1)), fmaxf(fminf(c2, d2), tminF));
+            float f1 = fminf(fminf(fmaxf(c0, d0), fmaxf(c1, d1)), fminf(fmaxf(c2, d2), tmaxF));
+            const bool h0 = inl && n0 <= f0, h1 = inl && n1 <= f1;
+            const uint32_t m0 = __ballot_sync(RT_FULL, h0), m1 = __ballot_sync(RT_FULL, h1);
+            if (m0 && m1) {
+                const uint32_t v1 = __ballot_sync(RT_FULL, h1 && (!h0 || n1 < n0));   // lanes preferring child 1
+                const bool swap = 2 * __popc(v1) > __popc(m0 | m1);
+                wstack[sp] = swap ? make_int2(ch.x, (int)m0) : make_int2(ch.y, (int)m1);
+                sp++;
+                if (COUNT && sp > C.maxStack) C.maxStack = sp;
+                cur = swap ? ch.y : ch.x;
+                curMask = swap ? m1 : m0;
+            } else if (m0) {
+                cur = ch.x; curMask = m0;
+            } else if (m1) {
+                cur = ch.y; curMask = m1;
+            } else {
+                RT_PACKET_POP();
+            }
+        }
+        if (cur != kEmptyRef) {  // leaf: triangles fetched once for the warp, tested by the lanes in curMask
+            const uint32_t ref = ~(uint32_t)cur;
+            const int first = I.triBase + (int)(ref >> 3), count = (int)(ref & 7u) + 1;
+            const bool inl = (curMask & bit) != 0;
+            bool occ = false;
+            for (int k = 0; k < count; k++) {
+                V3 v0, v1, v2;
+                loadTri(S, I, first + k, v0, v1, v2);
+                if (inl && !occ) {
+                    if (COUNT) C.tri++;
+                    double t, u, v;
+                    if (mtTest(v0, v1, v2, oL, dL, eps, t, u, v) && inWindow(t, tLow, hit.t, anyhit)) {
+                        if (anyhit) {
+                            occ = true;
+                        } else {
+                            hit.t = t; hit.u = u; hit.v = v; hit.inst = instIdx; hit.slot = first + k;
+                            tmaxF = __double2float_ru(t - t0);
+                        }
+                    }
+                }
+            }
+            if (anyhit) {
+                const uint32_t o = __ballot_sync(RT_FULL, occ);
+                occluded |= o;
+                live &= ~o;
+                if (!live) return occluded;
+            }
+        }
+        RT_PACKET_POP();
+    }
+#undef RT_PACKET_POP
+}
+
+// One instance for the lanes in inMask (warp-uniform instance index): RTContext.swift:657-705.
+template <bool COUNT>
+__device__ __forceinline__ uint32_t packetInstance(const DeviceScene& S, int idx, V3 o, V3 d, double eps, double tMin,
+                                                   HitRec& hit, bool anyhit, uint32_t inMask, int2* wstack, Counters& C) {
+    const GInstance& I = S.instances[idx];
+    const bool in = (inMask >> (threadIdx.x & 31)) & 1u;
+    V3 oL, dL;
+    toLocal(I, o, d, oL, dL);
+    if (COUNT && in) C.inst++;
+    const double tLow = dmax(eps, tMin);
+    if (I.kind == INST_MESH) return packetBlas<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, inMask, wstack, C);
+    bool occ = false;
+    if (in) occ = analyticInstance<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, C);
+    return __ballot_sync(RT_FULL, occ);   // always 0 for closest-hit queries
+}
+
+// Packet TLAS walk.  `active`: this lane carries a ray.  Closest hit: updates hit; any-hit (hit.t = tMax):
+// returns true for the lanes whose ray is occluded.
+template <bool COUNT>
+__device__ __forceinline__ bool packetScene(const DeviceScene& S, V3 o, V3 d, double tMin, HitRec& hit, bool active,
+                                            bool anyhit, int2* wstack, Counters& C) {
+    const uint32_t bit = 1u << (threadIdx.x & 31);
+    uint32_t live = __ballot_sync(RT_FULL, active);
+    if (!live) return false;
+    const double eps = S.eps;
+    int32_t cur = S.tlasRootRef;
+    if (cur == kEmptyRef) return false;
+    if (cur < 0) return (packetInstance<COUNT>(S, ~cur, o, d, eps, tMin, hit, anyhit, live, wstack, C) & bit) != 0;
+    const V3 ia = refinedInv(d);
+    const double tLow = dmax(eps, tMin);
+    int2* tstack = wstack + RT_WSTACK;
+    uint32_t occluded = 0u, curMask = live;
+    int sp = 0;
+    for (;;) {
+        bool descended = false;
+        if (cur >= 0) {
+            const TNode& n = S.tlas[cur];
+            double n0, f0, n1, f1;
+            slabApprox(n.lo0, n.hi0, o, ia, n0, f0);
+            slabApprox(n.lo1, n.hi1, o, ia, n1, f1);
+            const bool inl = (curMask & bit) != 0;
+            if (COUNT && inl) C.box += 2;
+            const bool h0 = inl && !(n0 > f0) && !(f0 < tLow) && !(n0 > hit.t);
+            const bool h1 = inl && !(n1 > f1) && !(f1 < tLow) && !(n1 > hit.t);
+            const uint32_t m0 = __ballot_sync(RT_FULL, h0), m1 = __ballot_sync(RT_FULL, h1);
+            if (m0 && m1) {
+                const uint32_t v1 = __ballot_sync(RT_FULL, h1 && (!h0 || n1 < n0));
+                const bool swap = 2 * __popc(v1) > __popc(m0 | m1);
+                if (sp < RT_WTSTACK) { tstack[sp] = swap ? make_int2(n.child0, (int)m0) : make_int2(n.child1, (int)m1); sp++; }
+                cur = swap ? n.child1 : n.child0;
+                curMask = swap ? m1 : m0;
+                descended = true;
+            } else if (m0) { cur = n.child0; curMask = m0; descended = true; }
+            else if (m1) { cur = n.child1; curMask = m1; descended = true; }
+        } else {
+            const uint32_t o_ = packetInstance<COUNT>(S, ~cur, o, d, eps, tMin, hit, anyhit, curMask, wstack, C);
+            if (anyhit) {
+                occluded |= o_;
+                live &= ~o_;
+                if (!live) return (occluded & bit) != 0;
+            }
+        }
+        if (descended) continue;
+        for (;;) {
+            if (sp == 0) return (occluded & bit) != 0;
+            --sp;
+            const int2 e = tstack[sp];
+            cur = e.x;
+            curMask = (uint32_t)e.y & live;
+            if (curMask) break;
+        }
+    }
+}
+
+}  // namespace rtg

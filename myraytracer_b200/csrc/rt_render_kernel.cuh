@@ -1,0 +1,331 @@
+// rt_render_kernel.cuh — the persistent render kernels for sm_100a.   COMPILE WITH -fmad=false.
+//
+// One kernel replaces the reference's whole per-frame loop:
+//   Renderer.render pixel/sample loops     Extensions/Object+Extension.swift:285-361
+//   primary-ray generation                 :292-344      (PCG32 :556-589)
+//   trace closure                          :96-283       (rt_shade.cuh)
+//   sample average                         :354
+//   RGBA8 conversion                       RayTracer.swift:186-195
+// Work distribution (both kernels): warps pull 8x4-pixel tiles of the rank's 8-row chunks (the
+// reference's chunk unit, :75-82) from a global atomic counter (persistent threads).
+//
+//   renderKernelFast    lane = one (pixel, sample) item; the tile's 32*n*n items are walked 32 at a
+//                       time with the samples of a pixel in adjacent lanes (maximum ray coherence).
+//                       Depth 0 — the primary ray and its shadow rays — runs as a warp packet
+//                       (rt_packet.cuh) through ONE traversal call site; spawned children go to the
+//                       per-lane depth-first loop (rt_shade.cuh).  Sample s of a pixel starts its PCG32 stream 3 (5 with
+//                       DOF) draws after sample s-1 (:307-340), reached by the LCG skip-ahead; this is
+//                       exact as long as no draw happens inside `trace`, i.e. every material has
+//                       roughness == 0 (:191,210,259) — the host checks that.  The per-pixel sum is
+//                       formed in sample order (shuffles), so the FP64 result equals the sequential one.
+//   renderKernelGeneral lane = one pixel looping over its samples with one sequential PCG32 stream and
+//                       the per-lane traversal: the general path (glossy materials draw inside the recursion).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "rt_shade.cuh"
+
+namespace rtg {
+
+#ifndef RT_MIN_BLOCKS
+#define RT_MIN_BLOCKS 3
+#endif
+
+struct PrimaryRay {
+    V3 o, d;
+    double tMin;
+};
+
+// Object+Extension.swift:307-344 for sample (sx, sy) of pixel (i, j); draws xi1, xi2, [lens u, v], time.
+__device__ __forceinline__ PrimaryRay primaryRay(const CameraParams& cam, int i, int j, int sx, int sy, PCG32& rng) {
+    const V3 eye = ld3(cam.eye), cu = ld3(cam.u), cv = ld3(cam.v), cw = ld3(cam.w), q00 = ld3(cam.q00), cm = ld3(cam.m);
+    const int n = cam.n;
+    const double xi1 = rng.nextFloat();
+    const double xi2 = rng.nextFloat();
+    const double iOffset = ((double)sx + xi1) / (double)n;
+    const double jOffset = ((double)sy + xi2) / (double)n;
+    const double currentI = (double)i + iOffset;
+    const double currentJ = (double)j + jOffset;
+    const V3 vOff = cv * (currentJ * cam.dv);
+    const V3 rowTopLeft = q00 - vOff;
+    const V3 uOff = cu * (currentI * cam.du);
+    const V3 s = rowTopLeft + uOff;
+    const V3 dir0 = normalize(s - eye);
+    PrimaryRay r;
+    r.d = dir0; r.o = eye;
+    if (cam.dof) {  // :325-338
+        const V3 forward = -cw;
+        const double denom = dot(dir0, forward);
+        const double tFocus = fabs(denom) < 1e-6 ? cam.focus : (cam.focus / denom);
+        const V3 pFocus = eye + dir0 * tFocus;
+        const double uRand = rng.nextFloat() - 0.5;
+        const double vRand = rng.nextFloat() - 0.5;
+        const V3 lensOffset = (uRand * cu + vRand * cv) * cam.aperture;
+        const V3 a = eye + lensOffset;
+        r.d = normalize(pFocus - a);
+        r.o = a;
+    }
+    (void)rng.nextFloat();  // ray time: always drawn (:340); no motion in supported scenes
+    const double denomW = dot(r.d, cw);
+    const double tImg = dot(cm - r.o, cw) / (denomW == 0.0 ? 4.9406564584124654e-324 : denomW);  // :342
+    r.tMin = dmax(tImg, 0.0);
+    return r;
+}
+
+__device__ __forceinline__ void writePixel(const RenderTargets& out, size_t pix, V3 c) {
+    if (out.linear) { out.linear[pix * 3] = c.x; out.linear[pix * 3 + 1] = c.y; out.linear[pix * 3 + 2] = c.z; }
+    if (out.rgba) {
+        uchar4 q;
+        q.x = quantize(c.x); q.y = quantize(c.y); q.z = quantize(c.z); q.w = 255;
+        reinterpret_cast<uchar4*>(out.rgba)[pix] = q;
+    }
+}
+
+template <bool COUNT>
+__device__ __forceinline__ void flushCounters(const RenderTargets& out, Counters& C, RayCounts& R) {
+    for (int off = 16; off > 0; off >>= 1) {
+        R.primary += __shfl_down_sync(0xffffffffu, R.primary, off);
+        R.shadow += __shfl_down_sync(0xffffffffu, R.shadow, off);
+        R.secondary += __shfl_down_sync(0xffffffffu, R.secondary, off);
+        if (COUNT) {
+            C.box += __shfl_down_sync(0xffffffffu, C.box, off);
+            C.tri += __shfl_down_sync(0xffffffffu, C.tri, off);
+            C.sphere += __shfl_down_sync(0xffffffffu, C.sphere, off);
+            C.plane += __shfl_down_sync(0xffffffffu, C.plane, off);
+            C.inst += __shfl_down_sync(0xffffffffu, C.inst, off);
+            C.smooth += __shfl_down_sync(0xffffffffu, C.smooth, off);
+            int m = __shfl_down_sync(0xffffffffu, C.maxStack, off);
+            if (m > C.maxStack) C.maxStack = m;
+        }
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&out.counters[0], R.primary);
+        atomicAdd(&out.counters[1], R.shadow);
+        atomicAdd(&out.counters[2], R.secondary);
+        if (COUNT) {
+            atomicAdd(&out.counters[3], C.box);
+            atomicAdd(&out.counters[4], C.tri);
+            atomicAdd(&out.counters[5], C.sphere);
+            atomicAdd(&out.counters[6], C.plane);
+            atomicAdd(&out.counters[7], C.inst);
+            atomicMax(&out.counters[8], (unsigned long long)C.maxStack);
+            atomicAdd(&out.counters[9], C.smooth);
+        }
+    }
+}
+
+struct TileMap {
+    int tilesX, totalTiles, shardCount, shardIndex;
+    __device__ __forceinline__ TileMap(const CameraParams& cam) {
+        tilesX = (cam.width + 7) >> 3;
+        const int nChunks = (cam.height + 7) >> 3;
+        shardCount = cam.shardCount < 1 ? 1 : cam.shardCount;
+        shardIndex = cam.shardIndex;
+        const int owned = (nChunks - shardIndex + shardCount - 1) / shardCount;
+        totalTiles = owned * tilesX * 2;
+    }
+    // tile -> pixel origin (x0, y0) of its 8x4 block
+    __device__ __forceinline__ void origin(int tile, int& x0, int& y0) const {
+        const int k = tile / (tilesX * 2), rem = tile - k * (tilesX * 2);
+        const int ty = rem / tilesX, tx = rem - ty * tilesX;
+        x0 = tx * 8;
+        y0 = (k * shardCount + shardIndex) * 8 + ty * 4;
+    }
+};
+
+__device__ __forceinline__ double shflD(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
+
+template <bool COUNT>
+__global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS) renderKernelFast(DeviceScene S, CameraParams cam, RenderTargets out) {
+    __shared__ int32_t sstack[RT_STACK * RT_BLOCK];
+    __shared__ int2 wstacks[(RT_BLOCK / 32) * RT_WARP_STACK_INT2];
+    const int lane = threadIdx.x & 31;
+    TraceScratch T;
+    T.sstack = sstack;
+    T.wstack = wstacks + (threadIdx.x >> 5) * RT_WARP_STACK_INT2;
+    T.pathStack = out.pathStack;
+    T.gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    T.stride = (size_t)gridDim.x * blockDim.x;
+
+    Counters C;
+    C.box = C.tri = C.sphere = C.plane = C.inst = C.smooth = 0; C.maxStack = 0;
+    RayCounts R;
+    R.primary = R.shadow = R.secondary = 0;
+
+    const int W = cam.width, H = cam.height;
+    const TileMap tiles(cam);
+    const int n = cam.n, ns = n * n;                 // samples traced per pixel (:298-306)
+    const int drawsPerSample = cam.dof ? 5 : 3;      // xi1, xi2, [lens u, v], time
+    const double samplesD = (double)cam.samples;     // the sum is divided by `samples` (:354)
+    const bool segmented = ns < 32 && (32 % ns) == 0;
+    const V3 ambient = ld3(S.ambient), background = ld3(S.background);
+
+    for (;;) {
+        int tile = 0;
+        if (lane == 0) tile = atomicAdd(out.tileCounter, 1);
+        tile = __shfl_sync(0xffffffffu, tile, 0);
+        if (tile >= tiles.totalTiles) break;
+        int x0, y0;
+        tiles.origin(tile, x0, y0);
+        int openP = -1;               // ordered accumulation state of the generic path (warp-uniform)
+        V3 acc = mk(0, 0, 0);
+#pragma unroll 1
+        for (int it = 0; it < ns; it++) {
+            const int g = it * 32 + lane;
+            const int p = g / ns, s = g - p * ns;
+            // pixel p of the tile in Z-order: neighbouring lanes' pixels form compact blocks
+            const int px = (p & 1) | ((p >> 1) & 2) | ((p >> 2) & 4), py = ((p >> 1) & 1) | ((p >> 2) & 2);
+            const int i = x0 + px, j = y0 + py;
+            const bool active = i < W && j < H;
+            const int sy = s / n, sx = s - sy * n;
+            PCG32 rng;
+            rng.seed((((uint64_t)j << 32) ^ (uint64_t)i) + 0x9E3779B97F4A7C15ULL);  // :294 (Swift precedence)
+            rng.advance((uint64_t)(s * drawsPerSample));
+            const PrimaryRay pr = primaryRay(cam, i, j, sx, sy, rng);
+            if (active) R.primary++;
+            PathEntry cur0;
+            cur0.o = pr.o; cur0.d = pr.d; cur0.w = mk(1, 1, 1); cur0.beerMat = 0; cur0.depth = 0; cur0.beer = 0;
+
+            // ---- depth 0 as a warp packet: one traversal call site serves the primary ray (phase 0)
+            //      and the shadow ray towards light phase-1 (:118-143)
+            V3 ro = pr.o, rd = pr.d, wi = mk(0, 0, 1), Lo = mk(0, 0, 0);
+            double rtMin = pr.tMin, dist = 0;
+            HitRec hit;
+            hit.t = CUDART_INF; hit.u = hit.v = 0; hit.inst = -1; hit.slot = 0;
+            ShadePoint sp;
+            sp.p = sp.N = sp.w = mk(0, 0, 0); sp.mat = S.materials; sp.matId = 0; sp.frontFacing = sp.computeDirect = false;
+            bool rayOn = active, anyhit = false, isHit = false;
+            int phase = 0;
+            __syncwarp();
+#pragma unroll 1
+            for (;;) {
+                const bool occ = packetScene<COUNT>(S, ro, rd, rtMin, hit, rayOn, anyhit, T.wstack, C);
+                if (phase == 0) {
+                    isHit = active && hit.inst >= 0;
+                    Surface sf;
+                    sf.kind = 0; sf.prim = -1;
+                    if (isHit) {
+                        resolveHit(S, hit, pr.o, pr.d, sf);
+                        if (COUNT && sf.kind == 1 && S.instances[hit.inst].smooth) C.smooth++;
+                        setupShade(S, sf, cur0, hit.t, sp);
+                        if (sp.computeDirect) Lo = ambient * ld3(sp.mat->ambient);
+                    }
+                    if (out.ids && active) {
+                        HitId& h = out.ids[((size_t)j * W + i) * (size_t)ns + (size_t)s];
+                        h.inst = hit.inst; h.kind = sf.kind; h.prim = sf.prim; h.t = hit.t;
+                    }
+                    if (__ballot_sync(0xffffffffu, sp.computeDirect) == 0u) break;
+                } else if (rayOn && !occ) {
+                    Lo = Lo + pointLightTerm(*sp.mat, S.pointLights[phase - 1], sp.N, pr.d, wi, dist);
+                }
+                if (phase >= S.nPointLights) break;
+                shadowRay(S.pointLights[phase], sp.p, S.shadowEps, ro, wi, dist);
+                rd = wi; rtMin = 0.0;
+                hit.t = dist;                                   // tMax = dist (:124)
+                rayOn = sp.computeDirect; anyhit = true;
+                if (rayOn) R.shadow++;
+                phase++;
+            }
+            // ---- the value of trace(...) for this sample (:345): miss -> background, NaN guard, recursion
+            V3 c = mk(0, 0, 0);
+            if (active) {
+                if (!isHit) {
+                    c = c + cur0.w * background;                                        // :101-103
+                } else if (finite3(Lo)) {                                               // :277-280
+                    c = c + sp.w * Lo;
+                    PathEntry c1, c2;
+                    const int nc = spawnChildren(S, sp, cur0, rng, c1, c2);
+                    if (nc > 0) {
+                        if (nc == 2) pathStore(T.pathStack, T.stride, T.gtid, 0, c2);
+                        R.secondary += nc;
+                        c = scalarPathLoop<COUNT>(S, T, c1, nc - 1, false, 0.0, nullptr, rng, C, R, c);
+                    }
+                }
+            }
+            __syncwarp();
+            // ---- pixelColor += trace(...) in sample order (:345), then / samples (:354)
+            if (segmented) {
+                const int base = lane & ~(ns - 1);
+                V3 sum = mk(0, 0, 0);
+#pragma unroll 1
+                for (int k = 0; k < ns; k++) {
+                    const V3 ck = mk(shflD(c.x, base + k), shflD(c.y, base + k), shflD(c.z, base + k));
+                    sum = sum + ck;
+                }
+                if (active && s == 0) writePixel(out, (size_t)j * W + i, sum / samplesD);
+            } else {
+#pragma unroll 1
+                for (int k = 0; k < 32; k++) {
+                    const int pk = (it * 32 + k) / ns;
+                    const V3 ck = mk(shflD(c.x, k), shflD(c.y, k), shflD(c.z, k));
+                    if (pk != openP) {
+                        if (openP >= 0 && lane == 0) {
+                            const int qx = (openP & 1) | ((openP >> 1) & 2) | ((openP >> 2) & 4), qy = ((openP >> 1) & 1) | ((openP >> 2) & 2);
+                            if (x0 + qx < W && y0 + qy < H) writePixel(out, (size_t)(y0 + qy) * W + (x0 + qx), acc / samplesD);
+                        }
+                        openP = pk;
+                        acc = mk(0, 0, 0);
+                    }
+                    acc = acc + ck;
+                }
+            }
+        }
+        if (!segmented && openP >= 0 && lane == 0) {
+            const int qx = (openP & 1) | ((openP >> 1) & 2) | ((openP >> 2) & 4), qy = ((openP >> 1) & 1) | ((openP >> 2) & 2);
+            if (x0 + qx < W && y0 + qy < H) writePixel(out, (size_t)(y0 + qy) * W + (x0 + qx), acc / samplesD);
+        }
+    }
+    flushCounters<COUNT>(out, C, R);
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS) renderKernelGeneral(DeviceScene S, CameraParams cam, RenderTargets out) {
+    __shared__ int32_t sstack[RT_STACK * RT_BLOCK];
+    const int lane = threadIdx.x & 31;
+    TraceScratch T;
+    T.sstack = sstack;
+    T.wstack = nullptr;
+    T.pathStack = out.pathStack;
+    T.gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    T.stride = (size_t)gridDim.x * blockDim.x;
+
+    Counters C;
+    C.box = C.tri = C.sphere = C.plane = C.inst = C.smooth = 0; C.maxStack = 0;
+    RayCounts R;
+    R.primary = R.shadow = R.secondary = 0;
+
+    const int W = cam.width, H = cam.height;
+    const TileMap tiles(cam);
+    const int n = cam.n, samples = cam.samples;
+
+    for (;;) {
+        int tile = 0;
+        if (lane == 0) tile = atomicAdd(out.tileCounter, 1);
+        tile = __shfl_sync(0xffffffffu, tile, 0);
+        if (tile >= tiles.totalTiles) break;
+        int x0, y0;
+        tiles.origin(tile, x0, y0);
+        const int i = x0 + (lane & 7), j = y0 + (lane >> 3);
+        if (i >= W || j >= H) continue;
+
+        PCG32 rng;
+        rng.seed((((uint64_t)j << 32) ^ (uint64_t)i) + 0x9E3779B97F4A7C15ULL);  // :294 (Swift precedence)
+        V3 pixel = mk(0, 0, 0);
+        int sampleIndex = 0;
+        for (int sy = 0; sy < n && sampleIndex < samples; sy++) {
+            for (int sx = 0; sx < n && sampleIndex < samples; sx++) {
+                const PrimaryRay pr = primaryRay(cam, i, j, sx, sy, rng);
+                R.primary++;
+                HitId* idSlot = out.ids ? out.ids + (((size_t)j * W + i) * (size_t)(n * n) + (size_t)(sy * n + sx)) : nullptr;
+                PathEntry cur0;
+                cur0.o = pr.o; cur0.d = pr.d; cur0.w = mk(1, 1, 1); cur0.beerMat = 0; cur0.depth = 0; cur0.beer = 0;
+                pixel = pixel + scalarPathLoop<COUNT>(S, T, cur0, 0, true, pr.tMin, idSlot, rng, C, R, mk(0, 0, 0));
+                sampleIndex++;
+            }
+        }
+        writePixel(out, (size_t)j * W + i, pixel / (double)samples);                                   // :354
+    }
+    flushCounters<COUNT>(out, C, R);
+}
+
+}  // namespace rtg

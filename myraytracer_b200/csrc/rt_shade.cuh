@@ -1,0 +1,279 @@
+// rt_shade.cuh — the trace closure of the reference as an explicit depth-first loop (device).
+//
+//   trace (shading + recursion)            Extensions/Object+Extension.swift:96-283
+//   Fresnel / reflect / Beer helpers       :467-505, orthonormalBasis :530-552
+// The recursion is an explicit per-thread stack of (ray, throughput) entries processed depth-first,
+// reflection before refraction, which keeps the reference's RNG draw order (scalarPathLoop).  The pieces
+// (surface set-up, one point light, child-ray spawning) are shared with the packet kernel, which handles
+// depth 0 itself and hands spawned children to scalarPathLoop.
+#pragma once
+#include <math_constants.h>
+
+#include "rt_kernels.h"
+#include "rt_packet.cuh"
+
+namespace rtg {
+
+#define PATH_FIELDS 11
+
+struct PathEntry {
+    V3 o, d, w;
+    long long beerMat;   // Hit.mat of the dielectric surface this refraction ray entered
+    int depth;
+    int beer;            // 1: apply Beer attenuation at the next hit (Object+Extension.swift:245-248)
+};
+
+__device__ __forceinline__ void pathStore(double* base, size_t stride, size_t gtid, int level, const PathEntry& e) {
+    double* p = base + ((size_t)level * PATH_FIELDS) * stride + gtid;
+    p[0 * stride] = e.o.x; p[1 * stride] = e.o.y; p[2 * stride] = e.o.z;
+    p[3 * stride] = e.d.x; p[4 * stride] = e.d.y; p[5 * stride] = e.d.z;
+    p[6 * stride] = e.w.x; p[7 * stride] = e.w.y; p[8 * stride] = e.w.z;
+    p[9 * stride] = __longlong_as_double(e.beerMat);
+    p[10 * stride] = __longlong_as_double((long long)e.depth | ((long long)e.beer << 32));
+}
+__device__ __forceinline__ void pathLoad(const double* base, size_t stride, size_t gtid, int level, PathEntry& e) {
+    const double* p = base + ((size_t)level * PATH_FIELDS) * stride + gtid;
+    e.o = mk(p[0 * stride], p[1 * stride], p[2 * stride]);
+    e.d = mk(p[3 * stride], p[4 * stride], p[5 * stride]);
+    e.w = mk(p[6 * stride], p[7 * stride], p[8 * stride]);
+    e.beerMat = __double_as_longlong(p[9 * stride]);
+    long long m = __double_as_longlong(p[10 * stride]);
+    e.depth = (int)(m & 0xffffffffLL);
+    e.beer = (int)(m >> 32);
+}
+
+__device__ __forceinline__ V3 reflectDir(V3 d, V3 n) { return d - 2.0 * dot(d, n) * n; }  // :467
+
+// :530-552
+__device__ __forceinline__ void orthonormalBasis(V3 n, V3& tangent, V3& bitangent) {
+    double sign = n.z >= 0 ? 1.0 : -1.0;
+    double a = -1.0 / (sign + n.z);
+    double b = n.x * n.y * a;
+    tangent = normalize(mk(1.0 + sign * n.x * n.x * a, sign * b, -sign * n.x));
+    bitangent = normalize(mk(b, sign + n.y * n.y * a, -n.y));
+}
+
+// :476-490
+__device__ __forceinline__ void fresnelDielectric(double n1, double n2, double cosI, double& R, bool& hasCosT, double& cosT,
+                                                  double& sin2T) {
+    double cosTheta = dmax(0.0, dmin(1.0, fabs(cosI)));
+    double eta = n1 / n2;
+    sin2T = eta * eta * dmax(0.0, 1.0 - cosTheta * cosTheta);
+    if (sin2T > 1.0) { R = 1.0; hasCosT = false; cosT = 0; return; }
+    double cosPhi = sqrt(dmax(0.0, 1.0 - sin2T));
+    double Rs = (n2 * cosTheta - n1 * cosPhi) / (n2 * cosTheta + n1 * cosPhi);
+    double Rp = (n1 * cosTheta - n2 * cosPhi) / (n1 * cosTheta + n2 * cosPhi);
+    R = 0.5 * (Rs * Rs + Rp * Rp);
+    hasCosT = true; cosT = cosPhi;
+}
+
+// :492-505
+__device__ __forceinline__ double fresnelConductor(double eta, double k, double cosI_) {
+    double cosI = dmax(0.0, dmin(1.0, fabs(cosI_)));
+    double cos2 = cosI * cosI;
+    double eta2k2 = eta * eta + k * k;
+    double twoEtaCos = 2.0 * eta * cosI;
+    double Rs = (eta2k2 - twoEtaCos + cos2) / (eta2k2 + twoEtaCos + cos2);
+    double Rp = ((eta2k2 * cos2) - twoEtaCos + 1.0) / ((eta2k2 * cos2) + twoEtaCos + 1.0);
+    return 0.5 * (Rs + Rp);
+}
+
+__device__ __forceinline__ unsigned char quantize(double c) {  // RayTracer.swift:189-193
+    double x = dmin(dmax(c, 0.0), 255.0);
+    return (unsigned char)(int)x;
+}
+
+
+struct RayCounts {
+    unsigned long long primary, shadow, secondary;
+};
+
+struct TraceScratch {
+    int32_t* sstack;   // per-lane traversal stacks (shared memory, RT_STACK x RT_BLOCK)
+    int2* wstack;      // this warp's packet stack (shared memory, RT_WARP_STACK_INT2)
+    double* pathStack; // per-thread recursion stack (global)
+    size_t stride, gtid;
+};
+
+// What `trace` derives from a hit before lighting it (Object+Extension.swift:105-117).
+struct ShadePoint {
+    V3 p, N;               // hit point, face-forwarded normal
+    V3 w;                  // throughput of this path vertex (after Beer attenuation)
+    const GMaterial* mat;
+    long long matId;       // Hit.mat
+    bool frontFacing, computeDirect;
+};
+
+__device__ __forceinline__ void setupShade(const DeviceScene& S, const Surface& sf, const PathEntry& cur, double hitT, ShadePoint& sp) {
+    long long mi = sf.mat - 1;                                                          // :105
+    if (mi > (long long)S.nMaterials - 1) mi = (long long)S.nMaterials - 1;
+    if (mi < 0) mi = 0;
+    const GMaterial& mat = S.materials[mi];
+    sp.mat = &mat;
+    sp.matId = sf.mat;
+    V3 w = cur.w;
+    if (cur.beer && sf.mat == cur.beerMat) {                                            // :245-248
+        const double dist = dmax(hitT, 0.0);
+        if (isfinite(dist) && dist > 0)
+            w = w * mk(exp(-mat.absorption[0] * dist), exp(-mat.absorption[1] * dist), exp(-mat.absorption[2] * dist));
+    }
+    sp.w = w;
+    sp.p = sf.p;
+    sp.frontFacing = dot(cur.d, sf.n) < 0;                                               // :109
+    sp.N = sp.frontFacing ? sf.n : -sf.n;
+    sp.computeDirect = !(mat.ior > 0) || sp.frontFacing;                                // :112-115
+}
+
+// Shadow ray towards one point light (:120-124): direction, distance (= tMax), offset origin.
+__device__ __forceinline__ void shadowRay(const GPointLight& pl, V3 p, double shadowEps, V3& org, V3& wi, double& dist) {
+    wi = ld3(pl.position) - p;
+    dist = length(wi);
+    wi = normalize(wi);
+    org = p + wi * shadowEps;
+}
+
+// Blinn-Phong term of one visible point light (:126-140).
+__device__ __forceinline__ V3 pointLightTerm(const GMaterial& mat, const GPointLight& pl, V3 N, V3 rayDir, V3 wi, double dist) {
+    const double NdotL = dmax(0.0, dot(N, wi));
+    if (!(NdotL > 0)) return mk(0, 0, 0);
+    const double shininess = dmax(1.0, mat.phong);
+    const V3 Ld = ld3(mat.diffuse) * NdotL;
+    const V3 view = normalize(-rayDir);
+    const V3 h = normalize(wi + view);
+    const double NdotH = dmax(0.0, dot(N, h));
+    const V3 Ls = ld3(mat.specular) * pow(NdotH, shininess);
+    const V3 atten = ld3(pl.intensity) / dmax(dist * dist, 1e-12);
+    return (Ld + Ls) * atten;
+}
+
+// Recursive branches of `trace` (:189-275): fills c1 (always) and c2 (refraction) and returns the child count.
+__device__ __forceinline__ int spawnChildren(const DeviceScene& S, const ShadePoint& sp, const PathEntry& cur, PCG32& rng,
+                                             PathEntry& c1, PathEntry& c2) {
+    const GMaterial& mat = *sp.mat;
+    if (!(cur.depth < S.maxDepth) || mat.type == 0) return 0;
+    const double shadowEps = S.shadowEps;
+    const V3 p = sp.p, N = sp.N, w = sp.w;
+    int count = 1;
+    c1.depth = c2.depth = cur.depth + 1;
+    c1.beer = c2.beer = 0; c1.beerMat = c2.beerMat = 0;
+    if (mat.type == 1) {                                                                // mirror :189-206
+        V3 rd = normalize(reflectDir(cur.d, N));
+        if (mat.roughness != 0) {
+            V3 t, b;
+            orthonormalBasis(rd, t, b);
+            const double rand1 = rng.nextFloat() - 0.5;
+            const double rand2 = rng.nextFloat() - 0.5;
+            rd = rd + (mat.roughness * rand1) * b + (mat.roughness * rand2) * t;
+            rd = normalize(rd);
+        }
+        c1.o = p + N * shadowEps; c1.d = rd; c1.w = w * ld3(mat.mirror);
+    } else if (mat.type == 2) {                                                         // dielectric :207-251
+        V3 mN = N;
+        if (mat.roughness != 0) {
+            V3 t, b;
+            orthonormalBasis(N, t, b);
+            const double r1 = (rng.nextFloat() * 2.0) - 1.0;
+            const double r2 = (rng.nextFloat() * 2.0) - 1.0;
+            mN = normalize(N + (t * r1 * mat.roughness) + (b * r2 * mat.roughness));
+        }
+        const bool entering = sp.frontFacing;
+        const double n1 = entering ? 1.0 : mat.ior;
+        const double n2 = entering ? mat.ior : 1.0;
+        const double cosI = -dot(cur.d, mN);
+        double Rf, cosT, sin2T;
+        bool hasCosT;
+        fresnelDielectric(n1, n2, cosI, Rf, hasCosT, cosT, sin2T);
+        const V3 rd = normalize(reflectDir(cur.d, mN));
+        c1.o = p + rd * shadowEps; c1.d = rd;
+        if (!hasCosT || sin2T > 1) {
+            c1.w = w;                                                                   // total internal reflection :235-236
+        } else {
+            c1.w = w * Rf;
+            const double eta = n1 / n2;
+            const V3 td = normalize((cur.d * eta) + (mN * (eta * cosI - cosT)));
+            c2.o = p + td * shadowEps; c2.d = td; c2.w = w * (1.0 - Rf);
+            c2.beer = (entering && mat.hasAbsorption) ? 1 : 0;
+            c2.beerMat = sp.matId;
+            count = 2;
+        }
+    } else {                                                                            // conductor :252-275
+        const double cosI = dmax(0.0, -dot(cur.d, N));
+        const double Rf = fresnelConductor(mat.ior, mat.absorptionIndex, cosI);
+        V3 rd = normalize(reflectDir(cur.d, N));
+        if (mat.roughness != 0) {
+            V3 t, b;
+            orthonormalBasis(rd, t, b);
+            const double rand1 = rng.nextFloat() - 0.5;
+            const double rand2 = rng.nextFloat() - 0.5;
+            rd = rd + (mat.roughness * rand1) * b + (mat.roughness * rand2) * t;
+            rd = normalize(rd);
+        }
+        c1.o = p + N * shadowEps; c1.d = rd; c1.w = w * (mk(Rf, Rf, Rf) * ld3(mat.mirror));
+    }
+    return count;
+}
+
+// Depth-first processing of path entries with the per-lane traversal: `cur` is the entry to start with and
+// `level` the number of entries already waiting on this thread's path stack.  firstIsPrimary: `cur` is the
+// camera ray (tMin = near-plane clip :341-344, hit id recorded).  Returns `color` plus the w * Lo of all
+// processed entries, added in processing order.
+template <bool COUNT>
+__device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceScratch& T, PathEntry cur, int level,
+                                             bool firstIsPrimary, double tMinPrimary, HitId* idSlot, PCG32& rng, Counters& C,
+                                             RayCounts& R, V3 color) {
+    const V3 ambient = ld3(S.ambient), background = ld3(S.background);
+    bool primary = firstIsPrimary;
+    for (;;) {
+        HitRec hit;
+        hit.t = CUDART_INF; hit.u = hit.v = 0; hit.inst = -1; hit.slot = 0;
+        traceScene<COUNT>(S, cur.o, cur.d, primary ? tMinPrimary : 0.0, hit, false, T.sstack, C);
+        Surface sf;
+        if (hit.inst >= 0) {
+            resolveHit(S, hit, cur.o, cur.d, sf);
+            if (COUNT && sf.kind == 1 && S.instances[hit.inst].smooth) C.smooth++;
+        }
+        if (primary && idSlot) {
+            idSlot->inst = hit.inst;
+            idSlot->kind = hit.inst >= 0 ? sf.kind : 0;
+            idSlot->prim = hit.inst >= 0 ? sf.prim : -1;
+            idSlot->t = hit.t;
+        }
+        primary = false;
+        int spawned = 0;
+        if (hit.inst < 0) {
+            color = color + cur.w * background;                                         // :101-103
+        } else {
+            ShadePoint sp;
+            setupShade(S, sf, cur, hit.t, sp);
+            V3 Lo = sp.computeDirect ? ambient * ld3(sp.mat->ambient) : mk(0, 0, 0);
+            if (sp.computeDirect) {
+                for (int l = 0; l < S.nPointLights; l++) {                             // :118-143
+                    const GPointLight& pl = S.pointLights[l];
+                    V3 so, wi;
+                    double dist;
+                    shadowRay(pl, sp.p, S.shadowEps, so, wi, dist);
+                    HitRec sh;
+                    sh.t = dist; sh.u = sh.v = 0; sh.inst = -1; sh.slot = 0;             // tMax = dist (:124)
+                    R.shadow++;
+                    if (!traceScene<COUNT>(S, so, wi, 0.0, sh, true, T.sstack, C))
+                        Lo = Lo + pointLightTerm(*sp.mat, pl, sp.N, cur.d, wi, dist);
+                }
+            }
+            if (finite3(Lo)) {                                                          // NaN guard, :277-280
+                color = color + sp.w * Lo;
+                PathEntry c1, c2;
+                const int nc = spawnChildren(S, sp, cur, rng, c1, c2);
+                if (nc == 2) { pathStore(T.pathStack, T.stride, T.gtid, level, c2); level++; }
+                if (nc > 0) { cur = c1; spawned = 1; R.secondary += nc; }
+            }
+        }
+        if (!spawned) {
+            if (level == 0) break;
+            level--;
+            pathLoad(T.pathStack, T.stride, T.gtid, level, cur);
+        }
+    }
+    return color;
+}
+
+}  // namespace rtg

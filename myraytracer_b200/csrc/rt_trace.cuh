@@ -13,19 +13,12 @@ __device__ __forceinline__ void toLocal(const GInstance& I, V3 o, V3 d, V3& oL, 
     else { oL = xfmPoint(I.w2l, o); dL = xfmVector(I.w2l, d); }
 }
 
-// Closest-hit / any-hit test of one instance.  tLow = max(eps, tMin); hit.t = current closest t or tMax.
-template <bool ANYHIT, bool COUNT>
-__device__ __forceinline__ bool enterInstance(const DeviceScene& S, int idx, V3 o, V3 d, double eps, double tMin,
-                                              HitRec& hit, int32_t* sstack, Counters& C) {
-    const GInstance& I = S.instances[idx];
-    V3 oL, dL;
-    toLocal(I, o, d, oL, dL);
-    if (COUNT) C.inst++;
-    const double tLow = dmax(eps, tMin);
+// Analytic instance (sphere / plane / lone triangle): the reference's 1-primitive BLAS root test, then the
+// primitive, bit-exact FP64.  oL/dL: local-space ray.  Returns true for an any-hit.
+template <bool COUNT>
+__device__ __forceinline__ bool analyticInstance(const DeviceScene& S, const GInstance& I, int idx, V3 oL, V3 dL, double eps,
+                                                 double tLow, HitRec& hit, bool anyhit, Counters& C) {
     const int kind = I.kind;
-    if (kind == INST_MESH) return traverseBlas<ANYHIT, COUNT>(S, I, idx, oL, dL, eps, tLow, hit, sstack, C);
-
-    // analytic primitive: the reference's 1-primitive BLAS root test, then the primitive (bit-exact FP64)
     V3 inv = mk(1.0 / dL.x, 1.0 / dL.y, 1.0 / dL.z);
     if (COUNT) C.box++;
     if (!hitAABBExact(I.rootLo, I.rootHi, oL, inv, eps)) return false;
@@ -33,7 +26,7 @@ __device__ __forceinline__ bool enterInstance(const DeviceScene& S, int idx, V3 
     if (kind == INST_SPHERE) {
         if (COUNT) C.sphere++;
         // closest: second root if t < eps (RTContext.swift:522); shadow: if t < max(eps,tMin) (:860)
-        if (!sphereT(I.prim, oL, dL, eps, ANYHIT ? tLow : eps, t)) return false;
+        if (!sphereT(I.prim, oL, dL, eps, anyhit ? tLow : eps, t)) return false;
     } else if (kind == INST_PLANE) {
         if (COUNT) C.plane++;
         if (!planeT(I.prim, oL, dL, eps, t)) return false;
@@ -43,20 +36,33 @@ __device__ __forceinline__ bool enterInstance(const DeviceScene& S, int idx, V3 
         loadTri(S, I, I.triBase, v0, v1, v2);
         if (!mtTest(v0, v1, v2, oL, dL, eps, t, u, v)) return false;
     }
-    if (ANYHIT) return (t > tLow && t < hit.t);
-    if (t <= tLow || t >= hit.t) return false;
+    if (!inWindow(t, tLow, hit.t, anyhit)) return false;
+    if (anyhit) return true;
     hit.t = t; hit.u = u; hit.v = v; hit.inst = idx; hit.slot = I.triBase;
     return false;
 }
 
+// Closest-hit / any-hit test of one instance.  tLow = max(eps, tMin); hit.t = current closest t or tMax.
+template <bool COUNT>
+__device__ __forceinline__ bool enterInstance(const DeviceScene& S, int idx, V3 o, V3 d, double eps, double tMin,
+                                              HitRec& hit, bool anyhit, int32_t* sstack, Counters& C) {
+    const GInstance& I = S.instances[idx];
+    V3 oL, dL;
+    toLocal(I, o, d, oL, dL);
+    if (COUNT) C.inst++;
+    const double tLow = dmax(eps, tMin);
+    if (I.kind == INST_MESH) return traverseBlas<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, sstack, C);
+    return analyticInstance<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, C);
+}
+
 // TLAS walk (FP64 boxes = unions of Instance.worldBounds, widened interval; near child first).
-template <bool ANYHIT, bool COUNT>
-__device__ __forceinline__ bool traceScene(const DeviceScene& S, V3 o, V3 d, double tMin, HitRec& hit, int32_t* sstack,
-                                           Counters& C) {
+template <bool COUNT>
+__device__ __forceinline__ bool traceScene(const DeviceScene& S, V3 o, V3 d, double tMin, HitRec& hit, bool anyhit,
+                                           int32_t* sstack, Counters& C) {
     const double eps = S.eps;
     int32_t cur = S.tlasRootRef;
     if (cur == kEmptyRef) return false;
-    if (cur < 0) return enterInstance<ANYHIT, COUNT>(S, ~cur, o, d, eps, tMin, hit, sstack, C);
+    if (cur < 0) return enterInstance<COUNT>(S, ~cur, o, d, eps, tMin, hit, anyhit, sstack, C);
     const V3 ia = refinedInv(d);
     const double tLow = dmax(eps, tMin);
     int32_t tstack[RT_TLAS_STACK];
@@ -74,14 +80,14 @@ __device__ __forceinline__ bool traceScene(const DeviceScene& S, V3 o, V3 d, dou
             bool h1 = !(n1 > f1) && !(f1 < tLow) && !(n1 > hit.t);
             int32_t c0 = n.child0, c1 = n.child1;
             if (h0 && h1) {
-                if (!ANYHIT && n1 < n0) { int32_t t = c0; c0 = c1; c1 = t; }
+                if (n1 < n0) { int32_t t = c0; c0 = c1; c1 = t; }
                 if (sp < RT_TLAS_STACK) tstack[sp++] = c1;
                 cur = c0;
                 continue;
             } else if (h0) { cur = c0; continue; }
             else if (h1) { cur = c1; continue; }
         } else {
-            if (enterInstance<ANYHIT, COUNT>(S, ~cur, o, d, eps, tMin, hit, sstack, C)) return true;
+            if (enterInstance<COUNT>(S, ~cur, o, d, eps, tMin, hit, anyhit, sstack, C)) return true;
         }
         if (sp == 0) return false;
         cur = tstack[--sp];

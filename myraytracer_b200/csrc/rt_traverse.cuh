@@ -13,16 +13,11 @@
 // reference finds is culled; TLAS boxes are FP64 with a widened interval.
 #pragma once
 #include "gpu_layout.h"
+#include "rt_kernels.h"
 #include "rt_math.cuh"
 
 namespace rtg {
 
-#ifndef RT_BLOCK
-#define RT_BLOCK 128
-#endif
-#ifndef RT_STACK
-#define RT_STACK 64   // same capacity as the reference's fixed stacks (RTContext.swift:550,626)
-#endif
 
 struct Counters {
     unsigned long long box, tri, sphere, plane, inst, smooth;
@@ -102,6 +97,12 @@ __device__ __forceinline__ bool mtTest(V3 v0, V3 v1, V3 v2, V3 org, V3 dir, doub
     return true;
 }
 
+// t window: closest-hit rejects `t <= max(eps,tMin) || t >= hit.t` (RTContext.swift:494,523,534); any-hit accepts
+// `t > max(eps,tMin) && t < tMax` (:847,861,869).  The two forms differ only for NaN, kept as in the reference.
+__device__ __forceinline__ bool inWindow(double t, double tLow, double tHigh, bool anyhit) {
+    return anyhit ? (t > tLow && t < tHigh) : !(t <= tLow || t >= tHigh);
+}
+
 // RTContext.swift:512-523 (closest) and :851-861 (shadow: second-root rule uses max(eps,tMin))
 __device__ __forceinline__ bool sphereT(const double* sp, V3 o, V3 d, double eps, double rootLimit, double& t) {
     V3 oc = o - ld3(sp);
@@ -138,12 +139,13 @@ __device__ __forceinline__ void loadTri(const DeviceScene& S, const GInstance& I
     }
 }
 
-// One BLAS (mesh instance) traversal.  ANYHIT: return true at the first accepted primitive.
+// One BLAS (mesh instance) traversal.  anyhit (run-time flag: ONE copy of the loop serves closest-hit and
+// shadow queries, which halves the instruction-cache footprint): return true at the first accepted primitive.
 // oL/dL: local-space FP64 ray (bit-identical to the reference's).  tLow = max(eps, tMin).
 // hit.t is the current closest t (closest) or tMax (any-hit); updated on accept.
-template <bool ANYHIT, bool COUNT>
+template <bool COUNT>
 __device__ __forceinline__ bool traverseBlas(const DeviceScene& S, const GInstance& I, int instIdx, V3 oL, V3 dL, double eps,
-                                             double tLow, HitRec& hit, int32_t* sstack, Counters& C) {
+                                             double tLow, HitRec& hit, bool anyhit, int32_t* sstack, Counters& C) {
     // Advance the origin to the BLAS in FP64 so that its FP32 copy is accurate relative to the
     // box size: t0 = entry distance into the (exact) root box, from a widened FP64 slab test.
     V3 ia = refinedInv(dL);
@@ -158,7 +160,12 @@ __device__ __forceinline__ bool traverseBlas(const DeviceScene& S, const GInstan
     if (!(t0 < 1e300)) t0 = 0.0;
     V3 o2 = oc + dL * t0;
     const float ox = (float)o2.x, oy = (float)o2.y, oz = (float)o2.z;
-    const float ix = 1.0f / (float)dL.x, iy = 1.0f / (float)dL.y, iz = 1.0f / (float)dL.z;
+    // |1/d| clamped to 1e30 (a zero direction component becomes +-1e-30: moves < pad over any finite t) so that
+    // plane * inv - o * inv never produces inf - inf
+    const float ix = fminf(fmaxf(1.0f / (float)dL.x, -1e30f), 1e30f);
+    const float iy = fminf(fmaxf(1.0f / (float)dL.y, -1e30f), 1e30f);
+    const float iz = fminf(fmaxf(1.0f / (float)dL.z, -1e30f), 1e30f);
+    const float nx = -(ox * ix), ny = -(oy * iy), nz = -(oz * iz);
     float tminF = __double2float_rd(tLow - t0);
     float tmaxF = __double2float_ru(hit.t - t0);
 
@@ -173,21 +180,22 @@ __device__ __forceinline__ bool traverseBlas(const DeviceScene& S, const GInstan
             const int4 ch = __ldg(reinterpret_cast<const int4*>(np + 3));
             if (COUNT) C.box += 2;
             // child 0: lo = q0.xyz, hi = (q0.w, q1.x, q1.y); child 1: lo = (q1.z, q1.w, q2.x), hi = q2.yzw
-            float a0 = (q0.x - ox) * ix, b0 = (q0.w - ox) * ix;
-            float a1 = (q0.y - oy) * iy, b1 = (q1.x - oy) * iy;
-            float a2 = (q0.z - oz) * iz, b2 = (q1.y - oz) * iz;
+            // (plane - o) * inv as one explicit FMA: plane * inv + (-o * inv); intrinsics are immune to -fmad=false
+            float a0 = __fmaf_rn(q0.x, ix, nx), b0 = __fmaf_rn(q0.w, ix, nx);
+            float a1 = __fmaf_rn(q0.y, iy, ny), b1 = __fmaf_rn(q1.x, iy, ny);
+            float a2 = __fmaf_rn(q0.z, iz, nz), b2 = __fmaf_rn(q1.y, iz, nz);
             float n0 = fmaxf(fmaxf(fminf(a0, b0), fminf(a1, b1)), fmaxf(fminf(a2, b2), tminF));
             float f0 = fminf(fminf(fmaxf(a0, b0), fmaxf(a1, b1)), fminf(fmaxf(a2, b2), tmaxF));
-            float c0 = (q1.z - ox) * ix, d0 = (q2.y - ox) * ix;
-            float c1 = (q1.w - oy) * iy, d1 = (q2.z - oy) * iy;
-            float c2 = (q2.x - oz) * iz, d2 = (q2.w - oz) * iz;
+            float c0 = __fmaf_rn(q1.z, ix, nx), d0 = __fmaf_rn(q2.y, ix, nx);
+            float c1 = __fmaf_rn(q1.w, iy, ny), d1 = __fmaf_rn(q2.z, iy, ny);
+            float c2 = __fmaf_rn(q2.x, iz, nz), d2 = __fmaf_rn(q2.w, iz, nz);
             float n1 = fmaxf(fmaxf(fminf(c0, d0), fminf(c1, d1)), fmaxf(fminf(c2, d2), tminF));
             float f1 = fminf(fminf(fmaxf(c0, d0), fmaxf(c1, d1)), fminf(fmaxf(c2, d2), tmaxF));
             // the padding of the stored boxes covers every FP32 rounding here
             const bool h0 = n0 <= f0, h1 = n1 <= f1;
             if (h0 && h1) {
                 int32_t nearC = ch.x, farC = ch.y;
-                if (!ANYHIT && n1 < n0) { nearC = ch.y; farC = ch.x; }
+                if (n1 < n0) { nearC = ch.y; farC = ch.x; }
                 sstack[sp * RT_BLOCK + tid] = farC;
                 sp++;
                 if (COUNT && sp > C.maxStack) C.maxStack = sp;
@@ -211,13 +219,10 @@ __device__ __forceinline__ bool traverseBlas(const DeviceScene& S, const GInstan
                 if (COUNT) C.tri++;
                 double t, u, v;
                 if (!mtTest(v0, v1, v2, oL, dL, eps, t, u, v)) continue;
-                if (ANYHIT) {
-                    if (t > tLow && t < hit.t) return true;
-                } else {
-                    if (t <= tLow || t >= hit.t) continue;
-                    hit.t = t; hit.u = u; hit.v = v; hit.inst = instIdx; hit.slot = first + k;
-                    tmaxF = __double2float_ru(t - t0);
-                }
+                if (!inWindow(t, tLow, hit.t, anyhit)) continue;
+                if (anyhit) return true;
+                hit.t = t; hit.u = u; hit.v = v; hit.inst = instIdx; hit.slot = first + k;
+                tmaxF = __double2float_ru(t - t0);
             }
         }
         if (sp == 0) return false;

@@ -71,13 +71,14 @@ class ShardedRenderer:
     torch.distributed group (or 0/1 when it is not initialised)."""
 
     def __init__(self, scene_url: str, device: int = 0, rank: Optional[int] = None, world: Optional[int] = None,
-                 camera_index: int = 0):
+                 camera_index: int = 0, variant: int = 0):
         from .engine import RayTracerEngine
         if rank is None:
             rank = dist.get_rank() if dist.is_initialized() else 0
         if world is None:
             world = dist.get_world_size() if dist.is_initialized() else 1
         self.rank, self.world, self.device, self.camera_index = rank, world, device, camera_index
+        self.variant = variant  # rt_render_params.kernelVariant (0 = automatic)
         self.engine = RayTracerEngine(scene_url, device=device)
         if not self.engine.ready:
             raise RuntimeError("engine not ready: " + self.engine.load_error)
@@ -97,7 +98,7 @@ class ShardedRenderer:
         """Kernel for this rank's chunks + gather to rank 0, on torch's current stream; no host sync."""
         st = torch.cuda.current_stream(self.device).cuda_stream
         self.engine.render_device(self.camera_index, d_rgba=self.fb.data_ptr(), stream=st, shard_index=self.rank,
-                                  shard_count=self.world, counters=counters)
+                                  shard_count=self.world, counters=counters, variant=self.variant)
         gather_chunks(self.fb, self.rank, self.world, self.send, self.recv)
 
     def finish(self) -> dict:

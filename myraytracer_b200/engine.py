@@ -102,7 +102,7 @@ class RayTracerEngine:
     # -- render -----------------------------------------------------------
     def render(self, camera_index: int = 0, want_linear: bool = False, want_ids: bool = False,
                shard_index: int = 0, shard_count: int = 1, counters: bool = False,
-               progress: Optional[Callable[[int, int], bool]] = None) -> RenderResult:
+               progress: Optional[Callable[[int, int], bool]] = None, variant: int = 0) -> RenderResult:
         if not self._h or self._lib.rth_engine_camera_count(self._h) == 0 and not self.ready:
             pass  # let the C side produce the reference's error codes
         cam = None
@@ -118,6 +118,7 @@ class RayTracerEngine:
         ids = np.zeros((H, W, n * n), capi.HIT_ID_DTYPE) if want_ids else None
         prm = capi.rt_render_params()
         prm.shardIndex, prm.shardCount, prm.collectCounters = shard_index, shard_count, 1 if counters else 0
+        prm.kernelVariant = variant
         cb = None
         if progress is not None:
             cb = capi.rt_progress_fn(lambda done, total, _u: 0 if progress(done, total) else 1)
@@ -130,12 +131,13 @@ class RayTracerEngine:
 
 
     def render_device(self, camera_index: int = 0, d_rgba: int = 0, d_linear: int = 0, d_ids: int = 0, stream: int = 0,
-                      shard_index: int = 0, shard_count: int = 1, counters: bool = False) -> None:
+                      shard_index: int = 0, shard_count: int = 1, counters: bool = False, variant: int = 0) -> None:
         """rt_render_device: enqueue one frame on `stream` with caller-owned DEVICE buffers (raw pointers,
         e.g. torch.Tensor.data_ptr()); does not synchronise.  Pair with finish()."""
         cam = self.camera(camera_index)
         prm = capi.rt_render_params()
         prm.shardIndex, prm.shardCount, prm.collectCounters = shard_index, shard_count, 1 if counters else 0
+        prm.kernelVariant = variant
         rc = self._lib.rt_render_device(self.scene_handle(), C.byref(cam), C.byref(prm), d_rgba or None, d_linear or None,
                                         d_ids or None, stream or None)
         if rc != 0:

@@ -37,6 +37,29 @@ def test_parity_vs_oracle(name, scene_dir):
         assert abs(a - b) <= max(4, 1e-4 * b), rep
 
 
+@pytest.mark.parametrize("variant", [1, 2])
+@pytest.mark.parametrize("name", ["c1", "c3", "c5s"])
+def test_kernel_variants_vs_oracle(name, variant, scene_dir):
+    """Every kernel variant (fast: sample lanes + warp packets; general: pixel lanes, per-lane traversal) meets the parity bars, and the
+    variants agree with each other except at hit-distance ties."""
+    case = CASES[name]
+    kw = dict(case["kw"])
+    if name == "c1":
+        kw.update(width=200, height=200, samples=9)      # 9 spp: the non-power-of-two ordered-sum path
+    path = case["fn"](scene_dir, **kw)
+    eng = RayTracerEngine(path)
+    got = eng.render(0, want_ids=True, want_linear=True, variant=variant)
+    ref = oracle_lib.OracleScene(path).render(want_ids=True, want_linear=True)
+    rep = parity.compare(got, ref)
+    print(name, variant, rep)
+    assert rep["id_agree"] >= 0.9999 and rep["id_bad"] == 0, rep
+    assert rep["px_within_1"] >= 0.999, rep
+    assert rep["rays_gpu"][0] == rep["rays_ref"][0]
+    base = eng.render(0, want_linear=True, variant=2)
+    same = (base.rgba == got.rgba).all(axis=-1).mean()
+    assert same >= 0.9999, same
+
+
 def test_shards_are_bit_identical(scene_dir):
     """Decomposition invariance: per-pixel RNG depends only on (i, j) (Object+Extension.swift:294)."""
     path = scenegen.config_c3(scene_dir, width=128, height=100, samples=4, depth=3, ico_level=2)
