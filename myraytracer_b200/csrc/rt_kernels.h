@@ -30,6 +30,9 @@ static const int kPathFields = 11;
 #ifndef RT_STACK
 #define RT_STACK 64   // same capacity as the reference's fixed stacks (RTContext.swift:550,626)
 #endif
+#ifndef RT_SSTACK
+#define RT_SSTACK 24  // entries of the per-lane stack kept in shared memory; the rest spill to local memory
+#endif
 
 // kernel variants (rt_kernels.cu); values match rt_render_params.kernelVariant - 1
 enum KernelVariant { KV_FAST = 0, KV_GENERAL = 1, KV_COUNT = 2 };

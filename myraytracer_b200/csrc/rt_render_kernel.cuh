@@ -27,8 +27,13 @@
 
 namespace rtg {
 
-#ifndef RT_MIN_BLOCKS
-#define RT_MIN_BLOCKS 3
+// Resident blocks per SM the kernels are compiled for (register cap = 65536 / (128 * blocks)).  Measured on
+// B200 (C4, profiles/): the traversal is latency-bound, so more resident warps beat fewer spills.
+#ifndef RT_FAST_BLOCKS
+#define RT_FAST_BLOCKS 8
+#endif
+#ifndef RT_GEN_BLOCKS
+#define RT_GEN_BLOCKS 5
 #endif
 
 struct PrimaryRay {
@@ -136,8 +141,8 @@ struct TileMap {
 __device__ __forceinline__ double shflD(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
 
 template <bool COUNT>
-__global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS) renderKernelFast(DeviceScene S, CameraParams cam, RenderTargets out) {
-    __shared__ int32_t sstack[RT_STACK * RT_BLOCK];
+__global__ void __launch_bounds__(RT_BLOCK, RT_FAST_BLOCKS) renderKernelFast(DeviceScene S, CameraParams cam, RenderTargets out) {
+    __shared__ int32_t sstack[RT_SSTACK * RT_BLOCK];
     __shared__ int2 wstacks[(RT_BLOCK / 32) * RT_WARP_STACK_INT2];
     const int lane = threadIdx.x & 31;
     TraceScratch T;
@@ -279,8 +284,8 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS) renderKernelFast(Devi
 }
 
 template <bool COUNT>
-__global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS) renderKernelGeneral(DeviceScene S, CameraParams cam, RenderTargets out) {
-    __shared__ int32_t sstack[RT_STACK * RT_BLOCK];
+__global__ void __launch_bounds__(RT_BLOCK, RT_GEN_BLOCKS) renderKernelGeneral(DeviceScene S, CameraParams cam, RenderTargets out) {
+    __shared__ int32_t sstack[RT_SSTACK * RT_BLOCK];
     const int lane = threadIdx.x & 31;
     TraceScratch T;
     T.sstack = sstack;

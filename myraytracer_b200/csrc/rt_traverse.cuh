@@ -170,6 +170,8 @@ __device__ __forceinline__ bool traverseBlas(const DeviceScene& S, const GInstan
     float tmaxF = __double2float_ru(hit.t - t0);
 
     const GNode* nodes = S.nodes + I.nodeBase;
+    // stack: the first RT_SSTACK entries in shared memory (per-lane column), deeper ones in local memory
+    int32_t lstack[RT_STACK - RT_SSTACK];
     int sp = 0;
     int32_t cur = I.rootRef;
     const int tid = threadIdx.x;
@@ -196,7 +198,7 @@ __device__ __forceinline__ bool traverseBlas(const DeviceScene& S, const GInstan
             if (h0 && h1) {
                 int32_t nearC = ch.x, farC = ch.y;
                 if (n1 < n0) { nearC = ch.y; farC = ch.x; }
-                sstack[sp * RT_BLOCK + tid] = farC;
+                if (sp < RT_SSTACK) sstack[sp * RT_BLOCK + tid] = farC; else lstack[sp - RT_SSTACK] = farC;
                 sp++;
                 if (COUNT && sp > C.maxStack) C.maxStack = sp;
                 cur = nearC;
@@ -207,7 +209,7 @@ __device__ __forceinline__ bool traverseBlas(const DeviceScene& S, const GInstan
             } else {
                 if (sp == 0) return false;
                 sp--;
-                cur = sstack[sp * RT_BLOCK + tid];
+                cur = sp < RT_SSTACK ? sstack[sp * RT_BLOCK + tid] : lstack[sp - RT_SSTACK];
             }
         }
         if (cur != kEmptyRef) {  // leaf
@@ -227,7 +229,7 @@ __device__ __forceinline__ bool traverseBlas(const DeviceScene& S, const GInstan
         }
         if (sp == 0) return false;
         sp--;
-        cur = sstack[sp * RT_BLOCK + tid];
+        cur = sp < RT_SSTACK ? sstack[sp * RT_BLOCK + tid] : lstack[sp - RT_SSTACK];
     }
 }
 
