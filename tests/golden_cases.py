@@ -1,0 +1,9 @@
+"""Small seeded scenes whose oracle renders are frozen under tests/golden/ (tools/make_golden.py)."""
+from myraytracer_b200 import scenegen
+
+GOLDEN_CASES = {
+    "c1_small": (scenegen.config_c1, dict(width=96, height=96, samples=1)),
+    "c2_small": (scenegen.config_c2, dict(n=40, width=96, height=96, samples=1)),
+    "c3_small": (scenegen.config_c3, dict(width=64, height=64, samples=4, depth=4, ico_level=1)),
+    "c5_small": (scenegen.config_c5, dict(n=24, width=96, height=54, samples=4, meshes=3)),
+}

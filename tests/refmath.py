@@ -1,0 +1,150 @@
+"""Second, independent restatement (numpy / pure Python) of the pieces of the reference that pin the oracle:
+PCG32, the pixel seed, primary-ray generation and a brute-force (no BVH) closest hit.  Written from the
+reference's source (cited per function), NOT from oracle/: the CPU tests check oracle/ against this file, so an
+error has to be made twice, independently, to go unnoticed (SURVEY.md §8c iv).  Test infrastructure only."""
+from __future__ import annotations
+
+import math
+
+import numpy as np
+
+M64 = (1 << 64) - 1
+
+
+class PCG32:
+    """Extensions/Object+Extension.swift:556-589 (non-standard seeding :561-567)."""
+
+    def __init__(self, seed: int):
+        self.state = 0
+        self.inc = ((seed << 1) | 1) & M64
+        self.next()
+        self.state = (self.state + 0x9E3779B97F4A7C15) & M64
+        self.next()
+
+    def next(self) -> int:
+        old = self.state
+        self.state = (old * 6364136223846793005 + self.inc) & M64
+        xorshifted = (((old >> 18) ^ old) >> 27) & 0xFFFFFFFF
+        rot = (old >> 59) & 31
+        return ((xorshifted >> rot) | (xorshifted << ((-rot) & 31))) & 0xFFFFFFFF
+
+    def next_float(self) -> float:
+        return float(self.next()) * 2.3283064365386963e-10
+
+
+def pixel_seed(i: int, j: int) -> int:
+    """:294 — Swift: `^` and `&+` share AdditionPrecedence and associate left."""
+    return ((((j << 32) & M64) ^ i) + 0x9E3779B97F4A7C15) & M64
+
+
+def _norm(v):
+    return v * (1.0 / math.sqrt((v[0] * v[0] + v[1] * v[1]) + v[2] * v[2]))
+
+
+def _dot(a, b):
+    return (a[0] * b[0] + a[1] * b[1]) + a[2] * b[2]
+
+
+def camera_basis(cam: dict):
+    """makeCameraBasis, :382-427, + du, dv, m, q00 (:67-70).  cam: dict of the Camera fields."""
+    W, H = max(1, cam["width"]), max(1, cam["height"])
+    aspect = W / H
+    e = np.asarray(cam["position"], np.float64)
+    nd = cam["nearDistance"]
+    if cam["isLookAt"]:
+        w = -_norm(np.asarray(cam["gazePoint"], np.float64) - e)
+        u = _norm(np.cross(_norm(np.asarray(cam["up"], np.float64)), w))
+        v = _norm(np.cross(w, u))
+        t = nd * math.tan((cam["fovy"] * math.pi) / (2.0 * 180.0)) if cam.get("fovy") is not None else nd * 0.5
+        b, r = -t, t * aspect
+        l = -r
+    else:
+        l, r, b, t = cam["nearPlane"]
+        w = -_norm(np.asarray(cam["gaze"], np.float64))
+        u = _norm(np.cross(_norm(np.asarray(cam["up"], np.float64)), w))
+        v = _norm(np.cross(w, u))
+    m = e - w * nd
+    q00 = (m + u * l) + v * t
+    return dict(e=e, u=u, v=v, w=w, m=m, q00=q00, du=(r - l) / W, dv=(t - b) / H, W=W, H=H)
+
+
+def primary_rays(cam: dict, i: int, j: int):
+    """All n*n primary rays of pixel (i, j): list of (origin, dir, tMin), :294-344 without DOF."""
+    B = camera_basis(cam)
+    samples = max(1, cam["numSamples"])
+    n = int(math.sqrt(samples))
+    rng = PCG32(pixel_seed(i, j))
+    out = []
+    for sy in range(n):
+        for sx in range(n):
+            xi1, xi2 = rng.next_float(), rng.next_float()
+            ci = float(i) + (float(sx) + xi1) / float(n)
+            cj = float(j) + (float(sy) + xi2) / float(n)
+            s = (B["q00"] - B["v"] * (cj * B["dv"])) + B["u"] * (ci * B["du"])
+            d = _norm(s - B["e"])
+            rng.next_float()  # ray time (:340)
+            t_img = _dot(B["m"] - B["e"], B["w"]) / _dot(d, B["w"])
+            out.append((B["e"].copy(), d, max(t_img, 0.0)))
+    return out
+
+
+def brute_force_triangles(o, d, tris, eps, t_min):
+    """Closest Moeller-Trumbore hit over ALL triangles, RTContext.swift:479-494 — vectorised, no BVH.
+    tris: (N, 3, 3).  Returns (index or -1, t)."""
+    v0, e1, e2 = tris[:, 0], tris[:, 1] - tris[:, 0], tris[:, 2] - tris[:, 0]
+    pvec = np.cross(d[None, :], e2)
+    det = (e1[:, 0] * pvec[:, 0] + e1[:, 1] * pvec[:, 1]) + e1[:, 2] * pvec[:, 2]
+    ok = np.abs(det) >= eps
+    with np.errstate(divide="ignore", invalid="ignore"):
+        inv = 1.0 / det
+        tvec = o[None, :] - v0
+        u = ((tvec[:, 0] * pvec[:, 0] + tvec[:, 1] * pvec[:, 1]) + tvec[:, 2] * pvec[:, 2]) * inv
+        q = np.cross(tvec, e1)
+        v = ((d[0] * q[:, 0] + d[1] * q[:, 1]) + d[2] * q[:, 2]) * inv
+        t = ((e2[:, 0] * q[:, 0] + e2[:, 1] * q[:, 1]) + e2[:, 2] * q[:, 2]) * inv
+    ok &= (u >= 0) & (u <= 1) & (v >= 0) & (u + v <= 1) & (t > max(eps, t_min))
+    if not ok.any():
+        return -1, math.inf
+    t = np.where(ok, t, np.inf)
+    k = int(np.argmin(t))
+    return k, float(t[k])
+
+
+def brute_force_sphere(o, d, c, r, eps, t_min):
+    """intersectSphere, RTContext.swift:512-523."""
+    oc = o - c
+    a = _dot(d, d)
+    b = 2.0 * _dot(oc, d)
+    cc = _dot(oc, oc) - r * r
+    disc = b * b - 4 * a * cc
+    if disc < 0:
+        return math.inf
+    sd = math.sqrt(disc)
+    t = (-b - sd) / (2 * a)
+    if t < eps:
+        t = (-b + sd) / (2 * a)
+    return t if t > max(eps, t_min) else math.inf
+
+
+def fresnel_dielectric(n1, n2, cos_i):
+    """:476-490 -> (R, cosT or None)."""
+    c = max(0.0, min(1.0, abs(cos_i)))
+    eta = n1 / n2
+    s2 = eta * eta * max(0.0, 1.0 - c * c)
+    if s2 > 1.0:
+        return 1.0, None
+    cp = math.sqrt(max(0.0, 1.0 - s2))
+    rs = (n2 * c - n1 * cp) / (n2 * c + n1 * cp)
+    rp = (n1 * c - n2 * cp) / (n1 * c + n2 * cp)
+    return 0.5 * (rs * rs + rp * rp), cp
+
+
+def fresnel_conductor(eta, k, cos_i):
+    """:492-505."""
+    c = max(0.0, min(1.0, abs(cos_i)))
+    c2 = c * c
+    e = eta * eta + k * k
+    t = 2.0 * eta * c
+    rs = (e - t + c2) / (e + t + c2)
+    rp = ((e * c2) - t + 1.0) / ((e * c2) + t + 1.0)
+    return 0.5 * (rs + rp)

