@@ -47,6 +47,25 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+_REAL_STDOUT = None
+
+
+def capture_stdout():
+    """Everything libraries print to fd 1 (NCCL's version banner, ...) goes to stderr; the contract's ONE JSON line is
+    written to the real stdout by emit()."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line: dict):
+    data = (json.dumps(line) + "\n").encode()
+    sys.stdout.flush()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
+
+
 def make_scene(config: str, rank: int) -> str:
     """Write the synthetic scene for `config` (seeded, deterministic) into a per-rank scratch dir."""
     from myraytracer_b200 import scenegen
@@ -164,7 +183,7 @@ def run_reference(args):
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": info["cores"], "kind": "port", "sample": info["sample"]},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -210,7 +229,7 @@ def run_ours(args):
 
     t0 = time.time()
     path = make_scene(args.config, rank)
-    R = ShardedRenderer(path, device=local, rank=rank, world=world, variant=args.variant)
+    R = ShardedRenderer(path, device=local, rank=rank, world=world, variant=args.variant, gather=args.gather)
     info = R.engine.scene_info()
     W, H = R.width, R.height
     log(f"[rank {rank}] scene ready in {time.time() - t0:.1f}s: {info}")
@@ -272,6 +291,7 @@ def run_ours(args):
                    "timer, RayTracer.swift:44,166); per step the camera/launch parameters go down and the RGBA8 frame "
                    "+ ray counters come back to pinned host memory"}
 
+    R.close()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -295,7 +315,7 @@ def run_ours(args):
             "data": "synthetic",
             "config": {"workload": BENCH_CONFIGS[args.config][2], "width": W, "height": H, "triangles": info["triangles"],
                        "rays_per_frame": int(rays), "rays_primary": int(rp), "rays_shadow": int(rs),
-                       "rays_secondary": int(rays - rp - rs), "parallelism": f"tiles{world}", "kernel_variant": args.variant,
+                       "rays_secondary": int(rays - rp - rs), "parallelism": f"tiles{world}", "gather": R.gather, "kernel_variant": args.variant,
                        "l2": "256 MB buffer written between timed iterations (L2 flush); scene working set "
                              f"{info['deviceBytes'] / 1e6:.0f} MB"},
             "wall_ms_per_step": wall * 1e3 / args.steps, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
@@ -304,7 +324,7 @@ def run_ours(args):
         mr, ci = cpu_sample(path, target_s=args.cpu_seconds)
         line["cpu_baseline"] = {"value": mr, "unit": UNIT, "cores": ci["cores"], "kind": "port", "sample": ci["sample"],
                                 "ms": ci["ms"], "per_core": mr / ci["cores"]}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -325,8 +345,11 @@ def main():
     ap.add_argument("--config", choices=sorted(BENCH_CONFIGS), default="c4")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--gather", choices=["p2p", "nccl"], default="p2p",
+                    help="N>1 framebuffer exchange: kernel stores into rank 0's frame over NVLink (p2p) or NCCL gather")
     ap.add_argument("--variant", type=int, default=0, help="rt_render_params.kernelVariant (0 = automatic; A/B runs)")
     args = ap.parse_args()
+    capture_stdout()
     if args.warmup < 3 and args.impl == "ours":
         log("note: timing rules ask for >= 3 warm-up steps")
     return run_reference(args) if args.impl == "reference" else run_ours(args)

@@ -197,6 +197,19 @@ int32_t rt_render_device(rt_scene_t* scene, const rt_camera* camera, const rt_re
                          void* dRgbaOut, void* dLinearOut, void* dIdsOut, void* cudaStream);
 int32_t rt_render_finish(rt_scene_t* scene, rt_stats* statsOut);
 
+/* Multi-GPU framebuffer (one process per GPU): the reference merges finished 8-row chunks into
+ * one [Vec3] array by plain copies (Object+Extension.swift:363-373).  Here rank 0 owns the RGBA8 frame in device
+ * memory and exports it; every other rank maps it over NVLink (CUDA IPC, peer access) and passes the mapped
+ * pointer as dRgbaOut to rt_render_device, so its kernel stores finished pixels straight into rank 0's frame —
+ * the gather is fused into the render kernel's epilogue, no staging copy and no collective on the data path.
+ *   create: cudaMalloc on `device`, zero-filled; handleOut receives the 64-byte IPC handle to send to the peers
+ *   open:   map a peer's buffer into this process on `device`
+ *   close:  unmap (opened) or free (created) */
+#define RT_IPC_HANDLE_BYTES 64
+int32_t rt_shared_buffer_create(int32_t device, uint64_t bytes, void** devPtrOut, uint8_t* handleOut);
+int32_t rt_shared_buffer_open(int32_t device, const uint8_t* handle, void** devPtrOut);
+int32_t rt_shared_buffer_close(int32_t device, void* devPtr, int32_t wasOpened);
+
 #ifdef __cplusplus
 }
 #endif

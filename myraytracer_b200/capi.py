@@ -14,6 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RTCUDA_LIB") or os.path.join(HERE, "librtcuda.so")
 
 RT_ABI_VERSION = 1
+RT_IPC_HANDLE_BYTES = 64
 RT_OK, RT_ERR_INVALID, RT_ERR_CUDA, RT_ERR_UNSUPPORTED, RT_ERR_CANCELLED = 0, -1, -2, -3, -4
 RT_ERR_BAD_CAMERA, RT_ERR_NO_SCENE, RT_ERR_NO_RENDERER = -10, -20, -21
 RT_GEO_MESH, RT_GEO_TRIANGLE, RT_GEO_SPHERE, RT_GEO_PLANE = 0, 1, 2, 3
@@ -116,6 +117,7 @@ HIT_ID_DTYPE = np.dtype([("inst", "<i4"), ("kind", "<i4"), ("prim", "<i8"), ("t"
 # every symbol include/rtcuda.h and include/rtcuda_host.h declare
 EXPORTS = ["rt_abi_version", "rt_device_count", "rt_last_error", "rt_scene_create", "rt_scene_destroy",
            "rt_scene_get_info", "rt_render", "rt_render_device", "rt_render_finish",
+           "rt_shared_buffer_create", "rt_shared_buffer_open", "rt_shared_buffer_close",
            "rth_last_error", "rth_engine_create", "rth_engine_destroy", "rth_engine_ready", "rth_engine_camera_count",
            "rth_engine_camera", "rth_engine_scene", "rth_engine_describe", "rth_engine_instance_object_ids",
            "rth_engine_render", "rth_context_create", "rth_context_destroy", "rth_context_describe"]
@@ -144,6 +146,9 @@ def load():
     L.rt_render.argtypes = [vp, C.POINTER(rt_camera), C.POINTER(rt_render_params), vp, vp, vp, C.POINTER(rt_stats)]
     L.rt_render_device.argtypes = [vp, C.POINTER(rt_camera), C.POINTER(rt_render_params), vp, vp, vp, vp]
     L.rt_render_finish.argtypes = [vp, C.POINTER(rt_stats)]
+    L.rt_shared_buffer_create.argtypes = [C.c_int32, C.c_uint64, C.POINTER(vp), vp]
+    L.rt_shared_buffer_open.argtypes = [C.c_int32, vp, C.POINTER(vp)]
+    L.rt_shared_buffer_close.argtypes = [C.c_int32, vp, C.c_int32]
     L.rth_last_error.restype = C.c_char_p
     L.rth_engine_create.restype = vp
     L.rth_engine_create.argtypes = [C.c_char_p, C.c_int32]

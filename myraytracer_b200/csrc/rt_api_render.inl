@@ -175,4 +175,38 @@ int32_t rt_render(rt_scene_t* sc, const rt_camera* camera, const rt_render_param
     return RT_OK;
 }
 
+int32_t rt_shared_buffer_create(int32_t device, uint64_t bytes, void** devPtrOut, uint8_t* handleOut) {
+    if (!devPtrOut || !handleOut || bytes == 0) return fail(RT_ERR_INVALID, "rt_shared_buffer_create: bad argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == RT_IPC_HANDLE_BYTES, "IPC handle size");
+    CK(cudaSetDevice(device));
+    void* p = nullptr;
+    CK(cudaMalloc(&p, bytes));
+    CK(cudaMemset(p, 0, bytes));
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) { cudaFree(p); g_err = std::string("cudaIpcGetMemHandle: ") + cudaGetErrorString(e); return RT_ERR_CUDA; }
+    std::memcpy(handleOut, &h, sizeof h);
+    *devPtrOut = p;
+    return RT_OK;
+}
+
+int32_t rt_shared_buffer_open(int32_t device, const uint8_t* handle, void** devPtrOut) {
+    if (!devPtrOut || !handle) return fail(RT_ERR_INVALID, "rt_shared_buffer_open: bad argument");
+    CK(cudaSetDevice(device));
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, sizeof h);
+    void* p = nullptr;
+    CK(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    *devPtrOut = p;
+    return RT_OK;
+}
+
+int32_t rt_shared_buffer_close(int32_t device, void* devPtr, int32_t wasOpened) {
+    if (!devPtr) return RT_OK;
+    CK(cudaSetDevice(device));
+    if (wasOpened) CK(cudaIpcCloseMemHandle(devPtr));
+    else CK(cudaFree(devPtr));
+    return RT_OK;
+}
+
 }  // extern "C"

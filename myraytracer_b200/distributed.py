@@ -67,11 +67,19 @@ def gather_chunks(fb: torch.Tensor, rank: int, world: int, send: Optional[torch.
 
 
 class ShardedRenderer:
-    """RayTracerEngine on this rank's GPU + the framebuffer gather.  rank/world default to the
-    torch.distributed group (or 0/1 when it is not initialised)."""
+    """RayTracerEngine on this rank's GPU + the framebuffer exchange.  rank/world default to the
+    torch.distributed group (or 0/1 when it is not initialised).
+
+    gather="p2p" (default for world > 1): rank 0 owns the RGBA8 frame (rt_shared_buffer_create) and every rank
+    maps it over NVLink (CUDA IPC); each rank's render kernel stores its finished pixels straight into rank 0's
+    frame, and one 4-byte all-reduce on the launch stream tells rank 0 that every rank's kernel has completed.
+    gather="nccl": each rank renders into a private frame, packs its chunks and rank 0 gathers them (NCCL or gloo).
+    """
 
     def __init__(self, scene_url: str, device: int = 0, rank: Optional[int] = None, world: Optional[int] = None,
-                 camera_index: int = 0, variant: int = 0):
+                 camera_index: int = 0, variant: int = 0, gather: str = "p2p"):
+        import ctypes as C
+        from . import capi
         from .engine import RayTracerEngine
         if rank is None:
             rank = dist.get_rank() if dist.is_initialized() else 0
@@ -79,6 +87,7 @@ class ShardedRenderer:
             world = dist.get_world_size() if dist.is_initialized() else 1
         self.rank, self.world, self.device, self.camera_index = rank, world, device, camera_index
         self.variant = variant  # rt_render_params.kernelVariant (0 = automatic)
+        self.gather = gather if world > 1 else "none"
         self.engine = RayTracerEngine(scene_url, device=device)
         if not self.engine.ready:
             raise RuntimeError("engine not ready: " + self.engine.load_error)
@@ -86,20 +95,60 @@ class ShardedRenderer:
         self.width, self.height = max(1, cam.width), max(1, cam.height)
         dev = torch.device("cuda", device)
         hp = n_chunks(self.height) * CHUNK_ROWS
-        self.fb = torch.zeros((hp, self.width, 4), dtype=torch.uint8, device=dev)  # padded to whole chunks
-        self.send = self.recv = None
-        if world > 1:
-            self.send = torch.zeros((max_owned(self.height, world), CHUNK_ROWS * self.width * 4), dtype=torch.uint8, device=dev)
+        self.send = self.recv = self.flag = None
+        self._lib, self._shared_ptr, self._opened = capi.load(), None, 0
+        if self.gather == "p2p":
+            nbytes = hp * self.width * 4
+            handle = torch.zeros(capi.RT_IPC_HANDLE_BYTES, dtype=torch.uint8)
+            ptr = C.c_void_p()
             if rank == 0:
-                self.recv = [torch.empty_like(self.send) for _ in range(world)]
+                hb = (C.c_uint8 * capi.RT_IPC_HANDLE_BYTES)()
+                rc = self._lib.rt_shared_buffer_create(device, nbytes, C.byref(ptr), hb)
+                if rc != 0:
+                    raise RuntimeError("rt_shared_buffer_create: " + self._lib.rt_last_error().decode())
+                handle = torch.tensor(list(hb), dtype=torch.uint8)
+            hdev = handle.to(dev)
+            dist.broadcast(hdev, src=0)
+            if rank != 0:
+                hb = (C.c_uint8 * capi.RT_IPC_HANDLE_BYTES)(*hdev.cpu().tolist())
+                rc = self._lib.rt_shared_buffer_open(device, hb, C.byref(ptr))
+                if rc != 0:
+                    raise RuntimeError("rt_shared_buffer_open: " + self._lib.rt_last_error().decode())
+                self._opened = 1
+            self._shared_ptr = ptr.value
+            self.fb_ptr = ptr.value
+            self.fb = None
+            self.flag = torch.zeros(1, dtype=torch.int32, device=dev)
+            if rank == 0:   # rank 0 reads the frame through torch: wrap the raw allocation without copying
+                self.fb = _wrap_device_memory(ptr.value, (hp, self.width, 4), device)
+        else:
+            self.fb = torch.zeros((hp, self.width, 4), dtype=torch.uint8, device=dev)  # padded to whole chunks
+            self.fb_ptr = self.fb.data_ptr()
+            if self.gather == "nccl":
+                self.send = torch.zeros((max_owned(self.height, world), CHUNK_ROWS * self.width * 4), dtype=torch.uint8, device=dev)
+                if rank == 0:
+                    self.recv = [torch.empty_like(self.send) for _ in range(world)]
         self.host = torch.empty((self.height, self.width, 4), dtype=torch.uint8, pin_memory=True) if rank == 0 else None
 
+    def close(self):
+        if self._shared_ptr:
+            torch.cuda.synchronize(self.device)
+            if dist.is_initialized() and self.world > 1:
+                dist.barrier()          # nobody unmaps / frees while a peer may still write
+            self.fb = None
+            self._lib.rt_shared_buffer_close(self.device, self._shared_ptr, self._opened)
+            self._shared_ptr = None
+        self.engine.close()
+
     def enqueue(self, counters: bool = False) -> None:
-        """Kernel for this rank's chunks + gather to rank 0, on torch's current stream; no host sync."""
+        """Kernel for this rank's chunks + frame exchange towards rank 0, on torch's current stream; no host sync."""
         st = torch.cuda.current_stream(self.device).cuda_stream
-        self.engine.render_device(self.camera_index, d_rgba=self.fb.data_ptr(), stream=st, shard_index=self.rank,
+        self.engine.render_device(self.camera_index, d_rgba=self.fb_ptr, stream=st, shard_index=self.rank,
                                   shard_count=self.world, counters=counters, variant=self.variant)
-        gather_chunks(self.fb, self.rank, self.world, self.send, self.recv)
+        if self.gather == "p2p":
+            dist.all_reduce(self.flag)          # completion fence: returns on-stream once every rank's kernel is done
+        elif self.gather == "nccl":
+            gather_chunks(self.fb, self.rank, self.world, self.send, self.recv)
 
     def finish(self) -> dict:
         return self.engine.finish()
@@ -116,3 +165,12 @@ class ShardedRenderer:
     @property
     def d2h_bytes(self) -> int:
         return self.height * self.width * 4 if self.rank == 0 else 0
+
+
+def _wrap_device_memory(ptr: int, shape, device: int) -> torch.Tensor:
+    """uint8 torch view of a raw device allocation (no copy, no ownership) via __cuda_array_interface__."""
+    class _Raw:
+        pass
+    r = _Raw()
+    r.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
+    return torch.as_tensor(r, device=torch.device("cuda", device))

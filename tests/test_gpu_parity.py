@@ -107,3 +107,17 @@ def test_error_codes(scene_dir):
     with pytest.raises(RenderError) as e:
         empty.render(0)
     assert e.value.code == -20                            # "No scene loaded" (:142-145)
+
+
+def test_multi_gpu_frame_equals_single_gpu_frame():
+    """>= 2 GPUs only: torchrun, one rank per GPU, P2P (kernel stores into rank 0's frame) and NCCL gather."""
+    import os, subprocess, sys
+    import torch
+    n = min(torch.cuda.device_count(), 4)
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    here = os.path.dirname(os.path.abspath(__file__))
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr",
+                          "127.0.0.1", "--master-port", "29533", os.path.join(here, "mgpu_check.py")], capture_output=True,
+                         text=True, timeout=600)
+    assert out.returncode == 0 and "MGPU_OK" in out.stdout, out.stdout[-2000:] + out.stderr[-4000:]
