@@ -166,16 +166,22 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_FAST_BLOCKS) renderKernelFast(Dev
     const V3 ambient = ld3(S.ambient), background = ld3(S.background);
 
     for (;;) {
-        int tile = 0;
-        if (lane == 0) tile = atomicAdd(out.tileCounter, 1);
-        tile = __shfl_sync(0xffffffffu, tile, 0);
-        if (tile >= tiles.totalTiles) break;
+        // work unit: one 32-ray pass of a tile when the pixels of a pass are complete in themselves (ns divides
+        // 32), else the whole tile (the ordered per-pixel sum is carried across passes).  Small units keep the
+        // tail short when a frame is split over 8 GPUs (a few thousand warps share ~8k tiles per rank).
+        int unit = 0;
+        if (lane == 0) unit = atomicAdd(out.tileCounter, 1);
+        unit = __shfl_sync(0xffffffffu, unit, 0);
+        const int unitsPerTile = segmented ? ns : 1;
+        if (unit >= tiles.totalTiles * unitsPerTile) break;
+        const int tile = unit / unitsPerTile;
+        const int itBegin = segmented ? unit - tile * unitsPerTile : 0, itEnd = segmented ? itBegin + 1 : ns;
         int x0, y0;
         tiles.origin(tile, x0, y0);
         int openP = -1;               // ordered accumulation state of the generic path (warp-uniform)
         V3 acc = mk(0, 0, 0);
 #pragma unroll 1
-        for (int it = 0; it < ns; it++) {
+        for (int it = itBegin; it < itEnd; it++) {
             const int g = it * 32 + lane;
             const int p = g / ns, s = g - p * ns;
             // pixel p of the tile in Z-order: neighbouring lanes' pixels form compact blocks
