@@ -142,11 +142,10 @@ __device__ __forceinline__ double shflD(double v, int src) { return __shfl_sync(
 
 template <bool COUNT>
 __global__ void __launch_bounds__(RT_BLOCK, RT_FAST_BLOCKS) renderKernelFast(DeviceScene S, CameraParams cam, RenderTargets out) {
-    __shared__ int32_t sstack[RT_SSTACK * RT_BLOCK];
     __shared__ int2 wstacks[(RT_BLOCK / 32) * RT_WARP_STACK_INT2];
     const int lane = threadIdx.x & 31;
     TraceScratch T;
-    T.sstack = sstack;
+    T.sstack = nullptr; T.sstackN = 0;   // secondary rays keep their private stack in local memory: shared memory stays L1
     T.wstack = wstacks + (threadIdx.x >> 5) * RT_WARP_STACK_INT2;
     T.pathStack = out.pathStack;
     T.gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -294,7 +293,7 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_GEN_BLOCKS) renderKernelGeneral(D
     __shared__ int32_t sstack[RT_SSTACK * RT_BLOCK];
     const int lane = threadIdx.x & 31;
     TraceScratch T;
-    T.sstack = sstack;
+    T.sstack = sstack; T.sstackN = RT_SSTACK;
     T.wstack = nullptr;
     T.pathStack = out.pathStack;
     T.gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;

@@ -89,7 +89,8 @@ struct RayCounts {
 };
 
 struct TraceScratch {
-    int32_t* sstack;   // per-lane traversal stacks (shared memory, RT_STACK x RT_BLOCK)
+    int32_t* sstack;   // per-lane traversal stacks (shared memory, sstackN x RT_BLOCK; deeper entries in local memory)
+    int sstackN;
     int2* wstack;      // this warp's packet stack (shared memory, RT_WARP_STACK_INT2)
     double* pathStack; // per-thread recursion stack (global)
     size_t stride, gtid;
@@ -226,7 +227,7 @@ __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceSc
     for (;;) {
         HitRec hit;
         hit.t = CUDART_INF; hit.u = hit.v = 0; hit.inst = -1; hit.slot = 0;
-        traceScene<COUNT>(S, cur.o, cur.d, primary ? tMinPrimary : 0.0, hit, false, T.sstack, C);
+        traceScene<COUNT>(S, cur.o, cur.d, primary ? tMinPrimary : 0.0, hit, false, T.sstack, T.sstackN, C);
         Surface sf;
         if (hit.inst >= 0) {
             resolveHit(S, hit, cur.o, cur.d, sf);
@@ -255,7 +256,7 @@ __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceSc
                     HitRec sh;
                     sh.t = dist; sh.u = sh.v = 0; sh.inst = -1; sh.slot = 0;             // tMax = dist (:124)
                     R.shadow++;
-                    if (!traceScene<COUNT>(S, so, wi, 0.0, sh, true, T.sstack, C))
+                    if (!traceScene<COUNT>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, C))
                         Lo = Lo + pointLightTerm(*sp.mat, pl, sp.N, cur.d, wi, dist);
                 }
             }

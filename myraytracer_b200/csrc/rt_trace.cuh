@@ -45,24 +45,24 @@ __device__ __forceinline__ bool analyticInstance(const DeviceScene& S, const GIn
 // Closest-hit / any-hit test of one instance.  tLow = max(eps, tMin); hit.t = current closest t or tMax.
 template <bool COUNT>
 __device__ __forceinline__ bool enterInstance(const DeviceScene& S, int idx, V3 o, V3 d, double eps, double tMin,
-                                              HitRec& hit, bool anyhit, int32_t* sstack, Counters& C) {
+                                              HitRec& hit, bool anyhit, int32_t* sstack, int sstackN, Counters& C) {
     const GInstance& I = S.instances[idx];
     V3 oL, dL;
     toLocal(I, o, d, oL, dL);
     if (COUNT) C.inst++;
     const double tLow = dmax(eps, tMin);
-    if (I.kind == INST_MESH) return traverseBlas<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, sstack, C);
+    if (I.kind == INST_MESH) return traverseBlas<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, sstack, sstackN, C);
     return analyticInstance<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, C);
 }
 
 // TLAS walk (FP64 boxes = unions of Instance.worldBounds, widened interval; near child first).
 template <bool COUNT>
 __device__ __forceinline__ bool traceScene(const DeviceScene& S, V3 o, V3 d, double tMin, HitRec& hit, bool anyhit,
-                                           int32_t* sstack, Counters& C) {
+                                           int32_t* sstack, int sstackN, Counters& C) {
     const double eps = S.eps;
     int32_t cur = S.tlasRootRef;
     if (cur == kEmptyRef) return false;
-    if (cur < 0) return enterInstance<COUNT>(S, ~cur, o, d, eps, tMin, hit, anyhit, sstack, C);
+    if (cur < 0) return enterInstance<COUNT>(S, ~cur, o, d, eps, tMin, hit, anyhit, sstack, sstackN, C);
     const V3 ia = refinedInv(d);
     const double tLow = dmax(eps, tMin);
     int32_t tstack[RT_TLAS_STACK];
@@ -87,7 +87,7 @@ __device__ __forceinline__ bool traceScene(const DeviceScene& S, V3 o, V3 d, dou
             } else if (h0) { cur = c0; continue; }
             else if (h1) { cur = c1; continue; }
         } else {
-            if (enterInstance<COUNT>(S, ~cur, o, d, eps, tMin, hit, anyhit, sstack, C)) return true;
+            if (enterInstance<COUNT>(S, ~cur, o, d, eps, tMin, hit, anyhit, sstack, sstackN, C)) return true;
         }
         if (sp == 0) return false;
         cur = tstack[--sp];

@@ -145,7 +145,7 @@ __device__ __forceinline__ void loadTri(const DeviceScene& S, const GInstance& I
 // hit.t is the current closest t (closest) or tMax (any-hit); updated on accept.
 template <bool COUNT>
 __device__ __forceinline__ bool traverseBlas(const DeviceScene& S, const GInstance& I, int instIdx, V3 oL, V3 dL, double eps,
-                                             double tLow, HitRec& hit, bool anyhit, int32_t* sstack, Counters& C) {
+                                             double tLow, HitRec& hit, bool anyhit, int32_t* sstack, int sstackN, Counters& C) {
     // Advance the origin to the BLAS in FP64 so that its FP32 copy is accurate relative to the
     // box size: t0 = entry distance into the (exact) root box, from a widened FP64 slab test.
     V3 ia = refinedInv(dL);
@@ -170,8 +170,8 @@ __device__ __forceinline__ bool traverseBlas(const DeviceScene& S, const GInstan
     float tmaxF = __double2float_ru(hit.t - t0);
 
     const GNode* nodes = S.nodes + I.nodeBase;
-    // stack: the first RT_SSTACK entries in shared memory (per-lane column), deeper ones in local memory
-    int32_t lstack[RT_STACK - RT_SSTACK];
+    // stack: the first sstackN (<= RT_SSTACK) entries in shared memory (per-lane column), deeper ones in local memory
+    int32_t lstack[RT_STACK];
     int sp = 0;
     int32_t cur = I.rootRef;
     const int tid = threadIdx.x;
@@ -198,7 +198,7 @@ __device__ __forceinline__ bool traverseBlas(const DeviceScene& S, const GInstan
             if (h0 && h1) {
                 int32_t nearC = ch.x, farC = ch.y;
                 if (n1 < n0) { nearC = ch.y; farC = ch.x; }
-                if (sp < RT_SSTACK) sstack[sp * RT_BLOCK + tid] = farC; else lstack[sp - RT_SSTACK] = farC;
+                if (sp < sstackN) sstack[sp * RT_BLOCK + tid] = farC; else lstack[sp - sstackN] = farC;
                 sp++;
                 if (COUNT && sp > C.maxStack) C.maxStack = sp;
                 cur = nearC;
@@ -209,7 +209,7 @@ __device__ __forceinline__ bool traverseBlas(const DeviceScene& S, const GInstan
             } else {
                 if (sp == 0) return false;
                 sp--;
-                cur = sp < RT_SSTACK ? sstack[sp * RT_BLOCK + tid] : lstack[sp - RT_SSTACK];
+                cur = sp < sstackN ? sstack[sp * RT_BLOCK + tid] : lstack[sp - sstackN];
             }
         }
         if (cur != kEmptyRef) {  // leaf
@@ -229,7 +229,7 @@ __device__ __forceinline__ bool traverseBlas(const DeviceScene& S, const GInstan
         }
         if (sp == 0) return false;
         sp--;
-        cur = sp < RT_SSTACK ? sstack[sp * RT_BLOCK + tid] : lstack[sp - RT_SSTACK];
+        cur = sp < sstackN ? sstack[sp * RT_BLOCK + tid] : lstack[sp - sstackN];
     }
 }
 
