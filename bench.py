@@ -304,7 +304,7 @@ def run_ours(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = my_bytes / (kern_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "renderKernel<false>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+    roofline = {"bound": "hbm", "kernel": "renderKernelFast<false>" if not args.variant or args.variant == 1 else "renderKernelGeneral<false>", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": None, "peak_source": "measured" if peaks else "fallback",
                 "algorithmic_bytes_per_launch": my_bytes, "kernel_ms": kern_ms,
                 "counts": {k: int(cst[k]) for k in list(BYTES) + ["maxStack"]},

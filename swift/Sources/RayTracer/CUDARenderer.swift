@@ -1,0 +1,150 @@
+//
+//  CUDARenderer.swift — drop-in body for `Renderer` (Extensions/Object+Extension.swift:13-19, 52-379)
+//
+//  The binding a maintainer adds to the reference: same class name, same `init(ctx:)`, same
+//  `render(scene:cameraIndex:progressRow:) async throws -> [Vec3]`; the per-pixel loop, `trace`, the
+//  TLAS/BLAS traversal and the primitive tests run in the CRTCuda module (hand-written CUDA for sm_100a)
+//  instead of the Swift TaskGroup.  `renderRGBA8(...)` additionally hands back the RGBA8 frame the kernel
+//  already produced, so `renderRGBA8Async` (RayTracer.swift:186-195) can skip its conversion loop.
+//
+//  NOT COMPILED in this repository: no Swift toolchain exists in the build container or on the GPU box, and
+//  the reference itself needs Apple's `simd` and the un-vendored ParsingKit.  The identical C ABI is
+//  exercised by the C++ mirror in myraytracer_b200/host/ and by tests/ (see INTEGRATION.md).
+//
+
+import Foundation
+import simd
+import CRTCuda
+@preconcurrency import ParsingKit
+
+final class Renderer: @unchecked Sendable {
+    public let ctx: RTContext
+    private var handle: OpaquePointer?            // rt_scene_t*
+
+    /// Renderer(ctx:) — flattens RTContext (Models/RTContext.swift:74-92) into rt_scene_desc and uploads it.
+    public init(ctx: RTContext, scene: Scene, device: Int32 = 0) {
+        self.ctx = ctx
+        var triV = [Double](); triV.reserveCapacity(ctx.triangles.count * 9)
+        var triN = [Double](); triN.reserveCapacity(ctx.triangles.count * 9)
+        for t in ctx.triangles {
+            for v in [t.v0, t.v1, t.v2] { triV += [v.x, v.y, v.z] }
+            for n in [t.n0, t.n1, t.n2] { triN += [n.x, n.y, n.z] }
+        }
+        var spheres = ctx.spheres.map { rt_sphere(center: ($0.center.x, $0.center.y, $0.center.z), radius: $0.radius) }
+        var planes = ctx.planes.map { rt_plane(center: ($0.center.x, $0.center.y, $0.center.z),
+                                               normal: ($0.normal.x, $0.normal.y, $0.normal.z)) }
+        // BLAS.prims (RTContext.swift:34-42) become contiguous ranges of one prim array
+        var prims = [rt_prim](), blas = [rt_blas](), blasIndex = [ObjectIdentifier: Int32]()
+        var instances = [rt_instance]()
+        for inst in ctx.instances {
+            let key = ObjectIdentifier(inst.blas)
+            if blasIndex[key] == nil {
+                blasIndex[key] = Int32(blas.count)
+                blas.append(rt_blas(firstPrim: Int64(prims.count), primCount: Int64(inst.blas.prims.count)))
+                for p in inst.blas.prims {
+                    prims.append(rt_prim(type: Int32(p.type.rawValue), smooth: p.shadingMode == .smooth ? 1 : 0,
+                                         primitiveIndex: Int64(p.primitiveIndex), materialID: Int64(p.materialID)))
+                }
+            }
+            var ri = rt_instance()
+            ri.blas = blasIndex[key]!
+            ri.hasMaterialOverride = inst.materialOverride == nil ? 0 : 1
+            ri.materialOverride = Int64(inst.materialOverride ?? 0)
+            withUnsafeMutableBytes(of: &ri.localToWorld) { $0.copyBytes(from: Self.bytes(inst.localToWorld)) }
+            withUnsafeMutableBytes(of: &ri.worldToLocal) { $0.copyBytes(from: Self.bytes(inst.worldToLocal)) }
+            withUnsafeMutableBytes(of: &ri.normalMatrix) { $0.copyBytes(from: Self.bytes3(inst.normalMatrix)) }
+            ri.worldBounds = (inst.worldBounds.minP.x, inst.worldBounds.minP.y, inst.worldBounds.minP.z,
+                              inst.worldBounds.maxP.x, inst.worldBounds.maxP.y, inst.worldBounds.maxP.z)
+            ri.instanceMotion = (inst.instanceMotion.x, inst.instanceMotion.y, inst.instanceMotion.z)
+            instances.append(ri)
+        }
+        var materials = scene.materials.map { m -> rt_material in
+            var r = rt_material()
+            switch m.type { case "mirror": r.type = 1; case "dielectric": r.type = 2; case "conductor": r.type = 3; default: r.type = 0 }
+            r.ambient = (m.ambient.x, m.ambient.y, m.ambient.z); r.diffuse = (m.diffuse.x, m.diffuse.y, m.diffuse.z)
+            r.specular = (m.specular.x, m.specular.y, m.specular.z); r.mirror = (m.mirror.x, m.mirror.y, m.mirror.z)
+            r.absorption = (m.absorption.x, m.absorption.y, m.absorption.z)
+            r.phong = m.phong; r.ior = m.ior; r.absorptionIndex = m.absorptionIndex; r.roughness = m.roughness
+            return r
+        }
+        var lights = scene.lights.points.compactMap { $0 as? PointLight }.map {
+            rt_point_light(position: ($0.position.x, $0.position.y, $0.position.z),
+                           intensity: ($0.intensity.x, $0.intensity.y, $0.intensity.z))
+        }
+        var desc = rt_scene_desc()
+        desc.abiVersion = UInt32(RT_ABI_VERSION)
+        desc.nTriangles = Int64(ctx.triangles.count)
+        desc.nSpheres = Int64(spheres.count); desc.nPlanes = Int64(planes.count)
+        desc.nPrims = Int64(prims.count); desc.nBlas = Int64(blas.count); desc.nInstances = Int64(instances.count)
+        desc.nMaterials = Int64(materials.count); desc.nPointLights = Int64(lights.count)
+        desc.ambient = (scene.lights.ambient.x, scene.lights.ambient.y, scene.lights.ambient.z)
+        desc.background = (scene.backgroundColor.x, scene.backgroundColor.y, scene.backgroundColor.z)
+        desc.intersectionTestEpsilon = scene.intersectionTestEpsilon
+        desc.shadowRayEpsilon = scene.shadowRayEpsilon
+        desc.maxRecursionDepth = Int32(scene.maxRecursionDepth)
+        // borrowed pointers: valid for the duration of rt_scene_create only (the module copies to the device)
+        handle = triV.withUnsafeBufferPointer { v in triN.withUnsafeBufferPointer { n in
+            spheres.withUnsafeBufferPointer { s in planes.withUnsafeBufferPointer { p in
+            prims.withUnsafeBufferPointer { pr in blas.withUnsafeBufferPointer { b in
+            instances.withUnsafeBufferPointer { i in materials.withUnsafeBufferPointer { m in
+            lights.withUnsafeBufferPointer { l -> OpaquePointer? in
+                desc.triVertices = v.baseAddress; desc.triNormals = n.baseAddress
+                desc.spheres = s.baseAddress; desc.planes = p.baseAddress; desc.prims = pr.baseAddress
+                desc.blas = b.baseAddress; desc.instances = i.baseAddress; desc.materials = m.baseAddress
+                desc.pointLights = l.baseAddress
+                return rt_scene_create(&desc, device)          // NULL on failure, never throws (CPly convention)
+            } } } } } } } } }
+        if handle == nil { print("❌ CRTCuda: \(String(cString: rt_last_error()))") }
+    }
+
+    deinit { rt_scene_destroy(handle) }              // destroy(NULL) is safe
+
+    /// render(scene:cameraIndex:progressRow:) — same signature and result as the reference (:52-56): W*H Vec3, 0..255 scale.
+    @Sendable public func render(scene: Scene, cameraIndex: Int = 0,
+                                 progressRow: (@Sendable (Int) -> Void)? = nil) async throws -> [Vec3] {
+        let (linear, _, _) = try renderBoth(scene: scene, cameraIndex: cameraIndex, wantLinear: true, wantRGBA: false, progressRow: progressRow)
+        return linear
+    }
+
+    /// RGBA8 straight from the kernel epilogue (clamp + truncate, alpha 255: RayTracer.swift:186-195) + ray counts.
+    public func renderRGBA8(scene: Scene, cameraIndex: Int = 0,
+                            progressRow: (@Sendable (Int) -> Void)? = nil) throws -> ([UInt8], rt_stats) {
+        let (_, rgba, st) = try renderBoth(scene: scene, cameraIndex: cameraIndex, wantLinear: false, wantRGBA: true, progressRow: progressRow)
+        return (rgba, st)
+    }
+
+    private func renderBoth(scene: Scene, cameraIndex: Int, wantLinear: Bool, wantRGBA: Bool,
+                            progressRow: (@Sendable (Int) -> Void)?) throws -> ([Vec3], [UInt8], rt_stats) {
+        guard let handle else { throw NSError(domain: "Render", code: -21, userInfo: [NSLocalizedDescriptionKey: "Renderer not initialized."]) }
+        let cam = scene.cameras[cameraIndex]
+        let width = max(1, cam.imageResolution.0), height = max(1, cam.imageResolution.1)
+        var rc = rt_camera()
+        rc.width = Int32(width); rc.height = Int32(height); rc.numSamples = Int32(cam.numSamples)
+        rc.isLookAt = (cam.type?.lowercased() == "lookat") ? 1 : 0
+        rc.hasFovy = cam.fovy == nil ? 0 : 1; rc.fovy = cam.fovy ?? 0
+        rc.position = (cam.position.x, cam.position.y, cam.position.z); rc.gaze = (cam.gaze.x, cam.gaze.y, cam.gaze.z)
+        rc.gazePoint = (cam.gazePoint.x, cam.gazePoint.y, cam.gazePoint.z); rc.up = (cam.up.x, cam.up.y, cam.up.z)
+        rc.nearPlane = (cam.nearPlane[0], cam.nearPlane[1], cam.nearPlane[2], cam.nearPlane[3])
+        rc.nearDistance = cam.nearDistance; rc.apertureSize = cam.apertureSize; rc.focusDistance = cam.focusDistance
+        var linear = [Double](repeating: 0, count: wantLinear ? width * height * 3 : 0)
+        var rgba = [UInt8](repeating: 0, count: wantRGBA ? width * height * 4 : 0)
+        var stats = rt_stats()
+        var params = rt_render_params()               // whole frame on this GPU, automatic kernel choice
+        let status = linear.withUnsafeMutableBufferPointer { lp in rgba.withUnsafeMutableBufferPointer { rp in
+            rt_render(handle, &rc, &params, wantRGBA ? rp.baseAddress : nil, wantLinear ? lp.baseAddress : nil, nil, &stats)
+        } }
+        guard status == RT_OK else {
+            throw NSError(domain: "Render", code: Int(status), userInfo: [NSLocalizedDescriptionKey: String(cString: rt_last_error())])
+        }
+        progressRow?(height - 1)                      // the GPU frame completes at once
+        var out = [Vec3](); out.reserveCapacity(width * height)
+        if wantLinear { for p in 0..<(width * height) { out.append(Vec3(linear[3 * p], linear[3 * p + 1], linear[3 * p + 2])) } }
+        return (out, rgba, stats)
+    }
+
+    private static func bytes(_ m: Mat4) -> [UInt8] { withUnsafeBytes(of: m) { Array($0) } }          // simd_double4x4 is column-major
+    private static func bytes3(_ m: simd_double3x3) -> [UInt8] {                                       // 3 columns padded to 32 B each
+        var out = [Double](); for c in [m.columns.0, m.columns.1, m.columns.2] { out += [c.x, c.y, c.z] }
+        return out.withUnsafeBytes { Array($0) }
+    }
+}
