@@ -308,8 +308,17 @@ def run_ours(args):
                 "frac": achieved / peak, "traffic": None, "peak_source": "measured" if peaks else "fallback",
                 "algorithmic_bytes_per_launch": my_bytes, "kernel_ms": kern_ms,
                 "counts": {k: int(cst[k]) for k in list(BYTES) + ["maxStack"]},
-                "note": "working set (nodes+triangles) is mostly L2-resident at C4, so the HBM fraction is low by "
-                        "construction; the path is latency/issue bound — see profiles/ and DESIGN.md"}
+                "note": "algorithmic bytes are served by L1/L2 (traffic = ncu DRAM bytes of one launch), so a fraction above 1 "
+                        "only says the working set is cache resident; the path is issue/latency bound — profiles/, "
+                        "DESIGN.md section 5"}
+    try:   # DRAM traffic of one launch from the committed `ncu --set full` capture of this workload (profiles/)
+        tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        key = f"{args.config}_n{world}_v{args.variant}"
+        if key in tr:
+            roofline["traffic"] = tr[key]["dram_bytes_per_launch"]
+            roofline["traffic_source"] = tr[key]["source"]
+    except Exception:
+        pass
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
