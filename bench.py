@@ -243,7 +243,8 @@ def run_ours(args):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     def step():
-        flush.zero_()                     # L2 flush between timed iterations (outside the event pair)
+        if not args.no_flush:
+            flush.zero_()                 # L2 flush between timed iterations (outside the event pair)
         e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
         e0.record()
         R.enqueue()
@@ -266,6 +267,7 @@ def run_ours(args):
     barrier()
     wall = time.perf_counter() - wall0
     clocks = sampler.stop() if rank == 0 else None
+    log(f"[rank {rank}] step {ms_sum / args.steps:.3f} ms, kernel {kern_ms_sum / args.steps:.3f} ms, rays {st['rays']}")
     ms_step = allreduce(ms_sum / args.steps, dist.ReduceOp.MAX if world > 1 else None)
     rays = allreduce(float(st["rays"]), dist.ReduceOp.SUM if world > 1 else None)
     rp = allreduce(float(st["raysPrimary"]), dist.ReduceOp.SUM if world > 1 else None)
@@ -325,7 +327,7 @@ def run_ours(args):
             "config": {"workload": BENCH_CONFIGS[args.config][2], "width": W, "height": H, "triangles": info["triangles"],
                        "rays_per_frame": int(rays), "rays_primary": int(rp), "rays_shadow": int(rs),
                        "rays_secondary": int(rays - rp - rs), "parallelism": f"tiles{world}", "gather": R.gather, "kernel_variant": args.variant,
-                       "l2": "256 MB buffer written between timed iterations (L2 flush); scene working set "
+                       "l2": ("NOT FLUSHED (diagnostic run); " if args.no_flush else "") + "256 MB buffer written between timed iterations (L2 flush); scene working set "
                              f"{info['deviceBytes'] / 1e6:.0f} MB"},
             "wall_ms_per_step": wall * 1e3 / args.steps, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
             "roofline": roofline, "build_ms": info["buildMs"], "upload_ms": info["uploadMs"]}
@@ -354,6 +356,7 @@ def main():
     ap.add_argument("--config", choices=sorted(BENCH_CONFIGS), default="c4")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--no-flush", action="store_true", help="diagnostic only: skip the L2 flush between frames")
     ap.add_argument("--gather", choices=["p2p", "nccl"], default="p2p",
                     help="N>1 framebuffer exchange: kernel stores into rank 0's frame over NVLink (p2p) or NCCL gather")
     ap.add_argument("--variant", type=int, default=0, help="rt_render_params.kernelVariant (0 = automatic; A/B runs)")

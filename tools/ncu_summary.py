@@ -14,6 +14,7 @@ from collections import defaultdict
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 from ncu_by_line import line_map  # noqa: E402
 
+SORT = 0 if os.environ.get("NCU_SORT") == "inst" else 2
 KEYS = ["gpu__time_duration.sum", "launch__registers_per_thread", "launch__grid_size", "launch__block_size",
         "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__thread_inst_executed_per_inst_executed.ratio",
         "sm__inst_executed.avg.per_cycle_active", "smsp__issue_active.avg.pct_of_peak_sustained_active",
@@ -78,7 +79,7 @@ def source(rep, obj, pat, top):
           f"(executed {tot[4]} = {tot[4] * 16 / 1024:.1f} KB)")
     for title, dct, n in (("by file", byfile, 20), ("by line", byline, top)):
         print(f"-- {title}: inst%  samples%  avg-threads  executed-SASS")
-        for k, e in sorted(dct.items(), key=lambda kv: -kv[1][2])[:n]:
+        for k, e in sorted(dct.items(), key=lambda kv: -kv[1][SORT])[:n]:
             print(f"  {k:30s} {100 * e[0] / max(1, tot[0]):6.2f} {100 * e[2] / max(1, tot[2]):6.2f} {e[1] / max(1, e[0]):6.1f} {e[3]:6d}")
 
 
