@@ -229,7 +229,8 @@ def run_ours(args):
 
     t0 = time.time()
     path = make_scene(args.config, rank)
-    R = ShardedRenderer(path, device=local, rank=rank, world=world, variant=args.variant, gather=args.gather)
+    R = ShardedRenderer(path, device=local, rank=rank, world=world, variant=args.variant, gather=args.gather, balance=args.balance,
+                        schedule=1 if args.schedule == "spatial" else 0)
     info = R.engine.scene_info()
     W, H = R.width, R.height
     log(f"[rank {rank}] scene ready in {time.time() - t0:.1f}s: {info}")
@@ -238,6 +239,8 @@ def run_ours(args):
     R.enqueue(counters=True)
     cst = R.finish()
     my_pixels = sum(min(8, H - c * 8) for c in owned_chunks(H, rank, world)) * W
+    if R.balance == "dynamic":
+        my_pixels = W * H // world    # units are drawn dynamically; the share is ~1/world
     my_bytes = algorithmic_bytes(cst, my_pixels)
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
@@ -275,6 +278,18 @@ def run_ours(args):
     value = rays / (ms_step * 1e-3) / 1e6
     kern_ms = kern_ms_sum / args.steps
     launches = int(allreduce(float(st["kernelLaunches"] * args.steps), dist.ReduceOp.SUM if world > 1 else None))
+    scheduled = int(st["tilesScheduled"])
+
+    # ---- the same frame with the tiles drawn top to bottom (what the first frame of a camera gets), for comparison
+    spatial_ms = None
+    if R.schedule == 0:
+        R.schedule = 1
+        step()
+        barrier()
+        sp_sum = sum(step()[0] for _ in range(min(5, args.steps)))
+        spatial_ms = allreduce(sp_sum / min(5, args.steps), dist.ReduceOp.MAX if world > 1 else None)
+        R.schedule = 0
+        barrier()
 
     # ---- e2e: public call, framebuffer back in pinned host memory every step
     for _ in range(2):
@@ -326,7 +341,10 @@ def run_ours(args):
             "data": "synthetic",
             "config": {"workload": BENCH_CONFIGS[args.config][2], "width": W, "height": H, "triangles": info["triangles"],
                        "rays_per_frame": int(rays), "rays_primary": int(rp), "rays_shadow": int(rs),
-                       "rays_secondary": int(rays - rp - rs), "parallelism": f"tiles{world}", "gather": R.gather, "kernel_variant": args.variant,
+                       "rays_secondary": int(rays - rp - rs), "parallelism": f"tiles{world}", "gather": R.gather, "balance": R.balance, "kernel_variant": args.variant,
+                       "schedule": ("tiles drawn longest-first from the per-tile cost recorded on the previous frame "
+                                    f"({scheduled} tiles on rank 0); warm-up frames train it" if scheduled else "spatial order"),
+                       "ms_per_step_spatial_order": spatial_ms,
                        "l2": ("NOT FLUSHED (diagnostic run); " if args.no_flush else "") + "256 MB buffer written between timed iterations (L2 flush); scene working set "
                              f"{info['deviceBytes'] / 1e6:.0f} MB"},
             "wall_ms_per_step": wall * 1e3 / args.steps, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
@@ -354,11 +372,15 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--config", choices=sorted(BENCH_CONFIGS), default="c4")
+    ap.add_argument("--schedule", choices=["adaptive", "spatial"], default="adaptive",
+                    help="rt_render_params.scheduleMode: tile order learnt from the previous frame, or top to bottom")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-flush", action="store_true", help="diagnostic only: skip the L2 flush between frames")
     ap.add_argument("--gather", choices=["p2p", "nccl"], default="p2p",
                     help="N>1 framebuffer exchange: kernel stores into rank 0's frame over NVLink (p2p) or NCCL gather")
+    ap.add_argument("--balance", choices=["static", "dynamic"], default="static",
+                    help="N>1: chunks dealt round-robin (static) or one work counter shared over NVLink (dynamic)")
     ap.add_argument("--variant", type=int, default=0, help="rt_render_params.kernelVariant (0 = automatic; A/B runs)")
     args = ap.parse_args()
     capture_stdout()

@@ -128,6 +128,9 @@ typedef struct rt_camera {
  * return non-zero to cancel (RayTracer.swift:178-180) */
 typedef int (*rt_progress_fn)(int32_t rowsDone, int32_t rowsTotal, void* user);
 
+#define RT_SCHEDULE_ADAPTIVE 0
+#define RT_SCHEDULE_SPATIAL  1
+
 typedef struct rt_render_params {
     /* 8-row chunks c with c % shardCount == shardIndex are rendered; other rows are left untouched.
      * shardCount <= 1 renders the whole frame.  (Multi-process sharding: one rank per GPU.) */
@@ -138,6 +141,19 @@ typedef struct rt_render_params {
                                    * a scene with roughness != 0), 2 = general kernel (lane = pixel, sequential RNG). */
     rt_progress_fn progress;      /* may be NULL */
     void* progressUser;
+    /* Dynamic work sharing between GPUs (optional, rt_render_device only): device pointer to a zeroed int32 that
+     * every participating rank passes for the same frame — typically in rank 0's memory, mapped by the peers with
+     * rt_shared_buffer_open.  Warps of all GPUs then draw 32-ray work units of the WHOLE frame from this one counter
+     * with system-scope atomics over NVLink (shardIndex/shardCount must be 0/1), so every GPU finishes at the same
+     * time whatever the image content.  The caller zeroes the counter before any rank launches the frame. */
+    void* workCounter;
+    int32_t workGroups;           /* number of GPUs sharing workCounter; > 1 makes the draws system-scope atomics */
+    /* Order in which the warps draw the 8x4-pixel tiles of the frame.  RT_SCHEDULE_ADAPTIVE (0, default): every frame
+     * records the time spent per tile, and the next frame with the same image size, sample count, shard and kernel
+     * draws the longest tiles first, so that it ends on its cheapest work instead of waiting for a few slow packets
+     * (rt_stats.tilesScheduled tells whether a learnt order was used; the first frame uses the spatial order).
+     * RT_SCHEDULE_SPATIAL (1): always top to bottom.  The image is the same either way. */
+    int32_t scheduleMode;
 } rt_render_params;
 
 /* identity of one primary ray's closest hit (the reference's Hit has no primitive id) */
@@ -159,6 +175,7 @@ typedef struct rt_stats {
     /* only with collectCounters: */
     int64_t boxTests, triTests, sphereTests, planeTests, instEntries, maxStack;
     int64_t smoothHits;           /* closest hits resolved on smooth-shaded triangles (3 normals fetched) */
+    int64_t tilesScheduled;       /* tiles drawn in the cost order learnt from the previous frame (0: spatial order) */
 } rt_stats;
 
 typedef struct rt_scene_info {
@@ -181,6 +198,10 @@ const char* rt_last_error(void);
 rt_scene_t* rt_scene_create(const rt_scene_desc* desc, int32_t device);
 void rt_scene_destroy(rt_scene_t* scene);
 int32_t rt_scene_get_info(const rt_scene_t* scene, rt_scene_info* out);
+/* The tile order the next frame of the last rendered geometry will use (rt_render_params.scheduleMode): returns the
+ * number of tiles (0: nothing learnt yet, < 0: error) and copies min(n, capacity) entries — slot k draws tile
+ * orderOut[k], tiles numbered row-major within the shard (8x4 pixels each).  No reference analogue; for tests. */
+int64_t rt_scene_get_schedule(rt_scene_t* scene, int32_t* orderOut, int64_t capacity);
 
 /* Render one camera.  Blocking.  Host buffers, all optional except one of rgbaOut/linearOut:
  *   rgbaOut   width*height*4 bytes, row 0 = top (RayTracer.swift:186-195)

@@ -89,7 +89,8 @@ rt_progress_fn = C.CFUNCTYPE(C.c_int, C.c_int32, C.c_int32, C.c_void_p)
 
 class rt_render_params(C.Structure):
     _fields_ = [("shardIndex", C.c_int32), ("shardCount", C.c_int32), ("collectCounters", C.c_int32),
-                ("kernelVariant", C.c_int32), ("progress", rt_progress_fn), ("progressUser", C.c_void_p)]
+                ("kernelVariant", C.c_int32), ("progress", rt_progress_fn), ("progressUser", C.c_void_p),
+                ("workCounter", C.c_void_p), ("workGroups", C.c_int32), ("scheduleMode", C.c_int32)]
 
 
 class rt_stats(C.Structure):
@@ -97,7 +98,7 @@ class rt_stats(C.Structure):
                                          "raysPrimary", "raysShadow", "raysSecondary")]
     _fields_ += [("deviceMs", C.c_double), ("kernelLaunches", C.c_int64)]
     _fields_ += [(n, C.c_int64) for n in ("boxTests", "triTests", "sphereTests", "planeTests", "instEntries", "maxStack",
-                                         "smoothHits")]
+                                         "smoothHits", "tilesScheduled")]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -116,7 +117,7 @@ HIT_ID_DTYPE = np.dtype([("inst", "<i4"), ("kind", "<i4"), ("prim", "<i8"), ("t"
 
 # every symbol include/rtcuda.h and include/rtcuda_host.h declare
 EXPORTS = ["rt_abi_version", "rt_device_count", "rt_last_error", "rt_scene_create", "rt_scene_destroy",
-           "rt_scene_get_info", "rt_render", "rt_render_device", "rt_render_finish",
+           "rt_scene_get_info", "rt_scene_get_schedule", "rt_render", "rt_render_device", "rt_render_finish",
            "rt_shared_buffer_create", "rt_shared_buffer_open", "rt_shared_buffer_close",
            "rth_last_error", "rth_engine_create", "rth_engine_destroy", "rth_engine_ready", "rth_engine_camera_count",
            "rth_engine_camera", "rth_engine_scene", "rth_engine_describe", "rth_engine_instance_object_ids",
@@ -143,6 +144,8 @@ def load():
     L.rt_scene_destroy.argtypes = [vp]
     L.rt_scene_destroy.restype = None
     L.rt_scene_get_info.argtypes = [vp, C.POINTER(rt_scene_info)]
+    L.rt_scene_get_schedule.argtypes = [vp, C.POINTER(C.c_int32), C.c_int64]
+    L.rt_scene_get_schedule.restype = C.c_int64
     L.rt_render.argtypes = [vp, C.POINTER(rt_camera), C.POINTER(rt_render_params), vp, vp, vp, C.POINTER(rt_stats)]
     L.rt_render_device.argtypes = [vp, C.POINTER(rt_camera), C.POINTER(rt_render_params), vp, vp, vp, vp]
     L.rt_render_finish.argtypes = [vp, C.POINTER(rt_stats)]

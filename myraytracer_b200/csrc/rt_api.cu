@@ -9,6 +9,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -66,6 +67,11 @@ struct rt_scene {
     TNode* dTlas = nullptr; GInstance* dInst = nullptr; GMaterial* dMat = nullptr; GPointLight* dLights = nullptr;
     // render state (re-used across calls)
     int* dTileCounter = nullptr; unsigned long long* dCounters = nullptr;
+    // tile schedule learnt from the previous frame of the same geometry (rt_kernels.cu: scheduleKernel)
+    unsigned* dTileCost = nullptr; size_t tileCostBytes = 0;
+    int* dTileOrder = nullptr; size_t tileOrderBytes = 0;
+    unsigned* dSchedWork = nullptr; size_t schedWorkBytes = 0;
+    int schedKey[8] = {}; bool schedValid = false; int64_t pendingScheduled = 0;
     double* dPathStack = nullptr; size_t pathStackBytes = 0;
     uint8_t* dRgba = nullptr; size_t rgbaBytes = 0;
     double* dLinear = nullptr; size_t linearBytes = 0;
@@ -275,6 +281,7 @@ void rt_scene_destroy(rt_scene_t* sc) {
     cudaSetDevice(sc->device);
     cudaFree(sc->dNodes); cudaFree(sc->dTris); cudaFree(sc->dTrisD); cudaFree(sc->dNormals); cudaFree(sc->dTlas);
     cudaFree(sc->dInst); cudaFree(sc->dMat); cudaFree(sc->dLights); cudaFree(sc->dTileCounter); cudaFree(sc->dCounters);
+    cudaFree(sc->dTileCost); cudaFree(sc->dTileOrder); cudaFree(sc->dSchedWork);
     cudaFree(sc->dPathStack); cudaFree(sc->dRgba); cudaFree(sc->dLinear); cudaFree(sc->dIds);
     if (sc->hCounters) cudaFreeHost(sc->hCounters);
     if (sc->evStart) cudaEventDestroy(sc->evStart);
@@ -302,6 +309,19 @@ int32_t rt_scene_get_info(const rt_scene_t* sc, rt_scene_info* out) {
     if (!sc || !out) return fail(RT_ERR_NO_SCENE, "No scene loaded. Can't render.");
     *out = sc->info;
     return RT_OK;
+}
+
+int64_t rt_scene_get_schedule(rt_scene_t* sc, int32_t* orderOut, int64_t capacity) {
+    if (!sc) return fail(RT_ERR_NO_SCENE, "No scene loaded. Can't render.");
+    if (sc->pending) return fail(RT_ERR_INVALID, "a render is in flight on this scene (call rt_render_finish)");
+    if (!sc->schedValid) return 0;
+    const int64_t n = sc->schedKey[7];
+    if (orderOut && capacity > 0) {
+        if (cudaSetDevice(sc->device) != cudaSuccess ||
+            cudaMemcpy(orderOut, sc->dTileOrder, (size_t)(n < capacity ? n : capacity) * sizeof(int32_t), cudaMemcpyDeviceToHost) != cudaSuccess)
+            return fail(RT_ERR_CUDA, "rt_scene_get_schedule: copy failed");
+    }
+    return n;
 }
 
 }  // extern "C"

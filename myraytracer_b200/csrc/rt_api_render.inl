@@ -53,10 +53,14 @@ int buildCamera(const rt_camera* c, const rt_render_params* prm, CameraParams& c
     cp.width = W; cp.height = H;
     cp.samples = c->numSamples > 1 ? c->numSamples : 1;
     cp.n = (int)std::sqrt((double)cp.samples);
-    cp.shardIndex = 0; cp.shardCount = 1;
+    cp.shardIndex = 0; cp.shardCount = 1; cp.workGroups = 1;
     if (prm && prm->shardCount > 1) {
         if (prm->shardIndex < 0 || prm->shardIndex >= prm->shardCount) return fail(RT_ERR_INVALID, "shardIndex outside [0, shardCount)");
         cp.shardIndex = prm->shardIndex; cp.shardCount = prm->shardCount;
+    }
+    if (prm && prm->workCounter) {
+        if (prm->shardCount > 1) return fail(RT_ERR_INVALID, "workCounter shares the whole frame: shardCount must be 0 or 1");
+        cp.workGroups = prm->workGroups > 1 ? prm->workGroups : 1;
     }
     return RT_OK;
 }
@@ -74,6 +78,12 @@ int ensure(T** p, size_t* have, size_t need) {
 }  // namespace
 
 extern "C" {
+
+#ifdef RT_WARPTIMES
+static unsigned long long* g_wt = nullptr;
+static size_t g_wtBytes = 0;
+static unsigned long long g_wtWarps = 0;
+#endif
 
 int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_render_params* params, void* dRgbaOut,
                          void* dLinearOut, void* dIdsOut, void* cudaStream) {
@@ -101,15 +111,50 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
 
     RenderTargets rt{};
     rt.rgba = (uint8_t*)dRgbaOut; rt.linear = (double*)dLinearOut; rt.ids = (HitId*)dIdsOut;
-    rt.pathStack = sc->dPathStack; rt.tileCounter = sc->dTileCounter; rt.counters = sc->dCounters;
+    rt.pathStack = sc->dPathStack; rt.counters = sc->dCounters;
+    const bool sharedCounter = params && params->workCounter;
+    rt.tileCounter = sharedCounter ? (int*)params->workCounter : sc->dTileCounter;
+    // Tile schedule: the frame records its cost per tile, the next frame of the same geometry draws the longest
+    // tiles first.  Not with a counter shared between GPUs (each rank sees only part of the costs).
+    const int tilesX = (cp.width + 7) / 8, nChunks = (cp.height + 7) / 8;
+    const int nTiles = (nChunks - cp.shardIndex + cp.shardCount - 1) / cp.shardCount * tilesX * 2;
+    const bool adaptive = !(params && params->scheduleMode == RT_SCHEDULE_SPATIAL) && !sharedCounter && nTiles > 0;
+    if (params && (params->scheduleMode < 0 || params->scheduleMode > RT_SCHEDULE_SPATIAL)) return fail(RT_ERR_INVALID, "scheduleMode outside 0..1");
+    sc->pendingScheduled = 0;
+    if (adaptive) {
+        const int key[8] = {cp.width, cp.height, cp.n, cp.dof, cp.shardIndex, cp.shardCount, variant, nTiles};
+        const bool grown = sc->tileCostBytes < (size_t)nTiles * 4 || sc->tileOrderBytes < (size_t)nTiles * 4;
+        if ((rc = ensure(&sc->dTileCost, &sc->tileCostBytes, (size_t)nTiles * 4))) return rc;
+        if ((rc = ensure(&sc->dTileOrder, &sc->tileOrderBytes, (size_t)nTiles * 4))) return rc;
+        if ((rc = ensure(&sc->dSchedWork, &sc->schedWorkBytes, scheduleWorkBytes(nTiles)))) return rc;
+        if (grown || std::memcmp(key, sc->schedKey, sizeof key) != 0) sc->schedValid = false;
+        std::memcpy(sc->schedKey, key, sizeof key);
+        if (!sc->schedValid) CK(cudaMemsetAsync(sc->dTileCost, 0, (size_t)nTiles * 4, st));
+        rt.tileCost = sc->dTileCost;
+        rt.tileOrder = sc->schedValid ? sc->dTileOrder : nullptr;
+        sc->pendingScheduled = sc->schedValid ? nTiles : 0;
+    }
+#ifdef RT_WARPTIMES
+    {   // profiling build: per-warp timestamps, dumped by rt_render_finish to $RT_WARPTIMES_OUT
+        static unsigned long long* dWT = nullptr; static size_t wtBytes = 0;
+        const size_t needWT = (threads / 32 * 4 + (size_t)((cp.width + 7) / 8) * ((cp.height + 7) / 8 * 2) * 16 * 4) * sizeof(unsigned long long);
+        if ((rc = ensure(&dWT, &wtBytes, needWT))) return rc;
+        CK(cudaMemsetAsync(dWT, 0, needWT, st));
+        rt.warpTimes = dWT; g_wt = dWT; g_wtBytes = needWT; g_wtWarps = threads / 32;
+    }
+#endif
     CK(cudaEventRecord(sc->evStart, st));
-    CK(cudaMemsetAsync(sc->dTileCounter, 0, 64, st));
+    if (!sharedCounter) CK(cudaMemsetAsync(sc->dTileCounter, 0, 64, st));
     CK(cudaMemsetAsync(sc->dCounters, 0, 16 * sizeof(unsigned long long), st));
     CK(launchRender(variant, sc->ds, cp, rt, blocks, counters, st));
+    if (adaptive) {
+        CK(launchSchedule(sc->dTileCost, sc->dTileOrder, sc->dSchedWork, nTiles, st));      // costs of this frame -> order of the next
+        sc->schedValid = true;
+    }
     CK(cudaMemcpyAsync(sc->hCounters, sc->dCounters, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
     CK(cudaEventRecord(sc->evStop, st));
     sc->pending = true; sc->pendingCounters = counters; sc->pendingStream = st;
-    sc->launches = 1;
+    sc->launches = adaptive ? 3 : 1;
     return RT_OK;
 }
 
@@ -121,6 +166,13 @@ int32_t rt_render_finish(rt_scene_t* sc, rt_stats* st) {
     CK(cudaEventSynchronize(sc->evStop));
     float ms = 0;
     CK(cudaEventElapsedTime(&ms, sc->evStart, sc->evStop));
+#ifdef RT_WARPTIMES
+    if (const char* path = getenv("RT_WARPTIMES_OUT")) {
+        std::vector<unsigned long long> h(g_wtBytes / 8);
+        CK(cudaMemcpy(h.data(), g_wt, g_wtBytes, cudaMemcpyDeviceToHost));
+        if (FILE* f = fopen(path, "wb")) { fwrite(&g_wtWarps, 8, 1, f); fwrite(h.data(), 8, h.size(), f); fclose(f); }
+    }
+#endif
     if (st) {
         std::memset(st, 0, sizeof *st);
         st->meshes = sc->meshes; st->triangles = sc->info.triangles; st->spheres = sc->info.spheres; st->planes = sc->info.planes;
@@ -129,6 +181,7 @@ int32_t rt_render_finish(rt_scene_t* sc, rt_stats* st) {
         st->rays = st->raysPrimary + st->raysShadow + st->raysSecondary;
         st->deviceMs = ms;
         st->kernelLaunches = sc->launches;
+        st->tilesScheduled = sc->pendingScheduled;
         if (sc->pendingCounters) {
             st->boxTests = (int64_t)sc->hCounters[3]; st->triTests = (int64_t)sc->hCounters[4];
             st->sphereTests = (int64_t)sc->hCounters[5]; st->planeTests = (int64_t)sc->hCounters[6];

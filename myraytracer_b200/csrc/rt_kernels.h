@@ -20,6 +20,11 @@ struct RenderTargets {
     double* pathStack;             // (maxDepth+1) * PATH_FIELDS * totalThreads doubles
     int* tileCounter;              // zeroed before launch
     unsigned long long* counters;  // 16 x u64, zeroed before launch
+    const int* tileOrder;          // schedule: slot -> tile of this shard (null = identity)
+    unsigned* tileCost;            // per tile, clocks/64 spent on it this frame (null = not recorded); zeroed before launch
+#ifdef RT_WARPTIMES
+    unsigned long long* warpTimes; // profiling build only: 4 x u64 per warp (start, first unit done, last draw, exit; ns)
+#endif
 };
 
 static const int kPathFields = 11;
@@ -39,6 +44,9 @@ enum KernelVariant { KV_FAST = 0, KV_GENERAL = 1, KV_COUNT = 2 };
 
 cudaError_t launchRender(int variant, const DeviceScene& S, const CameraParams& cam, const RenderTargets& out, int blocks,
                          bool counters, cudaStream_t stream);
+// tileCost (clocks per tile of the frame just rendered) -> tileOrder for the next frame, longest first; clears tileCost
+cudaError_t launchSchedule(unsigned* tileCost, int* tileOrder, unsigned* work, int nTiles, cudaStream_t stream);
+size_t scheduleWorkBytes(int nTiles);   // scratch of launchSchedule
 int renderBlockSize();
 int renderStackCapacity();
 cudaError_t renderOccupancy(int variant, int* blocksPerSm, bool counters);

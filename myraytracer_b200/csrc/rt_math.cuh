@@ -70,6 +70,18 @@ struct PCG32 {
         next();
     }
     __device__ __forceinline__ double nextFloat() { return (double)next() * 2.3283064365386963e-10; }
+    // (A^k, 1 + A + ... + A^(k-1)) mod 2^64: with them k draws are skipped by `state = A^k state + G inc`
+    __device__ __forceinline__ static void skipFactors(uint64_t k, uint64_t& ak, uint64_t& gk) {
+        uint64_t curMult = 6364136223846793005ULL, curPlus = 1, accMult = 1, accPlus = 0;
+        while (k > 0) {
+            if (k & 1) { accMult *= curMult; accPlus = accPlus * curMult + curPlus; }
+            curPlus = (curMult + 1) * curPlus;
+            curMult *= curMult;
+            k >>= 1;
+        }
+        ak = accMult; gk = accPlus;
+    }
+    __device__ __forceinline__ void skip(uint64_t ak, uint64_t gk) { state = ak * state + gk * inc; }
     // skip `delta` draws in O(log delta): the LCG state after k steps is A^k*s + (A^k-1)/(A-1)*inc
     __device__ __forceinline__ void advance(uint64_t delta) {
         uint64_t curMult = 6364136223846793005ULL, curPlus = inc, accMult = 1, accPlus = 0;

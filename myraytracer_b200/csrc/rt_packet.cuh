@@ -20,11 +20,18 @@
 namespace rtg {
 
 #define RT_FULL 0xffffffffu
+
+__device__ __forceinline__ void prefetchL1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 #ifndef RT_WSTACK
 #define RT_WSTACK 64    // BLAS entries per warp (tree depth is checked against RT_STACK at build time)
 #endif
 #define RT_WTSTACK 40   // TLAS entries per warp
-#define RT_WARP_STACK_INT2 (RT_WSTACK + RT_WTSTACK)
+#ifdef RT_WARPTIMES
+#define RT_WT_EXTRA 2   // profiling build: (node visits, lanes), (leaf visits, lane-triangle tests) per warp
+#else
+#define RT_WT_EXTRA 0
+#endif
+#define RT_WARP_STACK_INT2 (RT_WSTACK + RT_WTSTACK + RT_WT_EXTRA)
 
 // Packet walk of one mesh BLAS.  inMask (warp-uniform): lanes whose ray takes part.
 // anyhit: run-time, warp-uniform (one copy of the loop for closest-hit and shadow packets).
@@ -78,8 +85,17 @@ __device__ __forceinline__ uint32_t packetBlas(const DeviceScene& S, const GInst
             const float4* np = reinterpret_cast<const float4*>(nodes + cur);
             const float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2);
             const int4 ch = __ldg(reinterpret_cast<const int4*>(np + 3));
+#ifdef RT_PREFETCH
+            // both children are requested before the box tests decide between them: the next visit's node
+            // (an L1 miss most of the time) is already on its way while this one is tested
+            if ((uint32_t)ch.x < 0x7fffffffu) prefetchL1(nodes + ch.x);
+            if ((uint32_t)ch.y < 0x7fffffffu) prefetchL1(nodes + ch.y);
+#endif
             const bool inl = (curMask & bit) != 0;
             if (COUNT && inl) C.box += 2;
+#ifdef RT_WARPTIMES
+            if (bit == 1u) { wstack[RT_WSTACK + RT_WTSTACK].x++; wstack[RT_WSTACK + RT_WTSTACK].y += __popc(curMask); }
+#endif
             float a0 = __fmaf_rn(q0.x, ix, nx), b0 = __fmaf_rn(q0.w, ix, nx);
             float a1 = __fmaf_rn(q0.y, iy, ny), b1 = __fmaf_rn(q1.x, iy, ny);
             float a2 = __fmaf_rn(q0.z, iz, nz), b2 = __fmaf_rn(q1.y, iz, nz);
@@ -113,6 +129,9 @@ __device__ __forceinline__ uint32_t packetBlas(const DeviceScene& S, const GInst
             const int first = I.triBase + (int)(ref >> 3), count = (int)(ref & 7u) + 1;
             const bool inl = (curMask & bit) != 0;
             bool occ = false;
+#ifdef RT_WARPTIMES
+            if (bit == 1u) { wstack[RT_WSTACK + RT_WTSTACK + 1].x++; wstack[RT_WSTACK + RT_WTSTACK + 1].y += __popc(curMask) * count; }
+#endif
             for (int k = 0; k < count; k++) {
                 V3 v0, v1, v2;
                 loadTri(S, I, first + k, v0, v1, v2);

@@ -32,6 +32,9 @@ namespace rtg {
 #ifndef RT_FAST_BLOCKS
 #define RT_FAST_BLOCKS 8
 #endif
+#ifndef RT_SKIPTAB
+#define RT_SKIPTAB 1
+#endif
 #ifndef RT_GEN_BLOCKS
 #define RT_GEN_BLOCKS 5
 #endif
@@ -138,6 +141,14 @@ struct TileMap {
     }
 };
 
+#ifdef RT_WARPTIMES
+__device__ __forceinline__ unsigned long long globalTimerNs() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+#endif
+
 __device__ __forceinline__ double shflD(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
 
 template <bool COUNT>
@@ -163,18 +174,57 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_FAST_BLOCKS) renderKernelFast(Dev
     const double samplesD = (double)cam.samples;     // the sum is divided by `samples` (:354)
     const bool segmented = ns < 32 && (32 % ns) == 0;
     const V3 ambient = ld3(S.ambient), background = ld3(S.background);
+    // sample s of a lane is the same in every pass when n*n divides 32: its skip-ahead factors are computed once
+    __shared__ ulonglong2 skipTab[RT_BLOCK];
+    {
+        uint64_t ak = 1, gk = 0;
+        if (segmented) PCG32::skipFactors((uint64_t)((lane % ns) * drawsPerSample), ak, gk);
+        skipTab[threadIdx.x] = make_ulonglong2(ak, gk);
+        __syncwarp();
+    }
+    const int unitsPerTile = segmented ? ns : 1;
+    const int totalUnits = tiles.totalTiles * unitsPerTile;
+    const bool remoteCounter = cam.workGroups > 1;          // counter shared with peer GPUs (rt_render_params.workCounter)
+    __shared__ uint2 unitNote[RT_BLOCK / 32];               // (clock at unit start, tile): read back when the unit ends
+#ifdef RT_WARPTIMES
+    unsigned long long wt0 = globalTimerNs(), wt1 = 0, wt2 = 0;
+    int wtUnits = 0, wtUnit = 0;
+#endif
 
     for (;;) {
+#ifdef RT_WARPTIMES
+        if (wtUnits == 1) wt1 = globalTimerNs();
+        if (wtUnits > 0 && lane == 0 && out.warpTimes) {    // [4 x warps] then (start, end, visits, tests) per unit
+            unsigned long long* u = out.warpTimes + 4 * (T.stride >> 5) + 4 * (size_t)wtUnit;
+            const int2 a = T.wstack[RT_WSTACK + RT_WTSTACK], b = T.wstack[RT_WSTACK + RT_WTSTACK + 1];
+            u[1] = globalTimerNs();
+            u[2] = ((unsigned long long)(unsigned)a.x << 32) | (unsigned)a.y;
+            u[3] = ((unsigned long long)(unsigned)b.x << 32) | (unsigned)b.y;
+        }
+        if (lane == 0) T.wstack[RT_WSTACK + RT_WTSTACK] = T.wstack[RT_WSTACK + RT_WTSTACK + 1] = make_int2(0, 0);
+        __syncwarp();
+        wt2 = globalTimerNs();
+        wtUnits++;
+#endif
         // work unit: one 32-ray pass of a tile when the pixels of a pass are complete in themselves (ns divides
         // 32), else the whole tile (the ordered per-pixel sum is carried across passes).  Small units keep the
         // tail short when a frame is split over 8 GPUs (a few thousand warps share ~8k tiles per rank).
+        // One unit per draw: consecutive units go to warps running at the same time, which share tiles, BVH
+        // nodes and triangles in L2 (drawing 8 at a time measured 10 % slower).
         int unit = 0;
-        if (lane == 0) unit = atomicAdd(out.tileCounter, 1);
+        if (lane == 0) unit = remoteCounter ? atomicAdd_system(out.tileCounter, 1) : atomicAdd(out.tileCounter, 1);
         unit = __shfl_sync(0xffffffffu, unit, 0);
-        const int unitsPerTile = segmented ? ns : 1;
-        if (unit >= tiles.totalTiles * unitsPerTile) break;
-        const int tile = unit / unitsPerTile;
-        const int itBegin = segmented ? unit - tile * unitsPerTile : 0, itEnd = segmented ? itBegin + 1 : ns;
+        if (unit >= totalUnits) break;
+        // Slot -> tile through the schedule of this frame: tiles in descending order of the cost measured on the
+        // previous frame (longest first), so the frame ends on its cheapest units instead of a few slow ones.
+        const int slot = unit / unitsPerTile;
+        const int tile = out.tileOrder ? __ldg(out.tileOrder + slot) : slot;
+        if (lane == 0) unitNote[threadIdx.x >> 5] = make_uint2((unsigned)clock(), (unsigned)tile);
+#ifdef RT_WARPTIMES
+        wtUnit = tile * unitsPerTile + (unit - slot * unitsPerTile);     // records are indexed by (tile, pass)
+        if (lane == 0 && out.warpTimes) out.warpTimes[4 * (T.stride >> 5) + 4 * (size_t)wtUnit] = wt2;
+#endif
+        const int itBegin = segmented ? unit - slot * unitsPerTile : 0, itEnd = segmented ? itBegin + 1 : ns;
         int x0, y0;
         tiles.origin(tile, x0, y0);
         int openP = -1;               // ordered accumulation state of the generic path (warp-uniform)
@@ -190,7 +240,8 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_FAST_BLOCKS) renderKernelFast(Dev
             const int sy = s / n, sx = s - sy * n;
             PCG32 rng;
             rng.seed((((uint64_t)j << 32) ^ (uint64_t)i) + 0x9E3779B97F4A7C15ULL);  // :294 (Swift precedence)
-            rng.advance((uint64_t)(s * drawsPerSample));
+            if (RT_SKIPTAB && segmented) rng.skip(skipTab[threadIdx.x].x, skipTab[threadIdx.x].y);   // s is fixed per lane
+            else rng.advance((uint64_t)(s * drawsPerSample));
             const PrimaryRay pr = primaryRay(cam, i, j, sx, sy, rng);
             if (active) R.primary++;
             PathEntry cur0;
@@ -244,11 +295,11 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_FAST_BLOCKS) renderKernelFast(Dev
                 } else if (finite3(Lo)) {                                               // :277-280
                     c = c + sp.w * Lo;
                     PathEntry c1, c2;
-                    const int nc = spawnChildren(S, sp, cur0, rng, c1, c2);
+                    const int nc = spawnChildren<false>(S, sp, cur0, rng, c1, c2);
                     if (nc > 0) {
                         if (nc == 2) pathStore(T.pathStack, T.stride, T.gtid, 0, c2);
                         R.secondary += nc;
-                        c = scalarPathLoop<COUNT>(S, T, c1, nc - 1, false, 0.0, nullptr, rng, C, R, c);
+                        c = scalarPathLoop<false, COUNT>(S, T, c1, nc - 1, false, 0.0, nullptr, rng, C, R, c);
                     }
                 }
             }
@@ -284,7 +335,17 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_FAST_BLOCKS) renderKernelFast(Dev
             const int qx = (openP & 1) | ((openP >> 1) & 2) | ((openP >> 2) & 4), qy = ((openP >> 1) & 1) | ((openP >> 2) & 2);
             if (x0 + qx < W && y0 + qy < H) writePixel(out, (size_t)(y0 + qy) * W + (x0 + qx), acc / samplesD);
         }
+        if (out.tileCost && lane == 0) {       // cost of the unit in clocks/64, summed per tile for the next frame's schedule
+            const uint2 note = unitNote[threadIdx.x >> 5];
+            atomicAdd(out.tileCost + note.y, ((unsigned)clock() - note.x) >> 6);
+        }
     }
+#ifdef RT_WARPTIMES
+    if (lane == 0 && out.warpTimes) {
+        unsigned long long* w = out.warpTimes + 4 * (T.gtid >> 5);
+        w[0] = wt0; w[1] = wt1; w[2] = wt2; w[3] = globalTimerNs();
+    }
+#endif
     flushCounters<COUNT>(out, C, R);
 }
 
@@ -308,11 +369,14 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_GEN_BLOCKS) renderKernelGeneral(D
     const TileMap tiles(cam);
     const int n = cam.n, samples = cam.samples;
 
+    const bool remoteCounter = cam.workGroups > 1;
     for (;;) {
-        int tile = 0;
-        if (lane == 0) tile = atomicAdd(out.tileCounter, 1);
-        tile = __shfl_sync(0xffffffffu, tile, 0);
-        if (tile >= tiles.totalTiles) break;
+        int slot = 0;
+        if (lane == 0) slot = remoteCounter ? atomicAdd_system(out.tileCounter, 1) : atomicAdd(out.tileCounter, 1);
+        slot = __shfl_sync(0xffffffffu, slot, 0);
+        if (slot >= tiles.totalTiles) break;
+        const int tile = out.tileOrder ? __ldg(out.tileOrder + slot) : slot;    // longest tiles of the previous frame first
+        const unsigned c0 = (unsigned)clock();
         int x0, y0;
         tiles.origin(tile, x0, y0);
         const int i = x0 + (lane & 7), j = y0 + (lane >> 3);
@@ -329,11 +393,13 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_GEN_BLOCKS) renderKernelGeneral(D
                 HitId* idSlot = out.ids ? out.ids + (((size_t)j * W + i) * (size_t)(n * n) + (size_t)(sy * n + sx)) : nullptr;
                 PathEntry cur0;
                 cur0.o = pr.o; cur0.d = pr.d; cur0.w = mk(1, 1, 1); cur0.beerMat = 0; cur0.depth = 0; cur0.beer = 0;
-                pixel = pixel + scalarPathLoop<COUNT>(S, T, cur0, 0, true, pr.tMin, idSlot, rng, C, R, mk(0, 0, 0));
+                pixel = pixel + scalarPathLoop<true, COUNT>(S, T, cur0, 0, true, pr.tMin, idSlot, rng, C, R, mk(0, 0, 0));
                 sampleIndex++;
             }
         }
         writePixel(out, (size_t)j * W + i, pixel / (double)samples);                                   // :354
+        __syncwarp();
+        if (out.tileCost && lane == 0) atomicAdd(out.tileCost + tile, ((unsigned)clock() - c0) >> 6);
     }
     flushCounters<COUNT>(out, C, R);
 }

@@ -148,6 +148,9 @@ __device__ __forceinline__ V3 pointLightTerm(const GMaterial& mat, const GPointL
 }
 
 // Recursive branches of `trace` (:189-275): fills c1 (always) and c2 (refraction) and returns the child count.
+// GLOSSY = false compiles the roughness perturbations (and their RNG draws) out: the fast kernel runs only on
+// scenes where every roughness is 0, so its RNG state is dead after primary-ray generation.
+template <bool GLOSSY>
 __device__ __forceinline__ int spawnChildren(const DeviceScene& S, const ShadePoint& sp, const PathEntry& cur, PCG32& rng,
                                              PathEntry& c1, PathEntry& c2) {
     const GMaterial& mat = *sp.mat;
@@ -159,7 +162,7 @@ __device__ __forceinline__ int spawnChildren(const DeviceScene& S, const ShadePo
     c1.beer = c2.beer = 0; c1.beerMat = c2.beerMat = 0;
     if (mat.type == 1) {                                                                // mirror :189-206
         V3 rd = normalize(reflectDir(cur.d, N));
-        if (mat.roughness != 0) {
+        if (GLOSSY && mat.roughness != 0) {
             V3 t, b;
             orthonormalBasis(rd, t, b);
             const double rand1 = rng.nextFloat() - 0.5;
@@ -170,7 +173,7 @@ __device__ __forceinline__ int spawnChildren(const DeviceScene& S, const ShadePo
         c1.o = p + N * shadowEps; c1.d = rd; c1.w = w * ld3(mat.mirror);
     } else if (mat.type == 2) {                                                         // dielectric :207-251
         V3 mN = N;
-        if (mat.roughness != 0) {
+        if (GLOSSY && mat.roughness != 0) {
             V3 t, b;
             orthonormalBasis(N, t, b);
             const double r1 = (rng.nextFloat() * 2.0) - 1.0;
@@ -201,7 +204,7 @@ __device__ __forceinline__ int spawnChildren(const DeviceScene& S, const ShadePo
         const double cosI = dmax(0.0, -dot(cur.d, N));
         const double Rf = fresnelConductor(mat.ior, mat.absorptionIndex, cosI);
         V3 rd = normalize(reflectDir(cur.d, N));
-        if (mat.roughness != 0) {
+        if (GLOSSY && mat.roughness != 0) {
             V3 t, b;
             orthonormalBasis(rd, t, b);
             const double rand1 = rng.nextFloat() - 0.5;
@@ -218,7 +221,7 @@ __device__ __forceinline__ int spawnChildren(const DeviceScene& S, const ShadePo
 // `level` the number of entries already waiting on this thread's path stack.  firstIsPrimary: `cur` is the
 // camera ray (tMin = near-plane clip :341-344, hit id recorded).  Returns `color` plus the w * Lo of all
 // processed entries, added in processing order.
-template <bool COUNT>
+template <bool GLOSSY, bool COUNT>
 __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceScratch& T, PathEntry cur, int level,
                                              bool firstIsPrimary, double tMinPrimary, HitId* idSlot, PCG32& rng, Counters& C,
                                              RayCounts& R, V3 color) {
@@ -263,7 +266,7 @@ __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceSc
             if (finite3(Lo)) {                                                          // NaN guard, :277-280
                 color = color + sp.w * Lo;
                 PathEntry c1, c2;
-                const int nc = spawnChildren(S, sp, cur, rng, c1, c2);
+                const int nc = spawnChildren<GLOSSY>(S, sp, cur, rng, c1, c2);
                 if (nc == 2) { pathStore(T.pathStack, T.stride, T.gtid, level, c2); level++; }
                 if (nc > 0) { cur = c1; spawned = 1; R.secondary += nc; }
             }

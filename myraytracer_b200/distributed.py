@@ -74,10 +74,16 @@ class ShardedRenderer:
     maps it over NVLink (CUDA IPC); each rank's render kernel stores its finished pixels straight into rank 0's
     frame, and one 4-byte all-reduce on the launch stream tells rank 0 that every rank's kernel has completed.
     gather="nccl": each rank renders into a private frame, packs its chunks and rank 0 gathers them (NCCL or gloo).
+
+    balance="static": rank r renders the 8-row chunks c with c % world == r (rt_render_params.shardIndex/Count).
+    balance="dynamic" (needs gather="p2p"): one work counter in rank 0's memory, mapped by every rank; the warps of
+    all GPUs draw 32-ray units of the whole frame from it with system-scope atomics over NVLink, so the GPUs finish
+    together whatever the image content.  Two counter slots alternate between frames; rank 0 zeroes the slot of the
+    next frame on its stream after the completion fence of the previous one.
     """
 
     def __init__(self, scene_url: str, device: int = 0, rank: Optional[int] = None, world: Optional[int] = None,
-                 camera_index: int = 0, variant: int = 0, gather: str = "p2p"):
+                 camera_index: int = 0, variant: int = 0, gather: str = "p2p", balance: str = "static", schedule: int = 0):
         import ctypes as C
         from . import capi
         from .engine import RayTracerEngine
@@ -87,7 +93,11 @@ class ShardedRenderer:
             world = dist.get_world_size() if dist.is_initialized() else 1
         self.rank, self.world, self.device, self.camera_index = rank, world, device, camera_index
         self.variant = variant  # rt_render_params.kernelVariant (0 = automatic)
+        self.schedule = schedule  # rt_render_params.scheduleMode (0 = longest tiles of the previous frame first)
         self.gather = gather if world > 1 else "none"
+        self.balance = balance if (world > 1 and self.gather == "p2p") else "static"
+        self.frame = 0
+        self._ctr_ptr, self._ctr_opened, self.ctr = None, 0, None
         self.engine = RayTracerEngine(scene_url, device=device)
         if not self.engine.ready:
             raise RuntimeError("engine not ready: " + self.engine.load_error)
@@ -99,26 +109,16 @@ class ShardedRenderer:
         self._lib, self._shared_ptr, self._opened = capi.load(), None, 0
         if self.gather == "p2p":
             nbytes = hp * self.width * 4
-            handle = torch.zeros(capi.RT_IPC_HANDLE_BYTES, dtype=torch.uint8)
-            ptr = C.c_void_p()
-            if rank == 0:
-                hb = (C.c_uint8 * capi.RT_IPC_HANDLE_BYTES)()
-                rc = self._lib.rt_shared_buffer_create(device, nbytes, C.byref(ptr), hb)
-                if rc != 0:
-                    raise RuntimeError("rt_shared_buffer_create: " + self._lib.rt_last_error().decode())
-                handle = torch.tensor(list(hb), dtype=torch.uint8)
-            hdev = handle.to(dev)
-            dist.broadcast(hdev, src=0)
-            if rank != 0:
-                hb = (C.c_uint8 * capi.RT_IPC_HANDLE_BYTES)(*hdev.cpu().tolist())
-                rc = self._lib.rt_shared_buffer_open(device, hb, C.byref(ptr))
-                if rc != 0:
-                    raise RuntimeError("rt_shared_buffer_open: " + self._lib.rt_last_error().decode())
-                self._opened = 1
+            ptrv, self._opened = self._share(nbytes, dev, C, capi)
+            ptr = C.c_void_p(ptrv)
             self._shared_ptr = ptr.value
             self.fb_ptr = ptr.value
             self.fb = None
             self.flag = torch.zeros(1, dtype=torch.int32, device=dev)
+            if self.balance == "dynamic":
+                self._ctr_ptr, self._ctr_opened = self._share(256, dev, C, capi)
+                if rank == 0:
+                    self.ctr = _wrap_device_memory(self._ctr_ptr, (256,), device)
             if rank == 0:   # rank 0 reads the frame through torch: wrap the raw allocation without copying
                 self.fb = _wrap_device_memory(ptr.value, (hp, self.width, 4), device)
         else:
@@ -130,21 +130,52 @@ class ShardedRenderer:
                     self.recv = [torch.empty_like(self.send) for _ in range(world)]
         self.host = torch.empty((self.height, self.width, 4), dtype=torch.uint8, pin_memory=True) if rank == 0 else None
 
+    def _share(self, nbytes, dev, C, capi):
+        """rank 0 allocates `nbytes` of zeroed device memory and every other rank maps it (CUDA IPC): (pointer, opened)."""
+        handle = torch.zeros(capi.RT_IPC_HANDLE_BYTES, dtype=torch.uint8)
+        ptr = C.c_void_p()
+        if self.rank == 0:
+            hb = (C.c_uint8 * capi.RT_IPC_HANDLE_BYTES)()
+            rc = self._lib.rt_shared_buffer_create(self.device, nbytes, C.byref(ptr), hb)
+            if rc != 0:
+                raise RuntimeError("rt_shared_buffer_create: " + self._lib.rt_last_error().decode())
+            handle = torch.tensor(list(hb), dtype=torch.uint8)
+        hdev = handle.to(dev)
+        dist.broadcast(hdev, src=0)
+        opened = 0
+        if self.rank != 0:
+            hb = (C.c_uint8 * capi.RT_IPC_HANDLE_BYTES)(*hdev.cpu().tolist())
+            rc = self._lib.rt_shared_buffer_open(self.device, hb, C.byref(ptr))
+            if rc != 0:
+                raise RuntimeError("rt_shared_buffer_open: " + self._lib.rt_last_error().decode())
+            opened = 1
+        return ptr.value, opened
+
     def close(self):
         if self._shared_ptr:
             torch.cuda.synchronize(self.device)
             if dist.is_initialized() and self.world > 1:
                 dist.barrier()          # nobody unmaps / frees while a peer may still write
-            self.fb = None
+            self.fb = self.ctr = None
             self._lib.rt_shared_buffer_close(self.device, self._shared_ptr, self._opened)
-            self._shared_ptr = None
+            if self._ctr_ptr:
+                self._lib.rt_shared_buffer_close(self.device, self._ctr_ptr, self._ctr_opened)
+            self._shared_ptr = self._ctr_ptr = None
         self.engine.close()
 
     def enqueue(self, counters: bool = False) -> None:
         """Kernel for this rank's chunks + frame exchange towards rank 0, on torch's current stream; no host sync."""
         st = torch.cuda.current_stream(self.device).cuda_stream
-        self.engine.render_device(self.camera_index, d_rgba=self.fb_ptr, stream=st, shard_index=self.rank,
-                                  shard_count=self.world, counters=counters, variant=self.variant)
+        if self.balance == "dynamic":
+            slot = self.frame & 1
+            if self.rank == 0:      # zero the slot of the NEXT frame: nobody uses it before the fence below has passed
+                self.ctr[(1 - slot) * 128:(1 - slot) * 128 + 4].zero_()
+            self.engine.render_device(self.camera_index, d_rgba=self.fb_ptr, stream=st, counters=counters,
+                                      variant=self.variant, work_counter=self._ctr_ptr + slot * 128, work_groups=self.world)
+            self.frame += 1
+        else:
+            self.engine.render_device(self.camera_index, d_rgba=self.fb_ptr, stream=st, shard_index=self.rank,
+                                      shard_count=self.world, counters=counters, variant=self.variant, schedule=self.schedule)
         if self.gather == "p2p":
             dist.all_reduce(self.flag)          # completion fence: returns on-stream once every rank's kernel is done
         elif self.gather == "nccl":

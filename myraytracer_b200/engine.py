@@ -86,6 +86,16 @@ class RayTracerEngine:
             raise RenderError(-21, self._lib.rt_last_error().decode())
         return info.as_dict()
 
+    def schedule(self) -> np.ndarray:
+        """rt_scene_get_schedule: tile order learnt for the next frame (empty before the first adaptive frame)."""
+        n = self._lib.rt_scene_get_schedule(self.scene_handle(), None, 0)
+        if n < 0:
+            raise RenderError(int(n), self._lib.rt_last_error().decode())
+        out = np.zeros(n, np.int32)
+        if n:
+            self._lib.rt_scene_get_schedule(self.scene_handle(), out.ctypes.data_as(C.POINTER(C.c_int32)), n)
+        return out
+
     def describe(self) -> capi.rt_scene_desc:
         d = capi.rt_scene_desc()
         rc = self._lib.rth_engine_describe(self._h, C.byref(d))
@@ -102,7 +112,7 @@ class RayTracerEngine:
     # -- render -----------------------------------------------------------
     def render(self, camera_index: int = 0, want_linear: bool = False, want_ids: bool = False,
                shard_index: int = 0, shard_count: int = 1, counters: bool = False,
-               progress: Optional[Callable[[int, int], bool]] = None, variant: int = 0) -> RenderResult:
+               progress: Optional[Callable[[int, int], bool]] = None, variant: int = 0, schedule: int = 0) -> RenderResult:
         if not self._h or self._lib.rth_engine_camera_count(self._h) == 0 and not self.ready:
             pass  # let the C side produce the reference's error codes
         cam = None
@@ -119,6 +129,7 @@ class RayTracerEngine:
         prm = capi.rt_render_params()
         prm.shardIndex, prm.shardCount, prm.collectCounters = shard_index, shard_count, 1 if counters else 0
         prm.kernelVariant = variant
+        prm.scheduleMode = schedule     # 0: longest tiles of the previous frame first, 1: spatial order
         cb = None
         if progress is not None:
             cb = capi.rt_progress_fn(lambda done, total, _u: 0 if progress(done, total) else 1)
@@ -131,13 +142,17 @@ class RayTracerEngine:
 
 
     def render_device(self, camera_index: int = 0, d_rgba: int = 0, d_linear: int = 0, d_ids: int = 0, stream: int = 0,
-                      shard_index: int = 0, shard_count: int = 1, counters: bool = False, variant: int = 0) -> None:
+                      shard_index: int = 0, shard_count: int = 1, counters: bool = False, variant: int = 0,
+                      work_counter: int = 0, work_groups: int = 1, schedule: int = 0) -> None:
         """rt_render_device: enqueue one frame on `stream` with caller-owned DEVICE buffers (raw pointers,
         e.g. torch.Tensor.data_ptr()); does not synchronise.  Pair with finish()."""
         cam = self.camera(camera_index)
         prm = capi.rt_render_params()
         prm.shardIndex, prm.shardCount, prm.collectCounters = shard_index, shard_count, 1 if counters else 0
         prm.kernelVariant = variant
+        prm.workCounter = work_counter or None
+        prm.workGroups = work_groups
+        prm.scheduleMode = schedule
         rc = self._lib.rt_render_device(self.scene_handle(), C.byref(cam), C.byref(prm), d_rgba or None, d_linear or None,
                                         d_ids or None, stream or None)
         if rc != 0:

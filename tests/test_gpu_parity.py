@@ -95,6 +95,56 @@ def test_shards_are_bit_identical(scene_dir):
         assert np.array_equal(acc, full)
 
 
+@pytest.mark.parametrize("variant", [1, 2])
+def test_tile_schedule_does_not_change_the_frame(variant, scene_dir):
+    """rt_render_params.scheduleMode: the second frame draws its tiles in the cost order learnt from the first;
+    pixels, linear colours and hit ids are those of the spatial order, whole frame and per shard."""
+    path = scenegen.config_c3(scene_dir, width=200, height=120, samples=4, depth=3, ico_level=2)
+    eng = RayTracerEngine(path)
+    ref = eng.render(0, want_linear=True, want_ids=True, variant=variant, schedule=1)
+    assert ref.stats["tilesScheduled"] == 0
+    first = eng.render(0, want_linear=True, want_ids=True, variant=variant)
+    assert first.stats["tilesScheduled"] == 0               # nothing learnt yet: spatial order
+    assert sorted(eng.schedule().tolist()) == list(range(25 * 30))      # a permutation of the tiles
+    for _ in range(3):
+        again = eng.render(0, want_linear=True, want_ids=True, variant=variant)
+        assert again.stats["tilesScheduled"] == 25 * 30      # 8x4 tiles of the 200x120 frame
+        assert again.stats["kernelLaunches"] == 3
+        for a in (first, again):
+            assert np.array_equal(a.rgba, ref.rgba)
+            assert np.array_equal(a.linear, ref.linear)
+            assert np.array_equal(a.ids, ref.ids)
+        assert again.stats["rays"] == ref.stats["rays"]
+        assert sorted(eng.schedule().tolist()) == list(range(25 * 30))
+    # another shard layout invalidates the order, then learns its own
+    part = [eng.render(0, shard_index=1, shard_count=2, variant=variant) for _ in range(2)]
+    assert part[0].stats["tilesScheduled"] == 0 and part[1].stats["tilesScheduled"] == 25 * 2 * 7
+    assert np.array_equal(part[0].rgba, part[1].rgba)
+    assert sorted(eng.schedule().tolist()) == list(range(25 * 2 * 7))
+    rows = np.zeros(120, bool)
+    for c in range(1, 15, 2):
+        rows[c * 8:(c + 1) * 8] = True
+    assert np.array_equal(part[1].rgba[rows], ref.rgba[rows]) and (part[1].rgba[~rows] == 0).all()
+
+
+def test_tile_schedule_many_tiles(scene_dir):
+    """More tiles than one block of the schedule kernels sorts (1024): still a permutation, same frame."""
+    path = scenegen.config_c1(scene_dir, width=648, height=404)
+    eng = RayTracerEngine(path)
+    ref = eng.render(0, schedule=1).rgba
+    n_tiles = 81 * 51 * 2                                      # 51 chunks of 8 rows, two tile rows each
+    for k in range(3):
+        out = eng.render(0)
+        assert out.stats["tilesScheduled"] == (n_tiles if k else 0)
+        assert np.array_equal(out.rgba, ref)
+        order = eng.schedule()
+        assert len(order) == n_tiles and np.array_equal(np.sort(order), np.arange(n_tiles))
+    # tiles past the last image row (404 = 50.5 chunks) trace nothing: they are drawn towards the end
+    slot = np.empty(n_tiles, np.int64)
+    slot[order] = np.arange(n_tiles)
+    assert np.median(slot[n_tiles - 81:]) > 0.75 * n_tiles
+
+
 def test_error_codes(scene_dir):
     path = scenegen.config_c1(scene_dir, width=32, height=32)
     eng = RayTracerEngine(path)
