@@ -229,7 +229,7 @@ def run_ours(args):
 
     t0 = time.time()
     path = make_scene(args.config, rank)
-    R = ShardedRenderer(path, device=local, rank=rank, world=world, variant=args.variant, gather=args.gather, balance=args.balance,
+    R = ShardedRenderer(path, device=local, rank=rank, world=world, variant=args.variant, gather=args.gather,
                         schedule=1 if args.schedule == "spatial" else 0)
     info = R.engine.scene_info()
     W, H = R.width, R.height
@@ -239,8 +239,6 @@ def run_ours(args):
     R.enqueue(counters=True)
     cst = R.finish()
     my_pixels = sum(min(8, H - c * 8) for c in owned_chunks(H, rank, world)) * W
-    if R.balance == "dynamic":
-        my_pixels = W * H // world    # units are drawn dynamically; the share is ~1/world
     my_bytes = algorithmic_bytes(cst, my_pixels)
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
@@ -341,7 +339,7 @@ def run_ours(args):
             "data": "synthetic",
             "config": {"workload": BENCH_CONFIGS[args.config][2], "width": W, "height": H, "triangles": info["triangles"],
                        "rays_per_frame": int(rays), "rays_primary": int(rp), "rays_shadow": int(rs),
-                       "rays_secondary": int(rays - rp - rs), "parallelism": f"tiles{world}", "gather": R.gather, "balance": R.balance, "kernel_variant": args.variant,
+                       "rays_secondary": int(rays - rp - rs), "parallelism": f"tiles{world}", "gather": R.gather, "kernel_variant": args.variant,
                        "schedule": ("tiles drawn longest-first from the per-tile cost recorded on the previous frame "
                                     f"({scheduled} tiles on rank 0); warm-up frames train it" if scheduled else "spatial order"),
                        "ms_per_step_spatial_order": spatial_ms,
@@ -379,8 +377,6 @@ def main():
     ap.add_argument("--no-flush", action="store_true", help="diagnostic only: skip the L2 flush between frames")
     ap.add_argument("--gather", choices=["p2p", "nccl"], default="p2p",
                     help="N>1 framebuffer exchange: kernel stores into rank 0's frame over NVLink (p2p) or NCCL gather")
-    ap.add_argument("--balance", choices=["static", "dynamic"], default="static",
-                    help="N>1: chunks dealt round-robin (static) or one work counter shared over NVLink (dynamic)")
     ap.add_argument("--variant", type=int, default=0, help="rt_render_params.kernelVariant (0 = automatic; A/B runs)")
     args = ap.parse_args()
     capture_stdout()

@@ -141,19 +141,13 @@ typedef struct rt_render_params {
                                    * a scene with roughness != 0), 2 = general kernel (lane = pixel, sequential RNG). */
     rt_progress_fn progress;      /* may be NULL */
     void* progressUser;
-    /* Dynamic work sharing between GPUs (optional, rt_render_device only): device pointer to a zeroed int32 that
-     * every participating rank passes for the same frame — typically in rank 0's memory, mapped by the peers with
-     * rt_shared_buffer_open.  Warps of all GPUs then draw 32-ray work units of the WHOLE frame from this one counter
-     * with system-scope atomics over NVLink (shardIndex/shardCount must be 0/1), so every GPU finishes at the same
-     * time whatever the image content.  The caller zeroes the counter before any rank launches the frame. */
-    void* workCounter;
-    int32_t workGroups;           /* number of GPUs sharing workCounter; > 1 makes the draws system-scope atomics */
     /* Order in which the warps draw the 8x4-pixel tiles of the frame.  RT_SCHEDULE_ADAPTIVE (0, default): every frame
      * records the time spent per tile, and the next frame with the same image size, sample count, shard and kernel
      * draws the longest tiles first, so that it ends on its cheapest work instead of waiting for a few slow packets
      * (rt_stats.tilesScheduled tells whether a learnt order was used; the first frame uses the spatial order).
      * RT_SCHEDULE_SPATIAL (1): always top to bottom.  The image is the same either way. */
     int32_t scheduleMode;
+    int32_t reserved2;
 } rt_render_params;
 
 /* identity of one primary ray's closest hit (the reference's Hit has no primitive id) */

@@ -113,7 +113,7 @@ struct CameraParams {
     int32_t width, height, samples, n;  // n = floor(sqrt(samples))
     int32_t dof;
     int32_t shardIndex, shardCount;
-    int32_t workGroups;           // GPUs drawing from the same work counter (1 unless rt_render_params.workCounter is shared)
+    int32_t pad;
 };
 
 }  // namespace rtg

@@ -53,14 +53,10 @@ int buildCamera(const rt_camera* c, const rt_render_params* prm, CameraParams& c
     cp.width = W; cp.height = H;
     cp.samples = c->numSamples > 1 ? c->numSamples : 1;
     cp.n = (int)std::sqrt((double)cp.samples);
-    cp.shardIndex = 0; cp.shardCount = 1; cp.workGroups = 1;
+    cp.shardIndex = 0; cp.shardCount = 1;
     if (prm && prm->shardCount > 1) {
         if (prm->shardIndex < 0 || prm->shardIndex >= prm->shardCount) return fail(RT_ERR_INVALID, "shardIndex outside [0, shardCount)");
         cp.shardIndex = prm->shardIndex; cp.shardCount = prm->shardCount;
-    }
-    if (prm && prm->workCounter) {
-        if (prm->shardCount > 1) return fail(RT_ERR_INVALID, "workCounter shares the whole frame: shardCount must be 0 or 1");
-        cp.workGroups = prm->workGroups > 1 ? prm->workGroups : 1;
     }
     return RT_OK;
 }
@@ -112,13 +108,12 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     RenderTargets rt{};
     rt.rgba = (uint8_t*)dRgbaOut; rt.linear = (double*)dLinearOut; rt.ids = (HitId*)dIdsOut;
     rt.pathStack = sc->dPathStack; rt.counters = sc->dCounters;
-    const bool sharedCounter = params && params->workCounter;
-    rt.tileCounter = sharedCounter ? (int*)params->workCounter : sc->dTileCounter;
+    rt.tileCounter = sc->dTileCounter;
     // Tile schedule: the frame records its cost per tile, the next frame of the same geometry draws the longest
-    // tiles first.  Not with a counter shared between GPUs (each rank sees only part of the costs).
+    // tiles first.
     const int tilesX = (cp.width + 7) / 8, nChunks = (cp.height + 7) / 8;
     const int nTiles = (nChunks - cp.shardIndex + cp.shardCount - 1) / cp.shardCount * tilesX * 2;
-    const bool adaptive = !(params && params->scheduleMode == RT_SCHEDULE_SPATIAL) && !sharedCounter && nTiles > 0;
+    const bool adaptive = !(params && params->scheduleMode == RT_SCHEDULE_SPATIAL) && nTiles > 0;
     if (params && (params->scheduleMode < 0 || params->scheduleMode > RT_SCHEDULE_SPATIAL)) return fail(RT_ERR_INVALID, "scheduleMode outside 0..1");
     sc->pendingScheduled = 0;
     if (adaptive) {
@@ -144,7 +139,7 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     }
 #endif
     CK(cudaEventRecord(sc->evStart, st));
-    if (!sharedCounter) CK(cudaMemsetAsync(sc->dTileCounter, 0, 64, st));
+    CK(cudaMemsetAsync(sc->dTileCounter, 0, 64, st));
     CK(cudaMemsetAsync(sc->dCounters, 0, 16 * sizeof(unsigned long long), st));
     CK(launchRender(variant, sc->ds, cp, rt, blocks, counters, st));
     if (adaptive) {

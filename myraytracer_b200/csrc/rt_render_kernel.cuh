@@ -184,7 +184,6 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_FAST_BLOCKS) renderKernelFast(Dev
     }
     const int unitsPerTile = segmented ? ns : 1;
     const int totalUnits = tiles.totalTiles * unitsPerTile;
-    const bool remoteCounter = cam.workGroups > 1;          // counter shared with peer GPUs (rt_render_params.workCounter)
     __shared__ uint2 unitNote[RT_BLOCK / 32];               // (clock at unit start, tile): read back when the unit ends
 #ifdef RT_WARPTIMES
     unsigned long long wt0 = globalTimerNs(), wt1 = 0, wt2 = 0;
@@ -212,7 +211,7 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_FAST_BLOCKS) renderKernelFast(Dev
         // One unit per draw: consecutive units go to warps running at the same time, which share tiles, BVH
         // nodes and triangles in L2 (drawing 8 at a time measured 10 % slower).
         int unit = 0;
-        if (lane == 0) unit = remoteCounter ? atomicAdd_system(out.tileCounter, 1) : atomicAdd(out.tileCounter, 1);
+        if (lane == 0) unit = atomicAdd(out.tileCounter, 1);
         unit = __shfl_sync(0xffffffffu, unit, 0);
         if (unit >= totalUnits) break;
         // Slot -> tile through the schedule of this frame: tiles in descending order of the cost measured on the
@@ -369,10 +368,9 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_GEN_BLOCKS) renderKernelGeneral(D
     const TileMap tiles(cam);
     const int n = cam.n, samples = cam.samples;
 
-    const bool remoteCounter = cam.workGroups > 1;
     for (;;) {
         int slot = 0;
-        if (lane == 0) slot = remoteCounter ? atomicAdd_system(out.tileCounter, 1) : atomicAdd(out.tileCounter, 1);
+        if (lane == 0) slot = atomicAdd(out.tileCounter, 1);
         slot = __shfl_sync(0xffffffffu, slot, 0);
         if (slot >= tiles.totalTiles) break;
         const int tile = out.tileOrder ? __ldg(out.tileOrder + slot) : slot;    // longest tiles of the previous frame first

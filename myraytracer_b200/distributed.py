@@ -75,15 +75,15 @@ class ShardedRenderer:
     frame, and one 4-byte all-reduce on the launch stream tells rank 0 that every rank's kernel has completed.
     gather="nccl": each rank renders into a private frame, packs its chunks and rank 0 gathers them (NCCL or gloo).
 
-    balance="static": rank r renders the 8-row chunks c with c % world == r (rt_render_params.shardIndex/Count).
-    balance="dynamic" (needs gather="p2p"): one work counter in rank 0's memory, mapped by every rank; the warps of
-    all GPUs draw 32-ray units of the whole frame from it with system-scope atomics over NVLink, so the GPUs finish
-    together whatever the image content.  Two counter slots alternate between frames; rank 0 zeroes the slot of the
-    next frame on its stream after the completion fence of the previous one.
+    Rank r renders the 8-row chunks c with c % world == r (rt_render_params.shardIndex/Count); within its share each
+    GPU draws the tiles in the order learnt from the previous frame (rt_render_params.scheduleMode), which removes
+    the tail of slow packets that would otherwise not shrink with the number of GPUs.  (A work counter shared by
+    all GPUs over NVLink was tried instead of the static deal: the remote atomic's latency cost more than the
+    imbalance it removed.)
     """
 
     def __init__(self, scene_url: str, device: int = 0, rank: Optional[int] = None, world: Optional[int] = None,
-                 camera_index: int = 0, variant: int = 0, gather: str = "p2p", balance: str = "static", schedule: int = 0):
+                 camera_index: int = 0, variant: int = 0, gather: str = "p2p", schedule: int = 0):
         import ctypes as C
         from . import capi
         from .engine import RayTracerEngine
@@ -95,9 +95,6 @@ class ShardedRenderer:
         self.variant = variant  # rt_render_params.kernelVariant (0 = automatic)
         self.schedule = schedule  # rt_render_params.scheduleMode (0 = longest tiles of the previous frame first)
         self.gather = gather if world > 1 else "none"
-        self.balance = balance if (world > 1 and self.gather == "p2p") else "static"
-        self.frame = 0
-        self._ctr_ptr, self._ctr_opened, self.ctr = None, 0, None
         self.engine = RayTracerEngine(scene_url, device=device)
         if not self.engine.ready:
             raise RuntimeError("engine not ready: " + self.engine.load_error)
@@ -115,10 +112,6 @@ class ShardedRenderer:
             self.fb_ptr = ptr.value
             self.fb = None
             self.flag = torch.zeros(1, dtype=torch.int32, device=dev)
-            if self.balance == "dynamic":
-                self._ctr_ptr, self._ctr_opened = self._share(256, dev, C, capi)
-                if rank == 0:
-                    self.ctr = _wrap_device_memory(self._ctr_ptr, (256,), device)
             if rank == 0:   # rank 0 reads the frame through torch: wrap the raw allocation without copying
                 self.fb = _wrap_device_memory(ptr.value, (hp, self.width, 4), device)
         else:
@@ -156,26 +149,16 @@ class ShardedRenderer:
             torch.cuda.synchronize(self.device)
             if dist.is_initialized() and self.world > 1:
                 dist.barrier()          # nobody unmaps / frees while a peer may still write
-            self.fb = self.ctr = None
+            self.fb = None
             self._lib.rt_shared_buffer_close(self.device, self._shared_ptr, self._opened)
-            if self._ctr_ptr:
-                self._lib.rt_shared_buffer_close(self.device, self._ctr_ptr, self._ctr_opened)
-            self._shared_ptr = self._ctr_ptr = None
+            self._shared_ptr = None
         self.engine.close()
 
     def enqueue(self, counters: bool = False) -> None:
         """Kernel for this rank's chunks + frame exchange towards rank 0, on torch's current stream; no host sync."""
         st = torch.cuda.current_stream(self.device).cuda_stream
-        if self.balance == "dynamic":
-            slot = self.frame & 1
-            if self.rank == 0:      # zero the slot of the NEXT frame: nobody uses it before the fence below has passed
-                self.ctr[(1 - slot) * 128:(1 - slot) * 128 + 4].zero_()
-            self.engine.render_device(self.camera_index, d_rgba=self.fb_ptr, stream=st, counters=counters,
-                                      variant=self.variant, work_counter=self._ctr_ptr + slot * 128, work_groups=self.world)
-            self.frame += 1
-        else:
-            self.engine.render_device(self.camera_index, d_rgba=self.fb_ptr, stream=st, shard_index=self.rank,
-                                      shard_count=self.world, counters=counters, variant=self.variant, schedule=self.schedule)
+        self.engine.render_device(self.camera_index, d_rgba=self.fb_ptr, stream=st, shard_index=self.rank,
+                                  shard_count=self.world, counters=counters, variant=self.variant, schedule=self.schedule)
         if self.gather == "p2p":
             dist.all_reduce(self.flag)          # completion fence: returns on-stream once every rank's kernel is done
         elif self.gather == "nccl":

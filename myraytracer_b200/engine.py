@@ -143,15 +143,13 @@ class RayTracerEngine:
 
     def render_device(self, camera_index: int = 0, d_rgba: int = 0, d_linear: int = 0, d_ids: int = 0, stream: int = 0,
                       shard_index: int = 0, shard_count: int = 1, counters: bool = False, variant: int = 0,
-                      work_counter: int = 0, work_groups: int = 1, schedule: int = 0) -> None:
+                      schedule: int = 0) -> None:
         """rt_render_device: enqueue one frame on `stream` with caller-owned DEVICE buffers (raw pointers,
         e.g. torch.Tensor.data_ptr()); does not synchronise.  Pair with finish()."""
         cam = self.camera(camera_index)
         prm = capi.rt_render_params()
         prm.shardIndex, prm.shardCount, prm.collectCounters = shard_index, shard_count, 1 if counters else 0
         prm.kernelVariant = variant
-        prm.workCounter = work_counter or None
-        prm.workGroups = work_groups
         prm.scheduleMode = schedule
         rc = self._lib.rt_render_device(self.scene_handle(), C.byref(cam), C.byref(prm), d_rgba or None, d_linear or None,
                                         d_ids or None, stream or None)
