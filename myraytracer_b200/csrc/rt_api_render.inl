@@ -101,7 +101,7 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     const int blocks = sc->blocks[variant][counters ? 1 : 0];
     cudaStream_t st = (cudaStream_t)cudaStream;
 
-    const size_t threads = (size_t)blocks * renderBlockSize();
+    const size_t threads = (size_t)blocks * renderBlockSize(variant);
     const size_t need = (size_t)(sc->ds.maxDepth + 1) * kPathFields * threads * sizeof(double);
     if ((rc = ensure(&sc->dPathStack, &sc->pathStackBytes, need))) return rc;
 

@@ -11,21 +11,25 @@ namespace rtg {
 #if RT_V_FAST
 #define RT_KERNEL renderKernelFast
 #define RT_NAME(x) x##Fast
+#define RT_THREADS RT_FAST_BLOCK
 #else
 #define RT_KERNEL renderKernelGeneral
 #define RT_NAME(x) x##General
+#define RT_THREADS RT_BLOCK
 #endif
 
 cudaError_t RT_NAME(launchVariant)(const DeviceScene& S, const CameraParams& cam, const RenderTargets& out, int blocks,
                                    bool counters, cudaStream_t stream) {
-    if (counters) RT_KERNEL<true><<<blocks, RT_BLOCK, 0, stream>>>(S, cam, out);
-    else RT_KERNEL<false><<<blocks, RT_BLOCK, 0, stream>>>(S, cam, out);
+    if (counters) RT_KERNEL<true><<<blocks, RT_THREADS, 0, stream>>>(S, cam, out);
+    else RT_KERNEL<false><<<blocks, RT_THREADS, 0, stream>>>(S, cam, out);
     return cudaGetLastError();
 }
 
 cudaError_t RT_NAME(occupancyVariant)(int* blocksPerSm, bool counters) {
-    if (counters) return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocksPerSm, RT_KERNEL<true>, RT_BLOCK, 0);
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocksPerSm, RT_KERNEL<false>, RT_BLOCK, 0);
+    if (counters) return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocksPerSm, RT_KERNEL<true>, RT_THREADS, 0);
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocksPerSm, RT_KERNEL<false>, RT_THREADS, 0);
 }
+
+int RT_NAME(blockSizeVariant)() { return RT_THREADS; }
 
 }  // namespace rtg

@@ -11,6 +11,8 @@ cudaError_t launchVariantFast(const DeviceScene&, const CameraParams&, const Ren
 cudaError_t launchVariantGeneral(const DeviceScene&, const CameraParams&, const RenderTargets&, int, bool, cudaStream_t);
 cudaError_t occupancyVariantFast(int*, bool);
 cudaError_t occupancyVariantGeneral(int*, bool);
+int blockSizeVariantFast();
+int blockSizeVariantGeneral();
 
 cudaError_t launchRender(int variant, const DeviceScene& S, const CameraParams& cam, const RenderTargets& out, int blocks,
                          bool counters, cudaStream_t stream) {
@@ -115,7 +117,7 @@ cudaError_t launchSchedule(unsigned* tileCost, int* tileOrder, unsigned* work, i
     return cudaGetLastError();
 }
 
-int renderBlockSize() { return RT_BLOCK; }
+int renderBlockSize(int variant) { return variant == KV_FAST ? blockSizeVariantFast() : blockSizeVariantGeneral(); }
 int renderStackCapacity() { return RT_STACK; }
 
 }  // namespace rtg

@@ -47,7 +47,7 @@ cudaError_t launchRender(int variant, const DeviceScene& S, const CameraParams& 
 // tileCost (clocks per tile of the frame just rendered) -> tileOrder for the next frame, longest first; clears tileCost
 cudaError_t launchSchedule(unsigned* tileCost, int* tileOrder, unsigned* work, int nTiles, cudaStream_t stream);
 size_t scheduleWorkBytes(int nTiles);   // scratch of launchSchedule
-int renderBlockSize();
+int renderBlockSize(int variant);
 int renderStackCapacity();
 cudaError_t renderOccupancy(int variant, int* blocksPerSm, bool counters);
 

@@ -27,10 +27,16 @@
 
 namespace rtg {
 
-// Resident blocks per SM the kernels are compiled for (register cap = 65536 / (128 * blocks)).  Measured on
+// Resident blocks per SM the kernels are compiled for (register cap = 65536 / (threads * blocks)).  Measured on
 // B200 (C4, profiles/): the traversal is latency-bound, so more resident warps beat fewer spills.
+// The fast kernel runs ONE WARP PER BLOCK, 32 blocks per SM (64 registers): nothing is shared between the warps
+// of a block, and with a single warp the packet stack sits at a fixed shared-memory address — the compiler no
+// longer rebuilds it from threadIdx inside the node loop (3.5 % of the frame, measured).
+#ifndef RT_FAST_BLOCK
+#define RT_FAST_BLOCK 32
+#endif
 #ifndef RT_FAST_BLOCKS
-#define RT_FAST_BLOCKS 8
+#define RT_FAST_BLOCKS 32
 #endif
 #ifndef RT_SKIPTAB
 #define RT_SKIPTAB 1
@@ -152,12 +158,13 @@ __device__ __forceinline__ unsigned long long globalTimerNs() {
 __device__ __forceinline__ double shflD(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
 
 template <bool COUNT>
-__global__ void __launch_bounds__(RT_BLOCK, RT_FAST_BLOCKS) renderKernelFast(DeviceScene S, CameraParams cam, RenderTargets out) {
-    __shared__ int2 wstacks[(RT_BLOCK / 32) * RT_WARP_STACK_INT2];
+__global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFast(DeviceScene S, CameraParams cam, RenderTargets out) {
+    __shared__ int2 wstacks[(RT_FAST_BLOCK / 32) * RT_WARP_STACK_INT2];
     const int lane = threadIdx.x & 31;
     TraceScratch T;
     T.sstack = nullptr; T.sstackN = 0;   // secondary rays keep their private stack in local memory: shared memory stays L1
-    T.wstack = wstacks + (threadIdx.x >> 5) * RT_WARP_STACK_INT2;
+    const int warpInBlock = RT_FAST_BLOCK == 32 ? 0 : (int)(threadIdx.x >> 5);
+    T.wstack = wstacks + warpInBlock * RT_WARP_STACK_INT2;
     T.pathStack = out.pathStack;
     T.gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     T.stride = (size_t)gridDim.x * blockDim.x;
@@ -175,7 +182,7 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_FAST_BLOCKS) renderKernelFast(Dev
     const bool segmented = ns < 32 && (32 % ns) == 0;
     const V3 ambient = ld3(S.ambient), background = ld3(S.background);
     // sample s of a lane is the same in every pass when n*n divides 32: its skip-ahead factors are computed once
-    __shared__ ulonglong2 skipTab[RT_BLOCK];
+    __shared__ ulonglong2 skipTab[RT_FAST_BLOCK];
     {
         uint64_t ak = 1, gk = 0;
         if (segmented) PCG32::skipFactors((uint64_t)((lane % ns) * drawsPerSample), ak, gk);
@@ -184,7 +191,7 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_FAST_BLOCKS) renderKernelFast(Dev
     }
     const int unitsPerTile = segmented ? ns : 1;
     const int totalUnits = tiles.totalTiles * unitsPerTile;
-    __shared__ uint2 unitNote[RT_BLOCK / 32];               // (clock at unit start, tile): read back when the unit ends
+    __shared__ uint2 unitNote[RT_FAST_BLOCK / 32];               // (clock at unit start, tile): read back when the unit ends
 #ifdef RT_WARPTIMES
     unsigned long long wt0 = globalTimerNs(), wt1 = 0, wt2 = 0;
     int wtUnits = 0, wtUnit = 0;
@@ -218,7 +225,7 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_FAST_BLOCKS) renderKernelFast(Dev
         // previous frame (longest first), so the frame ends on its cheapest units instead of a few slow ones.
         const int slot = unit / unitsPerTile;
         const int tile = out.tileOrder ? __ldg(out.tileOrder + slot) : slot;
-        if (lane == 0) unitNote[threadIdx.x >> 5] = make_uint2((unsigned)clock(), (unsigned)tile);
+        if (lane == 0) unitNote[warpInBlock] = make_uint2((unsigned)clock(), (unsigned)tile);
 #ifdef RT_WARPTIMES
         wtUnit = tile * unitsPerTile + (unit - slot * unitsPerTile);     // records are indexed by (tile, pass)
         if (lane == 0 && out.warpTimes) out.warpTimes[4 * (T.stride >> 5) + 4 * (size_t)wtUnit] = wt2;
@@ -304,7 +311,26 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_FAST_BLOCKS) renderKernelFast(Dev
             }
             __syncwarp();
             // ---- pixelColor += trace(...) in sample order (:345), then / samples (:354)
-            if (segmented) {
+            if (segmented && ns >= 4) {
+                // The colours go through shared memory (the packet stack is idle here) and lanes s = 0, 1, 2 of
+                // each pixel add up one component each, in sample order: 16 loads + adds instead of every lane
+                // shuffling all three components of all samples.
+                const int base = lane & ~(ns - 1);
+                static_assert(RT_WARP_STACK_INT2 * sizeof(int2) >= 96 * sizeof(double), "sample colours of a warp fit the packet stack");
+                double* scratch = reinterpret_cast<double*>(T.wstack);
+                scratch[lane * 3] = c.x; scratch[lane * 3 + 1] = c.y; scratch[lane * 3 + 2] = c.z;
+                __syncwarp();
+                double comp = 0.0;
+                if (s < 3) {
+                    const double* col = scratch + base * 3 + s;
+#pragma unroll 4
+                    for (int k = 0; k < ns; k++) comp = comp + col[k * 3];
+                    comp = comp / samplesD;
+                }
+                const V3 px3 = mk(shflD(comp, base), shflD(comp, base + 1), shflD(comp, base + 2));
+                if (active && s == 0) writePixel(out, (size_t)j * W + i, px3);
+                __syncwarp();
+            } else if (segmented) {
                 const int base = lane & ~(ns - 1);
                 V3 sum = mk(0, 0, 0);
 #pragma unroll 1
@@ -335,7 +361,7 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_FAST_BLOCKS) renderKernelFast(Dev
             if (x0 + qx < W && y0 + qy < H) writePixel(out, (size_t)(y0 + qy) * W + (x0 + qx), acc / samplesD);
         }
         if (out.tileCost && lane == 0) {       // cost of the unit in clocks/64, summed per tile for the next frame's schedule
-            const uint2 note = unitNote[threadIdx.x >> 5];
+            const uint2 note = unitNote[warpInBlock];
             atomicAdd(out.tileCost + note.y, ((unsigned)clock() - note.x) >> 6);
         }
     }
