@@ -25,8 +25,12 @@
 
 namespace rtg {
 
-// Child reference: >= 0 inner node index (relative to the BLAS / TLAS node array);
-// < 0 leaf: ~ref = (first << 3) | (count - 1), count in 1..8; kEmptyRef = no child.
+// Child reference: >= 0 inner node index; < 0 leaf: ~ref = (first << 3) | (count - 1), count in 1..8;
+// kEmptyRef = no child.  The builder emits both relative to one BLAS (node 0 = its first node, triangle 0 = its
+// first leaf-ordered triangle); on the device they are ABSOLUTE in DeviceScene::nodes and ::tris / ::trisD
+// (rt_api.cu rebases them when the BLASes are concatenated), with bit 3 of a leaf's ~ref telling which
+// triangle array: ~ref = (first << 4) | (f64 << 3) | (count - 1), count in 1..kMaxLeaf.  The traversal then
+// needs nothing from the instance record inside its loop.
 static const int32_t kEmptyRef = 0x7fffffff;
 static const int kMaxLeaf = 4;
 

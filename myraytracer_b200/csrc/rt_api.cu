@@ -166,6 +166,17 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
         bi.triBase = (int32_t)(out.f64 ? trisD.size() : tris.size());
         bi.rootRef = out.rootRef;
         std::memcpy(bi.lo, out.rootLo, 24); std::memcpy(bi.hi, out.rootHi, 24); std::memcpy(bi.centre, out.centre, 24);
+        // device references are absolute (gpu_layout.h): rebase the builder's BLAS-relative ones
+        auto rebase = [&](int32_t ref) -> int32_t {
+            if (ref == kEmptyRef) return ref;
+            if (ref >= 0) return ref + bi.nodeBase;
+            const uint32_t r = ~(uint32_t)ref;
+            return ~(int32_t)((((r >> 3) + (uint32_t)bi.triBase) << 4) | (out.f64 ? 8u : 0u) | (r & 7u));
+        };
+        if ((int64_t)bi.triBase + bl.primCount >= (int64_t)1 << 27 || (int64_t)nodes.size() + (int64_t)out.nodes.size() >= kEmptyRef)
+            return fail(RT_ERR_UNSUPPORTED, "scene exceeds the 2^27 triangles / 2^31 nodes of the device references");
+        for (GNode& g : out.nodes) { g.child0 = rebase(g.child0); g.child1 = rebase(g.child1); }
+        bi.rootRef = rebase(out.rootRef);
         nodes.insert(nodes.end(), out.nodes.begin(), out.nodes.end());
         if (out.f64) trisD.insert(trisD.end(), out.trisD.begin(), out.trisD.end());
         else tris.insert(tris.end(), out.tris.begin(), out.tris.end());

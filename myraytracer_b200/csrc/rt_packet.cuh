@@ -62,9 +62,9 @@ __device__ __forceinline__ uint32_t packetBlas(const DeviceScene& S, const GInst
     const float iz = fminf(fmaxf(1.0f / (float)dL.z, -1e30f), 1e30f);
     const float nx = -(ox * ix), ny = -(oy * iy), nz = -(oz * iz);
     const float tminF = __double2float_rd(tLow - t0);
-    float tmaxF = __double2float_ru(hit.t - t0);
+    float tmaxF = alive ? __double2float_ru(hit.t - t0) : -CUDART_INF_F;
 
-    const GNode* nodes = S.nodes + I.nodeBase;
+    const GNode* nodes = S.nodes;        // child references are absolute (gpu_layout.h)
     uint32_t occluded = 0u;
     int sp = 0;
     int32_t cur = I.rootRef;
@@ -91,8 +91,7 @@ __device__ __forceinline__ uint32_t packetBlas(const DeviceScene& S, const GInst
             if ((uint32_t)ch.x < 0x7fffffffu) prefetchL1(nodes + ch.x);
             if ((uint32_t)ch.y < 0x7fffffffu) prefetchL1(nodes + ch.y);
 #endif
-            const bool inl = (curMask & bit) != 0;
-            if (COUNT && inl) C.box += 2;
+            if (COUNT && (curMask & bit) != 0) C.box += 2;
 #ifdef RT_WARPTIMES
             if (bit == 1u) { wstack[RT_WSTACK + RT_WTSTACK].x++; wstack[RT_WSTACK + RT_WTSTACK].y += __popc(curMask); }
 #endif
@@ -106,7 +105,9 @@ __device__ __forceinline__ uint32_t packetBlas(const DeviceScene& S, const GInst
             float c2 = __fmaf_rn(q2.x, iz, nz), d2 = __fmaf_rn(q2.w, iz, nz);
             float n1 = fmaxf(fmaxf(fminf(c0, d0), fminf(c1, d1)), fmaxf(fminf(c2, d2), tminF));
             float f1 = fminf(fminf(fmaxf(c0, d0), fmaxf(c1, d1)), fminf(fmaxf(c2, d2), tmaxF));
-            const bool h0 = inl && n0 <= f0, h1 = inl && n1 <= f1;
+            // No test of curMask here: a lane whose ray missed an ancestor's box misses the boxes inside it too, and
+            // lanes that are not part of the packet (any more) carry tmaxF = -inf, which fails every box.
+            const bool h0 = n0 <= f0, h1 = n1 <= f1;
             const uint32_t m0 = __ballot_sync(RT_FULL, h0), m1 = __ballot_sync(RT_FULL, h1);
             if (m0 && m1) {
                 const uint32_t v1 = __ballot_sync(RT_FULL, h1 && (!h0 || n1 < n0));   // lanes preferring child 1
@@ -126,7 +127,8 @@ __device__ __forceinline__ uint32_t packetBlas(const DeviceScene& S, const GInst
         }
         if (cur != kEmptyRef) {  // leaf: triangles fetched once for the warp, tested by the lanes in curMask
             const uint32_t ref = ~(uint32_t)cur;
-            const int first = I.triBase + (int)(ref >> 3), count = (int)(ref & 7u) + 1;
+            const int first = (int)(ref >> 4), count = (int)(ref & 7u) + 1;
+            const bool f64 = (ref & 8u) != 0;
             const bool inl = (curMask & bit) != 0;
             bool occ = false;
 #ifdef RT_WARPTIMES
@@ -134,7 +136,7 @@ __device__ __forceinline__ uint32_t packetBlas(const DeviceScene& S, const GInst
 #endif
             for (int k = 0; k < count; k++) {
                 V3 v0, v1, v2;
-                loadTri(S, I, first + k, v0, v1, v2);
+                loadTri(S, f64, first + k, v0, v1, v2);
                 if (inl && !occ) {
                     if (COUNT) C.tri++;
                     double t, u, v;
@@ -153,6 +155,7 @@ __device__ __forceinline__ uint32_t packetBlas(const DeviceScene& S, const GInst
                 occluded |= o;
                 live &= ~o;
                 if (!live) return occluded;
+                if (occ) tmaxF = -CUDART_INF_F;      // this lane is done: it fails every box from here on
             }
         }
         RT_PACKET_POP();

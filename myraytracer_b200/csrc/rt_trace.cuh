@@ -33,7 +33,7 @@ __device__ __forceinline__ bool analyticInstance(const DeviceScene& S, const GIn
     } else {
         if (COUNT) C.tri++;
         V3 v0, v1, v2;
-        loadTri(S, I, I.triBase, v0, v1, v2);
+        loadTri(S, I.triF64 != 0, I.triBase, v0, v1, v2);
         if (!mtTest(v0, v1, v2, oL, dL, eps, t, u, v)) return false;
     }
     if (!inWindow(t, tLow, hit.t, anyhit)) return false;
@@ -109,7 +109,7 @@ __device__ __forceinline__ void resolveHit(const DeviceScene& S, const HitRec& h
     const int kind = I.kind;
     if (kind == INST_MESH || kind == INST_TRI) {
         V3 v0, v1, v2;
-        loadTri(S, I, hit.slot, v0, v1, v2);
+        loadTri(S, I.triF64 != 0, hit.slot, v0, v1, v2);
         int64_t triIndex = I.triF64 ? S.trisD[hit.slot].triIndex : (int64_t)S.tris[hit.slot].triIndex;
         V3 e1 = v1 - v0, e2 = v2 - v0;
         const double u = hit.u, v = hit.v;

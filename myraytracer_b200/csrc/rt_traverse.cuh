@@ -126,8 +126,8 @@ __device__ __forceinline__ bool planeT(const double* pl, V3 o, V3 d, double eps,
     return true;
 }
 
-__device__ __forceinline__ void loadTri(const DeviceScene& S, const GInstance& I, int slot, V3& v0, V3& v1, V3& v2) {
-    if (I.triF64) {
+__device__ __forceinline__ void loadTri(const DeviceScene& S, bool f64, int slot, V3& v0, V3& v1, V3& v2) {
+    if (f64) {
         const GTriD* p = S.trisD + slot;
         v0 = ld3(p->v0); v1 = ld3(p->v1); v2 = ld3(p->v2);
     } else {
@@ -169,7 +169,7 @@ __device__ __forceinline__ bool traverseBlas(const DeviceScene& S, const GInstan
     float tminF = __double2float_rd(tLow - t0);
     float tmaxF = __double2float_ru(hit.t - t0);
 
-    const GNode* nodes = S.nodes + I.nodeBase;
+    const GNode* nodes = S.nodes;        // child references are absolute (gpu_layout.h)
     // stack: the first sstackN (<= RT_SSTACK) entries in shared memory (per-lane column), deeper ones in local memory
     int32_t lstack[RT_STACK];
     int sp = 0;
@@ -214,10 +214,11 @@ __device__ __forceinline__ bool traverseBlas(const DeviceScene& S, const GInstan
         }
         if (cur != kEmptyRef) {  // leaf
             const uint32_t ref = ~(uint32_t)cur;
-            const int first = I.triBase + (int)(ref >> 3), count = (int)(ref & 7u) + 1;
+            const int first = (int)(ref >> 4), count = (int)(ref & 7u) + 1;
+            const bool f64 = (ref & 8u) != 0;
             for (int k = 0; k < count; k++) {
                 V3 v0, v1, v2;
-                loadTri(S, I, first + k, v0, v1, v2);
+                loadTri(S, f64, first + k, v0, v1, v2);
                 if (COUNT) C.tri++;
                 double t, u, v;
                 if (!mtTest(v0, v1, v2, oL, dL, eps, t, u, v)) continue;
