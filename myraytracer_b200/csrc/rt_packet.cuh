@@ -21,7 +21,16 @@ namespace rtg {
 
 #define RT_FULL 0xffffffffu
 
-__device__ __forceinline__ void prefetchL1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+// Packet stack entries through 32-bit shared-window addresses: the stack pointer IS the address, so the loop
+// never rebuilds the shared base (three uniform-datapath instructions per push and per pop otherwise).
+__device__ __forceinline__ void stsPair(uint32_t addr, int a, int b) {
+    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr), "r"(a), "r"(b) : "memory");
+}
+__device__ __forceinline__ int2 ldsPair(uint32_t addr) {
+    int2 v;
+    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr) : "memory");
+    return v;
+}
 #ifndef RT_WSTACK
 #define RT_WSTACK 64    // BLAS entries per warp (tree depth is checked against RT_STACK at build time)
 #endif
@@ -66,19 +75,23 @@ __device__ __forceinline__ uint32_t packetBlas(const DeviceScene& S, const GInst
 
     const GNode* nodes = S.nodes;        // child references are absolute (gpu_layout.h)
     uint32_t occluded = 0u;
-    int sp = 0;
+    // sp: shared-window address of the next free entry.  Entry 0 is a sentinel (kEmptyRef, all lanes): popping it
+    // ends the walk, so the loop needs neither the stack base nor a depth counter.
+    const uint32_t spBase = (uint32_t)__cvta_generic_to_shared(wstack);
+    uint32_t sp = spBase + 8u;
+    stsPair(spBase, kEmptyRef, (int)RT_FULL);
     int32_t cur = I.rootRef;
     uint32_t curMask = live;
 
 #define RT_PACKET_POP()                                  \
     for (;;) {                                           \
-        if (sp == 0) return occluded;                    \
-        --sp;                                            \
-        const int2 e_ = wstack[sp];                      \
+        sp -= 8u;                                        \
+        const int2 e_ = ldsPair(sp);                     \
         cur = e_.x;                                      \
         curMask = (uint32_t)e_.y & live;                 \
         if (curMask) break;                              \
-    }
+    }                                                    \
+    if (cur == kEmptyRef) return occluded;
 
     for (;;) {
         while ((uint32_t)cur < 0x7fffffffu) {  // inner node, fetched once for the warp
@@ -112,9 +125,9 @@ __device__ __forceinline__ uint32_t packetBlas(const DeviceScene& S, const GInst
             if (m0 && m1) {
                 const uint32_t v1 = __ballot_sync(RT_FULL, h1 && (!h0 || n1 < n0));   // lanes preferring child 1
                 const bool swap = 2 * __popc(v1) > __popc(m0 | m1);
-                wstack[sp] = swap ? make_int2(ch.x, (int)m0) : make_int2(ch.y, (int)m1);
-                sp++;
-                if (COUNT && sp > C.maxStack) C.maxStack = sp;
+                stsPair(sp, swap ? ch.x : ch.y, (int)(swap ? m0 : m1));
+                sp += 8u;
+                if (COUNT && (int)((sp - spBase) >> 3) - 1 > C.maxStack) C.maxStack = (int)((sp - spBase) >> 3) - 1;
                 cur = swap ? ch.y : ch.x;
                 curMask = swap ? m1 : m0;
             } else if (m0) {
