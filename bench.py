@@ -200,7 +200,7 @@ def run_ours(args):
     import torch
     import torch.distributed as dist
     from myraytracer_b200 import capi
-    from myraytracer_b200.distributed import ShardedRenderer, owned_chunks
+    from myraytracer_b200.distributed import ShardedRenderer
 
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -229,7 +229,7 @@ def run_ours(args):
 
     t0 = time.time()
     path = make_scene(args.config, rank)
-    R = ShardedRenderer(path, device=local, rank=rank, world=world, variant=args.variant, gather=args.gather,
+    R = ShardedRenderer(path, device=local, rank=rank, world=world, variant=args.variant, gather=args.gather, shard=args.shard,
                         schedule=1 if args.schedule == "spatial" else 0)
     info = R.engine.scene_info()
     W, H = R.width, R.height
@@ -238,7 +238,8 @@ def run_ours(args):
     # ---- counters pass (untimed, slower kernel variant): algorithmic bytes of this rank's launch
     R.enqueue(counters=True)
     cst = R.finish()
-    my_pixels = sum(min(8, H - c * 8) for c in owned_chunks(H, rank, world)) * W
+    n_side = max(1, int(max(1, int(R.engine.camera(0).numSamples)) ** 0.5))
+    my_pixels = int(cst["raysPrimary"]) // (n_side * n_side)                 # pixels of this rank's shard
     my_bytes = algorithmic_bytes(cst, my_pixels)
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
@@ -258,8 +259,7 @@ def run_ours(args):
         step()
     sampler = ClockSampler(local)
     barrier()
-    if rank == 0:
-        sampler.start()
+    sampler.start()          # every rank samples its own GPU (the ranks' kernel times differ by GPU); rank 0's is reported
     wall0 = time.perf_counter()
     ms_sum, kern_ms_sum, st = 0.0, 0.0, None
     for _ in range(args.steps):
@@ -267,8 +267,9 @@ def run_ours(args):
         ms_sum += ms; kern_ms_sum += st["deviceMs"]
     barrier()
     wall = time.perf_counter() - wall0
-    clocks = sampler.stop() if rank == 0 else None
-    log(f"[rank {rank}] step {ms_sum / args.steps:.3f} ms, kernel {kern_ms_sum / args.steps:.3f} ms, rays {st['rays']}")
+    clocks = sampler.stop()
+    log(f"[rank {rank}] step {ms_sum / args.steps:.3f} ms, kernel {kern_ms_sum / args.steps:.3f} ms, rays {st['rays']}, "
+        f"clocks {clocks}")
     ms_step = allreduce(ms_sum / args.steps, dist.ReduceOp.MAX if world > 1 else None)
     rays = allreduce(float(st["rays"]), dist.ReduceOp.SUM if world > 1 else None)
     rp = allreduce(float(st["raysPrimary"]), dist.ReduceOp.SUM if world > 1 else None)
@@ -339,7 +340,7 @@ def run_ours(args):
             "data": "synthetic",
             "config": {"workload": BENCH_CONFIGS[args.config][2], "width": W, "height": H, "triangles": info["triangles"],
                        "rays_per_frame": int(rays), "rays_primary": int(rp), "rays_shadow": int(rs),
-                       "rays_secondary": int(rays - rp - rs), "parallelism": f"tiles{world}", "gather": R.gather, "kernel_variant": args.variant,
+                       "rays_secondary": int(rays - rp - rs), "parallelism": f"tiles{world}", "gather": R.gather, "shard": R.shard, "kernel_variant": args.variant,
                        "schedule": ("tiles drawn longest-first from the per-tile cost recorded on the previous frame "
                                     f"({scheduled} tiles on rank 0); warm-up frames train it" if scheduled else "spatial order"),
                        "ms_per_step_spatial_order": spatial_ms,
@@ -370,6 +371,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--config", choices=sorted(BENCH_CONFIGS), default="c4")
+    ap.add_argument("--shard", choices=["tiles", "rows"], default=None,
+                    help="N>1: 8-row chunks round-robin (default) or 8x4 tiles dealt along diagonals (p2p only)")
     ap.add_argument("--schedule", choices=["adaptive", "spatial"], default="adaptive",
                     help="rt_render_params.scheduleMode: tile order learnt from the previous frame, or top to bottom")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")

@@ -128,12 +128,14 @@ typedef struct rt_camera {
  * return non-zero to cancel (RayTracer.swift:178-180) */
 typedef int (*rt_progress_fn)(int32_t rowsDone, int32_t rowsTotal, void* user);
 
+#define RT_SHARD_ROWS  0
+#define RT_SHARD_TILES 1
 #define RT_SCHEDULE_ADAPTIVE 0
 #define RT_SCHEDULE_SPATIAL  1
 
 typedef struct rt_render_params {
-    /* 8-row chunks c with c % shardCount == shardIndex are rendered; other rows are left untouched.
-     * shardCount <= 1 renders the whole frame.  (Multi-process sharding: one rank per GPU.) */
+    /* One shard of the frame is rendered, the other pixels are left untouched; shardCount <= 1 renders the whole
+     * frame.  (Multi-process sharding: one rank per GPU.)  Which pixels: see shardMode below. */
     int32_t shardIndex, shardCount;
     int32_t collectCounters;      /* 1: also fill rt_stats box/primitive test counts (slower kernel variant) */
     int32_t kernelVariant;        /* 0 = automatic.  For measurements only: 1 = fast kernel (lane = (pixel, sample), warp
@@ -147,7 +149,11 @@ typedef struct rt_render_params {
      * (rt_stats.tilesScheduled tells whether a learnt order was used; the first frame uses the spatial order).
      * RT_SCHEDULE_SPATIAL (1): always top to bottom.  The image is the same either way. */
     int32_t scheduleMode;
-    int32_t reserved2;
+    /* RT_SHARD_ROWS (0): the 8-row chunks c (Object+Extension.swift:75) with c % shardCount == shardIndex.
+     * RT_SHARD_TILES (1): the 8x4-pixel tiles (tx, ty) with (tx + ty) % shardCount == shardIndex — every shard samples
+     * the whole image, so the shards finish together whatever the image shows (for frames written in place into one
+     * shared buffer, rt_shared_buffer_*). */
+    int32_t shardMode;
 } rt_render_params;
 
 /* identity of one primary ray's closest hit (the reference's Hit has no primitive id) */

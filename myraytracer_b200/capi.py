@@ -90,7 +90,7 @@ rt_progress_fn = C.CFUNCTYPE(C.c_int, C.c_int32, C.c_int32, C.c_void_p)
 class rt_render_params(C.Structure):
     _fields_ = [("shardIndex", C.c_int32), ("shardCount", C.c_int32), ("collectCounters", C.c_int32),
                 ("kernelVariant", C.c_int32), ("progress", rt_progress_fn), ("progressUser", C.c_void_p),
-                ("scheduleMode", C.c_int32), ("reserved2", C.c_int32)]
+                ("scheduleMode", C.c_int32), ("shardMode", C.c_int32)]
 
 
 class rt_stats(C.Structure):

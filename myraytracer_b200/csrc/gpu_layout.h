@@ -117,7 +117,51 @@ struct CameraParams {
     int32_t width, height, samples, n;  // n = floor(sqrt(samples))
     int32_t dof;
     int32_t shardIndex, shardCount;
-    int32_t pad;
+    int32_t shardTiles;           // 0: 8-row chunks dealt round-robin, 1: 8x4 tiles dealt along diagonals (rt_render_params.shardMode)
+};
+
+#if defined(__CUDACC__)
+#define RT_HD __host__ __device__
+#else
+#define RT_HD
+#endif
+
+// The tiles (8x4 pixels) one shard renders, numbered 0..count-1 in the order they are drawn without a schedule.
+//   rows mode   chunk c (8 rows = two tile rows) belongs to shard c % shardCount — the reference's decomposition
+//               (Object+Extension.swift:75-82) dealt round-robin
+//   tiles mode  tile (tx, ty) belongs to shard (tx + ty) % shardCount: every shard samples the whole image at tile
+//               granularity, so the shards' costs differ by a fraction of a percent whatever the image shows; the
+//               tile grid is padded to a multiple of shardCount columns (tiles outside the image trace nothing)
+struct ShardTiles {
+    int tilesX, perRow, count, shardIndex, shardCount, byTile;
+    RT_HD ShardTiles(int width, int height, int index, int n, int tilesMode) {
+        tilesX = (width + 7) >> 3;
+        const int nChunks = (height + 7) >> 3;
+        shardCount = n < 1 ? 1 : n;
+        shardIndex = index;
+        byTile = tilesMode && shardCount > 1;
+        if (byTile) {
+            perRow = (tilesX + shardCount - 1) / shardCount;
+            count = perRow * nChunks * 2;
+        } else {
+            perRow = tilesX;
+            count = (nChunks - shardIndex + shardCount - 1) / shardCount * tilesX * 2;
+        }
+    }
+    // tile -> pixel origin (x0, y0) of its 8x4 block
+    RT_HD void origin(int tile, int& x0, int& y0) const {
+        if (byTile) {
+            const int ty = tile / perRow, j = tile - ty * perRow;
+            const int first = (shardIndex + shardCount - ty % shardCount) % shardCount;
+            x0 = (first + j * shardCount) * 8;
+            y0 = ty * 4;
+        } else {
+            const int k = tile / (tilesX * 2), rem = tile - k * (tilesX * 2);
+            const int ty = rem / tilesX, tx = rem - ty * tilesX;
+            x0 = tx * 8;
+            y0 = (k * shardCount + shardIndex) * 8 + ty * 4;
+        }
+    }
 };
 
 }  // namespace rtg

@@ -53,10 +53,11 @@ int buildCamera(const rt_camera* c, const rt_render_params* prm, CameraParams& c
     cp.width = W; cp.height = H;
     cp.samples = c->numSamples > 1 ? c->numSamples : 1;
     cp.n = (int)std::sqrt((double)cp.samples);
-    cp.shardIndex = 0; cp.shardCount = 1;
+    cp.shardIndex = 0; cp.shardCount = 1; cp.shardTiles = 0;
     if (prm && prm->shardCount > 1) {
         if (prm->shardIndex < 0 || prm->shardIndex >= prm->shardCount) return fail(RT_ERR_INVALID, "shardIndex outside [0, shardCount)");
-        cp.shardIndex = prm->shardIndex; cp.shardCount = prm->shardCount;
+        if (prm->shardMode < 0 || prm->shardMode > RT_SHARD_TILES) return fail(RT_ERR_INVALID, "shardMode outside 0..1");
+        cp.shardIndex = prm->shardIndex; cp.shardCount = prm->shardCount; cp.shardTiles = prm->shardMode == RT_SHARD_TILES ? 1 : 0;
     }
     return RT_OK;
 }
@@ -111,13 +112,12 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     rt.tileCounter = sc->dTileCounter;
     // Tile schedule: the frame records its cost per tile, the next frame of the same geometry draws the longest
     // tiles first.
-    const int tilesX = (cp.width + 7) / 8, nChunks = (cp.height + 7) / 8;
-    const int nTiles = (nChunks - cp.shardIndex + cp.shardCount - 1) / cp.shardCount * tilesX * 2;
+    const int nTiles = ShardTiles(cp.width, cp.height, cp.shardIndex, cp.shardCount, cp.shardTiles).count;
     const bool adaptive = !(params && params->scheduleMode == RT_SCHEDULE_SPATIAL) && nTiles > 0;
     if (params && (params->scheduleMode < 0 || params->scheduleMode > RT_SCHEDULE_SPATIAL)) return fail(RT_ERR_INVALID, "scheduleMode outside 0..1");
     sc->pendingScheduled = 0;
     if (adaptive) {
-        const int key[8] = {cp.width, cp.height, cp.n, cp.dof, cp.shardIndex, cp.shardCount, variant, nTiles};
+        const int key[8] = {cp.width, cp.height, cp.n, cp.dof, cp.shardIndex, cp.shardCount * 2 + cp.shardTiles, variant, nTiles};
         const bool grown = sc->tileCostBytes < (size_t)nTiles * 4 || sc->tileOrderBytes < (size_t)nTiles * 4;
         if ((rc = ensure(&sc->dTileCost, &sc->tileCostBytes, (size_t)nTiles * 4))) return rc;
         if ((rc = ensure(&sc->dTileOrder, &sc->tileOrderBytes, (size_t)nTiles * 4))) return rc;

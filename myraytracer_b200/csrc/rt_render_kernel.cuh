@@ -128,25 +128,6 @@ __device__ __forceinline__ void flushCounters(const RenderTargets& out, Counters
     }
 }
 
-struct TileMap {
-    int tilesX, totalTiles, shardCount, shardIndex;
-    __device__ __forceinline__ TileMap(const CameraParams& cam) {
-        tilesX = (cam.width + 7) >> 3;
-        const int nChunks = (cam.height + 7) >> 3;
-        shardCount = cam.shardCount < 1 ? 1 : cam.shardCount;
-        shardIndex = cam.shardIndex;
-        const int owned = (nChunks - shardIndex + shardCount - 1) / shardCount;
-        totalTiles = owned * tilesX * 2;
-    }
-    // tile -> pixel origin (x0, y0) of its 8x4 block
-    __device__ __forceinline__ void origin(int tile, int& x0, int& y0) const {
-        const int k = tile / (tilesX * 2), rem = tile - k * (tilesX * 2);
-        const int ty = rem / tilesX, tx = rem - ty * tilesX;
-        x0 = tx * 8;
-        y0 = (k * shardCount + shardIndex) * 8 + ty * 4;
-    }
-};
-
 #ifdef RT_WARPTIMES
 __device__ __forceinline__ unsigned long long globalTimerNs() {
     unsigned long long t;
@@ -175,7 +156,7 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFas
     R.primary = R.shadow = R.secondary = 0;
 
     const int W = cam.width, H = cam.height;
-    const TileMap tiles(cam);
+    const ShardTiles tiles(cam.width, cam.height, cam.shardIndex, cam.shardCount, cam.shardTiles);
     const int n = cam.n, ns = n * n;                 // samples traced per pixel (:298-306)
     const int drawsPerSample = cam.dof ? 5 : 3;      // xi1, xi2, [lens u, v], time
     const double samplesD = (double)cam.samples;     // the sum is divided by `samples` (:354)
@@ -190,7 +171,7 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFas
         __syncwarp();
     }
     const int unitsPerTile = segmented ? ns : 1;
-    const int totalUnits = tiles.totalTiles * unitsPerTile;
+    const int totalUnits = tiles.count * unitsPerTile;
     __shared__ uint2 unitNote[RT_FAST_BLOCK / 32];               // (clock at unit start, tile): read back when the unit ends
 #ifdef RT_WARPTIMES
     unsigned long long wt0 = globalTimerNs(), wt1 = 0, wt2 = 0;
@@ -391,14 +372,14 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_GEN_BLOCKS) renderKernelGeneral(D
     R.primary = R.shadow = R.secondary = 0;
 
     const int W = cam.width, H = cam.height;
-    const TileMap tiles(cam);
+    const ShardTiles tiles(cam.width, cam.height, cam.shardIndex, cam.shardCount, cam.shardTiles);
     const int n = cam.n, samples = cam.samples;
 
     for (;;) {
         int slot = 0;
         if (lane == 0) slot = atomicAdd(out.tileCounter, 1);
         slot = __shfl_sync(0xffffffffu, slot, 0);
-        if (slot >= tiles.totalTiles) break;
+        if (slot >= tiles.count) break;
         const int tile = out.tileOrder ? __ldg(out.tileOrder + slot) : slot;    // longest tiles of the previous frame first
         const unsigned c0 = (unsigned)clock();
         int x0, y0;

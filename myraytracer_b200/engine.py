@@ -112,7 +112,8 @@ class RayTracerEngine:
     # -- render -----------------------------------------------------------
     def render(self, camera_index: int = 0, want_linear: bool = False, want_ids: bool = False,
                shard_index: int = 0, shard_count: int = 1, counters: bool = False,
-               progress: Optional[Callable[[int, int], bool]] = None, variant: int = 0, schedule: int = 0) -> RenderResult:
+               progress: Optional[Callable[[int, int], bool]] = None, variant: int = 0, schedule: int = 0,
+               shard_mode: int = 0) -> RenderResult:
         if not self._h or self._lib.rth_engine_camera_count(self._h) == 0 and not self.ready:
             pass  # let the C side produce the reference's error codes
         cam = None
@@ -130,6 +131,7 @@ class RayTracerEngine:
         prm.shardIndex, prm.shardCount, prm.collectCounters = shard_index, shard_count, 1 if counters else 0
         prm.kernelVariant = variant
         prm.scheduleMode = schedule     # 0: longest tiles of the previous frame first, 1: spatial order
+        prm.shardMode = shard_mode      # 0: 8-row chunks, 1: 8x4 tiles along diagonals
         cb = None
         if progress is not None:
             cb = capi.rt_progress_fn(lambda done, total, _u: 0 if progress(done, total) else 1)
@@ -143,7 +145,7 @@ class RayTracerEngine:
 
     def render_device(self, camera_index: int = 0, d_rgba: int = 0, d_linear: int = 0, d_ids: int = 0, stream: int = 0,
                       shard_index: int = 0, shard_count: int = 1, counters: bool = False, variant: int = 0,
-                      schedule: int = 0) -> None:
+                      schedule: int = 0, shard_mode: int = 0) -> None:
         """rt_render_device: enqueue one frame on `stream` with caller-owned DEVICE buffers (raw pointers,
         e.g. torch.Tensor.data_ptr()); does not synchronise.  Pair with finish()."""
         cam = self.camera(camera_index)
@@ -151,6 +153,7 @@ class RayTracerEngine:
         prm.shardIndex, prm.shardCount, prm.collectCounters = shard_index, shard_count, 1 if counters else 0
         prm.kernelVariant = variant
         prm.scheduleMode = schedule
+        prm.shardMode = shard_mode
         rc = self._lib.rt_render_device(self.scene_handle(), C.byref(cam), C.byref(prm), d_rgba or None, d_linear or None,
                                         d_ids or None, stream or None)
         if rc != 0:

@@ -22,12 +22,12 @@ def main():
     d = tempfile.mkdtemp(prefix=f"mgpu_r{rank}_")
     path = scenegen.config_c3(d, width=200, height=150, samples=4, depth=3, ico_level=2)
     full = RayTracerEngine(path, device=local).render(0).rgba if rank == 0 else None
-    for mode in ("p2p", "nccl"):
-        R = ShardedRenderer(path, device=local, rank=rank, world=world, gather=mode)
+    for mode, shard in (("p2p", "tiles"), ("p2p", "rows"), ("nccl", "rows")):
+        R = ShardedRenderer(path, device=local, rank=rank, world=world, gather=mode, shard=shard)
         for _ in range(3):
             frame, stats = R.render()
         if rank == 0:
-            assert np.array_equal(frame, full), f"{mode}: sharded frame differs from the single-GPU frame"
+            assert np.array_equal(frame, full), f"{mode}/{shard}: sharded frame differs from the single-GPU frame"
         tot = torch.tensor([stats["raysPrimary"]], dtype=torch.int64, device="cuda")
         dist.all_reduce(tot)
         assert tot.item() == 200 * 150 * 4

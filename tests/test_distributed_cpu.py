@@ -100,3 +100,38 @@ def test_bench_reference_arm_prints_the_contract_line():
     out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--config", "c1", "--steps", "1",
                           "--warmup", "1"], capture_output=True, text=True, timeout=600, env=env)
     assert out.returncode == 0 and out.stdout.strip() == ""
+
+
+@pytest.mark.parametrize("shard", ["rows", "tiles"])
+@pytest.mark.parametrize("H,W,world", [(50, 70, 2), (41, 33, 3), (1080, 1920, 8), (7, 5, 4)])
+def test_owned_mask_partitions_the_frame(shard, H, W, world):
+    total = sum(D.owned_mask(H, W, r, world, shard).astype(int) for r in range(world))
+    assert (total == 1).all()                                   # every pixel rendered by exactly one rank
+    if shard == "tiles" and H * W > 10000:                      # tile deal: shares equal to within a tile row
+        share = [int(D.owned_mask(H, W, r, world, shard).sum()) for r in range(world)]
+        assert max(share) - min(share) <= 32 * ((H + 3) // 4)
+
+
+def test_device_tile_enumeration_matches_owned_mask(tmp_path):
+    """ShardTiles (gpu_layout.h, shared by the host code and the kernels) enumerates exactly the tiles of owned_mask,
+    each once, for both shard modes; tiles it adds beyond the image (padding of the tile grid) hold no pixel."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = tmp_path / "probe.cpp"
+    src.write_text('#include <cstdio>\n#include <cstdlib>\n#include "myraytracer_b200/csrc/gpu_layout.h"\n'
+                   'int main(int c, char** v) { int W = atoi(v[1]), H = atoi(v[2]), r = atoi(v[3]), n = atoi(v[4]), m = atoi(v[5]);\n'
+                   '  rtg::ShardTiles t(W, H, r, n, m);\n'
+                   '  for (int k = 0; k < t.count; k++) { int x, y; t.origin(k, x, y); printf("%d %d\\n", x, y); } return 0; }\n')
+    exe = tmp_path / "probe"
+    subprocess.run(["g++", "-std=c++17", "-I", root, "-I", "/usr/local/cuda/include", str(src), "-o", str(exe)], check=True)
+    for (W, H, n) in [(70, 50, 2), (33, 41, 3), (200, 120, 8), (1920, 1080, 8)]:
+        for mode, shard in ((0, "rows"), (1, "tiles")):
+            for r in range(n):
+                out = subprocess.run([str(exe), str(W), str(H), str(r), str(n), str(mode)], capture_output=True, text=True, check=True).stdout
+                tiles = [tuple(map(int, ln.split())) for ln in out.splitlines()]
+                assert len(set(tiles)) == len(tiles)
+                inside = {(x, y) for x, y in tiles if x < W and y < H}
+                m = D.owned_mask(H, W, r, n, shard)
+                want = {(x, y) for y in range(0, H, 4) for x in range(0, W, 8) if m[y, x]}
+                assert inside == want
+                assert all(x % 8 == 0 and y % 4 == 0 for x, y in tiles)

@@ -77,21 +77,22 @@ def test_gpu_matches_committed_golden(name, scene_dir):
     assert got.stats["raysPrimary"] == int(g["rays"][0])
 
 
-def test_shards_are_bit_identical(scene_dir):
-    """Decomposition invariance: per-pixel RNG depends only on (i, j) (Object+Extension.swift:294)."""
-    path = scenegen.config_c3(scene_dir, width=128, height=100, samples=4, depth=3, ico_level=2)
+@pytest.mark.parametrize("shard", ["rows", "tiles"])
+def test_shards_are_bit_identical(shard, scene_dir):
+    """Decomposition invariance: per-pixel RNG depends only on (i, j) (Object+Extension.swift:294).  Both
+    rt_render_params.shardMode rules partition the frame; a shard leaves the other pixels untouched (zero here)."""
+    from myraytracer_b200.distributed import owned_mask
+    path = scenegen.config_c3(scene_dir, width=130, height=100, samples=4, depth=3, ico_level=2)
     eng = RayTracerEngine(path)
     full = eng.render(0).rgba
     acc = np.zeros_like(full)
-    for n in (2, 3):
+    for n in (2, 3, 8):
         acc[:] = 0
         for k in range(n):
-            part = eng.render(0, shard_index=k, shard_count=n).rgba
-            rows = np.zeros(full.shape[0], bool)
-            for c in range(k, (full.shape[0] + 7) // 8, n):
-                rows[c * 8:(c + 1) * 8] = True
-            assert (part[~rows] == 0).all()
-            acc[rows] = part[rows]
+            part = eng.render(0, shard_index=k, shard_count=n, shard_mode=1 if shard == "tiles" else 0).rgba
+            own = owned_mask(100, 130, k, n, shard)
+            assert (part[~own] == 0).all()
+            acc[own] = part[own]
         assert np.array_equal(acc, full)
 
 
