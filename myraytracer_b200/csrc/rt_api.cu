@@ -57,6 +57,8 @@ bool isIdentity34(const double* m16) {
 
 }  // namespace
 
+static const size_t kFrameStateBytes = 16 * sizeof(unsigned long long) + 64;
+
 struct rt_scene {
     int device = 0;
     DeviceScene ds{};
@@ -77,7 +79,9 @@ struct rt_scene {
     double* dLinear = nullptr; size_t linearBytes = 0;
     HitId* dIds = nullptr; size_t idsBytes = 0;
     unsigned long long* hCounters = nullptr;  // pinned
-    cudaEvent_t evStart = nullptr, evStop = nullptr;
+    cudaEvent_t evStart = nullptr, evStop = nullptr, evSide = nullptr;
+    cudaStream_t side = nullptr;       // epilogue of a frame (counters to the host, tile order of the next frame)
+    bool sideBusy = false;
     int blocks[KV_COUNT][2] = {};      // [variant][counters]
     bool glossy = false;               // some material has roughness != 0: RNG draws inside trace
     int pendingVariant = 0;
@@ -254,11 +258,14 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     if ((rc = upload(inst, &sc->dInst, bytes))) return rc;
     if ((rc = upload(mats, &sc->dMat, bytes))) return rc;
     if ((rc = upload(lights, &sc->dLights, bytes))) return rc;
-    CK(cudaMalloc((void**)&sc->dTileCounter, 64));
-    CK(cudaMalloc((void**)&sc->dCounters, 16 * sizeof(unsigned long long)));
+    // ray / test counters (16 x u64) and the work counter behind them: one allocation, one memset per frame
+    CK(cudaMalloc((void**)&sc->dCounters, kFrameStateBytes));
+    sc->dTileCounter = reinterpret_cast<int*>(sc->dCounters + 16);
     CK(cudaMallocHost((void**)&sc->hCounters, 16 * sizeof(unsigned long long)));
     CK(cudaEventCreate(&sc->evStart));
     CK(cudaEventCreate(&sc->evStop));
+    CK(cudaEventCreateWithFlags(&sc->evSide, cudaEventDisableTiming));
+    CK(cudaStreamCreateWithFlags(&sc->side, cudaStreamNonBlocking));
     CK(cudaDeviceSynchronize());
     const double t2 = nowMs();
 
@@ -291,12 +298,14 @@ void rt_scene_destroy(rt_scene_t* sc) {
     if (!sc) return;
     cudaSetDevice(sc->device);
     cudaFree(sc->dNodes); cudaFree(sc->dTris); cudaFree(sc->dTrisD); cudaFree(sc->dNormals); cudaFree(sc->dTlas);
-    cudaFree(sc->dInst); cudaFree(sc->dMat); cudaFree(sc->dLights); cudaFree(sc->dTileCounter); cudaFree(sc->dCounters);
+    cudaFree(sc->dInst); cudaFree(sc->dMat); cudaFree(sc->dLights); cudaFree(sc->dCounters);
     cudaFree(sc->dTileCost); cudaFree(sc->dTileOrder); cudaFree(sc->dSchedWork);
     cudaFree(sc->dPathStack); cudaFree(sc->dRgba); cudaFree(sc->dLinear); cudaFree(sc->dIds);
     if (sc->hCounters) cudaFreeHost(sc->hCounters);
     if (sc->evStart) cudaEventDestroy(sc->evStart);
     if (sc->evStop) cudaEventDestroy(sc->evStop);
+    if (sc->evSide) cudaEventDestroy(sc->evSide);
+    if (sc->side) { cudaStreamSynchronize(sc->side); cudaStreamDestroy(sc->side); }
     delete sc;
 }
 

@@ -124,7 +124,10 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
         if ((rc = ensure(&sc->dSchedWork, &sc->schedWorkBytes, scheduleWorkBytes(nTiles)))) return rc;
         if (grown || std::memcmp(key, sc->schedKey, sizeof key) != 0) sc->schedValid = false;
         std::memcpy(sc->schedKey, key, sizeof key);
-        if (!sc->schedValid) CK(cudaMemsetAsync(sc->dTileCost, 0, (size_t)nTiles * 4, st));
+        if (!sc->schedValid) {
+            if (sc->sideBusy) CK(cudaStreamWaitEvent(st, sc->evSide, 0));
+            CK(cudaMemsetAsync(sc->dTileCost, 0, (size_t)nTiles * 4, st));
+        }
         rt.tileCost = sc->dTileCost;
         rt.tileOrder = sc->schedValid ? sc->dTileOrder : nullptr;
         sc->pendingScheduled = sc->schedValid ? nTiles : 0;
@@ -138,16 +141,22 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
         rt.warpTimes = dWT; g_wt = dWT; g_wtBytes = needWT; g_wtWarps = threads / 32;
     }
 #endif
+    // The frame on the caller's stream is [memset, render kernel]; what follows the kernel — counters to the host,
+    // tile order of the next frame — runs on a side stream, off the caller's critical path (a frame split over 8
+    // GPUs lasts 1.5 ms: five more stream operations were 2 % of it).  The next frame waits for that epilogue.
+    if (sc->sideBusy) CK(cudaStreamWaitEvent(st, sc->evSide, 0));
     CK(cudaEventRecord(sc->evStart, st));
-    CK(cudaMemsetAsync(sc->dTileCounter, 0, 64, st));
-    CK(cudaMemsetAsync(sc->dCounters, 0, 16 * sizeof(unsigned long long), st));
+    CK(cudaMemsetAsync(sc->dCounters, 0, kFrameStateBytes, st));
     CK(launchRender(variant, sc->ds, cp, rt, blocks, counters, st));
+    CK(cudaEventRecord(sc->evStop, st));
+    CK(cudaStreamWaitEvent(sc->side, sc->evStop, 0));
+    CK(cudaMemcpyAsync(sc->hCounters, sc->dCounters, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, sc->side));
     if (adaptive) {
-        CK(launchSchedule(sc->dTileCost, sc->dTileOrder, sc->dSchedWork, nTiles, st));      // costs of this frame -> order of the next
+        CK(launchSchedule(sc->dTileCost, sc->dTileOrder, sc->dSchedWork, nTiles, sc->side));   // costs of this frame -> order of the next
         sc->schedValid = true;
     }
-    CK(cudaMemcpyAsync(sc->hCounters, sc->dCounters, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
-    CK(cudaEventRecord(sc->evStop, st));
+    CK(cudaEventRecord(sc->evSide, sc->side));
+    sc->sideBusy = true;
     sc->pending = true; sc->pendingCounters = counters; sc->pendingStream = st;
     sc->launches = adaptive ? 3 : 1;
     return RT_OK;
@@ -159,6 +168,7 @@ int32_t rt_render_finish(rt_scene_t* sc, rt_stats* st) {
     CK(cudaSetDevice(sc->device));
     sc->pending = false;
     CK(cudaEventSynchronize(sc->evStop));
+    CK(cudaEventSynchronize(sc->evSide));       // counters are on the host, the next frame's tile order is ready
     float ms = 0;
     CK(cudaEventElapsedTime(&ms, sc->evStart, sc->evStop));
 #ifdef RT_WARPTIMES

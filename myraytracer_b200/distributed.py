@@ -123,16 +123,21 @@ class ShardedRenderer:
         hp = n_chunks(self.height) * CHUNK_ROWS
         self.send = self.recv = self.flag = None
         self._lib, self._shared_ptr, self._opened = capi.load(), None, 0
+        self.frames = 0         # frames enqueued so far; the shared frame is double-buffered on its parity
+        self._frame_bytes = hp * self.width * 4
         if self.gather == "p2p":
-            nbytes = hp * self.width * 4
-            ptrv, self._opened = self._share(nbytes, dev, C, capi)
+            # Two frames: while rank 0 still copies frame f to the host, the peers may already store pixels of frame
+            # f + 1 into the other half; they cannot reach frame f + 2 before rank 0 has passed the fence of f + 1,
+            # which its stream orders after that copy.
+            ptrv, self._opened = self._share(2 * self._frame_bytes, dev, C, capi)
             ptr = C.c_void_p(ptrv)
             self._shared_ptr = ptr.value
             self.fb_ptr = ptr.value
             self.fb = None
             self.flag = torch.zeros(1, dtype=torch.int32, device=dev)
-            if rank == 0:   # rank 0 reads the frame through torch: wrap the raw allocation without copying
-                self.fb = _wrap_device_memory(ptr.value, (hp, self.width, 4), device)
+            if rank == 0:   # rank 0 reads the frames through torch: wrap the raw allocation without copying
+                self._fb2 = _wrap_device_memory(ptr.value, (2, hp, self.width, 4), device)
+                self.fb = self._fb2[0]
         else:
             self.fb = torch.zeros((hp, self.width, 4), dtype=torch.uint8, device=dev)  # padded to whole chunks
             self.fb_ptr = self.fb.data_ptr()
@@ -168,7 +173,7 @@ class ShardedRenderer:
             torch.cuda.synchronize(self.device)
             if dist.is_initialized() and self.world > 1:
                 dist.barrier()          # nobody unmaps / frees while a peer may still write
-            self.fb = None
+            self.fb = self._fb2 = None
             self._lib.rt_shared_buffer_close(self.device, self._shared_ptr, self._opened)
             self._shared_ptr = None
         self.engine.close()
@@ -176,7 +181,14 @@ class ShardedRenderer:
     def enqueue(self, counters: bool = False) -> None:
         """Kernel for this rank's chunks + frame exchange towards rank 0, on torch's current stream; no host sync."""
         st = torch.cuda.current_stream(self.device).cuda_stream
-        self.engine.render_device(self.camera_index, d_rgba=self.fb_ptr, stream=st, shard_index=self.rank,
+        target = self.fb_ptr
+        if self.gather == "p2p":
+            half = self.frames & 1
+            target = self._shared_ptr + half * self._frame_bytes
+            if self.rank == 0:
+                self.fb = self._fb2[half]           # the frame this call renders
+        self.frames += 1
+        self.engine.render_device(self.camera_index, d_rgba=target, stream=st, shard_index=self.rank,
                                   shard_count=self.world, counters=counters, variant=self.variant, schedule=self.schedule,
                                   shard_mode=1 if self.shard == "tiles" else 0)
         if self.gather == "p2p":
