@@ -369,8 +369,11 @@ def config_c4(out_dir: str, n: int = 708, width: int = 1920, height: int = 1080,
 
 
 def config_c3(out_dir: str, width: int = 1024, height: int = 1024, samples: int = 4, depth: int = 6,
-              ico_level: int = 4) -> str:
-    """C3: closed box (10 lone triangles), mirror / dielectric / conductor spheres, dielectric PLY icosphere."""
+              ico_level: int = 4, roughness: float = 0.0, aperture: float = 0.0, focus: float = 0.0) -> str:
+    """C3: closed box (10 lone triangles), mirror / dielectric / conductor spheres, dielectric PLY icosphere.
+    Beyond BASELINE.json's C3: `roughness` != 0 makes the mirror, conductor and dielectric
+    materials glossy (random draws inside `trace`, Object+Extension.swift:191-197,210-216,259-265); `aperture` and
+    `focus` > 0 give the camera a thin lens (:325-338)."""
     rng = SplitMix64(3)
     pos, tris = icosphere_mesh(ico_level, radius=1.0)
     write_ply(os.path.join(out_dir, "c3_ico.ply"), pos, tris)
@@ -410,9 +413,12 @@ def config_c3(out_dir: str, width: int = 1024, height: int = 1024, samples: int 
     objs.append(SceneObject(OBJ_MESH, id=14, material=7, smooth=False, plyPath="c3_ico.ply", transform=colmajor(Mi)))
     sc.objects = objs
     sc.pointLights = [PointLight((0.0, 9.0, 2.0), (6000, 6000, 6000)), PointLight((-3.0, 6.0, 4.0), (2600, 2400, 2200))]
+    for m in sc.materials:
+        if m.type != MAT_PLAIN:
+            m.roughness = roughness
     sc.cameras = [Camera(id=1, imageName="c3.png", width=width, height=height, numSamples=samples,
                          position=(0.0, 4.0, 14.5), gazePoint=(0.0, 3.0, 0.0), up=(0, 1, 0),
-                         nearDistance=1.0, fovy=40.0, isLookAt=True)]
+                         nearDistance=1.0, fovy=40.0, isLookAt=True, apertureSize=aperture, focusDistance=focus)]
     path = os.path.join(out_dir, "c3.rtscene")
     write_rtscene(sc, path)
     return path

@@ -14,6 +14,12 @@ CASES = {
     "c3": dict(fn=scenegen.config_c3, kw=dict(width=256, height=256, samples=4)),   # depth 6 recursion
     "c4s": dict(fn=scenegen.config_c4, kw=dict(n=260, width=480, height=270, samples=4)),
     "c5s": dict(fn=scenegen.config_c5, kw=dict(n=64, width=320, height=180, samples=4, meshes=4)),
+    # SURVEY.md 8f row 3, beyond BASELINE.json's configs: thin-lens camera (fast kernel, 5 draws per sample),
+    # glossy materials (general kernel: draws inside the recursion), both
+    "c3dof": dict(fn=scenegen.config_c3, kw=dict(width=192, height=192, samples=4, aperture=0.35, focus=13.0)),
+    "c3glossy": dict(fn=scenegen.config_c3, kw=dict(width=192, height=192, samples=4, roughness=0.12)),
+    "c3glossydof": dict(fn=scenegen.config_c3, kw=dict(width=160, height=160, samples=9, depth=4, roughness=0.3,
+                                                       aperture=0.2, focus=14.0)),
 }
 
 
