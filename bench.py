@@ -227,6 +227,8 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
+    if args.build:
+        os.environ["RTCUDA_BUILD"] = args.build        # rt_scene_desc.buildMode override (include/rtcuda.h)
     t0 = time.time()
     path = make_scene(args.config, rank)
     R = ShardedRenderer(path, device=local, rank=rank, world=world, variant=args.variant, gather=args.gather, shard=args.shard,
@@ -347,7 +349,8 @@ def run_ours(args):
                        "l2": ("NOT FLUSHED (diagnostic run); " if args.no_flush else "") + "256 MB buffer written between timed iterations (L2 flush); scene working set "
                              f"{info['deviceBytes'] / 1e6:.0f} MB"},
             "wall_ms_per_step": wall * 1e3 / args.steps, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
-            "roofline": roofline, "build_ms": info["buildMs"], "upload_ms": info["uploadMs"]}
+            "roofline": roofline, "build_ms": info["buildMs"], "upload_ms": info["uploadMs"],
+            "bvh_build": "device LBVH" if info["deviceBuiltBlas"] else "host binned SAH"}
     if world == 1 and not args.no_cpu:
         mr, ci = cpu_sample(path, target_s=args.cpu_seconds)
         line["cpu_baseline"] = {"value": mr, "unit": UNIT, "cores": ci["cores"], "kind": "port", "sample": ci["sample"],
@@ -373,6 +376,8 @@ def main():
     ap.add_argument("--config", choices=sorted(BENCH_CONFIGS), default="c4")
     ap.add_argument("--shard", choices=["tiles", "rows"], default=None,
                     help="N>1: 8-row chunks round-robin (default) or 8x4 tiles dealt along diagonals (p2p only)")
+    ap.add_argument("--build", choices=["host", "device"], default=None,
+                    help="who builds the mesh BVHs: host = multi-threaded binned SAH (default), device = CUDA LBVH")
     ap.add_argument("--schedule", choices=["adaptive", "spatial"], default="adaptive",
                     help="rt_render_params.scheduleMode: tile order learnt from the previous frame, or top to bottom")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")

@@ -108,7 +108,7 @@ typedef struct rt_scene_desc {
     double background[3];         /* scene.backgroundColor */
     double intersectionTestEpsilon, shadowRayEpsilon;
     int32_t maxRecursionDepth;
-    int32_t reserved2;
+    int32_t buildMode;            /* RT_BUILD_* : who builds the mesh BVHs */
 } rt_scene_desc;
 
 /* ParsingKit Camera fields read by render/makeCameraBasis (Object+Extension.swift:58-63,385-425) */
@@ -127,6 +127,13 @@ typedef struct rt_camera {
 /* progress: rows finished so far (multiples of the 8-row chunk of Object+Extension.swift:75);
  * return non-zero to cancel (RayTracer.swift:178-180) */
 typedef int (*rt_progress_fn)(int32_t rowsDone, int32_t rowsTotal, void* user);
+
+/* rt_scene_desc.buildMode.  The reference builds on the CPU (Accelearion/BVH.swift:78-250); the image does not depend
+ * on the tree.  HOST_SAH (default): multi-threaded binned SAH, best traversal speed.  DEVICE_LBVH: Morton-order radix
+ * tree built by CUDA kernels, ~20x faster to build, slower to traverse; a tree too deep for the traversal stack falls
+ * back to HOST_SAH for that mesh.  The environment variable RTCUDA_BUILD=device|host overrides the field. */
+#define RT_BUILD_HOST_SAH    0
+#define RT_BUILD_DEVICE_LBVH 1
 
 #define RT_SHARD_ROWS  0
 #define RT_SHARD_TILES 1
@@ -184,7 +191,7 @@ typedef struct rt_scene_info {
     int64_t deviceBytes;
     double buildMs, uploadMs;
     int32_t device;
-    int32_t reserved;
+    int32_t deviceBuiltBlas;      /* mesh BVHs built by the device builder (RT_BUILD_DEVICE_LBVH) */
 } rt_scene_info;
 
 typedef struct rt_scene rt_scene_t;

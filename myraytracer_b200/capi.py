@@ -73,7 +73,7 @@ class rt_scene_desc(C.Structure):
                 ("nAreaLights", C.c_int64), ("areaLights", C.POINTER(rt_area_light)),
                 ("ambient", D3), ("background", D3),
                 ("intersectionTestEpsilon", C.c_double), ("shadowRayEpsilon", C.c_double),
-                ("maxRecursionDepth", C.c_int32), ("reserved2", C.c_int32)]
+                ("maxRecursionDepth", C.c_int32), ("buildMode", C.c_int32)]
 
 
 class rt_camera(C.Structure):
@@ -107,7 +107,7 @@ class rt_stats(C.Structure):
 class rt_scene_info(C.Structure):
     _fields_ = [(n, C.c_int64) for n in ("triangles", "spheres", "planes", "instances", "blasCount", "blasNodes",
                                          "tlasNodes", "maxLeafSize", "maxDepth", "deviceBytes")]
-    _fields_ += [("buildMs", C.c_double), ("uploadMs", C.c_double), ("device", C.c_int32), ("reserved", C.c_int32)]
+    _fields_ += [("buildMs", C.c_double), ("uploadMs", C.c_double), ("device", C.c_int32), ("deviceBuiltBlas", C.c_int32)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

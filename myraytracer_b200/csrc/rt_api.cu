@@ -118,6 +118,20 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     sc->device = device;
     const double t0 = nowMs();
 
+    // ---- who builds the mesh BVHs (rt_scene_desc.buildMode, overridden by RTCUDA_BUILD)
+    bool deviceBuild = d->buildMode == RT_BUILD_DEVICE_LBVH;
+    if (const char* e = std::getenv("RTCUDA_BUILD")) deviceBuild = std::strcmp(e, "device") == 0;
+    if (d->buildMode != RT_BUILD_HOST_SAH && d->buildMode != RT_BUILD_DEVICE_LBVH) return fail(RT_ERR_INVALID, "rt_scene_desc.buildMode outside 0..1");
+    struct DevVerts {       // the scene's triangle vertices on the device, for the device builder only
+        double* p = nullptr;
+        ~DevVerts() { cudaFree(p); }
+    } dVerts;
+    if (deviceBuild && d->nTriangles > 0) {
+        CK(cudaMalloc((void**)&dVerts.p, (size_t)d->nTriangles * 9 * sizeof(double)));
+        CK(cudaMemcpy(dVerts.p, d->triVertices, (size_t)d->nTriangles * 9 * sizeof(double), cudaMemcpyHostToDevice));
+    }
+    int deviceBuilt = 0;
+
     // ---- BLAS build (one per rt_blas, shared by instances)
     struct BlasInfo {
         int kind = INST_MESH; int64_t prim = 0; int64_t matId = 0; int smooth = 0;
@@ -161,7 +175,13 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
         BlasBuildInput in{};
         in.triVertices = d->triVertices; in.triIndices = idx.data(); in.count = bl.primCount; in.threads = 0;
         BlasBuildOutput out;
-        buildBlas(in, out);
+        bool built = false;
+        if (deviceBuild && bl.primCount >= 2) {
+            CK(buildBlasDevice(dVerts.p, in, out));
+            built = out.maxDepth <= renderStackCapacity() - 2;      // too deep for the stacks: the SAH builder takes over
+            if (built) deviceBuilt++;
+        }
+        if (!built) buildBlas(in, out);
         if (out.maxDepth > renderStackCapacity() - 2) return fail(RT_ERR_UNSUPPORTED, "BLAS deeper than the traversal stack");
         bi.kind = bl.primCount == 1 ? INST_TRI : INST_MESH;
         bi.prim = pr[0].primitiveIndex;
@@ -290,7 +310,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     rt_scene_info& I = sc->info;
     I.triangles = d->nTriangles; I.spheres = d->nSpheres; I.planes = d->nPlanes; I.instances = d->nInstances; I.blasCount = d->nBlas;
     I.blasNodes = (int64_t)nodes.size(); I.tlasNodes = (int64_t)tl.nodes.size(); I.maxLeafSize = maxLeaf; I.maxDepth = maxDepth;
-    I.deviceBytes = bytes; I.buildMs = t1 - t0; I.uploadMs = t2 - t1; I.device = device;
+    I.deviceBytes = bytes; I.buildMs = t1 - t0; I.uploadMs = t2 - t1; I.device = device; I.deviceBuiltBlas = deviceBuilt;
     return RT_OK;
 }
 
