@@ -286,7 +286,7 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFas
                     if (nc > 0) {
                         if (nc == 2) pathStore(T.pathStack, T.stride, T.gtid, 0, c2);
                         R.secondary += nc;
-                        c = scalarPathLoop<false, COUNT>(S, T, c1, nc - 1, false, 0.0, nullptr, rng, C, R, c);
+                        c = scalarPathLoop<false, COUNT, true>(S, T, c1, nc - 1, false, 0.0, nullptr, rng, C, R, c);
                     }
                 }
             }

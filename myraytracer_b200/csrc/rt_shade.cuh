@@ -221,7 +221,8 @@ __device__ __forceinline__ int spawnChildren(const DeviceScene& S, const ShadePo
 // `level` the number of entries already waiting on this thread's path stack.  firstIsPrimary: `cur` is the
 // camera ray (tMin = near-plane clip :341-344, hit id recorded).  Returns `color` plus the w * Lo of all
 // processed entries, added in processing order.
-template <bool GLOSSY, bool COUNT>
+// CALL: the traversal is the out-of-line traceSceneCall (fast kernel) instead of two inlined walks.
+template <bool GLOSSY, bool COUNT, bool CALL = false>
 __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceScratch& T, PathEntry cur, int level,
                                              bool firstIsPrimary, double tMinPrimary, HitId* idSlot, PCG32& rng, Counters& C,
                                              RayCounts& R, V3 color) {
@@ -230,7 +231,8 @@ __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceSc
     for (;;) {
         HitRec hit;
         hit.t = CUDART_INF; hit.u = hit.v = 0; hit.inst = -1; hit.slot = 0;
-        traceScene<COUNT>(S, cur.o, cur.d, primary ? tMinPrimary : 0.0, hit, false, T.sstack, T.sstackN, C);
+        if (CALL) hit = traceSceneCall<COUNT>(S, cur.o, cur.d, primary ? tMinPrimary : 0.0, hit, false, T.sstack, T.sstackN, COUNT ? &C : nullptr).hit;
+        else traceScene<COUNT>(S, cur.o, cur.d, primary ? tMinPrimary : 0.0, hit, false, T.sstack, T.sstackN, C);
         Surface sf;
         if (hit.inst >= 0) {
             resolveHit(S, hit, cur.o, cur.d, sf);
@@ -259,7 +261,9 @@ __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceSc
                     HitRec sh;
                     sh.t = dist; sh.u = sh.v = 0; sh.inst = -1; sh.slot = 0;             // tMax = dist (:124)
                     R.shadow++;
-                    if (!traceScene<COUNT>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, C))
+                    const bool occluded = CALL ? traceSceneCall<COUNT>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, COUNT ? &C : nullptr).occluded
+                                               : traceScene<COUNT>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, C);
+                    if (!occluded)
                         Lo = Lo + pointLightTerm(*sp.mat, pl, sp.N, cur.d, wi, dist);
                 }
             }
