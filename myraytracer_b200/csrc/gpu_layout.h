@@ -51,7 +51,7 @@ struct RT_ALIGN(16) GTriD {  // FP64 vertices
     int64_t triIndex;
 };
 
-struct RT_ALIGN(16) TNode {
+struct RT_ALIGN(16) TNode {             // TLAS builder output (FP64); rt_api.cu encodes it into GNode records
     double lo0[3], hi0[3], lo1[3], hi1[3];
     int32_t child0, child1, pad0, pad1;  // leaf: ~ref = instance index (one instance per leaf)
 };
@@ -97,7 +97,8 @@ struct DeviceScene {
     const GTriD* trisD;
     const double* triNormals;      // original triangle index * 9
     const double* triVertsD;       // original triangle index * 9 (FP64 v0,v1,v2; hit point / flat normal)
-    const TNode* tlas;
+    const GNode* tlas;             // TLAS in the BLAS node format: conservative FP32 boxes relative to tlasCentre;
+                                   // child < 0: ~ref = instance index (one instance per leaf)
     const GInstance* instances;
     const GMaterial* materials;
     const GPointLight* pointLights;
@@ -107,6 +108,7 @@ struct DeviceScene {
     int32_t pad;
     double ambient[3], background[3];
     double eps, shadowEps;
+    double tlasLo[3], tlasHi[3], tlasCentre[3];   // exact world bounds of all instances and their centre
 };
 
 struct CameraParams {

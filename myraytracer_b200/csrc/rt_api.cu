@@ -66,7 +66,7 @@ struct rt_scene {
     int64_t meshes = 0;
     // device allocations
     GNode* dNodes = nullptr; GTri* dTris = nullptr; GTriD* dTrisD = nullptr; double* dNormals = nullptr;
-    TNode* dTlas = nullptr; GInstance* dInst = nullptr; GMaterial* dMat = nullptr; GPointLight* dLights = nullptr;
+    GNode* dTlas = nullptr; GInstance* dInst = nullptr; GMaterial* dMat = nullptr; GPointLight* dLights = nullptr;
     // render state (re-used across calls)
     int* dTileCounter = nullptr; unsigned long long* dCounters = nullptr;
     // tile schedule learnt from the previous frame of the same geometry (rt_kernels.cu: scheduleKernel)
@@ -274,7 +274,35 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     if ((rc = upload(tris, &sc->dTris, bytes))) return rc;
     if ((rc = upload(trisD, &sc->dTrisD, bytes))) return rc;
     if ((rc = upload(normals, &sc->dNormals, bytes))) return rc;
-    if ((rc = upload(tl.nodes, &sc->dTlas, bytes))) return rc;
+    // TLAS records: the BLAS node format — FP32 boxes relative to the centre of the scene bounds, padded by
+    // M * 2^-19 and rounded outward (conservative: the instance's own exact test decides)
+    std::vector<GNode> tlasF(tl.nodes.size());
+    double sLo[3] = {0, 0, 0}, sHi[3] = {0, 0, 0}, sC[3] = {0, 0, 0};
+    if (!tl.nodes.empty()) {
+        const TNode& r = tl.nodes[0];
+        double M = 0;
+        for (int a = 0; a < 3; a++) {
+            sLo[a] = std::fmin(r.lo0[a], r.lo1[a]); sHi[a] = std::fmax(r.hi0[a], r.hi1[a]); sC[a] = 0.5 * (sLo[a] + sHi[a]);
+            M = std::fmax(M, std::fmax(std::fabs(sLo[a] - sC[a]), std::fabs(sHi[a] - sC[a])));
+        }
+        const double P = std::fmax(M * std::ldexp(1.0, -19), 1e-30);
+        auto down = [](double x) { float f = (float)x; return (double)f > x ? std::nextafterf(f, -INFINITY) : f; };
+        auto up = [](double x) { float f = (float)x; return (double)f < x ? std::nextafterf(f, INFINITY) : f; };
+        for (size_t i = 0; i < tl.nodes.size(); i++) {
+            const TNode& t = tl.nodes[i];
+            GNode& g = tlasF[i];
+            float lo0[3], hi0[3], lo1[3], hi1[3];
+            for (int a = 0; a < 3; a++) {
+                lo0[a] = down(t.lo0[a] - sC[a] - P); hi0[a] = up(t.hi0[a] - sC[a] + P);
+                lo1[a] = down(t.lo1[a] - sC[a] - P); hi1[a] = up(t.hi1[a] - sC[a] + P);
+            }
+            g.q0[0] = lo0[0]; g.q0[1] = lo0[1]; g.q0[2] = lo0[2]; g.q0[3] = hi0[0];
+            g.q1[0] = hi0[1]; g.q1[1] = hi0[2]; g.q1[2] = lo1[0]; g.q1[3] = lo1[1];
+            g.q2[0] = lo1[2]; g.q2[1] = hi1[0]; g.q2[2] = hi1[1]; g.q2[3] = hi1[2];
+            g.child0 = t.child0; g.child1 = t.child1; g.pad0 = g.pad1 = 0;
+        }
+    }
+    if ((rc = upload(tlasF, &sc->dTlas, bytes))) return rc;
     if ((rc = upload(inst, &sc->dInst, bytes))) return rc;
     if ((rc = upload(mats, &sc->dMat, bytes))) return rc;
     if ((rc = upload(lights, &sc->dLights, bytes))) return rc;
@@ -293,6 +321,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     S.nodes = sc->dNodes; S.tris = sc->dTris; S.trisD = sc->dTrisD; S.triNormals = sc->dNormals; S.triVertsD = nullptr;
     S.tlas = sc->dTlas; S.instances = sc->dInst; S.materials = sc->dMat; S.pointLights = sc->dLights;
     S.tlasRootRef = tl.rootRef;
+    std::memcpy(S.tlasLo, sLo, 24); std::memcpy(S.tlasHi, sHi, 24); std::memcpy(S.tlasCentre, sC, 24);
     S.nInstances = (int32_t)d->nInstances; S.nMaterials = (int32_t)d->nMaterials; S.nPointLights = (int32_t)d->nPointLights;
     S.maxDepth = d->maxRecursionDepth;
     std::memcpy(S.ambient, d->ambient, 24); std::memcpy(S.background, d->background, 24);

@@ -204,38 +204,44 @@ __device__ __forceinline__ bool packetScene(const DeviceScene& S, V3 o, V3 d, do
     int32_t cur = S.tlasRootRef;
     if (cur == kEmptyRef) return false;
     if (cur < 0) return (packetInstance<COUNT>(S, ~cur, o, d, eps, tMin, hit, anyhit, live, wstack, C) & bit) != 0;
-    const V3 ia = refinedInv(d);
     const double tLow = dmax(eps, tMin);
+    RayF rf = makeRayF(S.tlasLo, S.tlasHi, S.tlasCentre, o, d, refinedInv(d), tLow, hit.t);
+    if (COUNT && active) C.box++;
+    live = __ballot_sync(RT_FULL, active && rf.hits);
+    if (!live) return false;
+    if (!(active && rf.hits)) rf.tmax = -CUDART_INF_F;          // not part of the packet: fails every box
     int2* tstack = wstack + RT_WSTACK;
     uint32_t occluded = 0u, curMask = live;
     int sp = 0;
     for (;;) {
         bool descended = false;
         if (cur >= 0) {
-            const TNode& n = S.tlas[cur];
-            double n0, f0, n1, f1;
-            slabApprox(n.lo0, n.hi0, o, ia, n0, f0);
-            slabApprox(n.lo1, n.hi1, o, ia, n1, f1);
+            float n0, n1;
+            bool h0, h1;
+            int2 ch;
+            twoBoxes(S.tlas + cur, rf, n0, h0, n1, h1, ch);       // conservative FP32, like the BLAS nodes
             const bool inl = (curMask & bit) != 0;
             if (COUNT && inl) C.box += 2;
-            const bool h0 = inl && !(n0 > f0) && !(f0 < tLow) && !(n0 > hit.t);
-            const bool h1 = inl && !(n1 > f1) && !(f1 < tLow) && !(n1 > hit.t);
+            h0 = h0 && inl; h1 = h1 && inl;
             const uint32_t m0 = __ballot_sync(RT_FULL, h0), m1 = __ballot_sync(RT_FULL, h1);
             if (m0 && m1) {
                 const uint32_t v1 = __ballot_sync(RT_FULL, h1 && (!h0 || n1 < n0));
                 const bool swap = 2 * __popc(v1) > __popc(m0 | m1);
-                if (sp < RT_WTSTACK) { tstack[sp] = swap ? make_int2(n.child0, (int)m0) : make_int2(n.child1, (int)m1); sp++; }
-                cur = swap ? n.child1 : n.child0;
+                if (sp < RT_WTSTACK) { tstack[sp] = swap ? make_int2(ch.x, (int)m0) : make_int2(ch.y, (int)m1); sp++; }
+                cur = swap ? ch.y : ch.x;
                 curMask = swap ? m1 : m0;
                 descended = true;
-            } else if (m0) { cur = n.child0; curMask = m0; descended = true; }
-            else if (m1) { cur = n.child1; curMask = m1; descended = true; }
+            } else if (m0) { cur = ch.x; curMask = m0; descended = true; }
+            else if (m1) { cur = ch.y; curMask = m1; descended = true; }
         } else {
             const uint32_t o_ = packetInstance<COUNT>(S, ~cur, o, d, eps, tMin, hit, anyhit, curMask, wstack, C);
             if (anyhit) {
                 occluded |= o_;
                 live &= ~o_;
                 if (!live) return (occluded & bit) != 0;
+                if (o_ & bit) rf.tmax = -CUDART_INF_F;
+            } else {
+                rf.tmax = fminf(rf.tmax, __double2float_ru(hit.t - rf.t0));   // a closer hit prunes the boxes that follow
             }
         }
         if (descended) continue;

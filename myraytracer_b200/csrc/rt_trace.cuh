@@ -55,7 +55,8 @@ __device__ __forceinline__ bool enterInstance(const DeviceScene& S, int idx, V3 
     return analyticInstance<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, C);
 }
 
-// TLAS walk (FP64 boxes = unions of Instance.worldBounds, widened interval; near child first).
+// TLAS walk: conservative FP32 boxes (unions of Instance.worldBounds) like the BLAS nodes, near child first; every
+// instance reached is then tested exactly.
 template <bool COUNT>
 __device__ __forceinline__ bool traceScene(const DeviceScene& S, V3 o, V3 d, double tMin, HitRec& hit, bool anyhit,
                                            int32_t* sstack, int sstackN, Counters& C) {
@@ -63,22 +64,22 @@ __device__ __forceinline__ bool traceScene(const DeviceScene& S, V3 o, V3 d, dou
     int32_t cur = S.tlasRootRef;
     if (cur == kEmptyRef) return false;
     if (cur < 0) return enterInstance<COUNT>(S, ~cur, o, d, eps, tMin, hit, anyhit, sstack, sstackN, C);
-    const V3 ia = refinedInv(d);
     const double tLow = dmax(eps, tMin);
+    RayF rf = makeRayF(S.tlasLo, S.tlasHi, S.tlasCentre, o, d, refinedInv(d), tLow, hit.t);
+    if (COUNT) C.box++;
+    if (!rf.hits) return false;
     int32_t tstack[RT_TLAS_STACK];
     int sp = 0;
     for (;;) {
         if (cur >= 0) {
-            const TNode& n = S.tlas[cur];
-            double n0, f0, n1, f1;
-            slabApprox(n.lo0, n.hi0, o, ia, n0, f0);
-            slabApprox(n.lo1, n.hi1, o, ia, n1, f1);
-            if (COUNT) C.box += 2;
+            float n0, n1;
+            bool h0, h1;
+            int2 ch;
             // reference: enter iff tmax >= max(tmin, eps) (no culling against hit.t in the box test,
-            // RTContext.swift:632-640); culling against hit.t cannot change the closest hit.
-            bool h0 = !(n0 > f0) && !(f0 < tLow) && !(n0 > hit.t);
-            bool h1 = !(n1 > f1) && !(f1 < tLow) && !(n1 > hit.t);
-            int32_t c0 = n.child0, c1 = n.child1;
+            // RTContext.swift:632-640); culling against hit.t (rf.tmax) cannot change the closest hit.
+            twoBoxes(S.tlas + cur, rf, n0, h0, n1, h1, ch);
+            if (COUNT) C.box += 2;
+            int32_t c0 = ch.x, c1 = ch.y;
             if (h0 && h1) {
                 if (n1 < n0) { int32_t t = c0; c0 = c1; c1 = t; }
                 if (sp < RT_TLAS_STACK) tstack[sp++] = c1;
@@ -88,6 +89,7 @@ __device__ __forceinline__ bool traceScene(const DeviceScene& S, V3 o, V3 d, dou
             else if (h1) { cur = c1; continue; }
         } else {
             if (enterInstance<COUNT>(S, ~cur, o, d, eps, tMin, hit, anyhit, sstack, sstackN, C)) return true;
+            rf.tmax = __double2float_ru(hit.t - rf.t0);       // a closer hit prunes the boxes that follow
         }
         if (sp == 0) return false;
         cur = tstack[--sp];

@@ -53,6 +53,56 @@ __device__ __forceinline__ void slabApprox(const double* lo, const double* hi, V
     tf = tf + fabs(tf) * k;
 }
 
+// The conservative FP32 view of a ray against boxes stored relative to `centre` (BLAS nodes, TLAS nodes): the origin
+// is advanced in FP64 to its entry into the exact bounds [lo, hi] before it is rounded, so the FP32 error stays
+// relative to the box size; (plane - o) / d is one FMA, plane * inv + (-o * inv), with |inv| clamped to 1e30 so
+// that no inf - inf arises.  The stored boxes' padding covers every rounding here.
+struct RayF {
+    float ix, iy, iz, nx, ny, nz, tmin, tmax;
+    double t0;
+    bool hits;     // the exact bounds are reached within [tLow, tHigh] (widened FP64 test)
+};
+__device__ __forceinline__ RayF makeRayF(const double* lo, const double* hi, const double* centre, V3 o, V3 d, V3 ia,
+                                         double tLow, double tHigh) {
+    RayF r;
+    const V3 oc = o - ld3(centre);
+    const double l[3] = {lo[0] - centre[0], lo[1] - centre[1], lo[2] - centre[2]};
+    const double h[3] = {hi[0] - centre[0], hi[1] - centre[1], hi[2] - centre[2]};
+    double tn, tf;
+    slabApprox(l, h, oc, ia, tn, tf);
+    r.hits = !(tn > tf || tf < tLow || tn > tHigh);
+    double t0 = tn > 0.0 ? tn : 0.0;
+    if (!(t0 < 1e300)) t0 = 0.0;
+    r.t0 = t0;
+    const V3 o2 = oc + d * t0;
+    const float ox = (float)o2.x, oy = (float)o2.y, oz = (float)o2.z;
+    r.ix = fminf(fmaxf(1.0f / (float)d.x, -1e30f), 1e30f);
+    r.iy = fminf(fmaxf(1.0f / (float)d.y, -1e30f), 1e30f);
+    r.iz = fminf(fmaxf(1.0f / (float)d.z, -1e30f), 1e30f);
+    r.nx = -(ox * r.ix); r.ny = -(oy * r.iy); r.nz = -(oz * r.iz);
+    r.tmin = __double2float_rd(tLow - t0);
+    r.tmax = __double2float_ru(tHigh - t0);
+    return r;
+}
+// both children of a node record against the ray: entry distances n0, n1 (relative to t0) and hit flags
+__device__ __forceinline__ void twoBoxes(const GNode* node, const RayF& r, float& n0, bool& h0, float& n1, bool& h1, int2& child) {
+    const float4* np = reinterpret_cast<const float4*>(node);
+    const float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2);
+    const int4 ch = __ldg(reinterpret_cast<const int4*>(np + 3));
+    const float a0 = __fmaf_rn(q0.x, r.ix, r.nx), b0 = __fmaf_rn(q0.w, r.ix, r.nx);
+    const float a1 = __fmaf_rn(q0.y, r.iy, r.ny), b1 = __fmaf_rn(q1.x, r.iy, r.ny);
+    const float a2 = __fmaf_rn(q0.z, r.iz, r.nz), b2 = __fmaf_rn(q1.y, r.iz, r.nz);
+    n0 = fmaxf(fmaxf(fminf(a0, b0), fminf(a1, b1)), fmaxf(fminf(a2, b2), r.tmin));
+    const float f0 = fminf(fminf(fmaxf(a0, b0), fmaxf(a1, b1)), fminf(fmaxf(a2, b2), r.tmax));
+    const float c0 = __fmaf_rn(q1.z, r.ix, r.nx), d0 = __fmaf_rn(q2.y, r.ix, r.nx);
+    const float c1 = __fmaf_rn(q1.w, r.iy, r.ny), d1 = __fmaf_rn(q2.z, r.iy, r.ny);
+    const float c2 = __fmaf_rn(q2.x, r.iz, r.nz), d2 = __fmaf_rn(q2.w, r.iz, r.nz);
+    n1 = fmaxf(fmaxf(fminf(c0, d0), fminf(c1, d1)), fmaxf(fminf(c2, d2), r.tmin));
+    const float f1 = fminf(fminf(fmaxf(c0, d0), fmaxf(c1, d1)), fminf(fmaxf(c2, d2), r.tmax));
+    h0 = n0 <= f0; h1 = n1 <= f1;
+    child = make_int2(ch.x, ch.y);
+}
+
 // 1/d to ~1e-13 relative without an FP64 division: FP32 reciprocal + one Newton step.
 __device__ __forceinline__ double refinedInv1(double d) {
     double r = (double)(1.0f / (float)d);
