@@ -170,7 +170,10 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFas
         skipTab[threadIdx.x] = make_ulonglong2(ak, gk);
         __syncwarp();
     }
-    const int unitsPerTile = segmented ? ns : 1;
+    // n*n a multiple of 32 (32, 64 spp ...): a pixel's samples fill whole passes, so one pixel (n*n / 32 passes) is a
+    // unit and the ordered sum is carried inside it.  Only otherwise (9, 25, 36 spp ...) the whole tile is one unit.
+    const bool perPixel = !segmented && (ns % 32) == 0;
+    const int unitsPerTile = segmented ? ns : (perPixel ? 32 : 1);
     const int totalUnits = tiles.count * unitsPerTile;
     __shared__ uint2 unitNote[RT_FAST_BLOCK / 32];               // (clock at unit start, tile): read back when the unit ends
 #ifdef RT_WARPTIMES
@@ -194,7 +197,7 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFas
         wtUnits++;
 #endif
         // work unit: one 32-ray pass of a tile when the pixels of a pass are complete in themselves (ns divides
-        // 32), else the whole tile (the ordered per-pixel sum is carried across passes).  Small units keep the
+        // 32), one pixel when 32 divides ns, else the whole tile (the ordered per-pixel sum is carried across passes).  Small units keep the
         // tail short when a frame is split over 8 GPUs (a few thousand warps share ~8k tiles per rank).
         // One unit per draw: consecutive units go to warps running at the same time, which share tiles, BVH
         // nodes and triangles in L2 (drawing 8 at a time measured 10 % slower).
@@ -211,7 +214,9 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFas
         wtUnit = tile * unitsPerTile + (unit - slot * unitsPerTile);     // records are indexed by (tile, pass)
         if (lane == 0 && out.warpTimes) out.warpTimes[4 * (T.stride >> 5) + 4 * (size_t)wtUnit] = wt2;
 #endif
-        const int itBegin = segmented ? unit - slot * unitsPerTile : 0, itEnd = segmented ? itBegin + 1 : ns;
+        const int sub = unit - slot * unitsPerTile;
+        const int itBegin = segmented ? sub : (perPixel ? sub * (ns >> 5) : 0);
+        const int itEnd = segmented ? itBegin + 1 : (perPixel ? itBegin + (ns >> 5) : ns);
         int x0, y0;
         tiles.origin(tile, x0, y0);
         int openP = -1;               // ordered accumulation state of the generic path (warp-uniform)

@@ -16,6 +16,9 @@ CASES = {
     "c5s": dict(fn=scenegen.config_c5, kw=dict(n=64, width=320, height=180, samples=4, meshes=4)),
     # SURVEY.md 8f row 3, beyond BASELINE.json's configs: thin-lens camera (fast kernel, 5 draws per sample),
     # glossy materials (general kernel: draws inside the recursion), both
+    # 64 and 36 spp: units of one pixel (32 divides n*n) and of a whole tile (neither divides the other)
+    "c1x64": dict(fn=scenegen.config_c1, kw=dict(width=96, height=80, samples=64)),
+    "c1x36": dict(fn=scenegen.config_c1, kw=dict(width=96, height=80, samples=36)),
     "c3dof": dict(fn=scenegen.config_c3, kw=dict(width=192, height=192, samples=4, aperture=0.35, focus=13.0)),
     "c3glossy": dict(fn=scenegen.config_c3, kw=dict(width=192, height=192, samples=4, roughness=0.12)),
     "c3glossydof": dict(fn=scenegen.config_c3, kw=dict(width=160, height=160, samples=9, depth=4, roughness=0.3,
