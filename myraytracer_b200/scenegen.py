@@ -463,7 +463,44 @@ def config_c5(out_dir: str, n: int = 708, width: int = 3840, height: int = 2160,
     return path
 
 
-CONFIGS = {"c1": config_c1, "c2": config_c2, "c3": config_c3, "c4": config_c4, "c5": config_c5}
+def config_instances(out_dir: str, width: int = 256, height: int = 192, samples: int = 4, depth: int = 3) -> str:
+    """Not one of BASELINE.json's configs: the object kinds they leave out.  An infinite ground plane (its 1e5 bounds,
+    RTContext.swift:172-174, stretch the scene box), one PLY mesh and three MeshInstances of it sharing its BLAS
+    (:384-401): one with a material override, one mirrored (negative determinant -> flipped normals, :691-698),
+    one an instance of an instance; a dielectric sphere in front."""
+    pos, tris = icosphere_mesh(2, radius=1.0, seed=7, disp=0.15)
+    write_ply(os.path.join(out_dir, "inst_blob.ply"), pos, tris)
+    sc = Scene(maxRecursionDepth=depth, backgroundColor=(12, 14, 20), ambient=(20, 20, 20))
+    sc.materials = [_plain(1, (0.55, 0.55, 0.5), (0.1, 0.1, 0.1), 10.0),
+                    _plain(2, (0.8, 0.3, 0.2), (0.5, 0.5, 0.5), 60.0),
+                    _plain(3, (0.2, 0.5, 0.8), (0.4, 0.4, 0.4), 40.0),
+                    Material(id=4, type=MAT_MIRROR, ambient=(0, 0, 0), diffuse=(0.05, 0.05, 0.05),
+                             specular=(0.3, 0.3, 0.3), mirror=(0.85, 0.85, 0.85), phong=100.0),
+                    Material(id=5, type=MAT_DIELECTRIC, ambient=(0, 0, 0), diffuse=(0.02, 0.02, 0.02), specular=(0.2, 0.2, 0.2),
+                             mirror=(1, 1, 1), absorption=(0.02, 0.06, 0.04), phong=200.0, ior=1.5)]
+    sc.vertexData = np.asarray([(0.0, 0.0, 0.0), (0.8, 1.1, 4.0)], np.float64)
+    Mm = mat_translate((-0.5, 1.4, 0.0)) @ mat_rotate((0.2, 1.0, 0.1), 20.0) @ mat_scale((1.3, 1.3, 1.3))
+    Ma = mat_translate((3.2, 1.1, -2.5)) @ mat_scale((0.9, 1.1, 0.9))
+    Mb = mat_translate((-3.6, 1.2, -1.5)) @ mat_scale((-1.0, 1.0, 1.0))          # mirrored: det < 0
+    Mc = mat_translate((0.5, 3.6, -3.0)) @ mat_scale((0.6, 0.6, 0.6))
+    sc.objects = [
+        SceneObject(OBJ_PLANE, id=1, material=1, centerIdx=1, normal=(0.0, 1.0, 0.0)),
+        SceneObject(OBJ_SPHERE, id=2, material=5, centerIdx=2, radius=1.0),
+        SceneObject(OBJ_MESH, id=5, material=2, smooth=True, plyPath="inst_blob.ply", transform=colmajor(Mm)),
+        SceneObject(OBJ_MESH_INSTANCE, id=6, material=4, baseMeshID=5, transform=colmajor(Ma)),
+        SceneObject(OBJ_MESH_INSTANCE, id=7, material=None, baseMeshID=5, transform=colmajor(Mb)),
+        SceneObject(OBJ_MESH_INSTANCE, id=8, material=3, baseMeshID=6, transform=colmajor(Mc)),
+    ]
+    sc.pointLights = [PointLight((5.0, 10.0, 7.0), (22000, 22000, 22000)), PointLight((-6.0, 9.0, 2.0), (12000, 11000, 10000))]
+    sc.cameras = [Camera(id=1, imageName="instances.png", width=width, height=height, numSamples=samples,
+                         position=(0.5, 4.5, 12.0), gazePoint=(0.0, 1.2, 0.0), up=(0, 1, 0),
+                         nearDistance=1.0, fovy=45.0, isLookAt=True)]
+    path = os.path.join(out_dir, "instances.rtscene")
+    write_rtscene(sc, path)
+    return path
+
+
+CONFIGS = {"c1": config_c1, "instances": config_instances, "c2": config_c2, "c3": config_c3, "c4": config_c4, "c5": config_c5}
 
 if __name__ == "__main__":
     import argparse

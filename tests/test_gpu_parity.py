@@ -16,6 +16,9 @@ CASES = {
     "c5s": dict(fn=scenegen.config_c5, kw=dict(n=64, width=320, height=180, samples=4, meshes=4)),
     # SURVEY.md 8f row 3, beyond BASELINE.json's configs: thin-lens camera (fast kernel, 5 draws per sample),
     # glossy materials (general kernel: draws inside the recursion), both
+    # the object kinds BASELINE.json's configs leave out: infinite plane, MeshInstances sharing a BLAS (material
+    # override, mirrored transform, instance of an instance), depth 3
+    "instances": dict(fn=scenegen.config_instances, kw=dict()),
     # 64 and 36 spp: units of one pixel (32 divides n*n) and of a whole tile (neither divides the other)
     "c1x64": dict(fn=scenegen.config_c1, kw=dict(width=96, height=80, samples=64)),
     "c1x36": dict(fn=scenegen.config_c1, kw=dict(width=96, height=80, samples=36)),
@@ -47,7 +50,7 @@ def test_parity_vs_oracle(name, scene_dir):
 
 
 @pytest.mark.parametrize("variant", [1, 2])
-@pytest.mark.parametrize("name", ["c1", "c3", "c5s"])
+@pytest.mark.parametrize("name", ["c1", "c3", "c5s", "instances"])
 def test_kernel_variants_vs_oracle(name, variant, scene_dir):
     """Every kernel variant (fast: sample lanes + warp packets; general: pixel lanes, per-lane traversal) meets the parity bars, and the
     variants agree with each other except at hit-distance ties."""

@@ -90,6 +90,7 @@ def test_no_gpu_means_a_loud_failure_not_a_fallback(scene_dir):
     ("config_c2", dict(n=30, width=32, height=32)),
     ("config_c3", dict(width=32, height=32, ico_level=1)),
     ("config_c5", dict(n=16, width=32, height=18, meshes=3)),
+    ("config_instances", dict(width=32, height=24)),       # plane, MeshInstances (override, mirrored, nested)
 ])
 def test_flat_context_equals_oracle_context(name, kw, scene_dir):
     """host/rt_context.cpp and oracle/rtcontext_init.hpp restate RTContext.swift:94-418 independently (product vs
