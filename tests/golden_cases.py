@@ -6,4 +6,8 @@ GOLDEN_CASES = {
     "c2_small": (scenegen.config_c2, dict(n=40, width=96, height=96, samples=1)),
     "c3_small": (scenegen.config_c3, dict(width=64, height=64, samples=4, depth=4, ico_level=1)),
     "c5_small": (scenegen.config_c5, dict(n=24, width=96, height=54, samples=4, meshes=3)),
+    # beyond BASELINE.json's configs: plane + MeshInstances; glossy materials + thin-lens camera
+    "instances_small": (scenegen.config_instances, dict(width=64, height=48, samples=4)),
+    "c3_glossy_dof_small": (scenegen.config_c3, dict(width=48, height=48, samples=4, depth=3, ico_level=1, roughness=0.2,
+                                                     aperture=0.2, focus=14.0)),
 }
