@@ -134,7 +134,12 @@ def load():
     if not os.path.exists(LIB_PATH):
         raise RuntimeError(f"{LIB_PATH} is missing: build it with `make -C myraytracer_b200/csrc` "
                            "(or __graft_entry__.build()); there is no CPU fallback")
-    L = C.CDLL(LIB_PATH)
+    _lib = declare(C.CDLL(LIB_PATH))
+    return _lib
+
+
+def declare(L):
+    """Set the prototypes of every C-ABI entry point on a loaded library object."""
     vp = C.c_void_p
     L.rt_abi_version.restype = C.c_int32
     L.rt_device_count.restype = C.c_int32
@@ -170,5 +175,4 @@ def load():
     L.rth_context_destroy.argtypes = [vp]
     L.rth_context_destroy.restype = None
     L.rth_context_describe.argtypes = [vp, C.POINTER(rt_scene_desc)]
-    _lib = L
     return L

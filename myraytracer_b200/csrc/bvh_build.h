@@ -39,6 +39,9 @@ struct BlasBuildOutput {
 void buildBlas(const BlasBuildInput& in, BlasBuildOutput& out);
 
 #if defined(__CUDACC__) || defined(RT_WITH_CUDA_RUNTIME)
+}  // namespace rtg
+#include <cuda_runtime.h>
+namespace rtg {
 // Device-side construction of the same output (bvh_build_gpu.cu): Morton order + binary radix tree, leaves of <= 2
 // triangles.  dVerts: the scene's triangle vertices (9 doubles each) on the current device.  The caller checks
 // out.maxDepth against its traversal stack (a radix tree over clustered keys can be deep) and may fall back to buildBlas.

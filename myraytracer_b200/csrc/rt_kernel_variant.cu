@@ -20,8 +20,8 @@ namespace rtg {
 
 cudaError_t RT_NAME(launchVariant)(const DeviceScene& S, const CameraParams& cam, const RenderTargets& out, int blocks,
                                    bool counters, cudaStream_t stream) {
-    if (counters) RT_KERNEL<true><<<blocks, RT_THREADS, 0, stream>>>(S, cam, out);
-    else RT_KERNEL<false><<<blocks, RT_THREADS, 0, stream>>>(S, cam, out);
+    if (counters) RT_LAUNCH(RT_KERNEL<true>, blocks, RT_THREADS, stream, S, cam, out);
+    else RT_LAUNCH(RT_KERNEL<false>, blocks, RT_THREADS, stream, S, cam, out);
     return cudaGetLastError();
 }
 

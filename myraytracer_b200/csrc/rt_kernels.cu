@@ -112,8 +112,8 @@ size_t scheduleWorkBytes(int nTiles) {
 
 cudaError_t launchSchedule(unsigned* tileCost, int* tileOrder, unsigned* work, int nTiles, cudaStream_t stream) {
     const int blocks = (nTiles + RT_SCHED_THREADS - 1) / RT_SCHED_THREADS;
-    scheduleCount<<<blocks, RT_SCHED_THREADS, 0, stream>>>(tileCost, work, nTiles);
-    scheduleScatter<<<blocks, RT_SCHED_THREADS, 0, stream>>>(tileCost, tileOrder, work, nTiles);
+    RT_LAUNCH(scheduleCount, blocks, RT_SCHED_THREADS, stream, tileCost, work, nTiles);
+    RT_LAUNCH(scheduleScatter, blocks, RT_SCHED_THREADS, stream, tileCost, tileOrder, work, nTiles);
     return cudaGetLastError();
 }
 

@@ -29,6 +29,14 @@ struct RenderTargets {
 
 static const int kPathFields = 11;
 
+// Kernel launch.  RT_EMU: the host emulation build of tests/emu (test infrastructure only, never part of
+// librtcuda.so) runs the same kernel body on fibers.
+#ifdef RT_EMU
+#define RT_LAUNCH(kernel, grid, block, stream, ...) rtemu::launch(dim3((unsigned)(grid)), dim3((unsigned)(block)), [&]() { kernel(__VA_ARGS__); })
+#else
+#define RT_LAUNCH(kernel, grid, block, stream, ...) kernel<<<(grid), (block), 0, (stream)>>>(__VA_ARGS__)
+#endif
+
 #ifndef RT_BLOCK
 #define RT_BLOCK 128
 #endif

@@ -23,6 +23,7 @@ namespace rtg {
 
 // Packet stack entries through 32-bit shared-window addresses: the stack pointer IS the address, so the loop
 // never rebuilds the shared base (three uniform-datapath instructions per push and per pop otherwise).
+#ifndef RT_EMU
 __device__ __forceinline__ void stsPair(uint32_t addr, int a, int b) {
     asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr), "r"(a), "r"(b) : "memory");
 }
@@ -31,6 +32,12 @@ __device__ __forceinline__ int2 ldsPair(uint32_t addr) {
     asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr) : "memory");
     return v;
 }
+#else   // host emulation of the kernels (tests/emu, test infrastructure only): the shared window starts at an anchor
+__device__ __forceinline__ void stsPair(uint32_t addr, int a, int b) {
+    *reinterpret_cast<int2*>(rtemu::g_sharedBase + (intptr_t)(int32_t)addr) = make_int2(a, b);
+}
+__device__ __forceinline__ int2 ldsPair(uint32_t addr) { return *reinterpret_cast<int2*>(rtemu::g_sharedBase + (intptr_t)(int32_t)addr); }
+#endif
 #ifndef RT_WSTACK
 #define RT_WSTACK 64    // BLAS entries per warp (tree depth is checked against RT_STACK at build time)
 #endif

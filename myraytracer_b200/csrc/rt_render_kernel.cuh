@@ -390,24 +390,26 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_GEN_BLOCKS) renderKernelGeneral(D
         int x0, y0;
         tiles.origin(tile, x0, y0);
         const int i = x0 + (lane & 7), j = y0 + (lane >> 3);
-        if (i >= W || j >= H) continue;
-
-        PCG32 rng;
-        rng.seed((((uint64_t)j << 32) ^ (uint64_t)i) + 0x9E3779B97F4A7C15ULL);  // :294 (Swift precedence)
-        V3 pixel = mk(0, 0, 0);
-        int sampleIndex = 0;
-        for (int sy = 0; sy < n && sampleIndex < samples; sy++) {
-            for (int sx = 0; sx < n && sampleIndex < samples; sx++) {
-                const PrimaryRay pr = primaryRay(cam, i, j, sx, sy, rng);
-                R.primary++;
-                HitId* idSlot = out.ids ? out.ids + (((size_t)j * W + i) * (size_t)(n * n) + (size_t)(sy * n + sx)) : nullptr;
-                PathEntry cur0;
-                cur0.o = pr.o; cur0.d = pr.d; cur0.w = mk(1, 1, 1); cur0.beerMat = 0; cur0.depth = 0; cur0.beer = 0;
-                pixel = pixel + scalarPathLoop<true, COUNT>(S, T, cur0, 0, true, pr.tMin, idSlot, rng, C, R, mk(0, 0, 0));
-                sampleIndex++;
+        // lanes outside the image idle until the warp's barrier below (no `continue`: the full-mask shuffle at the
+        // top of the loop must be reached by all 32 lanes together)
+        if (i < W && j < H) {
+            PCG32 rng;
+            rng.seed((((uint64_t)j << 32) ^ (uint64_t)i) + 0x9E3779B97F4A7C15ULL);  // :294 (Swift precedence)
+            V3 pixel = mk(0, 0, 0);
+            int sampleIndex = 0;
+            for (int sy = 0; sy < n && sampleIndex < samples; sy++) {
+                for (int sx = 0; sx < n && sampleIndex < samples; sx++) {
+                    const PrimaryRay pr = primaryRay(cam, i, j, sx, sy, rng);
+                    R.primary++;
+                    HitId* idSlot = out.ids ? out.ids + (((size_t)j * W + i) * (size_t)(n * n) + (size_t)(sy * n + sx)) : nullptr;
+                    PathEntry cur0;
+                    cur0.o = pr.o; cur0.d = pr.d; cur0.w = mk(1, 1, 1); cur0.beerMat = 0; cur0.depth = 0; cur0.beer = 0;
+                    pixel = pixel + scalarPathLoop<true, COUNT>(S, T, cur0, 0, true, pr.tMin, idSlot, rng, C, R, mk(0, 0, 0));
+                    sampleIndex++;
+                }
             }
+            writePixel(out, (size_t)j * W + i, pixel / (double)samples);                                   // :354
         }
-        writePixel(out, (size_t)j * W + i, pixel / (double)samples);                                   // :354
         __syncwarp();
         if (out.tileCost && lane == 0) atomicAdd(out.tileCost + tile, ((unsigned)clock() - c0) >> 6);
     }

@@ -102,12 +102,17 @@ __device__ __forceinline__ bool traceScene(const DeviceScene& S, V3 o, V3 d, dou
 // 11.25 -> 8.3 ms.  The hit record travels in registers (by reference it would live in local memory and cost the
 // big-mesh scene C5 4 %).  The general kernel keeps the inlined walk: its lanes' rays are coherent and it has the
 // registers.
+#ifdef RT_EMU
+#define RT_NOINLINE __attribute__((noinline))
+#else
+#define RT_NOINLINE __noinline__
+#endif
 struct TraceOut {
     HitRec hit;
     bool occluded;
 };
 template <bool COUNT>
-__device__ __noinline__ TraceOut traceSceneCall(const DeviceScene& S, V3 o, V3 d, double tMin, HitRec hit, bool anyhit,
+__device__ RT_NOINLINE TraceOut traceSceneCall(const DeviceScene& S, V3 o, V3 d, double tMin, HitRec hit, bool anyhit,
                                                 int32_t* sstack, int sstackN, Counters* counters) {
     Counters C;
     C.box = C.tri = C.sphere = C.plane = C.inst = C.smooth = 0; C.maxStack = 0;

@@ -1,0 +1,93 @@
+"""Kernel logic on the CPU: the product's CUDA sources compiled for the host against the SIMT emulation shim
+(tests/emu: every CUDA thread a fiber, the lanes of a warp meeting at each *_sync intrinsic) and compared with the
+oracle through the same C ABI and the same parity bars as tests/test_gpu_parity.py, on scenes small enough for
+seconds.  This checks what a container without a GPU can check — arithmetic, control flow, warp-collective
+protocol, work distribution, the tile schedule kernels — and is test infrastructure only: the emulation library is
+never loaded by myraytracer_b200 (tests/emu_lib.py).  The -m gpu tests remain the parity tests proper."""
+import numpy as np
+import pytest
+
+import emu_lib
+import oracle_lib
+import parity
+from myraytracer_b200 import RayTracerEngine, scenegen
+
+
+@pytest.fixture()
+def emu():
+    with emu_lib.use_emulator() as lib:
+        yield lib
+
+
+CASES = {
+    # name: (generator, kwargs, kernel variants to run: 1 fast (warp packets), 2 general)
+    "c1": (scenegen.config_c1, dict(width=72, height=56, samples=1), (1, 2)),
+    "c1x4_ragged": (scenegen.config_c1, dict(width=50, height=37, samples=4), (1, 2)),      # image not a multiple of 8x4
+    "c1x9": (scenegen.config_c1, dict(width=40, height=32, samples=9), (1, 2)),             # whole-tile units
+    "c1x64": (scenegen.config_c1, dict(width=24, height=16, samples=64), (1,)),             # one-pixel units
+    "c2": (scenegen.config_c2, dict(n=24, width=64, height=48), (1, 2)),
+    "c3": (scenegen.config_c3, dict(width=64, height=48, samples=4, depth=4, ico_level=2), (1, 2)),
+    "c3dof": (scenegen.config_c3, dict(width=48, height=40, samples=4, depth=3, ico_level=2, aperture=0.35, focus=13.0), (1, 2)),
+    "c3glossy": (scenegen.config_c3, dict(width=48, height=40, samples=4, depth=3, ico_level=2, roughness=0.12), (2,)),
+    "c5": (scenegen.config_c5, dict(n=12, width=64, height=40, samples=4, meshes=3), (1, 2)),
+    "instances": (scenegen.config_instances, dict(width=64, height=48, samples=4), (1, 2)),
+}
+
+
+def check(got, ref):
+    rep = parity.compare(got, ref)
+    assert rep["alpha_ok"]
+    assert rep["id_agree"] >= 0.9999 and rep["id_bad"] == 0, rep
+    assert rep["px_within_1"] >= 0.999, rep
+    assert rep["rays_gpu"][0] == rep["rays_ref"][0], rep
+    for a, b in zip(rep["rays_gpu"][1:], rep["rays_ref"][1:]):
+        assert abs(a - b) <= max(4, 1e-4 * b), rep
+    return rep
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_emulated_kernels_vs_oracle(name, scene_dir, emu):
+    fn, kw, variants = CASES[name]
+    path = fn(scene_dir, **kw)
+    eng = RayTracerEngine(path)
+    assert eng.ready, eng.load_error
+    ref = oracle_lib.OracleScene(path).render(want_ids=True, want_linear=True)
+    before = emu.rtemu_kernel_launches()
+    for variant in variants:
+        got = eng.render(0, want_ids=True, want_linear=True, variant=variant, counters=(variant == 2))
+        rep = check(got, ref)
+        print(name, variant, rep)
+    assert emu.rtemu_kernel_launches() > before       # the kernels ran (on fibers), not some other path
+
+
+def test_emulated_shards_and_schedule(scene_dir, emu):
+    """Both shard rules partition the frame bit-identically; the learnt tile order does not change it."""
+    from myraytracer_b200.distributed import owned_mask
+    path = scenegen.config_c3(scene_dir, width=72, height=52, samples=4, depth=3, ico_level=2)
+    eng = RayTracerEngine(path)
+    full = eng.render(0, schedule=1)
+    for mode in ("rows", "tiles"):
+        acc = np.zeros_like(full.rgba)
+        for k in range(3):
+            part = eng.render(0, shard_index=k, shard_count=3, shard_mode=1 if mode == "tiles" else 0).rgba
+            own = owned_mask(52, 72, k, 3, mode)
+            assert (part[~own] == 0).all()
+            acc[own] = part[own]
+        assert np.array_equal(acc, full.rgba)
+    for variant in (1, 2):
+        first = eng.render(0, variant=variant)
+        assert first.stats["tilesScheduled"] == 0
+        again = eng.render(0, variant=variant)
+        n_tiles = 9 * 7 * 2
+        assert again.stats["tilesScheduled"] == n_tiles and again.stats["kernelLaunches"] == 3
+        assert sorted(eng.schedule().tolist()) == list(range(n_tiles))
+        assert np.array_equal(first.rgba, full.rgba) and np.array_equal(again.rgba, full.rgba)
+
+
+def test_emulator_is_not_the_product(emu):
+    """The product loader never hands out the emulation library, and the emulation build says what it is."""
+    import os
+    from myraytracer_b200 import capi
+    assert os.path.basename(capi.LIB_PATH) == "librtcuda.so"
+    assert "emu" not in capi.LIB_PATH
+    assert hasattr(emu, "rtemu_kernel_launches")
