@@ -89,6 +89,7 @@ struct GMaterial {
 };
 
 struct GPointLight { double position[3], intensity[3]; };
+struct GAreaLight { double position[3], normal[3], size, radiance[3]; };   // Object+Extension.swift:145-186
 
 // Everything the kernels read, passed by value as a kernel parameter.
 struct DeviceScene {
@@ -102,10 +103,12 @@ struct DeviceScene {
     const GInstance* instances;
     const GMaterial* materials;
     const GPointLight* pointLights;
+    const GAreaLight* areaLights;
+    const double* jitter;          // area lights: the 10x10 stratified table, xs[100] then ys[100] (:92-93,646-659)
     int32_t tlasRootRef;
     int32_t nInstances, nMaterials, nPointLights;
     int32_t maxDepth;
-    int32_t pad;
+    int32_t nAreaLights;
     double ambient[3], background[3];
     double eps, shadowEps;
     double tlasLo[3], tlasHi[3], tlasCentre[3];   // exact world bounds of all instances and their centre

@@ -67,6 +67,8 @@ struct rt_scene {
     // device allocations
     GNode* dNodes = nullptr; GTri* dTris = nullptr; GTriD* dTrisD = nullptr; double* dNormals = nullptr;
     GNode* dTlas = nullptr; GInstance* dInst = nullptr; GMaterial* dMat = nullptr; GPointLight* dLights = nullptr;
+    GAreaLight* dAreaLights = nullptr; double* dJitter = nullptr;
+    unsigned* dAreaIndex = nullptr; size_t areaIndexBytes = 0;   // per-pixel jitter index of an area-light frame
     // render state (re-used across calls)
     int* dTileCounter = nullptr; unsigned long long* dCounters = nullptr;
     // tile schedule learnt from the previous frame of the same geometry (rt_kernels.cu: scheduleKernel)
@@ -106,8 +108,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     if (!d) return fail(RT_ERR_INVALID, "null scene description");
     if (d->abiVersion != RT_ABI_VERSION) return fail(RT_ERR_INVALID, "rt_scene_desc.abiVersion mismatch");
     if (d->nMaterials < 1 || !d->materials) return fail(RT_ERR_INVALID, "at least one material is required");
-    if (d->nAreaLights > 0)
-        return fail(RT_ERR_UNSUPPORTED, "area lights are not implemented on the GPU path yet (SURVEY.md §8f row 3)");
+    if (d->nAreaLights < 0 || (d->nAreaLights > 0 && !d->areaLights)) return fail(RT_ERR_INVALID, "area light array missing");
     if (d->triMotionBlur)
         for (int64_t i = 0; i < d->nTriangles * 3; i++)
             if (d->triMotionBlur[i] != 0.0) return fail(RT_ERR_UNSUPPORTED, "motion blur is not implemented on the GPU path yet");
@@ -260,6 +261,33 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
         std::memcpy(lights[i].position, d->pointLights[i].position, 24);
         std::memcpy(lights[i].intensity, d->pointLights[i].intensity, 24);
     }
+    // area lights (:145-186) and the 10x10 stratified jitter table every frame rebuilds from a fixed seed (:92-93,646-659)
+    std::vector<GAreaLight> areaLights((size_t)d->nAreaLights);
+    for (int64_t i = 0; i < d->nAreaLights; i++) {
+        std::memcpy(areaLights[i].position, d->areaLights[i].position, 24);
+        std::memcpy(areaLights[i].normal, d->areaLights[i].normal, 24);
+        areaLights[i].size = d->areaLights[i].size;
+        std::memcpy(areaLights[i].radiance, d->areaLights[i].radiance, 24);
+    }
+    std::vector<double> jitter;
+    if (d->nAreaLights > 0) {
+        jitter.resize(200);
+        // PCG32(seed:) of the reference (:556-589): state = 0, inc = (seed << 1) | 1, next, state += golden, next
+        uint64_t state = 0, inc = (0x123456789ABCDEFULL << 1) | 1;
+        auto next = [&]() -> uint32_t {
+            const uint64_t old = state;
+            state = old * 6364136223846793005ULL + inc;
+            const uint32_t xs = (uint32_t)(((old >> 18) ^ old) >> 27), rot = (uint32_t)(old >> 59);
+            return (xs >> rot) | (xs << ((~rot + 1u) & 31u));
+        };
+        next(); state += 0x9E3779B97F4A7C15ULL; next();
+        int k = 0;
+        for (int gy = 0; gy < 10; gy++)
+            for (int gx = 0; gx < 10; gx++, k++) {
+                jitter[k] = (double)gx + (double)next() * 2.3283064365386963e-10;
+                jitter[100 + k] = (double)gy + (double)next() * 2.3283064365386963e-10;
+            }
+    }
     std::vector<double> normals;
     if (d->nTriangles > 0) {
         if (!d->triVertices || !d->triNormals) return fail(RT_ERR_INVALID, "triangle arrays missing");
@@ -306,6 +334,8 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     if ((rc = upload(inst, &sc->dInst, bytes))) return rc;
     if ((rc = upload(mats, &sc->dMat, bytes))) return rc;
     if ((rc = upload(lights, &sc->dLights, bytes))) return rc;
+    if ((rc = upload(areaLights, &sc->dAreaLights, bytes))) return rc;
+    if ((rc = upload(jitter, &sc->dJitter, bytes))) return rc;
     // ray / test counters (16 x u64) and the work counter behind them: one allocation, one memset per frame
     CK(cudaMalloc((void**)&sc->dCounters, kFrameStateBytes));
     sc->dTileCounter = reinterpret_cast<int*>(sc->dCounters + 16);
@@ -323,6 +353,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     S.tlasRootRef = tl.rootRef;
     std::memcpy(S.tlasLo, sLo, 24); std::memcpy(S.tlasHi, sHi, 24); std::memcpy(S.tlasCentre, sC, 24);
     S.nInstances = (int32_t)d->nInstances; S.nMaterials = (int32_t)d->nMaterials; S.nPointLights = (int32_t)d->nPointLights;
+    S.areaLights = sc->dAreaLights; S.jitter = sc->dJitter; S.nAreaLights = (int32_t)d->nAreaLights;
     S.maxDepth = d->maxRecursionDepth;
     std::memcpy(S.ambient, d->ambient, 24); std::memcpy(S.background, d->background, 24);
     S.eps = d->intersectionTestEpsilon; S.shadowEps = d->shadowRayEpsilon;
@@ -348,6 +379,7 @@ void rt_scene_destroy(rt_scene_t* sc) {
     cudaSetDevice(sc->device);
     cudaFree(sc->dNodes); cudaFree(sc->dTris); cudaFree(sc->dTrisD); cudaFree(sc->dNormals); cudaFree(sc->dTlas);
     cudaFree(sc->dInst); cudaFree(sc->dMat); cudaFree(sc->dLights); cudaFree(sc->dCounters);
+    cudaFree(sc->dAreaLights); cudaFree(sc->dJitter); cudaFree(sc->dAreaIndex);
     cudaFree(sc->dTileCost); cudaFree(sc->dTileOrder); cudaFree(sc->dSchedWork);
     cudaFree(sc->dPathStack); cudaFree(sc->dRgba); cudaFree(sc->dLinear); cudaFree(sc->dIds);
     if (sc->hCounters) cudaFreeHost(sc->hCounters);

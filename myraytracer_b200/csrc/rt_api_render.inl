@@ -92,13 +92,19 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     int rc = buildCamera(camera, params, cp);
     if (rc) return rc;
     const bool counters = params && params->collectCounters;
-    int variant = sc->glossy ? KV_GENERAL : KV_FAST;
+    const bool area = sc->ds.nAreaLights > 0;
+    int variant = (sc->glossy || area) ? KV_GENERAL : KV_FAST;
     if (params && params->kernelVariant != 0) {
         if (params->kernelVariant < 1 || params->kernelVariant > KV_COUNT) return fail(RT_ERR_INVALID, "kernelVariant outside 0..2");
         variant = params->kernelVariant - 1;
         if (sc->glossy && variant == KV_FAST)
             return fail(RT_ERR_UNSUPPORTED, "the fast kernel needs roughness == 0 on every material (RNG skip-ahead)");
+        if (area && variant == KV_FAST)
+            return fail(RT_ERR_UNSUPPORTED, "the fast kernel does not carry the area lights' per-chunk jitter index");
     }
+    // the area lights' jitter index runs through a whole 8-row chunk (Object+Extension.swift:288): chunks stay whole
+    if (area && cp.shardCount > 1 && cp.shardTiles)
+        return fail(RT_ERR_UNSUPPORTED, "scenes with area lights shard by 8-row chunks only (RT_SHARD_ROWS)");
     const int blocks = sc->blocks[variant][counters ? 1 : 0];
     cudaStream_t st = (cudaStream_t)cudaStream;
 
@@ -147,6 +153,17 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     if (sc->sideBusy) CK(cudaStreamWaitEvent(st, sc->evSide, 0));
     CK(cudaEventRecord(sc->evStart, st));
     CK(cudaMemsetAsync(sc->dCounters, 0, kFrameStateBytes, st));
+    if (area) {
+        // pass 1 follows every path and counts its jitter-table draws per pixel; the prefix kernel turns the counts
+        // into each pixel's first index within its chunk; pass 2 (below) is the frame
+        if ((rc = ensure(&sc->dAreaIndex, &sc->areaIndexBytes, (size_t)cp.width * cp.height * sizeof(unsigned)))) return rc;
+        rt.areaIndex = sc->dAreaIndex;
+        rt.areaPass = 1;
+        CK(launchRender(variant, sc->ds, cp, rt, blocks, counters, st));
+        CK(launchAreaPrefix(sc->dAreaIndex, cp.width, cp.height, cp.shardIndex, cp.shardCount, st));
+        CK(cudaMemsetAsync(sc->dTileCounter, 0, sizeof(int), st));
+        rt.areaPass = 2;
+    }
     CK(launchRender(variant, sc->ds, cp, rt, blocks, counters, st));
     CK(cudaEventRecord(sc->evStop, st));
     CK(cudaStreamWaitEvent(sc->side, sc->evStop, 0));
@@ -158,7 +175,7 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     CK(cudaEventRecord(sc->evSide, sc->side));
     sc->sideBusy = true;
     sc->pending = true; sc->pendingCounters = counters; sc->pendingStream = st;
-    sc->launches = adaptive ? 3 : 1;
+    sc->launches = (adaptive ? 3 : 1) + (area ? 2 : 0);
     return RT_OK;
 }
 

@@ -9,25 +9,33 @@
 namespace rtg {
 
 #if RT_V_FAST
-#define RT_KERNEL renderKernelFast
+#define RT_KERNEL(c) renderKernelFast<c>
 #define RT_NAME(x) x##Fast
 #define RT_THREADS RT_FAST_BLOCK
 #else
-#define RT_KERNEL renderKernelGeneral
+#define RT_KERNEL(c) renderKernelGeneral<c, false>
+#define RT_KERNEL_AREA(c) renderKernelGeneral<c, true>
 #define RT_NAME(x) x##General
 #define RT_THREADS RT_BLOCK
 #endif
 
 cudaError_t RT_NAME(launchVariant)(const DeviceScene& S, const CameraParams& cam, const RenderTargets& out, int blocks,
                                    bool counters, cudaStream_t stream) {
-    if (counters) RT_LAUNCH(RT_KERNEL<true>, blocks, RT_THREADS, stream, S, cam, out);
-    else RT_LAUNCH(RT_KERNEL<false>, blocks, RT_THREADS, stream, S, cam, out);
+#ifdef RT_KERNEL_AREA
+    if (out.areaPass != 0) {       // scene with area lights: same kernel, index bookkeeping compiled in
+        if (counters) RT_LAUNCH(RT_KERNEL_AREA(true), blocks, RT_THREADS, stream, S, cam, out);
+        else RT_LAUNCH(RT_KERNEL_AREA(false), blocks, RT_THREADS, stream, S, cam, out);
+        return cudaGetLastError();
+    }
+#endif
+    if (counters) RT_LAUNCH(RT_KERNEL(true), blocks, RT_THREADS, stream, S, cam, out);
+    else RT_LAUNCH(RT_KERNEL(false), blocks, RT_THREADS, stream, S, cam, out);
     return cudaGetLastError();
 }
 
 cudaError_t RT_NAME(occupancyVariant)(int* blocksPerSm, bool counters) {
-    if (counters) return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocksPerSm, RT_KERNEL<true>, RT_THREADS, 0);
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocksPerSm, RT_KERNEL<false>, RT_THREADS, 0);
+    if (counters) return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocksPerSm, RT_KERNEL(true), RT_THREADS, 0);
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocksPerSm, RT_KERNEL(false), RT_THREADS, 0);
 }
 
 int RT_NAME(blockSizeVariant)() { return RT_THREADS; }

@@ -106,6 +106,42 @@ __global__ void __launch_bounds__(RT_SCHED_THREADS) scheduleScatter(unsigned* __
     }
 }
 
+// ---- area lights: per-pixel draw counts -> first jitter index of every pixel ------------------------------------
+// One block per 8-row chunk of this shard (the reference's task unit, Object+Extension.swift:75-82,288): exclusive
+// prefix sum of the chunk's pixels in row-major order — the order in which the reference's chunk task advances its
+// jitterIndex — kept mod 100 like every use of the index (:152-153).
+#define RT_AREA_THREADS 256
+__global__ void __launch_bounds__(RT_AREA_THREADS) areaPrefixKernel(unsigned* __restrict__ areaIndex, int width, int height,
+                                                                    int shardIndex, int shardCount) {
+    __shared__ unsigned part[RT_AREA_THREADS];
+    const int chunk = (int)blockIdx.x * shardCount + shardIndex;
+    const int row0 = chunk * 8;
+    const int rows = height - row0 < 8 ? height - row0 : 8;
+    const int n = rows * width;
+    unsigned* a = areaIndex + (size_t)row0 * width;
+    const int per = (n + RT_AREA_THREADS - 1) / RT_AREA_THREADS;
+    const int tid = threadIdx.x;
+    const int begin = tid * per, end = begin + per < n ? begin + per : n;
+    unsigned sum = 0;
+    for (int k = begin; k < end; k++) sum += a[k];
+    part[tid] = sum % 100u;
+    __syncthreads();
+    if (tid == 0) {                    // 256 partial sums: a serial scan is a fraction of a microsecond
+        unsigned run = 0;
+        for (int t = 0; t < RT_AREA_THREADS; t++) { const unsigned v = part[t]; part[t] = run; run = (run + v) % 100u; }
+    }
+    __syncthreads();
+    unsigned run = part[tid];
+    for (int k = begin; k < end; k++) { const unsigned v = a[k]; a[k] = run; run = (run + v) % 100u; }
+}
+
+cudaError_t launchAreaPrefix(unsigned* areaIndex, int width, int height, int shardIndex, int shardCount, cudaStream_t stream) {
+    const int nChunks = (height + 7) / 8;
+    const int mine = (nChunks - shardIndex + shardCount - 1) / shardCount;
+    if (mine > 0) RT_LAUNCH(areaPrefixKernel, mine, RT_AREA_THREADS, stream, areaIndex, width, height, shardIndex, shardCount);
+    return cudaGetLastError();
+}
+
 size_t scheduleWorkBytes(int nTiles) {
     return (size_t)((nTiles + RT_SCHED_THREADS - 1) / RT_SCHED_THREADS) * RT_SCHED_CLASSES * sizeof(unsigned);
 }

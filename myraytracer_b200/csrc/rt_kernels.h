@@ -22,6 +22,13 @@ struct RenderTargets {
     unsigned long long* counters;  // 16 x u64, zeroed before launch
     const int* tileOrder;          // schedule: slot -> tile of this shard (null = identity)
     unsigned* tileCost;            // per tile, clocks/64 spent on it this frame (null = not recorded); zeroed before launch
+    // Area lights (general kernel only).  The reference draws the light sample of every shading point from a 100-entry
+    // table through ONE index per 8-row chunk that counts up in pixel, sample and recursion order
+    // (Object+Extension.swift:152-154,288).  areaPass 1 walks the paths without shading and leaves each pixel's number
+    // of draws (mod 100) in areaIndex[pixel]; launchAreaPrefix turns them into each pixel's first index (exclusive
+    // prefix over the chunk, row-major); areaPass 2 renders with it.  areaPass 0: scene without area lights.
+    unsigned* areaIndex;           // W*H or null
+    int areaPass;
 #ifdef RT_WARPTIMES
     unsigned long long* warpTimes; // profiling build only: 4 x u64 per warp (start, first unit done, last draw, exit; ns)
 #endif
@@ -53,6 +60,8 @@ enum KernelVariant { KV_FAST = 0, KV_GENERAL = 1, KV_COUNT = 2 };
 cudaError_t launchRender(int variant, const DeviceScene& S, const CameraParams& cam, const RenderTargets& out, int blocks,
                          bool counters, cudaStream_t stream);
 // tileCost (clocks per tile of the frame just rendered) -> tileOrder for the next frame, longest first; clears tileCost
+// areaIndex: per-pixel draw counts -> per-pixel first jitter index, for the 8-row chunks of this shard (rows mode)
+cudaError_t launchAreaPrefix(unsigned* areaIndex, int width, int height, int shardIndex, int shardCount, cudaStream_t stream);
 cudaError_t launchSchedule(unsigned* tileCost, int* tileOrder, unsigned* work, int nTiles, cudaStream_t stream);
 size_t scheduleWorkBytes(int nTiles);   // scratch of launchSchedule
 int renderBlockSize(int variant);

@@ -360,7 +360,9 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFas
     flushCounters<COUNT>(out, C, R);
 }
 
-template <bool COUNT>
+// AREA: scenes with area lights (RenderTargets::areaIndex / areaPass): pass 1 leaves each pixel's number of
+// jitter-table draws, pass 2 starts each pixel at its index within the 8-row chunk.
+template <bool COUNT, bool AREA>
 __global__ void __launch_bounds__(RT_BLOCK, RT_GEN_BLOCKS) renderKernelGeneral(DeviceScene S, CameraParams cam, RenderTargets out) {
     __shared__ int32_t sstack[RT_SSTACK * RT_BLOCK];
     const int lane = threadIdx.x & 31;
@@ -397,22 +399,31 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_GEN_BLOCKS) renderKernelGeneral(D
             rng.seed((((uint64_t)j << 32) ^ (uint64_t)i) + 0x9E3779B97F4A7C15ULL);  // :294 (Swift precedence)
             V3 pixel = mk(0, 0, 0);
             int sampleIndex = 0;
+            AreaState area;
+            area.jitterIndex = 0; area.countOnly = false;
+            if (AREA) {
+                area.countOnly = out.areaPass == 1;
+                if (!area.countOnly) area.jitterIndex = out.areaIndex[(size_t)j * W + i];
+            }
             for (int sy = 0; sy < n && sampleIndex < samples; sy++) {
                 for (int sx = 0; sx < n && sampleIndex < samples; sx++) {
                     const PrimaryRay pr = primaryRay(cam, i, j, sx, sy, rng);
                     R.primary++;
-                    HitId* idSlot = out.ids ? out.ids + (((size_t)j * W + i) * (size_t)(n * n) + (size_t)(sy * n + sx)) : nullptr;
+                    HitId* idSlot = (out.ids && !area.countOnly) ? out.ids + (((size_t)j * W + i) * (size_t)(n * n) + (size_t)(sy * n + sx)) : nullptr;
                     PathEntry cur0;
                     cur0.o = pr.o; cur0.d = pr.d; cur0.w = mk(1, 1, 1); cur0.beerMat = 0; cur0.depth = 0; cur0.beer = 0;
-                    pixel = pixel + scalarPathLoop<true, COUNT>(S, T, cur0, 0, true, pr.tMin, idSlot, rng, C, R, mk(0, 0, 0));
+                    pixel = pixel + scalarPathLoop<true, COUNT, false, AREA>(S, T, cur0, 0, true, pr.tMin, idSlot, rng, C, R, mk(0, 0, 0),
+                                                                             AREA ? &area : nullptr);
                     sampleIndex++;
                 }
             }
-            writePixel(out, (size_t)j * W + i, pixel / (double)samples);                                   // :354
+            if (AREA && area.countOnly) out.areaIndex[(size_t)j * W + i] = area.jitterIndex;
+            else writePixel(out, (size_t)j * W + i, pixel / (double)samples);                              // :354
         }
         __syncwarp();
         if (out.tileCost && lane == 0) atomicAdd(out.tileCost + tile, ((unsigned)clock() - c0) >> 6);
     }
+    if (AREA && out.areaPass == 1) return;      // the counting pass reports no rays: pass 2 traces them all again
     flushCounters<COUNT>(out, C, R);
 }
 

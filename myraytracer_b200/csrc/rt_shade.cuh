@@ -147,6 +147,45 @@ __device__ __forceinline__ V3 pointLightTerm(const GMaterial& mat, const GPointL
     return (Ld + Ls) * atten;
 }
 
+// Area lights (:145-186).  The light sample comes from the 10x10 jitter table through the chunk-wide running index
+// (see RenderTargets::areaIndex); countOnly: the index is advanced and nothing else happens (pass 1).
+struct AreaState {
+    unsigned jitterIndex;     // kept mod 100: only `jitterIndex % 100` is ever used (:152-153)
+    bool countOnly;
+};
+
+// The sample point of one area light for jitter entry k, and everything of its contribution that does not need
+// the shadow ray: returns false when the light is behind the surface or edge-on (:166-171).
+__device__ __forceinline__ bool areaLightSample(const DeviceScene& S, const GAreaLight& al, unsigned k, V3 p, V3 N, V3& nL, V3& wi,
+                                                double& dist, double& dist2, double& NdotL, double& Ln) {
+    nL = normalize(ld3(al.normal));
+    V3 t, b;
+    orthonormalBasis(nL, t, b);
+    const double size = al.size;
+    const double r1 = S.jitter[k] / 10.0 - 0.5;
+    const double r2 = S.jitter[100 + k] / 10.0 - 0.5;
+    const V3 samplePos = (ld3(al.position) + t * (r1 * size)) + b * (r2 * size);
+    wi = samplePos - p;
+    dist2 = dot(wi, wi);
+    dist = sqrt(dist2);
+    wi = wi / dist;
+    NdotL = dot(N, wi);
+    if (NdotL <= 0) return false;
+    Ln = fabs(dot(nL, -wi));
+    if (Ln <= 0) return false;
+    return true;
+}
+__device__ __forceinline__ V3 areaLightTerm(const GMaterial& mat, const GAreaLight& al, V3 N, V3 rayDir, V3 wi, double dist2,
+                                            double NdotL, double Ln) {
+    const double area = al.size * al.size;
+    const V3 view = normalize(-rayDir);
+    const V3 h = normalize(wi + view);
+    const V3 Ld = ld3(mat.diffuse) * NdotL;
+    const V3 Ls = ld3(mat.specular) * pow(dmax(0.0, dot(N, h)), mat.phong);       // raw phong exponent (:179)
+    const V3 brdf = Ld + Ls;
+    return ((brdf * ld3(al.radiance)) * (Ln / dist2)) * area;
+}
+
 // Recursive branches of `trace` (:189-275): fills c1 (always) and c2 (refraction) and returns the child count.
 // GLOSSY = false compiles the roughness perturbations (and their RNG draws) out: the fast kernel runs only on
 // scenes where every roughness is 0, so its RNG state is dead after primary-ray generation.
@@ -222,10 +261,11 @@ __device__ __forceinline__ int spawnChildren(const DeviceScene& S, const ShadePo
 // camera ray (tMin = near-plane clip :341-344, hit id recorded).  Returns `color` plus the w * Lo of all
 // processed entries, added in processing order.
 // CALL: the traversal is the out-of-line traceSceneCall (fast kernel) instead of two inlined walks.
-template <bool GLOSSY, bool COUNT, bool CALL = false>
+// AREA: the scene has area lights; `area` carries the chunk's jitter index through the path (general kernel only).
+template <bool GLOSSY, bool COUNT, bool CALL = false, bool AREA = false>
 __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceScratch& T, PathEntry cur, int level,
                                              bool firstIsPrimary, double tMinPrimary, HitId* idSlot, PCG32& rng, Counters& C,
-                                             RayCounts& R, V3 color) {
+                                             RayCounts& R, V3 color, AreaState* area = nullptr) {
     const V3 ambient = ld3(S.ambient), background = ld3(S.background);
     bool primary = firstIsPrimary;
     for (;;) {
@@ -252,7 +292,8 @@ __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceSc
             ShadePoint sp;
             setupShade(S, sf, cur, hit.t, sp);
             V3 Lo = sp.computeDirect ? ambient * ld3(sp.mat->ambient) : mk(0, 0, 0);
-            if (sp.computeDirect) {
+            const bool shade = !(AREA && area->countOnly);      // pass 1 of an area-light frame only follows the paths
+            if (sp.computeDirect && shade) {
                 for (int l = 0; l < S.nPointLights; l++) {                             // :118-143
                     const GPointLight& pl = S.pointLights[l];
                     V3 so, wi;
@@ -265,6 +306,24 @@ __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceSc
                                                : traceScene<COUNT>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, C);
                     if (!occluded)
                         Lo = Lo + pointLightTerm(*sp.mat, pl, sp.N, cur.d, wi, dist);
+                }
+            }
+            if (AREA && sp.computeDirect) {
+                for (int l = 0; l < S.nAreaLights; l++) {                               // :145-186
+                    const unsigned k = area->jitterIndex;
+                    area->jitterIndex = k + 1 >= 100u ? 0u : k + 1;                     // jitterIndex &+= 1, kept mod 100
+                    if (!shade) continue;
+                    const GAreaLight& al = S.areaLights[l];
+                    V3 nL, wi;
+                    double dist, dist2, NdotL, Ln;
+                    if (!areaLightSample(S, al, k, sp.p, sp.N, nL, wi, dist, dist2, NdotL, Ln)) continue;
+                    HitRec sh;
+                    sh.t = dist - S.shadowEps; sh.u = sh.v = 0; sh.inst = -1; sh.slot = 0;   // tMax = dist - shadowEps (:173)
+                    R.shadow++;
+                    const V3 so = sp.p + wi * S.shadowEps;
+                    const bool occluded = CALL ? traceSceneCall<COUNT>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, COUNT ? &C : nullptr).occluded
+                                               : traceScene<COUNT>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, C);
+                    if (!occluded) Lo = Lo + areaLightTerm(*sp.mat, al, sp.N, cur.d, wi, dist2, NdotL, Ln);
                 }
             }
             if (finite3(Lo)) {                                                          // NaN guard, :277-280

@@ -10,4 +10,6 @@ GOLDEN_CASES = {
     "instances_small": (scenegen.config_instances, dict(width=64, height=48, samples=4)),
     "c3_glossy_dof_small": (scenegen.config_c3, dict(width=48, height=48, samples=4, depth=3, ico_level=1, roughness=0.2,
                                                      aperture=0.2, focus=14.0)),
+    # area lights: the per-chunk jitter index (Object+Extension.swift:145-186,288)
+    "c3_area_small": (scenegen.config_c3, dict(width=56, height=44, samples=4, depth=3, ico_level=1, area_lights=3)),
 }

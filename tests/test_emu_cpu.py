@@ -31,6 +31,10 @@ CASES = {
     "c3glossy": (scenegen.config_c3, dict(width=48, height=40, samples=4, depth=3, ico_level=2, roughness=0.12), (2,)),
     "c5": (scenegen.config_c5, dict(n=12, width=64, height=40, samples=4, meshes=3), (1, 2)),
     "instances": (scenegen.config_instances, dict(width=64, height=48, samples=4), (1, 2)),
+    # area lights: counting pass, per-chunk prefix, shading pass (general kernel); ragged image, glossy recursion
+    "c3area": (scenegen.config_c3, dict(width=64, height=48, samples=4, depth=3, ico_level=2, area_lights=2), (2,)),
+    "c3area_glossy_ragged": (scenegen.config_c3, dict(width=50, height=37, samples=1, depth=4, ico_level=2, area_lights=3,
+                                                      roughness=0.1), (2,)),
 }
 
 
@@ -82,6 +86,28 @@ def test_emulated_shards_and_schedule(scene_dir, emu):
         assert again.stats["tilesScheduled"] == n_tiles and again.stats["kernelLaunches"] == 3
         assert sorted(eng.schedule().tolist()) == list(range(n_tiles))
         assert np.array_equal(first.rgba, full.rgba) and np.array_equal(again.rgba, full.rgba)
+
+
+def test_emulated_area_lights_shard_by_chunks(scene_dir, emu):
+    """The jitter index of the area lights runs through an 8-row chunk (Object+Extension.swift:288): shards made of
+    whole chunks reproduce the frame bit for bit; tile shards and the fast kernel are refused, not approximated."""
+    from myraytracer_b200 import RenderError
+    from myraytracer_b200.distributed import owned_mask
+    path = scenegen.config_c3(scene_dir, width=40, height=44, samples=4, depth=2, ico_level=1, area_lights=2)
+    eng = RayTracerEngine(path)
+    full = eng.render(0, want_linear=True)
+    assert full.stats["kernelLaunches"] == 5             # count pass, prefix, frame, two schedule kernels
+    acc = np.zeros_like(full.linear)
+    for k in range(3):
+        part = eng.render(0, want_linear=True, shard_index=k, shard_count=3).linear
+        own = owned_mask(44, 40, k, 3, "rows")
+        acc[own] = part[own]
+    assert np.array_equal(acc, full.linear)
+    assert np.array_equal(eng.render(0, want_linear=True).linear, full.linear)       # learnt tile order: same frame
+    for kw in (dict(shard_index=0, shard_count=2, shard_mode=1), dict(variant=1)):
+        with pytest.raises(RenderError) as e:
+            eng.render(0, **kw)
+        assert e.value.code == -3
 
 
 def test_emulator_is_not_the_product(emu):

@@ -26,6 +26,10 @@ CASES = {
     "c3glossy": dict(fn=scenegen.config_c3, kw=dict(width=192, height=192, samples=4, roughness=0.12)),
     "c3glossydof": dict(fn=scenegen.config_c3, kw=dict(width=160, height=160, samples=9, depth=4, roughness=0.3,
                                                        aperture=0.2, focus=14.0)),
+    # area lights (8f row 3): light samples come from a 100-entry table through one running index per 8-row chunk —
+    # counting pass, per-chunk prefix sum, shading pass (general kernel)
+    "c3area": dict(fn=scenegen.config_c3, kw=dict(width=192, height=180, samples=4, area_lights=2)),
+    "c3areaglossy": dict(fn=scenegen.config_c3, kw=dict(width=150, height=117, samples=9, depth=4, roughness=0.2, area_lights=3)),
 }
 
 
@@ -72,7 +76,7 @@ def test_kernel_variants_vs_oracle(name, variant, scene_dir):
     assert same >= 0.9999, same
 
 
-@pytest.mark.parametrize("name", ["c1_small", "c2_small", "c3_small", "c5_small"])
+@pytest.mark.parametrize("name", ["c1_small", "c2_small", "c3_small", "c5_small", "c3_area_small"])
 def test_gpu_matches_committed_golden(name, scene_dir):
     """CUDA path vs the frozen oracle renders under tests/golden/ (tools/make_golden.py)."""
     import os
