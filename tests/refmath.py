@@ -148,3 +148,74 @@ def fresnel_conductor(eta, k, cos_i):
     rs = (e - t + c2) / (e + t + c2)
     rp = ((e * c2) - t + 1.0) / ((e * c2) + t + 1.0)
     return 0.5 * (rs + rp)
+
+
+# ---------------------------------------------------------------------------------- area lights (:145-186)
+def jitter_table():
+    """buildStratifiedJitter, :646-659, from PCG32(seed: 0x123456789ABCDEF) (:92-93)."""
+    rng = PCG32(0x123456789ABCDEF)
+    xs, ys = [], []
+    for gy in range(10):
+        for gx in range(10):
+            xs.append(float(gx) + rng.next_float())
+            ys.append(float(gy) + rng.next_float())
+    return xs, ys
+
+
+def orthonormal_basis(n):
+    """:530-552."""
+    sign = 1.0 if n[2] >= 0 else -1.0
+    a = -1.0 / (sign + n[2])
+    b = n[0] * n[1] * a
+    t = _norm(np.array([1.0 + sign * n[0] * n[0] * a, sign * b, -sign * n[0]]))
+    bt = _norm(np.array([b, sign + n[1] * n[1] * a, -n[1]]))
+    return t, bt
+
+
+def mt_single(o, d, v0, v1, v2, eps):
+    """One Moeller-Trumbore test (RTContext.swift:479-494) -> (t, u, v) or None; the caller applies the t window."""
+    e1, e2 = v1 - v0, v2 - v0
+    pvec = np.cross(d, e2)
+    det = _dot(e1, pvec)
+    if abs(det) < eps:
+        return None
+    inv = 1.0 / det
+    tvec = o - v0
+    u = _dot(tvec, pvec) * inv
+    if u < 0 or u > 1:
+        return None
+    q = np.cross(tvec, e1)
+    v = _dot(d, q) * inv
+    if v < 0 or u + v > 1:
+        return None
+    return _dot(e2, q) * inv, u, v
+
+
+def area_light_sample(light: dict, k: int, xs, ys, p, N):
+    """:146-171 for jitter entry k: (nL, wi, dist, dist2, NdotL, Ln), or None when the sample does not face p."""
+    nL = _norm(np.asarray(light["normal"], np.float64))
+    t, b = orthonormal_basis(nL)
+    size = light["size"]
+    r1 = xs[k % 100] / 10.0 - 0.5
+    r2 = ys[k % 100] / 10.0 - 0.5
+    sample = (np.asarray(light["position"], np.float64) + t * (r1 * size)) + b * (r2 * size)
+    wi = sample - p
+    dist2 = _dot(wi, wi)
+    dist = math.sqrt(dist2)
+    wi = wi / dist
+    n_dot_l = _dot(N, wi)
+    if n_dot_l <= 0:
+        return None
+    ln = abs(_dot(nL, -wi))
+    if ln <= 0:
+        return None
+    return nL, wi, dist, dist2, n_dot_l, ln
+
+
+def area_light_term(light: dict, mat: dict, N, ray_dir, wi, dist2, n_dot_l, ln):
+    """:175-185: (diffuse*NdotL + specular*pow(max(0, N.h), phong)) * radiance * (Ln / dist2) * size^2."""
+    view = _norm(-ray_dir)
+    h = _norm(wi + view)
+    ld = np.asarray(mat["diffuse"], np.float64) * n_dot_l
+    ls = np.asarray(mat["specular"], np.float64) * math.pow(max(0.0, _dot(N, h)), mat["phong"])
+    return (((ld + ls) * np.asarray(light["radiance"], np.float64)) * (ln / dist2)) * (light["size"] * light["size"])
