@@ -40,6 +40,9 @@ BENCH_CONFIGS = {
     "c3": ("config_c3", {}, "C3: mirror/dielectric/conductor recursion depth 6, 1024x1024, 4 spp"),
     "c1": ("config_c1", {}, "C1: spheres + triangles, 2 point lights, 800x800, 1 spp"),
     "c5": ("config_c5", {}, "C5: 10 x 999,698-tri terrains + 3 reflective spheres, 3840x2160, 64 spp, depth 2"),
+    # SURVEY.md 8f row 3 (beyond BASELINE.json's configs; general kernel): glossy recursion, area lights
+    "c3glossy": ("config_c3", {"roughness": 0.12}, "C3 with glossy mirror/dielectric/conductor (roughness 0.12): RNG draws inside trace"),
+    "c3area": ("config_c3", {"area_lights": 2}, "C3 with 1 point light + 2 area lights: counting pass + per-chunk prefix + shading pass"),
 }
 
 
@@ -322,7 +325,10 @@ def run_ours(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = my_bytes / (kern_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "renderKernelFast<false>" if not args.variant or args.variant == 1 else "renderKernelGeneral<false>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+    general = args.variant == 2 or args.config in ("c3glossy", "c3area")
+    kernel_name = ("renderKernelGeneral<false, true> (x2: counting + shading pass)" if args.config == "c3area" else
+                   "renderKernelGeneral<false, false>") if general else "renderKernelFast<false>"
+    roofline = {"bound": "hbm", "kernel": kernel_name, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": None, "peak_source": "measured" if peaks else "fallback",
                 "algorithmic_bytes_per_launch": my_bytes, "kernel_ms": kern_ms,
                 "counts": {k: int(cst[k]) for k in list(BYTES) + ["maxStack"]},

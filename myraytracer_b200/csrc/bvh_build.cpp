@@ -281,4 +281,99 @@ void buildTlas(const double* wb, int64_t n, TlasBuildOutput& out) {
     out.rootRef = rec.go(0, n, 1);
 }
 
+// ---- the reference's TLAS, rebuilt exactly (scenes with instanceMotion; see bvh_build.h) ---------------------------
+namespace {
+struct RefBox {                          // AABB.swift:12-35,62-70
+    double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    void grow(const double* l, const double* h) {
+        for (int a = 0; a < 3; a++) { lo[a] = l[a] < lo[a] ? l[a] : lo[a]; hi[a] = h[a] > hi[a] ? h[a] : hi[a]; }
+    }
+    double area() const {
+        const double ex = hi[0] - lo[0], ey = hi[1] - lo[1], ez = hi[2] - lo[2];
+        return 2.0 * ((ex * ey + ey * ez) + ez * ex);
+    }
+};
+struct RefBuilder {
+    const double* wb; int64_t n;
+    std::vector<double> centroid;        // (minP + maxP) * 0.5 per instance (RTContext.swift:464)
+    std::vector<RefNode>& nodes; std::vector<int32_t>& idx;
+    int32_t used = 0;
+    static const int N = 12, maxLeaf = 2;
+
+    void updateBounds(int32_t ni) {                                        // BVH.swift:107-125
+        RefNode& nd = nodes[ni];
+        RefBox b;
+        for (int i = 0; i < nd.count; i++) { const int64_t p = idx[nd.leftFirst + i]; b.grow(wb + p * 6, wb + p * 6 + 3); }
+        for (int a = 0; a < 3; a++) { nd.lo[a] = b.lo[a]; nd.hi[a] = b.hi[a]; }
+    }
+    double bestSplit(const RefNode& nd, int& axis, double& pos) const {    // BVH.swift:189-250
+        double bestCost = INFINITY;
+        for (int a = 0; a < 3; a++) {
+            double bmin = INFINITY, bmax = -INFINITY;
+            for (int i = 0; i < nd.count; i++) {
+                const double c = centroid[(size_t)idx[nd.leftFirst + i] * 3 + a];
+                bmin = c < bmin ? c : bmin; bmax = c > bmax ? c : bmax;
+            }
+            if (bmax <= bmin) continue;
+            RefBox bin[N]; int cnt[N] = {};
+            const double scale = (double)N / (bmax - bmin);
+            for (int i = 0; i < nd.count; i++) {
+                const int64_t p = idx[nd.leftFirst + i];
+                int k = (int)((centroid[(size_t)p * 3 + a] - bmin) * scale);
+                if (k > N - 1) k = N - 1;
+                cnt[k]++;
+                bin[k].grow(wb + p * 6, wb + p * 6 + 3);
+            }
+            double leftArea[N - 1], rightArea[N - 1]; int leftCnt[N - 1], rightCnt[N - 1];
+            RefBox L, R; int sL = 0, sR = 0;
+            for (int i = 0; i < N - 1; i++) {
+                sL += cnt[i]; leftCnt[i] = sL; L.grow(bin[i].lo, bin[i].hi); leftArea[i] = L.area();
+                sR += cnt[N - 1 - i]; rightCnt[N - 2 - i] = sR; R.grow(bin[N - 1 - i].lo, bin[N - 1 - i].hi); rightArea[N - 2 - i] = R.area();
+            }
+            const double step = (bmax - bmin) / (double)N;
+            for (int i = 0; i < N - 1; i++) {
+                if (leftCnt[i] == 0 || rightCnt[i] == 0) continue;
+                const double cost = (double)leftCnt[i] * leftArea[i] + (double)rightCnt[i] * rightArea[i];
+                if (cost < bestCost) { bestCost = cost; axis = a; pos = bmin + step * (double)(i + 1); }
+            }
+        }
+        return bestCost;
+    }
+    void subdivide(int32_t ni) {                                           // BVH.swift:128-186
+        const RefNode nd = nodes[ni];
+        const int count = nd.count;
+        if (count <= maxLeaf && ni != 0) return;
+        int axis = 0; double pos = 0;
+        bestSplit(nd, axis, pos);
+        int i = nd.leftFirst, j = i + count - 1;
+        while (i <= j) {
+            if (centroid[(size_t)idx[i] * 3 + axis] < pos) i++;
+            else { std::swap(idx[i], idx[j]); j--; }
+        }
+        const int leftCount = i - nd.leftFirst;
+        if (leftCount == 0 || leftCount == count) return;
+        const int32_t l = ++used, r = ++used;
+        nodes[l].leftFirst = nd.leftFirst; nodes[l].count = leftCount;
+        nodes[r].leftFirst = i; nodes[r].count = count - leftCount;
+        nodes[ni].leftFirst = l; nodes[ni].count = 0;
+        updateBounds(l); updateBounds(r);
+        subdivide(l); subdivide(r);
+    }
+};
+}  // namespace
+
+void buildReferenceTlas(const double* worldBounds, int64_t n, RefTlasOutput& out) {
+    out.nodes.assign((size_t)std::max<int64_t>(1, 2 * n - 1), RefNode{});      // BVH.swift:90-91
+    out.primIdx.resize((size_t)n);
+    for (int64_t i = 0; i < n; i++) out.primIdx[i] = (int32_t)i;
+    RefBuilder b{worldBounds, n, {}, out.nodes, out.primIdx};
+    b.centroid.resize((size_t)n * 3);
+    for (int64_t i = 0; i < n; i++)
+        for (int a = 0; a < 3; a++) b.centroid[i * 3 + a] = (worldBounds[i * 6 + a] + worldBounds[i * 6 + 3 + a]) * 0.5;
+    out.nodes[0].leftFirst = 0; out.nodes[0].count = (int32_t)n;
+    b.updateBounds(0);
+    b.subdivide(0);
+    out.nodes.resize((size_t)b.used + 1);
+}
+
 }  // namespace rtg

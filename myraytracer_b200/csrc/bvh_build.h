@@ -56,4 +56,14 @@ struct TlasBuildOutput {
 };
 void buildTlas(const double* worldBounds /* n*6 */, int64_t n, TlasBuildOutput& out);
 
+// The reference's OWN TLAS over the instances' world bounds, for scenes with instanceMotion only (rt_trace.cuh:
+// traceSceneRef explains why its topology matters there): buildTLAS (Models/RTContext.swift:459-474) =
+// BVHBuilder(maxLeaf: 2, split: .sah, binCount: 12) (Accelearion/BVH.swift:78-250), restated operation by operation
+// so that nodes, boxes and the primitiveIdx permutation come out identical.
+struct RefTlasOutput {
+    std::vector<RefNode> nodes;         // node 0 = root; children of an inner node are leftFirst, leftFirst + 1
+    std::vector<int32_t> primIdx;       // instance indices in leaf order
+};
+void buildReferenceTlas(const double* worldBounds /* n*6 */, int64_t n, RefTlasOutput& out);
+
 }  // namespace rtg

@@ -88,6 +88,14 @@ struct GMaterial {
     int32_t type, hasAbsorption;
 };
 
+// One node of the reference-topology TLAS (scenes with instanceMotion only; rt_trace.cuh: traceSceneRef): the
+// reference's BVHNode (Accelearion/BVH.swift:16-30) — exact FP64 box, leftFirst = left child (right = left + 1) or
+// first entry of refTlasPrim, count > 0 for a leaf.
+struct RT_ALIGN(16) RefNode {
+    double lo[3], hi[3];
+    int32_t leftFirst, count, pad0, pad1;
+};
+
 struct GPointLight { double position[3], intensity[3]; };
 struct GAreaLight { double position[3], normal[3], size, radiance[3]; };   // Object+Extension.swift:145-186
 
@@ -105,6 +113,10 @@ struct DeviceScene {
     const GPointLight* pointLights;
     const GAreaLight* areaLights;
     const double* jitter;          // area lights: the 10x10 stratified table, xs[100] then ys[100] (:92-93,646-659)
+    const RefNode* refTlas;        // scenes with instanceMotion: the reference's own TLAS topology (else null)
+    const int32_t* refTlasPrim;    // its primitiveIdx array (instance indices in leaf order)
+    int32_t refTlasNodes;          // 0: not used
+    int32_t pad1;
     int32_t tlasRootRef;
     int32_t nInstances, nMaterials, nPointLights;
     int32_t maxDepth;

@@ -68,6 +68,8 @@ struct rt_scene {
     GNode* dNodes = nullptr; GTri* dTris = nullptr; GTriD* dTrisD = nullptr; double* dNormals = nullptr;
     GNode* dTlas = nullptr; GInstance* dInst = nullptr; GMaterial* dMat = nullptr; GPointLight* dLights = nullptr;
     GAreaLight* dAreaLights = nullptr; double* dJitter = nullptr;
+    RefNode* dRefTlas = nullptr; int32_t* dRefTlasPrim = nullptr;
+    bool motion = false;               // Mesh.motionBlur or MeshInstance.motionBlur somewhere: ray time matters
     unsigned* dAreaIndex = nullptr; size_t areaIndexBytes = 0;   // per-pixel jitter index of an area-light frame
     // render state (re-used across calls)
     int* dTileCounter = nullptr; unsigned long long* dCounters = nullptr;
@@ -109,9 +111,6 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     if (d->abiVersion != RT_ABI_VERSION) return fail(RT_ERR_INVALID, "rt_scene_desc.abiVersion mismatch");
     if (d->nMaterials < 1 || !d->materials) return fail(RT_ERR_INVALID, "at least one material is required");
     if (d->nAreaLights < 0 || (d->nAreaLights > 0 && !d->areaLights)) return fail(RT_ERR_INVALID, "area light array missing");
-    if (d->triMotionBlur)
-        for (int64_t i = 0; i < d->nTriangles * 3; i++)
-            if (d->triMotionBlur[i] != 0.0) return fail(RT_ERR_UNSUPPORTED, "motion blur is not implemented on the GPU path yet");
     int ndev = 0;
     CK(cudaGetDeviceCount(&ndev));
     if (device < 0 || device >= ndev) return fail(RT_ERR_INVALID, "invalid CUDA device index");
@@ -138,6 +137,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
         int kind = INST_MESH; int64_t prim = 0; int64_t matId = 0; int smooth = 0;
         int32_t nodeBase = 0, triBase = 0, rootRef = kEmptyRef; int f64 = 0;
         double lo[3], hi[3], centre[3];
+        double motion[3] = {0, 0, 0};      // Triangle.motionBlur of the mesh (RTContext.swift:280,345)
     };
     std::vector<BlasInfo> blasInfo((size_t)d->nBlas);
     std::vector<GNode> nodes;
@@ -175,9 +175,19 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
         }
         BlasBuildInput in{};
         in.triVertices = d->triVertices; in.triIndices = idx.data(); in.count = bl.primCount; in.threads = 0;
+        bool blur = false;
+        if (d->triMotionBlur) {            // one motion vector per mesh; the boxes grow by it (RTContext.swift:283-289)
+            const double* m0 = d->triMotionBlur + idx[0] * 3;
+            for (int64_t k = 0; k < bl.primCount; k++)
+                if (std::memcmp(d->triMotionBlur + idx[k] * 3, m0, 24) != 0)
+                    return fail(RT_ERR_UNSUPPORTED, "per-triangle motion vectors inside one BLAS");
+            std::memcpy(in.motionBlur, m0, 24); std::memcpy(bi.motion, m0, 24);
+            blur = m0[0] != 0 || m0[1] != 0 || m0[2] != 0;
+            if (blur) sc->motion = true;
+        }
         BlasBuildOutput out;
         bool built = false;
-        if (deviceBuild && bl.primCount >= 2) {
+        if (deviceBuild && bl.primCount >= 2 && !blur) {     // the device builder does not grow boxes by a motion vector
             CK(buildBlasDevice(dVerts.p, in, out));
             built = out.maxDepth <= renderStackCapacity() - 2;      // too deep for the stacks: the SAH builder takes over
             if (built) deviceBuilt++;
@@ -213,11 +223,12 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     // ---- instances
     std::vector<GInstance> inst((size_t)d->nInstances);
     std::vector<double> wb((size_t)d->nInstances * 6);
+    bool instanceMotion = false;
     for (int64_t i = 0; i < d->nInstances; i++) {
         const rt_instance& in = d->instances[i];
         if (in.blas < 0 || in.blas >= d->nBlas) return fail(RT_ERR_INVALID, "rt_instance.blas out of range");
-        if (in.instanceMotion[0] != 0 || in.instanceMotion[1] != 0 || in.instanceMotion[2] != 0)
-            return fail(RT_ERR_UNSUPPORTED, "instance motion blur is not implemented on the GPU path yet");
+        const bool moves = in.instanceMotion[0] != 0 || in.instanceMotion[1] != 0 || in.instanceMotion[2] != 0;
+        if (moves) { sc->motion = true; instanceMotion = true; }
         const BlasInfo& bi = blasInfo[in.blas];
         GInstance& g = inst[i];
         std::memset(&g, 0, sizeof g);
@@ -236,6 +247,8 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
         g.nodeBase = bi.nodeBase; g.triBase = bi.triBase; g.triF64 = bi.f64; g.rootRef = bi.rootRef;
         g.matId = in.hasMaterialOverride ? in.materialOverride : bi.matId;  // RTContext.swift:704
         g.primIndex = bi.prim;
+        std::memcpy(g.motion, in.instanceMotion, 24); std::memcpy(g.meshMotion, bi.motion, 24);
+        g.hasMotion = (moves || bi.motion[0] != 0 || bi.motion[1] != 0 || bi.motion[2] != 0) ? 1 : 0;
         if (bi.kind == INST_SPHERE) { const rt_sphere& s = d->spheres[bi.prim]; g.prim[0] = s.center[0]; g.prim[1] = s.center[1]; g.prim[2] = s.center[2]; g.prim[3] = s.radius; }
         if (bi.kind == INST_PLANE) { const rt_plane& p = d->planes[bi.prim]; for (int a = 0; a < 3; a++) { g.prim[a] = p.center[a]; g.prim[3 + a] = p.normal[a]; } }
         std::memcpy(&wb[i * 6], in.worldBounds, 48);
@@ -243,6 +256,10 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     TlasBuildOutput tl;
     buildTlas(wb.data(), d->nInstances, tl);
     if (tl.maxDepth > 38) return fail(RT_ERR_UNSUPPORTED, "TLAS deeper than the TLAS stack");
+    // instanceMotion: the reference's instance boxes do not follow the motion, so which displaced instances a ray
+    // reaches depends on the reference's own TLAS topology — rebuilt exactly and walked in FP64 (rt_trace.cuh)
+    RefTlasOutput refTl;
+    if (instanceMotion) buildReferenceTlas(wb.data(), d->nInstances, refTl);
 
     // ---- materials / lights
     std::vector<GMaterial> mats((size_t)d->nMaterials);
@@ -336,6 +353,8 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     if ((rc = upload(lights, &sc->dLights, bytes))) return rc;
     if ((rc = upload(areaLights, &sc->dAreaLights, bytes))) return rc;
     if ((rc = upload(jitter, &sc->dJitter, bytes))) return rc;
+    if ((rc = upload(refTl.nodes, &sc->dRefTlas, bytes))) return rc;
+    if ((rc = upload(refTl.primIdx, &sc->dRefTlasPrim, bytes))) return rc;
     // ray / test counters (16 x u64) and the work counter behind them: one allocation, one memset per frame
     CK(cudaMalloc((void**)&sc->dCounters, kFrameStateBytes));
     sc->dTileCounter = reinterpret_cast<int*>(sc->dCounters + 16);
@@ -354,6 +373,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     std::memcpy(S.tlasLo, sLo, 24); std::memcpy(S.tlasHi, sHi, 24); std::memcpy(S.tlasCentre, sC, 24);
     S.nInstances = (int32_t)d->nInstances; S.nMaterials = (int32_t)d->nMaterials; S.nPointLights = (int32_t)d->nPointLights;
     S.areaLights = sc->dAreaLights; S.jitter = sc->dJitter; S.nAreaLights = (int32_t)d->nAreaLights;
+    S.refTlas = sc->dRefTlas; S.refTlasPrim = sc->dRefTlasPrim; S.refTlasNodes = (int32_t)refTl.nodes.size();
     S.maxDepth = d->maxRecursionDepth;
     std::memcpy(S.ambient, d->ambient, 24); std::memcpy(S.background, d->background, 24);
     S.eps = d->intersectionTestEpsilon; S.shadowEps = d->shadowRayEpsilon;
@@ -380,6 +400,7 @@ void rt_scene_destroy(rt_scene_t* sc) {
     cudaFree(sc->dNodes); cudaFree(sc->dTris); cudaFree(sc->dTrisD); cudaFree(sc->dNormals); cudaFree(sc->dTlas);
     cudaFree(sc->dInst); cudaFree(sc->dMat); cudaFree(sc->dLights); cudaFree(sc->dCounters);
     cudaFree(sc->dAreaLights); cudaFree(sc->dJitter); cudaFree(sc->dAreaIndex);
+    cudaFree(sc->dRefTlas); cudaFree(sc->dRefTlasPrim);
     cudaFree(sc->dTileCost); cudaFree(sc->dTileOrder); cudaFree(sc->dSchedWork);
     cudaFree(sc->dPathStack); cudaFree(sc->dRgba); cudaFree(sc->dLinear); cudaFree(sc->dIds);
     if (sc->hCounters) cudaFreeHost(sc->hCounters);

@@ -93,7 +93,7 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     if (rc) return rc;
     const bool counters = params && params->collectCounters;
     const bool area = sc->ds.nAreaLights > 0;
-    int variant = (sc->glossy || area) ? KV_GENERAL : KV_FAST;
+    int variant = (sc->glossy || area || sc->motion) ? KV_GENERAL : KV_FAST;
     if (params && params->kernelVariant != 0) {
         if (params->kernelVariant < 1 || params->kernelVariant > KV_COUNT) return fail(RT_ERR_INVALID, "kernelVariant outside 0..2");
         variant = params->kernelVariant - 1;
@@ -101,6 +101,8 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
             return fail(RT_ERR_UNSUPPORTED, "the fast kernel needs roughness == 0 on every material (RNG skip-ahead)");
         if (area && variant == KV_FAST)
             return fail(RT_ERR_UNSUPPORTED, "the fast kernel does not carry the area lights' per-chunk jitter index");
+        if (sc->motion && variant == KV_FAST)
+            return fail(RT_ERR_UNSUPPORTED, "the fast kernel does not carry the ray time of motion blur");
     }
     // the area lights' jitter index runs through a whole 8-row chunk (Object+Extension.swift:288): chunks stay whole
     if (area && cp.shardCount > 1 && cp.shardTiles)
@@ -116,6 +118,7 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     rt.rgba = (uint8_t*)dRgbaOut; rt.linear = (double*)dLinearOut; rt.ids = (HitId*)dIdsOut;
     rt.pathStack = sc->dPathStack; rt.counters = sc->dCounters;
     rt.tileCounter = sc->dTileCounter;
+    rt.motion = sc->motion ? 1 : 0;
     // Tile schedule: the frame records its cost per tile, the next frame of the same geometry draws the longest
     // tiles first.
     const int nTiles = ShardTiles(cp.width, cp.height, cp.shardIndex, cp.shardCount, cp.shardTiles).count;

@@ -14,17 +14,17 @@ namespace rtg {
 #define RT_THREADS RT_FAST_BLOCK
 #else
 #define RT_KERNEL(c) renderKernelGeneral<c, false>
-#define RT_KERNEL_AREA(c) renderKernelGeneral<c, true>
+#define RT_KERNEL_EXT(c) renderKernelGeneral<c, true>
 #define RT_NAME(x) x##General
 #define RT_THREADS RT_BLOCK
 #endif
 
 cudaError_t RT_NAME(launchVariant)(const DeviceScene& S, const CameraParams& cam, const RenderTargets& out, int blocks,
                                    bool counters, cudaStream_t stream) {
-#ifdef RT_KERNEL_AREA
-    if (out.areaPass != 0) {       // scene with area lights: same kernel, index bookkeeping compiled in
-        if (counters) RT_LAUNCH(RT_KERNEL_AREA(true), blocks, RT_THREADS, stream, S, cam, out);
-        else RT_LAUNCH(RT_KERNEL_AREA(false), blocks, RT_THREADS, stream, S, cam, out);
+#ifdef RT_KERNEL_EXT
+    if (out.areaPass != 0 || out.motion) {     // area lights / motion blur: the instantiation that carries them
+        if (counters) RT_LAUNCH(RT_KERNEL_EXT(true), blocks, RT_THREADS, stream, S, cam, out);
+        else RT_LAUNCH(RT_KERNEL_EXT(false), blocks, RT_THREADS, stream, S, cam, out);
         return cudaGetLastError();
     }
 #endif

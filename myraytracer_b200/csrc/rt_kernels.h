@@ -29,6 +29,7 @@ struct RenderTargets {
     // prefix over the chunk, row-major); areaPass 2 renders with it.  areaPass 0: scene without area lights.
     unsigned* areaIndex;           // W*H or null
     int areaPass;
+    int motion;                    // 1: the scene has motion blur (general kernel, ray time carried down the path)
 #ifdef RT_WARPTIMES
     unsigned long long* warpTimes; // profiling build only: 4 x u64 per warp (start, first unit done, last draw, exit; ns)
 #endif

@@ -48,6 +48,7 @@ namespace rtg {
 struct PrimaryRay {
     V3 o, d;
     double tMin;
+    double time;      // Ray.time in [0, 1): only motion blur reads it
 };
 
 // Object+Extension.swift:307-344 for sample (sx, sy) of pixel (i, j); draws xi1, xi2, [lens u, v], time.
@@ -79,7 +80,7 @@ __device__ __forceinline__ PrimaryRay primaryRay(const CameraParams& cam, int i,
         r.d = normalize(pFocus - a);
         r.o = a;
     }
-    (void)rng.nextFloat();  // ray time: always drawn (:340); no motion in supported scenes
+    r.time = rng.nextFloat();  // ray time: always drawn (:340)
     const double denomW = dot(r.d, cw);
     const double tImg = dot(cm - r.o, cw) / (denomW == 0.0 ? 4.9406564584124654e-324 : denomW);  // :342
     r.tMin = dmax(tImg, 0.0);
@@ -360,9 +361,10 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFas
     flushCounters<COUNT>(out, C, R);
 }
 
-// AREA: scenes with area lights (RenderTargets::areaIndex / areaPass): pass 1 leaves each pixel's number of
-// jitter-table draws, pass 2 starts each pixel at its index within the 8-row chunk.
-template <bool COUNT, bool AREA>
+// EXT: scenes with area lights (RenderTargets::areaIndex / areaPass: pass 1 leaves each pixel's number of
+// jitter-table draws, pass 2 starts each pixel at its index within the 8-row chunk) and / or motion blur (ray time
+// carried down the path).  A second instantiation, so that scenes without them run exactly the code they always ran.
+template <bool COUNT, bool EXT>
 __global__ void __launch_bounds__(RT_BLOCK, RT_GEN_BLOCKS) renderKernelGeneral(DeviceScene S, CameraParams cam, RenderTargets out) {
     __shared__ int32_t sstack[RT_SSTACK * RT_BLOCK];
     const int lane = threadIdx.x & 31;
@@ -401,7 +403,7 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_GEN_BLOCKS) renderKernelGeneral(D
             int sampleIndex = 0;
             AreaState area;
             area.jitterIndex = 0; area.countOnly = false;
-            if (AREA) {
+            if (EXT && out.areaPass != 0) {
                 area.countOnly = out.areaPass == 1;
                 if (!area.countOnly) area.jitterIndex = out.areaIndex[(size_t)j * W + i];
             }
@@ -412,18 +414,18 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_GEN_BLOCKS) renderKernelGeneral(D
                     HitId* idSlot = (out.ids && !area.countOnly) ? out.ids + (((size_t)j * W + i) * (size_t)(n * n) + (size_t)(sy * n + sx)) : nullptr;
                     PathEntry cur0;
                     cur0.o = pr.o; cur0.d = pr.d; cur0.w = mk(1, 1, 1); cur0.beerMat = 0; cur0.depth = 0; cur0.beer = 0;
-                    pixel = pixel + scalarPathLoop<true, COUNT, false, AREA>(S, T, cur0, 0, true, pr.tMin, idSlot, rng, C, R, mk(0, 0, 0),
-                                                                             AREA ? &area : nullptr);
+                    pixel = pixel + scalarPathLoop<true, COUNT, false, EXT, EXT>(S, T, cur0, 0, true, pr.tMin, idSlot, rng, C, R, mk(0, 0, 0),
+                                                                                 EXT ? &area : nullptr, pr.time);
                     sampleIndex++;
                 }
             }
-            if (AREA && area.countOnly) out.areaIndex[(size_t)j * W + i] = area.jitterIndex;
+            if (EXT && area.countOnly) out.areaIndex[(size_t)j * W + i] = area.jitterIndex;
             else writePixel(out, (size_t)j * W + i, pixel / (double)samples);                              // :354
         }
         __syncwarp();
         if (out.tileCost && lane == 0) atomicAdd(out.tileCost + tile, ((unsigned)clock() - c0) >> 6);
     }
-    if (AREA && out.areaPass == 1) return;      // the counting pass reports no rays: pass 2 traces them all again
+    if (EXT && out.areaPass == 1) return;      // the counting pass reports no rays: pass 2 traces them all again
     flushCounters<COUNT>(out, C, R);
 }
 

@@ -262,20 +262,21 @@ __device__ __forceinline__ int spawnChildren(const DeviceScene& S, const ShadePo
 // processed entries, added in processing order.
 // CALL: the traversal is the out-of-line traceSceneCall (fast kernel) instead of two inlined walks.
 // AREA: the scene has area lights; `area` carries the chunk's jitter index through the path (general kernel only).
-template <bool GLOSSY, bool COUNT, bool CALL = false, bool AREA = false>
+// MOTION: motion blur; `time` is the sample's ray time, inherited by every ray of the path (:123,172,198,242).
+template <bool GLOSSY, bool COUNT, bool CALL = false, bool AREA = false, bool MOTION = false>
 __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceScratch& T, PathEntry cur, int level,
                                              bool firstIsPrimary, double tMinPrimary, HitId* idSlot, PCG32& rng, Counters& C,
-                                             RayCounts& R, V3 color, AreaState* area = nullptr) {
+                                             RayCounts& R, V3 color, AreaState* area = nullptr, double time = 0.0) {
     const V3 ambient = ld3(S.ambient), background = ld3(S.background);
     bool primary = firstIsPrimary;
     for (;;) {
         HitRec hit;
         hit.t = CUDART_INF; hit.u = hit.v = 0; hit.inst = -1; hit.slot = 0;
         if (CALL) hit = traceSceneCall<COUNT>(S, cur.o, cur.d, primary ? tMinPrimary : 0.0, hit, false, T.sstack, T.sstackN, COUNT ? &C : nullptr).hit;
-        else traceScene<COUNT>(S, cur.o, cur.d, primary ? tMinPrimary : 0.0, hit, false, T.sstack, T.sstackN, C);
+        else traceScene<COUNT, MOTION>(S, cur.o, cur.d, primary ? tMinPrimary : 0.0, hit, false, T.sstack, T.sstackN, C, time);
         Surface sf;
         if (hit.inst >= 0) {
-            resolveHit(S, hit, cur.o, cur.d, sf);
+            resolveHit<MOTION>(S, hit, cur.o, cur.d, sf, time);
             if (COUNT && sf.kind == 1 && S.instances[hit.inst].smooth) C.smooth++;
         }
         if (primary && idSlot) {
@@ -303,7 +304,7 @@ __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceSc
                     sh.t = dist; sh.u = sh.v = 0; sh.inst = -1; sh.slot = 0;             // tMax = dist (:124)
                     R.shadow++;
                     const bool occluded = CALL ? traceSceneCall<COUNT>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, COUNT ? &C : nullptr).occluded
-                                               : traceScene<COUNT>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, C);
+                                               : traceScene<COUNT, MOTION>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, C, time);
                     if (!occluded)
                         Lo = Lo + pointLightTerm(*sp.mat, pl, sp.N, cur.d, wi, dist);
                 }
@@ -322,7 +323,7 @@ __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceSc
                     R.shadow++;
                     const V3 so = sp.p + wi * S.shadowEps;
                     const bool occluded = CALL ? traceSceneCall<COUNT>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, COUNT ? &C : nullptr).occluded
-                                               : traceScene<COUNT>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, C);
+                                               : traceScene<COUNT, MOTION>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, C, time);
                     if (!occluded) Lo = Lo + areaLightTerm(*sp.mat, al, sp.N, cur.d, wi, dist2, NdotL, Ln);
                 }
             }

@@ -7,8 +7,11 @@ namespace rtg {
 
 #define RT_TLAS_STACK 40
 
-// world -> local ray (RTContext.swift:657-669); instanceMotion is rejected at scene creation.
-__device__ __forceinline__ void toLocal(const GInstance& I, V3 o, V3 d, V3& oL, V3& dL) {
+// world -> local ray (RTContext.swift:657-669).  MOTION: the instance is displaced by instanceMotion * ray.time,
+// applied to the ray origin before the transform (:658-661, :756-758).
+template <bool MOTION = false>
+__device__ __forceinline__ void toLocal(const GInstance& I, V3 o, V3 d, V3& oL, V3& dL, double time = 0.0) {
+    if (MOTION) o = o - ld3(I.motion) * time;
     if (I.identity) { oL = o; dL = d; }
     else { oL = xfmPoint(I.w2l, o); dL = xfmVector(I.w2l, d); }
 }
@@ -43,27 +46,71 @@ __device__ __forceinline__ bool analyticInstance(const DeviceScene& S, const GIn
 }
 
 // Closest-hit / any-hit test of one instance.  tLow = max(eps, tMin); hit.t = current closest t or tMax.
-template <bool COUNT>
+template <bool COUNT, bool MOTION = false>
 __device__ __forceinline__ bool enterInstance(const DeviceScene& S, int idx, V3 o, V3 d, double eps, double tMin,
-                                              HitRec& hit, bool anyhit, int32_t* sstack, int sstackN, Counters& C) {
+                                              HitRec& hit, bool anyhit, int32_t* sstack, int sstackN, Counters& C, double time = 0.0) {
     const GInstance& I = S.instances[idx];
     V3 oL, dL;
-    toLocal(I, o, d, oL, dL);
+    toLocal<MOTION>(I, o, d, oL, dL, time);
     if (COUNT) C.inst++;
     const double tLow = dmax(eps, tMin);
-    if (I.kind == INST_MESH) return traverseBlas<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, sstack, sstackN, C);
+    if (I.kind == INST_MESH) return traverseBlas<COUNT, MOTION>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, sstack, sstackN, C, time);
     return analyticInstance<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, C);
+}
+
+// Scenes with instanceMotion: the reference's instance boxes (Instance.worldBounds, RTContext.swift:437-455) do NOT
+// follow the motion, and its TLAS walk enters an instance iff the UNDISPLACED ray passes hitAABB on every node from
+// the root to the instance's leaf (:632-640, :745-747) — so which displaced instances a ray can reach depends on the
+// topology of the reference's own TLAS.  For those scenes the host rebuilds that TLAS (bvh_build.cpp:
+// buildReferenceTlas = BVHBuilder(maxLeaf 2, SAH, 12 bins) over the instances' bounds) and this walk reproduces the
+// reference's visit rule exactly in FP64: pop, test the node's own box, leaf -> its instances in primitiveIdx order,
+// inner -> both children tested, nearer pushed last (:600-606,710-716).
+__device__ __forceinline__ double hitRefBox(const RefNode& n, V3 o, V3 inv, double eps) {
+    const double t1x = (n.lo[0] - o.x) * inv.x, t1y = (n.lo[1] - o.y) * inv.y, t1z = (n.lo[2] - o.z) * inv.z;
+    const double t2x = (n.hi[0] - o.x) * inv.x, t2y = (n.hi[1] - o.y) * inv.y, t2z = (n.hi[2] - o.z) * inv.z;
+    const double tmin = dmax(dmax(dmin(t1x, t2x), dmin(t1y, t2y)), dmin(t1z, t2z));
+    const double tmax = dmin(dmax(t1x, t2x), dmin(dmax(t1y, t2y), dmax(t1z, t2z)));
+    return (tmax >= dmax(tmin, eps)) ? tmin : CUDART_INF;
+}
+template <bool COUNT>
+__device__ __forceinline__ bool traceSceneRef(const DeviceScene& S, V3 o, V3 d, double tMin, HitRec& hit, bool anyhit,
+                                              int32_t* sstack, int sstackN, Counters& C, double time) {
+    const double eps = S.eps;
+    const V3 inv = mk(1.0 / d.x, 1.0 / d.y, 1.0 / d.z);       // Ray.invDir
+    int32_t stack[64];                                          // the reference's fixed 64 slots (:626)
+    int sp = 0;
+    stack[sp++] = 0;
+    while (sp > 0) {
+        const RefNode& node = S.refTlas[stack[--sp]];
+        if (COUNT) C.box++;
+        if (hitRefBox(node, o, inv, eps) == CUDART_INF) continue;
+        if (node.count > 0) {
+            for (int k = 0; k < node.count; k++)
+                if (enterInstance<COUNT, true>(S, S.refTlasPrim[node.leftFirst + k], o, d, eps, tMin, hit, anyhit, sstack, sstackN, C, time))
+                    return true;
+            continue;
+        }
+        int32_t L = node.leftFirst, R = L + 1;
+        if (anyhit) { if (sp + 2 <= 64) { stack[sp++] = R; stack[sp++] = L; } continue; }      // :775-777
+        double d1 = hitRefBox(S.refTlas[L], o, inv, eps), d2 = hitRefBox(S.refTlas[R], o, inv, eps);
+        if (COUNT) C.box += 2;
+        if (d1 > d2) { const double td = d1; d1 = d2; d2 = td; const int32_t tn = L; L = R; R = tn; }
+        if (d2 != CUDART_INF && sp < 64) stack[sp++] = R;
+        if (d1 != CUDART_INF && sp < 64) stack[sp++] = L;
+    }
+    return false;
 }
 
 // TLAS walk: conservative FP32 boxes (unions of Instance.worldBounds) like the BLAS nodes, near child first; every
 // instance reached is then tested exactly.
-template <bool COUNT>
+template <bool COUNT, bool MOTION = false>
 __device__ __forceinline__ bool traceScene(const DeviceScene& S, V3 o, V3 d, double tMin, HitRec& hit, bool anyhit,
-                                           int32_t* sstack, int sstackN, Counters& C) {
+                                           int32_t* sstack, int sstackN, Counters& C, double time = 0.0) {
     const double eps = S.eps;
     int32_t cur = S.tlasRootRef;
     if (cur == kEmptyRef) return false;
-    if (cur < 0) return enterInstance<COUNT>(S, ~cur, o, d, eps, tMin, hit, anyhit, sstack, sstackN, C);
+    if (MOTION && S.refTlasNodes > 0) return traceSceneRef<COUNT>(S, o, d, tMin, hit, anyhit, sstack, sstackN, C, time);
+    if (cur < 0) return enterInstance<COUNT, MOTION>(S, ~cur, o, d, eps, tMin, hit, anyhit, sstack, sstackN, C, time);
     const double tLow = dmax(eps, tMin);
     RayF rf = makeRayF(S.tlasLo, S.tlasHi, S.tlasCentre, o, d, refinedInv(d), tLow, hit.t);
     if (COUNT) C.box++;
@@ -88,7 +135,7 @@ __device__ __forceinline__ bool traceScene(const DeviceScene& S, V3 o, V3 d, dou
             } else if (h0) { cur = c0; continue; }
             else if (h1) { cur = c1; continue; }
         } else {
-            if (enterInstance<COUNT>(S, ~cur, o, d, eps, tMin, hit, anyhit, sstack, sstackN, C)) return true;
+            if (enterInstance<COUNT, MOTION>(S, ~cur, o, d, eps, tMin, hit, anyhit, sstack, sstackN, C, time)) return true;
             rf.tmax = __double2float_ru(hit.t - rf.t0);       // a closer hit prunes the boxes that follow
         }
         if (sp == 0) return false;
@@ -133,7 +180,8 @@ struct Surface {
 
 // Hit.p / Hit.n / Hit.mat exactly as committed at RTContext.swift:496-509,524-526,535-537
 // and mapped to world space at :679-704.
-__device__ __forceinline__ void resolveHit(const DeviceScene& S, const HitRec& hit, V3 o, V3 d, Surface& s) {
+template <bool MOTION = false>
+__device__ __forceinline__ void resolveHit(const DeviceScene& S, const HitRec& hit, V3 o, V3 d, Surface& s, double time = 0.0) {
     const GInstance& I = S.instances[hit.inst];
     V3 pL, nL;
     const int kind = I.kind;
@@ -155,13 +203,14 @@ __device__ __forceinline__ void resolveHit(const DeviceScene& S, const HitRec& h
         s.prim = triIndex;
     } else {
         V3 oL, dL;
-        toLocal(I, o, d, oL, dL);
+        toLocal<MOTION>(I, o, d, oL, dL, time);
         pL = oL + dL * hit.t;
         if (kind == INST_SPHERE) { nL = normalize(pL - ld3(I.prim)); s.kind = 2; }
         else { nL = normalize(ld3(I.prim + 3)); s.kind = 3; }
         s.prim = I.primIndex;
     }
     s.p = I.identity ? pL : xfmPoint(I.l2w, pL);
+    if (MOTION) s.p = s.p + ld3(I.motion) * time;       // wp + instOffset (:681-701); the mesh's own motionBlur is not added (:504)
     V3 wn = normalize(mul3(I.nmat, nL));
     if (I.flipNormal) wn = -wn;
     s.n = wn;

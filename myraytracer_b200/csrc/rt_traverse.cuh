@@ -193,9 +193,15 @@ __device__ __forceinline__ void loadTri(const DeviceScene& S, bool f64, int slot
 // shadow queries, which halves the instruction-cache footprint): return true at the first accepted primitive.
 // oL/dL: local-space FP64 ray (bit-identical to the reference's).  tLow = max(eps, tMin).
 // hit.t is the current closest t (closest) or tMax (any-hit); updated on accept.
-template <bool COUNT>
+// MOTION (general kernel, scenes with motion blur): the triangles of a mesh with Mesh.motionBlur are displaced by
+// motionBlur * ray.time, which the reference applies to the ray origin of the triangle test only
+// (RTContext.swift:480-481,833-834); the node boxes were grown by the motion vector at build time (:283-289) and are
+// tested with the undisplaced ray, like the reference's.
+template <bool COUNT, bool MOTION = false>
 __device__ __forceinline__ bool traverseBlas(const DeviceScene& S, const GInstance& I, int instIdx, V3 oL, V3 dL, double eps,
-                                             double tLow, HitRec& hit, bool anyhit, int32_t* sstack, int sstackN, Counters& C) {
+                                             double tLow, HitRec& hit, bool anyhit, int32_t* sstack, int sstackN, Counters& C,
+                                             double time = 0.0) {
+    const V3 oTri = MOTION ? oL - ld3(I.meshMotion) * time : oL;
     // Advance the origin to the BLAS in FP64 so that its FP32 copy is accurate relative to the
     // box size: t0 = entry distance into the (exact) root box, from a widened FP64 slab test.
     V3 ia = refinedInv(dL);
@@ -271,7 +277,7 @@ __device__ __forceinline__ bool traverseBlas(const DeviceScene& S, const GInstan
                 loadTri(S, f64, first + k, v0, v1, v2);
                 if (COUNT) C.tri++;
                 double t, u, v;
-                if (!mtTest(v0, v1, v2, oL, dL, eps, t, u, v)) continue;
+                if (!mtTest(v0, v1, v2, oTri, dL, eps, t, u, v)) continue;
                 if (!inWindow(t, tLow, hit.t, anyhit)) continue;
                 if (anyhit) return true;
                 hit.t = t; hit.u = u; hit.v = v; hit.inst = instIdx; hit.slot = first + k;

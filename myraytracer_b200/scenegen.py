@@ -470,11 +470,16 @@ def config_c5(out_dir: str, n: int = 708, width: int = 3840, height: int = 2160,
     return path
 
 
-def config_instances(out_dir: str, width: int = 256, height: int = 192, samples: int = 4, depth: int = 3) -> str:
+def config_instances(out_dir: str, width: int = 256, height: int = 192, samples: int = 4, depth: int = 3,
+                     mesh_motion: Sequence[float] = (0.0, 0.0, 0.0), instance_motion: float = 0.0) -> str:
     """Not one of BASELINE.json's configs: the object kinds they leave out.  An infinite ground plane (its 1e5 bounds,
     RTContext.swift:172-174, stretch the scene box), one PLY mesh and three MeshInstances of it sharing its BLAS
     (:384-401): one with a material override, one mirrored (negative determinant -> flipped normals, :691-698),
-    one an instance of an instance; a dielectric sphere in front."""
+    one an instance of an instance; a dielectric sphere in front.
+    Motion blur: `mesh_motion` is the base mesh's Mesh.motionBlur (local space, applied in the
+    triangle test, boxes grown by it, RTContext.swift:283-289,480-481); `instance_motion` scales the
+    MeshInstance.motionBlur vectors of the three instances (world space, applied to the ray origin before the
+    instance transform while the instance boxes stay where they are, :437-455,658-661)."""
     pos, tris = icosphere_mesh(2, radius=1.0, seed=7, disp=0.15)
     write_ply(os.path.join(out_dir, "inst_blob.ply"), pos, tris)
     sc = Scene(maxRecursionDepth=depth, backgroundColor=(12, 14, 20), ambient=(20, 20, 20))
@@ -493,10 +498,14 @@ def config_instances(out_dir: str, width: int = 256, height: int = 192, samples:
     sc.objects = [
         SceneObject(OBJ_PLANE, id=1, material=1, centerIdx=1, normal=(0.0, 1.0, 0.0)),
         SceneObject(OBJ_SPHERE, id=2, material=5, centerIdx=2, radius=1.0),
-        SceneObject(OBJ_MESH, id=5, material=2, smooth=True, plyPath="inst_blob.ply", transform=colmajor(Mm)),
-        SceneObject(OBJ_MESH_INSTANCE, id=6, material=4, baseMeshID=5, transform=colmajor(Ma)),
-        SceneObject(OBJ_MESH_INSTANCE, id=7, material=None, baseMeshID=5, transform=colmajor(Mb)),
-        SceneObject(OBJ_MESH_INSTANCE, id=8, material=3, baseMeshID=6, transform=colmajor(Mc)),
+        SceneObject(OBJ_MESH, id=5, material=2, smooth=True, plyPath="inst_blob.ply", transform=colmajor(Mm),
+                    motionBlur=tuple(mesh_motion)),
+        SceneObject(OBJ_MESH_INSTANCE, id=6, material=4, baseMeshID=5, transform=colmajor(Ma),
+                    motionBlur=(0.9 * instance_motion, 0.0, 0.3 * instance_motion)),
+        SceneObject(OBJ_MESH_INSTANCE, id=7, material=None, baseMeshID=5, transform=colmajor(Mb),
+                    motionBlur=(0.0, 0.7 * instance_motion, 0.0)),
+        SceneObject(OBJ_MESH_INSTANCE, id=8, material=3, baseMeshID=6, transform=colmajor(Mc),
+                    motionBlur=(-0.5 * instance_motion, -0.4 * instance_motion, 0.6 * instance_motion)),
     ]
     sc.pointLights = [PointLight((5.0, 10.0, 7.0), (22000, 22000, 22000)), PointLight((-6.0, 9.0, 2.0), (12000, 11000, 10000))]
     sc.cameras = [Camera(id=1, imageName="instances.png", width=width, height=height, numSamples=samples,

@@ -12,4 +12,8 @@ GOLDEN_CASES = {
                                                      aperture=0.2, focus=14.0)),
     # area lights: the per-chunk jitter index (Object+Extension.swift:145-186,288)
     "c3_area_small": (scenegen.config_c3, dict(width=56, height=44, samples=4, depth=3, ico_level=1, area_lights=3)),
+    # motion blur: Mesh.motionBlur (triangle test) and MeshInstance.motionBlur (static instance boxes: the reference's
+    # own TLAS topology decides which displaced instances a ray reaches)
+    "motion_small": (scenegen.config_instances, dict(width=64, height=48, samples=4, mesh_motion=(0.4, -0.3, 0.2),
+                                                     instance_motion=1.5)),
 }

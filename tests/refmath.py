@@ -68,8 +68,8 @@ def camera_basis(cam: dict):
     return dict(e=e, u=u, v=v, w=w, m=m, q00=q00, du=(r - l) / W, dv=(t - b) / H, W=W, H=H)
 
 
-def primary_rays(cam: dict, i: int, j: int):
-    """All n*n primary rays of pixel (i, j): list of (origin, dir, tMin), :294-344 without DOF."""
+def primary_rays(cam: dict, i: int, j: int, with_time: bool = False):
+    """All n*n primary rays of pixel (i, j): list of (origin, dir, tMin[, time]), :294-344 without DOF."""
     B = camera_basis(cam)
     samples = max(1, cam["numSamples"])
     n = int(math.sqrt(samples))
@@ -82,9 +82,9 @@ def primary_rays(cam: dict, i: int, j: int):
             cj = float(j) + (float(sy) + xi2) / float(n)
             s = (B["q00"] - B["v"] * (cj * B["dv"])) + B["u"] * (ci * B["du"])
             d = _norm(s - B["e"])
-            rng.next_float()  # ray time (:340)
+            time = rng.next_float()  # ray time (:340)
             t_img = _dot(B["m"] - B["e"], B["w"]) / _dot(d, B["w"])
-            out.append((B["e"].copy(), d, max(t_img, 0.0)))
+            out.append((B["e"].copy(), d, max(t_img, 0.0), time) if with_time else (B["e"].copy(), d, max(t_img, 0.0)))
     return out
 
 

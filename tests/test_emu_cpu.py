@@ -33,6 +33,12 @@ CASES = {
     "instances": (scenegen.config_instances, dict(width=64, height=48, samples=4), (1, 2)),
     # area lights: counting pass, per-chunk prefix, shading pass (general kernel); ragged image, glossy recursion
     "c3area": (scenegen.config_c3, dict(width=64, height=48, samples=4, depth=3, ico_level=2, area_lights=2), (2,)),
+    # motion blur: ray time down the path; mesh motion in the triangle test; instance motion through the exact walk of
+    # the reference-topology TLAS
+    "motion_mesh": (scenegen.config_instances, dict(width=64, height=48, samples=4, mesh_motion=(0.5, 0.2, -0.3)), (2,)),
+    "motion_instances": (scenegen.config_instances, dict(width=64, height=48, samples=4, instance_motion=1.0), (2,)),
+    "motion_both_ragged": (scenegen.config_instances, dict(width=50, height=37, samples=9, mesh_motion=(0.4, -0.3, 0.2),
+                                                           instance_motion=1.5), (2,)),
     "c3area_glossy_ragged": (scenegen.config_c3, dict(width=50, height=37, samples=1, depth=4, ico_level=2, area_lights=3,
                                                       roughness=0.1), (2,)),
 }
@@ -108,6 +114,18 @@ def test_emulated_area_lights_shard_by_chunks(scene_dir, emu):
         with pytest.raises(RenderError) as e:
             eng.render(0, **kw)
         assert e.value.code == -3
+
+
+def test_emulated_motion_blur_changes_the_frame_and_refuses_the_fast_kernel(scene_dir, emu):
+    from myraytracer_b200 import RenderError
+    still = RayTracerEngine(scenegen.config_instances(scene_dir, width=48, height=36, samples=4)).render(0).rgba
+    path = scenegen.config_instances(scene_dir, width=48, height=36, samples=4, instance_motion=1.5)
+    eng = RayTracerEngine(path)
+    moved = eng.render(0).rgba
+    assert (moved != still).any(axis=-1).mean() > 0.02           # the motion is visible
+    with pytest.raises(RenderError) as e:
+        eng.render(0, variant=1)
+    assert e.value.code == -3
 
 
 def test_emulator_is_not_the_product(emu):

@@ -29,6 +29,11 @@ CASES = {
     # area lights (8f row 3): light samples come from a 100-entry table through one running index per 8-row chunk —
     # counting pass, per-chunk prefix sum, shading pass (general kernel)
     "c3area": dict(fn=scenegen.config_c3, kw=dict(width=192, height=180, samples=4, area_lights=2)),
+    # motion blur (8f row 3): Mesh.motionBlur and MeshInstance.motionBlur
+    "motionmesh": dict(fn=scenegen.config_instances, kw=dict(mesh_motion=(0.5, 0.2, -0.3))),
+    "motioninst": dict(fn=scenegen.config_instances, kw=dict(width=200, height=150, samples=9, instance_motion=1.2)),
+    "motionboth": dict(fn=scenegen.config_instances, kw=dict(width=243, height=181, samples=4, mesh_motion=(0.4, -0.3, 0.2),
+                                                            instance_motion=1.5)),
     "c3areaglossy": dict(fn=scenegen.config_c3, kw=dict(width=150, height=117, samples=9, depth=4, roughness=0.2, area_lights=3)),
 }
 
@@ -76,7 +81,7 @@ def test_kernel_variants_vs_oracle(name, variant, scene_dir):
     assert same >= 0.9999, same
 
 
-@pytest.mark.parametrize("name", ["c1_small", "c2_small", "c3_small", "c5_small", "c3_area_small"])
+@pytest.mark.parametrize("name", ["c1_small", "c2_small", "c3_small", "c5_small", "c3_area_small", "motion_small"])
 def test_gpu_matches_committed_golden(name, scene_dir):
     """CUDA path vs the frozen oracle renders under tests/golden/ (tools/make_golden.py)."""
     import os
