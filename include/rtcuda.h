@@ -205,6 +205,15 @@ const char* rt_last_error(void);
 rt_scene_t* rt_scene_create(const rt_scene_desc* desc, int32_t device);
 void rt_scene_destroy(rt_scene_t* scene);
 int32_t rt_scene_get_info(const rt_scene_t* scene, rt_scene_info* out);
+/* Animation: new placements for the instances of a resident scene.  Replaces
+ * RTContext.refitTLAS (Models/RTContext.swift:883-928) + BVHBuilder.refit (Accelearion/BVH.swift:254-292): `instances`
+ * has the scene's instance count, every entry keeps its `blas`; localToWorld / worldToLocal / normalMatrix /
+ * worldBounds / materialOverride are taken as given.  The instance records go to the device and the TLAS boxes are
+ * refitted there, bottom-up, with the topology kept (one small kernel on `cudaStream`, NULL = default stream); the
+ * mesh BVHs, triangles and materials are untouched.  Blocking.  Scenes with instanceMotion are refused
+ * (RT_ERR_UNSUPPORTED): their TLAS is the reference's own topology, rebuilt per scene. */
+int32_t rt_scene_update_instances(rt_scene_t* scene, const rt_instance* instances, int64_t nInstances, void* cudaStream);
+
 /* The tile order the next frame of the last rendered geometry will use (rt_render_params.scheduleMode): returns the
  * number of tiles (0: nothing learnt yet, < 0: error) and copies min(n, capacity) entries — slot k draws tile
  * orderOut[k], tiles numbered row-major within the shard (8x4 pixels each).  No reference analogue; for tests. */

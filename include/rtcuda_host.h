@@ -34,6 +34,23 @@ int32_t rth_engine_instance_object_ids(const rth_engine_t* engine, int32_t* out,
 int32_t rth_engine_render(rth_engine_t* engine, int32_t cameraIndex, const rt_render_params* params, uint8_t* rgbaOut,
                           double* linearOut, rt_hit_id* idsOut, rt_stats* statsOut);
 
+/* RayTracerEngine.inspect(scene:format:) — RayTracer.swift:52-67: counts4 = meshes, triangles, spheres, planes
+ * (sceneMeshAndTriangleCounts, :208-227); the CameraSpec fields come from rth_engine_camera / rth_engine_camera_name. */
+int32_t rth_engine_inspect(const rth_engine_t* engine, int64_t* counts4, int32_t* camerasOut);
+int32_t rth_engine_camera_name(const rth_engine_t* engine, int32_t cameraIndex, char* imageNameOut, int32_t capacity,
+                               int32_t* idOut);
+
+/* Animation.  The reference's batch driver builds a new engine per frame file
+ * (BatchRender/BatchRender.swift:26-40) and its RTContext.refitTLAS (RTContext.swift:883-928) is never called; here a
+ * frame is a new set of instance transforms on a resident scene: n = instance count, 16 doubles (column-major
+ * localToWorld) per instance in RTContext order (analytic primitives, mesh instances, base meshes).  worldToLocal,
+ * normal matrix and world bounds are re-derived as refitTLAS does, then rt_scene_update_instances refits the TLAS. */
+int32_t rth_engine_set_instance_transforms(rth_engine_t* engine, const double* localToWorld, int64_t n);
+
+/* Headless replacement of makeCGImage + PNG output (Helpers/Image.swift; ImageIO is Apple-only): writes the RGBA8
+ * frame as .png (8-bit RGBA, stored deflate) or .ppm (binary P6), chosen by the extension.  Row 0 = top. */
+int32_t rth_image_write(const char* path, const uint8_t* rgba, int32_t width, int32_t height);
+
 rth_context_t* rth_context_create(const char* sceneUrl);
 void rth_context_destroy(rth_context_t* ctx);
 int32_t rth_context_describe(const rth_context_t* ctx, rt_scene_desc* out);

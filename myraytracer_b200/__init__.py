@@ -8,4 +8,4 @@ Layout:
   scenegen.py seeded synthetic scenes (the five BASELINE.json configs)
 """
 from . import capi  # noqa: F401
-from .engine import FlatContext, RayTracerEngine, RenderError, RenderResult  # noqa: F401
+from .engine import FlatContext, RayTracerEngine, RenderError, RenderResult, write_image  # noqa: F401

@@ -117,11 +117,12 @@ HIT_ID_DTYPE = np.dtype([("inst", "<i4"), ("kind", "<i4"), ("prim", "<i8"), ("t"
 
 # every symbol include/rtcuda.h and include/rtcuda_host.h declare
 EXPORTS = ["rt_abi_version", "rt_device_count", "rt_last_error", "rt_scene_create", "rt_scene_destroy",
-           "rt_scene_get_info", "rt_scene_get_schedule", "rt_render", "rt_render_device", "rt_render_finish",
+           "rt_scene_get_info", "rt_scene_get_schedule", "rt_scene_update_instances", "rt_render", "rt_render_device", "rt_render_finish",
            "rt_shared_buffer_create", "rt_shared_buffer_open", "rt_shared_buffer_close",
            "rth_last_error", "rth_engine_create", "rth_engine_destroy", "rth_engine_ready", "rth_engine_camera_count",
            "rth_engine_camera", "rth_engine_scene", "rth_engine_describe", "rth_engine_instance_object_ids",
-           "rth_engine_render", "rth_context_create", "rth_context_destroy", "rth_context_describe"]
+           "rth_engine_render", "rth_engine_inspect", "rth_engine_camera_name", "rth_engine_set_instance_transforms",
+           "rth_image_write", "rth_context_create", "rth_context_destroy", "rth_context_describe"]
 
 _lib = None
 
@@ -170,6 +171,11 @@ def declare(L):
     L.rth_engine_describe.argtypes = [vp, C.POINTER(rt_scene_desc)]
     L.rth_engine_instance_object_ids.argtypes = [vp, vp, C.c_int64]
     L.rth_engine_render.argtypes = [vp, C.c_int32, C.POINTER(rt_render_params), vp, vp, vp, C.POINTER(rt_stats)]
+    L.rt_scene_update_instances.argtypes = [vp, C.POINTER(rt_instance), C.c_int64, vp]
+    L.rth_engine_inspect.argtypes = [vp, C.POINTER(C.c_int64), C.POINTER(C.c_int32)]
+    L.rth_engine_camera_name.argtypes = [vp, C.c_int32, C.c_char_p, C.c_int32, C.POINTER(C.c_int32)]
+    L.rth_engine_set_instance_transforms.argtypes = [vp, C.POINTER(C.c_double), C.c_int64]
+    L.rth_image_write.argtypes = [C.c_char_p, vp, C.c_int32, C.c_int32]
     L.rth_context_create.restype = vp
     L.rth_context_create.argtypes = [C.c_char_p]
     L.rth_context_destroy.argtypes = [vp]

@@ -59,6 +59,15 @@ bool isIdentity34(const double* m16) {
 
 static const size_t kFrameStateBytes = 16 * sizeof(unsigned long long) + 64;
 
+// What an instance record needs from its BLAS (kept by the scene: rt_scene_update_instances re-derives the records)
+struct BlasInfo {
+    int kind = INST_MESH; int64_t prim = 0; int64_t matId = 0; int smooth = 0;
+    int32_t nodeBase = 0, triBase = 0, rootRef = kEmptyRef; int f64 = 0;
+    double lo[3], hi[3], centre[3];
+    double motion[3] = {0, 0, 0};      // Triangle.motionBlur of the mesh (RTContext.swift:280,345)
+    double payload[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // sphere c.xyz, r | plane c.xyz, n.xyz
+};
+
 struct rt_scene {
     int device = 0;
     DeviceScene ds{};
@@ -70,6 +79,16 @@ struct rt_scene {
     GAreaLight* dAreaLights = nullptr; double* dJitter = nullptr;
     RefNode* dRefTlas = nullptr; int32_t* dRefTlasPrim = nullptr;
     bool motion = false;               // Mesh.motionBlur or MeshInstance.motionBlur somewhere: ray time matters
+    // animation (rt_scene_update_instances): BLAS facts, TLAS topology and its bottom-up order
+    std::vector<BlasInfo> blasInfo;
+    std::vector<int32_t> instBlas;     // rt_instance.blas of every instance
+    bool instanceMotion = false;
+    TNode* dTlasD = nullptr;           // FP64 TLAS nodes (topology + boxes), refitted on the device
+    int* dRefitOrder = nullptr;        // node indices, deepest level first
+    std::vector<int> refitLevelStart;  // level l = dRefitOrder[refitLevelStart[l] .. refitLevelStart[l + 1])
+    int* dRefitLevelStart = nullptr;
+    double* dInstBounds = nullptr;     // Instance.worldBounds, 6 doubles per instance
+    GInstance* hInst = nullptr; double* hInstBounds = nullptr;   // pinned staging for the per-frame upload
     unsigned* dAreaIndex = nullptr; size_t areaIndexBytes = 0;   // per-pixel jitter index of an area-light frame
     // render state (re-used across calls)
     int* dTileCounter = nullptr; unsigned long long* dCounters = nullptr;
@@ -93,6 +112,41 @@ struct rt_scene {
     cudaStream_t pendingStream = nullptr;
     int64_t launches = 0;
 };
+
+
+// Instance (RTContext.swift:43-61) -> device record
+static void fillInstance(const rt_instance& in, const BlasInfo& bi, GInstance& g) {
+    std::memset(&g, 0, sizeof g);
+    for (int c = 0; c < 4; c++)
+        for (int r = 0; r < 3; r++) { g.w2l[c * 3 + r] = in.worldToLocal[c * 4 + r]; g.l2w[c * 3 + r] = in.localToWorld[c * 4 + r]; }
+    std::memcpy(g.nmat, in.normalMatrix, sizeof g.nmat);
+    std::memcpy(g.rootLo, bi.lo, 24); std::memcpy(g.rootHi, bi.hi, 24); std::memcpy(g.centre, bi.centre, 24);
+    g.kind = bi.kind;
+    g.identity = (isIdentity34(in.worldToLocal) && isIdentity34(in.localToWorld)) ? 1 : 0;
+    // simd_determinant of the upper 3x3 (RTContext.swift:691-698), same expansion as the oracle
+    const double* m = in.localToWorld;
+    const double c0[3] = {m[0], m[1], m[2]}, c1[3] = {m[4], m[5], m[6]}, c2[3] = {m[8], m[9], m[10]};
+    const double cx = c1[1] * c2[2] - c1[2] * c2[1], cy = c1[2] * c2[0] - c1[0] * c2[2], cz = c1[0] * c2[1] - c1[1] * c2[0];
+    g.flipNormal = ((c0[0] * cx + c0[1] * cy) + c0[2] * cz) < 0.0 ? 1 : 0;
+    g.smooth = bi.smooth;
+    g.nodeBase = bi.nodeBase; g.triBase = bi.triBase; g.triF64 = bi.f64; g.rootRef = bi.rootRef;
+    g.matId = in.hasMaterialOverride ? in.materialOverride : bi.matId;  // RTContext.swift:704
+    g.primIndex = bi.prim;
+    const bool moves = in.instanceMotion[0] != 0 || in.instanceMotion[1] != 0 || in.instanceMotion[2] != 0;
+    std::memcpy(g.motion, in.instanceMotion, 24); std::memcpy(g.meshMotion, bi.motion, 24);
+    g.hasMotion = (moves || bi.motion[0] != 0 || bi.motion[1] != 0 || bi.motion[2] != 0) ? 1 : 0;
+    std::memcpy(g.prim, bi.payload, sizeof g.prim);
+}
+
+// Scene bounds, their centre and the padding of the FP32 TLAS boxes from the root node
+static double tlasFrame(const TNode& r, double* sLo, double* sHi, double* sC) {
+    double M = 0;
+    for (int a = 0; a < 3; a++) {
+        sLo[a] = std::fmin(r.lo0[a], r.lo1[a]); sHi[a] = std::fmax(r.hi0[a], r.hi1[a]); sC[a] = 0.5 * (sLo[a] + sHi[a]);
+        M = std::fmax(M, std::fmax(std::fabs(sLo[a] - sC[a]), std::fabs(sHi[a] - sC[a])));
+    }
+    return std::fmax(M * std::ldexp(1.0, -19), 1e-30);
+}
 
 extern "C" {
 
@@ -133,13 +187,8 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     int deviceBuilt = 0;
 
     // ---- BLAS build (one per rt_blas, shared by instances)
-    struct BlasInfo {
-        int kind = INST_MESH; int64_t prim = 0; int64_t matId = 0; int smooth = 0;
-        int32_t nodeBase = 0, triBase = 0, rootRef = kEmptyRef; int f64 = 0;
-        double lo[3], hi[3], centre[3];
-        double motion[3] = {0, 0, 0};      // Triangle.motionBlur of the mesh (RTContext.swift:280,345)
-    };
-    std::vector<BlasInfo> blasInfo((size_t)d->nBlas);
+    std::vector<BlasInfo>& blasInfo = sc->blasInfo;
+    blasInfo.assign((size_t)d->nBlas, BlasInfo());
     std::vector<GNode> nodes;
     std::vector<GTri> tris;
     std::vector<GTriD> trisD;
@@ -156,12 +205,14 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
             if (pr[0].primitiveIndex < 0 || pr[0].primitiveIndex >= d->nSpheres) return fail(RT_ERR_INVALID, "sphere index out of range");
             const rt_sphere& s = d->spheres[pr[0].primitiveIndex];
             bi.kind = INST_SPHERE; bi.prim = pr[0].primitiveIndex;
+            bi.payload[0] = s.center[0]; bi.payload[1] = s.center[1]; bi.payload[2] = s.center[2]; bi.payload[3] = s.radius;
             for (int a = 0; a < 3; a++) { bi.lo[a] = s.center[a] - s.radius; bi.hi[a] = s.center[a] + s.radius; bi.centre[a] = s.center[a]; }
             continue;
         }
         if (bl.primCount == 1 && pr[0].type == RT_GEO_PLANE) {
             if (pr[0].primitiveIndex < 0 || pr[0].primitiveIndex >= d->nPlanes) return fail(RT_ERR_INVALID, "plane index out of range");
             bi.kind = INST_PLANE; bi.prim = pr[0].primitiveIndex;
+            { const rt_plane& pl = d->planes[bi.prim]; for (int a = 0; a < 3; a++) { bi.payload[a] = pl.center[a]; bi.payload[3 + a] = pl.normal[a]; } }
             for (int a = 0; a < 3; a++) { bi.lo[a] = -1e5; bi.hi[a] = 1e5; bi.centre[a] = 0; }  // RTContext.swift:172-174
             continue;
         }
@@ -229,28 +280,8 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
         if (in.blas < 0 || in.blas >= d->nBlas) return fail(RT_ERR_INVALID, "rt_instance.blas out of range");
         const bool moves = in.instanceMotion[0] != 0 || in.instanceMotion[1] != 0 || in.instanceMotion[2] != 0;
         if (moves) { sc->motion = true; instanceMotion = true; }
-        const BlasInfo& bi = blasInfo[in.blas];
-        GInstance& g = inst[i];
-        std::memset(&g, 0, sizeof g);
-        for (int c = 0; c < 4; c++)
-            for (int r = 0; r < 3; r++) { g.w2l[c * 3 + r] = in.worldToLocal[c * 4 + r]; g.l2w[c * 3 + r] = in.localToWorld[c * 4 + r]; }
-        std::memcpy(g.nmat, in.normalMatrix, sizeof g.nmat);
-        std::memcpy(g.rootLo, bi.lo, 24); std::memcpy(g.rootHi, bi.hi, 24); std::memcpy(g.centre, bi.centre, 24);
-        g.kind = bi.kind;
-        g.identity = (isIdentity34(in.worldToLocal) && isIdentity34(in.localToWorld)) ? 1 : 0;
-        // simd_determinant of the upper 3x3 (RTContext.swift:691-698), same expansion as the oracle
-        const double* m = in.localToWorld;
-        const double c0[3] = {m[0], m[1], m[2]}, c1[3] = {m[4], m[5], m[6]}, c2[3] = {m[8], m[9], m[10]};
-        const double cx = c1[1] * c2[2] - c1[2] * c2[1], cy = c1[2] * c2[0] - c1[0] * c2[2], cz = c1[0] * c2[1] - c1[1] * c2[0];
-        g.flipNormal = ((c0[0] * cx + c0[1] * cy) + c0[2] * cz) < 0.0 ? 1 : 0;
-        g.smooth = bi.smooth;
-        g.nodeBase = bi.nodeBase; g.triBase = bi.triBase; g.triF64 = bi.f64; g.rootRef = bi.rootRef;
-        g.matId = in.hasMaterialOverride ? in.materialOverride : bi.matId;  // RTContext.swift:704
-        g.primIndex = bi.prim;
-        std::memcpy(g.motion, in.instanceMotion, 24); std::memcpy(g.meshMotion, bi.motion, 24);
-        g.hasMotion = (moves || bi.motion[0] != 0 || bi.motion[1] != 0 || bi.motion[2] != 0) ? 1 : 0;
-        if (bi.kind == INST_SPHERE) { const rt_sphere& s = d->spheres[bi.prim]; g.prim[0] = s.center[0]; g.prim[1] = s.center[1]; g.prim[2] = s.center[2]; g.prim[3] = s.radius; }
-        if (bi.kind == INST_PLANE) { const rt_plane& p = d->planes[bi.prim]; for (int a = 0; a < 3; a++) { g.prim[a] = p.center[a]; g.prim[3 + a] = p.normal[a]; } }
+        fillInstance(in, blasInfo[in.blas], inst[i]);
+        sc->instBlas.push_back(in.blas);
         std::memcpy(&wb[i * 6], in.worldBounds, 48);
     }
     TlasBuildOutput tl;
@@ -324,13 +355,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     std::vector<GNode> tlasF(tl.nodes.size());
     double sLo[3] = {0, 0, 0}, sHi[3] = {0, 0, 0}, sC[3] = {0, 0, 0};
     if (!tl.nodes.empty()) {
-        const TNode& r = tl.nodes[0];
-        double M = 0;
-        for (int a = 0; a < 3; a++) {
-            sLo[a] = std::fmin(r.lo0[a], r.lo1[a]); sHi[a] = std::fmax(r.hi0[a], r.hi1[a]); sC[a] = 0.5 * (sLo[a] + sHi[a]);
-            M = std::fmax(M, std::fmax(std::fabs(sLo[a] - sC[a]), std::fabs(sHi[a] - sC[a])));
-        }
-        const double P = std::fmax(M * std::ldexp(1.0, -19), 1e-30);
+        const double P = tlasFrame(tl.nodes[0], sLo, sHi, sC);
         auto down = [](double x) { float f = (float)x; return (double)f > x ? std::nextafterf(f, -INFINITY) : f; };
         auto up = [](double x) { float f = (float)x; return (double)f < x ? std::nextafterf(f, INFINITY) : f; };
         for (size_t i = 0; i < tl.nodes.size(); i++) {
@@ -346,6 +371,31 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
             g.q2[0] = lo1[2]; g.q2[1] = hi1[0]; g.q2[2] = hi1[1]; g.q2[3] = hi1[2];
             g.child0 = t.child0; g.child1 = t.child1; g.pad0 = g.pad1 = 0;
         }
+    }
+    // animation support: the FP64 TLAS, its nodes grouped by depth (deepest first) for the bottom-up refit kernel,
+    // the instances' world bounds, pinned staging for the per-frame instance upload
+    {
+        std::vector<int> depth(tl.nodes.size(), 0), order(tl.nodes.size());
+        int maxD = 0;
+        for (size_t i = 0; i < tl.nodes.size(); i++) {       // pre-order: a child's index is above its parent's
+            const int32_t ch[2] = {tl.nodes[i].child0, tl.nodes[i].child1};
+            for (int c = 0; c < 2; c++)
+                if (ch[c] >= 0 && ch[c] != kEmptyRef) { depth[ch[c]] = depth[i] + 1; if (depth[ch[c]] > maxD) maxD = depth[ch[c]]; }
+        }
+        sc->refitLevelStart.assign(1, 0);
+        size_t k = 0;
+        for (int lv = maxD; lv >= 0 && !tl.nodes.empty(); lv--) {
+            for (size_t i = 0; i < tl.nodes.size(); i++) if (depth[i] == lv) order[k++] = (int)i;
+            sc->refitLevelStart.push_back((int)k);
+        }
+        if ((rc = upload(tl.nodes, &sc->dTlasD, bytes))) return rc;
+        if ((rc = upload(order, &sc->dRefitOrder, bytes))) return rc;
+        if ((rc = upload(sc->refitLevelStart, &sc->dRefitLevelStart, bytes))) return rc;
+        if ((rc = upload(wb, &sc->dInstBounds, bytes))) return rc;
+        const size_t n = (size_t)d->nInstances;
+        CK(cudaMallocHost((void**)&sc->hInst, (n ? n : 1) * sizeof(GInstance)));
+        CK(cudaMallocHost((void**)&sc->hInstBounds, (n ? n : 1) * 6 * sizeof(double)));
+        sc->instanceMotion = instanceMotion;
     }
     if ((rc = upload(tlasF, &sc->dTlas, bytes))) return rc;
     if ((rc = upload(inst, &sc->dInst, bytes))) return rc;
@@ -401,6 +451,9 @@ void rt_scene_destroy(rt_scene_t* sc) {
     cudaFree(sc->dInst); cudaFree(sc->dMat); cudaFree(sc->dLights); cudaFree(sc->dCounters);
     cudaFree(sc->dAreaLights); cudaFree(sc->dJitter); cudaFree(sc->dAreaIndex);
     cudaFree(sc->dRefTlas); cudaFree(sc->dRefTlasPrim);
+    cudaFree(sc->dTlasD); cudaFree(sc->dRefitOrder); cudaFree(sc->dRefitLevelStart); cudaFree(sc->dInstBounds);
+    if (sc->hInst) cudaFreeHost(sc->hInst);
+    if (sc->hInstBounds) cudaFreeHost(sc->hInstBounds);
     cudaFree(sc->dTileCost); cudaFree(sc->dTileOrder); cudaFree(sc->dSchedWork);
     cudaFree(sc->dPathStack); cudaFree(sc->dRgba); cudaFree(sc->dLinear); cudaFree(sc->dIds);
     if (sc->hCounters) cudaFreeHost(sc->hCounters);
@@ -425,6 +478,47 @@ rt_scene_t* rt_scene_create(const rt_scene_desc* desc, int32_t device) {
     }
     if (sc) rt_scene_destroy(sc);
     return nullptr;
+}
+
+int32_t rt_scene_update_instances(rt_scene_t* sc, const rt_instance* instances, int64_t nInstances, void* cudaStream) {
+    if (!sc) return fail(RT_ERR_NO_SCENE, "No scene loaded. Can't render.");
+    if (sc->pending) return fail(RT_ERR_INVALID, "a render is in flight on this scene (call rt_render_finish)");
+    if (!instances || nInstances != (int64_t)sc->instBlas.size())
+        return fail(RT_ERR_INVALID, "rt_scene_update_instances: the instance count of a scene is fixed");
+    if (sc->instanceMotion)
+        return fail(RT_ERR_UNSUPPORTED, "scenes with instanceMotion walk the reference's own TLAS topology: rebuild the scene instead");
+    CK(cudaSetDevice(sc->device));
+    cudaStream_t st = (cudaStream_t)cudaStream;
+    const size_t n = (size_t)nInstances;
+    if (sc->sideBusy) CK(cudaEventSynchronize(sc->evSide));      // the previous frame's epilogue is done
+    for (size_t i = 0; i < n; i++) {
+        const rt_instance& in = instances[i];
+        if (in.blas != sc->instBlas[i]) return fail(RT_ERR_INVALID, "rt_scene_update_instances: an instance keeps its BLAS");
+        if (in.instanceMotion[0] != 0 || in.instanceMotion[1] != 0 || in.instanceMotion[2] != 0)
+            return fail(RT_ERR_UNSUPPORTED, "rt_scene_update_instances: instanceMotion cannot be introduced by an update");
+        fillInstance(in, sc->blasInfo[in.blas], sc->hInst[i]);
+        std::memcpy(sc->hInstBounds + i * 6, in.worldBounds, 48);
+    }
+    CK(cudaMemcpyAsync(sc->dInst, sc->hInst, n * sizeof(GInstance), cudaMemcpyHostToDevice, st));
+    if (sc->info.tlasNodes > 0) {
+        // scene bounds (the union of the instance bounds), their centre and the box padding: host, O(instances)
+        TNode root{};
+        for (int a = 0; a < 3; a++) { root.lo0[a] = root.lo1[a] = INFINITY; root.hi0[a] = root.hi1[a] = -INFINITY; }
+        for (size_t i = 0; i < n; i++)
+            for (int a = 0; a < 3; a++) {
+                root.lo0[a] = std::fmin(root.lo0[a], instances[i].worldBounds[a]);
+                root.hi0[a] = std::fmax(root.hi0[a], instances[i].worldBounds[3 + a]);
+            }
+        std::memcpy(root.lo1, root.lo0, 24); std::memcpy(root.hi1, root.hi0, 24);
+        double sLo[3], sHi[3], sC[3];
+        const double P = tlasFrame(root, sLo, sHi, sC);
+        CK(cudaMemcpyAsync(sc->dInstBounds, sc->hInstBounds, n * 6 * sizeof(double), cudaMemcpyHostToDevice, st));
+        CK(launchTlasRefit(sc->dTlasD, sc->dTlas, sc->dInstBounds, sc->dRefitOrder, sc->dRefitLevelStart,
+                           (int)sc->refitLevelStart.size() - 1, sC, P, st));
+        std::memcpy(sc->ds.tlasLo, sLo, 24); std::memcpy(sc->ds.tlasHi, sHi, 24); std::memcpy(sc->ds.tlasCentre, sC, 24);
+    }
+    CK(cudaStreamSynchronize(st));       // the staging buffers are free again when this returns
+    return RT_OK;
 }
 
 int32_t rt_scene_get_info(const rt_scene_t* sc, rt_scene_info* out) {

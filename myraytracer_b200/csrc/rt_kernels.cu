@@ -142,6 +142,58 @@ cudaError_t launchAreaPrefix(unsigned* areaIndex, int width, int height, int sha
     return cudaGetLastError();
 }
 
+// ---- animation: TLAS refit ---------------------------------------------------------------------------------------
+// One block walks the levels of the tree from the deepest to the root (order / levelStart from rt_scene_create); a
+// node takes each child's box from the instance bounds (leaf) or from the union of that child's two boxes (inner
+// node, refitted one level earlier) and re-encodes its record for the traversal kernels: FP32 relative to the scene
+// centre, padded by P and rounded outward (the encoding of rt_scene_create).
+#define RT_REFIT_THREADS 256
+struct RefitFrame { double c[3]; double pad; };
+__global__ void __launch_bounds__(RT_REFIT_THREADS) tlasRefitKernel(TNode* __restrict__ tn, GNode* __restrict__ out,
+                                                                    const double* __restrict__ instBounds, const int* __restrict__ order,
+                                                                    const int* __restrict__ levelStart, int nLevels, RefitFrame F) {
+    for (int lv = 0; lv < nLevels; lv++) {
+        for (int k = levelStart[lv] + (int)threadIdx.x; k < levelStart[lv + 1]; k += RT_REFIT_THREADS) {
+            const int ni = order[k];
+            TNode t = tn[ni];
+            const int32_t ch[2] = {t.child0, t.child1};
+            double* lo[2] = {t.lo0, t.lo1};
+            double* hi[2] = {t.hi0, t.hi1};
+            for (int c = 0; c < 2; c++) {
+                if (ch[c] == kEmptyRef) continue;
+                if (ch[c] < 0) {
+                    const double* b = instBounds + (size_t)(~ch[c]) * 6;
+                    for (int a = 0; a < 3; a++) { lo[c][a] = b[a]; hi[c][a] = b[3 + a]; }
+                } else {
+                    const TNode& s = tn[ch[c]];
+                    for (int a = 0; a < 3; a++) { lo[c][a] = fmin(s.lo0[a], s.lo1[a]); hi[c][a] = fmax(s.hi0[a], s.hi1[a]); }
+                }
+            }
+            tn[ni] = t;
+            GNode g;
+            float l0[3], h0[3], l1[3], h1[3];
+            for (int a = 0; a < 3; a++) {
+                l0[a] = __double2float_rd(t.lo0[a] - F.c[a] - F.pad); h0[a] = __double2float_ru(t.hi0[a] - F.c[a] + F.pad);
+                l1[a] = __double2float_rd(t.lo1[a] - F.c[a] - F.pad); h1[a] = __double2float_ru(t.hi1[a] - F.c[a] + F.pad);
+            }
+            g.q0[0] = l0[0]; g.q0[1] = l0[1]; g.q0[2] = l0[2]; g.q0[3] = h0[0];
+            g.q1[0] = h0[1]; g.q1[1] = h0[2]; g.q1[2] = l1[0]; g.q1[3] = l1[1];
+            g.q2[0] = l1[2]; g.q2[1] = h1[0]; g.q2[2] = h1[1]; g.q2[3] = h1[2];
+            g.child0 = t.child0; g.child1 = t.child1; g.pad0 = g.pad1 = 0;
+            out[ni] = g;
+        }
+        __syncthreads();
+    }
+}
+
+cudaError_t launchTlasRefit(TNode* tlasD, GNode* tlasOut, const double* instBounds, const int* order, const int* levelStart,
+                            int nLevels, const double* centre, double pad, cudaStream_t stream) {
+    RefitFrame F;
+    F.c[0] = centre[0]; F.c[1] = centre[1]; F.c[2] = centre[2]; F.pad = pad;
+    if (nLevels > 0) RT_LAUNCH(tlasRefitKernel, 1, RT_REFIT_THREADS, stream, tlasD, tlasOut, instBounds, order, levelStart, nLevels, F);
+    return cudaGetLastError();
+}
+
 size_t scheduleWorkBytes(int nTiles) {
     return (size_t)((nTiles + RT_SCHED_THREADS - 1) / RT_SCHED_THREADS) * RT_SCHED_CLASSES * sizeof(unsigned);
 }

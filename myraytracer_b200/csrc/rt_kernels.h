@@ -63,6 +63,10 @@ cudaError_t launchRender(int variant, const DeviceScene& S, const CameraParams& 
 // tileCost (clocks per tile of the frame just rendered) -> tileOrder for the next frame, longest first; clears tileCost
 // areaIndex: per-pixel draw counts -> per-pixel first jitter index, for the 8-row chunks of this shard (rows mode)
 cudaError_t launchAreaPrefix(unsigned* areaIndex, int width, int height, int shardIndex, int shardCount, cudaStream_t stream);
+// Animation: bottom-up refit of the TLAS after rt_scene_update_instances (topology kept, like BVHBuilder.refit,
+// Accelearion/BVH.swift:254-292): FP64 boxes in tlasD, conservative FP32 encoding (centre, padding P) in tlasOut.
+cudaError_t launchTlasRefit(TNode* tlasD, GNode* tlasOut, const double* instBounds, const int* order, const int* levelStart,
+                            int nLevels, const double* centre, double pad, cudaStream_t stream);
 cudaError_t launchSchedule(unsigned* tileCost, int* tileOrder, unsigned* work, int nTiles, cudaStream_t stream);
 size_t scheduleWorkBytes(int nTiles);   // scratch of launchSchedule
 int renderBlockSize(int variant);

@@ -109,6 +109,54 @@ class RayTracerEngine:
         self._lib.rth_engine_instance_object_ids(self._h, _ptr(out), n)
         return out
 
+    def inspect(self) -> dict:
+        """RayTracerEngine.inspect(scene:format:) (RayTracer.swift:52-67): SceneInfo as a dict."""
+        counts = (C.c_int64 * 4)()
+        ncam = C.c_int32()
+        rc = self._lib.rth_engine_inspect(self._h, counts, C.byref(ncam))
+        if rc != 0:
+            raise RenderError(rc, self._lib.rth_last_error().decode())
+        cams = []
+        for i in range(ncam.value):
+            name = C.create_string_buffer(256)
+            cid = C.c_int32()
+            self._lib.rth_engine_camera_name(self._h, i, name, 256, C.byref(cid))
+            cam = self.camera(i)
+            cams.append(dict(index=i, id=cid.value, imageName=name.value.decode(), width=cam.width, height=cam.height))
+        return dict(cameras=cams, meshes=counts[0], triangles=counts[1], spheres=counts[2], planes=counts[3])
+
+    def render_all(self, progress: Optional[Callable[[float, str], bool]] = None, **kw):
+        """RayTracerEngine.renderAll(progress:) (RayTracer.swift:70-103): every camera in order; the image name is
+        the camera's imageName or "Camera-<index>".  progress(fraction, message) -> keep going?"""
+        info = self.inspect()
+        total = max(1, sum(max(1, c["height"]) for c in info["cameras"]))
+        done_rows = 0
+        out = []
+        for c in info["cameras"]:
+            h = max(1, c["height"])
+            base = done_rows
+            cb = None
+            if progress is not None:
+                def cb(done, rows, base=base, c=c, h=h):
+                    y = min(h - 1, max(0, done - 1))
+                    return progress((base + y + 1) / total, f"Camera {c['index'] + 1}/{len(info['cameras'])} — Row {y + 1}/{h}")
+            res = self.render(c["index"], progress=cb, **kw)
+            out.append((c["imageName"] or f"Camera-{c['index']}", res))
+            done_rows += h
+        if progress is not None:
+            progress(1.0, "Done")
+        return out
+
+    # -- animation --------------------------------------------------------
+    def set_instance_transforms(self, local_to_world) -> None:
+        """A new frame of an animation: one column-major 4x4 localToWorld per instance (RTContext order).  Replaces
+        the per-frame engine rebuild of BatchRender.swift:26-40 by RTContext.refitTLAS semantics
+        (RTContext.swift:883-928): instance records re-derived, TLAS boxes refitted on the device."""
+        m = np.ascontiguousarray(np.asarray(local_to_world, np.float64).reshape(-1, 16))
+        rc = self._lib.rth_engine_set_instance_transforms(self._h, m.ctypes.data_as(C.POINTER(C.c_double)), m.shape[0])
+        if rc != 0:
+            raise RenderError(rc, self._lib.rth_last_error().decode())
+
     # -- render -----------------------------------------------------------
     def render(self, camera_index: int = 0, want_linear: bool = False, want_ids: bool = False,
                shard_index: int = 0, shard_count: int = 1, counters: bool = False,
@@ -166,6 +214,16 @@ class RayTracerEngine:
         if rc != 0:
             raise RenderError(rc, self._lib.rt_last_error().decode())
         return st.as_dict()
+
+
+def write_image(path: str, rgba: np.ndarray) -> None:
+    """Headless stand-in for makeCGImage + PNG output (Helpers/Image.swift): .png or .ppm by extension."""
+    a = np.ascontiguousarray(rgba, np.uint8)
+    if a.ndim != 3 or a.shape[2] != 4:
+        raise ValueError("rgba must be (H, W, 4) uint8")
+    rc = capi.load().rth_image_write(path.encode(), a.ctypes.data_as(C.c_void_p), a.shape[1], a.shape[0])
+    if rc != 0:
+        raise RenderError(rc, f"cannot write {path}")
 
 
 class FlatContext:

@@ -43,6 +43,20 @@ int Renderer::render(const pk::Scene& scene, int cameraIndex, std::vector<double
                      ids ? ids->data() : nullptr, stats);
 }
 
+int Renderer::refit(const RTContext& ctx) {
+    return rt_scene_update_instances(handle_, ctx.instances.data(), (int64_t)ctx.instances.size(), nullptr);
+}
+
+int RayTracerEngine::setInstanceTransforms(const double* l2w, int64_t n, RenderError& err) {
+    if (!hasScene_) { err = {"Render", -20, "No scene loaded. Can't render."}; return -20; }
+    if (!renderer_) { err = {"Render", -21, "Renderer not initialized."}; return -21; }
+    if (!l2w || n != (int64_t)ctx_.instances.size()) { err = {"Render", RT_ERR_INVALID, "one transform per instance is required"}; return RT_ERR_INVALID; }
+    for (int64_t i = 0; i < n; i++) ctx_.setInstanceTransform((size_t)i, l2w + i * 16);
+    const int rc = renderer_->refit(ctx_);
+    if (rc != RT_OK) err = {"Render", rc, rt_last_error()};
+    return rc;
+}
+
 RayTracerEngine::RayTracerEngine(const std::string& url, int device) {
     std::string err;
     if (!pk::loadSceneBlob(url.c_str(), scene_, err)) {   // "Error decoding scene" -> engine stays empty (:38-40)
@@ -182,6 +196,34 @@ int32_t rth_engine_render(rth_engine_t* h, int32_t cameraIndex, const rt_render_
         statsOut->meshes = m; statsOut->spheres = s; statsOut->planes = p;
     }
     return rc;
+}
+
+int32_t rth_engine_set_instance_transforms(rth_engine_t* h, const double* l2w, int64_t n) {
+    auto* e = reinterpret_cast<rthost::RayTracerEngine*>(h);
+    if (!e) { g_herr = "No scene loaded. Can't render."; return -20; }
+    rthost::RenderError err{"", 0, ""};
+    const int rc = e->setInstanceTransforms(l2w, n, err);
+    if (rc != 0) g_herr = err.message;
+    return rc;
+}
+
+int32_t rth_engine_inspect(const rth_engine_t* h, int64_t* counts4, int32_t* camerasOut) {
+    auto* e = reinterpret_cast<const rthost::RayTracerEngine*>(h);
+    if (!e || !e->hasScene()) { g_herr = "No scene loaded. Can't render."; return -20; }
+    const rthost::SceneInfo si = e->inspect();
+    if (counts4) { counts4[0] = si.meshes; counts4[1] = si.triangles; counts4[2] = si.spheres; counts4[3] = si.planes; }
+    if (camerasOut) *camerasOut = (int32_t)si.cameras.size();
+    return 0;
+}
+
+int32_t rth_engine_camera_name(const rth_engine_t* h, int32_t idx, char* out, int32_t capacity, int32_t* idOut) {
+    auto* e = reinterpret_cast<const rthost::RayTracerEngine*>(h);
+    if (!e || !e->hasScene()) { g_herr = "No scene loaded. Can't render."; return -20; }
+    if (idx < 0 || idx >= (int32_t)e->scene().cameras.size()) { g_herr = "Invalid camera index"; return -10; }
+    const pk::Camera& c = e->scene().cameras[idx];
+    if (out && capacity > 0) { std::strncpy(out, c.imageName.c_str(), (size_t)capacity - 1); out[capacity - 1] = 0; }
+    if (idOut) *idOut = c.id;
+    return 0;
 }
 
 // Flatten only (no GPU): lets CPU tests compare the mirror's RTContext with the oracle's.

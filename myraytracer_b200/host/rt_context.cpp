@@ -69,7 +69,27 @@ void transformBox(const double* lo, const double* hi, const double* M, double* o
     for (int r = 0; r < 3; r++) { olo[r] = cN[r] - eN[r]; ohi[r] = cN[r] + eN[r]; }
 }
 
+// localToWorld -> worldToLocal, normalMatrix, worldBounds of an instance (makeInstance :437-456, refitTLAS :889-912)
+void placeInstance(rt_instance& in, const double* m16, const std::vector<double>& pb) {
+    std::memcpy(in.localToWorld, m16, sizeof in.localToWorld);
+    inverse4(m16, in.worldToLocal);
+    normalMatrix(m16, in.normalMatrix);
+    const double inf = std::numeric_limits<double>::infinity();
+    double lo[3] = {inf, inf, inf}, hi[3] = {-inf, -inf, -inf};
+    for (size_t k = 0; k + 5 < pb.size(); k += 6) {
+        double tl[3], th[3];
+        transformBox(&pb[k], &pb[k + 3], m16, tl, th);
+        for (int a = 0; a < 3; a++) { lo[a] = mn(lo[a], tl[a]); hi[a] = mx(hi[a], th[a]); }
+    }
+    for (int a = 0; a < 3; a++) { in.worldBounds[a] = lo[a]; in.worldBounds[3 + a] = hi[a]; }
+}
+
 }  // namespace
+
+void RTContext::setInstanceTransform(size_t i, const double* m16) {
+    rt_instance& in = instances.at(i);
+    placeInstance(in, m16, blasPrimBounds.at((size_t)in.blas));
+}
 
 RTContext::RTContext(const pk::Scene& scene) {
     intersectionTestEpsilon = scene.intersectionTestEpsilon;
@@ -97,26 +117,13 @@ RTContext::RTContext(const pk::Scene& scene) {
         if (k >= scene.vertexData.size()) { warnings.push_back("vertex index out of range"); return D3{0, 0, 0}; }
         return d3(scene.vertexData[k]);
     };
-    // local-space bounds of every prim of a BLAS, kept to compute Instance.worldBounds (makeInstance, :437-447)
-    std::vector<std::vector<double>> blasPrimBounds;
 
     auto addInstance = [&](int32_t blasIdx, const pk::M4& M, bool hasOverride, int64_t matOverride, D3 motion, int32_t objectId) {
         rt_instance in{};
         in.blas = blasIdx;
         in.hasMaterialOverride = hasOverride ? 1 : 0;
         in.materialOverride = matOverride;
-        std::memcpy(in.localToWorld, M.m, sizeof in.localToWorld);
-        inverse4(M.m, in.worldToLocal);
-        normalMatrix(M.m, in.normalMatrix);
-        const double inf = std::numeric_limits<double>::infinity();
-        double lo[3] = {inf, inf, inf}, hi[3] = {-inf, -inf, -inf};
-        const std::vector<double>& pb = blasPrimBounds[blasIdx];
-        for (size_t k = 0; k + 5 < pb.size(); k += 6) {
-            double tl[3], th[3];
-            transformBox(&pb[k], &pb[k + 3], M.m, tl, th);
-            for (int a = 0; a < 3; a++) { lo[a] = mn(lo[a], tl[a]); hi[a] = mx(hi[a], th[a]); }
-        }
-        for (int a = 0; a < 3; a++) { in.worldBounds[a] = lo[a]; in.worldBounds[3 + a] = hi[a]; }
+        placeInstance(in, M.m, blasPrimBounds[blasIdx]);
         put(in.instanceMotion, motion);
         if (motion.x != 0 || motion.y != 0 || motion.z != 0) anyMotionBlur = true;
         instances.push_back(in);

@@ -471,7 +471,8 @@ def config_c5(out_dir: str, n: int = 708, width: int = 3840, height: int = 2160,
 
 
 def config_instances(out_dir: str, width: int = 256, height: int = 192, samples: int = 4, depth: int = 3,
-                     mesh_motion: Sequence[float] = (0.0, 0.0, 0.0), instance_motion: float = 0.0) -> str:
+                     mesh_motion: Sequence[float] = (0.0, 0.0, 0.0), instance_motion: float = 0.0, frame: float = 0.0,
+                     name: str = "instances") -> str:
     """Not one of BASELINE.json's configs: the object kinds they leave out.  An infinite ground plane (its 1e5 bounds,
     RTContext.swift:172-174, stretch the scene box), one PLY mesh and three MeshInstances of it sharing its BLAS
     (:384-401): one with a material override, one mirrored (negative determinant -> flipped normals, :691-698),
@@ -479,7 +480,9 @@ def config_instances(out_dir: str, width: int = 256, height: int = 192, samples:
     Motion blur: `mesh_motion` is the base mesh's Mesh.motionBlur (local space, applied in the
     triangle test, boxes grown by it, RTContext.swift:283-289,480-481); `instance_motion` scales the
     MeshInstance.motionBlur vectors of the three instances (world space, applied to the ray origin before the
-    instance transform while the instance boxes stay where they are, :437-455,658-661)."""
+    instance transform while the instance boxes stay where they are, :437-455,658-661).
+    Animation (8f row 4): `frame` moves, turns and scales the mesh, its instances and the sphere's placement —
+    same objects, same BLASes, other transforms."""
     pos, tris = icosphere_mesh(2, radius=1.0, seed=7, disp=0.15)
     write_ply(os.path.join(out_dir, "inst_blob.ply"), pos, tris)
     sc = Scene(maxRecursionDepth=depth, backgroundColor=(12, 14, 20), ambient=(20, 20, 20))
@@ -491,13 +494,15 @@ def config_instances(out_dir: str, width: int = 256, height: int = 192, samples:
                     Material(id=5, type=MAT_DIELECTRIC, ambient=(0, 0, 0), diffuse=(0.02, 0.02, 0.02), specular=(0.2, 0.2, 0.2),
                              mirror=(1, 1, 1), absorption=(0.02, 0.06, 0.04), phong=200.0, ior=1.5)]
     sc.vertexData = np.asarray([(0.0, 0.0, 0.0), (0.8, 1.1, 4.0)], np.float64)
-    Mm = mat_translate((-0.5, 1.4, 0.0)) @ mat_rotate((0.2, 1.0, 0.1), 20.0) @ mat_scale((1.3, 1.3, 1.3))
-    Ma = mat_translate((3.2, 1.1, -2.5)) @ mat_scale((0.9, 1.1, 0.9))
-    Mb = mat_translate((-3.6, 1.2, -1.5)) @ mat_scale((-1.0, 1.0, 1.0))          # mirrored: det < 0
-    Mc = mat_translate((0.5, 3.6, -3.0)) @ mat_scale((0.6, 0.6, 0.6))
+    f = float(frame)
+    Mm = mat_translate((-0.5 + 0.4 * f, 1.4, 0.3 * f)) @ mat_rotate((0.2, 1.0, 0.1), 20.0 + 35.0 * f) @ mat_scale((1.3, 1.3, 1.3))
+    Ma = mat_translate((3.2 - 0.8 * f, 1.1 + 0.5 * f, -2.5)) @ mat_rotate((0.0, 0.0, 1.0), 50.0 * f) @ mat_scale((0.9, 1.1 + 0.2 * f, 0.9))
+    Mb = mat_translate((-3.6, 1.2 + 0.6 * f, -1.5 + 1.2 * f)) @ mat_scale((-1.0, 1.0, 1.0))          # mirrored: det < 0
+    Mc = mat_translate((0.5 + 1.5 * f, 3.6 - 0.7 * f, -3.0)) @ mat_rotate((1.0, 0.3, 0.0), -40.0 * f) @ mat_scale((0.6, 0.6, 0.6))
+    Ms = mat_translate((-1.2 * f, 0.3 * f, 0.5 * f))                               # the sphere's object transform
     sc.objects = [
         SceneObject(OBJ_PLANE, id=1, material=1, centerIdx=1, normal=(0.0, 1.0, 0.0)),
-        SceneObject(OBJ_SPHERE, id=2, material=5, centerIdx=2, radius=1.0),
+        SceneObject(OBJ_SPHERE, id=2, material=5, centerIdx=2, radius=1.0, transform=colmajor(Ms)),
         SceneObject(OBJ_MESH, id=5, material=2, smooth=True, plyPath="inst_blob.ply", transform=colmajor(Mm),
                     motionBlur=tuple(mesh_motion)),
         SceneObject(OBJ_MESH_INSTANCE, id=6, material=4, baseMeshID=5, transform=colmajor(Ma),
@@ -511,7 +516,7 @@ def config_instances(out_dir: str, width: int = 256, height: int = 192, samples:
     sc.cameras = [Camera(id=1, imageName="instances.png", width=width, height=height, numSamples=samples,
                          position=(0.5, 4.5, 12.0), gazePoint=(0.0, 1.2, 0.0), up=(0, 1, 0),
                          nearDistance=1.0, fovy=45.0, isLookAt=True)]
-    path = os.path.join(out_dir, "instances.rtscene")
+    path = os.path.join(out_dir, f"{name}.rtscene")
     write_rtscene(sc, path)
     return path
 

@@ -135,3 +135,64 @@ def test_device_tile_enumeration_matches_owned_mask(tmp_path):
                 want = {(x, y) for y in range(0, H, 4) for x in range(0, W, 8) if m[y, x]}
                 assert inside == want
                 assert all(x % 8 == 0 and y % 4 == 0 for x, y in tiles)
+
+
+# ---------------------------------------------------------------------------------- frame-parallel animation
+def _anim_worker(rank, world, port, scene_dir, q):
+    """One rank of AnimationRenderer over gloo.  There is no GPU here, so the engine underneath is the emulation build
+    of the product sources (tests/emu, test infrastructure) — the frame assignment, the per-frame instance update
+    and the stats reduction are the product's."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import numpy as np
+    import emu_lib
+    from myraytracer_b200 import scenegen
+    from myraytracer_b200.engine import FlatContext
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    kw = dict(width=40, height=32, samples=1)
+    shared_dir = scene_dir
+    scene_dir = os.path.join(shared_dir, f"rank{rank}")           # the generators write the PLY next to the scene
+    os.makedirs(scene_dir, exist_ok=True)
+    with emu_lib.use_emulator():
+        frames = [0.0, 0.25, 0.5, 0.75, 1.0]
+        tf = []
+        for f in frames:
+            tf.append(FlatContext(scenegen.config_instances(scene_dir, frame=f, name=f"r{rank}f{f}", **kw)).instances()["l2w"])
+        A = D.AnimationRenderer(scenegen.config_instances(scene_dir, name=f"r{rank}base", **kw), rank=rank, world=world)
+        out_dir = os.path.join(shared_dir, "frames")
+        os.makedirs(out_dir, exist_ok=True)
+        mine = A.render_frames(np.asarray(tf), out_dir=out_dir)
+        stats = A.gather_stats()
+        dist.barrier()
+        if rank == 0:
+            S = D.AnimationRenderer(scenegen.config_instances(scene_dir, name="single", **kw), rank=0, world=1)
+            allf = S.render_frames(np.asarray(tf))
+            ok = sorted(mine) == list(D.frames_of_rank(len(frames), 0, world))
+            ok = ok and all(np.array_equal(mine[f].rgba, allf[f].rgba) for f in mine)
+            ok = ok and stats["rays"] == sum(int(r.stats["rays"]) for r in allf.values())
+            ok = ok and sorted(os.listdir(out_dir)) == [f"frame_{f:04d}.png" for f in range(len(frames))]
+            q.put(bool(ok))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_frames_of_rank_partition():
+    for n, world in [(5, 2), (7, 3), (3, 8), (0, 2)]:
+        seen = sorted(f for r in range(world) for f in D.frames_of_rank(n, r, world))
+        assert seen == list(range(n))
+
+
+def test_animation_frames_across_ranks_gloo(tmp_path):
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_anim_worker, args=(r, world, port, str(tmp_path), q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=300)
+        assert p.exitcode == 0
+    assert q.get(timeout=10) is True

@@ -128,6 +128,59 @@ def test_emulated_motion_blur_changes_the_frame_and_refuses_the_fast_kernel(scen
     assert e.value.code == -3
 
 
+def test_emulated_animation_refit_matches_rebuilt_scenes(scene_dir, emu):
+    """rt_scene_update_instances: new instance transforms on a resident scene (records re-derived, TLAS refitted by the
+    device kernel, topology kept) give the frame of a scene built from scratch with those transforms — and the
+    oracle's — for every frame, and going back to frame 0 gives frame 0."""
+    from myraytracer_b200.engine import FlatContext
+    kw = dict(width=64, height=48, samples=4)
+    eng = RayTracerEngine(scenegen.config_instances(scene_dir, **kw))
+    base = eng.render(0, want_linear=True)
+    for f in (0.5, 1.0, 0.0):
+        pf = scenegen.config_instances(scene_dir, frame=f, name=f"frame{f}", **kw)
+        eng.set_instance_transforms(FlatContext(pf).instances()["l2w"])
+        got = eng.render(0, want_ids=True, want_linear=True)
+        check(got, oracle_lib.OracleScene(pf).render(want_ids=True, want_linear=True))
+        fresh = RayTracerEngine(pf).render(0, want_linear=True)
+        assert np.array_equal(fresh.linear, got.linear)
+        assert (f == 0.0) == np.array_equal(got.linear, base.linear)
+    with pytest.raises(Exception):
+        eng.set_instance_transforms(np.zeros((2, 16)))          # the instance count of a scene is fixed
+
+
+def test_image_writers_round_trip(tmp_path, emu):
+    """rth_image_write: PNG (8-bit RGBA, stored deflate, CRCs, Adler-32) decodes to the frame; PPM is P6 RGB."""
+    import struct
+    import zlib
+    from myraytracer_b200 import write_image
+    rng = np.random.default_rng(3)
+    img = rng.integers(0, 256, size=(37, 301, 4), dtype=np.uint8)          # > 65535 raw bytes: several stored blocks
+    png, ppm = str(tmp_path / "a.png"), str(tmp_path / "a.ppm")
+    write_image(png, img)
+    write_image(ppm, img)
+    raw = open(png, "rb").read()
+    assert raw[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, idat, seen = 8, b"", []
+    while pos < len(raw):
+        n, kind = struct.unpack(">I4s", raw[pos:pos + 8])
+        body = raw[pos + 8:pos + 8 + n]
+        assert struct.unpack(">I", raw[pos + 8 + n:pos + 12 + n])[0] == zlib.crc32(kind + body)
+        seen.append(kind)
+        if kind == b"IHDR":
+            assert struct.unpack(">IIBBBBB", body) == (301, 37, 8, 6, 0, 0, 0)
+        if kind == b"IDAT":
+            idat += body
+        pos += 12 + n
+    assert seen == [b"IHDR", b"IDAT", b"IEND"]
+    rows = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(37, 301 * 4 + 1)
+    assert (rows[:, 0] == 0).all() and np.array_equal(rows[:, 1:].reshape(37, 301, 4), img)
+    p = open(ppm, "rb").read()
+    head = b"P6\n301 37\n255\n"
+    assert p.startswith(head) and np.array_equal(np.frombuffer(p[len(head):], np.uint8).reshape(37, 301, 3), img[..., :3])
+    with pytest.raises(Exception):
+        write_image(str(tmp_path / "a.jpg"), img)
+
+
 def test_emulator_is_not_the_product(emu):
     """The product loader never hands out the emulation library, and the emulation build says what it is."""
     import os
