@@ -208,11 +208,14 @@ int32_t rt_scene_get_info(const rt_scene_t* scene, rt_scene_info* out);
 /* Animation: new placements for the instances of a resident scene.  Replaces
  * RTContext.refitTLAS (Models/RTContext.swift:883-928) + BVHBuilder.refit (Accelearion/BVH.swift:254-292): `instances`
  * has the scene's instance count, every entry keeps its `blas`; localToWorld / worldToLocal / normalMatrix /
- * worldBounds / materialOverride are taken as given.  The instance records go to the device and the TLAS boxes are
- * refitted there, bottom-up, with the topology kept (one small kernel on `cudaStream`, NULL = default stream); the
- * mesh BVHs, triangles and materials are untouched.  Blocking.  Scenes with instanceMotion are refused
- * (RT_ERR_UNSUPPORTED): their TLAS is the reference's own topology, rebuilt per scene. */
-int32_t rt_scene_update_instances(rt_scene_t* scene, const rt_instance* instances, int64_t nInstances, void* cudaStream);
+ * materialOverride are taken as given.  worldBounds too — except where the box is inverted (minP > maxP, e.g.
+ * +inf / -inf): that mesh instance's bounds are derived ON THE DEVICE from the BLAS's resident triangles (the union of
+ * their transformed boxes, bit-identical to the loop of refitTLAS step 1, which costs the reference O(triangles) host
+ * work per instance and frame) and written back into instances[i].worldBounds.  The instance records go to the
+ * device and the TLAS boxes are refitted there, bottom-up, with the topology kept (kernels on `cudaStream`, NULL =
+ * default stream); the mesh BVHs, triangles and materials are untouched.  Blocking.  Scenes with instanceMotion are
+ * refused (RT_ERR_UNSUPPORTED): their TLAS is the reference's own topology, rebuilt per scene. */
+int32_t rt_scene_update_instances(rt_scene_t* scene, rt_instance* instances, int64_t nInstances, void* cudaStream);
 
 /* The tile order the next frame of the last rendered geometry will use (rt_render_params.scheduleMode): returns the
  * number of tiles (0: nothing learnt yet, < 0: error) and copies min(n, capacity) entries — slot k draws tile

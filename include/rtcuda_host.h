@@ -44,8 +44,10 @@ int32_t rth_engine_camera_name(const rth_engine_t* engine, int32_t cameraIndex, 
  * (BatchRender/BatchRender.swift:26-40) and its RTContext.refitTLAS (RTContext.swift:883-928) is never called; here a
  * frame is a new set of instance transforms on a resident scene: n = instance count, 16 doubles (column-major
  * localToWorld) per instance in RTContext order (analytic primitives, mesh instances, base meshes).  worldToLocal,
- * normal matrix and world bounds are re-derived as refitTLAS does, then rt_scene_update_instances refits the TLAS. */
-int32_t rth_engine_set_instance_transforms(rth_engine_t* engine, const double* localToWorld, int64_t n);
+ * normal matrix and world bounds are re-derived as refitTLAS does, then rt_scene_update_instances refits the TLAS.
+ * boundsOnDevice != 0: the world bounds of mesh instances (a union over every triangle) come from the device kernel
+ * instead of the host loop — same values (tested), O(instances) host work. */
+int32_t rth_engine_set_instance_transforms(rth_engine_t* engine, const double* localToWorld, int64_t n, int32_t boundsOnDevice);
 
 /* Headless replacement of makeCGImage + PNG output (Helpers/Image.swift; ImageIO is Apple-only): writes the RGBA8
  * frame as .png (8-bit RGBA, stored deflate) or .ppm (binary P6), chosen by the extension.  Row 0 = top. */

@@ -174,7 +174,7 @@ def declare(L):
     L.rt_scene_update_instances.argtypes = [vp, C.POINTER(rt_instance), C.c_int64, vp]
     L.rth_engine_inspect.argtypes = [vp, C.POINTER(C.c_int64), C.POINTER(C.c_int32)]
     L.rth_engine_camera_name.argtypes = [vp, C.c_int32, C.c_char_p, C.c_int32, C.POINTER(C.c_int32)]
-    L.rth_engine_set_instance_transforms.argtypes = [vp, C.POINTER(C.c_double), C.c_int64]
+    L.rth_engine_set_instance_transforms.argtypes = [vp, C.POINTER(C.c_double), C.c_int64, C.c_int32]
     L.rth_image_write.argtypes = [C.c_char_p, vp, C.c_int32, C.c_int32]
     L.rth_context_create.restype = vp
     L.rth_context_create.argtypes = [C.c_char_p]

@@ -63,6 +63,7 @@ static const size_t kFrameStateBytes = 16 * sizeof(unsigned long long) + 64;
 struct BlasInfo {
     int kind = INST_MESH; int64_t prim = 0; int64_t matId = 0; int smooth = 0;
     int32_t nodeBase = 0, triBase = 0, rootRef = kEmptyRef; int f64 = 0;
+    int64_t triCount = 0;              // triangles of a mesh BLAS (slots triBase .. triBase + triCount of tris / trisD)
     double lo[3], hi[3], centre[3];
     double motion[3] = {0, 0, 0};      // Triangle.motionBlur of the mesh (RTContext.swift:280,345)
     double payload[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // sphere c.xyz, r | plane c.xyz, n.xyz
@@ -89,6 +90,9 @@ struct rt_scene {
     int* dRefitLevelStart = nullptr;
     double* dInstBounds = nullptr;     // Instance.worldBounds, 6 doubles per instance
     GInstance* hInst = nullptr; double* hInstBounds = nullptr;   // pinned staging for the per-frame upload
+    BoundsChunk* dBoundChunks = nullptr; int nBoundChunks = 0;   // (instance, triangle range) work items of launchInstanceBounds
+    int32_t* dDerive = nullptr; int32_t* hDerive = nullptr;      // per instance: 1 = derive worldBounds on the device
+    unsigned long long* dBoundsEnc = nullptr; unsigned long long* hBoundsEnc = nullptr;
     unsigned* dAreaIndex = nullptr; size_t areaIndexBytes = 0;   // per-pixel jitter index of an area-light frame
     // render state (re-used across calls)
     int* dTileCounter = nullptr; unsigned long long* dCounters = nullptr;
@@ -111,6 +115,7 @@ struct rt_scene {
     bool pending = false; bool pendingCounters = false;
     cudaStream_t pendingStream = nullptr;
     int64_t launches = 0;
+    int64_t updateLaunches = 0;        // kernels of the last rt_scene_update_instances
 };
 
 
@@ -250,6 +255,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
         bi.f64 = out.f64 ? 1 : 0;
         bi.nodeBase = (int32_t)nodes.size();
         bi.triBase = (int32_t)(out.f64 ? trisD.size() : tris.size());
+        bi.triCount = bl.primCount;
         bi.rootRef = out.rootRef;
         std::memcpy(bi.lo, out.rootLo, 24); std::memcpy(bi.hi, out.rootHi, 24); std::memcpy(bi.centre, out.centre, 24);
         // device references are absolute (gpu_layout.h): rebase the builder's BLAS-relative ones
@@ -395,6 +401,19 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
         const size_t n = (size_t)d->nInstances;
         CK(cudaMallocHost((void**)&sc->hInst, (n ? n : 1) * sizeof(GInstance)));
         CK(cudaMallocHost((void**)&sc->hInstBounds, (n ? n : 1) * 6 * sizeof(double)));
+        CK(cudaMallocHost((void**)&sc->hDerive, (n ? n : 1) * sizeof(int32_t)));
+        CK(cudaMallocHost((void**)&sc->hBoundsEnc, (n ? n : 1) * 6 * sizeof(unsigned long long)));
+        CK(cudaMalloc((void**)&sc->dDerive, (n ? n : 1) * sizeof(int32_t)));
+        CK(cudaMalloc((void**)&sc->dBoundsEnc, (n ? n : 1) * 6 * sizeof(unsigned long long)));
+        std::vector<BoundsChunk> chunks;                      // 4096 triangles per block of the bounds kernel
+        for (size_t i = 0; i < n; i++) {
+            const BlasInfo& bi = blasInfo[sc->instBlas[i]];
+            if (bi.kind != INST_MESH) continue;
+            for (int64_t f = 0; f < bi.triCount; f += 4096)
+                chunks.push_back(BoundsChunk{(int32_t)i, (int32_t)(bi.triBase + f), (int32_t)std::min<int64_t>(4096, bi.triCount - f), bi.f64});
+        }
+        sc->nBoundChunks = (int)chunks.size();
+        if ((rc = upload(chunks, &sc->dBoundChunks, bytes))) return rc;
         sc->instanceMotion = instanceMotion;
     }
     if ((rc = upload(tlasF, &sc->dTlas, bytes))) return rc;
@@ -454,6 +473,9 @@ void rt_scene_destroy(rt_scene_t* sc) {
     cudaFree(sc->dTlasD); cudaFree(sc->dRefitOrder); cudaFree(sc->dRefitLevelStart); cudaFree(sc->dInstBounds);
     if (sc->hInst) cudaFreeHost(sc->hInst);
     if (sc->hInstBounds) cudaFreeHost(sc->hInstBounds);
+    if (sc->hDerive) cudaFreeHost(sc->hDerive);
+    if (sc->hBoundsEnc) cudaFreeHost(sc->hBoundsEnc);
+    cudaFree(sc->dDerive); cudaFree(sc->dBoundsEnc); cudaFree(sc->dBoundChunks);
     cudaFree(sc->dTileCost); cudaFree(sc->dTileOrder); cudaFree(sc->dSchedWork);
     cudaFree(sc->dPathStack); cudaFree(sc->dRgba); cudaFree(sc->dLinear); cudaFree(sc->dIds);
     if (sc->hCounters) cudaFreeHost(sc->hCounters);
@@ -480,7 +502,7 @@ rt_scene_t* rt_scene_create(const rt_scene_desc* desc, int32_t device) {
     return nullptr;
 }
 
-int32_t rt_scene_update_instances(rt_scene_t* sc, const rt_instance* instances, int64_t nInstances, void* cudaStream) {
+int32_t rt_scene_update_instances(rt_scene_t* sc, rt_instance* instances, int64_t nInstances, void* cudaStream) {
     if (!sc) return fail(RT_ERR_NO_SCENE, "No scene loaded. Can't render.");
     if (sc->pending) return fail(RT_ERR_INVALID, "a render is in flight on this scene (call rt_render_finish)");
     if (!instances || nInstances != (int64_t)sc->instBlas.size())
@@ -491,23 +513,47 @@ int32_t rt_scene_update_instances(rt_scene_t* sc, const rt_instance* instances, 
     cudaStream_t st = (cudaStream_t)cudaStream;
     const size_t n = (size_t)nInstances;
     if (sc->sideBusy) CK(cudaEventSynchronize(sc->evSide));      // the previous frame's epilogue is done
+    bool anyDerived = false;
     for (size_t i = 0; i < n; i++) {
         const rt_instance& in = instances[i];
         if (in.blas != sc->instBlas[i]) return fail(RT_ERR_INVALID, "rt_scene_update_instances: an instance keeps its BLAS");
         if (in.instanceMotion[0] != 0 || in.instanceMotion[1] != 0 || in.instanceMotion[2] != 0)
             return fail(RT_ERR_UNSUPPORTED, "rt_scene_update_instances: instanceMotion cannot be introduced by an update");
-        fillInstance(in, sc->blasInfo[in.blas], sc->hInst[i]);
-        std::memcpy(sc->hInstBounds + i * 6, in.worldBounds, 48);
+        const BlasInfo& bi = sc->blasInfo[in.blas];
+        fillInstance(in, bi, sc->hInst[i]);
+        // an inverted box (minP > maxP) asks for Instance.worldBounds to be derived from the BLAS's triangles
+        const bool derive = !(in.worldBounds[0] <= in.worldBounds[3]) || !(in.worldBounds[1] <= in.worldBounds[4]) ||
+                            !(in.worldBounds[2] <= in.worldBounds[5]);
+        if (derive && bi.kind != INST_MESH)
+            return fail(RT_ERR_INVALID, "rt_scene_update_instances: only mesh instances can have their bounds derived");
+        sc->hDerive[i] = derive ? 1 : 0;
+        anyDerived = anyDerived || derive;
+        for (int a = 0; a < 3; a++) {
+            sc->hBoundsEnc[i * 6 + a] = encodeOrdered(derive ? (double)INFINITY : in.worldBounds[a]);
+            sc->hBoundsEnc[i * 6 + 3 + a] = encodeOrdered(derive ? -(double)INFINITY : in.worldBounds[3 + a]);
+        }
     }
     CK(cudaMemcpyAsync(sc->dInst, sc->hInst, n * sizeof(GInstance), cudaMemcpyHostToDevice, st));
+    if (anyDerived) {
+        CK(cudaMemcpyAsync(sc->dDerive, sc->hDerive, n * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(sc->dBoundsEnc, sc->hBoundsEnc, n * 6 * sizeof(unsigned long long), cudaMemcpyHostToDevice, st));
+        CK(launchInstanceBounds(sc->ds, sc->dBoundChunks, sc->nBoundChunks, sc->dDerive, sc->dBoundsEnc, st));
+        CK(cudaMemcpyAsync(sc->hBoundsEnc, sc->dBoundsEnc, n * 6 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+    }
+    for (size_t i = 0; i < n; i++)
+        for (int a = 0; a < 6; a++) {
+            sc->hInstBounds[i * 6 + a] = decodeOrdered(sc->hBoundsEnc[i * 6 + a]);
+            if (sc->hDerive[i]) instances[i].worldBounds[a] = sc->hInstBounds[i * 6 + a];     // handed back to the caller
+        }
     if (sc->info.tlasNodes > 0) {
         // scene bounds (the union of the instance bounds), their centre and the box padding: host, O(instances)
         TNode root{};
         for (int a = 0; a < 3; a++) { root.lo0[a] = root.lo1[a] = INFINITY; root.hi0[a] = root.hi1[a] = -INFINITY; }
         for (size_t i = 0; i < n; i++)
             for (int a = 0; a < 3; a++) {
-                root.lo0[a] = std::fmin(root.lo0[a], instances[i].worldBounds[a]);
-                root.hi0[a] = std::fmax(root.hi0[a], instances[i].worldBounds[3 + a]);
+                root.lo0[a] = std::fmin(root.lo0[a], sc->hInstBounds[i * 6 + a]);
+                root.hi0[a] = std::fmax(root.hi0[a], sc->hInstBounds[i * 6 + 3 + a]);
             }
         std::memcpy(root.lo1, root.lo0, 24); std::memcpy(root.hi1, root.hi0, 24);
         double sLo[3], sHi[3], sC[3];
@@ -518,6 +564,7 @@ int32_t rt_scene_update_instances(rt_scene_t* sc, const rt_instance* instances, 
         std::memcpy(sc->ds.tlasLo, sLo, 24); std::memcpy(sc->ds.tlasHi, sHi, 24); std::memcpy(sc->ds.tlasCentre, sC, 24);
     }
     CK(cudaStreamSynchronize(st));       // the staging buffers are free again when this returns
+    sc->updateLaunches = (anyDerived ? 1 : 0) + (sc->info.tlasNodes > 0 ? 1 : 0);
     return RT_OK;
 }
 

@@ -3,6 +3,8 @@
 //   KV_FAST     lane = (pixel, sample); depth 0 (primary + shadow rays) as warp packets; valid when no
 //               material draws random numbers inside `trace` (roughness == 0): the default
 //   KV_GENERAL  lane = pixel, sequential PCG32 stream, per-lane traversal: any scene
+#include <math_constants.h>
+
 #include "rt_kernels.h"
 
 namespace rtg {
@@ -139,6 +141,72 @@ cudaError_t launchAreaPrefix(unsigned* areaIndex, int width, int height, int sha
     const int nChunks = (height + 7) / 8;
     const int mine = (nChunks - shardIndex + shardCount - 1) / shardCount;
     if (mine > 0) RT_LAUNCH(areaPrefixKernel, mine, RT_AREA_THREADS, stream, areaIndex, width, height, shardIndex, shardCount);
+    return cudaGetLastError();
+}
+
+// ---- animation: world bounds of the mesh instances ------------------------------------------------------------------
+#define RT_BOUNDS_THREADS 256
+__device__ __forceinline__ unsigned long long encOrdered(double d) {
+    const unsigned long long b = (unsigned long long)__double_as_longlong(d);
+    return (b >> 63) ? ~b : (b | 0x8000000000000000ULL);
+}
+__global__ void __launch_bounds__(RT_BOUNDS_THREADS) instanceBoundsKernel(DeviceScene S, const BoundsChunk* __restrict__ chunks,
+                                                                          const int32_t* __restrict__ derive,
+                                                                          unsigned long long* __restrict__ boundsEnc) {
+    __shared__ double red[6][RT_BOUNDS_THREADS / 32];
+    const BoundsChunk ck = chunks[blockIdx.x];
+    if (!derive[ck.inst]) return;
+    const GInstance& I = S.instances[ck.inst];
+    double M[12];
+    for (int k = 0; k < 12; k++) M[k] = I.l2w[k];                 // column-major 3x4: M[c * 3 + r]
+    const double mb[3] = {I.meshMotion[0], I.meshMotion[1], I.meshMotion[2]};
+    double lo[3] = {CUDART_INF, CUDART_INF, CUDART_INF}, hi[3] = {-CUDART_INF, -CUDART_INF, -CUDART_INF};
+    for (int k = (int)threadIdx.x; k < ck.count; k += RT_BOUNDS_THREADS) {
+        double v[3][3];
+        if (ck.f64) {
+            const GTriD& t = S.trisD[ck.first + k];
+            for (int a = 0; a < 3; a++) { v[0][a] = t.v0[a]; v[1][a] = t.v1[a]; v[2][a] = t.v2[a]; }
+        } else {
+            const GTri& t = S.tris[ck.first + k];
+            for (int a = 0; a < 3; a++) { v[0][a] = (double)t.v0[a]; v[1][a] = (double)t.v1[a]; v[2][a] = (double)t.v2[a]; }
+        }
+        double pl[3], ph[3];                                       // the prim's local box, grown by the mesh motion (:283-289)
+        for (int a = 0; a < 3; a++) {
+            pl[a] = fmin(v[0][a], fmin(v[1][a], v[2][a]));
+            ph[a] = fmax(v[0][a], fmax(v[1][a], v[2][a]));
+            pl[a] = fmin(pl[a], pl[a] + mb[a]);
+            ph[a] = fmax(ph[a], ph[a] + mb[a]);
+        }
+        // AABB.transformed(by:): centre and half extent through the matrix and its absolute value
+        const double cO[3] = {(pl[0] + ph[0]) * 0.5, (pl[1] + ph[1]) * 0.5, (pl[2] + ph[2]) * 0.5};
+        const double eO[3] = {(ph[0] - pl[0]) * 0.5, (ph[1] - pl[1]) * 0.5, (ph[2] - pl[2]) * 0.5};
+        for (int r = 0; r < 3; r++) {
+            const double cN = ((M[r] * cO[0] + M[3 + r] * cO[1]) + M[6 + r] * cO[2]) + M[9 + r];
+            const double eN = (fabs(M[r]) * eO[0] + fabs(M[3 + r]) * eO[1]) + fabs(M[6 + r]) * eO[2];
+            lo[r] = fmin(lo[r], cN - eN);
+            hi[r] = fmax(hi[r], cN + eN);
+        }
+    }
+    for (int a = 0; a < 3; a++)
+        for (int off = 16; off > 0; off >>= 1) {
+            lo[a] = fmin(lo[a], __shfl_down_sync(0xffffffffu, lo[a], off));
+            hi[a] = fmax(hi[a], __shfl_down_sync(0xffffffffu, hi[a], off));
+        }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) for (int a = 0; a < 3; a++) { red[a][warp] = lo[a]; red[3 + a][warp] = hi[a]; }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        double r = red[threadIdx.x][0];
+        for (int w = 1; w < RT_BOUNDS_THREADS / 32; w++) r = threadIdx.x < 3 ? fmin(r, red[threadIdx.x][w]) : fmax(r, red[threadIdx.x][w]);
+        unsigned long long* dst = boundsEnc + (size_t)ck.inst * 6 + threadIdx.x;
+        if (threadIdx.x < 3) atomicMin(dst, encOrdered(r));
+        else atomicMax(dst, encOrdered(r));
+    }
+}
+
+cudaError_t launchInstanceBounds(const DeviceScene& S, const BoundsChunk* chunks, int nChunks, const int32_t* derive,
+                                 unsigned long long* boundsEnc, cudaStream_t stream) {
+    if (nChunks > 0) RT_LAUNCH(instanceBoundsKernel, nChunks, RT_BOUNDS_THREADS, stream, S, chunks, derive, boundsEnc);
     return cudaGetLastError();
 }
 

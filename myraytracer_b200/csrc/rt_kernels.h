@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <string.h>
 
 #include "gpu_layout.h"
 
@@ -65,6 +66,25 @@ cudaError_t launchRender(int variant, const DeviceScene& S, const CameraParams& 
 cudaError_t launchAreaPrefix(unsigned* areaIndex, int width, int height, int shardIndex, int shardCount, cudaStream_t stream);
 // Animation: bottom-up refit of the TLAS after rt_scene_update_instances (topology kept, like BVHBuilder.refit,
 // Accelearion/BVH.swift:254-292): FP64 boxes in tlasD, conservative FP32 encoding (centre, padding P) in tlasOut.
+// Instance.worldBounds of mesh instances on the device: the union over the BLAS's triangles of their transformed
+// boxes, exactly the reference's makeInstance / refitTLAS loop (RTContext.swift:437-447,891-900; AABB.transformed,
+// AABB.swift:71-92).  chunks: (instance, first triangle slot, count, f64) work items made at scene creation;
+// boundsEnc: 6 order-preserving u64 per instance (encodeOrdered), pre-set to (+inf, -inf) for the instances to derive
+// and left alone for the others (derive[i] == 0).
+struct BoundsChunk { int32_t inst, first, count, f64; };
+cudaError_t launchInstanceBounds(const DeviceScene& S, const BoundsChunk* chunks, int nChunks, const int32_t* derive,
+                                 unsigned long long* boundsEnc, cudaStream_t stream);
+inline unsigned long long encodeOrdered(double d) {
+    unsigned long long b;
+    memcpy(&b, &d, 8);
+    return (b >> 63) ? ~b : (b | 0x8000000000000000ULL);
+}
+inline double decodeOrdered(unsigned long long u) {
+    const unsigned long long b = (u >> 63) ? (u & 0x7fffffffffffffffULL) : ~u;
+    double d;
+    memcpy(&d, &b, 8);
+    return d;
+}
 cudaError_t launchTlasRefit(TNode* tlasD, GNode* tlasOut, const double* instBounds, const int* order, const int* levelStart,
                             int nLevels, const double* centre, double pad, cudaStream_t stream);
 cudaError_t launchSchedule(unsigned* tileCost, int* tileOrder, unsigned* work, int nTiles, cudaStream_t stream);

@@ -148,12 +148,13 @@ class RayTracerEngine:
         return out
 
     # -- animation --------------------------------------------------------
-    def set_instance_transforms(self, local_to_world) -> None:
+    def set_instance_transforms(self, local_to_world, bounds_on_device: bool = True) -> None:
         """A new frame of an animation: one column-major 4x4 localToWorld per instance (RTContext order).  Replaces
         the per-frame engine rebuild of BatchRender.swift:26-40 by RTContext.refitTLAS semantics
         (RTContext.swift:883-928): instance records re-derived, TLAS boxes refitted on the device."""
         m = np.ascontiguousarray(np.asarray(local_to_world, np.float64).reshape(-1, 16))
-        rc = self._lib.rth_engine_set_instance_transforms(self._h, m.ctypes.data_as(C.POINTER(C.c_double)), m.shape[0])
+        rc = self._lib.rth_engine_set_instance_transforms(self._h, m.ctypes.data_as(C.POINTER(C.c_double)), m.shape[0],
+                                                          1 if bounds_on_device else 0)
         if rc != 0:
             raise RenderError(rc, self._lib.rth_last_error().decode())
 

@@ -43,15 +43,15 @@ int Renderer::render(const pk::Scene& scene, int cameraIndex, std::vector<double
                      ids ? ids->data() : nullptr, stats);
 }
 
-int Renderer::refit(const RTContext& ctx) {
+int Renderer::refit(RTContext& ctx) {
     return rt_scene_update_instances(handle_, ctx.instances.data(), (int64_t)ctx.instances.size(), nullptr);
 }
 
-int RayTracerEngine::setInstanceTransforms(const double* l2w, int64_t n, RenderError& err) {
+int RayTracerEngine::setInstanceTransforms(const double* l2w, int64_t n, RenderError& err, bool boundsOnDevice) {
     if (!hasScene_) { err = {"Render", -20, "No scene loaded. Can't render."}; return -20; }
     if (!renderer_) { err = {"Render", -21, "Renderer not initialized."}; return -21; }
     if (!l2w || n != (int64_t)ctx_.instances.size()) { err = {"Render", RT_ERR_INVALID, "one transform per instance is required"}; return RT_ERR_INVALID; }
-    for (int64_t i = 0; i < n; i++) ctx_.setInstanceTransform((size_t)i, l2w + i * 16);
+    for (int64_t i = 0; i < n; i++) ctx_.setInstanceTransform((size_t)i, l2w + i * 16, boundsOnDevice);
     const int rc = renderer_->refit(ctx_);
     if (rc != RT_OK) err = {"Render", rc, rt_last_error()};
     return rc;
@@ -198,11 +198,11 @@ int32_t rth_engine_render(rth_engine_t* h, int32_t cameraIndex, const rt_render_
     return rc;
 }
 
-int32_t rth_engine_set_instance_transforms(rth_engine_t* h, const double* l2w, int64_t n) {
+int32_t rth_engine_set_instance_transforms(rth_engine_t* h, const double* l2w, int64_t n, int32_t boundsOnDevice) {
     auto* e = reinterpret_cast<rthost::RayTracerEngine*>(h);
     if (!e) { g_herr = "No scene loaded. Can't render."; return -20; }
     rthost::RenderError err{"", 0, ""};
-    const int rc = e->setInstanceTransforms(l2w, n, err);
+    const int rc = e->setInstanceTransforms(l2w, n, err, boundsOnDevice != 0);
     if (rc != 0) g_herr = err.message;
     return rc;
 }

@@ -48,7 +48,7 @@ struct RTContext {
     int64_t triangleCount() const { return (int64_t)triVertices.size() / 9; }
     // Animation: a new localToWorld for instance i — worldToLocal, normalMatrix and worldBounds re-derived exactly as
     // RTContext.refitTLAS step 1 does (Models/RTContext.swift:889-912).  m16: column-major 4x4.
-    void setInstanceTransform(size_t i, const double* m16);
+    void setInstanceTransform(size_t i, const double* m16, bool boundsOnDevice = false);
     // borrowed view for rt_scene_create (valid while *this is alive and unmodified)
     rt_scene_desc describe(const pk::Scene& scene) const;
 };
@@ -81,7 +81,7 @@ public:
                std::vector<rt_hit_id>* ids, rt_stats* stats, const rt_render_params* params = nullptr);
     // refitTLAS steps 2-4 (RTContext.swift:914-927): the instances of `ctx` replace the scene's, the TLAS boxes are
     // refitted on the device, the BLASes stay
-    int refit(const RTContext& ctx);
+    int refit(RTContext& ctx);
 
 private:
     rt_scene_t* handle_ = nullptr;
@@ -103,7 +103,7 @@ public:
     // Animation: n = instance count, 16 doubles (column-major localToWorld) per instance, in
     // the order of context().instances.  The reference's batch driver reloads and rebuilds everything per frame
     // (BatchRender/BatchRender.swift:26-40); here only the instance records and the TLAS boxes change.
-    int setInstanceTransforms(const double* l2w, int64_t n, RenderError& err);
+    int setInstanceTransforms(const double* l2w, int64_t n, RenderError& err, bool boundsOnDevice = true);
     // sceneMeshAndTriangleCounts(_:) — :208-227
     void sceneMeshAndTriangleCounts(int64_t& meshes, int64_t& tris, int64_t& spheres, int64_t& planes) const;
     // render(format:cameraIndex:progress:) — :115-131 via renderRGBA8Async :137-205.

@@ -86,9 +86,17 @@ void placeInstance(rt_instance& in, const double* m16, const std::vector<double>
 
 }  // namespace
 
-void RTContext::setInstanceTransform(size_t i, const double* m16) {
+void RTContext::setInstanceTransform(size_t i, const double* m16, bool boundsOnDevice) {
     rt_instance& in = instances.at(i);
-    placeInstance(in, m16, blasPrimBounds.at((size_t)in.blas));
+    const std::vector<double>& pb = blasPrimBounds.at((size_t)in.blas);
+    if (boundsOnDevice && pb.size() > 6) {
+        // a mesh: the union over its triangles is left to rt_scene_update_instances (inverted box = "derive"),
+        // which computes the same values on the device and writes them back here
+        static const std::vector<double> none;
+        placeInstance(in, m16, none);
+    } else {
+        placeInstance(in, m16, pb);
+    }
 }
 
 RTContext::RTContext(const pk::Scene& scene) {

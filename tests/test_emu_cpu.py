@@ -138,7 +138,14 @@ def test_emulated_animation_refit_matches_rebuilt_scenes(scene_dir, emu):
     base = eng.render(0, want_linear=True)
     for f in (0.5, 1.0, 0.0):
         pf = scenegen.config_instances(scene_dir, frame=f, name=f"frame{f}", **kw)
-        eng.set_instance_transforms(FlatContext(pf).instances()["l2w"])
+        want = FlatContext(pf).instances()
+        # Instance.worldBounds of the meshes derived by the device kernel (default), then by the host loop of
+        # refitTLAS step 1: the same doubles as a context flattened from scratch, either way
+        for on_device in (True, False):
+            eng.set_instance_transforms(want["l2w"], bounds_on_device=on_device)
+            d = eng.describe()
+            bounds = np.array([list(d.instances[i].worldBounds) for i in range(d.nInstances)])
+            assert np.array_equal(bounds, want["bounds"]), on_device
         got = eng.render(0, want_ids=True, want_linear=True)
         check(got, oracle_lib.OracleScene(pf).render(want_ids=True, want_linear=True))
         fresh = RayTracerEngine(pf).render(0, want_linear=True)

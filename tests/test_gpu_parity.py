@@ -202,7 +202,11 @@ def test_animation_refit_matches_rebuilt_scenes(scene_dir):
     base = eng.render(0, want_linear=True)
     for f in (0.3, 1.0, 0.0):
         pf = scenegen.config_instances(scene_dir, frame=f, name=f"frame{f}", **kw)
-        eng.set_instance_transforms(FlatContext(pf).instances()["l2w"])
+        want = FlatContext(pf).instances()
+        eng.set_instance_transforms(want["l2w"])                # mesh bounds derived by the device kernel
+        d = eng.describe()
+        bounds = np.array([list(d.instances[i].worldBounds) for i in range(d.nInstances)])
+        assert np.array_equal(bounds, want["bounds"])           # bit-identical to the host loop of refitTLAS step 1
         got = eng.render(0, want_ids=True, want_linear=True)
         rep = parity.compare(got, oracle_lib.OracleScene(pf).render(want_ids=True, want_linear=True))
         assert rep["id_agree"] >= 0.9999 and rep["id_bad"] == 0 and rep["px_within_1"] >= 0.999, rep
