@@ -237,6 +237,35 @@ int32_t rt_render_device(rt_scene_t* scene, const rt_camera* camera, const rt_re
                          void* dRgbaOut, void* dLinearOut, void* dIdsOut, void* cudaStream);
 int32_t rt_render_finish(rt_scene_t* scene, rt_stats* statsOut);
 
+/* PLY -> device ingest.  The reference reads a mesh through miniply behind the CPly C ABI
+ * (ply_reader_load_element / ply_reader_extract_properties / ply_reader_extract_list, Sources/CPly/include/
+ * PLYReaderWrapper.h:38-66, driven by Helpers/PLYReader.swift:54-210) and turns it into Triangle objects in the mesh
+ * branch of RTContext.init (Models/RTContext.swift:251-363), all on one thread.  Here the caller hands over the RAW
+ * element blocks of a binary_little_endian file plus their layout, and kernels produce the per-triangle FP64 arrays
+ * rt_scene_desc takes — bit-identical to the reference's loops (positions read as Float and widened, file normals
+ * normalised, quads split 0,1,3 / 2,3,1, smooth vertex normals = sum of unit face normals in face order,
+ * flat normals normalised twice). */
+typedef struct rt_ply_layout {
+    int64_t vertexCount, faceCount;
+    int32_t vertexStride;         /* bytes of one vertex record */
+    int32_t posOffset[3];         /* byte offsets of the float32 properties x, y, z in a vertex record */
+    int32_t normalOffset[3];      /* float32 nx, ny, nz; -1: the file has no normals */
+    int32_t faceLeadBytes;        /* scalar properties before the index list in a face record */
+    int32_t faceCountBytes;       /* size of the list's count (uchar = 1) */
+    int32_t faceIndexBytes;       /* size of one index (int / uint = 4) */
+    int32_t faceTrailBytes;       /* scalar properties after the index list */
+    int32_t verticesPerFace;      /* 3 or 4: every face record has this count (verified on the device) */
+    int32_t reserved;
+} rt_ply_layout;
+
+typedef struct rt_ply_stats { int64_t triangles, kernelLaunches; double deviceMs; } rt_ply_stats;
+
+/* triVerticesOut / triNormalsOut: faceCount * (verticesPerFace == 4 ? 2 : 1) * 9 doubles each, caller-owned host
+ * buffers.  smooth: the mesh's ShadingMode.  RT_ERR_INVALID: a face index out of range or a face with another vertex
+ * count (message in rt_last_error).  Blocking. */
+int32_t rt_ply_ingest(const rt_ply_layout* layout, const void* vertexBlock, const void* faceBlock, int32_t smooth,
+                      int32_t device, double* triVerticesOut, double* triNormalsOut, rt_ply_stats* statsOut);
+
 /* Multi-GPU framebuffer (one process per GPU): the reference merges finished 8-row chunks into
  * one [Vec3] array by plain copies (Object+Extension.swift:363-373).  Here rank 0 owns the RGBA8 frame in device
  * memory and exports it; every other rank maps it over NVLink (CUDA IPC, peer access) and passes the mapped

@@ -1,0 +1,249 @@
+// ply_ingest.cu — PLY -> device ingest.   COMPILE WITH -fmad=false.
+//
+// The step right before the hot path.  The reference goes PLY -> [Float] -> [Vec3] (FP64) -> Triangle objects on one
+// thread: miniply through the CPly C ABI (Helpers/PLYReader.swift:54-210), then the mesh branch of RTContext.init
+// (Models/RTContext.swift:251-363): face normals, smooth vertex normals as the sum of the UNIT face normals of the
+// faces around a vertex (:305-326), one Triangle per face with v0,v1,v2,n0,n1,n2.  Here the raw binary-little-endian
+// vertex and face blocks of the file go to the GPU as they are and kernels produce the same per-triangle FP64 arrays
+// (rt_scene_desc.triVertices / triNormals), bit for bit:
+//   * positions are read as Float and widened (PLYReader.swift:85-101); file normals are normalised (:104-122)
+//   * quads split 0,1,3 / 2,3,1 like miniply (miniply.cpp:1976-1985)
+//   * a vertex normal is summed in (face, corner) order — the order of the reference's loop — so the FP64 sum is the
+//     same: the faces around each vertex are gathered into a CSR list (count, exclusive scan, fill), each short list is
+//     sorted, then added up sequentially by one thread
+//   * flat shading normalises the unit face normal once more (:343)
+// No warp-level primitives: atomics, a three-kernel scan and plain per-element kernels — HBM-bound byte and FP64 work.
+#include <math_constants.h>
+
+#include "../../include/rtcuda.h"
+#include "rt_kernels.h"
+#include "rt_math.cuh"
+
+namespace rtg {
+
+#define RT_PLY_THREADS 256
+
+struct PlyDev {
+    rt_ply_layout L;
+    const unsigned char* vblock;
+    const unsigned char* fblock;
+    int32_t faceRecord;          // bytes of one face record
+    int32_t trisPerFace;         // 1 or 2
+    double* pos;                 // vertexCount * 3
+    double* vnormFile;           // vertexCount * 3 (file normals, normalised) or null
+    int32_t* idx;                // nTris * 3
+    double* faceN;               // nTris * 3 (unit)
+    unsigned* count;             // vertexCount + 1: faces-around-vertex counts, then their exclusive prefix
+    unsigned* cursor;            // vertexCount
+    unsigned* entries;           // nTris * 3: corner ids (t * 3 + c) grouped by vertex
+    double* vnorm;               // vertexCount * 3: smooth vertex normals
+    int* error;                  // 1: a face record with another vertex count, 2: index out of range
+};
+
+__device__ __forceinline__ float loadF32(const unsigned char* p) {
+    unsigned u = (unsigned)p[0] | ((unsigned)p[1] << 8) | ((unsigned)p[2] << 16) | ((unsigned)p[3] << 24);
+    return __uint_as_float(u);
+}
+__device__ __forceinline__ long long loadInt(const unsigned char* p, int bytes) {
+    unsigned u = 0;
+    for (int k = 0; k < bytes; k++) u |= (unsigned)p[k] << (8 * k);
+    if (bytes == 4) return (long long)(int)u;             // Int32 indices (PLYReader.swift:186-198)
+    return (long long)u;
+}
+
+__global__ void __launch_bounds__(RT_PLY_THREADS) plyVertices(PlyDev P) {
+    const long long v = (long long)blockIdx.x * RT_PLY_THREADS + threadIdx.x;
+    if (v >= P.L.vertexCount) return;
+    const unsigned char* r = P.vblock + v * P.L.vertexStride;
+    for (int a = 0; a < 3; a++) P.pos[v * 3 + a] = (double)loadF32(r + P.L.posOffset[a]);
+    P.count[v] = 0;
+    if (v == 0) P.count[P.L.vertexCount] = 0;
+    P.cursor[v] = 0;
+    if (P.vnormFile) {
+        const double a = (double)loadF32(r + P.L.normalOffset[0]), b = (double)loadF32(r + P.L.normalOffset[1]),
+                     c = (double)loadF32(r + P.L.normalOffset[2]);
+        const double inv = 1.0 / sqrt((a * a + b * b) + c * c);
+        P.vnormFile[v * 3] = a * inv; P.vnormFile[v * 3 + 1] = b * inv; P.vnormFile[v * 3 + 2] = c * inv;
+    }
+}
+
+__global__ void __launch_bounds__(RT_PLY_THREADS) plyFaces(PlyDev P) {
+    const long long f = (long long)blockIdx.x * RT_PLY_THREADS + threadIdx.x;
+    if (f >= P.L.faceCount) return;
+    const unsigned char* r = P.fblock + f * P.faceRecord + P.L.faceLeadBytes;
+    const int k = P.L.verticesPerFace;
+    if (loadInt(r, P.L.faceCountBytes) != k) { *P.error = 1; return; }
+    long long q[4] = {0, 0, 0, 0};
+    bool ok = true;
+    for (int c = 0; c < k; c++) {
+        q[c] = loadInt(r + P.L.faceCountBytes + c * P.L.faceIndexBytes, P.L.faceIndexBytes);
+        ok = ok && q[c] >= 0 && q[c] < P.L.vertexCount;
+    }
+    if (!ok) { *P.error = 2; return; }
+    int32_t* o = P.idx + f * P.trisPerFace * 3;
+    if (k == 3) { o[0] = (int32_t)q[0]; o[1] = (int32_t)q[1]; o[2] = (int32_t)q[2]; }
+    else { o[0] = (int32_t)q[0]; o[1] = (int32_t)q[1]; o[2] = (int32_t)q[3]; o[3] = (int32_t)q[2]; o[4] = (int32_t)q[3]; o[5] = (int32_t)q[1]; }
+}
+
+// unit face normal (RTContext.swift:307-314) and, for smooth meshes, the faces-around-vertex counts
+__global__ void __launch_bounds__(RT_PLY_THREADS) plyFaceNormals(PlyDev P, long long nTris, int smooth) {
+    const long long t = (long long)blockIdx.x * RT_PLY_THREADS + threadIdx.x;
+    if (t >= nTris) return;
+    const int32_t* i3 = P.idx + t * 3;
+    const V3 v0 = ld3(P.pos + (long long)i3[0] * 3), v1 = ld3(P.pos + (long long)i3[1] * 3), v2 = ld3(P.pos + (long long)i3[2] * 3);
+    const V3 n = normalize(cross(v1 - v0, v2 - v0));
+    P.faceN[t * 3] = n.x; P.faceN[t * 3 + 1] = n.y; P.faceN[t * 3 + 2] = n.z;
+    if (smooth)
+        for (int c = 0; c < 3; c++) atomicAdd(P.count + i3[c], 1u);
+}
+
+// ---- exclusive scan of count[0 .. n] in place: per-block scan, scan of the block sums, add-back ---------------------
+#define RT_SCAN_ITEMS 8
+#define RT_SCAN_BLOCK (RT_PLY_THREADS * RT_SCAN_ITEMS)
+__global__ void __launch_bounds__(RT_PLY_THREADS) scanBlocks(unsigned* a, long long n, unsigned* blockSums) {
+    __shared__ unsigned part[RT_PLY_THREADS];
+    const long long base = (long long)blockIdx.x * RT_SCAN_BLOCK + (long long)threadIdx.x * RT_SCAN_ITEMS;
+    unsigned v[RT_SCAN_ITEMS], sum = 0;
+    for (int k = 0; k < RT_SCAN_ITEMS; k++) { v[k] = base + k < n ? a[base + k] : 0u; sum += v[k]; }
+    part[threadIdx.x] = sum;
+    __syncthreads();
+    for (int d = 1; d < RT_PLY_THREADS; d <<= 1) {               // Hillis-Steele inclusive scan of the thread sums
+        const unsigned add = threadIdx.x >= (unsigned)d ? part[threadIdx.x - d] : 0u;
+        __syncthreads();
+        part[threadIdx.x] += add;
+        __syncthreads();
+    }
+    unsigned run = part[threadIdx.x] - sum;
+    for (int k = 0; k < RT_SCAN_ITEMS; k++) { if (base + k < n) a[base + k] = run; run += v[k]; }
+    if (threadIdx.x == RT_PLY_THREADS - 1) blockSums[blockIdx.x] = part[threadIdx.x];
+}
+__global__ void scanSums(unsigned* blockSums, int nBlocks) {      // a few thousand entries at most: one thread
+    unsigned run = 0;
+    for (int b = 0; b < nBlocks; b++) { const unsigned v = blockSums[b]; blockSums[b] = run; run += v; }
+}
+__global__ void __launch_bounds__(RT_PLY_THREADS) scanAdd(unsigned* a, long long n, const unsigned* blockSums) {
+    const long long base = (long long)blockIdx.x * RT_SCAN_BLOCK + (long long)threadIdx.x * RT_SCAN_ITEMS;
+    const unsigned off = blockSums[blockIdx.x];
+    for (int k = 0; k < RT_SCAN_ITEMS; k++) if (base + k < n) a[base + k] += off;
+}
+
+__global__ void __launch_bounds__(RT_PLY_THREADS) plyFillAdjacency(PlyDev P, long long nTris) {
+    const long long t = (long long)blockIdx.x * RT_PLY_THREADS + threadIdx.x;
+    if (t >= nTris) return;
+    for (int c = 0; c < 3; c++) {
+        const int32_t v = P.idx[t * 3 + c];
+        P.entries[P.count[v] + atomicAdd(P.cursor + v, 1u)] = (unsigned)(t * 3 + c);
+    }
+}
+
+// Smooth vertex normal (:316-326): the unit face normals around the vertex added in (face, corner) order — the order of
+// `for t in faces { for c in 0..<3 { vtxNormals[idx] += faceNormals[t] } }` — then normalised.  A vertex used by no
+// face gets normalize(0) = NaN, as in the reference.
+__global__ void __launch_bounds__(RT_PLY_THREADS) plyVertexNormals(PlyDev P) {
+    const long long v = (long long)blockIdx.x * RT_PLY_THREADS + threadIdx.x;
+    if (v >= P.L.vertexCount) return;
+    unsigned* e = P.entries + P.count[v];
+    const int n = (int)(P.count[v + 1] - P.count[v]);
+    for (int i = 1; i < n; i++) {                                 // insertion sort: the valence is small
+        const unsigned key = e[i];
+        int j = i - 1;
+        while (j >= 0 && e[j] > key) { e[j + 1] = e[j]; j--; }
+        e[j + 1] = key;
+    }
+    V3 a = mk(0, 0, 0);
+    for (int i = 0; i < n; i++) a = a + ld3(P.faceN + (long long)(e[i] / 3u) * 3);
+    a = normalize(a);
+    P.vnorm[v * 3] = a.x; P.vnorm[v * 3 + 1] = a.y; P.vnorm[v * 3 + 2] = a.z;
+}
+
+// One Triangle per face: v0, v1, v2 and n0, n1, n2 (:270-281, :327-346)
+__global__ void __launch_bounds__(RT_PLY_THREADS) plyEmit(PlyDev P, long long nTris, int smooth, double* __restrict__ triVerts,
+                                                          double* __restrict__ triNormals) {
+    const long long t = (long long)blockIdx.x * RT_PLY_THREADS + threadIdx.x;
+    if (t >= nTris) return;
+    const int32_t* i3 = P.idx + t * 3;
+    for (int c = 0; c < 3; c++)
+        for (int a = 0; a < 3; a++) triVerts[t * 9 + c * 3 + a] = P.pos[(long long)i3[c] * 3 + a];
+    if (P.vnormFile) {
+        for (int c = 0; c < 3; c++)
+            for (int a = 0; a < 3; a++) triNormals[t * 9 + c * 3 + a] = P.vnormFile[(long long)i3[c] * 3 + a];
+    } else if (smooth) {
+        for (int c = 0; c < 3; c++)
+            for (int a = 0; a < 3; a++) triNormals[t * 9 + c * 3 + a] = P.vnorm[(long long)i3[c] * 3 + a];
+    } else {
+        const V3 n = normalize(ld3(P.faceN + t * 3));              // :343 (normalised twice)
+        for (int c = 0; c < 3; c++) { triNormals[t * 9 + c * 3] = n.x; triNormals[t * 9 + c * 3 + 1] = n.y; triNormals[t * 9 + c * 3 + 2] = n.z; }
+    }
+}
+
+struct DevBuf {
+    void* p = nullptr;
+    ~DevBuf() { cudaFree(p); }
+    cudaError_t alloc(size_t bytes) { return cudaMalloc(&p, bytes ? bytes : 16); }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+// Returns 0, or -1 with `msg` set (CUDA error or malformed data); *launches counts the kernels run.
+int plyIngestDevice(const rt_ply_layout& L, const void* vertexBlock, const void* faceBlock, int smooth, double* triVertsOut,
+                    double* triNormalsOut, const char** msg, int64_t* launches, double* deviceMs) {
+    *msg = "";
+#define PCK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { *msg = cudaGetErrorString(e_); return -1; } } while (0)
+    const int k = L.verticesPerFace;
+    const long long nV = L.vertexCount, nF = L.faceCount, nT = nF * (k == 4 ? 2 : 1);
+    const bool fileNormals = L.normalOffset[0] >= 0 && L.normalOffset[1] >= 0 && L.normalOffset[2] >= 0;
+    const bool needSmooth = smooth && !fileNormals;
+    PlyDev P{};
+    P.L = L;
+    P.faceRecord = L.faceLeadBytes + L.faceCountBytes + k * L.faceIndexBytes + L.faceTrailBytes;
+    P.trisPerFace = k == 4 ? 2 : 1;
+    DevBuf vb, fb, pos, vnf, idx, fn, cnt, cur, ent, vn, err, sums, tv, tn;
+    PCK(vb.alloc((size_t)nV * L.vertexStride)); PCK(fb.alloc((size_t)nF * P.faceRecord));
+    PCK(pos.alloc((size_t)nV * 24)); PCK(idx.alloc((size_t)nT * 12)); PCK(fn.alloc((size_t)nT * 24));
+    PCK(cnt.alloc((size_t)(nV + 1) * 4)); PCK(cur.alloc((size_t)nV * 4)); PCK(err.alloc(4));
+    PCK(tv.alloc((size_t)nT * 72)); PCK(tn.alloc((size_t)nT * 72));
+    if (fileNormals) PCK(vnf.alloc((size_t)nV * 24));
+    const int scanBlocksN = (int)((nV + 1 + RT_SCAN_BLOCK - 1) / RT_SCAN_BLOCK);
+    if (needSmooth) { PCK(ent.alloc((size_t)nT * 12)); PCK(vn.alloc((size_t)nV * 24)); PCK(sums.alloc((size_t)scanBlocksN * 4)); }
+    cudaEvent_t e0, e1;
+    PCK(cudaEventCreate(&e0)); PCK(cudaEventCreate(&e1));
+    PCK(cudaMemcpyAsync(vb.p, vertexBlock, (size_t)nV * L.vertexStride, cudaMemcpyHostToDevice, 0));
+    PCK(cudaMemcpyAsync(fb.p, faceBlock, (size_t)nF * P.faceRecord, cudaMemcpyHostToDevice, 0));
+    PCK(cudaMemsetAsync(err.p, 0, 4, 0));
+    P.vblock = vb.as<unsigned char>(); P.fblock = fb.as<unsigned char>();
+    P.pos = pos.as<double>(); P.vnormFile = fileNormals ? vnf.as<double>() : nullptr; P.idx = idx.as<int32_t>();
+    P.faceN = fn.as<double>(); P.count = cnt.as<unsigned>(); P.cursor = cur.as<unsigned>(); P.entries = ent.as<unsigned>();
+    P.vnorm = vn.as<double>(); P.error = err.as<int>();
+    const int gV = (int)((nV + RT_PLY_THREADS - 1) / RT_PLY_THREADS), gF = (int)((nF + RT_PLY_THREADS - 1) / RT_PLY_THREADS),
+              gT = (int)((nT + RT_PLY_THREADS - 1) / RT_PLY_THREADS);
+    int64_t n = 0;
+    PCK(cudaEventRecord(e0, 0));
+    if (gV > 0) { RT_LAUNCH(plyVertices, gV, RT_PLY_THREADS, 0, P); n++; }
+    if (gF > 0) { RT_LAUNCH(plyFaces, gF, RT_PLY_THREADS, 0, P); n++; }
+    int herr = 0;
+    PCK(cudaMemcpy(&herr, err.p, 4, cudaMemcpyDeviceToHost));      // indices are validated before anything dereferences them
+    if (herr == 1) { *msg = "face records with differing vertex counts (device ingest takes uniform triangle or quad lists)"; return -1; }
+    if (herr == 2) { *msg = "mesh face index out of range"; return -1; }
+    if (gT > 0 && !fileNormals) { RT_LAUNCH(plyFaceNormals, gT, RT_PLY_THREADS, 0, P, nT, needSmooth ? 1 : 0); n++; }
+    if (needSmooth && gT > 0) {
+        RT_LAUNCH(scanBlocks, scanBlocksN, RT_PLY_THREADS, 0, P.count, nV + 1, sums.as<unsigned>());
+        RT_LAUNCH(scanSums, 1, 1, 0, sums.as<unsigned>(), scanBlocksN);
+        RT_LAUNCH(scanAdd, scanBlocksN, RT_PLY_THREADS, 0, P.count, nV + 1, sums.as<unsigned>());
+        RT_LAUNCH(plyFillAdjacency, gT, RT_PLY_THREADS, 0, P, nT);
+        RT_LAUNCH(plyVertexNormals, gV, RT_PLY_THREADS, 0, P);
+        n += 5;
+    }
+    if (gT > 0) { RT_LAUNCH(plyEmit, gT, RT_PLY_THREADS, 0, P, nT, needSmooth ? 1 : 0, tv.as<double>(), tn.as<double>()); n++; }
+    PCK(cudaEventRecord(e1, 0));
+    PCK(cudaGetLastError());
+    PCK(cudaMemcpy(triVertsOut, tv.p, (size_t)nT * 72, cudaMemcpyDeviceToHost));
+    PCK(cudaMemcpy(triNormalsOut, tn.p, (size_t)nT * 72, cudaMemcpyDeviceToHost));
+    float ms = 0;
+    PCK(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (launches) *launches = n;
+    if (deviceMs) *deviceMs = ms;
+    return 0;
+#undef PCK
+}
+
+}  // namespace rtg

@@ -20,6 +20,11 @@
 
 using namespace rtg;
 
+namespace rtg {   // ply_ingest.cu
+int plyIngestDevice(const rt_ply_layout& L, const void* vertexBlock, const void* faceBlock, int smooth, double* triVertsOut,
+                    double* triNormalsOut, const char** msg, int64_t* launches, double* deviceMs);
+}
+
 namespace {
 
 thread_local std::string g_err;
@@ -565,6 +570,33 @@ int32_t rt_scene_update_instances(rt_scene_t* sc, rt_instance* instances, int64_
     }
     CK(cudaStreamSynchronize(st));       // the staging buffers are free again when this returns
     sc->updateLaunches = (anyDerived ? 1 : 0) + (sc->info.tlasNodes > 0 ? 1 : 0);
+    return RT_OK;
+}
+
+int32_t rt_ply_ingest(const rt_ply_layout* L, const void* vertexBlock, const void* faceBlock, int32_t smooth, int32_t device,
+                      double* triVerticesOut, double* triNormalsOut, rt_ply_stats* statsOut) {
+    if (!L || !triVerticesOut || !triNormalsOut) return fail(RT_ERR_INVALID, "rt_ply_ingest: null argument");
+    if (L->vertexCount < 0 || L->faceCount < 0 || L->vertexStride < 12 || (L->verticesPerFace != 3 && L->verticesPerFace != 4) ||
+        L->faceCountBytes < 1 || L->faceCountBytes > 4 || (L->faceIndexBytes != 1 && L->faceIndexBytes != 2 && L->faceIndexBytes != 4) ||
+        L->faceLeadBytes < 0 || L->faceTrailBytes < 0)
+        return fail(RT_ERR_INVALID, "rt_ply_ingest: inconsistent layout");
+    for (int a = 0; a < 3; a++)
+        if (L->posOffset[a] < 0 || L->posOffset[a] + 4 > L->vertexStride || L->normalOffset[a] + 4 > L->vertexStride)
+            return fail(RT_ERR_INVALID, "rt_ply_ingest: property offset outside the vertex record");
+    if ((L->vertexCount > 0 && !vertexBlock) || (L->faceCount > 0 && !faceBlock)) return fail(RT_ERR_INVALID, "rt_ply_ingest: null block");
+    if (L->vertexCount >= ((int64_t)1 << 31) || L->faceCount >= ((int64_t)1 << 30)) return fail(RT_ERR_UNSUPPORTED, "rt_ply_ingest: mesh too large for 32-bit indices");
+    int ndev = 0;
+    CK(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail(RT_ERR_INVALID, "invalid CUDA device index");
+    CK(cudaSetDevice(device));
+    const char* msg = "";
+    int64_t launches = 0;
+    double ms = 0;
+    if (plyIngestDevice(*L, vertexBlock, faceBlock, smooth, triVerticesOut, triNormalsOut, &msg, &launches, &ms) != 0) {
+        cudaGetLastError();
+        return fail(RT_ERR_INVALID, std::string("rt_ply_ingest: ") + msg);
+    }
+    if (statsOut) { statsOut->triangles = L->faceCount * (L->verticesPerFace == 4 ? 2 : 1); statsOut->kernelLaunches = launches; statsOut->deviceMs = ms; }
     return RT_OK;
 }
 

@@ -2,6 +2,7 @@
 // small `rth_*` C surface Python tests and bench.py drive them through.
 #include <chrono>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "raytracer_host.hpp"
@@ -43,6 +44,14 @@ int Renderer::render(const pk::Scene& scene, int cameraIndex, std::vector<double
                      ids ? ids->data() : nullptr, stats);
 }
 
+// Where PLY meshes are ingested: RTCUDA_INGEST=host keeps the host loader; otherwise the engine's CUDA device when
+// there is one (the render path needs it anyway).
+static int ingestDeviceFor(int device) {
+    const char* e = std::getenv("RTCUDA_INGEST");
+    if (e && std::strcmp(e, "host") == 0) return -1;
+    return rt_device_count() > device && device >= 0 ? device : -1;
+}
+
 int Renderer::refit(RTContext& ctx) {
     return rt_scene_update_instances(handle_, ctx.instances.data(), (int64_t)ctx.instances.size(), nullptr);
 }
@@ -64,7 +73,7 @@ RayTracerEngine::RayTracerEngine(const std::string& url, int device) {
         return;
     }
     hasScene_ = true;
-    ctx_ = RTContext(scene_);                              // RTContext(scene:) :44
+    ctx_ = RTContext(scene_, ingestDeviceFor(device));     // RTContext(scene:) :44
     renderer_.reset(new Renderer(ctx_, scene_, device));   // Renderer(ctx:) :45
     if (!renderer_->valid()) { loadError_ = renderer_->error(); renderer_.reset(); }
 }
@@ -232,7 +241,8 @@ rth_context_t* rth_context_create(const char* sceneUrl) {
         auto* s = new std::pair<pk::Scene, rthost::RTContext>();
         std::string err;
         if (!pk::loadSceneBlob(sceneUrl, s->first, err)) { g_herr = err; delete s; return nullptr; }
-        s->second = rthost::RTContext(s->first);
+        const char* ing = std::getenv("RTCUDA_INGEST");   // flatten-only contexts ingest on the host unless asked
+        s->second = rthost::RTContext(s->first, (ing && std::strcmp(ing, "device") == 0 && rt_device_count() > 0) ? 0 : -1);
         return reinterpret_cast<rth_context_t*>(s);
     } catch (const std::exception& ex) {
         g_herr = ex.what();

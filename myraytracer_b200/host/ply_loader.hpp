@@ -17,6 +17,8 @@
 #include <string>
 #include <vector>
 
+#include "../../include/rtcuda.h"
+
 namespace rthost {
 
 struct PlyMesh {
@@ -153,6 +155,97 @@ inline bool loadPly(const std::string& path, PlyMesh& mesh, std::string& err) {
     }
     if (!gotVerts) { err = "vertex data missing"; return false; }
     if (!gotFaces) { err = "face data missing"; return false; }
+    return true;
+}
+
+// ---- raw element blocks for the device ingest (rt_ply_ingest, include/rtcuda.h) -----------------------------------
+// Eligible files: binary_little_endian; first element `vertex` with scalar properties only, x / y / z (and nx / ny /
+// nz when present) of type float; second element `face` with exactly one list property (vertex_indices, 4-byte
+// indices) and any scalar properties around it, every face with the same number of vertices, 3 or 4 (the record size
+// is checked against the file; the per-face counts are verified on the device).  Anything else — ascii, big endian,
+// double coordinates, mixed polygons — is read by loadPly above.
+struct PlyBlocks {
+    rt_ply_layout layout{};
+    std::vector<unsigned char> vertexBlock, faceBlock;
+};
+
+inline bool loadPlyBlocks(const std::string& path, PlyBlocks& out, std::string& why) {
+    using namespace plydetail;
+    FILE* f = std::fopen(path.c_str(), "rb");
+    if (!f) { why = "cannot open " + path; return false; }
+    struct Closer { FILE* f; ~Closer() { std::fclose(f); } } closer{f};
+    char line[512];
+    if (!std::fgets(line, sizeof line, f) || std::strncmp(line, "ply", 3) != 0) { why = "not a PLY file"; return false; }
+    int fmt = -1;
+    std::vector<Elem> elems;
+    bool header = false;
+    while (std::fgets(line, sizeof line, f)) {
+        std::istringstream ss(line);
+        std::string kw;
+        ss >> kw;
+        if (kw == "format") { std::string s; ss >> s; fmt = s == "binary_little_endian" ? 1 : 0; }
+        else if (kw == "element") { Elem e; ss >> e.name >> e.count; elems.push_back(e); }
+        else if (kw == "property" && !elems.empty()) {
+            Prop p; std::string t; ss >> t;
+            if (t == "list") { std::string ct, it; ss >> ct >> it >> p.name; p.isList = true; p.countType = typeOf(ct); p.type = typeOf(it); }
+            else { p.type = typeOf(t); ss >> p.name; }
+            if (p.type < 0 || (p.isList && p.countType < 0)) { why = "unknown property type"; return false; }
+            elems.back().props.push_back(p);
+        } else if (kw == "end_header") { header = true; break; }
+    }
+    if (!header || fmt != 1) { why = "not binary_little_endian"; return false; }
+    if (elems.size() < 2 || elems[0].name != "vertex" || elems[1].name != "face") { why = "elements are not vertex, face"; return false; }
+    rt_ply_layout& L = out.layout;
+    L = rt_ply_layout{};
+    for (int a = 0; a < 3; a++) { L.posOffset[a] = -1; L.normalOffset[a] = -1; }
+    int off = 0;
+    for (const Prop& p : elems[0].props) {
+        if (p.isList) { why = "list property in the vertex element"; return false; }
+        int* slot = nullptr;
+        if (p.name == "x") slot = &L.posOffset[0]; else if (p.name == "y") slot = &L.posOffset[1]; else if (p.name == "z") slot = &L.posOffset[2];
+        else if (p.name == "nx") slot = &L.normalOffset[0]; else if (p.name == "ny") slot = &L.normalOffset[1]; else if (p.name == "nz") slot = &L.normalOffset[2];
+        if (slot) { if (p.type != 6) { why = "coordinates are not float"; return false; } *slot = off; }
+        off += sizeOf(p.type);
+    }
+    if (L.posOffset[0] < 0 || L.posOffset[1] < 0 || L.posOffset[2] < 0) { why = "vertex data missing"; return false; }
+    if (L.normalOffset[0] < 0 || L.normalOffset[1] < 0 || L.normalOffset[2] < 0) L.normalOffset[0] = L.normalOffset[1] = L.normalOffset[2] = -1;
+    L.vertexStride = off;
+    L.vertexCount = (int64_t)elems[0].count;
+    L.faceCount = (int64_t)elems[1].count;
+    bool seenList = false;
+    for (const Prop& p : elems[1].props) {
+        if (p.isList) {
+            if (seenList || (p.name != "vertex_indices" && p.name != "vertex_index")) { why = "unexpected list property in the face element"; return false; }
+            if (sizeOf(p.type) != 4 || p.type > 5) { why = "indices are not 4-byte integers"; return false; }
+            seenList = true;
+            L.faceCountBytes = sizeOf(p.countType); L.faceIndexBytes = 4;
+            if (p.countType > 5) { why = "list count is not an integer"; return false; }
+        } else if (!seenList) L.faceLeadBytes += sizeOf(p.type);
+        else L.faceTrailBytes += sizeOf(p.type);
+    }
+    if (!seenList) { why = "face data missing"; return false; }
+    const long dataStart = std::ftell(f);
+    std::fseek(f, 0, SEEK_END);
+    const int64_t fileBytes = (int64_t)std::ftell(f) - dataStart;
+    const int64_t vBytes = L.vertexCount * L.vertexStride;
+    if (vBytes > fileBytes) { why = "truncated PLY data"; return false; }
+    L.verticesPerFace = 3;
+    if (L.faceCount > 0) {
+        std::fseek(f, dataStart + (long)vBytes + L.faceLeadBytes, SEEK_SET);
+        unsigned char c[4] = {0, 0, 0, 0};
+        if (std::fread(c, 1, (size_t)L.faceCountBytes, f) != (size_t)L.faceCountBytes) { why = "truncated PLY data"; return false; }
+        const unsigned k = (unsigned)c[0] | ((unsigned)c[1] << 8) | ((unsigned)c[2] << 16) | ((unsigned)c[3] << 24);
+        if (k != 3 && k != 4) { why = "polygons with more than 4 vertices"; return false; }
+        L.verticesPerFace = (int32_t)k;
+    }
+    const int64_t rec = L.faceLeadBytes + L.faceCountBytes + (int64_t)L.verticesPerFace * L.faceIndexBytes + L.faceTrailBytes;
+    const int64_t fBytes = L.faceCount * rec;
+    if (vBytes + fBytes > fileBytes || (elems.size() == 2 && vBytes + fBytes != fileBytes)) { why = "faces are not uniform"; return false; }
+    out.vertexBlock.resize((size_t)vBytes);
+    out.faceBlock.resize((size_t)fBytes);
+    std::fseek(f, dataStart, SEEK_SET);
+    if ((vBytes && std::fread(out.vertexBlock.data(), 1, (size_t)vBytes, f) != (size_t)vBytes) ||
+        (fBytes && std::fread(out.faceBlock.data(), 1, (size_t)fBytes, f) != (size_t)fBytes)) { why = "truncated PLY data"; return false; }
     return true;
 }
 

@@ -44,7 +44,11 @@ struct RTContext {
     std::vector<std::vector<double>> blasPrimBounds;
 
     RTContext() {}
-    explicit RTContext(const pk::Scene& scene);
+    // ingestDevice >= 0: PLY meshes are ingested on that CUDA device (rt_ply_ingest) where the file layout allows;
+    // -1: everything on the host.  Same arrays either way.
+    explicit RTContext(const pk::Scene& scene, int ingestDevice = -1);
+    int64_t deviceIngestedTriangles = 0;
+    double deviceIngestMs = 0;
     int64_t triangleCount() const { return (int64_t)triVertices.size() / 9; }
     // Animation: a new localToWorld for instance i — worldToLocal, normalMatrix and worldBounds re-derived exactly as
     // RTContext.refitTLAS step 1 does (Models/RTContext.swift:889-912).  m16: column-major 4x4.

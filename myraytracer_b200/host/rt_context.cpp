@@ -99,7 +99,7 @@ void RTContext::setInstanceTransform(size_t i, const double* m16, bool boundsOnD
     }
 }
 
-RTContext::RTContext(const pk::Scene& scene) {
+RTContext::RTContext(const pk::Scene& scene, int ingestDevice) {
     intersectionTestEpsilon = scene.intersectionTestEpsilon;
     shadowRayEpsilon = scene.shadowRayEpsilon;
     for (const pk::Material& m : scene.materials) {
@@ -198,7 +198,27 @@ RTContext::RTContext(const pk::Scene& scene) {
             size_t nPos = 0;
             std::vector<double> normals;
             const bool fromPLY = !object.plyPath.empty();
-            if (fromPLY) {
+            // PLY -> device ingest (rt_ply_ingest): the file's raw vertex / face blocks go to the GPU, which returns
+            // the per-triangle arrays the loops below would produce (same bits); files the device path does not take
+            // (ascii, big endian, mixed polygons ...) are read and flattened here
+            std::vector<double> devTV, devTN;
+            bool fromDevice = false;
+            if (fromPLY && ingestDevice >= 0) {
+                PlyBlocks blocks; std::string why;
+                if (loadPlyBlocks(pk::dirOf(scene.path) + object.plyPath, blocks, why)) {
+                    const int64_t nT = blocks.layout.faceCount * (blocks.layout.verticesPerFace == 4 ? 2 : 1);
+                    devTV.resize((size_t)nT * 9); devTN.resize((size_t)nT * 9);
+                    rt_ply_stats ps{};
+                    const int rc = rt_ply_ingest(&blocks.layout, blocks.vertexBlock.data(), blocks.faceBlock.data(), isSmooth ? 1 : 0,
+                                                 ingestDevice, devTV.data(), devTN.data(), &ps);
+                    if (rc == RT_OK) { fromDevice = true; deviceIngestedTriangles += nT; deviceIngestMs += ps.deviceMs; }
+                    else if (std::string(rt_last_error()).find("index out of range") != std::string::npos) { warnings.push_back("mesh face index out of range"); continue; }
+                    else warnings.push_back(std::string("device ingest refused ") + object.plyPath + ": " + rt_last_error());
+                }
+            }
+            if (fromDevice) {
+                // nothing to load on the host
+            } else if (fromPLY) {
                 PlyMesh pm; std::string err;
                 if (!loadPly(pk::dirOf(scene.path) + object.plyPath, pm, err)) { warnings.push_back("PLY load failed: " + object.plyPath + " (" + err + ")"); continue; }
                 faceIdx = std::move(pm.indices); posStore = std::move(pm.positions); normals = std::move(pm.normals);
@@ -209,15 +229,15 @@ RTContext::RTContext(const pk::Scene& scene) {
                 nPos = scene.vertexData.size();
             }
             auto P = [&](int64_t i) -> D3 { return D3{pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]}; };
-            const int64_t triCount = (int64_t)faceIdx.size() / 3;
+            const int64_t triCount = fromDevice ? (int64_t)devTV.size() / 9 : (int64_t)faceIdx.size() / 3;
             const int64_t offset = (!normals.empty() || fromPLY) ? 0 : 1;    // :300-301 (with normals: used as-is, :270-272)
             bool bad = false;
-            for (int64_t k = 0; k < triCount * 3; k++)
+            for (int64_t k = 0; k < triCount * 3 && !fromDevice; k++)
                 if (faceIdx[k] - offset < 0 || (size_t)(faceIdx[k] - offset) >= nPos) bad = true;
             if (bad) { warnings.push_back("mesh face index out of range"); continue; }
             std::vector<D3> vtxNormals;
             std::vector<D3> faceNormals;
-            if (normals.empty()) {
+            if (normals.empty() && !fromDevice) {
                 faceNormals.resize((size_t)triCount);
                 for (int64_t t = 0; t < triCount; t++) {                     // :307-314
                     const D3 v0 = P(faceIdx[3 * t] - offset), v1 = P(faceIdx[3 * t + 1] - offset), v2 = P(faceIdx[3 * t + 2] - offset);
@@ -234,10 +254,16 @@ RTContext::RTContext(const pk::Scene& scene) {
             std::vector<double> pb;
             pb.reserve((size_t)triCount * 6);
             for (int64_t t = 0; t < triCount; t++) {
-                const int64_t i0 = faceIdx[3 * t] - offset, i1 = faceIdx[3 * t + 1] - offset, i2 = faceIdx[3 * t + 2] - offset;
-                const D3 v0 = P(i0), v1 = P(i1), v2 = P(i2);
+                const int64_t i0 = fromDevice ? 0 : faceIdx[3 * t] - offset, i1 = fromDevice ? 0 : faceIdx[3 * t + 1] - offset,
+                              i2 = fromDevice ? 0 : faceIdx[3 * t + 2] - offset;
+                const double* dv = fromDevice ? &devTV[(size_t)t * 9] : nullptr;
+                const double* dn = fromDevice ? &devTN[(size_t)t * 9] : nullptr;
+                const D3 v0 = fromDevice ? D3{dv[0], dv[1], dv[2]} : P(i0), v1 = fromDevice ? D3{dv[3], dv[4], dv[5]} : P(i1),
+                         v2 = fromDevice ? D3{dv[6], dv[7], dv[8]} : P(i2);
                 D3 n0, n1, n2;
-                if (!normals.empty()) {
+                if (fromDevice) {
+                    n0 = D3{dn[0], dn[1], dn[2]}; n1 = D3{dn[3], dn[4], dn[5]}; n2 = D3{dn[6], dn[7], dn[8]};
+                } else if (!normals.empty()) {
                     n0 = D3{normals[3 * i0], normals[3 * i0 + 1], normals[3 * i0 + 2]};
                     n1 = D3{normals[3 * i1], normals[3 * i1 + 1], normals[3 * i1 + 2]};
                     n2 = D3{normals[3 * i2], normals[3 * i2 + 1], normals[3 * i2 + 2]};

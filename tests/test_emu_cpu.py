@@ -188,6 +188,24 @@ def test_image_writers_round_trip(tmp_path, emu):
         write_image(str(tmp_path / "a.jpg"), img)
 
 
+def test_emulated_ply_ingest_equals_host_flatten(tmp_path, emu, monkeypatch):
+    """rt_ply_ingest (raw PLY blocks -> kernels -> per-triangle FP64 arrays) against the host loader + flatten loops of
+    the mirror, which tests/test_host_cpu.py in turn holds against the oracle's: same vertices and normals, bit for bit
+    (NaN normals of unused vertices included), for every layout the device path takes; the others go to the host."""
+    import ply_cases
+    from myraytracer_b200.engine import FlatContext
+    for name, path, n_tris, device in ply_cases.make_cases(str(tmp_path)):
+        monkeypatch.setenv("RTCUDA_INGEST", "host")
+        hv, hn = FlatContext(path).triangles()
+        before = emu.rtemu_kernel_launches()
+        monkeypatch.setenv("RTCUDA_INGEST", "device")
+        dv, dn = FlatContext(path).triangles()
+        ran = emu.rtemu_kernel_launches() - before
+        assert len(hv) == n_tris and len(dv) == n_tris, name
+        assert np.array_equal(hv, dv) and np.array_equal(hn, dn, equal_nan=True), name
+        assert (ran >= 2) == device, (name, ran)          # the kernels ran / the file was left to the host loader
+
+
 def test_emulator_is_not_the_product(emu):
     """The product loader never hands out the emulation library, and the emulation build says what it is."""
     import os

@@ -215,6 +215,24 @@ def test_animation_refit_matches_rebuilt_scenes(scene_dir):
         assert (f == 0.0) == np.array_equal(got.linear, base.linear)
 
 
+def test_ply_device_ingest_equals_host_flatten(tmp_path, scene_dir, monkeypatch):
+    """rt_ply_ingest on the B200 (8f row 2): bit-identical to the host loader + flatten loops on every layout of
+    tests/ply_cases.py and on the 999,698-triangle C4 mesh; engines ingest on the device by default."""
+    import time
+    import ply_cases
+    from myraytracer_b200.engine import FlatContext
+    cases = [(n, p, t) for n, p, t, _ in ply_cases.make_cases(str(tmp_path))]
+    cases.append(("c4", scenegen.config_c4(scene_dir, width=64, height=64, samples=1), 999698))
+    for name, path, n_tris in cases:
+        monkeypatch.setenv("RTCUDA_INGEST", "host")
+        t0 = time.perf_counter(); hv, hn = FlatContext(path).triangles(); t_host = time.perf_counter() - t0
+        monkeypatch.setenv("RTCUDA_INGEST", "device")
+        t0 = time.perf_counter(); dv, dn = FlatContext(path).triangles(); t_dev = time.perf_counter() - t0
+        print(f"ingest {name}: {n_tris} triangles, host {t_host * 1e3:.1f} ms, device path {t_dev * 1e3:.1f} ms")
+        assert len(hv) == n_tris and len(dv) == n_tris, name
+        assert np.array_equal(hv, dv) and np.array_equal(hn, dn, equal_nan=True), name
+
+
 def test_error_codes(scene_dir):
     path = scenegen.config_c1(scene_dir, width=32, height=32)
     eng = RayTracerEngine(path)
