@@ -201,19 +201,24 @@ RTContext::RTContext(const pk::Scene& scene, int ingestDevice) {
             // PLY -> device ingest (rt_ply_ingest): the file's raw vertex / face blocks go to the GPU, which returns
             // the per-triangle arrays the loops below would produce (same bits); files the device path does not take
             // (ascii, big endian, mixed polygons ...) are read and flattened here
-            std::vector<double> devTV, devTN;
+            int64_t devTris = 0;
             bool fromDevice = false;
             if (fromPLY && ingestDevice >= 0) {
                 PlyBlocks blocks; std::string why;
                 if (loadPlyBlocks(pk::dirOf(scene.path) + object.plyPath, blocks, why)) {
+                    // the kernels' output lands directly behind the triangles flattened so far
                     const int64_t nT = blocks.layout.faceCount * (blocks.layout.verticesPerFace == 4 ? 2 : 1);
-                    devTV.resize((size_t)nT * 9); devTN.resize((size_t)nT * 9);
+                    const size_t old = triVertices.size();
+                    triVertices.resize(old + (size_t)nT * 9); triNormals.resize(old + (size_t)nT * 9);
                     rt_ply_stats ps{};
                     const int rc = rt_ply_ingest(&blocks.layout, blocks.vertexBlock.data(), blocks.faceBlock.data(), isSmooth ? 1 : 0,
-                                                 ingestDevice, devTV.data(), devTN.data(), &ps);
-                    if (rc == RT_OK) { fromDevice = true; deviceIngestedTriangles += nT; deviceIngestMs += ps.deviceMs; }
-                    else if (std::string(rt_last_error()).find("index out of range") != std::string::npos) { warnings.push_back("mesh face index out of range"); continue; }
-                    else warnings.push_back(std::string("device ingest refused ") + object.plyPath + ": " + rt_last_error());
+                                                 ingestDevice, triVertices.data() + old, triNormals.data() + old, &ps);
+                    if (rc == RT_OK) { fromDevice = true; devTris = nT; deviceIngestedTriangles += nT; deviceIngestMs += ps.deviceMs; }
+                    else {
+                        triVertices.resize(old); triNormals.resize(old);
+                        if (std::string(rt_last_error()).find("index out of range") != std::string::npos) { warnings.push_back("mesh face index out of range"); continue; }
+                        warnings.push_back(std::string("device ingest refused ") + object.plyPath + ": " + rt_last_error());
+                    }
                 }
             }
             if (fromDevice) {
@@ -229,7 +234,7 @@ RTContext::RTContext(const pk::Scene& scene, int ingestDevice) {
                 nPos = scene.vertexData.size();
             }
             auto P = [&](int64_t i) -> D3 { return D3{pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]}; };
-            const int64_t triCount = fromDevice ? (int64_t)devTV.size() / 9 : (int64_t)faceIdx.size() / 3;
+            const int64_t triCount = fromDevice ? devTris : (int64_t)faceIdx.size() / 3;
             const int64_t offset = (!normals.empty() || fromPLY) ? 0 : 1;    // :300-301 (with normals: used as-is, :270-272)
             bool bad = false;
             for (int64_t k = 0; k < triCount * 3 && !fromDevice; k++)
@@ -253,17 +258,31 @@ RTContext::RTContext(const pk::Scene& scene, int ingestDevice) {
             const int64_t firstPrim = (int64_t)prims.size();
             std::vector<double> pb;
             pb.reserve((size_t)triCount * 6);
-            for (int64_t t = 0; t < triCount; t++) {
-                const int64_t i0 = fromDevice ? 0 : faceIdx[3 * t] - offset, i1 = fromDevice ? 0 : faceIdx[3 * t + 1] - offset,
-                              i2 = fromDevice ? 0 : faceIdx[3 * t + 2] - offset;
-                const double* dv = fromDevice ? &devTV[(size_t)t * 9] : nullptr;
-                const double* dn = fromDevice ? &devTN[(size_t)t * 9] : nullptr;
-                const D3 v0 = fromDevice ? D3{dv[0], dv[1], dv[2]} : P(i0), v1 = fromDevice ? D3{dv[3], dv[4], dv[5]} : P(i1),
-                         v2 = fromDevice ? D3{dv[6], dv[7], dv[8]} : P(i2);
+            if (fromDevice) {
+                // vertices and normals are in place; motion vectors, prim records and prim boxes in bulk
+                const int64_t first = triangleCount() - triCount;
+                triMotionBlur.resize((size_t)(first + triCount) * 3);
+                prims.resize((size_t)firstPrim + (size_t)triCount);
+                pb.resize((size_t)triCount * 6);
+                if (blur) anyMotionBlur = true;
+                for (int64_t t = 0; t < triCount; t++) {
+                    double* m = &triMotionBlur[(size_t)(first + t) * 3];
+                    m[0] = mb.x; m[1] = mb.y; m[2] = mb.z;
+                    prims[(size_t)(firstPrim + t)] = rt_prim{RT_GEO_TRIANGLE, isSmooth ? 1 : 0, first + t, matID};
+                    const double* v = &triVertices[(size_t)(first + t) * 9];
+                    double* b = &pb[(size_t)t * 6];
+                    for (int a = 0; a < 3; a++) {
+                        double lo = mn(v[a], mn(v[3 + a], v[6 + a])), hi = mx(v[a], mx(v[3 + a], v[6 + a]));
+                        if (blur) { const double m3 = a == 0 ? mb.x : (a == 1 ? mb.y : mb.z); lo = mn(lo, lo + m3); hi = mx(hi, hi + m3); }
+                        b[a] = lo; b[3 + a] = hi;
+                    }
+                }
+            }
+            for (int64_t t = 0; t < triCount && !fromDevice; t++) {
+                const int64_t i0 = faceIdx[3 * t] - offset, i1 = faceIdx[3 * t + 1] - offset, i2 = faceIdx[3 * t + 2] - offset;
+                const D3 v0 = P(i0), v1 = P(i1), v2 = P(i2);
                 D3 n0, n1, n2;
-                if (fromDevice) {
-                    n0 = D3{dn[0], dn[1], dn[2]}; n1 = D3{dn[3], dn[4], dn[5]}; n2 = D3{dn[6], dn[7], dn[8]};
-                } else if (!normals.empty()) {
+                if (!normals.empty()) {
                     n0 = D3{normals[3 * i0], normals[3 * i0 + 1], normals[3 * i0 + 2]};
                     n1 = D3{normals[3 * i1], normals[3 * i1 + 1], normals[3 * i1 + 2]};
                     n2 = D3{normals[3 * i2], normals[3 * i2 + 1], normals[3 * i2 + 2]};
