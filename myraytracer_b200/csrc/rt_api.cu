@@ -450,6 +450,9 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     S.refTlas = sc->dRefTlas; S.refTlasPrim = sc->dRefTlasPrim; S.refTlasNodes = (int32_t)refTl.nodes.size();
     S.maxDepth = d->maxRecursionDepth;
     std::memcpy(S.ambient, d->ambient, 24); std::memcpy(S.background, d->background, 24);
+    // a scene without instances has no TLAS, and `trace` then returns .zero, not the background
+    // (`guard let tlas = ctx.tlas else { return .zero }`, Object+Extension.swift:98; RTContext.swift:416)
+    if (d->nInstances == 0) S.background[0] = S.background[1] = S.background[2] = 0.0;
     S.eps = d->intersectionTestEpsilon; S.shadowEps = d->shadowRayEpsilon;
 
     cudaDeviceProp prop;

@@ -70,6 +70,23 @@ def test_emulated_kernels_vs_oracle(name, scene_dir, emu):
     assert emu.rtemu_kernel_launches() > before       # the kernels ran (on fibers), not some other path
 
 
+def test_emulated_edge_cases(scene_dir, emu):
+    """tests/edge_cases.py: empty scene (no TLAS: black, not background), one-instance TLAS, 1x1 / 9x5 / 33x17 images,
+    sample counts that are not squares (n = floor(sqrt), sum divided by the count), depth 0 with a mirror — both kernels,
+    linear colours identical to the oracle's."""
+    import edge_cases
+    for name in edge_cases.EDGE_CASES:
+        path = edge_cases.make(scene_dir, name)
+        eng = RayTracerEngine(path)
+        assert eng.ready, (name, eng.load_error)
+        ref = oracle_lib.OracleScene(path).render(want_ids=True, want_linear=True)
+        for variant in (1, 2):
+            got = eng.render(0, want_ids=True, want_linear=True, variant=variant)
+            rep = check(got, ref)
+            assert rep["px_exact"] == 1.0 and rep["rays_gpu"] == rep["rays_ref"], (name, variant, rep)
+            assert np.allclose(got.linear, ref["linear"], rtol=1e-12, atol=1e-9), (name, variant)
+
+
 def test_emulated_shards_and_schedule(scene_dir, emu):
     """Both shard rules partition the frame bit-identically; the learnt tile order does not change it."""
     from myraytracer_b200.distributed import owned_mask

@@ -233,6 +233,22 @@ def test_ply_device_ingest_equals_host_flatten(tmp_path, scene_dir, monkeypatch)
         assert np.array_equal(hv, dv) and np.array_equal(hn, dn, equal_nan=True), name
 
 
+def test_edge_cases_vs_oracle(scene_dir):
+    """tests/edge_cases.py on the B200: empty scene, one-instance TLAS, tiny and ragged images, non-square sample
+    counts, depth 0 with a mirror — both kernels."""
+    import edge_cases
+    for name in edge_cases.EDGE_CASES:
+        path = edge_cases.make(scene_dir, name)
+        eng = RayTracerEngine(path)
+        assert eng.ready, (name, eng.load_error)
+        ref = oracle_lib.OracleScene(path).render(want_ids=True, want_linear=True)
+        for variant in (1, 2):
+            got = eng.render(0, want_ids=True, want_linear=True, variant=variant)
+            rep = parity.compare(got, ref)
+            assert rep["id_agree"] >= 0.9999 and rep["id_bad"] == 0 and rep["px_within_1"] >= 0.999, (name, variant, rep)
+            assert rep["rays_gpu"] == rep["rays_ref"], (name, variant, rep)
+
+
 def test_error_codes(scene_dir):
     path = scenegen.config_c1(scene_dir, width=32, height=32)
     eng = RayTracerEngine(path)
