@@ -20,15 +20,22 @@ import CRTCuda
 final class Renderer: @unchecked Sendable {
     public let ctx: RTContext
     private var handle: OpaquePointer?            // rt_scene_t*
+    private var blasOfInstance = [Int32]()        // rt_instance.blas of every instance (fixed for the scene's life)
 
     /// Renderer(ctx:) — flattens RTContext (Models/RTContext.swift:74-92) into rt_scene_desc and uploads it.
     public init(ctx: RTContext, scene: Scene, device: Int32 = 0) {
         self.ctx = ctx
         var triV = [Double](); triV.reserveCapacity(ctx.triangles.count * 9)
         var triN = [Double](); triN.reserveCapacity(ctx.triangles.count * 9)
+        var triM = [Double](); triM.reserveCapacity(ctx.triangles.count * 3)   // Triangle.motionBlur (RTContext.swift:280,345)
         for t in ctx.triangles {
             for v in [t.v0, t.v1, t.v2] { triV += [v.x, v.y, v.z] }
             for n in [t.n0, t.n1, t.n2] { triN += [n.x, n.y, n.z] }
+            triM += [t.motionBlur.x, t.motionBlur.y, t.motionBlur.z]
+        }
+        var areaLights = ctx.areaLights.map {                                    // Object+Extension.swift:145-186
+            rt_area_light(position: ($0.position.x, $0.position.y, $0.position.z), normal: ($0.normal.x, $0.normal.y, $0.normal.z),
+                          size: $0.size, radiance: ($0.radiance.x, $0.radiance.y, $0.radiance.z))
         }
         var spheres = ctx.spheres.map { rt_sphere(center: ($0.center.x, $0.center.y, $0.center.z), radius: $0.radius) }
         var planes = ctx.planes.map { rt_plane(center: ($0.center.x, $0.center.y, $0.center.z),
@@ -48,6 +55,7 @@ final class Renderer: @unchecked Sendable {
             }
             var ri = rt_instance()
             ri.blas = blasIndex[key]!
+            blasOfInstance.append(ri.blas)
             ri.hasMaterialOverride = inst.materialOverride == nil ? 0 : 1
             ri.materialOverride = Int64(inst.materialOverride ?? 0)
             withUnsafeMutableBytes(of: &ri.localToWorld) { $0.copyBytes(from: Self.bytes(inst.localToWorld)) }
@@ -77,6 +85,7 @@ final class Renderer: @unchecked Sendable {
         desc.nSpheres = Int64(spheres.count); desc.nPlanes = Int64(planes.count)
         desc.nPrims = Int64(prims.count); desc.nBlas = Int64(blas.count); desc.nInstances = Int64(instances.count)
         desc.nMaterials = Int64(materials.count); desc.nPointLights = Int64(lights.count)
+        desc.nAreaLights = Int64(areaLights.count)
         desc.ambient = (scene.lights.ambient.x, scene.lights.ambient.y, scene.lights.ambient.z)
         desc.background = (scene.backgroundColor.x, scene.backgroundColor.y, scene.backgroundColor.z)
         desc.intersectionTestEpsilon = scene.intersectionTestEpsilon
@@ -88,16 +97,49 @@ final class Renderer: @unchecked Sendable {
             prims.withUnsafeBufferPointer { pr in blas.withUnsafeBufferPointer { b in
             instances.withUnsafeBufferPointer { i in materials.withUnsafeBufferPointer { m in
             lights.withUnsafeBufferPointer { l -> OpaquePointer? in
+            triM.withUnsafeBufferPointer { tm in areaLights.withUnsafeBufferPointer { al -> OpaquePointer? in
+                desc.triMotionBlur = tm.baseAddress; desc.areaLights = al.baseAddress
                 desc.triVertices = v.baseAddress; desc.triNormals = n.baseAddress
                 desc.spheres = s.baseAddress; desc.planes = p.baseAddress; desc.prims = pr.baseAddress
                 desc.blas = b.baseAddress; desc.instances = i.baseAddress; desc.materials = m.baseAddress
                 desc.pointLights = l.baseAddress
                 return rt_scene_create(&desc, device)          // NULL on failure, never throws (CPly convention)
-            } } } } } } } } }
+            } } } } } } } } } } }
         if handle == nil { print("❌ CRTCuda: \(String(cString: rt_last_error()))") }
     }
 
     deinit { rt_scene_destroy(handle) }              // destroy(NULL) is safe
+
+    /// Animation: the counterpart of RTContext.refitTLAS (Models/RTContext.swift:883-928), which the reference defines
+    /// but never calls — its batch driver builds a new engine per frame (BatchRender.swift:26-40).  New
+    /// localToWorld matrices for the instances of the resident scene; worldBounds of mesh instances are left inverted
+    /// (+inf / -inf) so that the module derives them on the device; the TLAS is refitted there.
+    public func refit(localToWorld: [Mat4]) throws {
+        guard let handle else { throw NSError(domain: "Render", code: -21, userInfo: [NSLocalizedDescriptionKey: "Renderer not initialized."]) }
+        precondition(localToWorld.count == ctx.instances.count)
+        var updated = [rt_instance]()
+        for (i, inst) in ctx.instances.enumerated() {
+            var ri = rt_instance()
+            ri.blas = blasOfInstance[i]
+            ri.hasMaterialOverride = inst.materialOverride == nil ? 0 : 1
+            ri.materialOverride = Int64(inst.materialOverride ?? 0)
+            let M = localToWorld[i]
+            withUnsafeMutableBytes(of: &ri.localToWorld) { $0.copyBytes(from: Self.bytes(M)) }
+            withUnsafeMutableBytes(of: &ri.worldToLocal) { $0.copyBytes(from: Self.bytes(M.inverse)) }
+            withUnsafeMutableBytes(of: &ri.normalMatrix) { $0.copyBytes(from: Self.bytes3(normalTransformMatrix(from: M))) }
+            if inst.blas.prims.count > 1 {
+                ri.worldBounds = (.infinity, .infinity, .infinity, -.infinity, -.infinity, -.infinity)      // derive on the device
+            } else {
+                let b = inst.blas.prims[0].bounds.transformed(by: M)
+                ri.worldBounds = (b.minP.x, b.minP.y, b.minP.z, b.maxP.x, b.maxP.y, b.maxP.z)
+            }
+            updated.append(ri)
+        }
+        let status = updated.withUnsafeMutableBufferPointer { rt_scene_update_instances(handle, $0.baseAddress, Int64($0.count), nil) }
+        guard status == RT_OK else {
+            throw NSError(domain: "Render", code: Int(status), userInfo: [NSLocalizedDescriptionKey: String(cString: rt_last_error())])
+        }
+    }
 
     /// render(scene:cameraIndex:progressRow:) — same signature and result as the reference (:52-56): W*H Vec3, 0..255 scale.
     @Sendable public func render(scene: Scene, cameraIndex: Int = 0,
