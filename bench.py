@@ -356,7 +356,8 @@ def run_ours(args):
                              f"{info['deviceBytes'] / 1e6:.0f} MB"},
             "wall_ms_per_step": wall * 1e3 / args.steps, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
             "roofline": roofline, "build_ms": info["buildMs"], "upload_ms": info["uploadMs"],
-            "bvh_build": "device LBVH" if info["deviceBuiltBlas"] else "host binned SAH"}
+            "bvh_build": ("host binned SAH" if not info["deviceBuiltBlas"] else
+                          "device binned SAH" if args.build == "device-sah" else "device LBVH")}
     if world == 1 and not args.no_cpu:
         mr, ci = cpu_sample(path, target_s=args.cpu_seconds)
         line["cpu_baseline"] = {"value": mr, "unit": UNIT, "cores": ci["cores"], "kind": "port", "sample": ci["sample"],
@@ -382,8 +383,9 @@ def main():
     ap.add_argument("--config", choices=sorted(BENCH_CONFIGS), default="c4")
     ap.add_argument("--shard", choices=["tiles", "rows"], default=None,
                     help="N>1: 8-row chunks round-robin (default) or 8x4 tiles dealt along diagonals (p2p only)")
-    ap.add_argument("--build", choices=["host", "device"], default=None,
-                    help="who builds the mesh BVHs: host = multi-threaded binned SAH (default), device = CUDA LBVH")
+    ap.add_argument("--build", choices=["host", "device", "device-sah"], default=None,
+                    help="who builds the mesh BVHs: host = multi-threaded binned SAH (default), device = CUDA LBVH, "
+                         "device-sah = the host builder's tree made by CUDA kernels")
     ap.add_argument("--schedule", choices=["adaptive", "spatial"], default="adaptive",
                     help="rt_render_params.scheduleMode: tile order learnt from the previous frame, or top to bottom")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")

@@ -131,9 +131,12 @@ typedef int (*rt_progress_fn)(int32_t rowsDone, int32_t rowsTotal, void* user);
 /* rt_scene_desc.buildMode.  The reference builds on the CPU (Accelearion/BVH.swift:78-250); the image does not depend
  * on the tree.  HOST_SAH (default): multi-threaded binned SAH, best traversal speed.  DEVICE_LBVH: Morton-order radix
  * tree built by CUDA kernels, ~20x faster to build, slower to traverse; a tree too deep for the traversal stack falls
- * back to HOST_SAH for that mesh.  The environment variable RTCUDA_BUILD=device|host overrides the field. */
+ * back to HOST_SAH for that mesh.  DEVICE_SAH: the HOST_SAH builder's own splits and leaves, made level by level by
+ * CUDA kernels (per-bin boxes through order-preserving 64-bit atomics) — the same tree up to node numbering and the
+ * triangle order inside a leaf.  The environment variable RTCUDA_BUILD=device|device-sah|host overrides the field. */
 #define RT_BUILD_HOST_SAH    0
 #define RT_BUILD_DEVICE_LBVH 1
+#define RT_BUILD_DEVICE_SAH  2
 
 #define RT_SHARD_ROWS  0
 #define RT_SHARD_TILES 1
@@ -191,7 +194,7 @@ typedef struct rt_scene_info {
     int64_t deviceBytes;
     double buildMs, uploadMs;
     int32_t device;
-    int32_t deviceBuiltBlas;      /* mesh BVHs built by the device builder (RT_BUILD_DEVICE_LBVH) */
+    int32_t deviceBuiltBlas;      /* mesh BVHs built by a device builder (RT_BUILD_DEVICE_*) */
 } rt_scene_info;
 
 typedef struct rt_scene rt_scene_t;

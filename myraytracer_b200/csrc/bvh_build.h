@@ -46,6 +46,10 @@ namespace rtg {
 // triangles.  dVerts: the scene's triangle vertices (9 doubles each) on the current device.  The caller checks
 // out.maxDepth against its traversal stack (a radix tree over clustered keys can be deep) and may fall back to buildBlas.
 cudaError_t buildBlasDevice(const double* dVerts, const BlasBuildInput& in, BlasBuildOutput& out);
+// Device-side binned SAH (bvh_build_sah_gpu.cu): buildBlas's own splits and leaves, one tree level per round of
+// kernels.  Grows the boxes by in.motionBlur like buildBlas.  out.maxDepth = 1 << 30 when the tree would grow past
+// depthLimit levels.  *launches (optional): kernels run.
+cudaError_t buildBlasDeviceSah(const double* dVerts, const BlasBuildInput& in, BlasBuildOutput& out, int depthLimit, int64_t* launches);
 #endif
 
 // TLAS over instance world bounds (FP64, one instance per leaf).

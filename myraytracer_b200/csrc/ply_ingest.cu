@@ -127,6 +127,16 @@ __global__ void __launch_bounds__(RT_PLY_THREADS) scanAdd(unsigned* a, long long
     for (int k = 0; k < RT_SCAN_ITEMS; k++) if (base + k < n) a[base + k] += off;
 }
 
+// In-place exclusive scan of a[0 .. n); blockSums holds ceil(n / 2048) entries.  Also used by bvh_build_sah_gpu.cu.
+cudaError_t launchExclusiveScan(unsigned* a, long long n, unsigned* blockSums, cudaStream_t stream) {
+    const int blocks = (int)((n + RT_SCAN_BLOCK - 1) / RT_SCAN_BLOCK);
+    if (blocks <= 0) return cudaSuccess;
+    RT_LAUNCH(scanBlocks, blocks, RT_PLY_THREADS, stream, a, n, blockSums);
+    RT_LAUNCH(scanSums, 1, 1, stream, blockSums, blocks);
+    RT_LAUNCH(scanAdd, blocks, RT_PLY_THREADS, stream, a, n, blockSums);
+    return cudaGetLastError();
+}
+
 __global__ void __launch_bounds__(RT_PLY_THREADS) plyFillAdjacency(PlyDev P, long long nTris) {
     const long long t = (long long)blockIdx.x * RT_PLY_THREADS + threadIdx.x;
     if (t >= nTris) return;
@@ -204,8 +214,12 @@ int plyIngestDevice(const rt_ply_layout& L, const void* vertexBlock, const void*
     if (fileNormals) PCK(vnf.alloc((size_t)nV * 24));
     const int scanBlocksN = (int)((nV + 1 + RT_SCAN_BLOCK - 1) / RT_SCAN_BLOCK);
     if (needSmooth) { PCK(ent.alloc((size_t)nT * 12)); PCK(vn.alloc((size_t)nV * 24)); PCK(sums.alloc((size_t)scanBlocksN * 4)); }
-    cudaEvent_t e0, e1;
-    PCK(cudaEventCreate(&e0)); PCK(cudaEventCreate(&e1));
+    struct Ev {                      // destroyed on every return path
+        cudaEvent_t e = nullptr;
+        ~Ev() { if (e) cudaEventDestroy(e); }
+    } ev0, ev1;
+    PCK(cudaEventCreate(&ev0.e)); PCK(cudaEventCreate(&ev1.e));
+    const cudaEvent_t e0 = ev0.e, e1 = ev1.e;
     PCK(cudaMemcpyAsync(vb.p, vertexBlock, (size_t)nV * L.vertexStride, cudaMemcpyHostToDevice, 0));
     PCK(cudaMemcpyAsync(fb.p, faceBlock, (size_t)nF * P.faceRecord, cudaMemcpyHostToDevice, 0));
     PCK(cudaMemsetAsync(err.p, 0, 4, 0));
@@ -225,9 +239,7 @@ int plyIngestDevice(const rt_ply_layout& L, const void* vertexBlock, const void*
     if (herr == 2) { *msg = "mesh face index out of range"; return -1; }
     if (gT > 0 && !fileNormals) { RT_LAUNCH(plyFaceNormals, gT, RT_PLY_THREADS, 0, P, nT, needSmooth ? 1 : 0); n++; }
     if (needSmooth && gT > 0) {
-        RT_LAUNCH(scanBlocks, scanBlocksN, RT_PLY_THREADS, 0, P.count, nV + 1, sums.as<unsigned>());
-        RT_LAUNCH(scanSums, 1, 1, 0, sums.as<unsigned>(), scanBlocksN);
-        RT_LAUNCH(scanAdd, scanBlocksN, RT_PLY_THREADS, 0, P.count, nV + 1, sums.as<unsigned>());
+        PCK(launchExclusiveScan(P.count, nV + 1, sums.as<unsigned>(), 0));
         RT_LAUNCH(plyFillAdjacency, gT, RT_PLY_THREADS, 0, P, nT);
         RT_LAUNCH(plyVertexNormals, gV, RT_PLY_THREADS, 0, P);
         n += 5;
@@ -239,7 +251,6 @@ int plyIngestDevice(const rt_ply_layout& L, const void* vertexBlock, const void*
     PCK(cudaMemcpy(triNormalsOut, tn.p, (size_t)nT * 72, cudaMemcpyDeviceToHost));
     float ms = 0;
     PCK(cudaEventElapsedTime(&ms, e0, e1));
-    cudaEventDestroy(e0); cudaEventDestroy(e1);
     if (launches) *launches = n;
     if (deviceMs) *deviceMs = ms;
     return 0;

@@ -183,9 +183,11 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     const double t0 = nowMs();
 
     // ---- who builds the mesh BVHs (rt_scene_desc.buildMode, overridden by RTCUDA_BUILD)
-    bool deviceBuild = d->buildMode == RT_BUILD_DEVICE_LBVH;
-    if (const char* e = std::getenv("RTCUDA_BUILD")) deviceBuild = std::strcmp(e, "device") == 0;
-    if (d->buildMode != RT_BUILD_HOST_SAH && d->buildMode != RT_BUILD_DEVICE_LBVH) return fail(RT_ERR_INVALID, "rt_scene_desc.buildMode outside 0..1");
+    if (d->buildMode < RT_BUILD_HOST_SAH || d->buildMode > RT_BUILD_DEVICE_SAH) return fail(RT_ERR_INVALID, "rt_scene_desc.buildMode outside 0..2");
+    int buildMode = d->buildMode;
+    if (const char* e = std::getenv("RTCUDA_BUILD"))
+        buildMode = std::strcmp(e, "device") == 0 ? RT_BUILD_DEVICE_LBVH : std::strcmp(e, "device-sah") == 0 ? RT_BUILD_DEVICE_SAH : RT_BUILD_HOST_SAH;
+    const bool deviceBuild = buildMode != RT_BUILD_HOST_SAH;
     struct DevVerts {       // the scene's triangle vertices on the device, for the device builder only
         double* p = nullptr;
         ~DevVerts() { cudaFree(p); }
@@ -248,7 +250,11 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
         }
         BlasBuildOutput out;
         bool built = false;
-        if (deviceBuild && bl.primCount >= 2 && !blur) {     // the device builder does not grow boxes by a motion vector
+        if (buildMode == RT_BUILD_DEVICE_SAH && bl.primCount >= 2) {
+            CK(buildBlasDeviceSah(dVerts.p, in, out, renderStackCapacity() - 2, nullptr));
+            built = out.maxDepth <= renderStackCapacity() - 2;      // deeper than the stacks: buildBlas reports it below
+            if (built) deviceBuilt++;
+        } else if (buildMode == RT_BUILD_DEVICE_LBVH && bl.primCount >= 2 && !blur) {   // the radix-tree builder does not grow boxes by a motion vector
             CK(buildBlasDevice(dVerts.p, in, out));
             built = out.maxDepth <= renderStackCapacity() - 2;      // too deep for the stacks: the SAH builder takes over
             if (built) deviceBuilt++;

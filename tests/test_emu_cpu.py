@@ -230,3 +230,76 @@ def test_emulator_is_not_the_product(emu):
     assert os.path.basename(capi.LIB_PATH) == "librtcuda.so"
     assert "emu" not in capi.LIB_PATH
     assert hasattr(emu, "rtemu_kernel_launches")
+
+
+SAH_CASES = {
+    # 3,042 triangles: the top levels run the blocks-of-one-node path (shared-memory bins), the deep ones the mixed path
+    "c2": (scenegen.config_c2, dict(n=40, width=64, height=48)),
+    "c3": (scenegen.config_c3, dict(width=48, height=40, samples=4, depth=3, ico_level=2)),
+    "c5": (scenegen.config_c5, dict(n=12, width=64, height=40, samples=4, meshes=3)),
+    "instances": (scenegen.config_instances, dict(width=64, height=48, samples=4)),
+    "motion_mesh": (scenegen.config_instances, dict(width=48, height=32, samples=4, mesh_motion=(0.5, 0.2, -0.3))),
+}
+
+
+@pytest.mark.parametrize("name", sorted(SAH_CASES))
+def test_emulated_device_sah_build_makes_the_host_builders_tree(name, scene_dir, emu, monkeypatch):
+    """RT_BUILD_DEVICE_SAH (csrc/bvh_build_sah_gpu.cu): the level-by-level device builder takes the host builder's
+    decisions, so the tree has the same nodes and boxes — the number of box tests of a frame is identical, the image
+    is identical bit for bit — and only the triangle order inside a leaf (hence the any-hit triangle-test count of the
+    shadow rays) may differ."""
+    fn, kw = SAH_CASES[name]
+    path = fn(scene_dir, **kw)
+    monkeypatch.setenv("RTCUDA_BUILD", "host")
+    host = RayTracerEngine(path)
+    assert host.scene_info()["deviceBuiltBlas"] == 0
+    a = host.render(0, want_ids=True, want_linear=True, variant=2, counters=True)
+    monkeypatch.setenv("RTCUDA_BUILD", "device-sah")
+    before = emu.rtemu_kernel_launches()
+    dev = RayTracerEngine(path)
+    assert emu.rtemu_kernel_launches() > before
+    hi, di = host.scene_info(), dev.scene_info()
+    assert di["deviceBuiltBlas"] >= 1
+    for key in ("blasNodes", "tlasNodes", "maxLeafSize", "maxDepth", "triangles"):
+        assert hi[key] == di[key], (key, hi, di)
+    b = dev.render(0, want_ids=True, want_linear=True, variant=2, counters=True)
+    assert a.stats["boxTests"] == b.stats["boxTests"] and a.stats["maxStack"] == b.stats["maxStack"]
+    assert abs(a.stats["triTests"] - b.stats["triTests"]) <= 0.01 * a.stats["triTests"]
+    assert np.array_equal(a.rgba, b.rgba) and np.array_equal(a.linear, b.linear)
+    assert (a.ids["prim"] == b.ids["prim"]).mean() >= 0.9999
+    ref = oracle_lib.OracleScene(path).render(want_ids=True, want_linear=True)
+    check(b, ref)
+    if not name.startswith("motion"):        # the fast kernel does not carry a ray time
+        check(dev.render(0, want_ids=True, want_linear=True, variant=1), ref)
+
+
+def test_emulated_device_sah_build_degenerate_meshes(scene_dir, emu, monkeypatch):
+    """Coincident centroids (a stack of identical triangles: no plane separates them, the list is halved until the
+    leaves hold <= 4), two triangles, one triangle, and a mesh whose coordinates need FP64 records."""
+    import ply_cases
+    rng = np.random.default_rng(5)
+    base = np.array([[-1.0, -1.0, 0.0], [1.0, -1.0, 0.0], [0.0, 1.0, 0.0]])
+    meshes = {
+        "stack": (np.tile(base, (11, 1)), np.arange(33).reshape(11, 3)),
+        "pair": (np.array([[-1.0, -1, 0], [1, -1, 0], [1, 1, 0], [-1, 1, 0]]), np.array([[0, 1, 2], [0, 2, 3]])),
+        "single": (base, np.array([[0, 1, 2]])),
+        "scatter": (rng.uniform(-2, 2, (90, 3)), np.arange(90).reshape(30, 3)),
+    }
+    for name, (pos, tris) in meshes.items():
+        scenegen.write_ply(f"{scene_dir}/{name}.ply", pos.astype(np.float32), tris.astype(np.int32))
+        path = ply_cases._mesh_scene(scene_dir, name, f"{name}.ply", smooth=False)
+        out = {}
+        for mode in ("host", "device-sah"):
+            monkeypatch.setenv("RTCUDA_BUILD", mode)
+            eng = RayTracerEngine(path)
+            assert eng.ready, (name, mode, eng.load_error)
+            out[mode] = (eng.render(0, want_ids=True, want_linear=True, variant=2, counters=True), eng.scene_info())
+        (a, hi), (b, di) = out["host"], out["device-sah"]
+        assert di["deviceBuiltBlas"] == (1 if len(tris) >= 2 else 0), (name, di)
+        assert di["maxLeafSize"] <= 4
+        assert np.array_equal(a.linear, b.linear), name
+        # the same distance everywhere; which of several coincident triangles reports it may differ
+        assert np.array_equal(a.ids["t"], b.ids["t"]) and np.array_equal(a.ids["inst"], b.ids["inst"]), name
+        if name != "stack":
+            assert a.stats["boxTests"] == b.stats["boxTests"], name
+        check(b, oracle_lib.OracleScene(path).render(want_ids=True, want_linear=True)) if name != "stack" else None
