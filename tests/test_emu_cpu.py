@@ -303,3 +303,58 @@ def test_emulated_device_sah_build_degenerate_meshes(scene_dir, emu, monkeypatch
         if name != "stack":
             assert a.stats["boxTests"] == b.stats["boxTests"], name
         check(b, oracle_lib.OracleScene(path).render(want_ids=True, want_linear=True)) if name != "stack" else None
+
+
+def test_emulated_c_abi_error_behaviour(scene_dir, emu):
+    """Every refusal is loud and leaves the handle usable: the reference's own error cases (RayTracer.swift:160-168:
+    no renderer / no scene / invalid camera index) and this module's argument checks (include/rtcuda.h)."""
+    import ctypes as C
+    from myraytracer_b200 import capi
+    from myraytracer_b200.engine import FlatContext, RenderError
+    path = scenegen.config_c3(scene_dir, width=24, height=16, samples=1, depth=2, ico_level=1, roughness=0.1, area_lights=1)
+    eng = RayTracerEngine(path)
+    good = eng.render(0)
+
+    def code(fn):
+        with pytest.raises(RenderError) as e:
+            fn()
+        assert str(e.value), "an error without a message"
+        return e.value.code
+
+    assert code(lambda: eng.render(7)) == -10                                   # Invalid camera index
+    assert code(lambda: eng.render(-1)) == -10
+    assert code(lambda: eng.render(0, variant=9)) == -1
+    assert code(lambda: eng.render(0, variant=1)) == -3                         # glossy / area lights on the fast kernel
+    assert code(lambda: eng.render(0, schedule=5)) == -1
+    assert code(lambda: eng.render(0, shard_index=1, shard_count=2, shard_mode=1)) == -3   # area lights, tile shards
+    assert code(lambda: eng.render(0, shard_index=2, shard_count=2)) == -1      # shard index outside the count
+    assert code(eng.finish) == -1                                               # no frame in flight
+    assert np.array_equal(eng.render(0).rgba, good.rgba)                        # the handle still renders
+
+    # descriptions that cannot be a scene
+    ctx = FlatContext(path)
+    lib = capi.load()
+    for field, value, want in (("abiVersion", 999, "abiVersion"), ("buildMode", 7, "buildMode"), ("nMaterials", 0, "material")):
+        d = capi.rt_scene_desc.from_buffer_copy(ctx.desc)
+        setattr(d, field, value)
+        assert not lib.rt_scene_create(C.byref(d), 0)
+        assert want in lib.rt_last_error().decode()
+    d = capi.rt_scene_desc.from_buffer_copy(ctx.desc)
+    assert not lib.rt_scene_create(C.byref(d), 3)                               # device index outside the count
+    assert not lib.rt_scene_create(None, 0)
+    h = lib.rt_scene_create(C.byref(ctx.desc), 0)
+    assert h
+    info = capi.rt_scene_info()
+    assert lib.rt_scene_get_info(h, C.byref(info)) == 0 and info.instances == ctx.desc.nInstances
+    assert lib.rt_scene_update_instances(h, ctx.desc.instances, ctx.desc.nInstances + 1, None) == -1   # another instance count
+    assert lib.rt_render(h, None, None, None, None, None, None) == -10
+    cam = eng.camera(0)
+    assert lib.rt_render(h, C.byref(cam), None, None, None, None, None) == -1   # nowhere to put the frame
+    lib.rt_scene_destroy(h)
+    lib.rt_scene_destroy(None)
+    ctx.close()
+
+    # an engine without a scene file: not ready, renders report the reference's message
+    bad = RayTracerEngine(f"{scene_dir}/missing.rtscene")
+    assert not bad.ready and bad.load_error
+    assert code(lambda: bad.render(0)) in (-20, -21)
