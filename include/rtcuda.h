@@ -225,6 +225,11 @@ int32_t rt_scene_update_instances(rt_scene_t* scene, rt_instance* instances, int
  * orderOut[k], tiles numbered row-major within the shard (8x4 pixels each).  No reference analogue; for tests. */
 int64_t rt_scene_get_schedule(rt_scene_t* scene, int32_t* orderOut, int64_t capacity);
 
+/* The mesh BVHs as they lie on the device: 64-byte node records (two conservative FP32 child boxes + two child
+ * references, csrc/gpu_layout.h: GNode), all BLASes concatenated.  Returns the size in bytes (< 0: error) and copies
+ * min(size, capacityBytes).  No reference analogue; for tests (the builders of rt_scene_desc.buildMode compared). */
+int64_t rt_scene_read_blas_nodes(rt_scene_t* scene, void* nodesOut, int64_t capacityBytes);
+
 /* Render one camera.  Blocking.  Host buffers, all optional except one of rgbaOut/linearOut:
  *   rgbaOut   width*height*4 bytes, row 0 = top (RayTracer.swift:186-195)
  *   linearOut width*height*3 doubles, the [Vec3] Renderer.render returns (0..255 scale)

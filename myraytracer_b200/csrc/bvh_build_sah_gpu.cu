@@ -13,18 +13,20 @@
 //               4. exclusive scan of the "splits" flags -> slots of the children in the node pool   (scan kernels)
 //               5. children records (range, box = union of their bins)                             sahChildren
 //               6. triangles move to their child's range, warp-aggregated cursors                  sahPartition
-//   final       inner nodes numbered by a scan over the pool, leaves sorted by triangle index, GNode and GTri/GTriD
-//               records written exactly like the host builder's (same centre, padding and outward rounding)
+//   final       inner nodes numbered as the host builder numbers them (subtree counts up the levels, visiting ranks down
+//               the levels, one scan), leaves sorted by triangle index, GNode and GTri/GTriD records written exactly
+//               like the host builder's (same centre, padding and outward rounding)
 // min, max and integer counts do not depend on the order the atomics land in, so every level decides what
-// bvh_build.cpp's recursion decides: same splits, same leaves, same boxes.  Differences: nodes are numbered level by
-// level (the host numbers depth-first), triangles inside a leaf are in index order, and a node whose centroids all
-// coincide is halved with its own box handed to both halves (conservative).  Closest-hit results do not depend on
+// bvh_build.cpp's recursion decides: same splits, same leaves, same boxes, same node numbers: the GNode array is the host builder's
+// byte for byte.  Differences: triangles inside a leaf are in index order, and a node whose centroids all coincide is
+// halved with its own box handed to both halves (conservative).  Closest-hit results do not depend on
 // any of that; only equal-t ties inside one leaf may resolve differently.
 // A block whose 256 positions all belong to one node accumulates in shared memory and flushes once (the top levels);
 // mixed blocks go to global memory directly (deep levels, where the addresses are spread out anyway).
 // The arrays come back to the host, where rt_scene_create concatenates a scene's BLASes, as with the other builders.
 #include <cmath>
 #include <cstring>
+#include <utility>
 #include <vector>
 
 #include "bvh_build.h"
@@ -319,9 +321,40 @@ __global__ void __launch_bounds__(kT) sahPartition(SahState S, int cur, int leve
 }
 
 // ---- final passes ----------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kT) sahInnerFlags(const int* __restrict__ nLeft, int pool, unsigned* __restrict__ flag) {
+// Inner nodes get the host builder's numbers (bvh_build.cpp flattens depth-first, left subtree first, and hands a node's
+// inner children consecutive slots when the node is visited), so the GNode array is the host's, record for record:
+//   count[x]  inner nodes in the subtree of x                                   bottom-up, one launch per level
+//   pre[x]    x's rank among the inner nodes in that visiting order             top-down, one launch per level
+//   k[pre[x]] how many of x's children are inner; exclusive scan = slots handed out before x is visited
+__global__ void __launch_bounds__(kT) sahSubtreeCounts(const int* __restrict__ nLeft, int base, int A, int* __restrict__ count) {
+    const int j = blockIdx.x * kT + threadIdx.x;
+    if (j >= A) return;
+    const int L = nLeft[base + j];
+    count[base + j] = L >= 0 ? 1 + count[L] + count[L + 1] : 0;
+}
+__global__ void __launch_bounds__(kT) sahPreorder(const int* __restrict__ nLeft, int base, int A, const int* __restrict__ count,
+                                                   int* __restrict__ pre, unsigned* __restrict__ k) {
+    const int j = blockIdx.x * kT + threadIdx.x;
+    if (j >= A) return;
+    const int L = nLeft[base + j];
+    if (L < 0) return;
+    const int p = pre[base + j];
+    const bool li = nLeft[L] >= 0, ri = nLeft[L + 1] >= 0;
+    if (li) pre[L] = p + 1;
+    if (ri) pre[L + 1] = p + 1 + count[L];
+    k[p] = (li ? 1u : 0u) + (ri ? 1u : 0u);
+}
+__global__ void __launch_bounds__(kT) sahAssignSlots(const int* __restrict__ nLeft, int pool, const int* __restrict__ pre,
+                                                      const unsigned* __restrict__ kScan, unsigned* __restrict__ gIndex) {
     const int i = blockIdx.x * kT + threadIdx.x;
-    if (i <= pool) flag[i] = (i < pool && nLeft[i] >= 0) ? 1u : 0u;
+    if (i >= pool) return;
+    const int L = nLeft[i];
+    if (L < 0) return;
+    if (i == 0) gIndex[0] = 0u;
+    const unsigned base = 1u + kScan[pre[i]];
+    const bool li = nLeft[L] >= 0;
+    if (li) gIndex[L] = base;
+    if (nLeft[L + 1] >= 0) gIndex[L + 1] = base + (li ? 1u : 0u);
 }
 
 // leaves: triangles in index order (the order the atomics left them in is not reproducible), largest leaf
@@ -471,7 +504,9 @@ cudaError_t buildBlasDeviceSah(const double* dVerts, const BlasBuildInput& in, B
     SCK(sums.alloc(((size_t)(pool + 1) / 2048 + 2) * 4));
 
     int levelBase = 0, A = 1, depth = 1, cur = 0, used = 1;
+    std::vector<std::pair<int, int>> levels;          // (first pool node, nodes) of every level
     for (;;) {
+        levels.emplace_back(levelBase, A);
         const size_t a = (size_t)A;
         SCK(cbLo.atLeast(a * 24)); SCK(cbHi.atLeast(a * 24));
         SCK(binLo.atLeast(a * kSlots * 24)); SCK(binHi.atLeast(a * kSlots * 24)); SCK(binCnt.atLeast(a * kSlots * 4));
@@ -506,15 +541,31 @@ cudaError_t buildBlasDeviceSah(const double* dVerts, const BlasBuildInput& in, B
     }
     out.maxDepth = depth;
 
-    // inner nodes -> GNode slots, in pool (= level) order; the root is pool node 0 -> GNode 0
-    Buf gIndex, dNodes, dTris;
-    SCK(gIndex.alloc((size_t)(used + 1) * 4));
-    RT_LAUNCH(sahInnerFlags, blocksFor(used + 1), kT, 0, S.nLeft, used, gIndex.as<unsigned>());
-    SCK(launchExclusiveScan(gIndex.as<unsigned>(), (long long)used + 1, sums.as<unsigned>(), 0));
+    // inner nodes -> GNode slots in the host builder's order (above)
+    Buf gIndex, dNodes, dTris, subCount, pre, kArr;
+    SCK(gIndex.alloc((size_t)used * 4)); SCK(subCount.alloc((size_t)used * 4)); SCK(pre.alloc((size_t)used * 4));
+    for (size_t l = levels.size(); l-- > 0;) {
+        RT_LAUNCH(sahSubtreeCounts, blocksFor(levels[l].second), kT, 0, S.nLeft, levels[l].first, levels[l].second, subCount.as<int>());
+        nl++;
+    }
+    int inner = 0;
+    SCK(cudaMemcpy(&inner, subCount.p, 4, cudaMemcpyDeviceToHost));
+    if (inner > 0) {
+        SCK(kArr.alloc((size_t)(inner + 1) * 4));
+        SCK(cudaMemsetAsync(kArr.p, 0, (size_t)(inner + 1) * 4, 0));
+        SCK(cudaMemsetAsync(pre.p, 0, 4, 0));
+        for (size_t l = 0; l < levels.size(); l++) {
+            RT_LAUNCH(sahPreorder, blocksFor(levels[l].second), kT, 0, S.nLeft, levels[l].first, levels[l].second, subCount.as<int>(),
+                      pre.as<int>(), kArr.as<unsigned>());
+            nl++;
+        }
+        SCK(launchExclusiveScan(kArr.as<unsigned>(), (long long)inner + 1, sums.as<unsigned>(), 0));
+        RT_LAUNCH(sahAssignSlots, blocksFor(used), kT, 0, S.nLeft, used, pre.as<int>(), kArr.as<unsigned>(), gIndex.as<unsigned>());
+        nl += 4;
+    }
     RT_LAUNCH(sahSortLeaves, blocksFor(used), kT, 0, S, cur, used, dMaxLeaf);
-    nl += 5;
-    unsigned inner = 0;
-    SCK(cudaMemcpy(&inner, gIndex.as<unsigned>() + used, 4, cudaMemcpyDeviceToHost));
+    nl++;
+    SCK(cudaGetLastError());
     SCK(cudaMemcpy(&out.maxLeaf, dMaxLeaf, 4, cudaMemcpyDeviceToHost));
 
     SCK(dTris.alloc((size_t)n * (out.f64 ? sizeof(GTriD) : sizeof(GTri))));

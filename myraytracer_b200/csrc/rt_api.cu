@@ -628,6 +628,17 @@ int64_t rt_scene_get_schedule(rt_scene_t* sc, int32_t* orderOut, int64_t capacit
     return n;
 }
 
+int64_t rt_scene_read_blas_nodes(rt_scene_t* sc, void* nodesOut, int64_t capacityBytes) {
+    if (!sc) return fail(RT_ERR_NO_SCENE, "No scene loaded. Can't render.");
+    const int64_t bytes = sc->info.blasNodes * (int64_t)sizeof(GNode);
+    if (nodesOut && capacityBytes > 0 && bytes > 0) {
+        if (cudaSetDevice(sc->device) != cudaSuccess ||
+            cudaMemcpy(nodesOut, sc->dNodes, (size_t)(bytes < capacityBytes ? bytes : capacityBytes), cudaMemcpyDeviceToHost) != cudaSuccess)
+            return fail(RT_ERR_CUDA, "rt_scene_read_blas_nodes: copy failed");
+    }
+    return bytes;
+}
+
 }  // extern "C"
 
 #include "rt_api_render.inl"

@@ -96,6 +96,16 @@ class RayTracerEngine:
             self._lib.rt_scene_get_schedule(self.scene_handle(), out.ctypes.data_as(C.POINTER(C.c_int32)), n)
         return out
 
+    def blas_nodes(self) -> np.ndarray:
+        """rt_scene_read_blas_nodes: the mesh BVH node records on the device, (n, 16) uint32 words each."""
+        n = self._lib.rt_scene_read_blas_nodes(self.scene_handle(), None, 0)
+        if n < 0:
+            raise RenderError(int(n), self._lib.rt_last_error().decode())
+        out = np.zeros((n // 64, 16), np.uint32)
+        if n:
+            self._lib.rt_scene_read_blas_nodes(self.scene_handle(), _ptr(out), n)
+        return out
+
     def describe(self) -> capi.rt_scene_desc:
         d = capi.rt_scene_desc()
         rc = self._lib.rth_engine_describe(self._h, C.byref(d))

@@ -245,8 +245,9 @@ SAH_CASES = {
 @pytest.mark.parametrize("name", sorted(SAH_CASES))
 def test_emulated_device_sah_build_makes_the_host_builders_tree(name, scene_dir, emu, monkeypatch):
     """RT_BUILD_DEVICE_SAH (csrc/bvh_build_sah_gpu.cu): the level-by-level device builder takes the host builder's
-    decisions, so the tree has the same nodes and boxes — the number of box tests of a frame is identical, the image
-    is identical bit for bit — and only the triangle order inside a leaf (hence the any-hit triangle-test count of the
+    decisions and numbers the nodes as it does, so the node array on the device is the host builder's byte for byte —
+    the number of box tests of a frame is identical, the image is identical bit for bit — and only the triangle order
+    inside a leaf (hence the any-hit triangle-test count of the
     shadow rays) may differ."""
     fn, kw = SAH_CASES[name]
     path = fn(scene_dir, **kw)
@@ -262,6 +263,7 @@ def test_emulated_device_sah_build_makes_the_host_builders_tree(name, scene_dir,
     assert di["deviceBuiltBlas"] >= 1
     for key in ("blasNodes", "tlasNodes", "maxLeafSize", "maxDepth", "triangles"):
         assert hi[key] == di[key], (key, hi, di)
+    assert np.array_equal(host.blas_nodes(), dev.blas_nodes())       # boxes, child references and node numbers
     b = dev.render(0, want_ids=True, want_linear=True, variant=2, counters=True)
     assert a.stats["boxTests"] == b.stats["boxTests"] and a.stats["maxStack"] == b.stats["maxStack"]
     assert abs(a.stats["triTests"] - b.stats["triTests"]) <= 0.01 * a.stats["triTests"]
@@ -293,8 +295,8 @@ def test_emulated_device_sah_build_degenerate_meshes(scene_dir, emu, monkeypatch
             monkeypatch.setenv("RTCUDA_BUILD", mode)
             eng = RayTracerEngine(path)
             assert eng.ready, (name, mode, eng.load_error)
-            out[mode] = (eng.render(0, want_ids=True, want_linear=True, variant=2, counters=True), eng.scene_info())
-        (a, hi), (b, di) = out["host"], out["device-sah"]
+            out[mode] = (eng.render(0, want_ids=True, want_linear=True, variant=2, counters=True), eng.scene_info(), eng.blas_nodes())
+        (a, hi, _), (b, di, _) = out["host"], out["device-sah"]
         assert di["deviceBuiltBlas"] == (1 if len(tris) >= 2 else 0), (name, di)
         assert di["maxLeafSize"] <= 4
         assert np.array_equal(a.linear, b.linear), name
@@ -302,6 +304,7 @@ def test_emulated_device_sah_build_degenerate_meshes(scene_dir, emu, monkeypatch
         assert np.array_equal(a.ids["t"], b.ids["t"]) and np.array_equal(a.ids["inst"], b.ids["inst"]), name
         if name != "stack":
             assert a.stats["boxTests"] == b.stats["boxTests"], name
+            assert np.array_equal(out["host"][2], out["device-sah"][2]), name
         check(b, oracle_lib.OracleScene(path).render(want_ids=True, want_linear=True)) if name != "stack" else None
 
 

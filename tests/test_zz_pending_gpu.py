@@ -30,6 +30,7 @@ def test_device_sah_build_makes_the_host_builders_tree(name, scene_dir, monkeypa
     assert di["deviceBuiltBlas"] >= 1
     for key in ("blasNodes", "maxLeafSize", "maxDepth"):
         assert hi[key] == di[key], (key, hi, di)
+    assert np.array_equal(host.blas_nodes(), dev.blas_nodes())       # the host builder's node array, byte for byte
     b = dev.render(0, want_ids=True, want_linear=True, counters=True)
     assert a.stats["boxTests"] == b.stats["boxTests"]
     assert np.array_equal(a.rgba, b.rgba)
