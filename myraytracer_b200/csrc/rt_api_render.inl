@@ -242,10 +242,12 @@ int32_t rt_render(rt_scene_t* sc, const rt_camera* camera, const rt_render_param
     rc = rt_render_device(sc, camera, params, rgbaOut ? sc->dRgba : nullptr, linearOut ? sc->dLinear : nullptr,
                           idsOut ? sc->dIds : nullptr, nullptr);
     if (rc) return rc;
-    if (rgbaOut) CK(cudaMemcpyAsync(rgbaOut, sc->dRgba, W * H * 4, cudaMemcpyDeviceToHost, 0));
-    if (linearOut) CK(cudaMemcpyAsync(linearOut, sc->dLinear, W * H * 3 * sizeof(double), cudaMemcpyDeviceToHost, 0));
-    if (idsOut) CK(cudaMemcpyAsync(idsOut, sc->dIds, W * H * n * n * sizeof(HitId), cudaMemcpyDeviceToHost, 0));
-    rc = rt_render_finish(sc, statsOut);
+    cudaError_t ce = cudaSuccess;
+    if (rgbaOut) ce = cudaMemcpyAsync(rgbaOut, sc->dRgba, W * H * 4, cudaMemcpyDeviceToHost, 0);
+    if (linearOut && ce == cudaSuccess) ce = cudaMemcpyAsync(linearOut, sc->dLinear, W * H * 3 * sizeof(double), cudaMemcpyDeviceToHost, 0);
+    if (idsOut && ce == cudaSuccess) ce = cudaMemcpyAsync(idsOut, sc->dIds, W * H * n * n * sizeof(HitId), cudaMemcpyDeviceToHost, 0);
+    rc = rt_render_finish(sc, statsOut);        // also on a failed copy: the frame must not stay "in flight" on the handle
+    CK(ce);
     if (rc) return rc;
     CK(cudaStreamSynchronize(0));
     if (statsOut) statsOut->milliseconds = (int64_t)(nowMs() - w0);
