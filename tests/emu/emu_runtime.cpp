@@ -6,10 +6,14 @@
 // of converged full-mask code, which is what the render kernels promise.  A lane that exits, or waits at a different
 // barrier, while its warp waits is a bug in the kernel: the scheduler detects that no fiber can advance and aborts
 // with a message instead of hanging.
+// rtemu_set_schedule_seed(s != 0) shuffles the order in which the blocks of a grid run and, at every sweep, the order in
+// which the runnable fibers of a block are resumed: atomics land in another order, so a result that silently depends
+// on thread order (it must not: on the device there is none) changes with the seed and a test can see it.
 #include <ucontext.h>
 #include <sys/mman.h>
 
 #include <cstdio>
+#include <utility>
 #include <mutex>
 #include <vector>
 
@@ -22,6 +26,8 @@ dim3 g_blockDim, g_gridDim;
 static char g_sharedAnchor;
 uintptr_t g_sharedBase = (uintptr_t)&g_sharedAnchor;
 unsigned long long g_kernelLaunches = 0;
+unsigned long long g_scheduleSeed = 0;
+unsigned long long g_shuffles = 0;
 
 namespace {
 
@@ -51,6 +57,14 @@ struct BlockState {
 BlockState* g_blk = nullptr;
 std::mutex g_launchMutex;
 std::vector<char*> g_stackPool;
+
+struct Shuffler {                       // xorshift64*; Fisher-Yates
+    unsigned long long s;
+    unsigned long long next() { s ^= s >> 12; s ^= s << 25; s ^= s >> 27; return s * 2685821657736338717ULL; }
+    void shuffle(std::vector<unsigned>& v) {
+        for (size_t i = v.size(); i > 1; i--) std::swap(v[i - 1], v[next() % i]);
+    }
+};
 
 char* takeStack() {
     if (!g_stackPool.empty()) { char* s = g_stackPool.back(); g_stackPool.pop_back(); return s; }
@@ -118,7 +132,13 @@ void launch(dim3 grid, dim3 block, const std::function<void()>& body) {
     g_gridDim = grid;
     g_blockDim = block;
     const unsigned nThreads = block.x * block.y * block.z;
-    for (unsigned bi = 0; bi < grid.x; bi++) {
+    Shuffler rng{(g_scheduleSeed + g_kernelLaunches) * 0x9E3779B97F4A7C15ULL | 1ULL};
+    std::vector<unsigned> blockOrder(grid.x), threadOrder(nThreads);
+    for (unsigned i = 0; i < grid.x; i++) blockOrder[i] = i;
+    for (unsigned i = 0; i < nThreads; i++) threadOrder[i] = i;
+    if (g_scheduleSeed) rng.shuffle(blockOrder);
+    for (unsigned bo = 0; bo < grid.x; bo++) {
+        const unsigned bi = blockOrder[bo];
         BlockState b;
         b.nThreads = nThreads;
         b.fibers.resize(nThreads);
@@ -141,7 +161,9 @@ void launch(dim3 grid, dim3 block, const std::function<void()>& body) {
         for (;;) {
             bool alive = false;
             const unsigned long long before = b.progress;
-            for (unsigned t = 0; t < nThreads; t++) {
+            if (g_scheduleSeed) { rng.shuffle(threadOrder); g_shuffles++; }
+            for (unsigned to = 0; to < nThreads; to++) {
+                const unsigned t = threadOrder[to];
                 if (b.fibers[t].done) continue;
                 alive = true;
                 b.current = (int)t;
@@ -163,3 +185,5 @@ void launch(dim3 grid, dim3 block, const std::function<void()>& body) {
 }  // namespace rtemu
 
 extern "C" unsigned long long rtemu_kernel_launches(void) { return rtemu::g_kernelLaunches; }
+extern "C" unsigned long long rtemu_schedule_shuffles(void) { return rtemu::g_shuffles; }
+extern "C" void rtemu_set_schedule_seed(unsigned long long seed) { rtemu::g_scheduleSeed = seed; }

@@ -21,6 +21,9 @@ def load():
             raise RuntimeError("emulation build failed:\n" + r.stdout[-4000:])
         _emu = capi.declare(C.CDLL(EMU_PATH))
         _emu.rtemu_kernel_launches.restype = C.c_uint64
+        _emu.rtemu_set_schedule_seed.argtypes = [C.c_uint64]
+        _emu.rtemu_set_schedule_seed.restype = None
+        _emu.rtemu_schedule_shuffles.restype = C.c_uint64
     return _emu
 
 
@@ -30,7 +33,10 @@ class use_emulator:
     def __enter__(self):
         self._saved = capi._lib
         capi._lib = load()
+        # RTEMU_SCHEDULE_SEED=n runs a whole test session under a shuffled block / fiber order (emu_runtime.cpp)
+        capi._lib.rtemu_set_schedule_seed(int(os.environ.get("RTEMU_SCHEDULE_SEED", "0")))
         return capi._lib
 
     def __exit__(self, *a):
+        capi._lib.rtemu_set_schedule_seed(0)
         capi._lib = self._saved

@@ -361,3 +361,48 @@ def test_emulated_c_abi_error_behaviour(scene_dir, emu):
     bad = RayTracerEngine(f"{scene_dir}/missing.rtscene")
     assert not bad.ready and bad.load_error
     assert code(lambda: bad.render(0)) in (-20, -21)
+
+
+@pytest.mark.parametrize("seed", [1, 0xC0FFEE])
+def test_emulated_results_do_not_depend_on_thread_order(seed, scene_dir, tmp_path, emu, monkeypatch):
+    """On the device there is no thread order.  The emulator can impose different ones (rtemu_set_schedule_seed: blocks
+    of a grid and runnable fibers of a block resumed in shuffled order, so atomics land differently); everything
+    that goes through atomics must come out the same: the device SAH builder's node array, the PLY ingest's arrays
+    (adjacency lists filled by atomic cursors, then sorted), instance bounds and TLAS refit, the area lights' counting
+    pass and prefix, the frames."""
+    import ply_cases
+    from myraytracer_b200.engine import FlatContext
+    path = scenegen.config_c3(scene_dir, width=40, height=24, samples=4, depth=3, ico_level=2, area_lights=2)
+    mesh = scenegen.config_c2(scene_dir, n=24, width=40, height=24)
+    inst = scenegen.config_instances(scene_dir, width=40, height=24, samples=1)
+
+    def run():
+        out = {}
+        monkeypatch.setenv("RTCUDA_BUILD", "device-sah")
+        e = RayTracerEngine(mesh)
+        out["nodes"] = e.blas_nodes()
+        out["mesh"] = e.render(0, want_linear=True).linear
+        monkeypatch.setenv("RTCUDA_BUILD", "host")
+        out["area"] = RayTracerEngine(path).render(0, want_linear=True).linear
+        a = RayTracerEngine(inst)
+        l2w = FlatContext(inst).instances()["l2w"].copy()
+        l2w[:, 12] += 0.25                                   # every instance moves along x (column-major translation)
+        a.set_instance_transforms(l2w, bounds_on_device=True)
+        out["anim"] = a.render(0, want_linear=True).linear
+        for name, p, n_tris, device in ply_cases.make_cases(str(tmp_path)):
+            if device:
+                monkeypatch.setenv("RTCUDA_INGEST", "device")
+                v, nr = FlatContext(p).triangles()
+                out["ply_" + name] = np.concatenate([v.ravel(), nr.ravel()])
+        return out
+
+    emu.rtemu_set_schedule_seed(0)
+    base = run()
+    emu.rtemu_set_schedule_seed(seed)
+    shuffles = emu.rtemu_schedule_shuffles()
+    again = run()
+    assert emu.rtemu_schedule_shuffles() > shuffles + 100       # the other order was really imposed
+    emu.rtemu_set_schedule_seed(0)
+    assert base.keys() == again.keys() and len(base) > 6
+    for key in base:
+        assert np.array_equal(base[key], again[key], equal_nan=True), key
