@@ -1,0 +1,79 @@
+"""Pins the oracle's shading recursion (Extensions/Object+Extension.swift:96-283) against the independent pure-Python
+restatement in tests/reftrace.py: no BVH, no code shared with oracle/.  Covers what BASELINE's C3 exercises — ambient,
+point lights with shadow rays, mirror, dielectric (Fresnel, total internal reflection, Beer's law, light only on the
+outside), conductor, the depth rules — plus glossy roughness drawing from the pixel's PCG32 stream inside the
+recursion (reflection subtree before refraction subtree)."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_lib
+import reftrace
+from myraytracer_b200 import scenegen
+
+TYPES = {scenegen.MAT_PLAIN: "plain", scenegen.MAT_MIRROR: "mirror", scenegen.MAT_DIELECTRIC: "dielectric",
+         scenegen.MAT_CONDUCTOR: "conductor"}
+
+
+def _build(tmp, rough, depth, W=30, H=20, samples=4):
+    verts = np.asarray([(0, -1.0, 0), (-7, -1, -6), (7, -1, -6), (7, 6, -6), (-7, 6, -6),          # 1 plane point, 2-5 wall
+                        (-1.9, 0.1, 0.4), (1.7, 0.0, -0.3), (0.1, 0.35, 2.1), (-0.3, 2.3, -1.8)], np.float64)
+    M = scenegen.Material
+    mats = [M(id=1, ambient=(0.4, 0.5, 0.6), diffuse=(0.6, 0.5, 0.4), specular=(0.3, 0.3, 0.3), phong=12.5),
+            M(id=2, type=scenegen.MAT_MIRROR, ambient=(0.1, 0.1, 0.1), diffuse=(0.2, 0.2, 0.25), specular=(0.5, 0.5, 0.5), phong=40.0,
+              mirror=(0.8, 0.75, 0.7), roughness=rough),
+            M(id=3, type=scenegen.MAT_DIELECTRIC, ambient=(0.05, 0.05, 0.05), diffuse=(0.05, 0.06, 0.07), specular=(0.6, 0.6, 0.6),
+              phong=80.0, ior=1.5, absorption=(0.3, 0.1, 0.05), roughness=rough),
+            M(id=4, type=scenegen.MAT_CONDUCTOR, ambient=(0.1, 0.1, 0.1), diffuse=(0.3, 0.25, 0.1), specular=(0.7, 0.6, 0.3), phong=25.0,
+              mirror=(0.9, 0.8, 0.5), ior=0.37, absorptionIndex=2.82, roughness=rough),
+            M(id=5, ambient=(0.3, 0.3, 0.3), diffuse=(0.3, 0.7, 0.3), specular=(0.1, 0.1, 0.1), phong=0.5)]   # phong < 1: max(1, phong)
+    O = scenegen.SceneObject
+    objects = [O(scenegen.OBJ_PLANE, id=1, material=1, centerIdx=1, normal=(0.0, 2.0, 0.0)),       # normal not unit on purpose
+               O(scenegen.OBJ_TRIANGLE, id=2, material=2, indices=(2, 3, 4)),
+               O(scenegen.OBJ_TRIANGLE, id=3, material=2, indices=(2, 4, 5)),
+               O(scenegen.OBJ_SPHERE, id=4, material=3, centerIdx=6, radius=1.1),
+               O(scenegen.OBJ_SPHERE, id=5, material=4, centerIdx=7, radius=1.0),
+               O(scenegen.OBJ_SPHERE, id=6, material=3, centerIdx=8, radius=0.65),
+               O(scenegen.OBJ_SPHERE, id=7, material=5, centerIdx=9, radius=0.8)]
+    lights = [((4.0, 7.0, 6.0), (900.0, 850.0, 800.0)), ((-5.0, 4.0, 3.0), (300.0, 350.0, 500.0))]
+    sc = scenegen.Scene(maxRecursionDepth=depth, backgroundColor=(20, 30, 50), ambient=(25, 25, 25), shadowRayEpsilon=1e-3,
+                        intersectionTestEpsilon=1e-6)
+    sc.materials, sc.objects, sc.vertexData = mats, objects, verts
+    sc.pointLights = [scenegen.PointLight(p, i) for p, i in lights]
+    cam = dict(width=W, height=H, numSamples=samples, position=(0.4, 2.6, 8.5), gazePoint=(0.0, 0.4, 0.0), gaze=(0, 0, -1),
+               up=(0, 1, 0), nearPlane=(-1, 1, -1, 1), nearDistance=1.0, fovy=42.0, isLookAt=True)
+    sc.cameras = [scenegen.Camera(id=1, width=W, height=H, numSamples=samples, position=cam["position"],
+                                  gazePoint=cam["gazePoint"], up=cam["up"], nearDistance=1.0, fovy=42.0, isLookAt=True)]
+    path = os.path.join(tmp, f"trace_ref_{rough}_{depth}.rtscene")
+    scenegen.write_rtscene(sc, path)
+
+    prims = []
+    for ob in objects:
+        if ob.kind == scenegen.OBJ_PLANE:
+            prims.append(dict(kind="plane", mat=ob.material, c=verts[ob.centerIdx - 1], n=np.asarray(ob.normal, np.float64)))
+        elif ob.kind == scenegen.OBJ_TRIANGLE:
+            prims.append(dict(kind="tri", mat=ob.material, v=tuple(verts[k - 1] for k in ob.indices)))
+        else:
+            prims.append(dict(kind="sphere", mat=ob.material, c=verts[ob.centerIdx - 1], r=ob.radius))
+    materials = [dict(type=TYPES[m.type], ambient=m.ambient, diffuse=m.diffuse, specular=m.specular, mirror=m.mirror,
+                      absorption=m.absorption, phong=m.phong, ior=m.ior, absorptionIndex=m.absorptionIndex, roughness=m.roughness)
+                 for m in mats]
+    ref = reftrace.Scene(prims, materials, lights, sc.ambient, sc.backgroundColor, sc.intersectionTestEpsilon,
+                         sc.shadowRayEpsilon, depth)
+    return path, ref, cam
+
+
+@pytest.mark.parametrize("rough,depth", [(0.0, 4), (0.15, 3), (0.0, 0)])
+def test_oracle_trace_matches_independent_restatement(rough, depth, tmp_path):
+    path, ref, cam = _build(str(tmp_path), rough, depth)
+    want, counts = reftrace.render(ref, cam)
+    got = oracle_lib.OracleScene(path).render(want_ids=True, want_linear=True)
+    lin = got["linear"]
+    assert lin.shape == want.shape
+    err = np.abs(lin - want) / np.maximum(1.0, np.abs(want))
+    assert err.max() <= 1e-13, (err.max(), np.unravel_index(err.argmax(), err.shape))      # measured: identical bit for bit
+    c = got["counters"]
+    assert (c["raysPrimary"], c["raysShadow"], c["raysSecondary"]) == (counts["primary"], counts["shadow"], counts["secondary"])
+    if depth:
+        assert counts["secondary"] > counts["primary"]          # the recursion really branches
