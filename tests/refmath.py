@@ -69,10 +69,12 @@ def camera_basis(cam: dict):
 
 
 def primary_rays(cam: dict, i: int, j: int, with_time: bool = False):
-    """All n*n primary rays of pixel (i, j): list of (origin, dir, tMin[, time]), :294-344 without DOF."""
+    """All n*n primary rays of pixel (i, j): list of (origin, dir, tMin[, time]), :294-344, thin lens (:325-338)
+    when the camera has apertureSize > 0 and focusDistance > 0."""
     B = camera_basis(cam)
     samples = max(1, cam["numSamples"])
     n = int(math.sqrt(samples))
+    aperture, focus = cam.get("apertureSize", 0.0), cam.get("focusDistance", 0.0)
     rng = PCG32(pixel_seed(i, j))
     out = []
     for sy in range(n):
@@ -82,9 +84,18 @@ def primary_rays(cam: dict, i: int, j: int, with_time: bool = False):
             cj = float(j) + (float(sy) + xi2) / float(n)
             s = (B["q00"] - B["v"] * (cj * B["dv"])) + B["u"] * (ci * B["du"])
             d = _norm(s - B["e"])
+            eye = B["e"].copy()
+            if aperture > 0 and focus > 0:
+                denom = _dot(d, -B["w"])
+                t_focus = focus if abs(denom) < 1e-6 else focus / denom
+                p_focus = B["e"] + d * t_focus
+                u_rand = rng.next_float() - 0.5
+                v_rand = rng.next_float() - 0.5
+                eye = B["e"] + (u_rand * B["u"] + v_rand * B["v"]) * aperture
+                d = _norm(p_focus - eye)
             time = rng.next_float()  # ray time (:340)
-            t_img = _dot(B["m"] - B["e"], B["w"]) / _dot(d, B["w"])
-            out.append((B["e"].copy(), d, max(t_img, 0.0), time) if with_time else (B["e"].copy(), d, max(t_img, 0.0)))
+            t_img = _dot(B["m"] - eye, B["w"]) / _dot(d, B["w"])
+            out.append((eye, d, max(t_img, 0.0), time) if with_time else (eye, d, max(t_img, 0.0)))
     return out
 
 
