@@ -5,8 +5,11 @@ Fresnel weights, Beer's law, the depth rules and the non-finite guard — and of
 Written from the Swift source, NOT from oracle/: no BVH (every primitive is tried, Models/RTContext.swift:479-537 for the
 closest hit, :833-870 for the shadow tests), Python recursion instead of the oracle's C++.  The CPU tests hold the
 oracle's linear colours against this file, so an error in the shading path has to be made twice, independently, to go
-unnoticed (SURVEY.md §8c iv).  Scenes: top-level spheres, triangles (flat) and planes without transforms — the
-1-primitive BLAS + identity instance of RTContext.init (:96-250).  Test infrastructure only."""
+unnoticed (SURVEY.md §8c iv).  Scenes: top-level spheres, triangles (flat) and planes — the 1-primitive BLAS + instance
+of RTContext.init (:96-250) — and meshes with flat or smooth normals; a primitive without "M" is the identity instance
+(bit-exact path), one with "M" (4x4 localToWorld) goes through the instance step of intersectTLAS (:651-704): ray to
+local space without re-normalising the direction, hit point back through localToWorld, normal through the
+inverse-transpose and flipped when the determinant is negative, material override.  Test infrastructure only."""
 from __future__ import annotations
 
 import math
@@ -79,6 +82,128 @@ def closest(sc: Scene, o, d, t_min):
         return None
     t, p, n, mat, kind = best
     return t, p + 0.0, _norm(n), mat, kind
+
+
+def _local_ray(pr, o, d):
+    """world -> local, :658-668 (no instance motion here)."""
+    W = pr["W"]                                                            # worldToLocal = M.inverse (:449)
+    ol = (W @ np.append(o, 1.0))[:3]
+    dl = (W @ np.append(d, 0.0))[:3]
+    return ol, dl
+
+
+def prepare(sc: Scene):
+    """Per-instance matrices: worldToLocal, normal matrix (inverse transpose of the upper 3x3, :24-31), handedness."""
+    for pr in sc.prims:
+        if "M" in pr:
+            M = np.asarray(pr["M"], np.float64)
+            pr["W"] = np.linalg.inv(M)
+            pr["N"] = np.linalg.inv(M[:3, :3]).T
+            pr["flip"] = np.linalg.det(M[:3, :3]) < 0
+    return sc
+
+
+def _closest_transformed(sc: Scene, pr, o, d, t_min, best_t):
+    """One instance with a transform: (t, p_world, n_world, mat, kind, prim) or None; only hits closer than best_t."""
+    ol, dl = _local_ray(pr, o, d)
+    found = None
+    if pr["kind"] == "sphere":
+        t = refmath.brute_force_sphere(ol, dl, pr["c"], pr["r"], sc.eps, t_min)
+        if t < best_t:
+            p = ol + dl * t
+            found = (t, p, _norm(p - pr["c"]), "sphere", 0)
+    elif pr["kind"] == "mesh":
+        for k, (v0, v1, v2) in enumerate(pr["v"]):
+            h = refmath.mt_single(ol, dl, v0, v1, v2, sc.eps)
+            if h and h[0] > max(sc.eps, t_min) and h[0] < best_t:
+                e1, e2 = v1 - v0, v2 - v0
+                if pr.get("normals") is not None:                         # smooth: w*n0 + u*n1 + v*n2 (:497-500)
+                    n0, n1, n2 = pr["normals"][k]
+                    n = _norm(((1.0 - h[1] - h[2]) * n0 + h[1] * n1) + h[2] * n2)
+                else:
+                    n = _norm(np.cross(e1, e2))
+                best_t = h[0]
+                found = (h[0], (v0 + h[1] * e1) + h[2] * e2, n, "tri", pr["first"] + k)
+    else:
+        raise ValueError(pr["kind"])
+    if found is None:
+        return None
+    t, p, n, kind, prim = found
+    pw = (np.asarray(pr["M"], np.float64) @ np.append(p, 1.0))[:3]
+    nw = _norm(pr["N"] @ n)
+    if pr["flip"]:
+        nw = -nw
+    return t, pw, nw, pr["mat"], kind, prim
+
+
+def closest_any(sc: Scene, o, d, t_min):
+    """closest() over identity instances and transformed ones: (t, p, n, mat, kind, prim) or None."""
+    plain = Scene([p for p in sc.prims if "M" not in p], sc.materials, sc.lights, sc.ambient, sc.background, sc.eps,
+                  sc.shadow_eps, sc.max_depth)
+    h = closest(plain, o, d, t_min)
+    best = None if h is None else h + (-1,)
+    for pr in sc.prims:
+        if "M" in pr:
+            c = _closest_transformed(sc, pr, o, d, t_min, INF if best is None else best[0])
+            if c is not None:
+                best = c
+    return best
+
+
+def occluded_any(sc: Scene, o, d, t_max):
+    plain = Scene([p for p in sc.prims if "M" not in p], sc.materials, sc.lights, sc.ambient, sc.background, sc.eps,
+                  sc.shadow_eps, sc.max_depth)
+    if occluded(plain, o, d, t_max):
+        return True
+    for pr in sc.prims:
+        if "M" not in pr:
+            continue
+        ol, dl = _local_ray(pr, o, d)
+        if pr["kind"] == "sphere":
+            one = Scene([dict(kind="sphere", c=pr["c"], r=pr["r"], mat=pr["mat"])], sc.materials, sc.lights, sc.ambient,
+                        sc.background, sc.eps, sc.shadow_eps, sc.max_depth)
+            if occluded(one, ol, dl, t_max):
+                return True
+        else:
+            for v0, v1, v2 in pr["v"]:
+                h = refmath.mt_single(ol, dl, v0, v1, v2, sc.eps)
+                if h and max(sc.eps, 0.0) < h[0] < t_max:
+                    return True
+    return False
+
+
+def shade_direct(sc: Scene, d, hit):
+    """Depth-0 shading of a plain material (:105-143): ambient + point lights with shadow rays."""
+    t, p, n_geo, mat_id = hit[:4]
+    mat = sc.materials[max(0, min(len(sc.materials) - 1, mat_id - 1))]
+    front = _dot(d, n_geo) < 0
+    N = n_geo if front else -n_geo
+    Lo = sc.ambient * _v(mat["ambient"])
+    for lpos, lint in sc.lights:
+        wi = _v(lpos) - p
+        dist = math.sqrt(_dot(wi, wi))
+        wi = _norm(wi)
+        if occluded_any(sc, p + wi * sc.shadow_eps, wi, dist):
+            continue
+        n_dot_l = max(0.0, _dot(N, wi))
+        if n_dot_l > 0:
+            ld = _v(mat["diffuse"]) * n_dot_l
+            h = _norm(wi + _norm(-d))
+            ls = _v(mat["specular"]) * math.pow(max(0.0, _dot(N, h)), max(1.0, mat["phong"]))
+            Lo = Lo + (ld + ls) * (_v(lint) / max(dist * dist, 1e-12))
+    return Lo
+
+
+def smooth_vertex_normals(pos, faces0):
+    """RTContext.swift:305-326: unit face normals added to their three vertices in (face, corner) order, then
+    normalised.  faces0: zero-based (T, 3)."""
+    vn = np.zeros_like(pos)
+    for f in faces0:
+        v0, v1, v2 = pos[f[0]], pos[f[1]], pos[f[2]]
+        fn = _norm(np.cross(v1 - v0, v2 - v0))
+        for c in range(3):
+            vn[f[c]] = vn[f[c]] + fn
+    return np.asarray([_norm(x) for x in vn])
 
 
 def occluded(sc: Scene, o, d, t_max):

@@ -77,3 +77,92 @@ def test_oracle_trace_matches_independent_restatement(rough, depth, tmp_path):
     assert (c["raysPrimary"], c["raysShadow"], c["raysSecondary"]) == (counts["primary"], counts["shadow"], counts["secondary"])
     if depth:
         assert counts["secondary"] > counts["primary"]          # the recursion really branches
+
+
+def test_oracle_instances_and_smooth_normals_match_independent_restatement(tmp_path):
+    """The instance step of intersectTLAS (Models/RTContext.swift:651-704) and the smooth normals of RTContext.init
+    (:305-326, :497-500): a smooth mesh with a rotation + non-uniform scale, a mirrored MeshInstance of it with a
+    material override (negative determinant -> flipped normal), an instance of that instance, and a sphere stretched
+    into an ellipsoid — against a no-BVH restatement whose matrices come from numpy (inverse, inverse transpose,
+    determinant), so agreement is to rounding, not bit for bit: t to 1e-9 relative, colours to 1e-7."""
+    sg = scenegen
+    g = 5
+    rng = np.random.default_rng(3)
+    xs, zs = np.meshgrid(np.linspace(-1.5, 1.5, g), np.linspace(-1.5, 1.5, g), indexing="ij")
+    pos = np.stack([xs.ravel(), 0.35 * rng.standard_normal(g * g), zs.ravel()], axis=1)
+    faces0 = []
+    for a in range(g - 1):
+        for b in range(g - 1):
+            i = a * g + b
+            faces0 += [(i, i + 1, i + g), (i + 1, i + g + 1, i + g)]
+    faces0 = np.asarray(faces0, np.int32)
+    verts = np.concatenate([pos, [[0.2, 0.1, 0.3]]])
+    M_mesh = sg.mat_translate((-1.6, 0.4, 0.0)) @ sg.mat_rotate((0.3, 1.0, 0.2), 25.0) @ sg.mat_scale((1.2, 0.8, 1.1))
+    M_a = sg.mat_translate((2.0, 0.9, -1.0)) @ sg.mat_scale((-1.0, 1.0, 1.0)) @ sg.mat_rotate((0.0, 0.0, 1.0), 30.0)
+    M_b = sg.mat_translate((0.0, 2.6, -2.0)) @ sg.mat_rotate((1.0, 0.0, 0.0), -50.0) @ sg.mat_scale((0.7, 0.7, 0.7))
+    M_s = sg.mat_translate((0.4, -0.3, 2.2)) @ sg.mat_scale((1.5, 0.6, 1.0))
+    mats = [sg.Material(id=1, ambient=(0.3, 0.3, 0.3), diffuse=(0.7, 0.6, 0.5), specular=(0.3, 0.3, 0.3), phong=20.0),
+            sg.Material(id=2, ambient=(0.2, 0.3, 0.4), diffuse=(0.3, 0.5, 0.8), specular=(0.5, 0.5, 0.5), phong=45.0),
+            sg.Material(id=3, ambient=(0.4, 0.2, 0.2), diffuse=(0.8, 0.3, 0.2), specular=(0.2, 0.2, 0.2), phong=8.0)]
+    O = sg.SceneObject
+    objects = [O(sg.OBJ_MESH, id=10, material=1, smooth=True, faces=faces0 + 1, transform=sg.colmajor(M_mesh)),
+               O(sg.OBJ_MESH_INSTANCE, id=11, material=2, baseMeshID=10, transform=sg.colmajor(M_a)),
+               O(sg.OBJ_MESH_INSTANCE, id=12, material=3, baseMeshID=11, transform=sg.colmajor(M_b)),
+               O(sg.OBJ_SPHERE, id=13, material=2, centerIdx=g * g + 1, radius=0.7, transform=sg.colmajor(M_s))]
+    lights = [((3.0, 8.0, 7.0), (700.0, 700.0, 650.0))]
+    W, H, samples = 36, 24, 4
+    sc = sg.Scene(maxRecursionDepth=0, backgroundColor=(5, 8, 12), ambient=(30, 30, 30))
+    sc.materials, sc.objects, sc.vertexData = mats, objects, verts
+    sc.pointLights = [sg.PointLight(p, i) for p, i in lights]
+    cam = dict(width=W, height=H, numSamples=samples, position=(0.3, 3.2, 9.0), gazePoint=(0.0, 0.8, 0.0), gaze=(0, 0, -1),
+               up=(0, 1, 0), nearPlane=(-1, 1, -1, 1), nearDistance=1.0, fovy=40.0, isLookAt=True)
+    sc.cameras = [sg.Camera(id=1, width=W, height=H, numSamples=samples, position=cam["position"], gazePoint=cam["gazePoint"],
+                            up=cam["up"], nearDistance=1.0, fovy=40.0, isLookAt=True)]
+    path = os.path.join(str(tmp_path), "instances_ref.rtscene")
+    sg.write_rtscene(sc, path)
+
+    tri = pos[faces0]                                                     # (T, 3, 3)
+    vn = reftrace.smooth_vertex_normals(pos, faces0)[faces0]
+    mesh = dict(kind="mesh", v=tri, normals=vn, first=0)
+    prims = [dict(mesh, M=M_a, mat=2), dict(mesh, M=M_b, mat=3), dict(mesh, M=M_mesh, mat=1),
+             dict(kind="sphere", c=verts[-1], r=0.7, M=M_s, mat=2)]
+    materials = [dict(type="plain", ambient=m.ambient, diffuse=m.diffuse, specular=m.specular, mirror=m.mirror,
+                      absorption=m.absorption, phong=m.phong, ior=m.ior, absorptionIndex=m.absorptionIndex, roughness=0.0)
+                 for m in mats]
+    ref = reftrace.prepare(reftrace.Scene(prims, materials, lights, sc.ambient, sc.backgroundColor, 1e-6, 1e-3, 0))
+
+    got = oracle_lib.OracleScene(path).render(want_ids=True, want_linear=True)
+    ids, lin = got["ids"], got["linear"]
+    agree = total = hits = 0
+    worst = 0.0
+    for j in range(H):
+        for i in range(W):
+            colour = np.zeros(3)
+            same = True
+            for s, (o, d, tmin) in enumerate(refmath_primary(cam, i, j)):
+                h = reftrace.closest_any(ref, o, d, tmin)
+                r = ids[j, i, s]
+                total += 1
+                if h is None:
+                    ok = int(r["kind"]) == 0
+                    colour = colour + ref.background
+                else:
+                    hits += 1
+                    kind = 2 if h[4] == "sphere" else 1
+                    ok = int(r["kind"]) == kind and (kind == 2 or int(r["prim"]) == h[5]) and \
+                        abs(float(r["t"]) - h[0]) <= 1e-9 * h[0]
+                    colour = colour + reftrace.shade_direct(ref, d, h)
+                agree += ok
+                same = same and ok
+            if same:
+                want = colour / float(samples)
+                worst = max(worst, float(np.max(np.abs(lin[j, i] - want) / np.maximum(1.0, np.abs(want)))))
+    print("hits", hits, "agree", agree, "of", total, "worst colour error", worst)
+    assert hits > 0.15 * total                     # the objects fill a good part of the frame
+    assert agree >= 0.998 * total, (agree, total)  # silhouette samples may flip under the matrices' rounding
+    assert worst <= 1e-7, worst
+
+
+def refmath_primary(cam, i, j):
+    import refmath
+    return refmath.primary_rays(cam, i, j)
