@@ -36,7 +36,7 @@ def _build(tmp, rough, depth, W=30, H=20, samples=4):
                O(scenegen.OBJ_SPHERE, id=5, material=4, centerIdx=7, radius=1.0),
                O(scenegen.OBJ_SPHERE, id=6, material=3, centerIdx=8, radius=0.65),
                O(scenegen.OBJ_SPHERE, id=7, material=5, centerIdx=9, radius=0.8)]
-    lights = [((4.0, 7.0, 6.0), (900.0, 850.0, 800.0)), ((-5.0, 4.0, 3.0), (300.0, 350.0, 500.0))]
+    lights = [((4.0, 7.0, 6.0), (38000.0, 36000.0, 34000.0)), ((-5.0, 4.0, 3.0), (6000.0, 7000.0, 9000.0))]
     sc = scenegen.Scene(maxRecursionDepth=depth, backgroundColor=(20, 30, 50), ambient=(25, 25, 25), shadowRayEpsilon=1e-3,
                         intersectionTestEpsilon=1e-6)
     sc.materials, sc.objects, sc.vertexData = mats, objects, verts
@@ -75,6 +75,11 @@ def test_oracle_trace_matches_independent_restatement(rough, depth, tmp_path):
     assert err.max() <= 1e-13, (err.max(), np.unravel_index(err.argmax(), err.shape))      # measured: identical bit for bit
     c = got["counters"]
     assert (c["raysPrimary"], c["raysShadow"], c["raysSecondary"]) == (counts["primary"], counts["shadow"], counts["secondary"])
+    # RGBA8 (RayTracer.swift:186-195): clamp to [0, 255], UInt8(x) truncates towards zero, alpha 255
+    rgb = np.clip(want, 0.0, 255.0).astype(np.uint8)
+    assert np.array_equal(got["rgba"][..., :3], rgb) and (got["rgba"][..., 3] == 255).all()
+    if depth:
+        assert rgb.max() == 255 and 0 < rgb.min() < 255               # the clamp and the truncation are both exercised
     if depth:
         assert counts["secondary"] > counts["primary"]          # the recursion really branches
 
