@@ -357,7 +357,7 @@ def run_ours(args):
             "wall_ms_per_step": wall * 1e3 / args.steps, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
             "roofline": roofline, "build_ms": info["buildMs"], "upload_ms": info["uploadMs"],
             "bvh_build": ("host binned SAH" if not info["deviceBuiltBlas"] else
-                          "device binned SAH" if args.build == "device-sah" else "device LBVH")}
+                          "device binned SAH" if os.environ.get("RTCUDA_BUILD") == "device-sah" else "device LBVH")}
     if world == 1 and not args.no_cpu:
         mr, ci = cpu_sample(path, target_s=args.cpu_seconds)
         line["cpu_baseline"] = {"value": mr, "unit": UNIT, "cores": ci["cores"], "kind": "port", "sample": ci["sample"],
