@@ -406,3 +406,46 @@ def test_emulated_results_do_not_depend_on_thread_order(seed, scene_dir, tmp_pat
     assert base.keys() == again.keys() and len(base) > 6
     for key in base:
         assert np.array_equal(base[key], again[key], equal_nan=True), key
+
+
+def _c_driver(tmp_path, lib_path):
+    """Compiles tests/c_driver/driver.c with gcc (plain C, the two public headers only) against `lib_path`."""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "driver")
+    libdir, libname = os.path.split(lib_path)
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(root, "include"),
+                           os.path.join(root, "tests", "c_driver", "driver.c"), "-o", exe,
+                           "-L", libdir, "-l:" + libname, "-Wl,-rpath," + libdir])
+    return exe
+
+
+def run_c_driver(exe, scene, image):
+    import subprocess
+    r = subprocess.run([exe, scene, image], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
+    assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
+    return r.stdout.split()
+
+
+def fnv1a(data: bytes) -> int:
+    h = 1469598103934665603
+    for b in data:
+        h = ((h ^ b) * 1099511628211) & ((1 << 64) - 1)
+    return h
+
+
+def test_c_abi_from_a_plain_c_program(scene_dir, tmp_path, emu):
+    """The boundary without Python in between: a C99 program built from include/*.h alone creates
+    the engine, renders, writes the image, then feeds the flattened scene to the render module directly; here linked
+    against the emulation build, on the GPU box against librtcuda.so.  Its frame is the frame ctypes gets."""
+    exe = _c_driver(tmp_path, emu_lib.EMU_PATH)
+    path = scenegen.config_c3(scene_dir, width=40, height=24, samples=4, depth=3, ico_level=1)
+    out = run_c_driver(exe, path, str(tmp_path / "c.ppm"))
+    want = RayTracerEngine(path).render(0)
+    assert out[0] == "frame" and (int(out[1]), int(out[2])) == (40, 24)
+    assert out[3] == "fnv=%016x" % fnv1a(want.rgba.tobytes())
+    assert out[4] == "rays=%d" % want.stats["rays"]
+    assert out[6] == out[3].replace("fnv=", "fnv=") and out[5] == "module"
+    ppm = open(tmp_path / "c.ppm", "rb").read()
+    assert ppm.startswith(b"P6\n40 24\n255\n") and ppm[-40 * 24 * 3:] == want.rgba[..., :3].tobytes()

@@ -37,3 +37,16 @@ def test_device_sah_build_makes_the_host_builders_tree(name, scene_dir, monkeypa
     rep = parity.compare(b, oracle_lib.OracleScene(path).render(want_ids=True, want_linear=True))
     assert rep["id_agree"] >= 0.9999 and rep["id_bad"] == 0, rep
     assert rep["px_within_1"] >= 0.999, rep
+
+
+def test_c_abi_from_a_plain_c_program_on_the_gpu(scene_dir, tmp_path):
+    """tests/c_driver/driver.c linked against librtcuda.so: engine -> frame -> image file, then the flattened scene
+    straight into rt_scene_create / rt_render; same frame as through ctypes."""
+    from myraytracer_b200 import capi, scenegen
+    from test_emu_cpu import _c_driver, fnv1a, run_c_driver
+    exe = _c_driver(tmp_path, capi.LIB_PATH)
+    path = scenegen.config_c3(scene_dir, width=160, height=96, samples=4, depth=4, ico_level=2)
+    out = run_c_driver(exe, path, str(tmp_path / "c.png"))
+    want = RayTracerEngine(path).render(0)
+    assert out[3] == "fnv=%016x" % fnv1a(want.rgba.tobytes())
+    assert out[6] == out[3]
