@@ -54,6 +54,29 @@ def test_bvh_builder_invariants(n):
         assert (leaves[:, 1] <= 2).mean() > 0.9                  # maxLeaf 2 unless the split degenerates (:128-188)
 
 
+@pytest.mark.parametrize("n", [1, 2, 3, 5, 17, 200, 1500])
+def test_bvh_builder_matches_independent_restatement(n):
+    """oracle/bvh.hpp against tests/refbvh.py (pure Python, written from BVH.swift:78-250): node boxes, leftFirst /
+    primitiveCount of every node and the primitiveIdx permutation identical — the topology the reference's traversal
+    order, its tie-breaking and (with instance motion) its image depend on.  n = 5: coincident centroids, no split."""
+    import refbvh
+    L = oracle_lib.lib()
+    rng = np.random.default_rng(n)
+    c = rng.uniform(-5, 5, size=(n, 3))
+    h = rng.uniform(0.01, 0.3, size=(n, 3))
+    if n == 5:
+        c[:] = c[0]
+    bounds = np.concatenate([c - h, c + h], axis=1).copy()
+    nb = np.zeros((2 * n, 6)); meta = np.zeros((2 * n, 2), np.int64); prim = np.zeros(n, np.int64)
+    used = L.orc_bvh_build(n, _p(bounds), _p(c.copy()), _p(nb), _p(meta), _p(prim))
+    B = refbvh.Builder(bounds, c)
+    k = B.used + 1
+    assert used == k
+    assert prim.tolist() == B.prim_idx
+    assert np.array_equal(meta[:k, 0], B.left_first[:k]) and np.array_equal(meta[:k, 1], B.count[:k])
+    assert np.array_equal(nb[:k, :3], np.array(B.lo[:k])) and np.array_equal(nb[:k, 3:], np.array(B.hi[:k]))
+
+
 # ---------------------------------------------------------------------------------- PLY ingest
 def _write_quad_ply(path):
     with open(path, "wb") as f:
