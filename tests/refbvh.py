@@ -116,3 +116,42 @@ class Builder:
         self.update_bounds(rc)
         self.subdivide(lc)
         self.subdivide(rc)
+
+
+def hit_aabb(lo, hi, o, inv, eps):
+    """hitAABB of the traversal loops (Models/RTContext.swift:561-569): entry distance, or inf for a miss."""
+    t1 = [(lo[a] - o[a]) * inv[a] for a in range(3)]
+    t2 = [(hi[a] - o[a]) * inv[a] for a in range(3)]
+    tmin = max(max(min(t1[0], t2[0]), min(t1[1], t2[1])), min(t1[2], t2[2]))
+    tmax = min(max(t1[0], t2[0]), min(max(t1[1], t2[1]), max(t1[2], t2[2])))
+    return tmin if tmax >= max(tmin, eps) else INF
+
+
+def closest_in_blas(B: Builder, o, d, eps, t_min, test):
+    """intersectBLAS (:545-618): explicit stack, node re-tested when popped, near child pushed last, leaves walk
+    primitiveIdx in order.  test(prim, best_t) -> t or None applies the primitive's own rules (t > max(eps, tMin),
+    t < best_t: the FIRST primitive visited keeps an equal-t tie).  Returns (prim or -1, t, node visits)."""
+    inv = [1.0 / x for x in d]
+    best, best_t, visits = -1, INF, 0
+    stack = [0]
+    while stack:
+        visits += 1
+        k = stack.pop()
+        if hit_aabb(B.lo[k], B.hi[k], o, inv, eps) == INF:
+            continue
+        if B.count[k] > 0:
+            for i in range(B.left_first[k], B.left_first[k] + B.count[k]):
+                p = B.prim_idx[i]
+                t = test(p, best_t)
+                if t is not None:
+                    best, best_t = p, t
+            continue
+        L, R = B.left_first[k], B.left_first[k] + 1
+        d1, d2 = hit_aabb(B.lo[L], B.hi[L], o, inv, eps), hit_aabb(B.lo[R], B.hi[R], o, inv, eps)
+        if d1 > d2:
+            d1, d2, L, R = d2, d1, R, L
+        if d2 != INF:
+            stack.append(R)
+        if d1 != INF:
+            stack.append(L)
+    return best, best_t, visits

@@ -199,3 +199,57 @@ def test_oracle_chunk_sampling_is_consistent(scene_dir):
         rows[c * 8:(c + 1) * 8] = True
     assert np.array_equal(part["rgba"][rows], full["rgba"][rows])
     assert part["counters"]["raysPrimary"] == int(rows.sum()) * 64
+
+
+# ---------------------------------------------------------------------------------- traversal order and ties
+def test_tie_breaking_follows_the_reference_traversal_order(tmp_path):
+    """Hits are committed on strict t < hit.t (Models/RTContext.swift:494), so among primitives at exactly the same
+    distance the first one VISITED wins, and the visiting order is the reference's: its BVH (BVH.swift:78-250), its
+    near-first rule and stack discipline (:590-616), primitiveIdx order inside a leaf.  A mesh in which every triangle
+    exists three times makes every hit a three-way tie; the oracle must report the triangle that a pure-Python walk
+    of tests/refbvh.py's tree reports — for every primary ray."""
+    import refbvh
+    rng = np.random.default_rng(21)
+    nt = 40
+    base = rng.uniform(-3, 3, size=(nt, 1, 3)) + rng.uniform(-0.9, 0.9, size=(nt, 3, 3))
+    tri = np.concatenate([base, base, base])[rng.permutation(3 * nt)]          # 120 triangles, each position 3 times
+    verts = tri.reshape(-1, 3)
+    faces = (np.arange(len(verts), dtype=np.int32) + 1).reshape(-1, 3)
+    W, H, samples = 36, 28, 1
+    sc = scenegen.Scene(maxRecursionDepth=0, backgroundColor=(1, 2, 3), ambient=(10, 10, 10))
+    sc.vertexData = verts
+    sc.materials = [scenegen.Material(id=1)]
+    sc.objects = [scenegen.SceneObject(scenegen.OBJ_MESH, id=1, material=1, smooth=False, faces=faces)]
+    sc.pointLights = [scenegen.PointLight((0, 8, 8), (500, 500, 500))]
+    cam = dict(width=W, height=H, numSamples=samples, position=(0.2, 0.3, 9.0), gazePoint=(0, 0, 0), gaze=(0, 0, -1),
+               up=(0, 1, 0), nearPlane=(-1, 1, -1, 1), nearDistance=1.0, fovy=50.0, isLookAt=True)
+    sc.cameras = [scenegen.Camera(id=1, width=W, height=H, numSamples=samples, position=cam["position"],
+                                  gazePoint=cam["gazePoint"], up=cam["up"], nearDistance=1.0, fovy=50.0, isLookAt=True)]
+    path = os.path.join(str(tmp_path), "ties.rtscene")
+    scenegen.write_rtscene(sc, path)
+    ids = oracle_lib.OracleScene(path).render(want_ids=True)["ids"]
+
+    bounds = np.concatenate([tri.min(axis=1), tri.max(axis=1)], axis=1)
+    cent = ((tri[:, 0] + tri[:, 1]) + tri[:, 2]) / 3                            # tri.centroid, RTContext.swift:339
+    B = refbvh.Builder(bounds, cent)
+    eps = 1e-6
+    hits = ties = 0
+    for j in range(H):
+        for i in range(W):
+            (o, d, tmin), = refmath.primary_rays(cam, i, j)
+
+            def test(p, best_t):
+                h = refmath.mt_single(o, d, tri[p, 0], tri[p, 1], tri[p, 2], eps)
+                return h[0] if h and h[0] > max(eps, tmin) and h[0] < best_t else None
+
+            prim, t, _ = refbvh.closest_in_blas(B, list(o), list(d), eps, tmin, test)
+            r = ids[j, i, 0]
+            if prim < 0:
+                assert int(r["kind"]) == 0
+                continue
+            hits += 1
+            assert int(r["kind"]) == 1 and float(r["t"]) == t
+            assert int(r["prim"]) == prim, (i, j, int(r["prim"]), prim)
+            k, tb = refmath.brute_force_triangles(o, d, tri, eps, tmin)
+            ties += int(tb == t and k != prim)
+    assert hits > 100 and ties > 20, (hits, ties)       # the winner is often not the lowest-numbered of the three
