@@ -171,3 +171,62 @@ def test_oracle_instances_and_smooth_normals_match_independent_restatement(tmp_p
 def refmath_primary(cam, i, j):
     import refmath
     return refmath.primary_rays(cam, i, j)
+
+
+def _aabb_transformed(box, M):
+    """AABB.transformed(by:), Accelearion/AABB.swift:71-92: centre through the matrix, half extents through |R|."""
+    lo, hi = np.asarray(box[:3]), np.asarray(box[3:])
+    c_old, e_old = 0.5 * (lo + hi), 0.5 * (hi - lo)
+    R, t = M[:3, :3], M[:3, 3]
+    c_new = ((R[:, 0] * c_old[0] + R[:, 1] * c_old[1]) + R[:, 2] * c_old[2]) + t
+    A = np.abs(R)
+    e_new = (A[:, 0] * e_old[0] + A[:, 1] * e_old[1]) + A[:, 2] * e_old[2]
+    return np.concatenate([c_new - e_new, c_new + e_new])
+
+
+def test_oracle_instance_records_match_independent_restatement(tmp_path):
+    """makeInstance (Models/RTContext.swift:437-455): worldBounds = union over the BLAS's primitives of their boxes
+    moved by AABB.transformed (every triangle's box, not the mesh's box), worldToLocal = inverse, normal matrix =
+    inverse transpose of the upper 3x3 — for the analytic primitives, the MeshInstances (one mirrored, one an instance
+    of an instance) and the base mesh of config_instances, in RTContext's order (:96-410)."""
+    import ctypes as C
+    sg = scenegen
+    path = sg.config_instances(str(tmp_path), width=16, height=12, samples=1, frame=0.35)
+    orc = oracle_lib.OracleScene(path)
+    inst = orc.instances()
+    L = oracle_lib.lib()
+
+    # unit: AABB.transformed on random boxes and matrices (rotation, shear, mirror)
+    rng = np.random.default_rng(8)
+    for _ in range(20):
+        lo = rng.uniform(-3, 3, 3)
+        box = np.concatenate([lo, lo + rng.uniform(0, 2, 3)])
+        M = np.eye(4)
+        M[:3, :4] = rng.uniform(-2, 2, (3, 4))
+        out = np.zeros(6)
+        Mc = np.ascontiguousarray(M.T).ravel()                               # column-major
+        L.orc_aabb_transformed(box.ctypes.data_as(C.c_void_p), Mc.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p))
+        assert np.allclose(out, _aabb_transformed(box, M), rtol=1e-14, atol=1e-14)
+
+    # the scene's instances
+    pos, tris = sg.icosphere_mesh(2, radius=1.0, seed=7, disp=0.15)
+    pos = pos.astype(np.float32).astype(np.float64)                           # PLYReader.swift:85-101
+    tri = pos[tris]
+    tri_boxes = np.concatenate([tri.min(axis=1), tri.max(axis=1)], axis=1)
+    l2w = inst["l2w"].reshape(-1, 4, 4).transpose(0, 2, 1)                    # stored column-major
+    n = len(l2w)
+    assert n == 6                                                             # plane, sphere, 3 mesh instances, base mesh
+    seen_mesh = 0
+    for k in range(n):
+        M = l2w[k]
+        assert np.allclose(inst["w2l"][k].reshape(4, 4).T, np.linalg.inv(M), rtol=1e-12, atol=1e-12)
+        assert np.allclose(inst["nmat"][k].reshape(3, 3).T, np.linalg.inv(M[:3, :3]).T, rtol=1e-12, atol=1e-12)
+        got = inst["bounds"][k]
+        cands = {"plane": _aabb_transformed(np.array([-1e5] * 3 + [1e5] * 3), M),
+                 "sphere": _aabb_transformed(np.array([0.8 - 1.0, 1.1 - 1.0, 4.0 - 1.0, 0.8 + 1.0, 1.1 + 1.0, 4.0 + 1.0]), M)}
+        moved = np.asarray([_aabb_transformed(b, M) for b in tri_boxes])
+        cands["mesh"] = np.concatenate([moved[:, :3].min(axis=0), moved[:, 3:].max(axis=0)])
+        kind = [name for name, want in cands.items() if np.allclose(got, want, rtol=1e-12, atol=1e-9)]
+        assert len(kind) == 1, (k, got, cands)
+        seen_mesh += kind[0] == "mesh"
+    assert seen_mesh == 4
