@@ -9,6 +9,7 @@ import numpy as np
 import pytest
 
 import oracle_lib
+import refmath
 import reftrace
 from myraytracer_b200 import scenegen
 
@@ -230,3 +231,76 @@ def test_oracle_instance_records_match_independent_restatement(tmp_path):
         assert len(kind) == 1, (k, got, cands)
         seen_mesh += kind[0] == "mesh"
     assert seen_mesh == 4
+
+
+def _mul(M, v, w):
+    """simd_double4x4 * SIMD4(v, w): columns scaled and added left to right (column-major M given as 4x4 numpy)."""
+    return (((M[:3, 0] * v[0] + M[:3, 1] * v[1]) + M[:3, 2] * v[2]) + M[:3, 3] * w)
+
+
+def test_oracle_instance_motion_matches_independent_restatement(tmp_path):
+    """MeshInstance.motionBlur (Models/RTContext.swift:651-704): the TLAS boxes do not follow the motion (makeInstance,
+    :437-455), the box tests see the undisplaced ray, and only inside an instance is the origin moved by
+    -instanceMotion * time — so which displaced instances a ray can reach depends on the reference's own TLAS.  A
+    pure-Python walk of tests/refbvh.py's tree over the instance bounds, brute force inside each instance reached,
+    against the oracle's primary hits: same primitive, t bit for bit, for every sample (4 spp: 4 ray times a pixel)."""
+    import refbvh
+    sg = scenegen
+    W, H, samples, motion = 40, 30, 4, 1.2
+    path = sg.config_instances(str(tmp_path), width=W, height=H, samples=samples, instance_motion=motion)
+    orc = oracle_lib.OracleScene(path)
+    inst = orc.instances()
+    ids = orc.render(want_ids=True)["ids"]
+    cam = dict(width=W, height=H, numSamples=samples, position=(0.5, 4.5, 12.0), gazePoint=(0.0, 1.2, 0.0), gaze=(0, 0, -1),
+               up=(0, 1, 0), nearPlane=(-1, 1, -1, 1), nearDistance=1.0, fovy=45.0, isLookAt=True)
+    pos, tris = sg.icosphere_mesh(2, radius=1.0, seed=7, disp=0.15)
+    tri = pos.astype(np.float32).astype(np.float64)[tris]
+    w2l = inst["w2l"].reshape(-1, 4, 4).transpose(0, 2, 1)
+    move = {6: (0.9 * motion, 0.0, 0.3 * motion), 7: (0.0, 0.7 * motion, 0.0), 8: (-0.5 * motion, -0.4 * motion, 0.6 * motion)}
+    obj = inst["meta"][:, 0]
+    n = len(obj)
+    bounds = inst["bounds"]
+    tlas = refbvh.Builder(bounds, (bounds[:, :3] + bounds[:, 3:]) * 0.5)      # buildTLAS, :459-474
+    eps = 1e-6
+    box = (np.full(3, -1e5), np.full(3, 1e5))
+    moved_hits = total_hits = 0
+    for j in range(H):
+        for i in range(W):
+            for s, (o, d, tmin, time) in enumerate(refmath.primary_rays(cam, i, j, with_time=True)):
+                found = {}
+
+                def test(k, best_t):
+                    ol = _mul(w2l[k], o - np.asarray(move.get(int(obj[k]), (0.0, 0.0, 0.0))) * time, 1.0)
+                    dl = _mul(w2l[k], d, 0.0)
+                    if inst["meta"][k, 2] > 1:
+                        p, t = refmath.brute_force_triangles(ol, dl, tri, eps, tmin)
+                        kind = 1
+                    elif int(obj[k]) == 2:
+                        p, t, kind = 0, refmath.brute_force_sphere(ol, dl, np.array([0.8, 1.1, 4.0]), 1.0, eps, tmin), 2
+                    else:
+                        p, t, kind = 0, np.inf, 3
+                        with np.errstate(divide="ignore"):
+                            inv = 1.0 / dl
+                        nrm, ctr = np.array([0.0, 1.0, 0.0]), np.zeros(3)                    # intersectPlane, :526-536
+                        denom = refmath._dot(nrm, dl)
+                        if reftrace._hit_aabb(box[0], box[1], ol, inv, eps) and abs(denom) >= eps:
+                            tp = refmath._dot(ctr - ol, nrm) / denom
+                            if tp > max(eps, tmin):
+                                t = tp
+                    if t < best_t:
+                        found[k] = (kind, p)
+                        return t
+                    return None
+
+                k, t, _ = refbvh.closest_in_blas(tlas, list(o), list(d), eps, tmin, test)
+                r = ids[j, i, s]
+                if k < 0:
+                    assert int(r["kind"]) == 0, (i, j, s)
+                    continue
+                kind, p = found[k]
+                total_hits += 1
+                moved_hits += int(obj[k]) in move
+                assert int(r["kind"]) == kind and float(r["t"]) == t, (i, j, s, r, kind, t)
+                if kind == 1:
+                    assert int(r["prim"]) == p and int(r["inst"]) == k, (i, j, s, r, p, k)
+    assert total_hits > 0.5 * W * H * samples and moved_hits > 100, (total_hits, moved_hits)
