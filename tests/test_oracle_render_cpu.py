@@ -126,7 +126,7 @@ def test_ply_positions_are_float32_exact(tmp_path):
 
 
 # ---------------------------------------------------------------------------------- brute-force differential
-def _random_scene(tmp, seed, ntri=150, samples=4, W=40, H=30, aperture=0.0, focus=0.0):
+def _random_scene(tmp, seed, ntri=150, samples=4, W=40, H=30, aperture=0.0, focus=0.0, lookat=True):
     rng = np.random.default_rng(seed)
     base = rng.uniform(-3, 3, size=(ntri, 1, 3))
     tri = base + rng.uniform(-0.7, 0.7, size=(ntri, 3, 3))
@@ -141,20 +141,25 @@ def _random_scene(tmp, seed, ntri=150, samples=4, W=40, H=30, aperture=0.0, focu
     cam = dict(width=W, height=H, numSamples=samples, position=(0.3, 0.4, 9.0), gazePoint=(0, 0, 0), gaze=(0, 0, -1),
                up=(0, 1, 0), nearPlane=(-1, 1, -1, 1), nearDistance=1.0, fovy=50.0, isLookAt=True, apertureSize=aperture,
                focusDistance=focus)
+    if not lookat:                       # "simple" camera: gaze vector + explicit near plane (:404-427), up not orthogonal
+        cam.update(isLookAt=False, fovy=None, gaze=(-0.05, -0.04, -1.0), up=(0.1, 1.0, -0.2), nearPlane=(-0.55, 0.5, -0.4, 0.42),
+                   nearDistance=1.2)
     sc.cameras = [scenegen.Camera(id=1, width=W, height=H, numSamples=samples, position=cam["position"],
-                                  gazePoint=cam["gazePoint"], up=cam["up"], nearDistance=1.0, fovy=50.0, isLookAt=True,
+                                  gazePoint=cam["gazePoint"], gaze=cam["gaze"], up=cam["up"], nearPlane=cam["nearPlane"],
+                                  nearDistance=cam["nearDistance"], fovy=cam["fovy"], isLookAt=cam["isLookAt"],
                                   apertureSize=aperture, focusDistance=focus)]
     path = os.path.join(tmp, f"rand{seed}_{aperture}.rtscene")
     scenegen.write_rtscene(sc, path)
     return path, cam, tri, verts[-1], 0.8
 
 
-@pytest.mark.parametrize("seed,aperture,focus", [(11, 0.0, 0.0), (12, 0.0, 0.0), (13, 0.45, 8.5)])
-def test_primary_hits_match_brute_force(tmp_path, seed, aperture, focus):
+@pytest.mark.parametrize("seed,aperture,focus,lookat", [(11, 0.0, 0.0, True), (12, 0.0, 0.0, True), (13, 0.45, 8.5, True),
+                                                        (14, 0.0, 0.0, False), (15, 0.3, 9.0, False)])
+def test_primary_hits_match_brute_force(tmp_path, seed, aperture, focus, lookat):
     """Oracle (reference BVH + reference traversal order) vs an independent no-BVH search with independently
     written PCG32 / camera code: same primitive and bit-identical t for every primary ray — also through the thin
     lens (Object+Extension.swift:325-338: two more draws per sample, origin on the lens, image-plane tMin from there)."""
-    path, cam, tri, sc_c, sc_r = _random_scene(str(tmp_path), seed, aperture=aperture, focus=focus)
+    path, cam, tri, sc_c, sc_r = _random_scene(str(tmp_path), seed, aperture=aperture, focus=focus, lookat=lookat)
     r = oracle_lib.OracleScene(path).render(want_ids=True)
     ids = r["ids"]
     eps = 1e-6
