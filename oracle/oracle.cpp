@@ -9,7 +9,12 @@
 //  and cannot be built here (no Swift toolchain, Apple-only
 // imports, ParsingKit absent), so the render restatement is "parity unpinned";
 // it is held by per-function file:line traceability, hand-derived KATs and a
-// brute-force cross-check (tests/).  The one part pinned by REAL reference
+// second, independently written restatement in Python without any shared code
+// (tests/refmath.py, reftrace.py, refbvh.py: PCG32 and seed, both cameras and
+// the thin lens, BVHBuilder, traversal order and tie-breaking, instance
+// transforms and motion, smooth normals, area lights, the whole trace
+// recursion and the RGBA8 rule agree bit for bit or to rounding; DESIGN.md
+// section 7 lists the tests).  The one part pinned by REAL reference
 // code is PLY ingest: oracle/_ref/libcply.so is compiled from the reference's
 // own Sources/CPly and driven through its ply_reader_* ABI.
 #include <chrono>
