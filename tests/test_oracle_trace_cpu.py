@@ -65,9 +65,10 @@ def _build(tmp, rough, depth, W=30, H=20, samples=4):
     return path, ref, cam
 
 
-@pytest.mark.parametrize("rough,depth", [(0.0, 4), (0.15, 3), (0.0, 0)])
-def test_oracle_trace_matches_independent_restatement(rough, depth, tmp_path):
-    path, ref, cam = _build(str(tmp_path), rough, depth)
+@pytest.mark.parametrize("rough,depth,samples", [(0.0, 4, 4), (0.15, 3, 4), (0.0, 0, 4), (0.0, 1, 7)])
+def test_oracle_trace_matches_independent_restatement(rough, depth, samples, tmp_path):
+    # 7 samples: n = floor(sqrt(7)) = 2 -> four rays, their sum divided by 7 (Object+Extension.swift:299-356)
+    path, ref, cam = _build(str(tmp_path), rough, depth, samples=samples)
     want, counts = reftrace.render(ref, cam)
     got = oracle_lib.OracleScene(path).render(want_ids=True, want_linear=True)
     lin = got["linear"]
@@ -79,10 +80,9 @@ def test_oracle_trace_matches_independent_restatement(rough, depth, tmp_path):
     # RGBA8 (RayTracer.swift:186-195): clamp to [0, 255], UInt8(x) truncates towards zero, alpha 255
     rgb = np.clip(want, 0.0, 255.0).astype(np.uint8)
     assert np.array_equal(got["rgba"][..., :3], rgb) and (got["rgba"][..., 3] == 255).all()
-    if depth:
+    if depth >= 3:
         assert rgb.max() == 255 and 0 < rgb.min() < 255               # the clamp and the truncation are both exercised
-    if depth:
-        assert counts["secondary"] > counts["primary"]          # the recursion really branches
+        assert counts["secondary"] > counts["primary"]                # the recursion really branches
 
 
 def test_oracle_instances_and_smooth_normals_match_independent_restatement(tmp_path):
