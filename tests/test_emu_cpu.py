@@ -451,18 +451,25 @@ def test_c_abi_from_a_plain_c_program(scene_dir, tmp_path, emu):
     assert ppm.startswith(b"P6\n40 24\n255\n") and ppm[-40 * 24 * 3:] == want.rgba[..., :3].tobytes()
 
 
-@pytest.mark.parametrize("rough,depth,variants", [(0.0, 4, (1, 2)), (0.15, 3, (2,))])
-def test_emulated_kernels_vs_independent_restatement(rough, depth, variants, tmp_path, emu):
+@pytest.mark.parametrize("rough,depth,variants,inf_light", [(0.0, 4, (1, 2), False), (0.15, 3, (2,), False),
+                                                            (0.0, 2, (1, 2), True)])
+def test_emulated_kernels_vs_independent_restatement(rough, depth, variants, inf_light, tmp_path, emu):
     """The CUDA sources against tests/reftrace.py directly — the pure-Python restatement of `trace` written from the
     Swift source, no BVH, no oracle in between: linear colours of every pixel to 1e-12 and the same ray counts."""
     import reftrace
     from test_oracle_trace_cpu import _build
-    path, ref, cam = _build(str(tmp_path), rough, depth, W=24, H=16)
+    # inf_light: a light of infinite intensity -> non-finite Lo -> that level returns black (Object+Extension.swift:277-280)
+    path, ref, cam = _build(str(tmp_path), rough, depth, W=24, H=16, inf_light=inf_light)
     want, counts = reftrace.render(ref, cam)
     eng = RayTracerEngine(path)
     for variant in variants:
         got = eng.render(0, want_linear=True, variant=variant)
         err = np.abs(got.linear - want) / np.maximum(1.0, np.abs(want))
         assert err.max() <= 1e-12, (variant, err.max())
-        assert (got.stats["raysPrimary"], got.stats["raysShadow"], got.stats["raysSecondary"]) == \
-            (counts["primary"], counts["shadow"], counts["secondary"]), variant
+        rays = (got.stats["raysPrimary"], got.stats["raysShadow"], got.stats["raysSecondary"])
+        if inf_light:
+            # same image with fewer rays: a level whose direct light is already non-finite returns black without
+            # walking its children first (the reference walks them, then discards the result; DESIGN.md 4b)
+            assert rays[0] == counts["primary"] and rays[1] < counts["shadow"] and rays[2] < counts["secondary"], variant
+        else:
+            assert rays == (counts["primary"], counts["shadow"], counts["secondary"]), variant

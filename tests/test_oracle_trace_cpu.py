@@ -17,7 +17,7 @@ TYPES = {scenegen.MAT_PLAIN: "plain", scenegen.MAT_MIRROR: "mirror", scenegen.MA
          scenegen.MAT_CONDUCTOR: "conductor"}
 
 
-def _build(tmp, rough, depth, W=30, H=20, samples=4):
+def _build(tmp, rough, depth, W=30, H=20, samples=4, inf_light=False):
     verts = np.asarray([(0, -1.0, 0), (-7, -1, -6), (7, -1, -6), (7, 6, -6), (-7, 6, -6),          # 1 plane point, 2-5 wall
                         (-1.9, 0.1, 0.4), (1.7, 0.0, -0.3), (0.1, 0.35, 2.1), (-0.3, 2.3, -1.8)], np.float64)
     M = scenegen.Material
@@ -38,6 +38,8 @@ def _build(tmp, rough, depth, W=30, H=20, samples=4):
                O(scenegen.OBJ_SPHERE, id=6, material=3, centerIdx=8, radius=0.65),
                O(scenegen.OBJ_SPHERE, id=7, material=5, centerIdx=9, radius=0.8)]
     lights = [((4.0, 7.0, 6.0), (38000.0, 36000.0, 34000.0)), ((-5.0, 4.0, 3.0), (6000.0, 7000.0, 9000.0))]
+    if inf_light:                        # a shading point it reaches has a non-finite Lo: that level returns black (:277-280)
+        lights[1] = (lights[1][0], (float("inf"),) * 3)
     sc = scenegen.Scene(maxRecursionDepth=depth, backgroundColor=(20, 30, 50), ambient=(25, 25, 25), shadowRayEpsilon=1e-3,
                         intersectionTestEpsilon=1e-6)
     sc.materials, sc.objects, sc.vertexData = mats, objects, verts
@@ -46,7 +48,7 @@ def _build(tmp, rough, depth, W=30, H=20, samples=4):
                up=(0, 1, 0), nearPlane=(-1, 1, -1, 1), nearDistance=1.0, fovy=42.0, isLookAt=True)
     sc.cameras = [scenegen.Camera(id=1, width=W, height=H, numSamples=samples, position=cam["position"],
                                   gazePoint=cam["gazePoint"], up=cam["up"], nearDistance=1.0, fovy=42.0, isLookAt=True)]
-    path = os.path.join(tmp, f"trace_ref_{rough}_{depth}.rtscene")
+    path = os.path.join(tmp, f"trace_ref_{rough}_{depth}_{samples}_{int(inf_light)}.rtscene")
     scenegen.write_rtscene(sc, path)
 
     prims = []
@@ -65,10 +67,11 @@ def _build(tmp, rough, depth, W=30, H=20, samples=4):
     return path, ref, cam
 
 
-@pytest.mark.parametrize("rough,depth,samples", [(0.0, 4, 4), (0.15, 3, 4), (0.0, 0, 4), (0.0, 1, 7)])
-def test_oracle_trace_matches_independent_restatement(rough, depth, samples, tmp_path):
+@pytest.mark.parametrize("rough,depth,samples,inf_light", [(0.0, 4, 4, False), (0.15, 3, 4, False), (0.0, 0, 4, False),
+                                                           (0.0, 1, 7, False), (0.0, 2, 1, True)])
+def test_oracle_trace_matches_independent_restatement(rough, depth, samples, inf_light, tmp_path):
     # 7 samples: n = floor(sqrt(7)) = 2 -> four rays, their sum divided by 7 (Object+Extension.swift:299-356)
-    path, ref, cam = _build(str(tmp_path), rough, depth, samples=samples)
+    path, ref, cam = _build(str(tmp_path), rough, depth, samples=samples, inf_light=inf_light)
     want, counts = reftrace.render(ref, cam)
     got = oracle_lib.OracleScene(path).render(want_ids=True, want_linear=True)
     lin = got["linear"]
@@ -80,6 +83,8 @@ def test_oracle_trace_matches_independent_restatement(rough, depth, samples, tmp
     # RGBA8 (RayTracer.swift:186-195): clamp to [0, 255], UInt8(x) truncates towards zero, alpha 255
     rgb = np.clip(want, 0.0, 255.0).astype(np.uint8)
     assert np.array_equal(got["rgba"][..., :3], rgb) and (got["rgba"][..., 3] == 255).all()
+    if inf_light:
+        assert (want == 0).all(axis=-1).mean() > 0.2 and (want != 0).any(axis=-1).mean() > 0.05, "guard not exercised"
     if depth >= 3:
         assert rgb.max() == 255 and 0 < rgb.min() < 255               # the clamp and the truncation are both exercised
         assert counts["secondary"] > counts["primary"]                # the recursion really branches
