@@ -150,7 +150,7 @@ def test_oracle_instances_and_smooth_normals_match_independent_restatement(tmp_p
         for i in range(W):
             colour = np.zeros(3)
             same = True
-            for s, (o, d, tmin) in enumerate(refmath_primary(cam, i, j)):
+            for s, (o, d, tmin) in enumerate(refmath.primary_rays(cam, i, j)):
                 h = reftrace.closest_any(ref, o, d, tmin)
                 r = ids[j, i, s]
                 total += 1
@@ -174,9 +174,6 @@ def test_oracle_instances_and_smooth_normals_match_independent_restatement(tmp_p
     assert worst <= 1e-7, worst
 
 
-def refmath_primary(cam, i, j):
-    import refmath
-    return refmath.primary_rays(cam, i, j)
 
 
 def _aabb_transformed(box, M):
