@@ -285,10 +285,12 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFas
             if (active) {
                 if (!isHit) {
                     c = c + cur0.w * background;                                        // :101-103
-                } else if (finite3(Lo)) {                                               // :277-280
-                    c = c + sp.w * Lo;
+                } else {
+                    const bool dead = !finite3(Lo);                                     // :277-280, see scalarPathLoop
+                    if (!dead) c = c + sp.w * Lo;
                     PathEntry c1, c2;
                     const int nc = spawnChildren<false>(S, sp, cur0, rng, c1, c2);
+                    if (dead) { c1.beer |= PATH_DEAD; c2.beer |= PATH_DEAD; }
                     if (nc > 0) {
                         if (nc == 2) pathStore(T.pathStack, T.stride, T.gtid, 0, c2);
                         R.secondary += nc;

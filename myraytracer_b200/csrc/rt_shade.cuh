@@ -20,8 +20,12 @@ struct PathEntry {
     V3 o, d, w;
     long long beerMat;   // Hit.mat of the dielectric surface this refraction ray entered
     int depth;
-    int beer;            // 1: apply Beer attenuation at the next hit (Object+Extension.swift:245-248)
+    int beer;            // bit 0: apply Beer attenuation at the next hit (Object+Extension.swift:245-248)
+                         // bit 1 (PATH_DEAD): an ancestor's Lo was non-finite — the reference still walks this subtree
+                         // (rays, RNG draws, jitter index) and then throws the level away (:277-280): nothing is added
 };
+#define PATH_BEER 1
+#define PATH_DEAD 2
 
 __device__ __forceinline__ void pathStore(double* base, size_t stride, size_t gtid, int level, const PathEntry& e) {
     double* p = base + ((size_t)level * PATH_FIELDS) * stride + gtid;
@@ -113,7 +117,7 @@ __device__ __forceinline__ void setupShade(const DeviceScene& S, const Surface& 
     sp.mat = &mat;
     sp.matId = sf.mat;
     V3 w = cur.w;
-    if (cur.beer && sf.mat == cur.beerMat) {                                            // :245-248
+    if ((cur.beer & PATH_BEER) && sf.mat == cur.beerMat) {                                            // :245-248
         const double dist = dmax(hitT, 0.0);
         if (isfinite(dist) && dist > 0)
             w = w * mk(exp(-mat.absorption[0] * dist), exp(-mat.absorption[1] * dist), exp(-mat.absorption[2] * dist));
@@ -288,7 +292,7 @@ __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceSc
         primary = false;
         int spawned = 0;
         if (hit.inst < 0) {
-            color = color + cur.w * background;                                         // :101-103
+            if (!(cur.beer & PATH_DEAD)) color = color + cur.w * background;            // :101-103
         } else {
             ShadePoint sp;
             setupShade(S, sf, cur, hit.t, sp);
@@ -327,13 +331,17 @@ __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceSc
                     if (!occluded) Lo = Lo + areaLightTerm(*sp.mat, al, sp.N, cur.d, wi, dist2, NdotL, Ln);
                 }
             }
-            if (finite3(Lo)) {                                                          // NaN guard, :277-280
-                color = color + sp.w * Lo;
-                PathEntry c1, c2;
-                const int nc = spawnChildren<GLOSSY>(S, sp, cur, rng, c1, c2);
-                if (nc == 2) { pathStore(T.pathStack, T.stride, T.gtid, level, c2); level++; }
-                if (nc > 0) { cur = c1; spawned = 1; R.secondary += nc; }
-            }
+            // NaN guard (:277-280): the reference traces the children first (their rays, RNG draws and jitter-index
+            // steps happen) and then returns black for a level whose Lo is not finite.  A child's own level returns a
+            // finite value or black, so the level's total is non-finite exactly when its direct term is: such a level
+            // and everything below it is walked with PATH_DEAD set and adds nothing.
+            const bool dead = (cur.beer & PATH_DEAD) != 0 || !finite3(Lo);
+            if (!dead) color = color + sp.w * Lo;
+            PathEntry c1, c2;
+            const int nc = spawnChildren<GLOSSY>(S, sp, cur, rng, c1, c2);
+            if (dead) { c1.beer |= PATH_DEAD; c2.beer |= PATH_DEAD; }
+            if (nc == 2) { pathStore(T.pathStack, T.stride, T.gtid, level, c2); level++; }
+            if (nc > 0) { cur = c1; spawned = 1; R.secondary += nc; }
         }
         if (!spawned) {
             if (level == 0) break;

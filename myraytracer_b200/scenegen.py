@@ -370,12 +370,13 @@ def config_c4(out_dir: str, n: int = 708, width: int = 1920, height: int = 1080,
 
 def config_c3(out_dir: str, width: int = 1024, height: int = 1024, samples: int = 4, depth: int = 6,
               ico_level: int = 4, roughness: float = 0.0, aperture: float = 0.0, focus: float = 0.0,
-              area_lights: int = 0) -> str:
+              area_lights: int = 0, inf_light: bool = False) -> str:
     """C3: closed box (10 lone triangles), mirror / dielectric / conductor spheres, dielectric PLY icosphere.
     Beyond BASELINE.json's C3: `roughness` != 0 makes the mirror, conductor and dielectric
     materials glossy (random draws inside `trace`, Object+Extension.swift:191-197,210-216,259-265); `aperture` and
     `focus` > 0 give the camera a thin lens (:325-338); `area_lights` (0..3) adds square area lights sampled
-    through the per-chunk jitter index (:145-186) and drops the second point light."""
+    through the per-chunk jitter index (:145-186) and drops the second point light; `inf_light` gives the last light
+    (area light if there is one) an infinite intensity, so every level it reaches hits the non-finite guard (:277-280)."""
     rng = SplitMix64(3)
     pos, tris = icosphere_mesh(ico_level, radius=1.0)
     write_ply(os.path.join(out_dir, "c3_ico.ply"), pos, tris)
@@ -420,6 +421,13 @@ def config_c3(out_dir: str, width: int = 1024, height: int = 1024, samples: int 
         sc.areaLights = [AreaLight((0.5, 9.9, 0.5), (0.0, -1.0, 0.0), 3.0, (1500, 1450, 1300)),
                          AreaLight((-4.9, 5.0, 1.0), (1.0, -0.3, 0.4), 2.0, (900, 1100, 1400)),
                          AreaLight((2.0, 6.0, 4.5), (-0.2, -0.5, -1.0), 1.5, (1200, 800, 600))][:area_lights]
+    if inf_light:
+        inf = (float("inf"),) * 3
+        if area_lights > 0:
+            a = sc.areaLights[-1]
+            sc.areaLights[-1] = AreaLight(a.position, a.normal, a.size, inf)
+        else:
+            sc.pointLights[-1] = PointLight(sc.pointLights[-1].position, inf)
     for m in sc.materials:
         if m.type != MAT_PLAIN:
             m.roughness = roughness

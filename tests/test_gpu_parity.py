@@ -11,7 +11,9 @@ pytestmark = pytest.mark.gpu
 CASES = {
     "c1": dict(fn=scenegen.config_c1, kw=dict()),                                   # full config: 800x800, 1 spp
     "c2": dict(fn=scenegen.config_c2, kw=dict(width=512, height=512)),              # 69,938 triangles
+    "c2full": dict(fn=scenegen.config_c2, kw=dict()),                               # full config: 1024x1024, 1 spp
     "c3": dict(fn=scenegen.config_c3, kw=dict(width=256, height=256, samples=4)),   # depth 6 recursion
+    "c3full": dict(fn=scenegen.config_c3, kw=dict()),                               # full config: 1024x1024, 4 spp, depth 6
     "c4s": dict(fn=scenegen.config_c4, kw=dict(n=260, width=480, height=270, samples=4)),
     "c5s": dict(fn=scenegen.config_c5, kw=dict(n=64, width=320, height=180, samples=4, meshes=4)),
     # SURVEY.md 8f row 3, beyond BASELINE.json's configs: thin-lens camera (fast kernel, 5 draws per sample),
@@ -34,6 +36,10 @@ CASES = {
     "motioninst": dict(fn=scenegen.config_instances, kw=dict(width=200, height=150, samples=9, instance_motion=1.2)),
     "motionboth": dict(fn=scenegen.config_instances, kw=dict(width=243, height=181, samples=4, mesh_motion=(0.4, -0.3, 0.2),
                                                             instance_motion=1.5)),
+    # non-finite guard (a11, :277-280) with every side effect of the discarded children: area-light jitter index, glossy RNG
+    "c3areaglossyinf": dict(fn=scenegen.config_c3, kw=dict(width=120, height=96, samples=4, depth=3, roughness=0.15, area_lights=2,
+                                                          inf_light=True)),
+    "c3inf": dict(fn=scenegen.config_c3, kw=dict(width=120, height=96, samples=4, depth=3, inf_light=True)),
     "c3areaglossy": dict(fn=scenegen.config_c3, kw=dict(width=150, height=117, samples=9, depth=4, roughness=0.2, area_lights=3)),
 }
 
@@ -192,6 +198,44 @@ def test_device_built_bvh_meets_the_parity_bars(name, scene_dir, monkeypatch):
     assert (got.rgba == base.rgba).all(axis=-1).mean() >= 0.9999
 
 
+@pytest.mark.parametrize("name", ["c2", "c3", "c4s", "c5s"])
+def test_device_sah_build_makes_the_host_builders_tree(name, scene_dir, monkeypatch):
+    """rt_scene_desc.buildMode = RT_BUILD_DEVICE_SAH (csrc/bvh_build_sah_gpu.cu): same nodes, boxes and leaves as the
+    host builder — identical box-test count and image — and the parity bars against the oracle."""
+    case = CASES[name]
+    path = case["fn"](scene_dir, **case["kw"])
+    monkeypatch.setenv("RTCUDA_BUILD", "host")
+    host = RayTracerEngine(path)
+    a = host.render(0, want_ids=True, want_linear=True, counters=True)
+    monkeypatch.setenv("RTCUDA_BUILD", "device-sah")
+    dev = RayTracerEngine(path)
+    hi, di = host.scene_info(), dev.scene_info()
+    print(name, "host build ms", hi["buildMs"], "device-sah build ms", di["buildMs"])
+    assert hi["deviceBuiltBlas"] == 0 and di["deviceBuiltBlas"] >= 1
+    for key in ("blasNodes", "maxLeafSize", "maxDepth"):
+        assert hi[key] == di[key], (key, hi, di)
+    assert np.array_equal(host.blas_nodes(), dev.blas_nodes())       # the host builder's node array, byte for byte
+    b = dev.render(0, want_ids=True, want_linear=True, counters=True)
+    assert a.stats["boxTests"] == b.stats["boxTests"]
+    assert np.array_equal(a.rgba, b.rgba)
+    rep = parity.compare(b, oracle_lib.OracleScene(path).render(want_ids=True, want_linear=True))
+    assert rep["id_agree"] >= 0.9999 and rep["id_bad"] == 0, rep
+    assert rep["px_within_1"] >= 0.999, rep
+
+
+def test_c_abi_from_a_plain_c_program_on_the_gpu(scene_dir, tmp_path):
+    """tests/c_driver/driver.c linked against librtcuda.so: engine -> frame -> image file, then the flattened scene
+    straight into rt_scene_create / rt_render; same frame as through ctypes."""
+    from myraytracer_b200 import capi
+    from test_emu_cpu import _c_driver, fnv1a, run_c_driver
+    exe = _c_driver(tmp_path, capi.LIB_PATH)
+    path = scenegen.config_c3(scene_dir, width=160, height=96, samples=4, depth=4, ico_level=2)
+    out = run_c_driver(exe, path, str(tmp_path / "c.png"))
+    want = RayTracerEngine(path).render(0)
+    assert out[3] == "fnv=%016x" % fnv1a(want.rgba.tobytes())
+    assert out[6] == out[3]
+
+
 def test_animation_refit_matches_rebuilt_scenes(scene_dir):
     """rt_scene_update_instances (8f row 4): instance records re-derived and the TLAS refitted by the device kernel,
     topology kept; every frame equals the frame of a scene built from scratch with those transforms and meets the
@@ -247,6 +291,30 @@ def test_edge_cases_vs_oracle(scene_dir):
             rep = parity.compare(got, ref)
             assert rep["id_agree"] >= 0.9999 and rep["id_bad"] == 0 and rep["px_within_1"] >= 0.999, (name, variant, rep)
             assert rep["rays_gpu"] == rep["rays_ref"], (name, variant, rep)
+
+
+@pytest.mark.parametrize("rough,depth,variants", [(0.0, 3, (1, 2)), (0.2, 3, (2,))])
+def test_non_finite_light_level_is_discarded_like_the_reference(rough, depth, variants, tmp_path):
+    """Row a11 on the hardware (Object+Extension.swift:277-280): a point light of infinite intensity makes Lo
+    non-finite at every shading point it reaches; the reference still traces that level's children (their rays, and
+    with glossy materials their RNG draws) and then returns black for the level.  Against the pure-Python restatement
+    of `trace` (tests/reftrace.py) and against the oracle: same colours, same ray counts."""
+    import reftrace
+    from test_oracle_trace_cpu import _build
+    path, ref, cam = _build(str(tmp_path), rough, depth, W=48, H=32, inf_light=True)
+    want, counts = reftrace.render(ref, cam)
+    orc = oracle_lib.OracleScene(path).render(want_ids=True, want_linear=True)
+    eng = RayTracerEngine(path)
+    for variant in variants:
+        got = eng.render(0, want_linear=True, want_ids=True, variant=variant)
+        assert np.isfinite(got.linear).all()
+        err = np.abs(got.linear - want) / np.maximum(1.0, np.abs(want))
+        assert err.max() <= 1e-12, (variant, err.max())
+        assert (got.stats["raysPrimary"], got.stats["raysShadow"], got.stats["raysSecondary"]) == \
+            (counts["primary"], counts["shadow"], counts["secondary"]), variant
+        rep = parity.compare(got, orc)
+        assert rep["id_agree"] >= 0.9999 and rep["id_bad"] == 0 and rep["px_within_1"] >= 0.999, (variant, rep)
+        assert rep["rays_gpu"] == rep["rays_ref"], (variant, rep)
 
 
 def test_error_codes(scene_dir):
