@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 1
+#define RT_ABI_VERSION 2
 
 /* status codes; -10/-20/-21 mirror the reference's NSError codes (RayTracer.swift:121-123,142-154) */
 enum {
@@ -124,8 +124,13 @@ typedef struct rt_camera {
     double apertureSize, focusDistance;
 } rt_camera;
 
-/* progress: rows finished so far (multiples of the 8-row chunk of Object+Extension.swift:75);
- * return non-zero to cancel (RayTracer.swift:178-180) */
+/* progress: rows finished so far (multiples of the 8-row chunk of Object+Extension.swift:75); return non-zero to
+ * cancel (RayTracer.swift:178-180).  Called from the thread that called rt_render, WHILE the frame is in flight, like
+ * ProgressRelay reports finished chunks (Object+Extension.swift:22-41): rt_render reads the kernels' work counter
+ * through a side stream every ~100 us and reports the rows the finished share of the work amounts to (the kernels draw
+ * tiles in cost order, not top to bottom, so "rows" is the reference's unit, not a scanline position).  A non-zero
+ * return stops the frame: the work counter is pushed past its end, every warp exits at its next draw (< 1 ms), and
+ * rt_render returns RT_ERR_CANCELLED with the output buffers undefined. */
 typedef int (*rt_progress_fn)(int32_t rowsDone, int32_t rowsTotal, void* user);
 
 /* rt_scene_desc.buildMode.  The reference builds on the CPU (Accelearion/BVH.swift:78-250); the image does not depend
@@ -195,6 +200,9 @@ typedef struct rt_scene_info {
     double buildMs, uploadMs;
     int32_t device;
     int32_t deviceBuiltBlas;      /* mesh BVHs built by a device builder (RT_BUILD_DEVICE_*) */
+    int32_t deviceCount;          /* GPUs the scene is resident on (rt_scene_create_multi), 1 otherwise */
+    int32_t reserved;
+    double replicateMs;           /* device-to-device copies of the scene onto the other GPUs */
 } rt_scene_info;
 
 typedef struct rt_scene rt_scene_t;
@@ -207,6 +215,24 @@ const char* rt_last_error(void);
  * Replaces what Renderer.init(ctx:) keeps (Object+Extension.swift:13-19).  NULL on failure. */
 rt_scene_t* rt_scene_create(const rt_scene_desc* desc, int32_t device);
 void rt_scene_destroy(rt_scene_t* scene);
+
+/* The same scene resident on several GPUs of this process ("rt_render is blocking, internally
+ * asynchronous on CUDA streams across all selected GPUs"; 8e).  The acceleration structures are built ONCE and uploaded
+ * to devices[0]; the other GPUs receive device-to-device copies (NVLink peer copies), nothing is rebuilt.  rt_render on
+ * such a handle deals the frame's 8-row chunks (Object+Extension.swift:75-82) round-robin to the GPUs, runs every
+ * GPU's kernel on its own stream from its own host thread, and every GPU copies ITS rows straight into the caller's
+ * host buffers over its own PCIe link; no collective, no gather through one GPU.  rt_scene_update_instances updates
+ * every replica.  rt_render_device / rt_render_finish address devices[0] only.  NULL on failure. */
+rt_scene_t* rt_scene_create_multi(const rt_scene_desc* desc, const int32_t* devices, int32_t nDevices);
+int32_t rt_scene_device_count(const rt_scene_t* scene);
+
+/* Page-locked host memory for rt_render's output buffers (optional): every GPU of a multi-device scene then writes its
+ * rows by asynchronous DMA; pageable buffers work too, through the driver's staging.  Swift side:
+ * UnsafeMutableRawPointer, freed with rt_host_free (like the caller-owned buffers of ply_reader_extract_properties,
+ * Sources/CPly/include/PLYReaderWrapper.h:49-53, but allocated by the module). */
+void* rt_host_alloc(uint64_t bytes);
+void rt_host_free(void* p);
+
 int32_t rt_scene_get_info(const rt_scene_t* scene, rt_scene_info* out);
 /* Animation: new placements for the instances of a resident scene.  Replaces
  * RTContext.refitTLAS (Models/RTContext.swift:883-928) + BVHBuilder.refit (Accelearion/BVH.swift:254-292): `instances`
@@ -230,7 +256,9 @@ int64_t rt_scene_get_schedule(rt_scene_t* scene, int32_t* orderOut, int64_t capa
  * min(size, capacityBytes).  No reference analogue; for tests (the builders of rt_scene_desc.buildMode compared). */
 int64_t rt_scene_read_blas_nodes(rt_scene_t* scene, void* nodesOut, int64_t capacityBytes);
 
-/* Render one camera.  Blocking.  Host buffers, all optional except one of rgbaOut/linearOut:
+/* Render one camera.  Blocking; one render at a time per scene handle (not re-entrant), different scenes may render
+ * from different host threads at once (each scene has its own non-blocking stream).  Host buffers, all optional
+ * except one of rgbaOut/linearOut:
  *   rgbaOut   width*height*4 bytes, row 0 = top (RayTracer.swift:186-195)
  *   linearOut width*height*3 doubles, the [Vec3] Renderer.render returns (0..255 scale)
  *   idsOut    width*height*n*n records, n = floor(sqrt(max(1,numSamples)))

@@ -21,6 +21,8 @@ const char* rth_last_error(void);
 /* RayTracerEngine.init(from:) — RayTracer.swift:30-49.  Never NULL unless out of memory: like the
  * reference, a scene that fails to decode leaves an empty engine (rth_engine_ready() == 0). */
 rth_engine_t* rth_engine_create(const char* sceneUrl, int32_t device);
+/* The same engine with its scene resident on several GPUs (rt_scene_create_multi): render() shards every frame. */
+rth_engine_t* rth_engine_create_multi(const char* sceneUrl, const int32_t* devices, int32_t nDevices);
 void rth_engine_destroy(rth_engine_t* engine);
 int32_t rth_engine_ready(const rth_engine_t* engine);
 int32_t rth_engine_camera_count(const rth_engine_t* engine);

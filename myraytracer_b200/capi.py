@@ -13,7 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 # RTCUDA_LIB: developer override to A/B kernel build variants (always a CUDA build of this same source)
 LIB_PATH = os.environ.get("RTCUDA_LIB") or os.path.join(HERE, "librtcuda.so")
 
-RT_ABI_VERSION = 1
+RT_ABI_VERSION = 2
 RT_IPC_HANDLE_BYTES = 64
 RT_OK, RT_ERR_INVALID, RT_ERR_CUDA, RT_ERR_UNSUPPORTED, RT_ERR_CANCELLED = 0, -1, -2, -3, -4
 RT_ERR_BAD_CAMERA, RT_ERR_NO_SCENE, RT_ERR_NO_RENDERER = -10, -20, -21
@@ -107,7 +107,8 @@ class rt_stats(C.Structure):
 class rt_scene_info(C.Structure):
     _fields_ = [(n, C.c_int64) for n in ("triangles", "spheres", "planes", "instances", "blasCount", "blasNodes",
                                          "tlasNodes", "maxLeafSize", "maxDepth", "deviceBytes")]
-    _fields_ += [("buildMs", C.c_double), ("uploadMs", C.c_double), ("device", C.c_int32), ("deviceBuiltBlas", C.c_int32)]
+    _fields_ += [("buildMs", C.c_double), ("uploadMs", C.c_double), ("device", C.c_int32), ("deviceBuiltBlas", C.c_int32),
+                 ("deviceCount", C.c_int32), ("reserved", C.c_int32), ("replicateMs", C.c_double)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -117,6 +118,7 @@ HIT_ID_DTYPE = np.dtype([("inst", "<i4"), ("kind", "<i4"), ("prim", "<i8"), ("t"
 
 # every symbol include/rtcuda.h and include/rtcuda_host.h declare
 EXPORTS = ["rt_abi_version", "rt_device_count", "rt_last_error", "rt_scene_create", "rt_scene_destroy",
+           "rt_scene_create_multi", "rt_scene_device_count", "rt_host_alloc", "rt_host_free", "rth_engine_create_multi",
            "rt_scene_get_info", "rt_scene_get_schedule", "rt_scene_read_blas_nodes", "rt_scene_update_instances", "rt_ply_ingest", "rt_render", "rt_render_device", "rt_render_finish",
            "rt_shared_buffer_create", "rt_shared_buffer_open", "rt_shared_buffer_close",
            "rth_last_error", "rth_engine_create", "rth_engine_destroy", "rth_engine_ready", "rth_engine_camera_count",
@@ -147,6 +149,15 @@ def declare(L):
     L.rt_last_error.restype = C.c_char_p
     L.rt_scene_create.restype = vp
     L.rt_scene_create.argtypes = [C.POINTER(rt_scene_desc), C.c_int32]
+    L.rt_scene_create_multi.restype = vp
+    L.rt_scene_create_multi.argtypes = [C.POINTER(rt_scene_desc), C.POINTER(C.c_int32), C.c_int32]
+    L.rt_scene_device_count.argtypes = [vp]
+    L.rt_host_alloc.restype = vp
+    L.rt_host_alloc.argtypes = [C.c_uint64]
+    L.rt_host_free.argtypes = [vp]
+    L.rt_host_free.restype = None
+    L.rth_engine_create_multi.restype = vp
+    L.rth_engine_create_multi.argtypes = [C.c_char_p, C.POINTER(C.c_int32), C.c_int32]
     L.rt_scene_destroy.argtypes = [vp]
     L.rt_scene_destroy.restype = None
     L.rt_scene_get_info.argtypes = [vp, C.POINTER(rt_scene_info)]

@@ -11,7 +11,11 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/rtcuda.h"
@@ -39,13 +43,18 @@ int fail(int code, const std::string& msg) { g_err = msg; return code; }
         }                                                                                              \
     } while (0)
 
+// One device array of a scene: where its pointer lives inside rt_scene (byte offset) and its size — what
+// rt_scene_create_multi needs to replicate the scene on another GPU by device-to-device copies.
+struct SceneArray { size_t slotOffset, bytes; };
+
 template <class T>
-int upload(const std::vector<T>& v, T** d, int64_t& bytes) {
+int upload(const std::vector<T>& v, T** d, int64_t& bytes, std::vector<SceneArray>* reg = nullptr, const void* owner = nullptr) {
     *d = nullptr;
     size_t n = v.size() * sizeof(T);
     CK(cudaMalloc((void**)d, n ? n : 16));
     if (n) CK(cudaMemcpy(*d, v.data(), n, cudaMemcpyHostToDevice));
     bytes += (int64_t)n;
+    if (reg) reg->push_back(SceneArray{(size_t)((const char*)d - (const char*)owner), n ? n : 16});
     return RT_OK;
 }
 
@@ -74,9 +83,36 @@ struct BlasInfo {
     double payload[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // sphere c.xyz, r | plane c.xyz, n.xyz
 };
 
+// Worker threads of a multi-device scene: one per replica; run(job) executes job(replica index) on all of them.
+struct ReplicaPool {
+    std::vector<std::thread> threads;
+    std::mutex m;
+    std::condition_variable cvStart, cvDone;
+    std::function<int(int)> job;
+    std::vector<int> rc;
+    std::vector<std::string> err;
+    int generation = 0, remaining = 0;
+    bool quit = false;
+    void start(int n);
+    void launch(std::function<int(int)> j);     // returns at once; wait() joins the generation
+    void wait();
+    ~ReplicaPool();
+};
+
 struct rt_scene {
     int device = 0;
     DeviceScene ds{};
+    std::vector<SceneArray> arrays;    // every device array of the scene (what a replica copies)
+    // multi-device scenes (rt_scene_create_multi): replicas[0] == this, the others own a copy of the scene on their GPU
+    std::vector<rt_scene*> replicas;
+    ReplicaPool* pool = nullptr;
+    bool isReplica = false;
+    // rt_render's own streams: the frame (non-blocking, so scenes rendered from different host threads do not
+    // serialise on the legacy default stream) and the progress / cancel side channel
+    cudaStream_t stream = nullptr, poll = nullptr;
+    cudaEvent_t evReset = nullptr;     // the frame's counters have been zeroed: the work counter may be polled
+    int* hPoll = nullptr;              // pinned: [0] work counter read back, [1] the value that cancels a frame
+    int64_t pendingUnits = 0, pendingWarps = 0;   // work units of the frame in flight / warps drawing them
     rt_scene_info info{};
     int64_t meshes = 0;
     // device allocations
@@ -158,6 +194,40 @@ static double tlasFrame(const TNode& r, double* sLo, double* sHi, double* sC) {
     return std::fmax(M * std::ldexp(1.0, -19), 1e-30);
 }
 
+// Per-device state that is not scene data: frame counters, events, streams, pinned staging (a replica gets its own).
+static int allocFrameState(rt_scene* sc, size_t nInstances) {
+    const size_t n = nInstances ? nInstances : 1;
+    CK(cudaMallocHost((void**)&sc->hInst, n * sizeof(GInstance)));
+    CK(cudaMallocHost((void**)&sc->hInstBounds, n * 6 * sizeof(double)));
+    CK(cudaMallocHost((void**)&sc->hDerive, n * sizeof(int32_t)));
+    CK(cudaMallocHost((void**)&sc->hBoundsEnc, n * 6 * sizeof(unsigned long long)));
+    CK(cudaMalloc((void**)&sc->dDerive, n * sizeof(int32_t)));
+    CK(cudaMalloc((void**)&sc->dBoundsEnc, n * 6 * sizeof(unsigned long long)));
+    // ray / test counters (16 x u64) and the work counter behind them: one allocation, one memset per frame
+    CK(cudaMalloc((void**)&sc->dCounters, kFrameStateBytes));
+    sc->dTileCounter = reinterpret_cast<int*>(sc->dCounters + 16);
+    CK(cudaMallocHost((void**)&sc->hCounters, 16 * sizeof(unsigned long long)));
+    CK(cudaMallocHost((void**)&sc->hPoll, 2 * sizeof(int)));
+    sc->hPoll[0] = 0; sc->hPoll[1] = 1 << 30;
+    CK(cudaEventCreate(&sc->evStart));
+    CK(cudaEventCreate(&sc->evStop));
+    CK(cudaEventCreateWithFlags(&sc->evSide, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&sc->evReset, cudaEventDisableTiming));
+    CK(cudaStreamCreateWithFlags(&sc->side, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&sc->stream, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&sc->poll, cudaStreamNonBlocking));
+    return RT_OK;
+}
+
+// The pointers of DeviceScene are the scene's own device arrays (again after a replica copied them).
+static void bindDeviceScene(rt_scene* sc) {
+    DeviceScene& S = sc->ds;
+    S.nodes = sc->dNodes; S.tris = sc->dTris; S.trisD = sc->dTrisD; S.triNormals = sc->dNormals; S.triVertsD = nullptr;
+    S.tlas = sc->dTlas; S.instances = sc->dInst; S.materials = sc->dMat; S.pointLights = sc->dLights;
+    S.areaLights = sc->dAreaLights; S.jitter = sc->dJitter;
+    S.refTlas = sc->dRefTlas; S.refTlasPrim = sc->dRefTlasPrim;
+}
+
 extern "C" {
 
 int32_t rt_abi_version(void) { return RT_ABI_VERSION; }
@@ -175,6 +245,17 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     if (d->abiVersion != RT_ABI_VERSION) return fail(RT_ERR_INVALID, "rt_scene_desc.abiVersion mismatch");
     if (d->nMaterials < 1 || !d->materials) return fail(RT_ERR_INVALID, "at least one material is required");
     if (d->nAreaLights < 0 || (d->nAreaLights > 0 && !d->areaLights)) return fail(RT_ERR_INVALID, "area light array missing");
+    // every count non-negative, every array present when its count is not zero — before anything is dereferenced
+    if (d->nTriangles < 0 || d->nSpheres < 0 || d->nPlanes < 0 || d->nPrims < 0 || d->nBlas < 0 || d->nInstances < 0 || d->nPointLights < 0)
+        return fail(RT_ERR_INVALID, "negative element count in rt_scene_desc");
+    if (d->nTriangles > 0 && (!d->triVertices || !d->triNormals)) return fail(RT_ERR_INVALID, "triangle arrays missing");
+    if (d->nSpheres > 0 && !d->spheres) return fail(RT_ERR_INVALID, "sphere array missing");
+    if (d->nPlanes > 0 && !d->planes) return fail(RT_ERR_INVALID, "plane array missing");
+    if (d->nPrims > 0 && !d->prims) return fail(RT_ERR_INVALID, "prim array missing");
+    if (d->nBlas > 0 && !d->blas) return fail(RT_ERR_INVALID, "blas array missing");
+    if (d->nInstances > 0 && !d->instances) return fail(RT_ERR_INVALID, "instance array missing");
+    if (d->nPointLights > 0 && !d->pointLights) return fail(RT_ERR_INVALID, "point light array missing");
+    if (d->maxRecursionDepth < 0 || d->maxRecursionDepth > 64) return fail(RT_ERR_INVALID, "maxRecursionDepth outside 0..64");
     int ndev = 0;
     CK(cudaGetDeviceCount(&ndev));
     if (device < 0 || device >= ndev) return fail(RT_ERR_INVALID, "invalid CUDA device index");
@@ -354,19 +435,16 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
             }
     }
     std::vector<double> normals;
-    if (d->nTriangles > 0) {
-        if (!d->triVertices || !d->triNormals) return fail(RT_ERR_INVALID, "triangle arrays missing");
-        normals.assign(d->triNormals, d->triNormals + d->nTriangles * 9);
-    }
+    if (d->nTriangles > 0) normals.assign(d->triNormals, d->triNormals + d->nTriangles * 9);
     const double t1 = nowMs();
 
     // ---- upload
     int64_t bytes = 0;
     int rc;
-    if ((rc = upload(nodes, &sc->dNodes, bytes))) return rc;
-    if ((rc = upload(tris, &sc->dTris, bytes))) return rc;
-    if ((rc = upload(trisD, &sc->dTrisD, bytes))) return rc;
-    if ((rc = upload(normals, &sc->dNormals, bytes))) return rc;
+    if ((rc = upload(nodes, &sc->dNodes, bytes, &sc->arrays, sc))) return rc;
+    if ((rc = upload(tris, &sc->dTris, bytes, &sc->arrays, sc))) return rc;
+    if ((rc = upload(trisD, &sc->dTrisD, bytes, &sc->arrays, sc))) return rc;
+    if ((rc = upload(normals, &sc->dNormals, bytes, &sc->arrays, sc))) return rc;
     // TLAS records: the BLAS node format — FP32 boxes relative to the centre of the scene bounds, padded by
     // M * 2^-19 and rounded outward (conservative: the instance's own exact test decides)
     std::vector<GNode> tlasF(tl.nodes.size());
@@ -405,55 +483,40 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
             for (size_t i = 0; i < tl.nodes.size(); i++) if (depth[i] == lv) order[k++] = (int)i;
             sc->refitLevelStart.push_back((int)k);
         }
-        if ((rc = upload(tl.nodes, &sc->dTlasD, bytes))) return rc;
-        if ((rc = upload(order, &sc->dRefitOrder, bytes))) return rc;
-        if ((rc = upload(sc->refitLevelStart, &sc->dRefitLevelStart, bytes))) return rc;
-        if ((rc = upload(wb, &sc->dInstBounds, bytes))) return rc;
-        const size_t n = (size_t)d->nInstances;
-        CK(cudaMallocHost((void**)&sc->hInst, (n ? n : 1) * sizeof(GInstance)));
-        CK(cudaMallocHost((void**)&sc->hInstBounds, (n ? n : 1) * 6 * sizeof(double)));
-        CK(cudaMallocHost((void**)&sc->hDerive, (n ? n : 1) * sizeof(int32_t)));
-        CK(cudaMallocHost((void**)&sc->hBoundsEnc, (n ? n : 1) * 6 * sizeof(unsigned long long)));
-        CK(cudaMalloc((void**)&sc->dDerive, (n ? n : 1) * sizeof(int32_t)));
-        CK(cudaMalloc((void**)&sc->dBoundsEnc, (n ? n : 1) * 6 * sizeof(unsigned long long)));
+        if ((rc = upload(tl.nodes, &sc->dTlasD, bytes, &sc->arrays, sc))) return rc;
+        if ((rc = upload(order, &sc->dRefitOrder, bytes, &sc->arrays, sc))) return rc;
+        if ((rc = upload(sc->refitLevelStart, &sc->dRefitLevelStart, bytes, &sc->arrays, sc))) return rc;
+        if ((rc = upload(wb, &sc->dInstBounds, bytes, &sc->arrays, sc))) return rc;
         std::vector<BoundsChunk> chunks;                      // 4096 triangles per block of the bounds kernel
-        for (size_t i = 0; i < n; i++) {
+        for (size_t i = 0; i < (size_t)d->nInstances; i++) {
             const BlasInfo& bi = blasInfo[sc->instBlas[i]];
             if (bi.kind != INST_MESH) continue;
             for (int64_t f = 0; f < bi.triCount; f += 4096)
                 chunks.push_back(BoundsChunk{(int32_t)i, (int32_t)(bi.triBase + f), (int32_t)std::min<int64_t>(4096, bi.triCount - f), bi.f64});
         }
         sc->nBoundChunks = (int)chunks.size();
-        if ((rc = upload(chunks, &sc->dBoundChunks, bytes))) return rc;
+        if ((rc = upload(chunks, &sc->dBoundChunks, bytes, &sc->arrays, sc))) return rc;
         sc->instanceMotion = instanceMotion;
     }
-    if ((rc = upload(tlasF, &sc->dTlas, bytes))) return rc;
-    if ((rc = upload(inst, &sc->dInst, bytes))) return rc;
-    if ((rc = upload(mats, &sc->dMat, bytes))) return rc;
-    if ((rc = upload(lights, &sc->dLights, bytes))) return rc;
-    if ((rc = upload(areaLights, &sc->dAreaLights, bytes))) return rc;
-    if ((rc = upload(jitter, &sc->dJitter, bytes))) return rc;
-    if ((rc = upload(refTl.nodes, &sc->dRefTlas, bytes))) return rc;
-    if ((rc = upload(refTl.primIdx, &sc->dRefTlasPrim, bytes))) return rc;
-    // ray / test counters (16 x u64) and the work counter behind them: one allocation, one memset per frame
-    CK(cudaMalloc((void**)&sc->dCounters, kFrameStateBytes));
-    sc->dTileCounter = reinterpret_cast<int*>(sc->dCounters + 16);
-    CK(cudaMallocHost((void**)&sc->hCounters, 16 * sizeof(unsigned long long)));
-    CK(cudaEventCreate(&sc->evStart));
-    CK(cudaEventCreate(&sc->evStop));
-    CK(cudaEventCreateWithFlags(&sc->evSide, cudaEventDisableTiming));
-    CK(cudaStreamCreateWithFlags(&sc->side, cudaStreamNonBlocking));
+    if ((rc = upload(tlasF, &sc->dTlas, bytes, &sc->arrays, sc))) return rc;
+    if ((rc = upload(inst, &sc->dInst, bytes, &sc->arrays, sc))) return rc;
+    if ((rc = upload(mats, &sc->dMat, bytes, &sc->arrays, sc))) return rc;
+    if ((rc = upload(lights, &sc->dLights, bytes, &sc->arrays, sc))) return rc;
+    if ((rc = upload(areaLights, &sc->dAreaLights, bytes, &sc->arrays, sc))) return rc;
+    if ((rc = upload(jitter, &sc->dJitter, bytes, &sc->arrays, sc))) return rc;
+    if ((rc = upload(refTl.nodes, &sc->dRefTlas, bytes, &sc->arrays, sc))) return rc;
+    if ((rc = upload(refTl.primIdx, &sc->dRefTlasPrim, bytes, &sc->arrays, sc))) return rc;
+    if ((rc = allocFrameState(sc, (size_t)d->nInstances))) return rc;
     CK(cudaDeviceSynchronize());
     const double t2 = nowMs();
 
     DeviceScene& S = sc->ds;
-    S.nodes = sc->dNodes; S.tris = sc->dTris; S.trisD = sc->dTrisD; S.triNormals = sc->dNormals; S.triVertsD = nullptr;
-    S.tlas = sc->dTlas; S.instances = sc->dInst; S.materials = sc->dMat; S.pointLights = sc->dLights;
+    bindDeviceScene(sc);
     S.tlasRootRef = tl.rootRef;
     std::memcpy(S.tlasLo, sLo, 24); std::memcpy(S.tlasHi, sHi, 24); std::memcpy(S.tlasCentre, sC, 24);
     S.nInstances = (int32_t)d->nInstances; S.nMaterials = (int32_t)d->nMaterials; S.nPointLights = (int32_t)d->nPointLights;
-    S.areaLights = sc->dAreaLights; S.jitter = sc->dJitter; S.nAreaLights = (int32_t)d->nAreaLights;
-    S.refTlas = sc->dRefTlas; S.refTlasPrim = sc->dRefTlasPrim; S.refTlasNodes = (int32_t)refTl.nodes.size();
+    S.nAreaLights = (int32_t)d->nAreaLights;
+    S.refTlasNodes = (int32_t)refTl.nodes.size();
     S.maxDepth = d->maxRecursionDepth;
     std::memcpy(S.ambient, d->ambient, 24); std::memcpy(S.background, d->background, 24);
     // a scene without instances has no TLAS, and `trace` then returns .zero, not the background
@@ -479,7 +542,15 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
 
 void rt_scene_destroy(rt_scene_t* sc) {
     if (!sc) return;
+    if (!sc->isReplica) {
+        delete sc->pool;                                  // joins the worker threads
+        sc->pool = nullptr;
+        for (size_t r = 1; r < sc->replicas.size(); r++) rt_scene_destroy(sc->replicas[r]);
+        sc->replicas.clear();
+    }
     cudaSetDevice(sc->device);
+    if (sc->stream) cudaStreamSynchronize(sc->stream);
+    if (sc->side) cudaStreamSynchronize(sc->side);
     cudaFree(sc->dNodes); cudaFree(sc->dTris); cudaFree(sc->dTrisD); cudaFree(sc->dNormals); cudaFree(sc->dTlas);
     cudaFree(sc->dInst); cudaFree(sc->dMat); cudaFree(sc->dLights); cudaFree(sc->dCounters);
     cudaFree(sc->dAreaLights); cudaFree(sc->dJitter); cudaFree(sc->dAreaIndex);
@@ -493,10 +564,14 @@ void rt_scene_destroy(rt_scene_t* sc) {
     cudaFree(sc->dTileCost); cudaFree(sc->dTileOrder); cudaFree(sc->dSchedWork);
     cudaFree(sc->dPathStack); cudaFree(sc->dRgba); cudaFree(sc->dLinear); cudaFree(sc->dIds);
     if (sc->hCounters) cudaFreeHost(sc->hCounters);
+    if (sc->hPoll) cudaFreeHost(sc->hPoll);
     if (sc->evStart) cudaEventDestroy(sc->evStart);
     if (sc->evStop) cudaEventDestroy(sc->evStop);
     if (sc->evSide) cudaEventDestroy(sc->evSide);
-    if (sc->side) { cudaStreamSynchronize(sc->side); cudaStreamDestroy(sc->side); }
+    if (sc->evReset) cudaEventDestroy(sc->evReset);
+    if (sc->side) cudaStreamDestroy(sc->side);
+    if (sc->stream) cudaStreamDestroy(sc->stream);
+    if (sc->poll) cudaStreamDestroy(sc->poll);
     delete sc;
 }
 
@@ -506,6 +581,7 @@ rt_scene_t* rt_scene_create(const rt_scene_desc* desc, int32_t device) {
         sc = new rt_scene();
         int rc = createImpl(desc, device, sc);
         if (rc != RT_OK) { rt_scene_destroy(sc); return nullptr; }
+        sc->replicas.assign(1, sc);
         return sc;
     } catch (const std::exception& e) {
         g_err = e.what();
@@ -516,7 +592,140 @@ rt_scene_t* rt_scene_create(const rt_scene_desc* desc, int32_t device) {
     return nullptr;
 }
 
+// A copy of `src` on another GPU of this process: the scene's device arrays travel device to device (NVLink peer copy),
+// nothing is rebuilt or re-uploaded from the host; frame state (counters, streams, events, staging) is the replica's own.
+static int cloneScene(const rt_scene* src, int device, rt_scene* dst) {
+    dst->device = device;
+    dst->isReplica = true;
+    dst->ds = src->ds; dst->info = src->info; dst->info.device = device; dst->meshes = src->meshes;
+    dst->motion = src->motion; dst->glossy = src->glossy; dst->instanceMotion = src->instanceMotion;
+    dst->blasInfo = src->blasInfo; dst->instBlas = src->instBlas; dst->refitLevelStart = src->refitLevelStart;
+    dst->nBoundChunks = src->nBoundChunks;
+    dst->arrays = src->arrays;
+    CK(cudaSetDevice(device));
+    int can = 0;
+    CK(cudaDeviceCanAccessPeer(&can, device, src->device));
+    if (can) { cudaError_t e = cudaDeviceEnablePeerAccess(src->device, 0); if (e != cudaSuccess) cudaGetLastError(); }
+    for (const SceneArray& a : src->arrays) {
+        void* const from = *reinterpret_cast<void* const*>(reinterpret_cast<const char*>(src) + a.slotOffset);
+        void** to = reinterpret_cast<void**>(reinterpret_cast<char*>(dst) + a.slotOffset);
+        CK(cudaMalloc(to, a.bytes));
+        CK(cudaMemcpyPeerAsync(*to, device, from, src->device, a.bytes, nullptr));
+    }
+    int rc = allocFrameState(dst, dst->instBlas.size());
+    if (rc) return rc;
+    bindDeviceScene(dst);
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    for (int v = 0; v < KV_COUNT; v++)
+        for (int c = 0; c < 2; c++) {
+            int bps = 0;
+            CK(renderOccupancy(v, &bps, c != 0));
+            dst->blocks[v][c] = prop.multiProcessorCount * (bps > 0 ? bps : 1);
+        }
+    CK(cudaDeviceSynchronize());
+    return RT_OK;
+}
+
+rt_scene_t* rt_scene_create_multi(const rt_scene_desc* desc, const int32_t* devices, int32_t nDevices) {
+    if (!devices || nDevices < 1 || nDevices > 64) { fail(RT_ERR_INVALID, "rt_scene_create_multi: 1..64 devices are required"); return nullptr; }
+    for (int a = 0; a < nDevices; a++)
+        for (int b = a + 1; b < nDevices; b++)
+            if (devices[a] == devices[b]) { fail(RT_ERR_INVALID, "rt_scene_create_multi: a device is listed twice"); return nullptr; }
+    rt_scene* sc = rt_scene_create(desc, devices[0]);
+    if (!sc || nDevices == 1) return sc;
+    try {
+        const double t0 = nowMs();
+        int ndev = 0;
+        if (cudaGetDeviceCount(&ndev) != cudaSuccess) ndev = 0;
+        for (int k = 1; k < nDevices; k++) {
+            if (devices[k] < 0 || devices[k] >= ndev) { fail(RT_ERR_INVALID, "invalid CUDA device index"); rt_scene_destroy(sc); return nullptr; }
+            rt_scene* rep = new rt_scene();
+            sc->replicas.push_back(rep);                  // owned from here on: rt_scene_destroy(sc) frees it
+            if (cloneScene(sc, devices[k], rep) != RT_OK) { rt_scene_destroy(sc); return nullptr; }
+        }
+        sc->info.replicateMs = nowMs() - t0;
+        sc->info.deviceCount = nDevices;
+        sc->pool = new ReplicaPool();
+        sc->pool->start(nDevices);
+        cudaSetDevice(sc->device);
+        return sc;
+    } catch (const std::exception& e) {
+        g_err = e.what();
+    } catch (...) {
+        g_err = "unknown exception";
+    }
+    rt_scene_destroy(sc);
+    return nullptr;
+}
+
+int32_t rt_scene_device_count(const rt_scene_t* sc) { return sc ? (int32_t)sc->replicas.size() : 0; }
+
+void* rt_host_alloc(uint64_t bytes) {
+    void* p = nullptr;
+    if (bytes == 0 || cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); g_err = "rt_host_alloc: cudaHostAlloc failed"; return nullptr; }
+    return p;
+}
+void rt_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+static int updateInstancesOne(rt_scene_t* sc, rt_instance* instances, int64_t nInstances, void* cudaStream);
+
 int32_t rt_scene_update_instances(rt_scene_t* sc, rt_instance* instances, int64_t nInstances, void* cudaStream) {
+    if (!sc) return fail(RT_ERR_NO_SCENE, "No scene loaded. Can't render.");
+    int rc = updateInstancesOne(sc, instances, nInstances, cudaStream);
+    // replicas: the same records and the same refit on their own GPU (their own stream: `cudaStream` belongs to device 0)
+    for (size_t r = 1; r < sc->replicas.size() && rc == RT_OK; r++) rc = updateInstancesOne(sc->replicas[r], instances, nInstances, nullptr);
+    if (sc->replicas.size() > 1) cudaSetDevice(sc->device);
+    return rc;
+}
+
+}  // extern "C"
+
+void ReplicaPool::start(int n) {
+    rc.assign((size_t)n, 0); err.assign((size_t)n, std::string());
+    for (int i = 0; i < n; i++)
+        threads.emplace_back([this, i]() {
+            int seen = 0;
+            for (;;) {
+                std::function<int(int)> j;
+                {
+                    std::unique_lock<std::mutex> lk(m);
+                    cvStart.wait(lk, [&] { return quit || generation != seen; });
+                    if (quit) return;
+                    seen = generation;
+                    j = job;
+                }
+                int r;
+                try { r = j(i); } catch (...) { r = RT_ERR_CUDA; g_err = "exception in a replica worker"; }
+                {
+                    std::lock_guard<std::mutex> lk(m);
+                    rc[(size_t)i] = r;
+                    if (r != RT_OK) err[(size_t)i] = g_err;      // g_err is thread-local: hand the message to the caller's thread
+                    if (--remaining == 0) cvDone.notify_all();
+                }
+            }
+        });
+}
+void ReplicaPool::launch(std::function<int(int)> j) {
+    std::lock_guard<std::mutex> lk(m);
+    job = std::move(j);
+    remaining = (int)threads.size();
+    generation++;
+    cvStart.notify_all();
+}
+void ReplicaPool::wait() {
+    std::unique_lock<std::mutex> lk(m);
+    cvDone.wait(lk, [&] { return remaining == 0; });
+}
+ReplicaPool::~ReplicaPool() {
+    { std::lock_guard<std::mutex> lk(m); quit = true; }
+    cvStart.notify_all();
+    for (std::thread& t : threads) if (t.joinable()) t.join();
+}
+
+extern "C" {
+
+static int updateInstancesOne(rt_scene_t* sc, rt_instance* instances, int64_t nInstances, void* cudaStream) {
     if (!sc) return fail(RT_ERR_NO_SCENE, "No scene loaded. Can't render.");
     if (sc->pending) return fail(RT_ERR_INVALID, "a render is in flight on this scene (call rt_render_finish)");
     if (!instances || nInstances != (int64_t)sc->instBlas.size())

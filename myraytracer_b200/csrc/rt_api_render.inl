@@ -156,6 +156,14 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     if (sc->sideBusy) CK(cudaStreamWaitEvent(st, sc->evSide, 0));
     CK(cudaEventRecord(sc->evStart, st));
     CK(cudaMemsetAsync(sc->dCounters, 0, kFrameStateBytes, st));
+    CK(cudaEventRecord(sc->evReset, st));
+    {   // what the work counter counts up to (progress / cancel of rt_render): see the kernels' unit rules
+        const int ns = cp.n * cp.n;
+        int unitsPerTile = 1;
+        if (variant == KV_FAST) unitsPerTile = (ns < 32 && 32 % ns == 0) ? ns : (ns % 32 == 0 ? 32 : 1);
+        sc->pendingUnits = (int64_t)nTiles * unitsPerTile * (area ? 2 : 1);
+        sc->pendingWarps = (int64_t)(threads / 32);
+    }
     if (area) {
         // pass 1 follows every path and counts its jitter-table draws per pixel; the prefix kernel turns the counts
         // into each pixel's first index within its chunk; pass 2 (below) is the frame
@@ -217,41 +225,174 @@ int32_t rt_render_finish(rt_scene_t* sc, rt_stats* st) {
     return RT_OK;
 }
 
+// ---- rt_render: one frame into host buffers, on the scene's own stream(s) ------------------------------------------
+
+namespace {
+
+struct FrameShape { size_t W, H, nn, chunks; };
+
+// Device -> host copy of the rows replica r of N renders: its 8-row chunks c = r, r + N, ... are one strided 2-D copy
+// (pitch = N chunks) plus, when the image's last chunk is ragged and belongs to r, one copy of that chunk's rows.
+int copyOwnedRows(void* host, const void* dev, size_t rowBytes, const FrameShape& f, int r, int N, cudaStream_t st) {
+    if (N <= 1) { CK(cudaMemcpyAsync(host, dev, rowBytes * f.H, cudaMemcpyDeviceToHost, st)); return RT_OK; }
+    const size_t chunkBytes = rowBytes * 8, pitch = chunkBytes * (size_t)N;
+    const size_t fullChunks = f.H / 8;                                   // chunks with all 8 rows
+    const size_t mineFull = (size_t)r < fullChunks ? (fullChunks - (size_t)r + (size_t)N - 1) / (size_t)N : 0;
+    char* h = (char*)host + chunkBytes * (size_t)r;
+    const char* d = (const char*)dev + chunkBytes * (size_t)r;
+    if (mineFull > 0) CK(cudaMemcpy2DAsync(h, pitch, d, pitch, chunkBytes, mineFull, cudaMemcpyDeviceToHost, st));
+    if (f.chunks > fullChunks && (int)(fullChunks % (size_t)N) == r)       // the ragged last chunk is this replica's
+        CK(cudaMemcpyAsync((char*)host + chunkBytes * fullChunks, (const char*)dev + chunkBytes * fullChunks,
+                           rowBytes * (f.H - fullChunks * 8), cudaMemcpyDeviceToHost, st));
+    return RT_OK;
+}
+
+// Everything one GPU does for a frame of rt_render: buffers, launch, copies of its rows.  Enqueues only.
+int enqueueFrame(rt_scene* rep, int r, int N, const rt_camera* camera, const rt_render_params* params, const FrameShape& f,
+                 uint8_t* rgbaOut, double* linearOut, rt_hit_id* idsOut) {
+    CK(cudaSetDevice(rep->device));
+    int rc;
+    if (rgbaOut && (rc = ensure(&rep->dRgba, &rep->rgbaBytes, f.W * f.H * 4))) return rc;
+    if (linearOut && (rc = ensure(&rep->dLinear, &rep->linearBytes, f.W * f.H * 3 * sizeof(double)))) return rc;
+    if (idsOut && (rc = ensure(&rep->dIds, &rep->idsBytes, f.W * f.H * f.nn * sizeof(HitId)))) return rc;
+    rt_render_params prm{};
+    if (params) prm = *params;
+    if (N > 1) { prm.shardIndex = r; prm.shardCount = N; prm.shardMode = RT_SHARD_ROWS; }
+    // rows outside the caller's own shard (multi-process sharding) are defined as zero in the host buffers
+    if (N == 1 && prm.shardCount > 1) {
+        if (rgbaOut) CK(cudaMemsetAsync(rep->dRgba, 0, f.W * f.H * 4, rep->stream));
+        if (linearOut) CK(cudaMemsetAsync(rep->dLinear, 0, f.W * f.H * 3 * sizeof(double), rep->stream));
+        if (idsOut) CK(cudaMemsetAsync(rep->dIds, 0, f.W * f.H * f.nn * sizeof(HitId), rep->stream));
+    }
+    rc = rt_render_device(rep, camera, &prm, rgbaOut ? rep->dRgba : nullptr, linearOut ? rep->dLinear : nullptr,
+                          idsOut ? rep->dIds : nullptr, rep->stream);
+    if (rc) return rc;
+    cudaError_t ce = cudaSuccess;       // a failed copy must not leave the frame "in flight" on the handle
+    auto copy = [&](void* h, const void* d, size_t rowBytes) {
+        if (!h || ce != cudaSuccess) return;
+        if (copyOwnedRows(h, d, rowBytes, f, r, N, rep->stream) != RT_OK) ce = cudaErrorUnknown;
+    };
+    copy(rgbaOut, rep->dRgba, f.W * 4);
+    copy(linearOut, rep->dLinear, f.W * 3 * sizeof(double));
+    copy(idsOut, rep->dIds, f.W * f.nn * sizeof(HitId));
+    if (ce != cudaSuccess) { rt_render_finish(rep, nullptr); return RT_ERR_CUDA; }
+    return RT_OK;
+}
+
+// Share of the frame's work units already FINISHED on one GPU, from its work counter (drawn units minus the ones the
+// resident warps may still hold); -1 while the frame has not started.  cancel: push the counter past its end.
+double pollProgress(rt_scene* rep, bool cancel, int& lastDrawn, int64_t& base) {
+    if (cudaSetDevice(rep->device) != cudaSuccess) return -1;
+    if (cudaEventQuery(rep->evReset) != cudaSuccess) { cudaGetLastError(); return -1; }
+    if (cancel) cudaMemcpyAsync(rep->dTileCounter, rep->hPoll + 1, sizeof(int), cudaMemcpyHostToDevice, rep->poll);
+    cudaMemcpyAsync(rep->hPoll, rep->dTileCounter, sizeof(int), cudaMemcpyDeviceToHost, rep->poll);
+    if (cudaStreamSynchronize(rep->poll) != cudaSuccess) { cudaGetLastError(); return -1; }
+    const int drawn = rep->hPoll[0];
+    if (drawn < lastDrawn) base += rep->pendingUnits / 2;        // area lights: the second pass started (counter reset)
+    lastDrawn = drawn;
+    const int64_t passUnits = rep->ds.nAreaLights > 0 ? rep->pendingUnits / 2 : rep->pendingUnits;
+    int64_t done = (int64_t)drawn - rep->pendingWarps;
+    if (done < 0) done = 0;
+    if (done > passUnits) done = passUnits;
+    return rep->pendingUnits > 0 ? (double)(base + done) / (double)rep->pendingUnits : 1.0;
+}
+
+}  // namespace
+
 int32_t rt_render(rt_scene_t* sc, const rt_camera* camera, const rt_render_params* params, uint8_t* rgbaOut,
                   double* linearOut, rt_hit_id* idsOut, rt_stats* statsOut) {
     if (!sc) return fail(RT_ERR_NO_SCENE, "No scene loaded. Can't render.");
     if (!camera) return fail(RT_ERR_BAD_CAMERA, "Invalid camera index");
     if (!rgbaOut && !linearOut) return fail(RT_ERR_INVALID, "one of rgbaOut / linearOut is required");
     const double w0 = nowMs();
-    CK(cudaSetDevice(sc->device));
-    const size_t W = camera->width > 1 ? camera->width : 1, H = camera->height > 1 ? camera->height : 1;
+    const int N = (int)sc->replicas.size();
+    if (N > 1 && params && params->shardCount > 1)
+        return fail(RT_ERR_INVALID, "a multi-device scene shards the frame itself: shardCount must be 0 or 1");
+    FrameShape f;
+    f.W = camera->width > 1 ? camera->width : 1; f.H = camera->height > 1 ? camera->height : 1;
     const int samples = camera->numSamples > 1 ? camera->numSamples : 1;
     const size_t n = (size_t)std::sqrt((double)samples);
-    int rc;
-    if (rgbaOut && (rc = ensure(&sc->dRgba, &sc->rgbaBytes, W * H * 4))) return rc;
-    if (linearOut && (rc = ensure(&sc->dLinear, &sc->linearBytes, W * H * 3 * sizeof(double)))) return rc;
-    if (idsOut && (rc = ensure(&sc->dIds, &sc->idsBytes, W * H * n * n * sizeof(HitId)))) return rc;
-    // rows outside this rank's shard are defined as zero in the host buffers
-    const bool sharded = params && params->shardCount > 1;
-    if (sharded) {
-        if (rgbaOut) CK(cudaMemsetAsync(sc->dRgba, 0, W * H * 4, 0));
-        if (linearOut) CK(cudaMemsetAsync(sc->dLinear, 0, W * H * 3 * sizeof(double), 0));
-        if (idsOut) CK(cudaMemsetAsync(sc->dIds, 0, W * H * n * n * sizeof(HitId), 0));
+    f.nn = n * n; f.chunks = (f.H + 7) / 8;
+    const int32_t H = (int32_t)f.H;
+    rt_progress_fn progress = params ? params->progress : nullptr;
+    void* user = params ? params->progressUser : nullptr;
+    if (progress && progress(0, H, user)) return fail(RT_ERR_CANCELLED, "cancelled");
+
+    // ---- enqueue on every GPU (N > 1: each from its own host thread, so the launches do not queue up behind one another)
+    std::vector<rt_stats> stats((size_t)N);
+    auto frameJob = [&](int r) -> int {
+        rt_scene* rep = sc->replicas[(size_t)r];
+        int rc = enqueueFrame(rep, r, N, camera, params, f, rgbaOut, linearOut, idsOut);
+        if (rc) return rc;
+        rc = rt_render_finish(rep, &stats[(size_t)r]);       // waits for the kernels; the copies follow on the same stream
+        cudaError_t ce = cudaStreamSynchronize(rep->stream);
+        if (rc) return rc;
+        CK(ce);
+        return RT_OK;
+    };
+    int rc = RT_OK;
+    bool cancelled = false;
+    if (N > 1) sc->pool->launch(frameJob);
+    else if ((rc = enqueueFrame(sc, 0, 1, camera, params, f, rgbaOut, linearOut, idsOut))) return rc;
+
+    // ---- while the frame is in flight: progress and cancellation (RayTracer.swift:172-181)
+    if (progress) {
+        std::vector<int> lastDrawn((size_t)N, 0);
+        std::vector<int64_t> base((size_t)N, 0);
+        int32_t reported = 0;
+        for (;;) {
+            bool running = false;
+            if (N > 1) { std::lock_guard<std::mutex> lk(sc->pool->m); running = sc->pool->remaining > 0; }
+            else { cudaSetDevice(sc->device); running = cudaEventQuery(sc->evStop) == cudaErrorNotReady; cudaGetLastError(); }
+            if (!running) break;
+            double sum = 0;
+            bool started = true;
+            for (int r = 0; r < N; r++) {
+                rt_scene* rep = sc->replicas[(size_t)r];
+                if (N > 1 && !rep->pending) { started = false; continue; }       // its worker has not launched yet / is done
+                const double p = pollProgress(rep, cancelled, lastDrawn[(size_t)r], base[(size_t)r]);
+                if (p < 0) started = false; else sum += p;
+            }
+            if (started && !cancelled) {
+                const int32_t rows = std::min<int32_t>(H, (int32_t)((sum / N) * (double)f.chunks) * 8);
+                if (rows > reported) {
+                    reported = rows;
+                    if (progress(rows, H, user)) cancelled = true;                // takes effect at the next poll
+                }
+            }
+            std::this_thread::sleep_for(std::chrono::microseconds(cancelled ? 20 : 100));
+        }
     }
-    if (params && params->progress && params->progress(0, (int32_t)H, params->progressUser)) return fail(RT_ERR_CANCELLED, "cancelled");
-    rc = rt_render_device(sc, camera, params, rgbaOut ? sc->dRgba : nullptr, linearOut ? sc->dLinear : nullptr,
-                          idsOut ? sc->dIds : nullptr, nullptr);
+    if (N > 1) {
+        sc->pool->wait();
+        for (int r = 0; r < N; r++)
+            if (sc->pool->rc[(size_t)r] != RT_OK && rc == RT_OK) { rc = sc->pool->rc[(size_t)r]; g_err = sc->pool->err[(size_t)r]; }
+        cudaSetDevice(sc->device);
+    } else {
+        rc = rt_render_finish(sc, &stats[0]);
+        cudaError_t ce = cudaStreamSynchronize(sc->stream);
+        if (rc == RT_OK && ce != cudaSuccess) { g_err = std::string("rt_render: ") + cudaGetErrorString(ce); rc = RT_ERR_CUDA; }
+    }
+    if (cancelled) {
+        for (rt_scene* rep : sc->replicas) rep->schedValid = false;       // the costs of a cut-short frame order nothing
+        return fail(RT_ERR_CANCELLED, "cancelled");
+    }
     if (rc) return rc;
-    cudaError_t ce = cudaSuccess;
-    if (rgbaOut) ce = cudaMemcpyAsync(rgbaOut, sc->dRgba, W * H * 4, cudaMemcpyDeviceToHost, 0);
-    if (linearOut && ce == cudaSuccess) ce = cudaMemcpyAsync(linearOut, sc->dLinear, W * H * 3 * sizeof(double), cudaMemcpyDeviceToHost, 0);
-    if (idsOut && ce == cudaSuccess) ce = cudaMemcpyAsync(idsOut, sc->dIds, W * H * n * n * sizeof(HitId), cudaMemcpyDeviceToHost, 0);
-    rc = rt_render_finish(sc, statsOut);        // also on a failed copy: the frame must not stay "in flight" on the handle
-    CK(ce);
-    if (rc) return rc;
-    CK(cudaStreamSynchronize(0));
-    if (statsOut) statsOut->milliseconds = (int64_t)(nowMs() - w0);
-    if (params && params->progress) params->progress((int32_t)H, (int32_t)H, params->progressUser);
+    if (statsOut) {
+        rt_stats& o = *statsOut;
+        o = stats[0];
+        for (int r = 1; r < N; r++) {
+            const rt_stats& s2 = stats[(size_t)r];
+            o.rays += s2.rays; o.raysPrimary += s2.raysPrimary; o.raysShadow += s2.raysShadow; o.raysSecondary += s2.raysSecondary;
+            o.kernelLaunches += s2.kernelLaunches; o.tilesScheduled += s2.tilesScheduled;
+            o.boxTests += s2.boxTests; o.triTests += s2.triTests; o.sphereTests += s2.sphereTests; o.planeTests += s2.planeTests;
+            o.instEntries += s2.instEntries; o.smoothHits += s2.smoothHits;
+            if (s2.maxStack > o.maxStack) o.maxStack = s2.maxStack;
+            if (s2.deviceMs > o.deviceMs) o.deviceMs = s2.deviceMs;      // the GPUs run side by side: the frame takes the slowest
+        }
+        o.milliseconds = (int64_t)(nowMs() - w0);
+    }
+    if (progress) progress(H, H, user);
     return RT_OK;
 }
 

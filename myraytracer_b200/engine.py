@@ -37,9 +37,15 @@ def _ptr(a):
 
 
 class RayTracerEngine:
-    def __init__(self, url: str, device: int = 0):
+    def __init__(self, url: str, device: int = 0, devices=None):
+        """devices: a list of CUDA device indices — the scene is built once and replicated onto every one of them
+        (rt_scene_create_multi); render() then shards each frame across them inside the one rt_render call."""
         self._lib = capi.load()
-        self._h = self._lib.rth_engine_create(url.encode(), device)
+        if devices is not None and len(devices) > 1:
+            arr = (C.c_int32 * len(devices))(*devices)
+            self._h = self._lib.rth_engine_create_multi(url.encode(), arr, len(devices))
+        else:
+            self._h = self._lib.rth_engine_create(url.encode(), devices[0] if devices else device)
         if not self._h:
             raise MemoryError(self._lib.rth_last_error().decode())
         self.load_error = "" if self.ready else self._lib.rth_last_error().decode()

@@ -28,6 +28,13 @@ Renderer::Renderer(const RTContext& ctx, const pk::Scene& scene, int device) {
     if (!handle_) error_ = rt_last_error();
 }
 
+Renderer::Renderer(const RTContext& ctx, const pk::Scene& scene, const std::vector<int>& devices) {
+    rt_scene_desc d = ctx.describe(scene);
+    std::vector<int32_t> dev(devices.begin(), devices.end());
+    handle_ = rt_scene_create_multi(&d, dev.data(), (int32_t)dev.size());
+    if (!handle_) error_ = rt_last_error();
+}
+
 Renderer::~Renderer() { rt_scene_destroy(handle_); }
 
 int Renderer::render(const pk::Scene& scene, int cameraIndex, std::vector<double>* linear, std::vector<uint8_t>* rgba,
@@ -75,6 +82,15 @@ RayTracerEngine::RayTracerEngine(const std::string& url, int device) {
     hasScene_ = true;
     ctx_ = RTContext(scene_, ingestDeviceFor(device));     // RTContext(scene:) :44
     renderer_.reset(new Renderer(ctx_, scene_, device));   // Renderer(ctx:) :45
+    if (!renderer_->valid()) { loadError_ = renderer_->error(); renderer_.reset(); }
+}
+
+RayTracerEngine::RayTracerEngine(const std::string& url, const std::vector<int>& devices) {
+    std::string err;
+    if (!pk::loadSceneBlob(url.c_str(), scene_, err)) { loadError_ = err; return; }
+    hasScene_ = true;
+    ctx_ = RTContext(scene_, ingestDeviceFor(devices.empty() ? 0 : devices[0]));
+    renderer_.reset(new Renderer(ctx_, scene_, devices));
     if (!renderer_->valid()) { loadError_ = renderer_->error(); renderer_.reset(); }
 }
 
@@ -140,6 +156,21 @@ const char* rth_last_error(void) { return g_herr.c_str(); }
 rth_engine_t* rth_engine_create(const char* sceneUrl, int32_t device) {
     try {
         auto* e = new rthost::RayTracerEngine(sceneUrl ? sceneUrl : "", device);
+        if (!e->hasScene() || !e->renderer()) g_herr = e->loadError();
+        return reinterpret_cast<rth_engine_t*>(e);
+    } catch (const std::exception& ex) {
+        g_herr = ex.what();
+    } catch (...) {
+        g_herr = "unknown exception";
+    }
+    return nullptr;
+}
+
+rth_engine_t* rth_engine_create_multi(const char* sceneUrl, const int32_t* devices, int32_t nDevices) {
+    try {
+        std::vector<int> dev;
+        for (int32_t k = 0; devices && k < nDevices; k++) dev.push_back(devices[k]);
+        auto* e = new rthost::RayTracerEngine(sceneUrl ? sceneUrl : "", dev);
         if (!e->hasScene() || !e->renderer()) g_herr = e->loadError();
         return reinterpret_cast<rth_engine_t*>(e);
     } catch (const std::exception& ex) {

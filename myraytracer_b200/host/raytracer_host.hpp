@@ -74,6 +74,8 @@ class Renderer {
 public:
     // Renderer(ctx:) — uploads the context to `device` (Object+Extension.swift:16-18)
     Renderer(const RTContext& ctx, const pk::Scene& scene, int device);
+    // the same scene resident on several GPUs of this process (rt_scene_create_multi): render() shards the frame
+    Renderer(const RTContext& ctx, const pk::Scene& scene, const std::vector<int>& devices);
     ~Renderer();
     Renderer(const Renderer&) = delete;
     Renderer& operator=(const Renderer&) = delete;
@@ -98,6 +100,7 @@ class RayTracerEngine {
 public:
     // init(from url:) — RayTracer.swift:30-49; a decode failure leaves the engine empty (:38-40)
     explicit RayTracerEngine(const std::string& url, int device = 0);
+    RayTracerEngine(const std::string& url, const std::vector<int>& devices);   // one engine, several GPUs
     bool hasScene() const { return hasScene_; }
     const pk::Scene& scene() const { return scene_; }
     const RTContext& context() const { return ctx_; }

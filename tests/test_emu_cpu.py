@@ -426,9 +426,10 @@ def _c_driver(tmp_path, lib_path):
     return exe
 
 
-def run_c_driver(exe, scene, image):
+def run_c_driver(exe, scene, image, devices=1, env=None):
     import subprocess
-    r = subprocess.run([exe, scene, image], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
+    r = subprocess.run([exe, scene, image] + ([str(devices)] if devices > 1 else []), stdout=subprocess.PIPE,
+                       stderr=subprocess.PIPE, text=True, timeout=600, env=env)
     assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
     return r.stdout.split()
 
@@ -454,6 +455,75 @@ def test_c_abi_from_a_plain_c_program(scene_dir, tmp_path, emu):
     assert out[6] == out[3].replace("fnv=", "fnv=") and out[5] == "module"
     ppm = open(tmp_path / "c.ppm", "rb").read()
     assert ppm.startswith(b"P6\n40 24\n255\n") and ppm[-40 * 24 * 3:] == want.rgba[..., :3].tobytes()
+    assert out[7] == "progress" and out[9] == "last=24"
+
+
+def test_c_abi_multi_device_scene(scene_dir, tmp_path, emu):
+    """rt_scene_create_multi from plain C on three emulated devices (RTEMU_DEVICES): one build, replicas by device
+    copies, one rt_render call shards the 8-row chunks over the devices' worker threads and every device copies its own
+    rows into the caller's rt_host_alloc buffer — the frame and the ray total of the single-device scene.  41 rows:
+    the ragged last chunk belongs to replica 2."""
+    import os
+    exe = _c_driver(tmp_path, emu_lib.EMU_PATH)
+    path = scenegen.config_c3(scene_dir, width=40, height=41, samples=4, depth=3, ico_level=1)
+    out = run_c_driver(exe, path, str(tmp_path / "m.ppm"), devices=3, env=dict(os.environ, RTEMU_DEVICES="3"))
+    assert out[13] == "multi" and out[14] == "3", out
+    assert out[15] == out[3] and out[16] == out[4], out
+
+
+def test_multi_device_engine_matches_single(scene_dir, emu, monkeypatch):
+    """RayTracerEngine(devices=[...]): linear colours, hit ids and RGBA8 of the sharded frame are the single-device
+    frame's, bit for bit, for 2 and 3 (emulated) devices; progress is reported from the calling thread while the
+    replicas' workers render; rt_scene_update_instances reaches every replica."""
+    monkeypatch.setenv("RTEMU_DEVICES", "3")
+    path = scenegen.config_instances(scene_dir, width=64, height=52, samples=4)
+    one = RayTracerEngine(path)
+    ref = one.render(0, want_linear=True, want_ids=True)
+    for devs in ([0, 1], [0, 1, 2]):
+        eng = RayTracerEngine(path, devices=devs)
+        assert eng.ready, eng.load_error
+        assert eng.scene_info()["deviceCount"] == len(devs)
+        seen = []
+        got = eng.render(0, want_linear=True, want_ids=True, progress=lambda done, total: seen.append((done, total)) or True)
+        assert np.array_equal(got.rgba, ref.rgba) and np.array_equal(got.linear, ref.linear) and np.array_equal(got.ids, ref.ids)
+        assert got.stats["rays"] == ref.stats["rays"] and got.stats["raysPrimary"] == ref.stats["raysPrimary"]
+        assert seen[0] == (0, 52) and seen[-1] == (52, 52) and all(a[0] <= b[0] for a, b in zip(seen, seen[1:]))
+        # animation: new transforms on every replica
+        from myraytracer_b200.engine import FlatContext
+        pf = scenegen.config_instances(scene_dir, frame=0.6, name="mframe", width=64, height=52, samples=4)
+        want = FlatContext(pf).instances()
+        eng.set_instance_transforms(want["l2w"])
+        one.set_instance_transforms(want["l2w"])
+        assert np.array_equal(eng.render(0).rgba, one.render(0).rgba)
+        one.set_instance_transforms(FlatContext(path).instances()["l2w"])
+        with pytest.raises(Exception):
+            eng.render(0, shard_index=0, shard_count=2)          # a multi-device scene shards the frame itself
+        eng.close()
+
+
+def test_cancel_from_progress_callback(scene_dir, emu, monkeypatch):
+    """A non-zero return of the progress callback stops the frame: RT_ERR_CANCELLED (-4), and the handle renders the
+    next frame normally (two emulated devices: the callback runs while the workers' kernels are in flight)."""
+    from myraytracer_b200 import RenderError
+    monkeypatch.setenv("RTEMU_DEVICES", "2")
+    path = scenegen.config_c1(scene_dir, width=96, height=96, samples=4)
+    eng = RayTracerEngine(path, devices=[0, 1])
+    ref = eng.render(0).rgba
+    with pytest.raises(RenderError) as e:
+        eng.render(0, progress=lambda done, total: False)        # cancelled before the launch
+    assert e.value.code == -4
+    calls = []
+    def cb(done, total):
+        calls.append(done)
+        return not (0 < done < total)                            # cancel at the first in-flight report
+    try:
+        eng.render(0, progress=cb)
+        cut = False
+    except RenderError as err:
+        assert err.code == -4
+        cut = True
+    assert cut == any(0 < c < 96 for c in calls)
+    assert np.array_equal(eng.render(0).rgba, ref)
 
 
 @pytest.mark.parametrize("rough,depth,variants,inf_light", [(0.0, 4, (1, 2), False), (0.15, 3, (2,), False),

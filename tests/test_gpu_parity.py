@@ -234,6 +234,58 @@ def test_c_abi_from_a_plain_c_program_on_the_gpu(scene_dir, tmp_path):
     want = RayTracerEngine(path).render(0)
     assert out[3] == "fnv=%016x" % fnv1a(want.rgba.tobytes())
     assert out[6] == out[3]
+    assert out[7] == "progress" and out[9] == "last=96"
+
+
+def test_cancel_mid_flight_from_c(scene_dir, tmp_path):
+    """RayTracer.swift:172-181 through the C ABI: the progress callback of a full-size C4 frame (1920x1080x16, ~10 ms)
+    is called while the kernel runs and cancels at its first in-flight report; rt_render returns RT_ERR_CANCELLED
+    within 2 ms of the request (the work counter is pushed past its end; warps finish the unit they hold), and the
+    next frame on the same handle is complete and identical."""
+    from myraytracer_b200 import capi
+    from test_emu_cpu import _c_driver, run_c_driver
+    exe = _c_driver(tmp_path, capi.LIB_PATH)
+    out = run_c_driver(exe, scenegen.config_c4(scene_dir), str(tmp_path / "c4.ppm"))
+    calls = int(out[8].split("=")[1])
+    print(out[7:13])
+    assert calls >= 5, out                                   # reports while in flight, not just at row 0 and row H
+    assert out[10] == "cancel" and out[11] == "rc=-4", out
+    assert 0 <= float(out[12].split("=")[1]) < 2.0, out
+
+
+def test_multi_device_scene_from_c(scene_dir, tmp_path):
+    """>= 2 GPUs only: rt_scene_create_multi + one rt_render call from plain C (SURVEY.md 8b/8e through the boundary the
+    Swift host binds): same frame, same ray total as the single-device scene."""
+    import torch
+    from myraytracer_b200 import capi
+    from test_emu_cpu import _c_driver, run_c_driver
+    n = min(torch.cuda.device_count(), 8)
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    exe = _c_driver(tmp_path, capi.LIB_PATH)
+    path = scenegen.config_c3(scene_dir, width=320, height=203, samples=4, depth=4, ico_level=2)
+    out = run_c_driver(exe, path, str(tmp_path / "m.png"), devices=n)
+    assert out[13] == "multi" and out[14] == str(n) and out[15] == out[3] and out[16] == out[4], out
+
+
+def test_multi_device_engine_on_the_gpus(scene_dir):
+    """>= 2 GPUs only: RayTracerEngine(devices=[...]) — the frame of one rt_render call over all GPUs equals the
+    single-GPU frame bit for bit (rgba, linear, ids), at C4's reduced size and on the recursive C3."""
+    import torch
+    n = min(torch.cuda.device_count(), 8)
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    for name in ("c4s", "c3", "c3area"):
+        case = CASES[name]
+        path = case["fn"](scene_dir, **case["kw"])
+        ref = RayTracerEngine(path).render(0, want_linear=True, want_ids=True)
+        eng = RayTracerEngine(path, devices=list(range(n)))
+        assert eng.ready, eng.load_error
+        for _ in range(2):
+            got = eng.render(0, want_linear=True, want_ids=True)
+            assert np.array_equal(got.rgba, ref.rgba) and np.array_equal(got.linear, ref.linear) and np.array_equal(got.ids, ref.ids), name
+            assert got.stats["rays"] == ref.stats["rays"], name
+        eng.close()
 
 
 def test_animation_refit_matches_rebuilt_scenes(scene_dir):
