@@ -132,33 +132,46 @@ class ClockSampler:
 
 # --------------------------------------------------------------------------------------------------
 # CPU arm: the oracle (oracle/liboracle.so) timed on the host cores.  The only places bench.py touches
-# oracle/: the `cpu_baseline` leg and `--impl reference`.  Never on the product path.
+# oracle/: the `cpu_baseline` leg (+ the parity gate, which checks the GPU frame against it) and
+# `--impl reference`.  Never on the product path.
 # --------------------------------------------------------------------------------------------------
-def cpu_sample(path: str, target_s: float = 15.0, stride: int = 0, scene=None):
+IDS_LIMIT_BYTES = 2 << 30      # hit ids (24 B per primary ray) are compared only when they fit comfortably in host memory
+
+
+def cpu_sample(path: str, target_s: float = 15.0, stride: int = 0, scene=None, threads: int = 0, want_ids: bool = False):
     """Render a bounded sample of the frame (every `stride`-th 8-row chunk, the reference's own unit of
-    parallel work, Object+Extension.swift:75-82) with all host threads.  Returns (Mrays/s, info)."""
+    parallel work, Object+Extension.swift:75-82) with `threads` host threads (0 = all).  Returns (Mrays/s, info);
+    info["render"] keeps the oracle's frame (rgba, ids, counters) for the parity gate."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib
     o = scene if scene is not None else oracle_lib.OracleScene(path)
     cam = o.camera(0)
     nchunks = (cam.height + 7) // 8
     cores = os.cpu_count() or 1
+    used = cores if threads <= 0 else threads
     if stride <= 0:
         # size the sample: one chunk from the middle of the frame on one thread -> estimate of the full frame
         p = o.render(threads=1, chunk_stride=nchunks, chunk_offset=nchunks // 2)
-        est_full_s = p["ms"] * 1e-3 * nchunks / min(cores, nchunks)
+        est_full_s = p["ms"] * 1e-3 * nchunks / min(used, nchunks)
         stride = max(1, min(nchunks, int(round(est_full_s / target_s))))
-    r = o.render(threads=0, chunk_stride=stride, chunk_offset=0)
+    n2 = cam.sqrtSamples * cam.sqrtSamples
+    ids_ok = want_ids and cam.width * cam.height * n2 * 24 <= IDS_LIMIT_BYTES
+    r = o.render(threads=threads, chunk_stride=stride, chunk_offset=0, want_ids=ids_ok)
     c = r["counters"]
     rays = c["raysPrimary"] + c["raysShadow"] + c["raysSecondary"]
     mrays = rays / (r["ms"] * 1e-3) / 1e6
     nsel = len(range(0, nchunks, stride))
-    info = {"rays": rays, "ms": r["ms"], "cores": cores, "stride": stride, "chunks": nsel, "nchunks": nchunks,
+    info = {"rays": rays, "ms": r["ms"], "cores": used, "stride": stride, "chunks": nsel, "nchunks": nchunks,
             "sample": f"every {stride}-th 8-row chunk ({nsel} of {nchunks} chunks, {c['raysPrimary']} primary rays) of the "
-                      f"{cam.width}x{cam.height}x{cam.numSamples}spp frame, {cores} threads, FP64, reference BVH (SAH 12 bins, maxLeaf 2)",
-            "counters": c, "build_ms": o.info().buildMs}
-    info["scene"] = o
+                      f"{cam.width}x{cam.height}x{cam.numSamples}spp frame, {used} thread{'s' if used > 1 else ''}, FP64, "
+                      "reference BVH (SAH 12 bins, maxLeaf 2)",
+            "counters": c, "build_ms": o.info().buildMs, "render": r, "scene": o}
     return mrays, info
+
+
+def workload_config(config: str, W: int, H: int, spp: int, triangles: int) -> dict:
+    """`config` of the JSON line: the same keys from both arms."""
+    return {"workload": BENCH_CONFIGS[config][2], "width": W, "height": H, "spp": spp, "triangles": triangles}
 
 
 def run_reference(args):
@@ -179,10 +192,12 @@ def run_reference(args):
         _, i2 = cpu_sample(path, stride=stride, scene=scene)
         tot_rays += i2["rays"]; tot_ms += i2["ms"]
     value = tot_rays / (tot_ms * 1e-3) / 1e6
+    cam, oi = scene.camera(0), scene.info()
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": tot_ms / args.steps, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": BENCH_CONFIGS[args.config][2], "sample": info["sample"]},
+            "config": workload_config(args.config, cam.width, cam.height, cam.numSamples, int(oi.triangles)),
+            "sample": info["sample"],
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": info["cores"], "kind": "port", "sample": info["sample"]},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -199,11 +214,62 @@ def algorithmic_bytes(st: dict, pixels: int) -> int:
     return sum(BYTES[k] * int(st[k]) for k in BYTES) + 4 * pixels
 
 
+def frame_hash(a) -> str:
+    """64-bit BLAKE2b of the RGBA8 frame: one hash per frame, the same for every N (SURVEY.md §8(d) gate 4)."""
+    import hashlib
+    return hashlib.blake2b(a.tobytes(), digest_size=8).hexdigest()
+
+
+def parity_gate(gpu, cpu_info) -> dict:
+    """BASELINE.json's bars between the GPU frame of THIS run and the oracle frame of this run's cpu_baseline leg
+    (tests/parity.py: compare), on the chunks the CPU sample rendered."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import numpy as np
+    import parity
+    ref, stride, nchunks = cpu_info["render"], cpu_info["stride"], cpu_info["nchunks"]
+    H = ref["rgba"].shape[0]
+    rows = np.zeros(H, bool)
+    for c in range(0, nchunks, stride):
+        rows[c * 8:(c + 1) * 8] = True
+    g = {"rgba": gpu.rgba[rows], "ids": None if gpu.ids is None or ref["ids"] is None else gpu.ids[rows], "stats": None}
+    r = {"rgba": ref["rgba"][rows], "ids": None if ref["ids"] is None else ref["ids"][rows]}
+    rep = parity.compare(g, r)
+    out = {k: rep[k] for k in ("px_within_1", "px_exact", "px_max_diff", "id_agree", "id_disagree", "id_bad", "t_bit_exact") if k in rep}
+    c = ref["counters"]
+    out["rows_compared"] = int(rows.sum())
+    out["rays_ref"] = [int(c["raysPrimary"]), int(c["raysShadow"]), int(c["raysSecondary"])]
+    if stride == 1:
+        out["rays_gpu"] = [int(gpu.stats["raysPrimary"]), int(gpu.stats["raysShadow"]), int(gpu.stats["raysSecondary"])]
+    ok = out["px_within_1"] >= 0.999 and (out.get("id_agree", 1.0) >= 0.9999) and out.get("id_bad", 0) == 0
+    if stride == 1:
+        ok = ok and out["rays_gpu"][0] == out["rays_ref"][0] and \
+            all(abs(a - b) <= max(4, 1e-4 * b) for a, b in zip(out["rays_gpu"][1:], out["rays_ref"][1:]))
+    out["pass"] = bool(ok)
+    out["bars"] = "ids >= 99.99 % with disagreements only at t ties (1e-5 rel); 8-bit pixels within 1 LSB on >= 99.9 %"
+    return out
+
+
+def measured_roofs() -> dict:
+    """Roofs measured on this pool's B200 by tools/microbench.cu (committed under profiles/) and by the driver."""
+    out = {}
+    try:
+        out.update(json.load(open(os.path.join(ROOT, "profiles", "r2a_microbench.json"))))
+    except Exception:
+        pass
+    try:
+        out["driver"] = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    return out
+
+
 def run_ours(args):
+    import numpy as np
     import torch
     import torch.distributed as dist
-    from myraytracer_b200 import capi
+    from myraytracer_b200 import RayTracerEngine, capi
     from myraytracer_b200.distributed import ShardedRenderer
+    from myraytracer_b200.engine import host_buffer
 
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -238,12 +304,13 @@ def run_ours(args):
                         schedule=1 if args.schedule == "spatial" else 0)
     info = R.engine.scene_info()
     W, H = R.width, R.height
+    spp = int(R.engine.camera(0).numSamples)
     log(f"[rank {rank}] scene ready in {time.time() - t0:.1f}s: {info}")
 
-    # ---- counters pass (untimed, slower kernel variant): algorithmic bytes of this rank's launch
+    # ---- counters pass (untimed; the same traversal instantiated with counters): algorithmic bytes of this rank's launch
     R.enqueue(counters=True)
     cst = R.finish()
-    n_side = max(1, int(max(1, int(R.engine.camera(0).numSamples)) ** 0.5))
+    n_side = max(1, int(max(1, spp) ** 0.5))
     my_pixels = int(cst["raysPrimary"]) // (n_side * n_side)                 # pixels of this rank's shard
     my_bytes = algorithmic_bytes(cst, my_pixels)
 
@@ -260,7 +327,10 @@ def run_ours(args):
         e1.synchronize()
         return e0.elapsed_time(e1), st
 
-    for _ in range(args.warmup):
+    # ---- the first frame of a camera (what one RayTracerEngine.render call gets: no learnt tile order yet)
+    first_ms, _ = step()
+    first_ms = allreduce(first_ms, dist.ReduceOp.MAX if world > 1 else None)
+    for _ in range(max(0, args.warmup - 1)):
         step()
     sampler = ClockSampler(local)
     barrier()
@@ -284,7 +354,7 @@ def run_ours(args):
     launches = int(allreduce(float(st["kernelLaunches"] * args.steps), dist.ReduceOp.SUM if world > 1 else None))
     scheduled = int(st["tilesScheduled"])
 
-    # ---- the same frame with the tiles drawn top to bottom (what the first frame of a camera gets), for comparison
+    # ---- the same frame with the tiles drawn top to bottom, for comparison
     spatial_ms = None
     if R.schedule == 0:
         R.schedule = 1
@@ -295,73 +365,145 @@ def run_ours(args):
         R.schedule = 0
         barrier()
 
-    # ---- e2e: public call, framebuffer back in pinned host memory every step
+    # ---- the multi-process public call: every rank renders its chunks into rank 0's frame over NVLink, rank 0 copies
+    #      the frame to pinned host memory
     for _ in range(2):
         R.render()
     barrier()
     t1 = time.perf_counter()
     for _ in range(args.steps):
         flush.zero_()
-        R.render()
+        frame_ranks, _ = R.render()
     barrier()
-    e2e_ms = allreduce((time.perf_counter() - t1) * 1e3 / args.steps, dist.ReduceOp.MAX if world > 1 else None)
-    cam_bytes = ctypes_sizeof_camera()
-    e2e = {"value": rays / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": e2e_ms,
-           "h2d_bytes_per_step": cam_bytes * world, "d2h_bytes_per_step": W * H * 4 + 128 * world,
-           "note": "scene/BVH resident (uploaded once at engine creation, as the reference builds RTContext before its "
-                   "timer, RayTracer.swift:44,166); per step the camera/launch parameters go down and the RGBA8 frame "
-                   "+ ray counters come back to pinned host memory"}
-
+    ranks_ms = allreduce((time.perf_counter() - t1) * 1e3 / args.steps, dist.ReduceOp.MAX if world > 1 else None)
+    frame_hash_ranks = frame_hash(frame_ranks) if rank == 0 else None
     R.close()
+
+    # ---- e2e: the call the Swift host makes — rt_render(scene, camera, params, hostRgba, ...) through the C ABI, from ONE
+    #      process, host buffers, every device->host copy inside the timed region.  N > 1: a multi-device scene
+    #      (rt_scene_create_multi) on all N GPUs driven by rank 0 alone; the other ranks wait on the store (no GPU work).
+    e2e, parity, cpu_line, cpu1_line, frame_hash_abi = None, None, None, None, None
+    store = dist.distributed_c10d._get_default_store() if world > 1 else None
+    if rank == 0:
+        eng = RayTracerEngine(path, devices=list(range(world)))
+        assert eng.ready, eng.load_error
+        flushes = [flush] + [torch.empty(256 << 20, dtype=torch.uint8, device=torch.device("cuda", k)) for k in range(1, world)]
+        with host_buffer((H, W, 4)) as hb:
+            for _ in range(max(2, args.warmup)):
+                eng.render(0, out_rgba=hb.array)
+            dts = []
+            for _ in range(args.steps):
+                for k, fb in enumerate(flushes):          # L2 flush on every GPU of the scene
+                    fb.zero_()
+                    torch.cuda.synchronize(torch.device("cuda", k))
+                t1 = time.perf_counter()
+                res = eng.render(0, out_rgba=hb.array)
+                dts.append((time.perf_counter() - t1) * 1e3)
+            e2e_ms = sum(dts) / len(dts)
+            frame_hash_abi = frame_hash(hb.array)
+            e2e_rays = int(res.stats["rays"])
+            cam_bytes = ctypes_sizeof_camera()
+            e2e = {"value": e2e_rays / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": e2e_ms, "ms_min": min(dts),
+                   "h2d_bytes_per_step": cam_bytes * world, "d2h_bytes_per_step": W * H * 4 + 128 * world,
+                   "call": "rt_render(scene, camera, params, rgbaOut = page-locked host buffer of rt_host_alloc, ...) from one process"
+                           + (f" on a {world}-GPU scene (rt_scene_create_multi): every GPU copies its rows to the host buffer itself" if world > 1 else ""),
+                   "device_ms": float(res.stats["deviceMs"]),
+                   "note": "scene/BVH resident (built once at engine creation, as the reference builds RTContext before its "
+                           "timer, RayTracer.swift:44,166); per step the camera/launch parameters go down and the RGBA8 frame "
+                           "+ ray counters come back to host memory; wall clock around the blocking call",
+                   "ranks_path": {"value": rays / (ranks_ms * 1e-3) / 1e6, "ms_per_step": ranks_ms,
+                                  "call": "ShardedRenderer.render(): one process per GPU (torch.distributed), kernels store into rank 0's "
+                                          "frame over NVLink, rank 0 copies it to pinned host memory"}}
+        # ---- parity gate + CPU baseline (N = 1 only: the contract's cpu_baseline leg)
+        if world == 1 and not args.no_cpu:
+            mr, ci = cpu_sample(path, target_s=args.cpu_seconds, want_ids=True)
+            want_ids = ci["render"]["ids"] is not None
+            got = eng.render(0, want_ids=want_ids)
+            parity = parity_gate(got, ci)
+            parity["frame_equals_timed_frame"] = bool(frame_hash(got.rgba) == frame_hash_abi == frame_hash_ranks)
+            cpu_line = {"value": mr, "unit": UNIT, "cores": ci["cores"], "kind": "port", "sample": ci["sample"], "ms": ci["ms"],
+                        "counts_reference_order": {k: int(ci["counters"][k]) for k in ("nodeVisits", "boxTests", "triTests", "sphereTests",
+                                                                                      "planeTests", "instEntries", "maxStack")}}
+            m1, c1 = cpu_sample(path, target_s=min(10.0, args.cpu_seconds), scene=ci["scene"], threads=1)
+            cpu1_line = {"value": m1, "unit": UNIT, "cores": 1, "kind": "port", "sample": c1["sample"], "ms": c1["ms"]}
+        eng.close()
+        if store is not None:
+            store.set("bench_e2e_done", "1")
+    elif store is not None:
+        store.wait(["bench_e2e_done"])
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return 0
 
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
-    peak = float(peaks.get("hbm_gbs", 6650.0))
-    achieved = my_bytes / (kern_ms * 1e-3) / 1e9
+    roofs = measured_roofs()
+    drv = roofs.get("driver", {})
+    hbm_peak = float(drv.get("hbm_gbs", 6650.0))
     general = args.variant == 2 or args.config in ("c3glossy", "c3area")
     kernel_name = ("renderKernelGeneral<false, true> (x2: counting + shading pass)" if args.config == "c3area" else
                    "renderKernelGeneral<false, false>") if general else "renderKernelFast<false>"
-    roofline = {"bound": "hbm", "kernel": kernel_name, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": "measured" if peaks else "fallback",
-                "algorithmic_bytes_per_launch": my_bytes, "kernel_ms": kern_ms,
-                "counts": {k: int(cst[k]) for k in list(BYTES) + ["maxStack"]},
-                "note": "algorithmic bytes are served by L1/L2 (traffic = ncu DRAM bytes of one launch), so a fraction above 1 "
-                        "only says the working set is cache resident; the path is issue/latency bound — profiles/, "
-                        "DESIGN.md section 5"}
-    try:   # DRAM traffic of one launch from the committed `ncu --set full` capture of this workload (profiles/)
-        tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+    # Which roof binds: warp instructions issued per second against SMs x 4 schedulers x the SM clock seen under load.
+    # The instruction count of one launch is the ncu figure of the committed capture of this build (profiles/inst_counts.json;
+    # smsp__inst_executed.sum — it does not depend on the run); the duration and the clock are this run's.
+    inst, inst_src, traffic, traffic_src = None, None, None, None
+    try:
+        ic = json.load(open(os.path.join(ROOT, "profiles", "inst_counts.json")))
         key = f"{args.config}_n{world}_v{args.variant}"
-        if key in tr:
-            roofline["traffic"] = tr[key]["dram_bytes_per_launch"]
-            roofline["traffic_source"] = tr[key]["source"]
+        if key in ic:
+            inst, inst_src = ic[key]["warp_inst_per_launch"], ic[key]["source"]
+            traffic, traffic_src = ic[key].get("dram_bytes_per_launch"), ic[key]["source"]
     except Exception:
         pass
+    sm_mhz = clocks.get("sm_mhz") or float(drv.get("sm_max_mhz", 1965.0))
+    issue_peak = 148 * 4 * sm_mhz * 1e6 / 1e9                       # G warp-instructions / s
+    alg_gbs = my_bytes / (kern_ms * 1e-3) / 1e9
+    l2_peak = float(roofs.get("l2_read_gbs_32mb", 0.0)) or None
+    roofline = {"bound": "issue", "kernel": kernel_name, "unit": "G warp-inst/s",
+                "achieved": (inst / (kern_ms * 1e-3) / 1e9) if inst else None, "peak": issue_peak,
+                "frac": (inst / (kern_ms * 1e-3) / 1e9 / issue_peak) if inst else None,
+                "peak_source": f"148 SMs x 4 schedulers x {sm_mhz:.0f} MHz (clock sampled in this run); tools/microbench.cu reaches "
+                               f"{roofs.get('int_ginst')} of {roofs.get('issue_roof_ginst')} G/s with independent integer ops",
+                "warp_inst_per_launch": inst, "warp_inst_source": inst_src, "kernel_ms": kern_ms,
+                "traffic": traffic, "traffic_source": traffic_src,
+                "hbm": {"bound": "hbm", "achieved": alg_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": alg_gbs / hbm_peak,
+                        "peak_source": "measured (MEASURED_PEAKS.json)" if drv else "fallback",
+                        "algorithmic_bytes_per_launch": my_bytes,
+                        "dram_frac": (traffic / (kern_ms * 1e-3) / 1e9 / hbm_peak) if traffic else None,
+                        "note": "SURVEY.md 8(d) algorithmic bytes; they are served by L1/L2 (working set "
+                                f"{info['deviceBytes'] / 1e6:.0f} MB against 126 MB of L2), so this fraction can exceed 1 and "
+                                "HBM is not the roof that binds; dram_frac = DRAM bytes actually moved / peak"},
+                "l2": {"achieved": alg_gbs, "peak": l2_peak, "unit": "GB/s", "frac": (alg_gbs / l2_peak) if l2_peak else None,
+                       "peak_source": "tools/microbench.cu: float4 grid-stride reads over a 32 MB buffer (profiles/r2a_microbench.json)"},
+                "fp64": {"peak_ginst": roofs.get("dadd_ginst"), "note": "DADD / DMUL / DFMA issue at half the integer rate (tools/microbench.cu)"},
+                "counts": {k: int(cst[k]) for k in list(BYTES) + ["maxStack"]},
+                "counts_note": "kernel instantiated with counters (same traversal code, COUNT = true), untimed pass"}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64", "dtype_note": "everything that decides a result (ray generation, primitive tests, shading, sums) is FP64 "
+                                          "in the reference's operation order; box culling is conservative FP32",
             "data": "synthetic",
-            "config": {"workload": BENCH_CONFIGS[args.config][2], "width": W, "height": H, "triangles": info["triangles"],
-                       "rays_per_frame": int(rays), "rays_primary": int(rp), "rays_shadow": int(rs),
-                       "rays_secondary": int(rays - rp - rs), "parallelism": f"tiles{world}", "gather": R.gather, "shard": R.shard, "kernel_variant": args.variant,
-                       "schedule": ("tiles drawn longest-first from the per-tile cost recorded on the previous frame "
-                                    f"({scheduled} tiles on rank 0); warm-up frames train it" if scheduled else "spatial order"),
-                       "ms_per_step_spatial_order": spatial_ms,
+            "config": workload_config(args.config, W, H, spp, int(info["triangles"])),
+            "detail": {"rays_per_frame": int(rays), "rays_primary": int(rp), "rays_shadow": int(rs),
+                       "rays_secondary": int(rays - rp - rs), "parallelism": f"tiles{world}", "gather": R.gather, "shard": R.shard,
+                       "kernel_variant": args.variant,
+                       "schedule": ("timed frames: tiles drawn longest-first from the per-tile cost recorded on the previous frame "
+                                    f"({scheduled} tiles on rank 0; warm-up frames train it)" if scheduled else "spatial order"),
+                       "ms_first_frame": first_ms, "ms_per_step_spatial_order": spatial_ms,
                        "l2": ("NOT FLUSHED (diagnostic run); " if args.no_flush else "") + "256 MB buffer written between timed iterations (L2 flush); scene working set "
                              f"{info['deviceBytes'] / 1e6:.0f} MB"},
             "wall_ms_per_step": wall * 1e3 / args.steps, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+            "frame_hash": frame_hash_abi, "frame_hash_ranks_path": frame_hash_ranks,
+            "frame_hash_note": "BLAKE2b-64 of the RGBA8 frame rt_render returned / the multi-process path gathered: equal to each other and for every N",
             "roofline": roofline, "build_ms": info["buildMs"], "upload_ms": info["uploadMs"],
             "bvh_build": ("host binned SAH" if not info["deviceBuiltBlas"] else
                           "device binned SAH" if os.environ.get("RTCUDA_BUILD") == "device-sah" else "device LBVH")}
-    if world == 1 and not args.no_cpu:
-        mr, ci = cpu_sample(path, target_s=args.cpu_seconds)
-        line["cpu_baseline"] = {"value": mr, "unit": UNIT, "cores": ci["cores"], "kind": "port", "sample": ci["sample"],
-                                "ms": ci["ms"], "per_core": mr / ci["cores"]}
+    if parity is not None:
+        line["parity"] = parity
+    if cpu_line is not None:
+        line["cpu_baseline"] = cpu_line
+        line["cpu_baseline_1_thread"] = cpu1_line
+        line["speedup_measured"] = {"e2e_vs_all_host_threads": e2e["value"] / cpu_line["value"], "host_threads": cpu_line["cores"],
+                                    "e2e_vs_one_host_thread": e2e["value"] / cpu1_line["value"]}
     emit(line)
     if world > 1:
         dist.destroy_process_group()

@@ -536,7 +536,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     rt_scene_info& I = sc->info;
     I.triangles = d->nTriangles; I.spheres = d->nSpheres; I.planes = d->nPlanes; I.instances = d->nInstances; I.blasCount = d->nBlas;
     I.blasNodes = (int64_t)nodes.size(); I.tlasNodes = (int64_t)tl.nodes.size(); I.maxLeafSize = maxLeaf; I.maxDepth = maxDepth;
-    I.deviceBytes = bytes; I.buildMs = t1 - t0; I.uploadMs = t2 - t1; I.device = device; I.deviceBuiltBlas = deviceBuilt;
+    I.deviceBytes = bytes; I.buildMs = t1 - t0; I.uploadMs = t2 - t1; I.device = device; I.deviceBuiltBlas = deviceBuilt; I.deviceCount = 1;
     return RT_OK;
 }
 

@@ -247,9 +247,13 @@ int copyOwnedRows(void* host, const void* dev, size_t rowBytes, const FrameShape
     return RT_OK;
 }
 
-// Everything one GPU does for a frame of rt_render: buffers, launch, copies of its rows.  Enqueues only.
+int copyFrame(rt_scene* rep, int r, int N, const FrameShape& f, uint8_t* rgbaOut, double* linearOut, rt_hit_id* idsOut);
+
+// Everything one GPU does for a frame of rt_render: buffers, launch, copies of its rows.  Enqueues only — except that a
+// device -> host copy into PAGEABLE memory blocks the calling thread until the kernel before it has finished, which is
+// why a caller that wants to report progress from this thread defers the copies (copyFrame) until the kernel is done.
 int enqueueFrame(rt_scene* rep, int r, int N, const rt_camera* camera, const rt_render_params* params, const FrameShape& f,
-                 uint8_t* rgbaOut, double* linearOut, rt_hit_id* idsOut) {
+                 uint8_t* rgbaOut, double* linearOut, rt_hit_id* idsOut, bool deferCopies = false) {
     CK(cudaSetDevice(rep->device));
     int rc;
     if (rgbaOut && (rc = ensure(&rep->dRgba, &rep->rgbaBytes, f.W * f.H * 4))) return rc;
@@ -267,7 +271,14 @@ int enqueueFrame(rt_scene* rep, int r, int N, const rt_camera* camera, const rt_
     rc = rt_render_device(rep, camera, &prm, rgbaOut ? rep->dRgba : nullptr, linearOut ? rep->dLinear : nullptr,
                           idsOut ? rep->dIds : nullptr, rep->stream);
     if (rc) return rc;
-    cudaError_t ce = cudaSuccess;       // a failed copy must not leave the frame "in flight" on the handle
+    if (deferCopies) return RT_OK;
+    if ((rc = copyFrame(rep, r, N, f, rgbaOut, linearOut, idsOut))) { rt_render_finish(rep, nullptr); return rc; }
+    return RT_OK;
+}
+
+int copyFrame(rt_scene* rep, int r, int N, const FrameShape& f, uint8_t* rgbaOut, double* linearOut, rt_hit_id* idsOut) {
+    CK(cudaSetDevice(rep->device));
+    cudaError_t ce = cudaSuccess;
     auto copy = [&](void* h, const void* d, size_t rowBytes) {
         if (!h || ce != cudaSuccess) return;
         if (copyOwnedRows(h, d, rowBytes, f, r, N, rep->stream) != RT_OK) ce = cudaErrorUnknown;
@@ -275,8 +286,7 @@ int enqueueFrame(rt_scene* rep, int r, int N, const rt_camera* camera, const rt_
     copy(rgbaOut, rep->dRgba, f.W * 4);
     copy(linearOut, rep->dLinear, f.W * 3 * sizeof(double));
     copy(idsOut, rep->dIds, f.W * f.nn * sizeof(HitId));
-    if (ce != cudaSuccess) { rt_render_finish(rep, nullptr); return RT_ERR_CUDA; }
-    return RT_OK;
+    return ce != cudaSuccess ? RT_ERR_CUDA : RT_OK;
 }
 
 // Share of the frame's work units already FINISHED on one GPU, from its work counter (drawn units minus the ones the
@@ -333,7 +343,7 @@ int32_t rt_render(rt_scene_t* sc, const rt_camera* camera, const rt_render_param
     int rc = RT_OK;
     bool cancelled = false;
     if (N > 1) sc->pool->launch(frameJob);
-    else if ((rc = enqueueFrame(sc, 0, 1, camera, params, f, rgbaOut, linearOut, idsOut))) return rc;
+    else if ((rc = enqueueFrame(sc, 0, 1, camera, params, f, rgbaOut, linearOut, idsOut, progress != nullptr))) return rc;
 
     // ---- while the frame is in flight: progress and cancellation (RayTracer.swift:172-181)
     if (progress) {
@@ -369,6 +379,7 @@ int32_t rt_render(rt_scene_t* sc, const rt_camera* camera, const rt_render_param
             if (sc->pool->rc[(size_t)r] != RT_OK && rc == RT_OK) { rc = sc->pool->rc[(size_t)r]; g_err = sc->pool->err[(size_t)r]; }
         cudaSetDevice(sc->device);
     } else {
+        if (progress && !cancelled && (rc = copyFrame(sc, 0, 1, f, rgbaOut, linearOut, idsOut))) { rt_render_finish(sc, nullptr); return rc; }
         rc = rt_render_finish(sc, &stats[0]);
         cudaError_t ce = cudaStreamSynchronize(sc->stream);
         if (rc == RT_OK && ce != cudaSuccess) { g_err = std::string("rt_render: ") + cudaGetErrorString(ce); rc = RT_ERR_CUDA; }

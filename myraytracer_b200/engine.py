@@ -178,7 +178,9 @@ class RayTracerEngine:
     def render(self, camera_index: int = 0, want_linear: bool = False, want_ids: bool = False,
                shard_index: int = 0, shard_count: int = 1, counters: bool = False,
                progress: Optional[Callable[[int, int], bool]] = None, variant: int = 0, schedule: int = 0,
-               shard_mode: int = 0) -> RenderResult:
+               shard_mode: int = 0, out_rgba: Optional[np.ndarray] = None) -> RenderResult:
+        """out_rgba: caller-owned (H, W, 4) uint8 buffer to render into, e.g. page-locked memory of host_buffer()
+        (what a Swift caller passes to rt_render); default: a fresh pageable numpy array."""
         if not self._h or self._lib.rth_engine_camera_count(self._h) == 0 and not self.ready:
             pass  # let the C side produce the reference's error codes
         cam = None
@@ -189,7 +191,9 @@ class RayTracerEngine:
         W = max(1, cam.width) if cam else 1
         H = max(1, cam.height) if cam else 1
         n = int(np.floor(np.sqrt(max(1, cam.numSamples)))) if cam else 1
-        rgba = np.zeros((H, W, 4), np.uint8)
+        rgba = np.zeros((H, W, 4), np.uint8) if out_rgba is None else out_rgba
+        if rgba.shape != (H, W, 4) or rgba.dtype != np.uint8 or not rgba.flags["C_CONTIGUOUS"]:
+            raise ValueError("out_rgba must be a C-contiguous (H, W, 4) uint8 array")
         linear = np.zeros((H, W, 3), np.float64) if want_linear else None
         ids = np.zeros((H, W, n * n), capi.HIT_ID_DTYPE) if want_ids else None
         prm = capi.rt_render_params()
@@ -231,6 +235,30 @@ class RayTracerEngine:
         if rc != 0:
             raise RenderError(rc, self._lib.rt_last_error().decode())
         return st.as_dict()
+
+
+class host_buffer:
+    """Page-locked host memory from rt_host_alloc as a numpy array (`.array`); freed by close() / the context manager."""
+
+    def __init__(self, shape, dtype=np.uint8):
+        self._lib = capi.load()
+        n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        self._p = self._lib.rt_host_alloc(n)
+        if not self._p:
+            raise MemoryError(self._lib.rt_last_error().decode())
+        self.array = np.ctypeslib.as_array((C.c_uint8 * n).from_address(self._p)).view(dtype).reshape(shape)
+
+    def close(self):
+        if getattr(self, "_p", None):
+            self.array = None
+            self._lib.rt_host_free(self._p)
+            self._p = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
 
 
 def write_image(path: str, rgba: np.ndarray) -> None:
