@@ -181,4 +181,18 @@ struct ShardTiles {
     }
 };
 
+// Work units of the fast kernel: `passes` consecutive passes of 32 (pixel, sample) items of a tile, `perTile` units per
+// 8x4 tile.  ns = samples per pixel.  ns divides 32: a pass holds whole pixels, so one pass is a unit — or, for
+// scenes with recursion, up to RT_BATCH_PASSES passes, whose child rays are then traced together; 32 divides ns: the
+// ns / 32 passes of one pixel; otherwise the whole tile (the ordered per-pixel sum is carried across its ns passes).
+#define RT_BATCH_PASSES 4
+struct FastUnits {
+    int passes, perTile;
+    RT_HD FastUnits(int ns, bool recurse) {
+        if (ns < 32 && 32 % ns == 0) { passes = recurse ? (ns < RT_BATCH_PASSES ? ns : RT_BATCH_PASSES) : 1; perTile = ns / passes; }
+        else if (ns % 32 == 0) { passes = ns >> 5; perTile = 32; }
+        else { passes = ns; perTile = 1; }
+    }
+};
+
 }  // namespace rtg

@@ -152,6 +152,8 @@ struct rt_scene {
     bool sideBusy = false;
     int blocks[KV_COUNT][2] = {};      // [variant][counters]
     bool glossy = false;               // some material has roughness != 0: RNG draws inside trace
+    bool recurse = false;              // maxRecursionDepth > 0 and a mirror / dielectric / conductor material: child rays exist
+    bool nonFinite = false;            // a light / material / ambient constant is inf or NaN: the non-finite guard of `trace` can fire
     int pendingVariant = 0;
     bool pending = false; bool pendingCounters = false;
     cudaStream_t pendingStream = nullptr;
@@ -401,7 +403,17 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
         g.type = (m.type >= RT_MAT_MIRROR && m.type <= RT_MAT_CONDUCTOR) ? m.type : RT_MAT_PLAIN;
         g.hasAbsorption = (m.absorption[0] != 0 || m.absorption[1] != 0 || m.absorption[2] != 0) ? 1 : 0;
         if (g.type != RT_MAT_PLAIN && m.roughness != 0) sc->glossy = true;
+        if (g.type != RT_MAT_PLAIN && d->maxRecursionDepth > 0) sc->recurse = true;
+        const double* coef[5] = {m.ambient, m.diffuse, m.specular, m.mirror, m.absorption};
+        for (int k = 0; k < 5; k++)
+            for (int a = 0; a < 3; a++) if (!std::isfinite(coef[k][a])) sc->nonFinite = true;
+        if (!std::isfinite(m.phong) || !std::isfinite(m.ior) || !std::isfinite(m.absorptionIndex)) sc->nonFinite = true;
     }
+    for (int a = 0; a < 3; a++) if (!std::isfinite(d->ambient[a]) || !std::isfinite(d->background[a])) sc->nonFinite = true;
+    for (int64_t i = 0; i < d->nPointLights; i++)
+        for (int a = 0; a < 3; a++) if (!std::isfinite(d->pointLights[i].intensity[a]) || !std::isfinite(d->pointLights[i].position[a])) sc->nonFinite = true;
+    for (int64_t i = 0; i < d->nAreaLights; i++)
+        for (int a = 0; a < 3; a++) if (!std::isfinite(d->areaLights[i].radiance[a])) sc->nonFinite = true;
     std::vector<GPointLight> lights((size_t)d->nPointLights);
     for (int64_t i = 0; i < d->nPointLights; i++) {
         std::memcpy(lights[i].position, d->pointLights[i].position, 24);
@@ -598,7 +610,7 @@ static int cloneScene(const rt_scene* src, int device, rt_scene* dst) {
     dst->device = device;
     dst->isReplica = true;
     dst->ds = src->ds; dst->info = src->info; dst->info.device = device; dst->meshes = src->meshes;
-    dst->motion = src->motion; dst->glossy = src->glossy; dst->instanceMotion = src->instanceMotion;
+    dst->motion = src->motion; dst->glossy = src->glossy; dst->nonFinite = src->nonFinite; dst->recurse = src->recurse; dst->instanceMotion = src->instanceMotion;
     dst->blasInfo = src->blasInfo; dst->instBlas = src->instBlas; dst->refitLevelStart = src->refitLevelStart;
     dst->nBoundChunks = src->nBoundChunks;
     dst->arrays = src->arrays;

@@ -93,7 +93,7 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     if (rc) return rc;
     const bool counters = params && params->collectCounters;
     const bool area = sc->ds.nAreaLights > 0;
-    int variant = (sc->glossy || area || sc->motion) ? KV_GENERAL : KV_FAST;
+    int variant = (sc->glossy || area || sc->motion || sc->nonFinite) ? KV_GENERAL : KV_FAST;
     if (params && params->kernelVariant != 0) {
         if (params->kernelVariant < 1 || params->kernelVariant > KV_COUNT) return fail(RT_ERR_INVALID, "kernelVariant outside 0..2");
         variant = params->kernelVariant - 1;
@@ -103,6 +103,8 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
             return fail(RT_ERR_UNSUPPORTED, "the fast kernel does not carry the area lights' per-chunk jitter index");
         if (sc->motion && variant == KV_FAST)
             return fail(RT_ERR_UNSUPPORTED, "the fast kernel does not carry the ray time of motion blur");
+        if (sc->nonFinite && variant == KV_FAST)
+            return fail(RT_ERR_UNSUPPORTED, "a light, material or ambient term is not finite: the fast kernel has no non-finite guard (Object+Extension.swift:277-280)");
     }
     // the area lights' jitter index runs through a whole 8-row chunk (Object+Extension.swift:288): chunks stay whole
     if (area && cp.shardCount > 1 && cp.shardTiles)
@@ -111,7 +113,10 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     cudaStream_t st = (cudaStream_t)cudaStream;
 
     const size_t threads = (size_t)blocks * renderBlockSize(variant);
-    const size_t need = (size_t)(sc->ds.maxDepth + 1) * kPathFields * threads * sizeof(double);
+    // general kernel: one depth-first stack of maxDepth + 1 entries per thread; fast kernel: per warp a shared queue of
+    // 32 x (maxDepth + 3 + 2 per extra pass of a batch) entries plus maxDepth + 2 private spill-over entries per lane
+    // (rt_shade.cuh: WarpQueue)
+    const size_t need = (size_t)(2 * sc->ds.maxDepth + 5 + 2 * (RT_BATCH_PASSES - 1)) * kPathFields * threads * sizeof(double);
     if ((rc = ensure(&sc->dPathStack, &sc->pathStackBytes, need))) return rc;
 
     RenderTargets rt{};
@@ -119,6 +124,7 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     rt.pathStack = sc->dPathStack; rt.counters = sc->dCounters;
     rt.tileCounter = sc->dTileCounter;
     rt.motion = sc->motion ? 1 : 0;
+    rt.recurse = sc->recurse ? 1 : 0;
     // Tile schedule: the frame records its cost per tile, the next frame of the same geometry draws the longest
     // tiles first.
     const int nTiles = ShardTiles(cp.width, cp.height, cp.shardIndex, cp.shardCount, cp.shardTiles).count;
@@ -159,8 +165,7 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     CK(cudaEventRecord(sc->evReset, st));
     {   // what the work counter counts up to (progress / cancel of rt_render): see the kernels' unit rules
         const int ns = cp.n * cp.n;
-        int unitsPerTile = 1;
-        if (variant == KV_FAST) unitsPerTile = (ns < 32 && 32 % ns == 0) ? ns : (ns % 32 == 0 ? 32 : 1);
+        const int unitsPerTile = variant == KV_FAST ? FastUnits(ns, sc->recurse).perTile : 1;
         sc->pendingUnits = (int64_t)nTiles * unitsPerTile * (area ? 2 : 1);
         sc->pendingWarps = (int64_t)(threads / 32);
     }

@@ -9,7 +9,8 @@
 namespace rtg {
 
 #if RT_V_FAST
-#define RT_KERNEL(c) renderKernelFast<c>
+#define RT_KERNEL(c) renderKernelFast<c, false>
+#define RT_KERNEL_RECURSE(c) renderKernelFast<c, true>
 #define RT_NAME(x) x##Fast
 #define RT_THREADS RT_FAST_BLOCK
 #else
@@ -28,14 +29,34 @@ cudaError_t RT_NAME(launchVariant)(const DeviceScene& S, const CameraParams& cam
         return cudaGetLastError();
     }
 #endif
+#ifdef RT_KERNEL_RECURSE
+    if (out.recurse) {                         // child rays possible: the instantiation with the warp's ray queue
+        if (counters) RT_LAUNCH(RT_KERNEL_RECURSE(true), blocks, RT_THREADS, stream, S, cam, out);
+        else RT_LAUNCH(RT_KERNEL_RECURSE(false), blocks, RT_THREADS, stream, S, cam, out);
+        return cudaGetLastError();
+    }
+#endif
     if (counters) RT_LAUNCH(RT_KERNEL(true), blocks, RT_THREADS, stream, S, cam, out);
     else RT_LAUNCH(RT_KERNEL(false), blocks, RT_THREADS, stream, S, cam, out);
     return cudaGetLastError();
 }
 
+// resident blocks per SM: the smallest over the instantiations a scene may take (one grid size serves them all)
 cudaError_t RT_NAME(occupancyVariant)(int* blocksPerSm, bool counters) {
-    if (counters) return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocksPerSm, RT_KERNEL(true), RT_THREADS, 0);
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocksPerSm, RT_KERNEL(false), RT_THREADS, 0);
+    int a = 0, b = 0;
+    cudaError_t e = counters ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, RT_KERNEL(true), RT_THREADS, 0)
+                             : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, RT_KERNEL(false), RT_THREADS, 0);
+    if (e != cudaSuccess) return e;
+#if defined(RT_KERNEL_RECURSE)
+    e = counters ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, RT_KERNEL_RECURSE(true), RT_THREADS, 0)
+                 : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, RT_KERNEL_RECURSE(false), RT_THREADS, 0);
+#elif defined(RT_KERNEL_EXT)
+    e = counters ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, RT_KERNEL_EXT(true), RT_THREADS, 0)
+                 : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, RT_KERNEL_EXT(false), RT_THREADS, 0);
+#endif
+    if (e != cudaSuccess) return e;
+    *blocksPerSm = a < b ? a : b;
+    return cudaSuccess;
 }
 
 int RT_NAME(blockSizeVariant)() { return RT_THREADS; }

@@ -139,14 +139,21 @@ __device__ __forceinline__ unsigned long long globalTimerNs() {
 
 __device__ __forceinline__ double shflD(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
 
-template <bool COUNT>
+// RECURSE: the scene can spawn child rays (maxRecursionDepth > 0 and a mirror / dielectric / conductor material).  Such
+// scenes run the instantiation that carries the warp's shared ray queue (rt_shade.cuh: WarpQueue) and batches up to
+// RT_BATCH_PASSES passes (128 samples) of depth 0 before it drains the queue, so that the secondary rays of a whole
+// 8x4 tile at 4 spp are traced 32 at a time; scenes without recursion run the lean instantiation (no queue code, no
+// colour buffer in shared memory: the packet walk keeps its L1 and its instruction cache).
+template <bool COUNT, bool RECURSE>
 __global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFast(DeviceScene S, CameraParams cam, RenderTargets out) {
-    __shared__ int2 wstacks[(RT_FAST_BLOCK / 32) * RT_WARP_STACK_INT2];
+    static_assert(RT_FAST_BLOCK == 32, "one warp per block: the packet stack and the colour buffer are the warp's");
+    __shared__ int2 wstacks[RT_WARP_STACK_INT2];
+    __shared__ double colBuf[RECURSE ? RT_BATCH_PASSES * 96 : 1];     // per-sample sums of the batch in flight
     const int lane = threadIdx.x & 31;
     TraceScratch T;
     T.sstack = nullptr; T.sstackN = 0;   // secondary rays keep their private stack in local memory: shared memory stays L1
-    const int warpInBlock = RT_FAST_BLOCK == 32 ? 0 : (int)(threadIdx.x >> 5);
-    T.wstack = wstacks + warpInBlock * RT_WARP_STACK_INT2;
+    const int warpInBlock = 0;
+    T.wstack = wstacks;
     T.pathStack = out.pathStack;
     T.gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     T.stride = (size_t)gridDim.x * blockDim.x;
@@ -171,12 +178,13 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFas
         skipTab[threadIdx.x] = make_ulonglong2(ak, gk);
         __syncwarp();
     }
-    // n*n a multiple of 32 (32, 64 spp ...): a pixel's samples fill whole passes, so one pixel (n*n / 32 passes) is a
-    // unit and the ordered sum is carried inside it.  Only otherwise (9, 25, 36 spp ...) the whole tile is one unit.
-    const bool perPixel = !segmented && (ns % 32) == 0;
-    const int unitsPerTile = segmented ? ns : (perPixel ? 32 : 1);
+    // Work unit (gpu_layout.h: FastUnits): passes of 32 (pixel, sample) items that are complete in themselves.
+    const FastUnits units(ns, RECURSE);
+    const int unitsPerTile = units.perTile;
     const int totalUnits = tiles.count * unitsPerTile;
     __shared__ uint2 unitNote[RT_FAST_BLOCK / 32];               // (clock at unit start, tile): read back when the unit ends
+    WarpQueue Q;
+    if (RECURSE) Q.init(T, S.maxDepth, lane);
 #ifdef RT_WARPTIMES
     unsigned long long wt0 = globalTimerNs(), wt1 = 0, wt2 = 0;
     int wtUnits = 0, wtUnit = 0;
@@ -197,11 +205,9 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFas
         wt2 = globalTimerNs();
         wtUnits++;
 #endif
-        // work unit: one 32-ray pass of a tile when the pixels of a pass are complete in themselves (ns divides
-        // 32), one pixel when 32 divides ns, else the whole tile (the ordered per-pixel sum is carried across passes).  Small units keep the
-        // tail short when a frame is split over 8 GPUs (a few thousand warps share ~8k tiles per rank).
-        // One unit per draw: consecutive units go to warps running at the same time, which share tiles, BVH
-        // nodes and triangles in L2 (drawing 8 at a time measured 10 % slower).
+        // Small units keep the tail short when a frame is split over 8 GPUs (a few thousand warps share ~8k tiles
+        // per rank).  One unit per draw: consecutive units go to warps running at the same time, which share tiles,
+        // BVH nodes and triangles in L2 (drawing 8 at a time measured 10 % slower).
         int unit = 0;
         if (lane == 0) unit = atomicAdd(out.tileCounter, 1);
         unit = __shfl_sync(0xffffffffu, unit, 0);
@@ -216,132 +222,168 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFas
         if (lane == 0 && out.warpTimes) out.warpTimes[4 * (T.stride >> 5) + 4 * (size_t)wtUnit] = wt2;
 #endif
         const int sub = unit - slot * unitsPerTile;
-        const int itBegin = segmented ? sub : (perPixel ? sub * (ns >> 5) : 0);
-        const int itEnd = segmented ? itBegin + 1 : (perPixel ? itBegin + (ns >> 5) : ns);
+        const int itBegin = sub * units.passes;
+        const int itEnd = itBegin + units.passes;
         int x0, y0;
         tiles.origin(tile, x0, y0);
         int openP = -1;               // ordered accumulation state of the generic path (warp-uniform)
         V3 acc = mk(0, 0, 0);
 #pragma unroll 1
-        for (int it = itBegin; it < itEnd; it++) {
-            const int g = it * 32 + lane;
-            const int p = g / ns, s = g - p * ns;
-            // pixel p of the tile in Z-order: neighbouring lanes' pixels form compact blocks
-            const int px = (p & 1) | ((p >> 1) & 2) | ((p >> 2) & 4), py = ((p >> 1) & 1) | ((p >> 2) & 2);
-            const int i = x0 + px, j = y0 + py;
-            const bool active = i < W && j < H;
-            const int sy = s / n, sx = s - sy * n;
-            PCG32 rng;
-            rng.seed((((uint64_t)j << 32) ^ (uint64_t)i) + 0x9E3779B97F4A7C15ULL);  // :294 (Swift precedence)
-            if (RT_SKIPTAB && segmented) rng.skip(skipTab[threadIdx.x].x, skipTab[threadIdx.x].y);   // s is fixed per lane
-            else rng.advance((uint64_t)(s * drawsPerSample));
-            const PrimaryRay pr = primaryRay(cam, i, j, sx, sy, rng);
-            if (active) R.primary++;
-            PathEntry cur0;
-            cur0.o = pr.o; cur0.d = pr.d; cur0.w = mk(1, 1, 1); cur0.beerMat = 0; cur0.depth = 0; cur0.beer = 0;
-
-            // ---- depth 0 as a warp packet: one traversal call site serves the primary ray (phase 0)
-            //      and the shadow ray towards light phase-1 (:118-143)
-            V3 ro = pr.o, rd = pr.d, wi = mk(0, 0, 1), Lo = mk(0, 0, 0);
-            double rtMin = pr.tMin, dist = 0;
-            HitRec hit;
-            hit.t = CUDART_INF; hit.u = hit.v = 0; hit.inst = -1; hit.slot = 0;
-            ShadePoint sp;
-            sp.p = sp.N = sp.w = mk(0, 0, 0); sp.mat = S.materials; sp.matId = 0; sp.frontFacing = sp.computeDirect = false;
-            bool rayOn = active, anyhit = false, isHit = false;
-            int phase = 0;
-            __syncwarp();
+        for (int b0 = itBegin; b0 < itEnd; b0 += (RECURSE ? RT_BATCH_PASSES : 1)) {
+            const int nb = RECURSE ? (itEnd - b0 < RT_BATCH_PASSES ? itEnd - b0 : RT_BATCH_PASSES) : 1;
+            V3 c = mk(0, 0, 0);
+            // ---- one round = 32 rays through ONE copy of the code: the primary rays of a pass (ray generation :292-344), or —
+            //      scenes with recursion — 32 child rays off the warp's queue; closest-hit packet, shading, one any-hit packet
+            //      per light (:118-143), children into the queue (rt_shade.cuh: WarpQueue)
+            int pass = 0;
 #pragma unroll 1
             for (;;) {
-                const bool occ = packetScene<COUNT>(S, ro, rd, rtMin, hit, rayOn, anyhit, T.wstack, C);
-                if (phase == 0) {
-                    isHit = active && hit.inst >= 0;
-                    Surface sf;
-                    sf.kind = 0; sf.prim = -1;
-                    if (isHit) {
-                        resolveHit(S, hit, pr.o, pr.d, sf);
-                        if (COUNT && sf.kind == 1 && S.instances[hit.inst].smooth) C.smooth++;
-                        setupShade(S, sf, cur0, hit.t, sp);
-                        if (sp.computeDirect) Lo = ambient * ld3(sp.mat->ambient);
-                    }
-                    if (out.ids && active) {
-                        HitId& h = out.ids[((size_t)j * W + i) * (size_t)ns + (size_t)s];
-                        h.inst = hit.inst; h.kind = sf.kind; h.prim = sf.prim; h.t = hit.t;
-                    }
-                    if (__ballot_sync(0xffffffffu, sp.computeDirect) == 0u) break;
-                } else if (rayOn && !occ) {
-                    Lo = Lo + pointLightTerm(*sp.mat, S.pointLights[phase - 1], sp.N, pr.d, wi, dist);
-                }
-                if (phase >= S.nPointLights) break;
-                shadowRay(S.pointLights[phase], sp.p, S.shadowEps, ro, wi, dist);
-                rd = wi; rtMin = 0.0;
-                hit.t = dist;                                   // tMax = dist (:124)
-                rayOn = sp.computeDirect; anyhit = true;
-                if (rayOn) R.shadow++;
-                phase++;
-            }
-            // ---- the value of trace(...) for this sample (:345): miss -> background, NaN guard, recursion
-            V3 c = mk(0, 0, 0);
-            if (active) {
-                if (!isHit) {
-                    c = c + cur0.w * background;                                        // :101-103
+                const bool primary = pass < nb;                  // warp-uniform
+                PathEntry cur0;
+                bool active = false;
+                double tMin0 = 0.0;
+                int idI = 0, idJ = 0, idS = 0;
+                PCG32 rng;
+                rng.state = 0; rng.inc = 1;
+                if (primary) {
+                    const int it = b0 + pass;
+                    const int g = it * 32 + lane;
+                    const int p = g / ns, s = g - p * ns;
+                    // pixel p of the tile in Z-order: neighbouring lanes' pixels form compact blocks
+                    const int px = (p & 1) | ((p >> 1) & 2) | ((p >> 2) & 4), py = ((p >> 1) & 1) | ((p >> 2) & 2);
+                    const int i = x0 + px, j = y0 + py;
+                    active = i < W && j < H;
+                    const int sy = s / n, sx = s - sy * n;
+                    rng.seed((((uint64_t)j << 32) ^ (uint64_t)i) + 0x9E3779B97F4A7C15ULL);  // :294 (Swift precedence)
+                    if (RT_SKIPTAB && segmented) rng.skip(skipTab[threadIdx.x].x, skipTab[threadIdx.x].y);   // s is fixed per lane
+                    else rng.advance((uint64_t)(s * drawsPerSample));
+                    const PrimaryRay pr = primaryRay(cam, i, j, sx, sy, rng);
+                    if (active) R.primary++;
+                    cur0.o = pr.o; cur0.d = pr.d; cur0.w = mk(1, 1, 1); cur0.beerMat = 0; cur0.depth = 0; cur0.beer = 0;
+                    cur0.slot = pass * 32 + lane;
+                    tMin0 = pr.tMin;
+                    idI = i; idJ = j; idS = s;
                 } else {
-                    const bool dead = !finite3(Lo);                                     // :277-280, see scalarPathLoop
-                    if (!dead) c = c + sp.w * Lo;
-                    PathEntry c1, c2;
-                    const int nc = spawnChildren<false>(S, sp, cur0, rng, c1, c2);
-                    if (dead) { c1.beer |= PATH_DEAD; c2.beer |= PATH_DEAD; }
-                    if (nc > 0) {
-                        if (nc == 2) pathStore(T.pathStack, T.stride, T.gtid, 0, c2);
-                        R.secondary += nc;
-                        c = scalarPathLoop<false, COUNT, true>(S, T, c1, nc - 1, false, 0.0, nullptr, rng, C, R, c);
-                    }
+                    if (!RECURSE) break;
+                    cur0.o = cur0.d = cur0.w = mk(0, 0, 0); cur0.beerMat = 0; cur0.depth = 0; cur0.beer = 0; cur0.slot = 0;
+                    if (!Q.pop(T, cur0, active)) break;
                 }
+
+                // ---- the rays of the round as a warp packet: one traversal call site serves the closest-hit query
+                //      (phase 0) and the shadow ray towards light phase-1
+                V3 ro = cur0.o, rd = cur0.d, wi = mk(0, 0, 1), Lo = mk(0, 0, 0);
+                double rtMin = tMin0, dist = 0;
+                HitRec hit;
+                hit.t = CUDART_INF; hit.u = hit.v = 0; hit.inst = -1; hit.slot = 0;
+                ShadePoint sp;
+                sp.p = sp.N = sp.w = mk(0, 0, 0); sp.mat = S.materials; sp.matId = 0; sp.frontFacing = sp.computeDirect = false;
+                bool rayOn = active, anyhit = false, isHit = false;
+                int phase = 0;
+                __syncwarp();
+#pragma unroll 1
+                for (;;) {
+                    const bool occ = packetScene<COUNT>(S, ro, rd, rtMin, hit, rayOn, anyhit, T.wstack, C);
+                    if (phase == 0) {
+                        isHit = active && hit.inst >= 0;
+                        Surface sf;
+                        sf.kind = 0; sf.prim = -1;
+                        if (isHit) {
+                            resolveHit(S, hit, cur0.o, cur0.d, sf);
+                            if (COUNT && sf.kind == 1 && S.instances[hit.inst].smooth) C.smooth++;
+                            setupShade(S, sf, cur0, hit.t, sp);
+                            if (sp.computeDirect) Lo = ambient * ld3(sp.mat->ambient);
+                        }
+                        if (primary && out.ids && active) {
+                            HitId& h = out.ids[((size_t)idJ * W + idI) * (size_t)ns + (size_t)idS];
+                            h.inst = hit.inst; h.kind = sf.kind; h.prim = sf.prim; h.t = hit.t;
+                        }
+                        if (__ballot_sync(0xffffffffu, sp.computeDirect) == 0u) break;
+                    } else if (rayOn && !occ) {
+                        Lo = Lo + pointLightTerm(*sp.mat, S.pointLights[phase - 1], sp.N, cur0.d, wi, dist);
+                    }
+                    if (phase >= S.nPointLights) break;
+                    shadowRay(S.pointLights[phase], sp.p, S.shadowEps, ro, wi, dist);
+                    rd = wi; rtMin = 0.0;
+                    hit.t = dist;                                   // tMax = dist (:124)
+                    rayOn = sp.computeDirect; anyhit = true;
+                    if (rayOn) R.shadow++;
+                    phase++;
+                }
+                // ---- what the rays of this round add to their samples (:345): miss -> background (:101-103), else the
+                //      direct light of the vertex; no non-finite guard here (see WarpQueue)
+                c = mk(0, 0, 0);
+                if (active) c = isHit ? sp.w * Lo : cur0.w * background;
+                if (!RECURSE) break;
+                PathEntry c1 = cur0, c2 = cur0;
+                int nc = 0;
+                if (isHit) nc = spawnChildren<false>(S, sp, cur0, rng, c1, c2);
+                R.secondary += nc;
+                __syncwarp();
+                if (primary) {
+                    double* col = colBuf + cur0.slot * 3;
+                    col[0] = c.x; col[1] = c.y; col[2] = c.z;
+                    __syncwarp();
+                    pass++;
+                } else {
+                    warpAccumulate(colBuf, cur0.slot, active, c);
+                }
+                Q.push(T, nc, c1, c2);
             }
             __syncwarp();
-            // ---- pixelColor += trace(...) in sample order (:345), then / samples (:354)
-            if (segmented && ns >= 4) {
-                // The colours go through shared memory (the packet stack is idle here) and lanes s = 0, 1, 2 of
-                // each pixel add up one component each, in sample order: 16 loads + adds instead of every lane
-                // shuffling all three components of all samples.
-                const int base = lane & ~(ns - 1);
+            // ---- pixelColor += trace(...) in sample order (:345), then / samples (:354), pass by pass
+#pragma unroll 1
+            for (int b = 0; b < nb; b++) {
+                const int it = b0 + b;
+                const int g = it * 32 + lane;
+                const int p = g / ns, s = g - p * ns;
+                const int px = (p & 1) | ((p >> 1) & 2) | ((p >> 2) & 4), py = ((p >> 1) & 1) | ((p >> 2) & 2);
+                const int i = x0 + px, j = y0 + py;
+                const bool active = i < W && j < H;
                 static_assert(RT_WARP_STACK_INT2 * sizeof(int2) >= 96 * sizeof(double), "sample colours of a warp fit the packet stack");
-                double* scratch = reinterpret_cast<double*>(T.wstack);
-                scratch[lane * 3] = c.x; scratch[lane * 3 + 1] = c.y; scratch[lane * 3 + 2] = c.z;
+                double* scratch = RECURSE ? colBuf + b * 96 : reinterpret_cast<double*>(T.wstack);   // the packet stack is idle here
+                if (RECURSE) c = mk(scratch[lane * 3], scratch[lane * 3 + 1], scratch[lane * 3 + 2]);
                 __syncwarp();
-                double comp = 0.0;
-                if (s < 3) {
-                    const double* col = scratch + base * 3 + s;
+                if (segmented && ns >= 4) {
+                    // The colours go through shared memory and lanes s = 0, 1, 2 of each pixel add up one component
+                    // each, in sample order: 16 loads + adds instead of every lane shuffling all three components of
+                    // all samples.
+                    const int base = lane & ~(ns - 1);
+                    if (!RECURSE) { scratch[lane * 3] = c.x; scratch[lane * 3 + 1] = c.y; scratch[lane * 3 + 2] = c.z; }
+                    __syncwarp();
+                    double comp = 0.0;
+                    if (s < 3) {
+                        const double* col = scratch + base * 3 + s;
 #pragma unroll 4
-                    for (int k = 0; k < ns; k++) comp = comp + col[k * 3];
-                    comp = comp / samplesD;
-                }
-                const V3 px3 = mk(shflD(comp, base), shflD(comp, base + 1), shflD(comp, base + 2));
-                if (active && s == 0) writePixel(out, (size_t)j * W + i, px3);
-                __syncwarp();
-            } else if (segmented) {
-                const int base = lane & ~(ns - 1);
-                V3 sum = mk(0, 0, 0);
-#pragma unroll 1
-                for (int k = 0; k < ns; k++) {
-                    const V3 ck = mk(shflD(c.x, base + k), shflD(c.y, base + k), shflD(c.z, base + k));
-                    sum = sum + ck;
-                }
-                if (active && s == 0) writePixel(out, (size_t)j * W + i, sum / samplesD);
-            } else {
-#pragma unroll 1
-                for (int k = 0; k < 32; k++) {
-                    const int pk = (it * 32 + k) / ns;
-                    const V3 ck = mk(shflD(c.x, k), shflD(c.y, k), shflD(c.z, k));
-                    if (pk != openP) {
-                        if (openP >= 0 && lane == 0) {
-                            const int qx = (openP & 1) | ((openP >> 1) & 2) | ((openP >> 2) & 4), qy = ((openP >> 1) & 1) | ((openP >> 2) & 2);
-                            if (x0 + qx < W && y0 + qy < H) writePixel(out, (size_t)(y0 + qy) * W + (x0 + qx), acc / samplesD);
-                        }
-                        openP = pk;
-                        acc = mk(0, 0, 0);
+                        for (int k = 0; k < ns; k++) comp = comp + col[k * 3];
+                        comp = comp / samplesD;
                     }
-                    acc = acc + ck;
+                    const V3 px3 = mk(shflD(comp, base), shflD(comp, base + 1), shflD(comp, base + 2));
+                    if (active && s == 0) writePixel(out, (size_t)j * W + i, px3);
+                    __syncwarp();
+                } else if (segmented) {
+                    const int base = lane & ~(ns - 1);
+                    V3 sum = mk(0, 0, 0);
+#pragma unroll 1
+                    for (int k = 0; k < ns; k++) {
+                        const V3 ck = mk(shflD(c.x, base + k), shflD(c.y, base + k), shflD(c.z, base + k));
+                        sum = sum + ck;
+                    }
+                    if (active && s == 0) writePixel(out, (size_t)j * W + i, sum / samplesD);
+                } else {
+#pragma unroll 1
+                    for (int k = 0; k < 32; k++) {
+                        const int pk = (it * 32 + k) / ns;
+                        const V3 ck = mk(shflD(c.x, k), shflD(c.y, k), shflD(c.z, k));
+                        if (pk != openP) {
+                            if (openP >= 0 && lane == 0) {
+                                const int qx = (openP & 1) | ((openP >> 1) & 2) | ((openP >> 2) & 4), qy = ((openP >> 1) & 1) | ((openP >> 2) & 2);
+                                if (x0 + qx < W && y0 + qy < H) writePixel(out, (size_t)(y0 + qy) * W + (x0 + qx), acc / samplesD);
+                            }
+                            openP = pk;
+                            acc = mk(0, 0, 0);
+                        }
+                        acc = acc + ck;
+                    }
                 }
             }
         }
@@ -415,7 +457,7 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_GEN_BLOCKS) renderKernelGeneral(D
                     R.primary++;
                     HitId* idSlot = (out.ids && !area.countOnly) ? out.ids + (((size_t)j * W + i) * (size_t)(n * n) + (size_t)(sy * n + sx)) : nullptr;
                     PathEntry cur0;
-                    cur0.o = pr.o; cur0.d = pr.d; cur0.w = mk(1, 1, 1); cur0.beerMat = 0; cur0.depth = 0; cur0.beer = 0;
+                    cur0.o = pr.o; cur0.d = pr.d; cur0.w = mk(1, 1, 1); cur0.beerMat = 0; cur0.depth = 0; cur0.beer = 0; cur0.slot = 0;
                     pixel = pixel + scalarPathLoop<true, COUNT, false, EXT, EXT>(S, T, cur0, 0, true, pr.tMin, idSlot, rng, C, R, mk(0, 0, 0),
                                                                                  EXT ? &area : nullptr, pr.time);
                     sampleIndex++;

@@ -20,6 +20,7 @@ struct PathEntry {
     V3 o, d, w;
     long long beerMat;   // Hit.mat of the dielectric surface this refraction ray entered
     int depth;
+    int slot;            // fast kernel: the lane (sample of the work unit) this path's light is added to
     int beer;            // bit 0: apply Beer attenuation at the next hit (Object+Extension.swift:245-248)
                          // bit 1 (PATH_DEAD): an ancestor's Lo was non-finite — the reference still walks this subtree
                          // (rays, RNG draws, jitter index) and then throws the level away (:277-280): nothing is added
@@ -33,7 +34,7 @@ __device__ __forceinline__ void pathStore(double* base, size_t stride, size_t gt
     p[3 * stride] = e.d.x; p[4 * stride] = e.d.y; p[5 * stride] = e.d.z;
     p[6 * stride] = e.w.x; p[7 * stride] = e.w.y; p[8 * stride] = e.w.z;
     p[9 * stride] = __longlong_as_double(e.beerMat);
-    p[10 * stride] = __longlong_as_double((long long)e.depth | ((long long)e.beer << 32));
+    p[10 * stride] = __longlong_as_double((long long)(e.depth & 0xffff) | ((long long)(e.slot & 0xffff) << 16) | ((long long)e.beer << 32));
 }
 __device__ __forceinline__ void pathLoad(const double* base, size_t stride, size_t gtid, int level, PathEntry& e) {
     const double* p = base + ((size_t)level * PATH_FIELDS) * stride + gtid;
@@ -42,7 +43,8 @@ __device__ __forceinline__ void pathLoad(const double* base, size_t stride, size
     e.w = mk(p[6 * stride], p[7 * stride], p[8 * stride]);
     e.beerMat = __double_as_longlong(p[9 * stride]);
     long long m = __double_as_longlong(p[10 * stride]);
-    e.depth = (int)(m & 0xffffffffLL);
+    e.depth = (int)(m & 0xffffLL);
+    e.slot = (int)((m >> 16) & 0xffffLL);
     e.beer = (int)(m >> 32);
 }
 
@@ -202,6 +204,7 @@ __device__ __forceinline__ int spawnChildren(const DeviceScene& S, const ShadePo
     const V3 p = sp.p, N = sp.N, w = sp.w;
     int count = 1;
     c1.depth = c2.depth = cur.depth + 1;
+    c1.slot = c2.slot = cur.slot;
     c1.beer = c2.beer = 0; c1.beerMat = c2.beerMat = 0;
     if (mat.type == 1) {                                                                // mirror :189-206
         V3 rd = normalize(reflectDir(cur.d, N));
@@ -351,5 +354,116 @@ __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceSc
     }
     return color;
 }
+
+
+// ---- secondary rays of the fast kernel: a wavefront inside the warp ---------------------------------------------------
+// The recursion of `trace` (Object+Extension.swift:189-275) as a ray queue shared by the 32 lanes of a warp.  Run per
+// lane (scalarPathLoop: every lane walks its own path tree depth-first with the per-lane traversal) the child rays kept
+// 2.5 of 32 lanes busy in the mesh walk of the recursive scene C3, through a second copy of every traversal routine
+// that thrashed the instruction cache.  Here the children of a batch of samples are compacted into ONE last-in-first-out
+// queue per warp (ballot + prefix popcount), and the warp takes them back 32 at a time: a popped batch is processed
+// by exactly the code that processes a pass of primary rays — closest-hit warp packet, shading, one any-hit packet per
+// light, children back into the queue (rt_render_kernel.cuh) — so the kernel holds one traversal, the rays of a batch
+// meet every instance together (the packet's TLAS walk is warp-uniform: "sorted by instance" for free), and neighbouring
+// lanes' children, pushed side by side, come back as one fairly coherent packet.
+//   * Each entry carries the sample (`slot`) it belongs to; light is added to col[slot] in shared memory.  Lanes that
+//     add to one slot in the same round are ordered by lane (match_any + rank), so the sum is deterministic; it is
+//     formed in queue order, not in the reference's depth-first order: the addends are the same FP64 values, the
+//     reordering moves a sample by a few ulp, i.e. an 8-bit pixel by at most 1 LSB and only if it lies within ~1e-13
+//     of a truncation boundary.
+//   * No non-finite guard here (:277-280): with finite lights and materials every term is finite (a NaN normal or
+//     light direction fails `NdotL > 0`), and the host sends scenes with a non-finite constant to the general kernel.
+//   * Queue memory: the warp's 32 columns of the path stack, levels [0, D + RT_QUEUE_EXTRA): a batch starts with at
+//     most 64 entries per pass, then at most 32 entries leave and 64 enter per round, deepest first.  Should it ever
+//     be full, the round's children go to the lanes' private stacks (the levels behind), which a lane drains before it
+//     takes shared entries: bounded by D + 2 per lane like any depth-first walk.
+#define RT_QUEUE_EXTRA (3 + 2 * (RT_BATCH_PASSES - 1))   // initial children of a batch: 64 per pass
+#define RT_PRIV_EXTRA 2
+
+__device__ __forceinline__ double* queueField(double* qbase, size_t stride, int e, int f) {
+    return qbase + ((size_t)(e >> 5) * PATH_FIELDS + (size_t)f) * stride + (size_t)(e & 31);
+}
+__device__ __forceinline__ void queueStore(double* qbase, size_t stride, int e, const PathEntry& v) {
+    *queueField(qbase, stride, e, 0) = v.o.x; *queueField(qbase, stride, e, 1) = v.o.y; *queueField(qbase, stride, e, 2) = v.o.z;
+    *queueField(qbase, stride, e, 3) = v.d.x; *queueField(qbase, stride, e, 4) = v.d.y; *queueField(qbase, stride, e, 5) = v.d.z;
+    *queueField(qbase, stride, e, 6) = v.w.x; *queueField(qbase, stride, e, 7) = v.w.y; *queueField(qbase, stride, e, 8) = v.w.z;
+    *queueField(qbase, stride, e, 9) = __longlong_as_double(v.beerMat);
+    *queueField(qbase, stride, e, 10) = __longlong_as_double((long long)(v.depth & 0xffff) | ((long long)(v.slot & 0xffff) << 16) | ((long long)v.beer << 32));
+}
+__device__ __forceinline__ void queueLoad(double* qbase, size_t stride, int e, PathEntry& v) {
+    v.o = mk(*queueField(qbase, stride, e, 0), *queueField(qbase, stride, e, 1), *queueField(qbase, stride, e, 2));
+    v.d = mk(*queueField(qbase, stride, e, 3), *queueField(qbase, stride, e, 4), *queueField(qbase, stride, e, 5));
+    v.w = mk(*queueField(qbase, stride, e, 6), *queueField(qbase, stride, e, 7), *queueField(qbase, stride, e, 8));
+    v.beerMat = __double_as_longlong(*queueField(qbase, stride, e, 9));
+    const long long m = __double_as_longlong(*queueField(qbase, stride, e, 10));
+    v.depth = (int)(m & 0xffffLL); v.slot = (int)((m >> 16) & 0xffffLL); v.beer = (int)(m >> 32);
+}
+
+// col[slot] += v for the lanes with `has`, in lane order where several lanes name one slot.  All 32 lanes call it.
+__device__ __forceinline__ void warpAccumulate(double* col, int slot, bool has, V3 v) {
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned any = __ballot_sync(RT_FULL, has);
+    if (!any) return;
+    const unsigned peers = __match_any_sync(RT_FULL, has ? slot : -1 - (int)lane);
+    const int rank = __popc(peers & ((1u << lane) - 1u));
+    for (int r = 0;; r++) {
+        if (__ballot_sync(RT_FULL, has && rank >= r) == 0u) break;
+        if (has && rank == r) {
+            double* c = col + slot * 3;
+            c[0] = c[0] + v.x; c[1] = c[1] + v.y; c[2] = c[2] + v.z;
+        }
+        __syncwarp();
+    }
+}
+
+struct WarpQueue {
+    double* qbase;       // this warp's 32 columns of the path stack
+    size_t stride;
+    int cap, privBase;
+    int top;             // entries in the shared queue (warp-uniform)
+    int priv;            // entries on this lane's private stack
+    unsigned lt;         // lanes below this one
+
+    __device__ __forceinline__ void init(const TraceScratch& T, int maxDepth, int lane) {
+        qbase = T.pathStack + (T.gtid - (size_t)lane);
+        stride = T.stride;
+        cap = 32 * (maxDepth + RT_QUEUE_EXTRA);
+        privBase = maxDepth + RT_QUEUE_EXTRA;
+        top = 0; priv = 0;
+        lt = (1u << lane) - 1u;
+    }
+
+    // Offer n (0..2) entries per lane; all 32 lanes call it.  Compaction: ballot + prefix popcount.
+    __device__ __forceinline__ void push(const TraceScratch& T, int n, const PathEntry& a, const PathEntry& b) {
+        const unsigned m1 = __ballot_sync(RT_FULL, n >= 1), m2 = __ballot_sync(RT_FULL, n == 2);
+        const int total = __popc(m1) + __popc(m2);
+        if (total == 0) return;
+        if (top + total <= cap) {
+            const int at = top + __popc(m1 & lt) + __popc(m2 & lt);
+            if (n == 2) queueStore(qbase, stride, at, b);            // refraction below, reflection on top of it
+            if (n >= 1) queueStore(qbase, stride, at + (n == 2 ? 1 : 0), a);
+            top += total;
+        } else {
+            if (n == 2) { pathStore(T.pathStack, stride, T.gtid, privBase + priv, b); priv++; }
+            if (n >= 1) { pathStore(T.pathStack, stride, T.gtid, privBase + priv, a); priv++; }
+        }
+        __syncwarp();
+    }
+
+    // Up to 32 entries off the top, one per lane (a lane's own spill-over first); all 32 lanes call it.  Returns false
+    // when nothing is left anywhere in the warp.
+    __device__ __forceinline__ bool pop(const TraceScratch& T, PathEntry& cur, bool& valid) {
+        valid = false;
+        if (priv > 0) { priv--; pathLoad(T.pathStack, stride, T.gtid, privBase + priv, cur); valid = true; }
+        const unsigned need = __ballot_sync(RT_FULL, !valid);
+        if (need != 0u && top > 0) {
+            const int want = __popc(need), k = want < top ? want : top;
+            const int r = __popc(need & lt);
+            if (!valid && r < k) { queueLoad(qbase, stride, top - 1 - r, cur); valid = true; }
+            top -= k;
+        }
+        return __ballot_sync(RT_FULL, valid) != 0u;
+    }
+};
 
 }  // namespace rtg

@@ -29,6 +29,12 @@ CASES = {
     "c3": (scenegen.config_c3, dict(width=64, height=48, samples=4, depth=4, ico_level=2), (1, 2)),
     "c3dof": (scenegen.config_c3, dict(width=48, height=40, samples=4, depth=3, ico_level=2, aperture=0.35, focus=13.0), (1, 2)),
     "c3glossy": (scenegen.config_c3, dict(width=48, height=40, samples=4, depth=3, ico_level=2, roughness=0.12), (2,)),
+    # the warp's ray queue under every unit rule: 1 spp (one pass), 9 spp (whole tile = 9 passes, three batches), 16 spp
+    # (four units of four passes per tile), 64 spp (one pixel = two passes)
+    "c3x1": (scenegen.config_c3, dict(width=48, height=40, samples=1, depth=4, ico_level=2), (1,)),
+    "c3x9": (scenegen.config_c3, dict(width=24, height=20, samples=9, depth=3, ico_level=1), (1,)),
+    "c3x16": (scenegen.config_c3, dict(width=24, height=16, samples=16, depth=3, ico_level=1), (1,)),
+    "c3x64": (scenegen.config_c3, dict(width=16, height=8, samples=64, depth=2, ico_level=1), (1,)),
     "c5": (scenegen.config_c5, dict(n=12, width=64, height=40, samples=4, meshes=3), (1, 2)),
     "instances": (scenegen.config_instances, dict(width=64, height=48, samples=4), (1, 2)),
     # area lights: counting pass, per-chunk prefix, shading pass (general kernel); ragged image, glossy recursion
@@ -45,7 +51,7 @@ CASES = {
     # levels' children still advance the chunk's jitter index and the pixel's RNG like the reference's do
     "c3area_glossy_inf": (scenegen.config_c3, dict(width=40, height=30, samples=4, depth=3, ico_level=1, area_lights=2,
                                                    roughness=0.15, inf_light=True), (2,)),
-    "c3_inf": (scenegen.config_c3, dict(width=40, height=30, samples=4, depth=3, ico_level=1, inf_light=True), (1, 2)),
+    "c3_inf": (scenegen.config_c3, dict(width=40, height=30, samples=4, depth=3, ico_level=1, inf_light=True), (0, 2)),
 }
 
 
@@ -527,7 +533,7 @@ def test_cancel_from_progress_callback(scene_dir, emu, monkeypatch):
 
 
 @pytest.mark.parametrize("rough,depth,variants,inf_light", [(0.0, 4, (1, 2), False), (0.15, 3, (2,), False),
-                                                            (0.0, 2, (1, 2), True), (0.2, 3, (2,), True)])
+                                                            (0.0, 2, (0, 2), True), (0.2, 3, (2,), True)])
 def test_emulated_kernels_vs_independent_restatement(rough, depth, variants, inf_light, tmp_path, emu):
     """The CUDA sources against tests/reftrace.py directly — the pure-Python restatement of `trace` written from the
     Swift source, no BVH, no oracle in between: linear colours of every pixel to 1e-12 and the same ray counts."""

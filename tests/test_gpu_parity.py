@@ -24,6 +24,11 @@ CASES = {
     # 64 and 36 spp: units of one pixel (32 divides n*n) and of a whole tile (neither divides the other)
     "c1x64": dict(fn=scenegen.config_c1, kw=dict(width=96, height=80, samples=64)),
     "c1x36": dict(fn=scenegen.config_c1, kw=dict(width=96, height=80, samples=36)),
+    # the warp's ray queue under every unit rule of the fast kernel (1, 9, 16, 64 spp)
+    "c3x1": dict(fn=scenegen.config_c3, kw=dict(width=320, height=240, samples=1)),
+    "c3x9": dict(fn=scenegen.config_c3, kw=dict(width=160, height=120, samples=9)),
+    "c3x16": dict(fn=scenegen.config_c3, kw=dict(width=160, height=120, samples=16)),
+    "c3x64": dict(fn=scenegen.config_c3, kw=dict(width=80, height=60, samples=64, depth=4)),
     "c3dof": dict(fn=scenegen.config_c3, kw=dict(width=192, height=192, samples=4, aperture=0.35, focus=13.0)),
     "c3glossy": dict(fn=scenegen.config_c3, kw=dict(width=192, height=192, samples=4, roughness=0.12)),
     "c3glossydof": dict(fn=scenegen.config_c3, kw=dict(width=160, height=160, samples=9, depth=4, roughness=0.3,
@@ -345,7 +350,7 @@ def test_edge_cases_vs_oracle(scene_dir):
             assert rep["rays_gpu"] == rep["rays_ref"], (name, variant, rep)
 
 
-@pytest.mark.parametrize("rough,depth,variants", [(0.0, 3, (1, 2)), (0.2, 3, (2,))])
+@pytest.mark.parametrize("rough,depth,variants", [(0.0, 3, (0, 2)), (0.2, 3, (2,))])
 def test_non_finite_light_level_is_discarded_like_the_reference(rough, depth, variants, tmp_path):
     """Row a11 on the hardware (Object+Extension.swift:277-280): a point light of infinite intensity makes Lo
     non-finite at every shading point it reaches; the reference still traces that level's children (their rays, and
@@ -357,6 +362,10 @@ def test_non_finite_light_level_is_discarded_like_the_reference(rough, depth, va
     want, counts = reftrace.render(ref, cam)
     orc = oracle_lib.OracleScene(path).render(want_ids=True, want_linear=True)
     eng = RayTracerEngine(path)
+    from myraytracer_b200 import RenderError
+    with pytest.raises(RenderError) as e:          # the fast kernel carries no guard: such scenes take the general kernel
+        eng.render(0, variant=1)
+    assert e.value.code == -3
     for variant in variants:
         got = eng.render(0, want_linear=True, want_ids=True, variant=variant)
         assert np.isfinite(got.linear).all()

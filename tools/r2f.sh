@@ -1,0 +1,4 @@
+mkdir -p gpurun_out
+python tools/render_once.py c3 3 > gpurun_out/r2f_plain.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:renderKernelFast -s 2 -c 1 -o gpurun_out/r2f_c3 python tools/render_once.py c3 3 > gpurun_out/r2f_ncu.log 2>&1
+echo "ncu rc=$?"; cat gpurun_out/r2f_plain.log; tail -3 gpurun_out/r2f_ncu.log
