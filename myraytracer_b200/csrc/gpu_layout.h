@@ -33,6 +33,7 @@ namespace rtg {
 // needs nothing from the instance record inside its loop.
 static const int32_t kEmptyRef = 0x7fffffff;
 static const int kMaxLeaf = 4;
+static const int kBigBlasTriangles = 16384;
 
 struct RT_ALIGN(16) GNode {
     // q0 = lo0.x lo0.y lo0.z hi0.x | q1 = hi0.y hi0.z lo1.x lo1.y | q2 = lo1.z hi1.x hi1.y hi1.z
@@ -77,7 +78,8 @@ struct RT_ALIGN(16) GInstance {
     int32_t triF64;        // 1: GTriD array, 0: GTri array
     int32_t rootRef;       // child reference of the BLAS root (inner node 0 or a leaf)
     int32_t hasMotion;     // instanceMotion != 0 or mesh motion blur != 0
-    int32_t pad[3];
+    int32_t bigBlas;       // mesh with more than kBigBlasTriangles triangles: incoherent packets walk it per lane (rt_packet.cuh)
+    int32_t pad[2];
     double meshMotion[3];  // Triangle.motionBlur of this mesh
     double pad2;
 };
@@ -185,12 +187,15 @@ struct ShardTiles {
 // 8x4 tile.  ns = samples per pixel.  ns divides 32: a pass holds whole pixels, so one pass is a unit — or, for
 // scenes with recursion, up to RT_BATCH_PASSES passes, whose child rays are then traced together; 32 divides ns: the
 // ns / 32 passes of one pixel; otherwise the whole tile (the ordered per-pixel sum is carried across its ns passes).
-#define RT_BATCH_PASSES 4
+#ifndef RT_BATCH_PASSES
+#define RT_BATCH_PASSES 1    // measured on C3 (B200): 1 -> 6.0 ms, 2 -> 9.8 ms, 4 -> 17.5 ms: a unit's rounds are serial, long units are the tail
+#endif
 struct FastUnits {
-    int passes, perTile;
+    int passes, perTile, perPixel;
     RT_HD FastUnits(int ns, bool recurse) {
+        perPixel = 0;
         if (ns < 32 && 32 % ns == 0) { passes = recurse ? (ns < RT_BATCH_PASSES ? ns : RT_BATCH_PASSES) : 1; perTile = ns / passes; }
-        else if (ns % 32 == 0) { passes = ns >> 5; perTile = 32; }
+        else if (ns % 32 == 0) { passes = ns >> 5; perTile = 32; perPixel = 1; }
         else { passes = ns; perTile = 1; }
     }
 };

@@ -152,6 +152,7 @@ struct rt_scene {
     bool sideBusy = false;
     int blocks[KV_COUNT][2] = {};      // [variant][counters]
     bool glossy = false;               // some material has roughness != 0: RNG draws inside trace
+    int64_t bigBlasTriangles = kBigBlasTriangles;   // meshes above this size are walked per lane by incoherent packets (RTCUDA_BIG_BLAS overrides: tests)
     bool recurse = false;              // maxRecursionDepth > 0 and a mirror / dielectric / conductor material: child rays exist
     bool nonFinite = false;            // a light / material / ambient constant is inf or NaN: the non-finite guard of `trace` can fire
     int pendingVariant = 0;
@@ -163,7 +164,7 @@ struct rt_scene {
 
 
 // Instance (RTContext.swift:43-61) -> device record
-static void fillInstance(const rt_instance& in, const BlasInfo& bi, GInstance& g) {
+static void fillInstance(const rt_instance& in, const BlasInfo& bi, GInstance& g, int64_t bigBlasTriangles = kBigBlasTriangles) {
     std::memset(&g, 0, sizeof g);
     for (int c = 0; c < 4; c++)
         for (int r = 0; r < 3; r++) { g.w2l[c * 3 + r] = in.worldToLocal[c * 4 + r]; g.l2w[c * 3 + r] = in.localToWorld[c * 4 + r]; }
@@ -178,6 +179,7 @@ static void fillInstance(const rt_instance& in, const BlasInfo& bi, GInstance& g
     g.flipNormal = ((c0[0] * cx + c0[1] * cy) + c0[2] * cz) < 0.0 ? 1 : 0;
     g.smooth = bi.smooth;
     g.nodeBase = bi.nodeBase; g.triBase = bi.triBase; g.triF64 = bi.f64; g.rootRef = bi.rootRef;
+    g.bigBlas = (bi.kind == INST_MESH && bi.triCount > bigBlasTriangles) ? 1 : 0;
     g.matId = in.hasMaterialOverride ? in.materialOverride : bi.matId;  // RTContext.swift:704
     g.primIndex = bi.prim;
     const bool moves = in.instanceMotion[0] != 0 || in.instanceMotion[1] != 0 || in.instanceMotion[2] != 0;
@@ -271,6 +273,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     if (const char* e = std::getenv("RTCUDA_BUILD"))
         buildMode = std::strcmp(e, "device") == 0 ? RT_BUILD_DEVICE_LBVH : std::strcmp(e, "device-sah") == 0 ? RT_BUILD_DEVICE_SAH : RT_BUILD_HOST_SAH;
     const bool deviceBuild = buildMode != RT_BUILD_HOST_SAH;
+    if (const char* e = std::getenv("RTCUDA_BIG_BLAS")) sc->bigBlasTriangles = std::atoll(e);
     struct DevVerts {       // the scene's triangle vertices on the device, for the device builder only
         double* p = nullptr;
         ~DevVerts() { cudaFree(p); }
@@ -380,7 +383,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
         if (in.blas < 0 || in.blas >= d->nBlas) return fail(RT_ERR_INVALID, "rt_instance.blas out of range");
         const bool moves = in.instanceMotion[0] != 0 || in.instanceMotion[1] != 0 || in.instanceMotion[2] != 0;
         if (moves) { sc->motion = true; instanceMotion = true; }
-        fillInstance(in, blasInfo[in.blas], inst[i]);
+        fillInstance(in, blasInfo[in.blas], inst[i], sc->bigBlasTriangles);
         sc->instBlas.push_back(in.blas);
         std::memcpy(&wb[i * 6], in.worldBounds, 48);
     }
@@ -610,7 +613,7 @@ static int cloneScene(const rt_scene* src, int device, rt_scene* dst) {
     dst->device = device;
     dst->isReplica = true;
     dst->ds = src->ds; dst->info = src->info; dst->info.device = device; dst->meshes = src->meshes;
-    dst->motion = src->motion; dst->glossy = src->glossy; dst->nonFinite = src->nonFinite; dst->recurse = src->recurse; dst->instanceMotion = src->instanceMotion;
+    dst->motion = src->motion; dst->glossy = src->glossy; dst->nonFinite = src->nonFinite; dst->recurse = src->recurse; dst->bigBlasTriangles = src->bigBlasTriangles; dst->instanceMotion = src->instanceMotion;
     dst->blasInfo = src->blasInfo; dst->instBlas = src->instBlas; dst->refitLevelStart = src->refitLevelStart;
     dst->nBoundChunks = src->nBoundChunks;
     dst->arrays = src->arrays;
@@ -755,7 +758,7 @@ static int updateInstancesOne(rt_scene_t* sc, rt_instance* instances, int64_t nI
         if (in.instanceMotion[0] != 0 || in.instanceMotion[1] != 0 || in.instanceMotion[2] != 0)
             return fail(RT_ERR_UNSUPPORTED, "rt_scene_update_instances: instanceMotion cannot be introduced by an update");
         const BlasInfo& bi = sc->blasInfo[in.blas];
-        fillInstance(in, bi, sc->hInst[i]);
+        fillInstance(in, bi, sc->hInst[i], sc->bigBlasTriangles);
         // an inverted box (minP > maxP) asks for Instance.worldBounds to be derived from the BLAS's triangles
         const bool derive = !(in.worldBounds[0] <= in.worldBounds[3]) || !(in.worldBounds[1] <= in.worldBounds[4]) ||
                             !(in.worldBounds[2] <= in.worldBounds[5]);

@@ -125,6 +125,7 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     rt.tileCounter = sc->dTileCounter;
     rt.motion = sc->motion ? 1 : 0;
     rt.recurse = sc->recurse ? 1 : 0;
+    if (std::getenv("RTCUDA_FORCE_RECURSE")) rt.recurse = 1;       // measurements only: the queue instantiation on a scene without child rays
     // Tile schedule: the frame records its cost per tile, the next frame of the same geometry draws the longest
     // tiles first.
     const int nTiles = ShardTiles(cp.width, cp.height, cp.shardIndex, cp.shardCount, cp.shardTiles).count;

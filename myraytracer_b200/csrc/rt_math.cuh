@@ -28,8 +28,20 @@ __device__ __forceinline__ double dot(V3 a, V3 b) { return (a.x * b.x + a.y * b.
 __device__ __forceinline__ V3 cross(V3 a, V3 b) {
     return mk(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
 }
-__device__ __forceinline__ V3 normalize(V3 a) { return a * (1.0 / sqrt(dot(a, a))); }
-__device__ __forceinline__ double length(V3 a) { return sqrt(dot(a, a)); }
+// FP64 sqrt and 1/x expand to ~70 SASS instructions; `normalize` has some twenty call sites on the render path.  Out of
+// line (RT_NOINLINE_MATH, one copy each) the executed code of the kernels with recursion shrinks by a third, which is what
+// their instruction-cache stalls are made of.  Same operations, same results.
+#ifndef RT_NOINLINE_MATH
+#define RT_NOINLINE_MATH 0
+#endif
+#if RT_NOINLINE_MATH && !defined(RT_EMU)
+#define RT_MATH_FN static __device__ __noinline__
+#else
+#define RT_MATH_FN __device__ __forceinline__
+#endif
+RT_MATH_FN double rsqrtExact(double s) { return 1.0 / sqrt(s); }
+__device__ __forceinline__ V3 normalize(V3 a) { return a * rsqrtExact(dot(a, a)); }
+RT_MATH_FN double length(V3 a) { return sqrt(dot(a, a)); }
 // Swift.max/min on Doubles as used by the reference (a > b ? a : b), NaN-propagation irrelevant here
 __device__ __forceinline__ double dmax(double a, double b) { return a > b ? a : b; }
 __device__ __forceinline__ double dmin(double a, double b) { return a < b ? a : b; }

@@ -184,16 +184,29 @@ __device__ __forceinline__ uint32_t packetBlas(const DeviceScene& S, const GInst
 }
 
 // One instance for the lanes in inMask (warp-uniform instance index): RTContext.swift:657-705.
-template <bool COUNT>
+// INCOHERENT (compile time: the kernel instantiation with the ray queue) + incoherent (run time, warp-uniform: the rays
+// are child rays off the queue, not primary rays or their shadow rays): a mesh of more than kBigBlasTriangles
+// triangles is walked per lane — the lanes of the mask enter together and each follows its own path (while-while,
+// rt_traverse.cuh) — because a packet visits the UNION of its rays' paths, which for 32 reflected rays in a
+// million-triangle BVH is ten times one ray's path; small meshes and analytic primitives stay with the packet.
+template <bool COUNT, bool INCOHERENT = false>
 __device__ __forceinline__ uint32_t packetInstance(const DeviceScene& S, int idx, V3 o, V3 d, double eps, double tMin,
-                                                   HitRec& hit, bool anyhit, uint32_t inMask, int2* wstack, Counters& C) {
+                                                   HitRec& hit, bool anyhit, uint32_t inMask, int2* wstack, Counters& C,
+                                                   bool incoherent = false) {
     const GInstance& I = S.instances[idx];
     const bool in = (inMask >> (threadIdx.x & 31)) & 1u;
     V3 oL, dL;
     toLocal(I, o, d, oL, dL);
     if (COUNT && in) C.inst++;
     const double tLow = dmax(eps, tMin);
-    if (I.kind == INST_MESH) return packetBlas<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, inMask, wstack, C);
+    if (I.kind == INST_MESH) {
+        if (INCOHERENT && incoherent && I.bigBlas) {
+            bool o1 = false;
+            if (in) o1 = traverseBlas<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, nullptr, 0, C);
+            return __ballot_sync(RT_FULL, o1);
+        }
+        return packetBlas<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, inMask, wstack, C);
+    }
     bool occ = false;
     if (in) occ = analyticInstance<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, C);
     return __ballot_sync(RT_FULL, occ);   // always 0 for closest-hit queries
@@ -201,16 +214,16 @@ __device__ __forceinline__ uint32_t packetInstance(const DeviceScene& S, int idx
 
 // Packet TLAS walk.  `active`: this lane carries a ray.  Closest hit: updates hit; any-hit (hit.t = tMax):
 // returns true for the lanes whose ray is occluded.
-template <bool COUNT>
+template <bool COUNT, bool INCOHERENT = false>
 __device__ __forceinline__ bool packetScene(const DeviceScene& S, V3 o, V3 d, double tMin, HitRec& hit, bool active,
-                                            bool anyhit, int2* wstack, Counters& C) {
+                                            bool anyhit, int2* wstack, Counters& C, bool incoherent = false) {
     const uint32_t bit = 1u << (threadIdx.x & 31);
     uint32_t live = __ballot_sync(RT_FULL, active);
     if (!live) return false;
     const double eps = S.eps;
     int32_t cur = S.tlasRootRef;
     if (cur == kEmptyRef) return false;
-    if (cur < 0) return (packetInstance<COUNT>(S, ~cur, o, d, eps, tMin, hit, anyhit, live, wstack, C) & bit) != 0;
+    if (cur < 0) return (packetInstance<COUNT, INCOHERENT>(S, ~cur, o, d, eps, tMin, hit, anyhit, live, wstack, C, incoherent) & bit) != 0;
     const double tLow = dmax(eps, tMin);
     RayF rf = makeRayF(S.tlasLo, S.tlasHi, S.tlasCentre, o, d, refinedInv(d), tLow, hit.t);
     if (COUNT && active) C.box++;
@@ -241,7 +254,7 @@ __device__ __forceinline__ bool packetScene(const DeviceScene& S, V3 o, V3 d, do
             } else if (m0) { cur = ch.x; curMask = m0; descended = true; }
             else if (m1) { cur = ch.y; curMask = m1; descended = true; }
         } else {
-            const uint32_t o_ = packetInstance<COUNT>(S, ~cur, o, d, eps, tMin, hit, anyhit, curMask, wstack, C);
+            const uint32_t o_ = packetInstance<COUNT, INCOHERENT>(S, ~cur, o, d, eps, tMin, hit, anyhit, curMask, wstack, C, incoherent);
             if (anyhit) {
                 occluded |= o_;
                 live &= ~o_;

@@ -184,7 +184,7 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFas
     const int totalUnits = tiles.count * unitsPerTile;
     __shared__ uint2 unitNote[RT_FAST_BLOCK / 32];               // (clock at unit start, tile): read back when the unit ends
     WarpQueue Q;
-    if (RECURSE) Q.init(T, S.maxDepth, lane);
+    Q.init();
 #ifdef RT_WARPTIMES
     unsigned long long wt0 = globalTimerNs(), wt1 = 0, wt2 = 0;
     int wtUnits = 0, wtUnit = 0;
@@ -266,7 +266,7 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFas
                 } else {
                     if (!RECURSE) break;
                     cur0.o = cur0.d = cur0.w = mk(0, 0, 0); cur0.beerMat = 0; cur0.depth = 0; cur0.beer = 0; cur0.slot = 0;
-                    if (!Q.pop(T, cur0, active)) break;
+                    if (!Q.pop(out.pathStack, S.maxDepth, cur0, active)) break;
                 }
 
                 // ---- the rays of the round as a warp packet: one traversal call site serves the closest-hit query
@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFas
                 __syncwarp();
 #pragma unroll 1
                 for (;;) {
-                    const bool occ = packetScene<COUNT>(S, ro, rd, rtMin, hit, rayOn, anyhit, T.wstack, C);
+                    const bool occ = packetScene<COUNT, RECURSE>(S, ro, rd, rtMin, hit, rayOn, anyhit, T.wstack, C, !primary);
                     if (phase == 0) {
                         isHit = active && hit.inst >= 0;
                         Surface sf;
@@ -327,7 +327,7 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFas
                 } else {
                     warpAccumulate(colBuf, cur0.slot, active, c);
                 }
-                Q.push(T, nc, c1, c2);
+                Q.push(out.pathStack, S.maxDepth, nc, c1, c2);
             }
             __syncwarp();
             // ---- pixelColor += trace(...) in sample order (:345), then / samples (:354), pass by pass
@@ -369,6 +369,23 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFas
                         sum = sum + ck;
                     }
                     if (active && s == 0) writePixel(out, (size_t)j * W + i, sum / samplesD);
+                } else if (units.perPixel) {
+                    // 32 divides ns: the 32 samples of this pass are consecutive samples of ONE pixel.  Lanes 0..2 add one
+                    // component each, in sample order, carrying their sum from pass to pass (acc.x in all three).
+                    if (!RECURSE) { scratch[lane * 3] = c.x; scratch[lane * 3 + 1] = c.y; scratch[lane * 3 + 2] = c.z; }
+                    __syncwarp();
+                    if (lane < 3) {
+                        double comp = acc.x;
+#pragma unroll 8
+                        for (int k = 0; k < 32; k++) comp = comp + scratch[k * 3 + lane];
+                        acc.x = comp;
+                    }
+                    __syncwarp();
+                    if (it == itEnd - 1) {
+                        const double comp = acc.x / samplesD;
+                        const V3 px3 = mk(shflD(comp, 0), shflD(comp, 1), shflD(comp, 2));
+                        if (active && lane == 0) writePixel(out, (size_t)j * W + i, px3);
+                    }
                 } else {
 #pragma unroll 1
                     for (int k = 0; k < 32; k++) {
@@ -387,7 +404,7 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFas
                 }
             }
         }
-        if (!segmented && openP >= 0 && lane == 0) {
+        if (!segmented && !units.perPixel && openP >= 0 && lane == 0) {
             const int qx = (openP & 1) | ((openP >> 1) & 2) | ((openP >> 2) & 4), qy = ((openP >> 1) & 1) | ((openP >> 2) & 2);
             if (x0 + qx < W && y0 + qy < H) writePixel(out, (size_t)(y0 + qy) * W + (x0 + qx), acc / samplesD);
         }

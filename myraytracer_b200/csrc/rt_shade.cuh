@@ -416,50 +416,48 @@ __device__ __forceinline__ void warpAccumulate(double* col, int slot, bool has, 
     }
 }
 
+// Only `top` and `priv` live across a round; where the queue lies is re-derived from the launch geometry at every push
+// and pop (uniform arithmetic), so the packet walk in between does not carry the queue in registers.
 struct WarpQueue {
-    double* qbase;       // this warp's 32 columns of the path stack
-    size_t stride;
-    int cap, privBase;
     int top;             // entries in the shared queue (warp-uniform)
     int priv;            // entries on this lane's private stack
-    unsigned lt;         // lanes below this one
 
-    __device__ __forceinline__ void init(const TraceScratch& T, int maxDepth, int lane) {
-        qbase = T.pathStack + (T.gtid - (size_t)lane);
-        stride = T.stride;
-        cap = 32 * (maxDepth + RT_QUEUE_EXTRA);
-        privBase = maxDepth + RT_QUEUE_EXTRA;
-        top = 0; priv = 0;
-        lt = (1u << lane) - 1u;
-    }
+    __device__ __forceinline__ void init() { top = 0; priv = 0; }
 
     // Offer n (0..2) entries per lane; all 32 lanes call it.  Compaction: ballot + prefix popcount.
-    __device__ __forceinline__ void push(const TraceScratch& T, int n, const PathEntry& a, const PathEntry& b) {
+    __device__ __forceinline__ void push(double* pathStack, int maxDepth, int n, const PathEntry& a, const PathEntry& b) {
         const unsigned m1 = __ballot_sync(RT_FULL, n >= 1), m2 = __ballot_sync(RT_FULL, n == 2);
         const int total = __popc(m1) + __popc(m2);
         if (total == 0) return;
-        if (top + total <= cap) {
+        const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+        const size_t stride = (size_t)gridDim.x * blockDim.x, gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+        if (top + total <= 32 * (maxDepth + RT_QUEUE_EXTRA)) {
+            double* qbase = pathStack + (gtid - lane);
             const int at = top + __popc(m1 & lt) + __popc(m2 & lt);
             if (n == 2) queueStore(qbase, stride, at, b);            // refraction below, reflection on top of it
             if (n >= 1) queueStore(qbase, stride, at + (n == 2 ? 1 : 0), a);
             top += total;
         } else {
-            if (n == 2) { pathStore(T.pathStack, stride, T.gtid, privBase + priv, b); priv++; }
-            if (n >= 1) { pathStore(T.pathStack, stride, T.gtid, privBase + priv, a); priv++; }
+            const int privBase = maxDepth + RT_QUEUE_EXTRA;
+            if (n == 2) { pathStore(pathStack, stride, gtid, privBase + priv, b); priv++; }
+            if (n >= 1) { pathStore(pathStack, stride, gtid, privBase + priv, a); priv++; }
         }
         __syncwarp();
     }
 
     // Up to 32 entries off the top, one per lane (a lane's own spill-over first); all 32 lanes call it.  Returns false
     // when nothing is left anywhere in the warp.
-    __device__ __forceinline__ bool pop(const TraceScratch& T, PathEntry& cur, bool& valid) {
+    __device__ __forceinline__ bool pop(double* pathStack, int maxDepth, PathEntry& cur, bool& valid) {
         valid = false;
-        if (priv > 0) { priv--; pathLoad(T.pathStack, stride, T.gtid, privBase + priv, cur); valid = true; }
+        if (top == 0 && __ballot_sync(RT_FULL, priv > 0) == 0u) return false;
+        const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+        const size_t stride = (size_t)gridDim.x * blockDim.x, gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+        if (priv > 0) { priv--; pathLoad(pathStack, stride, gtid, maxDepth + RT_QUEUE_EXTRA + priv, cur); valid = true; }
         const unsigned need = __ballot_sync(RT_FULL, !valid);
         if (need != 0u && top > 0) {
             const int want = __popc(need), k = want < top ? want : top;
             const int r = __popc(need & lt);
-            if (!valid && r < k) { queueLoad(qbase, stride, top - 1 - r, cur); valid = true; }
+            if (!valid && r < k) { queueLoad(pathStack + (gtid - lane), stride, top - 1 - r, cur); valid = true; }
             top -= k;
         }
         return __ballot_sync(RT_FULL, valid) != 0u;
