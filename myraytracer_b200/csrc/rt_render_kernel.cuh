@@ -41,8 +41,12 @@ namespace rtg {
 #ifndef RT_SKIPTAB
 #define RT_SKIPTAB 1
 #endif
+// The general kernel wants registers, not warps: its per-lane FP64 path state (ray, throughput, shading point, light
+// sums, RNG, hit record) does not fit 96 registers, and every spill sits on the path between two dependent scene walks.
+// Measured on B200 (C3 glossy / C3 with area lights, ms per frame): 5 blocks of 128 threads per SM (96 registers) 18.6 /
+// 28.9, 3 blocks (168) 15.8 / 25.9, 2 blocks (255 registers, 8 warps per SM) 13.4 / 21.8.
 #ifndef RT_GEN_BLOCKS
-#define RT_GEN_BLOCKS 5
+#define RT_GEN_BLOCKS 2
 #endif
 
 struct PrimaryRay {
@@ -475,7 +479,7 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_GEN_BLOCKS) renderKernelGeneral(D
                     HitId* idSlot = (out.ids && !area.countOnly) ? out.ids + (((size_t)j * W + i) * (size_t)(n * n) + (size_t)(sy * n + sx)) : nullptr;
                     PathEntry cur0;
                     cur0.o = pr.o; cur0.d = pr.d; cur0.w = mk(1, 1, 1); cur0.beerMat = 0; cur0.depth = 0; cur0.beer = 0; cur0.slot = 0;
-                    pixel = pixel + scalarPathLoop<true, COUNT, false, EXT, EXT>(S, T, cur0, 0, true, pr.tMin, idSlot, rng, C, R, mk(0, 0, 0),
+                    pixel = pixel + scalarPathLoop<true, COUNT, EXT, EXT>(S, T, cur0, 0, true, pr.tMin, idSlot, rng, C, R, mk(0, 0, 0),
                                                                                  EXT ? &area : nullptr, pr.time);
                     sampleIndex++;
                 }

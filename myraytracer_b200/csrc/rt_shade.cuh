@@ -2,10 +2,10 @@
 //
 //   trace (shading + recursion)            Extensions/Object+Extension.swift:96-283
 //   Fresnel / reflect / Beer helpers       :467-505, orthonormalBasis :530-552
-// The recursion is an explicit per-thread stack of (ray, throughput) entries processed depth-first,
-// reflection before refraction, which keeps the reference's RNG draw order (scalarPathLoop).  The pieces
-// (surface set-up, one point light, child-ray spawning) are shared with the packet kernel, which handles
-// depth 0 itself and hands spawned children to scalarPathLoop.
+// The pieces of `trace` (surface set-up, one point / area light, child-ray spawning) are shared by the two kernels: the
+// general kernel walks every lane's path tree depth-first with an explicit per-thread stack of (ray, throughput)
+// entries, reflection before refraction, which keeps the reference's RNG draw order (scalarPathLoop); the fast kernel
+// sends child rays through the warp's ray queue (WarpQueue).
 #pragma once
 #include <math_constants.h>
 
@@ -267,10 +267,9 @@ __device__ __forceinline__ int spawnChildren(const DeviceScene& S, const ShadePo
 // `level` the number of entries already waiting on this thread's path stack.  firstIsPrimary: `cur` is the
 // camera ray (tMin = near-plane clip :341-344, hit id recorded).  Returns `color` plus the w * Lo of all
 // processed entries, added in processing order.
-// CALL: the traversal is the out-of-line traceSceneCall (fast kernel) instead of two inlined walks.
 // AREA: the scene has area lights; `area` carries the chunk's jitter index through the path (general kernel only).
 // MOTION: motion blur; `time` is the sample's ray time, inherited by every ray of the path (:123,172,198,242).
-template <bool GLOSSY, bool COUNT, bool CALL = false, bool AREA = false, bool MOTION = false>
+template <bool GLOSSY, bool COUNT, bool AREA = false, bool MOTION = false>
 __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceScratch& T, PathEntry cur, int level,
                                              bool firstIsPrimary, double tMinPrimary, HitId* idSlot, PCG32& rng, Counters& C,
                                              RayCounts& R, V3 color, AreaState* area = nullptr, double time = 0.0) {
@@ -279,8 +278,7 @@ __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceSc
     for (;;) {
         HitRec hit;
         hit.t = CUDART_INF; hit.u = hit.v = 0; hit.inst = -1; hit.slot = 0;
-        if (CALL) hit = traceSceneCall<COUNT>(S, cur.o, cur.d, primary ? tMinPrimary : 0.0, hit, false, T.sstack, T.sstackN, COUNT ? &C : nullptr).hit;
-        else traceScene<COUNT, MOTION>(S, cur.o, cur.d, primary ? tMinPrimary : 0.0, hit, false, T.sstack, T.sstackN, C, time);
+        traceScene<COUNT, MOTION>(S, cur.o, cur.d, primary ? tMinPrimary : 0.0, hit, false, T.sstack, T.sstackN, C, time);
         Surface sf;
         if (hit.inst >= 0) {
             resolveHit<MOTION>(S, hit, cur.o, cur.d, sf, time);
@@ -310,8 +308,7 @@ __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceSc
                     HitRec sh;
                     sh.t = dist; sh.u = sh.v = 0; sh.inst = -1; sh.slot = 0;             // tMax = dist (:124)
                     R.shadow++;
-                    const bool occluded = CALL ? traceSceneCall<COUNT>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, COUNT ? &C : nullptr).occluded
-                                               : traceScene<COUNT, MOTION>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, C, time);
+                    const bool occluded = traceScene<COUNT, MOTION>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, C, time);
                     if (!occluded)
                         Lo = Lo + pointLightTerm(*sp.mat, pl, sp.N, cur.d, wi, dist);
                 }
@@ -329,8 +326,7 @@ __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceSc
                     sh.t = dist - S.shadowEps; sh.u = sh.v = 0; sh.inst = -1; sh.slot = 0;   // tMax = dist - shadowEps (:173)
                     R.shadow++;
                     const V3 so = sp.p + wi * S.shadowEps;
-                    const bool occluded = CALL ? traceSceneCall<COUNT>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, COUNT ? &C : nullptr).occluded
-                                               : traceScene<COUNT, MOTION>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, C, time);
+                    const bool occluded = traceScene<COUNT, MOTION>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, C, time);
                     if (!occluded) Lo = Lo + areaLightTerm(*sp.mat, al, sp.N, cur.d, wi, dist2, NdotL, Ln);
                 }
             }

@@ -143,33 +143,11 @@ __device__ __forceinline__ bool traceScene(const DeviceScene& S, V3 o, V3 d, dou
     }
 }
 
-// traceScene as a real call, everything by value: used by the fast kernel for its secondary rays.  Two inlined
-// copies of the walk (closest hit + shadow) in the recursion loop made the executed code of the recursive scene C3
-// 128 KB, and ncu showed the warps waiting for instruction fetch 16 cycles per issue; one shared out-of-line copy:
-// 11.25 -> 8.3 ms.  The hit record travels in registers (by reference it would live in local memory and cost the
-// big-mesh scene C5 4 %).  The general kernel keeps the inlined walk: its lanes' rays are coherent and it has the
-// registers.
 #ifdef RT_EMU
 #define RT_NOINLINE __attribute__((noinline))
 #else
 #define RT_NOINLINE __noinline__
 #endif
-struct TraceOut {
-    HitRec hit;
-    bool occluded;
-};
-template <bool COUNT>
-__device__ RT_NOINLINE TraceOut traceSceneCall(const DeviceScene& S, V3 o, V3 d, double tMin, HitRec hit, bool anyhit,
-                                                int32_t* sstack, int sstackN, Counters* counters) {
-    Counters C;
-    C.box = C.tri = C.sphere = C.plane = C.inst = C.smooth = 0; C.maxStack = 0;
-    if (COUNT) C = *counters;
-    TraceOut r;
-    r.occluded = traceScene<COUNT>(S, o, d, tMin, hit, anyhit, sstack, sstackN, C);
-    r.hit = hit;
-    if (COUNT) *counters = C;
-    return r;
-}
 
 struct Surface {
     V3 p, n;          // world-space hit point and geometric normal (Hit.p, Hit.n)
