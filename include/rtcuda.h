@@ -302,6 +302,27 @@ typedef struct rt_ply_stats { int64_t triangles, kernelLaunches; double deviceMs
 int32_t rt_ply_ingest(const rt_ply_layout* layout, const void* vertexBlock, const void* faceBlock, int32_t smooth,
                       int32_t device, double* triVerticesOut, double* triNormalsOut, rt_ply_stats* statsOut);
 
+/* rt_ply_ingest without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same kernels, same results bit for bit, but:
+ *   - dVertexBlock / dFaceBlock / dTriVerticesOut / dTriNormalsOut are DEVICE pointers owned by the caller (valid on
+ *     `device`; sizes as for rt_ply_ingest), the kernels run on `cudaStream` (a cudaStream_t, NULL = default stream);
+ *   - every intermediate lives in one fixed device array inside the library (RT_PLY_STATIC_SCRATCH_BYTES, held by every
+ *     GPU that loads the library until the process exits), so a mesh may have at most RT_PLY_STATIC_MAX_VERTICES
+ *     vertices and RT_PLY_STATIC_MAX_TRIANGLES triangles (quads count twice): larger meshes are refused with
+ *     RT_ERR_UNSUPPORTED and a message — use rt_ply_ingest for them;
+ *   - the call allocates and frees nothing (no cudaMalloc / cudaFree / event or stream creation); the first call on a
+ *     device looks the array's address up once;
+ *   - all calls share the array, which keeps the last call's contents (the call clears what must start at zero): two
+ *     calls that overlap on one GPU — from two threads or two streams — RACE on it.  One call at a time per GPU.
+ * Blocking (the face indices are validated before anything dereferences them).  statsOut->deviceMs is 0. */
+#define RT_PLY_STATIC_MAX_VERTICES 65536
+#define RT_PLY_STATIC_MAX_TRIANGLES 131072
+#define RT_PLY_STATIC_SCRATCH_BYTES (10u << 20)
+int32_t rt_ply_ingest_static(const rt_ply_layout* layout, const void* dVertexBlock, const void* dFaceBlock, int32_t smooth,
+                             int32_t device, double* dTriVerticesOut, double* dTriNormalsOut, void* cudaStream,
+                             rt_ply_stats* statsOut);
+
 /* Multi-GPU framebuffer (one process per GPU): the reference merges finished 8-row chunks into
  * one [Vec3] array by plain copies (Object+Extension.swift:363-373).  Here rank 0 owns the RGBA8 frame in device
  * memory and exports it; every other rank maps it over NVLink (CUDA IPC, peer access) and passes the mapped

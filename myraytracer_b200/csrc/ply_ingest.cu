@@ -15,6 +15,8 @@
 // No warp-level primitives: atomics, a three-kernel scan and plain per-element kernels — HBM-bound byte and FP64 work.
 #include <math_constants.h>
 
+#include <mutex>
+
 #include "../../include/rtcuda.h"
 #include "rt_kernels.h"
 #include "rt_math.cuh"
@@ -253,6 +255,119 @@ int plyIngestDevice(const rt_ply_layout& L, const void* vertexBlock, const void*
     PCK(cudaEventElapsedTime(&ms, e0, e1));
     if (launches) *launches = n;
     if (deviceMs) *deviceMs = ms;
+    return 0;
+#undef PCK
+}
+
+// ---- rt_ply_ingest_static: the same kernels with NO allocation ------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Every intermediate of the pipeline
+// above (positions, normals, indices, face normals, adjacency lists, scan sums, error flag) lives in ONE file-scope
+// device array of fixed size, which every GPU that loads the library holds until exit; inputs and outputs are the
+// caller's DEVICE buffers.  Limits: kPlyStaticMaxVertices vertices, kPlyStaticMaxTriangles triangles.
+// All calls share the array and it keeps the last call's contents: whatever must start at zero (the faces-around-vertex
+// counts and cursors, the error flag) is cleared by the call itself; two calls that overlap on one GPU race on it.
+static const long long kPlyStaticMaxVertices = RT_PLY_STATIC_MAX_VERTICES;
+static const long long kPlyStaticMaxTriangles = RT_PLY_STATIC_MAX_TRIANGLES;
+static const size_t kPlyAlign = 256;
+static constexpr size_t plyUp(size_t n) { return (n + kPlyAlign - 1) / kPlyAlign * kPlyAlign; }
+// layout of the array: byte offsets of the intermediates at the maximum size
+static constexpr size_t kOffPos = 0;                                                           // nV * 3 doubles
+static constexpr size_t kOffVn = kOffPos + plyUp((size_t)RT_PLY_STATIC_MAX_VERTICES * 24);     // nV * 3 doubles: file OR smooth normals
+static constexpr size_t kOffCnt = kOffVn + plyUp((size_t)RT_PLY_STATIC_MAX_VERTICES * 24);     // nV + 1 counts
+static constexpr size_t kOffCur = kOffCnt + plyUp(((size_t)RT_PLY_STATIC_MAX_VERTICES + 1) * 4);
+static constexpr size_t kOffSums = kOffCur + plyUp((size_t)RT_PLY_STATIC_MAX_VERTICES * 4);    // scan block sums
+static constexpr size_t kOffErr = kOffSums + plyUp((((size_t)RT_PLY_STATIC_MAX_VERTICES + 1 + RT_SCAN_BLOCK - 1) / RT_SCAN_BLOCK) * 4);
+static constexpr size_t kOffIdx = kOffErr + kPlyAlign;                                         // nT * 3 int32
+static constexpr size_t kOffFaceN = kOffIdx + plyUp((size_t)RT_PLY_STATIC_MAX_TRIANGLES * 12); // nT * 3 doubles
+static constexpr size_t kOffEnt = kOffFaceN + plyUp((size_t)RT_PLY_STATIC_MAX_TRIANGLES * 24); // nT * 3 corner ids
+static constexpr size_t kPlyStaticBytes = kOffEnt + plyUp((size_t)RT_PLY_STATIC_MAX_TRIANGLES * 12);
+static_assert(kPlyStaticBytes <= RT_PLY_STATIC_SCRATCH_BYTES, "the intermediates of the largest mesh fit the static array");
+
+static __device__ __align__(256) unsigned char g_plyScratch[RT_PLY_STATIC_SCRATCH_BYTES];
+
+// In host code `g_plyScratch` is a host-side stand-in, not a device address: the address the kernels need comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+static const int kPlyMaxDevices = 64;
+static unsigned char* g_plyScratchPtr[kPlyMaxDevices];
+static bool g_plyScratchKnown[kPlyMaxDevices];
+
+static cudaError_t plyScratchFor(int device, unsigned char** out) {
+    if (!g_plyScratchKnown[device]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_plyScratch);
+        if (e != cudaSuccess) return e;
+        g_plyScratchPtr[device] = static_cast<unsigned char*>(p);
+        g_plyScratchKnown[device] = true;
+    }
+    *out = g_plyScratchPtr[device];
+    return cudaSuccess;
+}
+
+// The pipeline of plyIngestDevice on `stream` with every intermediate in g_plyScratch.  dVertexBlock / dFaceBlock /
+// dTriVertsOut / dTriNormalsOut are DEVICE pointers of the caller (valid on `device`, which must be current).
+// Calls no cudaMalloc / cudaFree / event or stream creation.  Blocking: the face indices are validated (one 4-byte
+// read-back) before any kernel dereferences them, and the call returns when the outputs are complete.
+// Returns 0, -1 with `msg` set (CUDA error or malformed data), -2 when the mesh exceeds the static limits.
+int plyIngestStatic(const rt_ply_layout& L, const void* dVertexBlock, const void* dFaceBlock, int smooth, int device,
+                    double* dTriVertsOut, double* dTriNormalsOut, cudaStream_t stream, const char** msg, int64_t* launches) {
+    *msg = "";
+#define PCK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { *msg = cudaGetErrorString(e_); return -1; } } while (0)
+    const int k = L.verticesPerFace;
+    const long long nV = L.vertexCount, nF = L.faceCount, nT = nF * (k == 4 ? 2 : 1);
+    if (device < 0 || device >= kPlyMaxDevices) { *msg = "device index outside 0..63"; return -1; }
+    if (nV > kPlyStaticMaxVertices || nT > kPlyStaticMaxTriangles) {
+        *msg = "mesh exceeds the static scratch of rt_ply_ingest_static (RT_PLY_STATIC_MAX_VERTICES vertices, "
+               "RT_PLY_STATIC_MAX_TRIANGLES triangles): use rt_ply_ingest";
+        return -2;
+    }
+    const bool fileNormals = L.normalOffset[0] >= 0 && L.normalOffset[1] >= 0 && L.normalOffset[2] >= 0;
+    const bool needSmooth = smooth && !fileNormals;
+    unsigned char* base = nullptr;
+    {
+        static std::mutex m;                        // the per-device address table is filled once per device
+        std::lock_guard<std::mutex> lk(m);
+        PCK(plyScratchFor(device, &base));
+    }
+    PlyDev P{};
+    P.L = L;
+    P.faceRecord = L.faceLeadBytes + L.faceCountBytes + k * L.faceIndexBytes + L.faceTrailBytes;
+    P.trisPerFace = k == 4 ? 2 : 1;
+    P.vblock = static_cast<const unsigned char*>(dVertexBlock);
+    P.fblock = static_cast<const unsigned char*>(dFaceBlock);
+    P.pos = reinterpret_cast<double*>(base + kOffPos);
+    P.vnormFile = fileNormals ? reinterpret_cast<double*>(base + kOffVn) : nullptr;
+    P.vnorm = reinterpret_cast<double*>(base + kOffVn);           // file normals and smooth normals exclude each other
+    P.count = reinterpret_cast<unsigned*>(base + kOffCnt);
+    P.cursor = reinterpret_cast<unsigned*>(base + kOffCur);
+    unsigned* sums = reinterpret_cast<unsigned*>(base + kOffSums);
+    P.error = reinterpret_cast<int*>(base + kOffErr);
+    P.idx = reinterpret_cast<int32_t*>(base + kOffIdx);
+    P.faceN = reinterpret_cast<double*>(base + kOffFaceN);
+    P.entries = reinterpret_cast<unsigned*>(base + kOffEnt);
+    const int gV = (int)((nV + RT_PLY_THREADS - 1) / RT_PLY_THREADS), gF = (int)((nF + RT_PLY_THREADS - 1) / RT_PLY_THREADS),
+              gT = (int)((nT + RT_PLY_THREADS - 1) / RT_PLY_THREADS);
+    int64_t n = 0;
+    // what must start at zero: the error flag here; counts and cursors of vertices 0 .. nV by plyVertices
+    PCK(cudaMemsetAsync(P.error, 0, 4, stream));
+    if (gV > 0) { RT_LAUNCH(plyVertices, gV, RT_PLY_THREADS, stream, P); n++; }
+    if (gF > 0) { RT_LAUNCH(plyFaces, gF, RT_PLY_THREADS, stream, P); n++; }
+    int herr = 0;
+    PCK(cudaMemcpyAsync(&herr, P.error, 4, cudaMemcpyDeviceToHost, stream));
+    PCK(cudaStreamSynchronize(stream));                            // indices are validated before anything dereferences them
+    if (herr == 1) { *msg = "face records with differing vertex counts (device ingest takes uniform triangle or quad lists)"; return -1; }
+    if (herr == 2) { *msg = "mesh face index out of range"; return -1; }
+    if (gT > 0 && !fileNormals) { RT_LAUNCH(plyFaceNormals, gT, RT_PLY_THREADS, stream, P, nT, needSmooth ? 1 : 0); n++; }
+    if (needSmooth && gT > 0) {
+        PCK(launchExclusiveScan(P.count, nV + 1, sums, stream));
+        RT_LAUNCH(plyFillAdjacency, gT, RT_PLY_THREADS, stream, P, nT);
+        RT_LAUNCH(plyVertexNormals, gV, RT_PLY_THREADS, stream, P);
+        n += 5;
+    }
+    if (gT > 0) { RT_LAUNCH(plyEmit, gT, RT_PLY_THREADS, stream, P, nT, needSmooth ? 1 : 0, dTriVertsOut, dTriNormalsOut); n++; }
+    PCK(cudaGetLastError());
+    PCK(cudaStreamSynchronize(stream));
+    if (launches) *launches = n;
     return 0;
 #undef PCK
 }

@@ -27,6 +27,8 @@ using namespace rtg;
 namespace rtg {   // ply_ingest.cu
 int plyIngestDevice(const rt_ply_layout& L, const void* vertexBlock, const void* faceBlock, int smooth, double* triVertsOut,
                     double* triNormalsOut, const char** msg, int64_t* launches, double* deviceMs);
+int plyIngestStatic(const rt_ply_layout& L, const void* dVertexBlock, const void* dFaceBlock, int smooth, int device,
+                    double* dTriVertsOut, double* dTriNormalsOut, cudaStream_t stream, const char** msg, int64_t* launches);
 }
 
 namespace {
@@ -830,6 +832,40 @@ int32_t rt_ply_ingest(const rt_ply_layout* L, const void* vertexBlock, const voi
         return fail(RT_ERR_INVALID, std::string("rt_ply_ingest: ") + msg);
     }
     if (statsOut) { statsOut->triangles = L->faceCount * (L->verticesPerFace == 4 ? 2 : 1); statsOut->kernelLaunches = launches; statsOut->deviceMs = ms; }
+    return RT_OK;
+}
+
+// rt_ply_ingest with every intermediate in a fixed device array inside the library: allocates and frees nothing
+// (ply_ingest.cu: plyIngestStatic).  No counterpart in the reference.
+int32_t rt_ply_ingest_static(const rt_ply_layout* L, const void* dVertexBlock, const void* dFaceBlock, int32_t smooth, int32_t device,
+                             double* dTriVerticesOut, double* dTriNormalsOut, void* cudaStream, rt_ply_stats* statsOut) {
+    if (!L || !dTriVerticesOut || !dTriNormalsOut) return fail(RT_ERR_INVALID, "rt_ply_ingest_static: null argument");
+    if (L->vertexCount < 0 || L->faceCount < 0 || L->vertexStride < 12 || (L->verticesPerFace != 3 && L->verticesPerFace != 4) ||
+        L->faceCountBytes < 1 || L->faceCountBytes > 4 || (L->faceIndexBytes != 1 && L->faceIndexBytes != 2 && L->faceIndexBytes != 4) ||
+        L->faceLeadBytes < 0 || L->faceTrailBytes < 0)
+        return fail(RT_ERR_INVALID, "rt_ply_ingest_static: inconsistent layout");
+    for (int a = 0; a < 3; a++)
+        if (L->posOffset[a] < 0 || L->posOffset[a] + 4 > L->vertexStride || L->normalOffset[a] + 4 > L->vertexStride)
+            return fail(RT_ERR_INVALID, "rt_ply_ingest_static: property offset outside the vertex record");
+    if ((L->vertexCount > 0 && !dVertexBlock) || (L->faceCount > 0 && !dFaceBlock)) return fail(RT_ERR_INVALID, "rt_ply_ingest_static: null block");
+    const int64_t nTris = L->faceCount * (L->verticesPerFace == 4 ? 2 : 1);
+    if (L->vertexCount > RT_PLY_STATIC_MAX_VERTICES || nTris > RT_PLY_STATIC_MAX_TRIANGLES)
+        return fail(RT_ERR_UNSUPPORTED, "rt_ply_ingest_static: the mesh has " + std::to_string(L->vertexCount) + " vertices and " +
+                    std::to_string(nTris) + " triangles, the static scratch holds " + std::to_string(RT_PLY_STATIC_MAX_VERTICES) + " and " +
+                    std::to_string(RT_PLY_STATIC_MAX_TRIANGLES) + ": use rt_ply_ingest");
+    int ndev = 0;
+    CK(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail(RT_ERR_INVALID, "invalid CUDA device index");
+    CK(cudaSetDevice(device));
+    const char* msg = "";
+    int64_t launches = 0;
+    const int rc = plyIngestStatic(*L, dVertexBlock, dFaceBlock, smooth, device, dTriVerticesOut, dTriNormalsOut, (cudaStream_t)cudaStream,
+                                   &msg, &launches);
+    if (rc != 0) {
+        cudaGetLastError();
+        return fail(rc == -2 ? RT_ERR_UNSUPPORTED : RT_ERR_INVALID, std::string("rt_ply_ingest_static: ") + msg);
+    }
+    if (statsOut) { statsOut->triangles = nTris; statsOut->kernelLaunches = launches; statsOut->deviceMs = 0; }
     return RT_OK;
 }
 

@@ -82,3 +82,33 @@ def make_cases(out_dir, seed=9):
     scenegen.write_ply(os.path.join(out_dir, "bad_index.ply"), pos, bad)
     add("bad_index", True, 0, True)
     return out
+
+
+# ---- raw element blocks for rt_ply_ingest / rt_ply_ingest_static (no file in between) --------------------------------
+def raw_blocks(pos, faces, normals=None):
+    """(layout kwargs, vertex block bytes, face block bytes) of a binary-little-endian mesh: float32 x, y, z [nx, ny, nz]
+    per vertex; `uchar count, int32 indices` per face (triangles or quads)."""
+    pos = np.ascontiguousarray(pos, "<f4")
+    faces = np.ascontiguousarray(faces, "<i4")
+    k = faces.shape[1]
+    if normals is None:
+        vblock, stride, noff = pos.tobytes(), 12, (-1, -1, -1)
+    else:
+        vblock, stride, noff = np.hstack([pos, np.ascontiguousarray(normals, "<f4")]).astype("<f4").tobytes(), 24, (12, 16, 20)
+    frec = np.zeros(len(faces), dtype=[("n", "u1"), ("i", "<i4", (k,))])
+    frec["n"] = k
+    frec["i"] = faces
+    layout = dict(vertexCount=len(pos), faceCount=len(faces), vertexStride=stride, posOffset=(0, 4, 8), normalOffset=noff,
+                  faceLeadBytes=0, faceCountBytes=1, faceIndexBytes=4, faceTrailBytes=0, verticesPerFace=k)
+    return layout, vblock, frec.tobytes()
+
+
+def make_layout(capi, kw):
+    L = capi.rt_ply_layout()
+    for name, v in kw.items():
+        if isinstance(v, tuple):
+            for a, x in enumerate(v):
+                getattr(L, name)[a] = x
+        else:
+            setattr(L, name, v)
+    return L

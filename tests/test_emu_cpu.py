@@ -567,3 +567,32 @@ def test_emulated_kernels_vs_independent_restatement(rough, depth, variants, inf
         # inf_light too: the children of a level with a non-finite Lo are walked (and counted) like the reference
         # walks them, then discarded (PATH_DEAD, Object+Extension.swift:277-280)
         assert rays == (counts["primary"], counts["shadow"], counts["secondary"]), variant
+
+
+def test_emulated_static_ingest_equals_rt_ply_ingest(emu):
+    """rt_ply_ingest_static (no allocation: intermediates in a fixed array inside the library) on the emulation build,
+    where device memory is host memory: bit-identical to rt_ply_ingest, call after call through the shared scratch,
+    limits enforced.  The B200 test is tests/test_zz_no_alloc.py."""
+    import ctypes as C
+    import ply_cases
+    from myraytracer_b200 import capi
+    L = emu
+    pos_a, tri_a = scenegen.terrain_mesh(40, 77)
+    pos_b, tri_b = scenegen.icosphere_mesh(2, radius=1.5, seed=9, disp=0.2)
+    quads = np.random.default_rng(5).integers(0, len(pos_b), size=(60, 4))
+    for blocks, smooth in ((ply_cases.raw_blocks(pos_a, tri_a), 1), (ply_cases.raw_blocks(pos_b, tri_b), 0),
+                           (ply_cases.raw_blocks(pos_b, quads, normals=pos_b * 1.7 + 0.1), 1), (ply_cases.raw_blocks(pos_a, tri_a), 1)):
+        kw, vblock, fblock = blocks
+        lay = ply_cases.make_layout(capi, kw)
+        n = kw["faceCount"] * (2 if kw["verticesPerFace"] == 4 else 1)
+        vb, fb = np.frombuffer(vblock, np.uint8), np.frombuffer(fblock, np.uint8)
+        p = lambda a: a.ctypes.data_as(C.c_void_p)
+        want_v, want_n, got_v, got_n = np.zeros((n, 9)), np.zeros((n, 9)), np.full((n, 9), np.nan), np.full((n, 9), np.nan)
+        assert L.rt_ply_ingest(C.byref(lay), p(vb), p(fb), smooth, 0, p(want_v), p(want_n), None) == 0
+        st = capi.rt_ply_stats()
+        assert L.rt_ply_ingest_static(C.byref(lay), p(vb), p(fb), smooth, 0, p(got_v), p(got_n), None, C.byref(st)) == 0, L.rt_last_error()
+        assert st.triangles == n
+        assert np.array_equal(got_v, want_v) and np.array_equal(got_n, want_n, equal_nan=True)
+    lay = ply_cases.make_layout(capi, dict(kw, vertexCount=capi.RT_PLY_STATIC_MAX_VERTICES + 1))
+    assert L.rt_ply_ingest_static(C.byref(lay), p(vb), p(fb), 1, 0, p(got_v), p(got_n), None, None) == capi.RT_ERR_UNSUPPORTED
+    assert b"65536" in L.rt_last_error()
