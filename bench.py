@@ -448,10 +448,14 @@ def run_ours(args):
     inst, inst_src, traffic, traffic_src = None, None, None, None
     try:
         ic = json.load(open(os.path.join(ROOT, "profiles", "inst_counts.json")))
-        key = f"{args.config}_n{world}_v{args.variant}"
+        key = f"{args.config}_n1_v{args.variant}"
         if key in ic:
-            inst, inst_src = ic[key]["warp_inst_per_launch"], ic[key]["source"]
-            traffic, traffic_src = ic[key].get("dram_bytes_per_launch"), ic[key]["source"]
+            # N > 1: ncu must not wrap a multi-rank command, so rank 0's launch is the N = 1 capture scaled by its share of the rays
+            share = float(st["rays"]) / float(ic[key]["rays_per_launch"]) if world > 1 else 1.0
+            inst, inst_src = ic[key]["warp_inst_per_launch"] * share, ic[key]["source"]
+            traffic, traffic_src = ic[key].get("dram_bytes_per_launch") * share, ic[key]["source"]
+            if world > 1:
+                inst_src = traffic_src = f"ESTIMATE: {share:.4f} (rank 0's share of the frame's rays) x the N = 1 capture; " + inst_src
     except Exception:
         pass
     sm_mhz = clocks.get("sm_mhz") or float(drv.get("sm_max_mhz", 1965.0))
