@@ -498,7 +498,7 @@ def run_ours(args):
             "wall_ms_per_step": wall * 1e3 / args.steps, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
             "frame_hash": frame_hash_abi, "frame_hash_ranks_path": frame_hash_ranks,
             "frame_hash_note": "BLAKE2b-64 of the RGBA8 frame rt_render returned / the multi-process path gathered: equal to each other and for every N",
-            "roofline": roofline, "build_ms": info["buildMs"], "upload_ms": info["uploadMs"],
+            "roofline": roofline, "build_ms": info["buildMs"], "upload_ms": info["uploadMs"], "wide_nodes": info.get("wideNodes", 0),
             "bvh_build": ("host binned SAH" if not info["deviceBuiltBlas"] else
                           "device binned SAH" if os.environ.get("RTCUDA_BUILD") == "device-sah" else "device LBVH")}
     if parity is not None:

@@ -201,7 +201,7 @@ typedef struct rt_scene_info {
     int32_t device;
     int32_t deviceBuiltBlas;      /* mesh BVHs built by a device builder (RT_BUILD_DEVICE_*) */
     int32_t deviceCount;          /* GPUs the scene is resident on (rt_scene_create_multi), 1 otherwise */
-    int32_t reserved;
+    int32_t wideNodes;            /* nodes of the wide BVHs the beam walk of coherent packets uses (0: none built) */
     double replicateMs;           /* device-to-device copies of the scene onto the other GPUs */
 } rt_scene_info;
 

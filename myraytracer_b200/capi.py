@@ -108,7 +108,7 @@ class rt_scene_info(C.Structure):
     _fields_ = [(n, C.c_int64) for n in ("triangles", "spheres", "planes", "instances", "blasCount", "blasNodes",
                                          "tlasNodes", "maxLeafSize", "maxDepth", "deviceBytes")]
     _fields_ += [("buildMs", C.c_double), ("uploadMs", C.c_double), ("device", C.c_int32), ("deviceBuiltBlas", C.c_int32),
-                 ("deviceCount", C.c_int32), ("reserved", C.c_int32), ("replicateMs", C.c_double)]
+                 ("deviceCount", C.c_int32), ("wideNodes", C.c_int32), ("replicateMs", C.c_double)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

@@ -237,6 +237,76 @@ void buildBlas(const BlasBuildInput& in, BlasBuildOutput& out) {
     }
 }
 
+void collapseWide(const std::vector<GNode>& nodes, int32_t rootRef, WideBuildOutput& out) {
+    out = WideBuildOutput();
+    if (rootRef < 0 || rootRef == kEmptyRef || nodes.empty()) return;
+    struct Child { float lo[3], hi[3]; int32_t ref; double area; };
+    auto children = [&](int32_t n, Child& a, Child& b) {
+        const GNode& g = nodes[(size_t)n];
+        a.lo[0] = g.q0[0]; a.lo[1] = g.q0[1]; a.lo[2] = g.q0[2]; a.hi[0] = g.q0[3]; a.hi[1] = g.q1[0]; a.hi[2] = g.q1[1];
+        b.lo[0] = g.q1[2]; b.lo[1] = g.q1[3]; b.lo[2] = g.q2[0]; b.hi[0] = g.q2[1]; b.hi[1] = g.q2[2]; b.hi[2] = g.q2[3];
+        a.ref = g.child0; b.ref = g.child1;
+        for (Child* c : {&a, &b}) {
+            const double ex = (double)c->hi[0] - c->lo[0], ey = (double)c->hi[1] - c->lo[1], ez = (double)c->hi[2] - c->lo[2];
+            c->area = ex * ey + ey * ez + ez * ex;
+        }
+    };
+    struct Item { int32_t bnode, wnode; int depth; };
+    std::vector<Item> todo;
+    out.nodes.emplace_back();
+    out.rootRef = 0;
+    todo.push_back({rootRef, 0, 1});
+    std::vector<Child> list;
+    while (!todo.empty()) {
+        const Item it = todo.back();
+        todo.pop_back();
+        if (it.depth > out.depth) out.depth = it.depth;
+        list.assign(2, Child());
+        children(it.bnode, list[0], list[1]);
+        for (size_t k = 0; k < list.size();)              // a binary node with one child only (kEmptyRef): drop the slot
+            if (list[k].ref == kEmptyRef) list.erase(list.begin() + (long)k); else k++;
+        while ((int)list.size() < kWide) {
+            int best = -1;
+            for (int k = 0; k < (int)list.size(); k++)
+                if (list[k].ref >= 0 && (best < 0 || list[k].area > list[best].area)) best = k;
+            if (best < 0) break;
+            Child a, b;
+            children(list[best].ref, a, b);
+            list[best] = a;
+            list.push_back(b);
+            for (size_t k = 0; k < list.size();)
+                if (list[k].ref == kEmptyRef) list.erase(list.begin() + (long)k); else k++;
+        }
+        WNode w;
+        std::memset(&w, 0, sizeof w);
+        const int n = (int)list.size();
+        for (int k = 0; k < kWide; k++) {
+            if (k < n) {
+                for (int a = 0; a < 3; a++) { w.lo[a][k] = list[k].lo[a]; w.hi[a][k] = list[k].hi[a]; }
+                if (list[k].ref >= 0) {
+                    w.child[k] = (int32_t)out.nodes.size();
+                    out.nodes.emplace_back();
+                    todo.push_back({list[k].ref, w.child[k], it.depth + 1});
+                } else {
+                    w.child[k] = list[k].ref;
+                }
+            } else {        // empty slot: an inverted box fails the beam test on every axis
+                for (int a = 0; a < 3; a++) { w.lo[a][k] = 1e30f; w.hi[a][k] = -1e30f; }
+                w.child[k] = kEmptyRef;
+            }
+        }
+        for (int a = 0; a < 3; a++) {
+            uint8_t asc[RT_WIDE], desc[RT_WIDE];
+            for (int k = 0; k < kWide; k++) asc[k] = desc[k] = (uint8_t)k;
+            std::stable_sort(asc, asc + n, [&](uint8_t x, uint8_t y) { return w.lo[a][x] < w.lo[a][y]; });
+            std::stable_sort(desc, desc + n, [&](uint8_t x, uint8_t y) { return w.hi[a][x] > w.hi[a][y]; });
+            std::memcpy(w.perm[2 * a], asc, (size_t)kWide);
+            std::memcpy(w.perm[2 * a + 1], desc, (size_t)kWide);
+        }
+        out.nodes[(size_t)it.wnode] = w;
+    }
+}
+
 void buildTlas(const double* wb, int64_t n, TlasBuildOutput& out) {
     out = TlasBuildOutput();
     if (n <= 0) return;

@@ -52,6 +52,18 @@ cudaError_t buildBlasDevice(const double* dVerts, const BlasBuildInput& in, Blas
 cudaError_t buildBlasDeviceSah(const double* dVerts, const BlasBuildInput& in, BlasBuildOutput& out, int depthLimit, int64_t* launches);
 #endif
 
+// Wide BVH of the beam walk (rt_beam.cuh, gpu_layout.h: WNode): the binary tree of any of the builders collapsed into
+// nodes of up to kWide children — starting from a node's two children, the inner child with the largest box is
+// replaced by its own two children until kWide are reached or only leaves are left.  Boxes and leaf references are
+// taken over unchanged, so the leaves (and the triangle order) are the binary tree's.  References stay relative to
+// the BLAS like the input's.  rootRef = kEmptyRef (no wide tree) when the binary root is a leaf.
+struct WideBuildOutput {
+    std::vector<WNode> nodes;       // node 0 = root
+    int32_t rootRef = kEmptyRef;
+    int depth = 0;                  // levels of wide nodes
+};
+void collapseWide(const std::vector<GNode>& nodes, int32_t rootRef, WideBuildOutput& out);
+
 // TLAS over instance world bounds (FP64, one instance per leaf).
 struct TlasBuildOutput {
     std::vector<TNode> nodes;

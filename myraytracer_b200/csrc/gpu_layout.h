@@ -41,6 +41,24 @@ struct RT_ALIGN(16) GNode {
     int32_t child0, child1, pad0, pad1;
 };
 
+// Wide node of the beam walk (rt_beam.cuh): kWide children, one lane of the warp per child.  Structure of arrays
+// inside the node, so that the lanes' loads of one field are one contiguous run: lo[axis][slot], hi[axis][slot] are
+// the GNode boxes of the collapsed BVH2 (same centre, same padding, same outward rounding), child[slot] a wide node
+// index (>= 0), a leaf reference (< 0, as in GNode) or kEmptyRef with an inverted box.  perm[2 * axis + (sigma < 0)]
+// lists the slots by the coordinate of the face a beam travelling along +axis / -axis meets first (lo ascending / hi
+// descending), empty slots last: lane r tests slot perm[..][r], so the hit mask of a visit is already in
+// front-to-back order.  No counterpart in the reference (its BVHNode is the 96-byte binary node of
+// Accelearion/BVH.swift:16-30).
+#ifndef RT_WIDE
+#define RT_WIDE 16
+#endif
+static const int kWide = RT_WIDE;
+struct RT_ALIGN(128) WNode {
+    float lo[3][RT_WIDE], hi[3][RT_WIDE];
+    int32_t child[RT_WIDE];
+    uint8_t perm[6][RT_WIDE];
+};
+
 struct RT_ALIGN(16) GTri {   // float-exact vertices (PLY meshes: Helpers/PLYReader.swift:85-101)
     float v0[3]; int32_t triIndex;
     float v1[3]; int32_t pad1;
@@ -79,7 +97,8 @@ struct RT_ALIGN(16) GInstance {
     int32_t rootRef;       // child reference of the BLAS root (inner node 0 or a leaf)
     int32_t hasMotion;     // instanceMotion != 0 or mesh motion blur != 0
     int32_t bigBlas;       // mesh with more than kBigBlasTriangles triangles: incoherent packets walk it per lane (rt_packet.cuh)
-    int32_t pad[2];
+    int32_t wideRoot;      // root of the mesh's wide BVH in DeviceScene::wnodes (beam walk, rt_beam.cuh); kEmptyRef: none
+    int32_t pad;
     double meshMotion[3];  // Triangle.motionBlur of this mesh
     double pad2;
 };
@@ -117,6 +136,7 @@ struct DeviceScene {
     const double* jitter;          // area lights: the 10x10 stratified table, xs[100] then ys[100] (:92-93,646-659)
     const RefNode* refTlas;        // scenes with instanceMotion: the reference's own TLAS topology (else null)
     const int32_t* refTlasPrim;    // its primitiveIdx array (instance indices in leaf order)
+    const WNode* wnodes;           // wide BVHs of the meshes (collapsed from `nodes`), all BLASes concatenated
     int32_t refTlasNodes;          // 0: not used
     int32_t pad1;
     int32_t tlasRootRef;

@@ -79,6 +79,7 @@ static const size_t kFrameStateBytes = 16 * sizeof(unsigned long long) + 64;
 struct BlasInfo {
     int kind = INST_MESH; int64_t prim = 0; int64_t matId = 0; int smooth = 0;
     int32_t nodeBase = 0, triBase = 0, rootRef = kEmptyRef; int f64 = 0;
+    int32_t wideRoot = kEmptyRef;      // root in DeviceScene::wnodes, kEmptyRef = this mesh has no wide BVH
     int64_t triCount = 0;              // triangles of a mesh BLAS (slots triBase .. triBase + triCount of tris / trisD)
     double lo[3], hi[3], centre[3];
     double motion[3] = {0, 0, 0};      // Triangle.motionBlur of the mesh (RTContext.swift:280,345)
@@ -118,6 +119,7 @@ struct rt_scene {
     rt_scene_info info{};
     int64_t meshes = 0;
     // device allocations
+    WNode* dWNodes = nullptr;          // wide BVHs of the beam walk (collapsed from dNodes)
     GNode* dNodes = nullptr; GTri* dTris = nullptr; GTriD* dTrisD = nullptr; double* dNormals = nullptr;
     GNode* dTlas = nullptr; GInstance* dInst = nullptr; GMaterial* dMat = nullptr; GPointLight* dLights = nullptr;
     GAreaLight* dAreaLights = nullptr; double* dJitter = nullptr;
@@ -182,6 +184,7 @@ static void fillInstance(const rt_instance& in, const BlasInfo& bi, GInstance& g
     g.smooth = bi.smooth;
     g.nodeBase = bi.nodeBase; g.triBase = bi.triBase; g.triF64 = bi.f64; g.rootRef = bi.rootRef;
     g.bigBlas = (bi.kind == INST_MESH && bi.triCount > bigBlasTriangles) ? 1 : 0;
+    g.wideRoot = bi.kind == INST_MESH ? bi.wideRoot : kEmptyRef;
     g.matId = in.hasMaterialOverride ? in.materialOverride : bi.matId;  // RTContext.swift:704
     g.primIndex = bi.prim;
     const bool moves = in.instanceMotion[0] != 0 || in.instanceMotion[1] != 0 || in.instanceMotion[2] != 0;
@@ -232,6 +235,7 @@ static void bindDeviceScene(rt_scene* sc) {
     S.tlas = sc->dTlas; S.instances = sc->dInst; S.materials = sc->dMat; S.pointLights = sc->dLights;
     S.areaLights = sc->dAreaLights; S.jitter = sc->dJitter;
     S.refTlas = sc->dRefTlas; S.refTlasPrim = sc->dRefTlasPrim;
+    S.wnodes = sc->dWNodes;
 }
 
 extern "C" {
@@ -290,9 +294,15 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     std::vector<BlasInfo>& blasInfo = sc->blasInfo;
     blasInfo.assign((size_t)d->nBlas, BlasInfo());
     std::vector<GNode> nodes;
+    std::vector<WNode> wnodes;
     std::vector<GTri> tris;
     std::vector<GTriD> trisD;
     int64_t maxDepth = 0, maxLeaf = 0;
+    // wide BVHs for the beam walk of coherent packets (rt_beam.cuh): RTCUDA_WIDE=1 builds them (first B200 run: C4 12.4 ms
+    // against 10.8 ms for the binary packet walk, profiles/r2q — off until it wins)
+    const char* wideEnv = std::getenv("RTCUDA_WIDE");
+    const bool wantWide = wideEnv && std::atoi(wideEnv) != 0;
+    const int64_t wideMinTris = 64;
     for (int64_t b = 0; b < d->nBlas; b++) {
         const rt_blas& bl = d->blas[b];
         BlasInfo& bi = blasInfo[b];
@@ -366,6 +376,22 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
         };
         if ((int64_t)bi.triBase + bl.primCount >= (int64_t)1 << 27 || (int64_t)nodes.size() + (int64_t)out.nodes.size() >= kEmptyRef)
             return fail(RT_ERR_UNSUPPORTED, "scene exceeds the 2^27 triangles / 2^31 nodes of the device references");
+        if (wantWide && bl.primCount >= wideMinTris && out.rootRef >= 0 && out.rootRef != kEmptyRef) {
+            WideBuildOutput wide;
+            collapseWide(out.nodes, out.rootRef, wide);
+            // every visit pushes at most kWide entries and pops one: the beam stack must hold a root-to-leaf path of them
+            if (wide.rootRef == 0 && (wide.depth - 1) * (kWide - 1) + kWide + 1 <= beamStackCapacity() &&
+                wnodes.size() + wide.nodes.size() < (size_t)kEmptyRef / (size_t)kWide) {
+                const int32_t wbase = (int32_t)wnodes.size();
+                for (WNode& w : wide.nodes)
+                    for (int k = 0; k < kWide; k++) {
+                        if (w.child[k] == kEmptyRef) continue;
+                        w.child[k] = w.child[k] >= 0 ? w.child[k] + wbase : rebase(w.child[k]);
+                    }
+                bi.wideRoot = wbase;
+                wnodes.insert(wnodes.end(), wide.nodes.begin(), wide.nodes.end());
+            }
+        }
         for (GNode& g : out.nodes) { g.child0 = rebase(g.child0); g.child1 = rebase(g.child1); }
         bi.rootRef = rebase(out.rootRef);
         nodes.insert(nodes.end(), out.nodes.begin(), out.nodes.end());
@@ -459,6 +485,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     int64_t bytes = 0;
     int rc;
     if ((rc = upload(nodes, &sc->dNodes, bytes, &sc->arrays, sc))) return rc;
+    if ((rc = upload(wnodes, &sc->dWNodes, bytes, &sc->arrays, sc))) return rc;
     if ((rc = upload(tris, &sc->dTris, bytes, &sc->arrays, sc))) return rc;
     if ((rc = upload(trisD, &sc->dTrisD, bytes, &sc->arrays, sc))) return rc;
     if ((rc = upload(normals, &sc->dNormals, bytes, &sc->arrays, sc))) return rc;
@@ -554,6 +581,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     I.triangles = d->nTriangles; I.spheres = d->nSpheres; I.planes = d->nPlanes; I.instances = d->nInstances; I.blasCount = d->nBlas;
     I.blasNodes = (int64_t)nodes.size(); I.tlasNodes = (int64_t)tl.nodes.size(); I.maxLeafSize = maxLeaf; I.maxDepth = maxDepth;
     I.deviceBytes = bytes; I.buildMs = t1 - t0; I.uploadMs = t2 - t1; I.device = device; I.deviceBuiltBlas = deviceBuilt; I.deviceCount = 1;
+    I.wideNodes = (int32_t)wnodes.size();
     return RT_OK;
 }
 
@@ -568,6 +596,7 @@ void rt_scene_destroy(rt_scene_t* sc) {
     cudaSetDevice(sc->device);
     if (sc->stream) cudaStreamSynchronize(sc->stream);
     if (sc->side) cudaStreamSynchronize(sc->side);
+    cudaFree(sc->dWNodes);
     cudaFree(sc->dNodes); cudaFree(sc->dTris); cudaFree(sc->dTrisD); cudaFree(sc->dNormals); cudaFree(sc->dTlas);
     cudaFree(sc->dInst); cudaFree(sc->dMat); cudaFree(sc->dLights); cudaFree(sc->dCounters);
     cudaFree(sc->dAreaLights); cudaFree(sc->dJitter); cudaFree(sc->dAreaIndex);

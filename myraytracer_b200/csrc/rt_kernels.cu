@@ -275,5 +275,6 @@ cudaError_t launchSchedule(unsigned* tileCost, int* tileOrder, unsigned* work, i
 
 int renderBlockSize(int variant) { return variant == KV_FAST ? blockSizeVariantFast() : blockSizeVariantGeneral(); }
 int renderStackCapacity() { return RT_STACK; }
+int beamStackCapacity() { return RT_BSTACK; }
 
 }  // namespace rtg

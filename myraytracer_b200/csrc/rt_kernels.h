@@ -57,6 +57,10 @@ static const int kPathFields = 11;
 #define RT_SSTACK 24  // entries of the per-lane stack kept in shared memory; the rest spill to local memory
 #endif
 
+#ifndef RT_BSTACK
+#define RT_BSTACK 127 // entries of the beam walk's stack (rt_beam.cuh) besides its sentinel; it shares the packet stack's memory
+#endif
+
 // kernel variants (rt_kernels.cu); values match rt_render_params.kernelVariant - 1
 enum KernelVariant { KV_FAST = 0, KV_GENERAL = 1, KV_COUNT = 2 };
 
@@ -92,6 +96,7 @@ cudaError_t launchSchedule(unsigned* tileCost, int* tileOrder, unsigned* work, i
 size_t scheduleWorkBytes(int nTiles);   // scratch of launchSchedule
 int renderBlockSize(int variant);
 int renderStackCapacity();
+int beamStackCapacity();                // entries of the beam walk's stack (rt_beam.cuh)
 cudaError_t renderOccupancy(int variant, int* blocksPerSm, bool counters);
 
 }  // namespace rtg

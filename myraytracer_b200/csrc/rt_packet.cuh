@@ -39,8 +39,8 @@ __device__ __forceinline__ void stsPair(uint32_t addr, int a, int b) {
 __device__ __forceinline__ int2 ldsPair(uint32_t addr) { return *reinterpret_cast<int2*>(rtemu::g_sharedBase + (intptr_t)(int32_t)addr); }
 #endif
 #ifndef RT_WSTACK
-#define RT_WSTACK 64    // BLAS entries per warp (tree depth is checked against RT_STACK at build time)
-#endif
+#define RT_WSTACK (RT_BSTACK + 1)   // BLAS entries per warp: the packet walk needs the tree depth (checked against RT_STACK at
+#endif                              // build time, <= 64), the beam walk of the wide tree RT_BSTACK entries + its sentinel
 #define RT_WTSTACK 40   // TLAS entries per warp
 #ifdef RT_WARPTIMES
 #define RT_WT_EXTRA 2   // profiling build: (node visits, lanes), (leaf visits, lane-triangle tests) per warp
@@ -48,6 +48,10 @@ __device__ __forceinline__ int2 ldsPair(uint32_t addr) { return *reinterpret_cas
 #define RT_WT_EXTRA 0
 #endif
 #define RT_WARP_STACK_INT2 (RT_WSTACK + RT_WTSTACK + RT_WT_EXTRA)
+
+}  // namespace rtg
+#include "rt_beam.cuh"
+namespace rtg {
 
 // Packet walk of one mesh BLAS.  inMask (warp-uniform): lanes whose ray takes part.
 // anyhit: run-time, warp-uniform (one copy of the loop for closest-hit and shadow packets).
@@ -112,6 +116,9 @@ __device__ __forceinline__ uint32_t packetBlas(const DeviceScene& S, const GInst
             if ((uint32_t)ch.y < 0x7fffffffu) prefetchL1(nodes + ch.y);
 #endif
             if (COUNT && (curMask & bit) != 0) C.box += 2;
+#ifdef RT_BEAM_STATS
+            if (COUNT && bit == 1u) C.sphere++;           // warp-level: binary node visits
+#endif
 #ifdef RT_WARPTIMES
             if (bit == 1u) { wstack[RT_WSTACK + RT_WTSTACK].x++; wstack[RT_WSTACK + RT_WTSTACK].y += __popc(curMask); }
 #endif
@@ -151,6 +158,9 @@ __device__ __forceinline__ uint32_t packetBlas(const DeviceScene& S, const GInst
             const bool f64 = (ref & 8u) != 0;
             const bool inl = (curMask & bit) != 0;
             bool occ = false;
+#ifdef RT_BEAM_STATS
+            if (COUNT && bit == 2u) C.plane++;            // warp-level: leaf visits
+#endif
 #ifdef RT_WARPTIMES
             if (bit == 1u) { wstack[RT_WSTACK + RT_WTSTACK + 1].x++; wstack[RT_WSTACK + RT_WTSTACK + 1].y += __popc(curMask) * count; }
 #endif
@@ -204,6 +214,13 @@ __device__ __forceinline__ uint32_t packetInstance(const DeviceScene& S, int idx
             bool o1 = false;
             if (in) o1 = traverseBlas<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, nullptr, 0, C);
             return __ballot_sync(RT_FULL, o1);
+        }
+        if (!(INCOHERENT && incoherent) && I.wideRoot != kEmptyRef) {     // coherent packet, mesh with a wide tree: beam walk
+            bool formed;
+            const uint32_t r = beamBlas<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, inMask, wstack, C, formed);
+            if (formed) return r;
+            // no beam, or its budget spent: the packet walk finishes (closest hits found so far stand; lanes found occluded are done)
+            return r | packetBlas<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, inMask & ~r, wstack, C);
         }
         return packetBlas<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, inMask, wstack, C);
     }

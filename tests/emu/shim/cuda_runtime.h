@@ -14,6 +14,7 @@
 #error "the emulation shim is for -DRT_EMU test builds only"
 #endif
 
+#include <fenv.h>
 #include <math.h>
 #include <stdint.h>
 #include <stdlib.h>
@@ -109,12 +110,35 @@ inline unsigned __match_any_sync(unsigned, int v) {
     for (int l = 0; l < rtemu::warpLanes(); l++) if (*rtemu::exchangeSlot(l) == (uint64_t)(uint32_t)v) m |= 1u << l;
     return m;
 }
+inline int __reduce_min_sync(unsigned, int v) {
+    const int lane = (int)(threadIdx.x & 31u);
+    rtemu::nextExchange();
+    *rtemu::exchangeSlot(lane) = (uint64_t)(uint32_t)v;
+    rtemu::warpBarrier();
+    int m = v;
+    for (int l = 0; l < rtemu::warpLanes(); l++) { const int o = (int)(uint32_t)*rtemu::exchangeSlot(l); if (o < m) m = o; }
+    return m;
+}
+inline int __reduce_max_sync(unsigned, int v) {
+    const int lane = (int)(threadIdx.x & 31u);
+    rtemu::nextExchange();
+    *rtemu::exchangeSlot(lane) = (uint64_t)(uint32_t)v;
+    rtemu::warpBarrier();
+    int m = v;
+    for (int l = 0; l < rtemu::warpLanes(); l++) { const int o = (int)(uint32_t)*rtemu::exchangeSlot(l); if (o > m) m = o; }
+    return m;
+}
 inline void __syncwarp(unsigned = 0xffffffffu) { rtemu::warpBarrier(); }
 inline void __syncthreads() { rtemu::blockBarrier(); }
 
 // ---- scalar intrinsics --------------------------------------------------------------------------------------------
 template <class T> inline T __ldg(const T* p) { return *p; }
 inline float __fmaf_rn(float a, float b, float c) { return fmaf(a, b, c); }
+// one rounding, towards -inf / +inf (FFMA.RM / FFMA.RP): fmaf under the directed rounding mode
+inline float __fmaf_rd(float a, float b, float c) { const int o = fegetround(); fesetround(FE_DOWNWARD); volatile float r = fmaf(a, b, c); fesetround(o); return r; }
+inline float __fmaf_ru(float a, float b, float c) { const int o = fegetround(); fesetround(FE_UPWARD); volatile float r = fmaf(a, b, c); fesetround(o); return r; }
+inline int __float_as_int(float f) { int i; memcpy(&i, &f, 4); return i; }
+inline float __int_as_float(int i) { float f; memcpy(&f, &i, 4); return f; }
 inline float __double2float_rd(double x) { float f = (float)x; return (double)f > x ? nextafterf(f, -INFINITY) : f; }
 inline float __double2float_ru(double x) { float f = (float)x; return (double)f < x ? nextafterf(f, INFINITY) : f; }
 inline double __longlong_as_double(long long v) { double d; memcpy(&d, &v, 8); return d; }

@@ -10,7 +10,7 @@ for tag in $2; do
 import json
 try:
     d = json.loads(open("gpurun_out/ab_${tag}_$c.json").read())
-    print("$tag", "$c", round(d["ms_per_step"], 3), round(d["detail"]["ms_first_frame"], 3), round(d["e2e"]["ms_per_step"], 3), d["frame_hash"])
+    print("$tag", "$c", round(d["ms_per_step"], 3), round(d["detail"]["ms_first_frame"], 3), round(d["e2e"]["ms_per_step"], 3), d["frame_hash"], "wide", d.get("wide_nodes"))
 except Exception as e:
     print("$tag", "$c", "FAILED", e)
 PY
