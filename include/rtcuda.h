@@ -255,6 +255,10 @@ int64_t rt_scene_get_schedule(rt_scene_t* scene, int32_t* orderOut, int64_t capa
  * references, csrc/gpu_layout.h: GNode), all BLASes concatenated.  Returns the size in bytes (< 0: error) and copies
  * min(size, capacityBytes).  No reference analogue; for tests (the builders of rt_scene_desc.buildMode compared). */
 int64_t rt_scene_read_blas_nodes(rt_scene_t* scene, void* nodesOut, int64_t capacityBytes);
+/* The wide BVHs of the beam walk (built when RTCUDA_WIDE=1; csrc/gpu_layout.h: WNode, 16 children of 32 bytes: FP32
+ * box, child reference, sort axis in child 0), all BLASes concatenated; rt_scene_info.wideNodes of them.  Same calling
+ * convention.  No reference analogue; for tests (the collapse of the binary tree checked leaf by leaf). */
+int64_t rt_scene_read_wide_nodes(rt_scene_t* scene, void* nodesOut, int64_t capacityBytes);
 
 /* Render one camera.  Blocking; one render at a time per scene handle (not re-entrant), different scenes may render
  * from different host threads at once (each scene has its own non-blocking stream).  Host buffers, all optional

@@ -131,7 +131,7 @@ HIT_ID_DTYPE = np.dtype([("inst", "<i4"), ("kind", "<i4"), ("prim", "<i8"), ("t"
 # every symbol include/rtcuda.h and include/rtcuda_host.h declare
 EXPORTS = ["rt_abi_version", "rt_device_count", "rt_last_error", "rt_scene_create", "rt_scene_destroy",
            "rt_scene_create_multi", "rt_scene_device_count", "rt_host_alloc", "rt_host_free", "rth_engine_create_multi",
-           "rt_scene_get_info", "rt_scene_get_schedule", "rt_scene_read_blas_nodes", "rt_scene_update_instances", "rt_ply_ingest", "rt_ply_ingest_static", "rt_render", "rt_render_device", "rt_render_finish",
+           "rt_scene_get_info", "rt_scene_get_schedule", "rt_scene_read_blas_nodes", "rt_scene_read_wide_nodes", "rt_scene_update_instances", "rt_ply_ingest", "rt_ply_ingest_static", "rt_render", "rt_render_device", "rt_render_finish",
            "rt_shared_buffer_create", "rt_shared_buffer_open", "rt_shared_buffer_close",
            "rth_last_error", "rth_engine_create", "rth_engine_destroy", "rth_engine_ready", "rth_engine_camera_count",
            "rth_engine_camera", "rth_engine_scene", "rth_engine_describe", "rth_engine_instance_object_ids",
@@ -177,6 +177,8 @@ def declare(L):
     L.rt_scene_get_schedule.restype = C.c_int64
     L.rt_scene_read_blas_nodes.argtypes = [vp, vp, C.c_int64]
     L.rt_scene_read_blas_nodes.restype = C.c_int64
+    L.rt_scene_read_wide_nodes.argtypes = [vp, vp, C.c_int64]
+    L.rt_scene_read_wide_nodes.restype = C.c_int64
     L.rt_ply_ingest.argtypes = [C.POINTER(rt_ply_layout), vp, vp, C.c_int32, C.c_int32, vp, vp, C.POINTER(rt_ply_stats)]
     L.rt_ply_ingest_static.argtypes = [C.POINTER(rt_ply_layout), vp, vp, C.c_int32, C.c_int32, vp, vp, vp, C.POINTER(rt_ply_stats)]
     L.rt_render.argtypes = [vp, C.POINTER(rt_camera), C.POINTER(rt_render_params), vp, vp, vp, C.POINTER(rt_stats)]

@@ -277,32 +277,40 @@ void collapseWide(const std::vector<GNode>& nodes, int32_t rootRef, WideBuildOut
             for (size_t k = 0; k < list.size();)
                 if (list[k].ref == kEmptyRef) list.erase(list.begin() + (long)k); else k++;
         }
+        // front-to-back order: sort by the box centre along the axis on which the centres spread the most
+        const int n = (int)list.size();
+        int axis = 0;
+        {
+            double best = -1;
+            for (int a = 0; a < 3; a++) {
+                double cmin = kInfD, cmax = -kInfD;
+                for (int k = 0; k < n; k++) { const double c = (double)list[k].lo[a] + list[k].hi[a]; cmin = std::min(cmin, c); cmax = std::max(cmax, c); }
+                if (cmax - cmin > best) { best = cmax - cmin; axis = a; }
+            }
+            std::stable_sort(list.begin(), list.end(), [&](const Child& x, const Child& y) {
+                return (double)x.lo[axis] + x.hi[axis] < (double)y.lo[axis] + y.hi[axis];
+            });
+        }
         WNode w;
         std::memset(&w, 0, sizeof w);
-        const int n = (int)list.size();
         for (int k = 0; k < kWide; k++) {
+            WChild& c = w.c[k];
             if (k < n) {
-                for (int a = 0; a < 3; a++) { w.lo[a][k] = list[k].lo[a]; w.hi[a][k] = list[k].hi[a]; }
+                c.lo[0] = list[k].lo[0]; c.lo[1] = list[k].lo[1]; c.lo[2] = list[k].lo[2];
+                c.hi0 = list[k].hi[0]; c.hi1 = list[k].hi[1]; c.hi2 = list[k].hi[2];
                 if (list[k].ref >= 0) {
-                    w.child[k] = (int32_t)out.nodes.size();
+                    c.ref = (int32_t)out.nodes.size();
                     out.nodes.emplace_back();
-                    todo.push_back({list[k].ref, w.child[k], it.depth + 1});
+                    todo.push_back({list[k].ref, c.ref, it.depth + 1});
                 } else {
-                    w.child[k] = list[k].ref;
+                    c.ref = list[k].ref;
                 }
-            } else {        // empty slot: an inverted box fails the beam test on every axis
-                for (int a = 0; a < 3; a++) { w.lo[a][k] = 1e30f; w.hi[a][k] = -1e30f; }
-                w.child[k] = kEmptyRef;
+            } else {        // empty slot: an inverted box fails the beam test
+                c.lo[0] = c.lo[1] = c.lo[2] = 1e30f; c.hi0 = c.hi1 = c.hi2 = -1e30f;
+                c.ref = kEmptyRef;
             }
         }
-        for (int a = 0; a < 3; a++) {
-            uint8_t asc[RT_WIDE], desc[RT_WIDE];
-            for (int k = 0; k < kWide; k++) asc[k] = desc[k] = (uint8_t)k;
-            std::stable_sort(asc, asc + n, [&](uint8_t x, uint8_t y) { return w.lo[a][x] < w.lo[a][y]; });
-            std::stable_sort(desc, desc + n, [&](uint8_t x, uint8_t y) { return w.hi[a][x] > w.hi[a][y]; });
-            std::memcpy(w.perm[2 * a], asc, (size_t)kWide);
-            std::memcpy(w.perm[2 * a + 1], desc, (size_t)kWide);
-        }
+        w.c[0].aux = axis;
         out.nodes[(size_t)it.wnode] = w;
     }
 }

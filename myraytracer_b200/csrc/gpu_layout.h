@@ -41,22 +41,25 @@ struct RT_ALIGN(16) GNode {
     int32_t child0, child1, pad0, pad1;
 };
 
-// Wide node of the beam walk (rt_beam.cuh): kWide children, one lane of the warp per child.  Structure of arrays
-// inside the node, so that the lanes' loads of one field are one contiguous run: lo[axis][slot], hi[axis][slot] are
-// the GNode boxes of the collapsed BVH2 (same centre, same padding, same outward rounding), child[slot] a wide node
-// index (>= 0), a leaf reference (< 0, as in GNode) or kEmptyRef with an inverted box.  perm[2 * axis + (sigma < 0)]
-// lists the slots by the coordinate of the face a beam travelling along +axis / -axis meets first (lo ascending / hi
-// descending), empty slots last: lane r tests slot perm[..][r], so the hit mask of a visit is already in
-// front-to-back order.  No counterpart in the reference (its BVHNode is the 96-byte binary node of
-// Accelearion/BVH.swift:16-30).
+// Wide node of the beam walk (rt_beam.cuh): kWide children, one lane of the warp per child.  A child is one 32-byte
+// record — two 16-byte vector loads per lane, the warp's loads covering the node's 512 contiguous bytes: the GNode box
+// of the collapsed BVH2 (same centre, same padding, same outward rounding) and `ref`, a wide node index (>= 0), a leaf
+// reference (< 0, as in GNode) or kEmptyRef with an inverted box.  The children are sorted by their centre along
+// the axis on which the node's children spread the most (child[0].aux), empty slots last: a beam travelling up that
+// axis meets them in slot order, one travelling down it in reverse order.  No counterpart in the reference (its
+// BVHNode is the 96-byte binary node of Accelearion/BVH.swift:16-30).
 #ifndef RT_WIDE
 #define RT_WIDE 16
 #endif
 static const int kWide = RT_WIDE;
+struct RT_ALIGN(16) WChild {
+    float lo[3], hi0;        // lo.x lo.y lo.z hi.x
+    float hi1, hi2;          // hi.y hi.z
+    int32_t ref;
+    int32_t aux;             // child 0: the node's sort axis (0..2)
+};
 struct RT_ALIGN(128) WNode {
-    float lo[3][RT_WIDE], hi[3][RT_WIDE];
-    int32_t child[RT_WIDE];
-    uint8_t perm[6][RT_WIDE];
+    WChild c[RT_WIDE];
 };
 
 struct RT_ALIGN(16) GTri {   // float-exact vertices (PLY meshes: Helpers/PLYReader.swift:85-101)
@@ -100,7 +103,7 @@ struct RT_ALIGN(16) GInstance {
     int32_t wideRoot;      // root of the mesh's wide BVH in DeviceScene::wnodes (beam walk, rt_beam.cuh); kEmptyRef: none
     int32_t pad;
     double meshMotion[3];  // Triangle.motionBlur of this mesh
-    double pad2;
+    double beamSlack;      // absolute widening of a beam in this BLAS's space (rt_beam.cuh): 2^-15 of the largest |coordinate - centre|
 };
 
 struct GMaterial {

@@ -185,6 +185,11 @@ static void fillInstance(const rt_instance& in, const BlasInfo& bi, GInstance& g
     g.nodeBase = bi.nodeBase; g.triBase = bi.triBase; g.triF64 = bi.f64; g.rootRef = bi.rootRef;
     g.bigBlas = (bi.kind == INST_MESH && bi.triCount > bigBlasTriangles) ? 1 : 0;
     g.wideRoot = bi.kind == INST_MESH ? bi.wideRoot : kEmptyRef;
+    {
+        double M = 0;
+        for (int a = 0; a < 3; a++) M = std::fmax(M, std::fmax(std::fabs(bi.lo[a] - bi.centre[a]), std::fabs(bi.hi[a] - bi.centre[a])));
+        g.beamSlack = std::ldexp(M, -15);
+    }
     g.matId = in.hasMaterialOverride ? in.materialOverride : bi.matId;  // RTContext.swift:704
     g.primIndex = bi.prim;
     const bool moves = in.instanceMotion[0] != 0 || in.instanceMotion[1] != 0 || in.instanceMotion[2] != 0;
@@ -385,8 +390,9 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
                 const int32_t wbase = (int32_t)wnodes.size();
                 for (WNode& w : wide.nodes)
                     for (int k = 0; k < kWide; k++) {
-                        if (w.child[k] == kEmptyRef) continue;
-                        w.child[k] = w.child[k] >= 0 ? w.child[k] + wbase : rebase(w.child[k]);
+                        int32_t& r = w.c[k].ref;
+                        if (r == kEmptyRef) continue;
+                        r = r >= 0 ? r + wbase : rebase(r);
                     }
                 bi.wideRoot = wbase;
                 wnodes.insert(wnodes.end(), wide.nodes.begin(), wide.nodes.end());
@@ -915,6 +921,17 @@ int64_t rt_scene_get_schedule(rt_scene_t* sc, int32_t* orderOut, int64_t capacit
             return fail(RT_ERR_CUDA, "rt_scene_get_schedule: copy failed");
     }
     return n;
+}
+
+int64_t rt_scene_read_wide_nodes(rt_scene_t* sc, void* nodesOut, int64_t capacityBytes) {
+    if (!sc) return fail(RT_ERR_NO_SCENE, "No scene loaded. Can't render.");
+    const int64_t bytes = (int64_t)sc->info.wideNodes * (int64_t)sizeof(WNode);
+    if (nodesOut && capacityBytes > 0 && bytes > 0) {
+        if (cudaSetDevice(sc->device) != cudaSuccess ||
+            cudaMemcpy(nodesOut, sc->dWNodes, (size_t)(bytes < capacityBytes ? bytes : capacityBytes), cudaMemcpyDeviceToHost) != cudaSuccess)
+            return fail(RT_ERR_CUDA, "rt_scene_read_wide_nodes: copy failed");
+    }
+    return bytes;
 }
 
 int64_t rt_scene_read_blas_nodes(rt_scene_t* sc, void* nodesOut, int64_t capacityBytes) {

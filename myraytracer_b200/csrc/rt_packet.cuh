@@ -56,10 +56,12 @@ namespace rtg {
 // Packet walk of one mesh BLAS.  inMask (warp-uniform): lanes whose ray takes part.
 // anyhit: run-time, warp-uniform (one copy of the loop for closest-hit and shadow packets).
 // Returns (any-hit only) the warp-uniform mask of lanes found occluded.
+// tryBeam (warp-uniform): the packet is coherent and the mesh has a wide tree — the beam walk (rt_beam.cuh) goes first
+// and this walk only finishes what it gives up.
 template <bool COUNT>
 __device__ __forceinline__ uint32_t packetBlas(const DeviceScene& S, const GInstance& I, int instIdx, V3 oL, V3 dL,
                                                double eps, double tLow, HitRec& hit, bool anyhit, uint32_t inMask,
-                                               int2* wstack, Counters& C) {
+                                               int2* wstack, Counters& C, bool tryBeam = false) {
     const uint32_t bit = 1u << (threadIdx.x & 31);
     // per-lane root test + origin advance, exactly as traverseBlas
     V3 ia = refinedInv(dL);
@@ -73,19 +75,24 @@ __device__ __forceinline__ uint32_t packetBlas(const DeviceScene& S, const GInst
     const bool alive = in && !(tn > tf || tf < tLow || tn > hit.t);
     uint32_t live = __ballot_sync(RT_FULL, alive);
     if (!live) return 0u;
-    double t0 = tn > 0.0 ? tn : 0.0;
-    if (!(t0 < 1e300)) t0 = 0.0;
-    V3 o2 = oc + dL * t0;
-    const float ox = (float)o2.x, oy = (float)o2.y, oz = (float)o2.z;
-    const float ix = fminf(fmaxf(1.0f / (float)dL.x, -1e30f), 1e30f);
-    const float iy = fminf(fmaxf(1.0f / (float)dL.y, -1e30f), 1e30f);
-    const float iz = fminf(fmaxf(1.0f / (float)dL.z, -1e30f), 1e30f);
-    const float nx = -(ox * ix), ny = -(oy * iy), nz = -(oz * iz);
-    const float tminF = __double2float_rd(tLow - t0);
-    float tmaxF = alive ? __double2float_ru(hit.t - t0) : -CUDART_INF_F;
+    LaneRayF L;
+    L.t0 = tn > 0.0 ? tn : 0.0;
+    if (!(L.t0 < 1e300)) L.t0 = 0.0;
+    V3 o2 = oc + dL * L.t0;
+    L.ox = (float)o2.x; L.oy = (float)o2.y; L.oz = (float)o2.z;
+    L.ix = fminf(fmaxf(1.0f / (float)dL.x, -1e30f), 1e30f);
+    L.iy = fminf(fmaxf(1.0f / (float)dL.y, -1e30f), 1e30f);
+    L.iz = fminf(fmaxf(1.0f / (float)dL.z, -1e30f), 1e30f);
+    L.nx = -(L.ox * L.ix); L.ny = -(L.oy * L.iy); L.nz = -(L.oz * L.iz);
+    L.tminF = __double2float_rd(tLow - L.t0);
+    L.tmaxF = alive ? __double2float_ru(hit.t - L.t0) : -CUDART_INF_F;
+    uint32_t occluded = 0u;
+    if (tryBeam && beamWalk<COUNT>(S, I, instIdx, oL, dL, eps, tLow, hit, anyhit, live, occluded, L, wstack, C)) return occluded;
+    const float ix = L.ix, iy = L.iy, iz = L.iz, nx = L.nx, ny = L.ny, nz = L.nz, tminF = L.tminF;
+    float tmaxF = L.tmaxF;
+    const double t0 = L.t0;
 
     const GNode* nodes = S.nodes;        // child references are absolute (gpu_layout.h)
-    uint32_t occluded = 0u;
     // sp: shared-window address of the next free entry.  Entry 0 is a sentinel (kEmptyRef, all lanes): popping it
     // ends the walk, so the loop needs neither the stack base nor a depth counter.
     const uint32_t spBase = (uint32_t)__cvta_generic_to_shared(wstack);
@@ -116,9 +123,6 @@ __device__ __forceinline__ uint32_t packetBlas(const DeviceScene& S, const GInst
             if ((uint32_t)ch.y < 0x7fffffffu) prefetchL1(nodes + ch.y);
 #endif
             if (COUNT && (curMask & bit) != 0) C.box += 2;
-#ifdef RT_BEAM_STATS
-            if (COUNT && bit == 1u) C.sphere++;           // warp-level: binary node visits
-#endif
 #ifdef RT_WARPTIMES
             if (bit == 1u) { wstack[RT_WSTACK + RT_WTSTACK].x++; wstack[RT_WSTACK + RT_WTSTACK].y += __popc(curMask); }
 #endif
@@ -158,9 +162,6 @@ __device__ __forceinline__ uint32_t packetBlas(const DeviceScene& S, const GInst
             const bool f64 = (ref & 8u) != 0;
             const bool inl = (curMask & bit) != 0;
             bool occ = false;
-#ifdef RT_BEAM_STATS
-            if (COUNT && bit == 2u) C.plane++;            // warp-level: leaf visits
-#endif
 #ifdef RT_WARPTIMES
             if (bit == 1u) { wstack[RT_WSTACK + RT_WTSTACK + 1].x++; wstack[RT_WSTACK + RT_WTSTACK + 1].y += __popc(curMask) * count; }
 #endif
@@ -215,14 +216,9 @@ __device__ __forceinline__ uint32_t packetInstance(const DeviceScene& S, int idx
             if (in) o1 = traverseBlas<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, nullptr, 0, C);
             return __ballot_sync(RT_FULL, o1);
         }
-        if (!(INCOHERENT && incoherent) && I.wideRoot != kEmptyRef) {     // coherent packet, mesh with a wide tree: beam walk
-            bool formed;
-            const uint32_t r = beamBlas<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, inMask, wstack, C, formed);
-            if (formed) return r;
-            // no beam, or its budget spent: the packet walk finishes (closest hits found so far stand; lanes found occluded are done)
-            return r | packetBlas<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, inMask & ~r, wstack, C);
-        }
-        return packetBlas<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, inMask, wstack, C);
+        // coherent packet, mesh with a wide tree: the beam walk first
+        const bool tryBeam = !(INCOHERENT && incoherent) && I.wideRoot != kEmptyRef;
+        return packetBlas<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, inMask, wstack, C, tryBeam);
     }
     bool occ = false;
     if (in) occ = analyticInstance<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, C);

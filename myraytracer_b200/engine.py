@@ -112,6 +112,17 @@ class RayTracerEngine:
             self._lib.rt_scene_read_blas_nodes(self.scene_handle(), _ptr(out), n)
         return out
 
+    def wide_nodes(self) -> np.ndarray:
+        """rt_scene_read_wide_nodes: the wide BVH nodes of the beam walk, (n, 16 children, 8) uint32 words:
+        lo.xyz, hi.xyz (float bits), child reference, aux (child 0: sort axis)."""
+        n = self._lib.rt_scene_read_wide_nodes(self.scene_handle(), None, 0)
+        if n < 0:
+            raise RenderError(int(n), self._lib.rt_last_error().decode())
+        out = np.zeros((n // 512, 16, 8), np.uint32)
+        if n:
+            self._lib.rt_scene_read_wide_nodes(self.scene_handle(), _ptr(out), n)
+        return out
+
     def describe(self) -> capi.rt_scene_desc:
         d = capi.rt_scene_desc()
         rc = self._lib.rth_engine_describe(self._h, C.byref(d))

@@ -137,6 +137,7 @@ inline float __fmaf_rn(float a, float b, float c) { return fmaf(a, b, c); }
 // one rounding, towards -inf / +inf (FFMA.RM / FFMA.RP): fmaf under the directed rounding mode
 inline float __fmaf_rd(float a, float b, float c) { const int o = fegetround(); fesetround(FE_DOWNWARD); volatile float r = fmaf(a, b, c); fesetround(o); return r; }
 inline float __fmaf_ru(float a, float b, float c) { const int o = fegetround(); fesetround(FE_UPWARD); volatile float r = fmaf(a, b, c); fesetround(o); return r; }
+inline float __fdividef(float a, float b) { return a / b; }
 inline int __float_as_int(float f) { int i; memcpy(&i, &f, 4); return i; }
 inline float __int_as_float(int i) { float f; memcpy(&f, &i, 4); return f; }
 inline float __double2float_rd(double x) { float f = (float)x; return (double)f > x ? nextafterf(f, -INFINITY) : f; }

@@ -596,3 +596,100 @@ def test_emulated_static_ingest_equals_rt_ply_ingest(emu):
     lay = ply_cases.make_layout(capi, dict(kw, vertexCount=capi.RT_PLY_STATIC_MAX_VERTICES + 1))
     assert L.rt_ply_ingest_static(C.byref(lay), p(vb), p(fb), 1, 0, p(got_v), p(got_n), None, None) == capi.RT_ERR_UNSUPPORTED
     assert b"65536" in L.rt_last_error()
+
+
+# ---- beam walk of the wide BVH (rt_beam.cuh; built when RTCUDA_WIDE=1)
+
+def _wide_leaves(wn, root):
+    """Leaf references and boxes under wide node `root`, depth first; also the tree's depth."""
+    leaves, depth, stack = [], 0, [(int(root), 1)]
+    while stack:
+        n, d = stack.pop()
+        depth = max(depth, d)
+        kids = wn[n]
+        refs = kids[:, 6].view(np.int32)
+        real = refs != 0x7fffffff
+        assert real[:int(real.sum())].all(), "empty slots come last"
+        assert int(real.sum()) >= 2
+        axis = int(kids[0, 7])
+        assert 0 <= axis <= 2
+        box = kids[:, :6].view(np.float32)
+        centre = box[real, axis].astype(np.float64) + box[real, 3 + axis]
+        assert (np.diff(centre) >= 0).all(), "children sorted up the node's sort axis"
+        assert (box[~real, :3] > box[~real, 3:]).all(), "empty slots carry an inverted box"
+        for k in np.nonzero(real)[0]:
+            if refs[k] >= 0:
+                stack.append((int(refs[k]), d + 1))
+            else:
+                leaves.append((int(refs[k]), tuple(box[k])))
+    return leaves, depth
+
+
+def _binary_leaves(bn, root):
+    leaves, stack = [], [int(root)]
+    while stack:
+        n = stack.pop()
+        rec = bn[n]
+        f = rec[:12].view(np.float32)
+        boxes = [(f[0], f[1], f[2], f[3], f[4], f[5]), (f[6], f[7], f[8], f[9], f[10], f[11])]
+        for ref, box in zip(rec[12:14].view(np.int32), boxes):
+            if ref == 0x7fffffff:
+                continue
+            if ref >= 0:
+                stack.append(int(ref))
+            else:
+                leaves.append((int(ref), tuple(box)))
+    return leaves
+
+
+@pytest.mark.parametrize("name", ["c2", "c5", "c3"])
+def test_emulated_wide_tree_is_the_binary_tree_collapsed(name, scene_dir, emu, monkeypatch):
+    """bvh_build.cpp: collapseWide — every leaf of the binary tree hangs under the wide tree exactly once with the same
+    reference and the same conservative box; children sorted along the node's sort axis, empty slots last."""
+    monkeypatch.setenv("RTCUDA_WIDE", "1")
+    fn, kw, _ = CASES[name]
+    eng = RayTracerEngine(fn(scene_dir, **kw))
+    info = eng.scene_info()
+    assert info["wideNodes"] > 0
+    wn, bn = eng.wide_nodes(), eng.blas_nodes()
+    assert wn.shape[0] == info["wideNodes"]
+    # roots: a wide node that no other wide node refers to, one per mesh BLAS with >= 64 triangles
+    refs = wn[:, :, 6].view(np.int32)
+    inner = refs[(refs >= 0) & (refs != 0x7fffffff)]
+    roots = sorted(set(range(wn.shape[0])) - set(inner.tolist()))
+    brefs = bn[:, 12:14].view(np.int32)
+    broots = sorted(set(range(bn.shape[0])) - set(brefs[(brefs >= 0) & (brefs != 0x7fffffff)].tolist()))
+    wide_sets = [sorted(_wide_leaves(wn, r)[0]) for r in roots]
+    bin_sets = [sorted(_binary_leaves(bn, r)) for r in broots]
+    for ws in wide_sets:
+        assert ws in bin_sets            # same leaves, same boxes, as one of the binary trees
+    assert len(wide_sets) >= 1
+
+
+@pytest.mark.parametrize("name", ["c2", "c5", "c3", "c3x16", "instances", "c1x4_ragged"])
+def test_emulated_beam_walk_vs_oracle(name, scene_dir, emu, monkeypatch):
+    """The fast kernel with the beam walk switched on (RTCUDA_WIDE=1): same parity bars against the oracle, and the
+    frame of the packet walk bit for bit up to tie-breaking (the beam only culls; t, u, v come from the same FP64 test)."""
+    fn, kw, _ = CASES[name]
+    path = fn(scene_dir, **kw)
+    ref = oracle_lib.OracleScene(path).render(want_ids=True, want_linear=True)
+    base = RayTracerEngine(path).render(0, want_linear=True, variant=1, counters=True)
+    monkeypatch.setenv("RTCUDA_WIDE", "1")
+    eng = RayTracerEngine(path)
+    got = eng.render(0, want_ids=True, want_linear=True, variant=1, counters=True)
+    check(got, ref)
+    assert (base.rgba == got.rgba).all(axis=-1).mean() >= 0.9999
+    if eng.scene_info()["wideNodes"] > 0:
+        assert got.stats["boxTests"] != base.stats["boxTests"]          # the beam walk ran
+    assert got.stats["raysPrimary"] == base.stats["raysPrimary"] and got.stats["raysSecondary"] == base.stats["raysSecondary"]
+
+
+def test_emulated_beam_walk_budget_falls_back_to_the_packet_walk(scene_dir, emu, monkeypatch):
+    """A low-resolution frame over a fine mesh makes fat beams (an 8x4-pixel packet spans hundreds of triangles): the
+    visit budget runs out and the packet walk finishes — same image."""
+    path = scenegen.config_c2(scene_dir, n=96, width=48, height=32)
+    base = RayTracerEngine(path).render(0, want_ids=True, variant=1)
+    monkeypatch.setenv("RTCUDA_WIDE", "1")
+    got = RayTracerEngine(path).render(0, want_ids=True, variant=1)
+    assert (base.rgba == got.rgba).all()
+    assert (base.ids["prim"] == got.ids["prim"]).mean() >= 0.9999

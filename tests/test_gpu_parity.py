@@ -228,6 +228,28 @@ def test_device_sah_build_makes_the_host_builders_tree(name, scene_dir, monkeypa
     assert rep["px_within_1"] >= 0.999, rep
 
 
+@pytest.mark.parametrize("name", ["c2full", "c4s", "c5s", "c3", "instances"])
+def test_beam_walk_meets_the_parity_bars(name, scene_dir, monkeypatch):
+    """RTCUDA_WIDE=1: coherent packets walk the wide BVH as a beam (rt_beam.cuh: one lane per child box, per-ray tests at
+    the leaves only).  Same parity bars against the oracle, and the packet walk's frame up to tie-breaking."""
+    case = CASES[name]
+    path = case["fn"](scene_dir, **case["kw"])
+    base = RayTracerEngine(path).render(0, variant=1)
+    monkeypatch.setenv("RTCUDA_WIDE", "1")
+    eng = RayTracerEngine(path)
+    assert eng.ready, eng.load_error
+    assert eng.scene_info()["wideNodes"] > 0
+    got = eng.render(0, want_ids=True, want_linear=True, variant=1)
+    ref = oracle_lib.OracleScene(path).render(want_ids=True, want_linear=True)
+    rep = parity.compare(got, ref)
+    print(name, "beam", rep)
+    assert rep["id_agree"] >= 0.9999 and rep["id_bad"] == 0, rep
+    assert rep["px_within_1"] >= 0.999, rep
+    assert rep["t_bit_exact"] == 1.0, rep
+    assert (base.rgba == got.rgba).all(axis=-1).mean() >= 0.9999
+    assert got.stats["raysPrimary"] == base.stats["raysPrimary"]
+
+
 def test_c_abi_from_a_plain_c_program_on_the_gpu(scene_dir, tmp_path):
     """tests/c_driver/driver.c linked against librtcuda.so: engine -> frame -> image file, then the flattened scene
     straight into rt_scene_create / rt_render; same frame as through ctypes."""
