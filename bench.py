@@ -500,7 +500,8 @@ def run_ours(args):
             "frame_hash_note": "BLAKE2b-64 of the RGBA8 frame rt_render returned / the multi-process path gathered: equal to each other and for every N",
             "roofline": roofline, "build_ms": info["buildMs"], "upload_ms": info["uploadMs"], "wide_nodes": info.get("wideNodes", 0),
             "bvh_build": ("host binned SAH" if not info["deviceBuiltBlas"] else
-                          "device binned SAH" if os.environ.get("RTCUDA_BUILD") == "device-sah" else "device LBVH")}
+                          "device LBVH" if os.environ.get("RTCUDA_BUILD") == "device" else
+                          "device binned SAH (the host builder's tree, node array identical)")}
     if parity is not None:
         line["parity"] = parity
     if cpu_line is not None:
@@ -529,7 +530,7 @@ def main():
     ap.add_argument("--config", choices=sorted(BENCH_CONFIGS), default="c4")
     ap.add_argument("--shard", choices=["tiles", "rows"], default=None,
                     help="N>1: 8-row chunks round-robin (default) or 8x4 tiles dealt along diagonals (p2p only)")
-    ap.add_argument("--build", choices=["host", "device", "device-sah"], default=None,
+    ap.add_argument("--build", choices=["auto", "host", "device", "device-sah"], default=None,
                     help="who builds the mesh BVHs: host = multi-threaded binned SAH (default), device = CUDA LBVH, "
                          "device-sah = the host builder's tree made by CUDA kernels")
     ap.add_argument("--schedule", choices=["adaptive", "spatial"], default="adaptive",

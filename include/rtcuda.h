@@ -134,14 +134,19 @@ typedef struct rt_camera {
 typedef int (*rt_progress_fn)(int32_t rowsDone, int32_t rowsTotal, void* user);
 
 /* rt_scene_desc.buildMode.  The reference builds on the CPU (Accelearion/BVH.swift:78-250); the image does not depend
- * on the tree.  HOST_SAH (default): multi-threaded binned SAH, best traversal speed.  DEVICE_LBVH: Morton-order radix
- * tree built by CUDA kernels, ~20x faster to build, slower to traverse; a tree too deep for the traversal stack falls
- * back to HOST_SAH for that mesh.  DEVICE_SAH: the HOST_SAH builder's own splits and leaves, made level by level by
- * CUDA kernels (per-bin boxes through order-preserving 64-bit atomics) — the same tree up to node numbering and the
- * triangle order inside a leaf.  The environment variable RTCUDA_BUILD=device|device-sah|host overrides the field. */
-#define RT_BUILD_HOST_SAH    0
+ * on the tree.  SAH (default): this module's binned-SAH tree (16 bins, leaf-cost rule, <= 4 triangles per leaf), best
+ * traversal speed — built by the device builder for meshes of RT_BUILD_AUTO_DEVICE_TRIANGLES triangles and more (3x
+ * faster on a million triangles and the SAME node array byte for byte), by the multi-threaded host builder below
+ * that.  DEVICE_LBVH: Morton-order radix tree built by CUDA kernels, faster still to build, 66 % slower to traverse; a
+ * tree too deep for the traversal stack falls back to the SAH builder for that mesh.  DEVICE_SAH: every mesh through
+ * the device SAH builder (the host builder's own splits and leaves, made level by level by CUDA kernels, per-bin
+ * boxes through order-preserving 64-bit atomics).  HOST_SAH: every mesh through the host builder.  The environment
+ * variable RTCUDA_BUILD=auto|device|device-sah|host overrides the field. */
+#define RT_BUILD_SAH         0
 #define RT_BUILD_DEVICE_LBVH 1
 #define RT_BUILD_DEVICE_SAH  2
+#define RT_BUILD_HOST_SAH    3
+#define RT_BUILD_AUTO_DEVICE_TRIANGLES 65536
 
 #define RT_SHARD_ROWS  0
 #define RT_SHARD_TILES 1

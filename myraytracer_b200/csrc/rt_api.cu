@@ -279,11 +279,14 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     const double t0 = nowMs();
 
     // ---- who builds the mesh BVHs (rt_scene_desc.buildMode, overridden by RTCUDA_BUILD)
-    if (d->buildMode < RT_BUILD_HOST_SAH || d->buildMode > RT_BUILD_DEVICE_SAH) return fail(RT_ERR_INVALID, "rt_scene_desc.buildMode outside 0..2");
+    if (d->buildMode < RT_BUILD_SAH || d->buildMode > RT_BUILD_HOST_SAH) return fail(RT_ERR_INVALID, "rt_scene_desc.buildMode outside 0..3");
     int buildMode = d->buildMode;
     if (const char* e = std::getenv("RTCUDA_BUILD"))
-        buildMode = std::strcmp(e, "device") == 0 ? RT_BUILD_DEVICE_LBVH : std::strcmp(e, "device-sah") == 0 ? RT_BUILD_DEVICE_SAH : RT_BUILD_HOST_SAH;
-    const bool deviceBuild = buildMode != RT_BUILD_HOST_SAH;
+        buildMode = std::strcmp(e, "device") == 0 ? RT_BUILD_DEVICE_LBVH : std::strcmp(e, "device-sah") == 0 ? RT_BUILD_DEVICE_SAH :
+                    std::strcmp(e, "host") == 0 ? RT_BUILD_HOST_SAH : RT_BUILD_SAH;
+    bool deviceBuild = buildMode == RT_BUILD_DEVICE_LBVH || buildMode == RT_BUILD_DEVICE_SAH;
+    if (buildMode == RT_BUILD_SAH)          // the SAH tree, big meshes on the device (same node array as the host builder's)
+        for (int64_t b = 0; b < d->nBlas && d->blas; b++) deviceBuild = deviceBuild || d->blas[b].primCount >= RT_BUILD_AUTO_DEVICE_TRIANGLES;
     if (const char* e = std::getenv("RTCUDA_BIG_BLAS")) sc->bigBlasTriangles = std::atoll(e);
     struct DevVerts {       // the scene's triangle vertices on the device, for the device builder only
         double* p = nullptr;
@@ -353,7 +356,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
         }
         BlasBuildOutput out;
         bool built = false;
-        if (buildMode == RT_BUILD_DEVICE_SAH && bl.primCount >= 2) {
+        if ((buildMode == RT_BUILD_DEVICE_SAH && bl.primCount >= 2) || (buildMode == RT_BUILD_SAH && bl.primCount >= RT_BUILD_AUTO_DEVICE_TRIANGLES)) {
             CK(buildBlasDeviceSah(dVerts.p, in, out, renderStackCapacity() - 2, nullptr));
             built = out.maxDepth <= renderStackCapacity() - 2;      // deeper than the stacks: buildBlas reports it below
             if (built) deviceBuilt++;

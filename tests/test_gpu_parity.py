@@ -184,6 +184,7 @@ def test_device_built_bvh_meets_the_parity_bars(name, scene_dir, monkeypatch):
     builder (Morton order + radix tree); the image must not depend on the tree."""
     case = CASES[name]
     path = case["fn"](scene_dir, **case["kw"])
+    monkeypatch.setenv("RTCUDA_BUILD", "host")
     host = RayTracerEngine(path)
     assert host.scene_info()["deviceBuiltBlas"] == 0
     base = host.render(0, want_ids=True)
@@ -248,6 +249,21 @@ def test_beam_walk_meets_the_parity_bars(name, scene_dir, monkeypatch):
     assert rep["t_bit_exact"] == 1.0, rep
     assert (base.rgba == got.rgba).all(axis=-1).mean() >= 0.9999
     assert got.stats["raysPrimary"] == base.stats["raysPrimary"]
+
+
+def test_default_build_mode_sends_big_meshes_to_the_device_builder(scene_dir, monkeypatch):
+    """RT_BUILD_SAH (the default): a mesh of RT_BUILD_AUTO_DEVICE_TRIANGLES triangles or more is built by the device SAH
+    builder — the host builder's node array byte for byte, so the frame is the host-built one — smaller meshes on the host."""
+    monkeypatch.delenv("RTCUDA_BUILD", raising=False)
+    big = RayTracerEngine(scenegen.config_c2(scene_dir))                    # 69,938 triangles
+    small = RayTracerEngine(scenegen.config_c2(scene_dir, n=100))           # 19,602 triangles
+    assert big.scene_info()["deviceBuiltBlas"] == 1 and small.scene_info()["deviceBuiltBlas"] == 0
+    frame, nodes = big.render(0).rgba, big.blas_nodes()
+    monkeypatch.setenv("RTCUDA_BUILD", "host")
+    host = RayTracerEngine(scenegen.config_c2(scene_dir))
+    assert host.scene_info()["deviceBuiltBlas"] == 0
+    assert (host.blas_nodes() == nodes).all()
+    assert (host.render(0).rgba == frame).all(axis=-1).mean() >= 0.9999      # the triangle order inside a leaf may differ: ties only
 
 
 def test_c_abi_from_a_plain_c_program_on_the_gpu(scene_dir, tmp_path):

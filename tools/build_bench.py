@@ -6,6 +6,7 @@ import json
 import os
 import sys
 import tempfile
+import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -20,14 +21,17 @@ def main():
     RayTracerEngine(scenegen.config_c1(d, width=16, height=16)).close()      # CUDA context up before anything is timed
     out = dict(workload=which, builders={})
     base = None
-    for mode in ("host", "device", "device-sah"):
+    for mode in ("host", "auto", "device", "device-sah"):
         os.environ["RTCUDA_BUILD"] = mode
-        build = []
+        build, create, upload = [], [], []
         for _ in range(reps):
+            t0 = time.perf_counter()
             eng = RayTracerEngine(path)
+            create.append((time.perf_counter() - t0) * 1e3)     # the whole engine: file, flatten / device ingest, BVHs, upload
             assert eng.ready, eng.load_error
             info = eng.scene_info()
             build.append(info["buildMs"])
+            upload.append(info["uploadMs"])
             if _ < reps - 1:
                 eng.close()
         frames = []
@@ -37,7 +41,7 @@ def main():
         rgba = r.rgba
         if base is None:
             base = rgba
-        out["builders"][mode] = dict(build_ms_min=min(build), build_ms_all=build, blasNodes=info["blasNodes"], maxDepth=info["maxDepth"],
+        out["builders"][mode] = dict(create_ms_min=min(create), create_ms_all=create, upload_ms_min=min(upload), build_ms_min=min(build), build_ms_all=build, blasNodes=info["blasNodes"], maxDepth=info["maxDepth"],
                                      maxLeafSize=info["maxLeafSize"], deviceBuiltBlas=info["deviceBuiltBlas"],
                                      frame_ms_min=min(frames[2:7]), boxTests=r.stats["boxTests"], triTests=r.stats["triTests"],
                                      image_equals_host=bool((rgba == base).all()))
