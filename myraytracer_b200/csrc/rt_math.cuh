@@ -23,7 +23,7 @@ __device__ __forceinline__ V3 operator-(V3 a) { return mk(-a.x, -a.y, -a.z); }
 __device__ __forceinline__ V3 operator*(V3 a, V3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
 __device__ __forceinline__ V3 operator*(V3 a, double s) { return mk(a.x * s, a.y * s, a.z * s); }
 __device__ __forceinline__ V3 operator*(double s, V3 a) { return mk(s * a.x, s * a.y, s * a.z); }
-__device__ __forceinline__ V3 operator/(V3 a, double s) { return mk(a.x / s, a.y / s, a.z / s); }
+__device__ __forceinline__ V3 operator/(V3 a, double s);
 __device__ __forceinline__ double dot(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
 __device__ __forceinline__ V3 cross(V3 a, V3 b) {
     return mk(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
@@ -39,7 +39,13 @@ __device__ __forceinline__ V3 cross(V3 a, V3 b) {
 #else
 #define RT_MATH_FN __device__ __forceinline__
 #endif
+// FP64 a / b: ~25 inlined instructions plus a slow-path call at every site (59 sites in the fast kernel with the ray queue,
+// 136 in the general kernel with area lights); behind RT_NOINLINE_MATH one copy serves them all.  IEEE division either way.
+RT_MATH_FN double ddiv(double a, double b) { return a / b; }
+RT_MATH_FN double dsqrt(double a) { return sqrt(a); }
+RT_MATH_FN double dpow(double a, double b) { return pow(a, b); }
 RT_MATH_FN double rsqrtExact(double s) { return 1.0 / sqrt(s); }
+__device__ __forceinline__ V3 operator/(V3 a, double s) { return mk(ddiv(a.x, s), ddiv(a.y, s), ddiv(a.z, s)); }
 __device__ __forceinline__ V3 normalize(V3 a) { return a * rsqrtExact(dot(a, a)); }
 RT_MATH_FN double length(V3 a) { return sqrt(dot(a, a)); }
 // Swift.max/min on Doubles as used by the reference (a > b ? a : b), NaN-propagation irrelevant here

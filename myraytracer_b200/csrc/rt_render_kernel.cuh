@@ -61,8 +61,8 @@ __device__ __forceinline__ PrimaryRay primaryRay(const CameraParams& cam, int i,
     const int n = cam.n;
     const double xi1 = rng.nextFloat();
     const double xi2 = rng.nextFloat();
-    const double iOffset = ((double)sx + xi1) / (double)n;
-    const double jOffset = ((double)sy + xi2) / (double)n;
+    const double iOffset = ddiv((double)sx + xi1, (double)n);
+    const double jOffset = ddiv((double)sy + xi2, (double)n);
     const double currentI = (double)i + iOffset;
     const double currentJ = (double)j + jOffset;
     const V3 vOff = cv * (currentJ * cam.dv);
@@ -75,7 +75,7 @@ __device__ __forceinline__ PrimaryRay primaryRay(const CameraParams& cam, int i,
     if (cam.dof) {  // :325-338
         const V3 forward = -cw;
         const double denom = dot(dir0, forward);
-        const double tFocus = fabs(denom) < 1e-6 ? cam.focus : (cam.focus / denom);
+        const double tFocus = fabs(denom) < 1e-6 ? cam.focus : ddiv(cam.focus, denom);
         const V3 pFocus = eye + dir0 * tFocus;
         const double uRand = rng.nextFloat() - 0.5;
         const double vRand = rng.nextFloat() - 0.5;
@@ -86,7 +86,7 @@ __device__ __forceinline__ PrimaryRay primaryRay(const CameraParams& cam, int i,
     }
     r.time = rng.nextFloat();  // ray time: always drawn (:340)
     const double denomW = dot(r.d, cw);
-    const double tImg = dot(cm - r.o, cw) / (denomW == 0.0 ? 4.9406564584124654e-324 : denomW);  // :342
+    const double tImg = ddiv(dot(cm - r.o, cw), denomW == 0.0 ? 4.9406564584124654e-324 : denomW);  // :342
     r.tMin = dmax(tImg, 0.0);
     return r;
 }
@@ -359,7 +359,7 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFas
                         const double* col = scratch + base * 3 + s;
 #pragma unroll 4
                         for (int k = 0; k < ns; k++) comp = comp + col[k * 3];
-                        comp = comp / samplesD;
+                        comp = ddiv(comp, samplesD);
                     }
                     const V3 px3 = mk(shflD(comp, base), shflD(comp, base + 1), shflD(comp, base + 2));
                     if (active && s == 0) writePixel(out, (size_t)j * W + i, px3);
@@ -386,7 +386,7 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFas
                     }
                     __syncwarp();
                     if (it == itEnd - 1) {
-                        const double comp = acc.x / samplesD;
+                        const double comp = ddiv(acc.x, samplesD);
                         const V3 px3 = mk(shflD(comp, 0), shflD(comp, 1), shflD(comp, 2));
                         if (active && lane == 0) writePixel(out, (size_t)j * W + i, px3);
                     }

@@ -53,7 +53,7 @@ __device__ __forceinline__ V3 reflectDir(V3 d, V3 n) { return d - 2.0 * dot(d, n
 // :530-552
 __device__ __forceinline__ void orthonormalBasis(V3 n, V3& tangent, V3& bitangent) {
     double sign = n.z >= 0 ? 1.0 : -1.0;
-    double a = -1.0 / (sign + n.z);
+    double a = ddiv(-1.0, sign + n.z);
     double b = n.x * n.y * a;
     tangent = normalize(mk(1.0 + sign * n.x * n.x * a, sign * b, -sign * n.x));
     bitangent = normalize(mk(b, sign + n.y * n.y * a, -n.y));
@@ -63,12 +63,12 @@ __device__ __forceinline__ void orthonormalBasis(V3 n, V3& tangent, V3& bitangen
 __device__ __forceinline__ void fresnelDielectric(double n1, double n2, double cosI, double& R, bool& hasCosT, double& cosT,
                                                   double& sin2T) {
     double cosTheta = dmax(0.0, dmin(1.0, fabs(cosI)));
-    double eta = n1 / n2;
+    double eta = ddiv(n1, n2);
     sin2T = eta * eta * dmax(0.0, 1.0 - cosTheta * cosTheta);
     if (sin2T > 1.0) { R = 1.0; hasCosT = false; cosT = 0; return; }
-    double cosPhi = sqrt(dmax(0.0, 1.0 - sin2T));
-    double Rs = (n2 * cosTheta - n1 * cosPhi) / (n2 * cosTheta + n1 * cosPhi);
-    double Rp = (n1 * cosTheta - n2 * cosPhi) / (n1 * cosTheta + n2 * cosPhi);
+    double cosPhi = dsqrt(dmax(0.0, 1.0 - sin2T));
+    double Rs = ddiv(n2 * cosTheta - n1 * cosPhi, n2 * cosTheta + n1 * cosPhi);
+    double Rp = ddiv(n1 * cosTheta - n2 * cosPhi, n1 * cosTheta + n2 * cosPhi);
     R = 0.5 * (Rs * Rs + Rp * Rp);
     hasCosT = true; cosT = cosPhi;
 }
@@ -79,8 +79,8 @@ __device__ __forceinline__ double fresnelConductor(double eta, double k, double 
     double cos2 = cosI * cosI;
     double eta2k2 = eta * eta + k * k;
     double twoEtaCos = 2.0 * eta * cosI;
-    double Rs = (eta2k2 - twoEtaCos + cos2) / (eta2k2 + twoEtaCos + cos2);
-    double Rp = ((eta2k2 * cos2) - twoEtaCos + 1.0) / ((eta2k2 * cos2) + twoEtaCos + 1.0);
+    double Rs = ddiv(eta2k2 - twoEtaCos + cos2, eta2k2 + twoEtaCos + cos2);
+    double Rp = ddiv((eta2k2 * cos2) - twoEtaCos + 1.0, (eta2k2 * cos2) + twoEtaCos + 1.0);
     return 0.5 * (Rs + Rp);
 }
 
@@ -148,7 +148,7 @@ __device__ __forceinline__ V3 pointLightTerm(const GMaterial& mat, const GPointL
     const V3 view = normalize(-rayDir);
     const V3 h = normalize(wi + view);
     const double NdotH = dmax(0.0, dot(N, h));
-    const V3 Ls = ld3(mat.specular) * pow(NdotH, shininess);
+    const V3 Ls = ld3(mat.specular) * dpow(NdotH, shininess);
     const V3 atten = ld3(pl.intensity) / dmax(dist * dist, 1e-12);
     return (Ld + Ls) * atten;
 }
@@ -168,12 +168,12 @@ __device__ __forceinline__ bool areaLightSample(const DeviceScene& S, const GAre
     V3 t, b;
     orthonormalBasis(nL, t, b);
     const double size = al.size;
-    const double r1 = S.jitter[k] / 10.0 - 0.5;
-    const double r2 = S.jitter[100 + k] / 10.0 - 0.5;
+    const double r1 = ddiv(S.jitter[k], 10.0) - 0.5;
+    const double r2 = ddiv(S.jitter[100 + k], 10.0) - 0.5;
     const V3 samplePos = (ld3(al.position) + t * (r1 * size)) + b * (r2 * size);
     wi = samplePos - p;
     dist2 = dot(wi, wi);
-    dist = sqrt(dist2);
+    dist = dsqrt(dist2);
     wi = wi / dist;
     NdotL = dot(N, wi);
     if (NdotL <= 0) return false;
@@ -187,7 +187,7 @@ __device__ __forceinline__ V3 areaLightTerm(const GMaterial& mat, const GAreaLig
     const V3 view = normalize(-rayDir);
     const V3 h = normalize(wi + view);
     const V3 Ld = ld3(mat.diffuse) * NdotL;
-    const V3 Ls = ld3(mat.specular) * pow(dmax(0.0, dot(N, h)), mat.phong);       // raw phong exponent (:179)
+    const V3 Ls = ld3(mat.specular) * dpow(dmax(0.0, dot(N, h)), mat.phong);       // raw phong exponent (:179)
     const V3 brdf = Ld + Ls;
     return ((brdf * ld3(al.radiance)) * (Ln / dist2)) * area;
 }
@@ -239,7 +239,7 @@ __device__ __forceinline__ int spawnChildren(const DeviceScene& S, const ShadePo
             c1.w = w;                                                                   // total internal reflection :235-236
         } else {
             c1.w = w * Rf;
-            const double eta = n1 / n2;
+            const double eta = ddiv(n1, n2);
             const V3 td = normalize((cur.d * eta) + (mN * (eta * cosI - cosT)));
             c2.o = p + td * shadowEps; c2.d = td; c2.w = w * (1.0 - Rf);
             c2.beer = (entering && mat.hasAbsorption) ? 1 : 0;

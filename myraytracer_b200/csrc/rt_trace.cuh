@@ -22,7 +22,7 @@ template <bool COUNT>
 __device__ __forceinline__ bool analyticInstance(const DeviceScene& S, const GInstance& I, int idx, V3 oL, V3 dL, double eps,
                                                  double tLow, HitRec& hit, bool anyhit, Counters& C) {
     const int kind = I.kind;
-    V3 inv = mk(1.0 / dL.x, 1.0 / dL.y, 1.0 / dL.z);
+    V3 inv = mk(ddiv(1.0, dL.x), ddiv(1.0, dL.y), ddiv(1.0, dL.z));
     if (COUNT) C.box++;
     if (!hitAABBExact(I.rootLo, I.rootHi, oL, inv, eps)) return false;
     double t, u = 0, v = 0;
@@ -76,7 +76,7 @@ template <bool COUNT>
 __device__ __forceinline__ bool traceSceneRef(const DeviceScene& S, V3 o, V3 d, double tMin, HitRec& hit, bool anyhit,
                                               int32_t* sstack, int sstackN, Counters& C, double time) {
     const double eps = S.eps;
-    const V3 inv = mk(1.0 / d.x, 1.0 / d.y, 1.0 / d.z);       // Ray.invDir
+    const V3 inv = mk(ddiv(1.0, d.x), ddiv(1.0, d.y), ddiv(1.0, d.z));       // Ray.invDir
     int32_t stack[64];                                          // the reference's fixed 64 slots (:626)
     int sp = 0;
     stack[sp++] = 0;

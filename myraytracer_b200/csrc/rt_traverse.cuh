@@ -138,7 +138,7 @@ __device__ __forceinline__ bool mtTest(V3 v0, V3 v1, V3 v2, V3 org, V3 dir, doub
         if ((nv < 0.0) != (det < 0.0)) return false;
         if (fabs(nu) + fabs(nv) > lim * (1.0 + 1e-15) && fabs(nu) > tiny) return false;
     }
-    double invDet = 1.0 / det;
+    double invDet = ddiv(1.0, det);
     u = nu * invDet;
     if (u < 0.0 || u > 1.0) return false;
     v = nv * invDet;
@@ -161,9 +161,9 @@ __device__ __forceinline__ bool sphereT(const double* sp, V3 o, V3 d, double eps
     double c = dot(oc, oc) - sp[3] * sp[3];
     double disc = b * b - 4 * a * c;
     if (disc < 0) return false;
-    double sd = sqrt(disc);
-    t = (-b - sd) / (2 * a);
-    if (t < rootLimit) t = (-b + sd) / (2 * a);
+    double sd = dsqrt(disc);
+    t = ddiv(-b - sd, 2 * a);
+    if (t < rootLimit) t = ddiv(-b + sd, 2 * a);
     return true;
 }
 
@@ -172,7 +172,7 @@ __device__ __forceinline__ bool planeT(const double* pl, V3 o, V3 d, double eps,
     V3 n = ld3(pl + 3);
     double denom = dot(n, d);
     if (fabs(denom) < eps) return false;
-    t = dot(ld3(pl) - o, n) / denom;
+    t = ddiv(dot(ld3(pl) - o, n), denom);
     return true;
 }
 
