@@ -166,7 +166,9 @@ typedef struct rt_render_params {
     /* Order in which the warps draw the 8x4-pixel tiles of the frame.  RT_SCHEDULE_ADAPTIVE (0, default): every frame
      * records the time spent per tile, and the next frame with the same image size, sample count, shard and kernel
      * draws the longest tiles first, so that it ends on its cheapest work instead of waiting for a few slow packets
-     * (rt_stats.tilesScheduled tells whether a learnt order was used; the first frame uses the spatial order).
+     * (rt_stats.tilesScheduled tells whether a cost order was used).  The first frame of a geometry — the reference's
+     * usage: one render per camera, RayTracer.swift:169 — takes its order from one probe ray per tile, traced just before
+     * the frame (a frame of fewer than 256 tiles, or RTCUDA_PROBE=0, runs in the spatial order).
      * RT_SCHEDULE_SPATIAL (1): always top to bottom.  The image is the same either way. */
     int32_t scheduleMode;
     /* RT_SHARD_ROWS (0): the 8-row chunks c (Object+Extension.swift:75) with c % shardCount == shardIndex.
@@ -195,7 +197,7 @@ typedef struct rt_stats {
     /* only with collectCounters: */
     int64_t boxTests, triTests, sphereTests, planeTests, instEntries, maxStack;
     int64_t smoothHits;           /* closest hits resolved on smooth-shaded triangles (3 normals fetched) */
-    int64_t tilesScheduled;       /* tiles drawn in the cost order learnt from the previous frame (0: spatial order) */
+    int64_t tilesScheduled;       /* tiles drawn in cost order — measured on the previous frame, or estimated by the probe rays of a first frame (0: spatial order) */
 } rt_stats;
 
 typedef struct rt_scene_info {

@@ -146,6 +146,7 @@ struct rt_scene {
     int* dTileOrder = nullptr; size_t tileOrderBytes = 0;
     unsigned* dSchedWork = nullptr; size_t schedWorkBytes = 0;
     int schedKey[8] = {}; bool schedValid = false; int64_t pendingScheduled = 0;
+    bool pendingProbe = false;         // the frame in flight took its tile order from probe rays (first frame of a geometry)
     double* dPathStack = nullptr; size_t pathStackBytes = 0;
     uint8_t* dRgba = nullptr; size_t rgbaBytes = 0;
     double* dLinear = nullptr; size_t linearBytes = 0;

@@ -131,7 +131,7 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     const int nTiles = ShardTiles(cp.width, cp.height, cp.shardIndex, cp.shardCount, cp.shardTiles).count;
     const bool adaptive = !(params && params->scheduleMode == RT_SCHEDULE_SPATIAL) && nTiles > 0;
     if (params && (params->scheduleMode < 0 || params->scheduleMode > RT_SCHEDULE_SPATIAL)) return fail(RT_ERR_INVALID, "scheduleMode outside 0..1");
-    sc->pendingScheduled = 0;
+    sc->pendingScheduled = 0; sc->pendingProbe = false;
     if (adaptive) {
         const int key[8] = {cp.width, cp.height, cp.n, cp.dof, cp.shardIndex, cp.shardCount * 2 + cp.shardTiles, variant, nTiles};
         const bool grown = sc->tileCostBytes < (size_t)nTiles * 4 || sc->tileOrderBytes < (size_t)nTiles * 4;
@@ -140,13 +140,27 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
         if ((rc = ensure(&sc->dSchedWork, &sc->schedWorkBytes, scheduleWorkBytes(nTiles)))) return rc;
         if (grown || std::memcmp(key, sc->schedKey, sizeof key) != 0) sc->schedValid = false;
         std::memcpy(sc->schedKey, key, sizeof key);
-        if (!sc->schedValid) {
+        bool probed = false;
+        // RTCUDA_PROBE=0: first frames in the spatial order; =2 (measurements): EVERY frame is ordered by probe rays, as if
+        // it were the first of its geometry
+        const char* pe = std::getenv("RTCUDA_PROBE");
+        const int probeMode = pe ? std::atoi(pe) : 1;
+        if (!sc->schedValid || probeMode == 2) {
             if (sc->sideBusy) CK(cudaStreamWaitEvent(st, sc->evSide, 0));
-            CK(cudaMemsetAsync(sc->dTileCost, 0, (size_t)nTiles * 4, st));
+            // no frame of this geometry has measured its tiles yet: one probe ray per tile estimates them, and this frame
+            // already draws the expensive tiles first (RT_SCHEDULE_ADAPTIVE)
+            if (probeMode != 0 && !sc->motion && nTiles >= 256) {
+                CK(launchTileProbe(sc->ds, cp, sc->dTileCost, nTiles, st));
+                CK(launchSchedule(sc->dTileCost, sc->dTileOrder, sc->dSchedWork, nTiles, st));      // leaves tileCost zeroed
+                probed = true;
+            } else {
+                CK(cudaMemsetAsync(sc->dTileCost, 0, (size_t)nTiles * 4, st));
+            }
         }
         rt.tileCost = sc->dTileCost;
-        rt.tileOrder = sc->schedValid ? sc->dTileOrder : nullptr;
-        sc->pendingScheduled = sc->schedValid ? nTiles : 0;
+        rt.tileOrder = (sc->schedValid || probed) ? sc->dTileOrder : nullptr;
+        sc->pendingScheduled = (sc->schedValid || probed) ? nTiles : 0;
+        sc->pendingProbe = probed;
     }
 #ifdef RT_WARPTIMES
     {   // profiling build: per-warp timestamps, dumped by rt_render_finish to $RT_WARPTIMES_OUT
@@ -192,7 +206,7 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     CK(cudaEventRecord(sc->evSide, sc->side));
     sc->sideBusy = true;
     sc->pending = true; sc->pendingCounters = counters; sc->pendingStream = st;
-    sc->launches = (adaptive ? 3 : 1) + (area ? 2 : 0);
+    sc->launches = (adaptive ? 3 : 1) + (area ? 2 : 0) + (adaptive && sc->pendingProbe ? 3 : 0);
     return RT_OK;
 }
 

@@ -23,7 +23,11 @@ final class Renderer: @unchecked Sendable {
     private var blasOfInstance = [Int32]()        // rt_instance.blas of every instance (fixed for the scene's life)
 
     /// Renderer(ctx:) — flattens RTContext (Models/RTContext.swift:74-92) into rt_scene_desc and uploads it.
-    public init(ctx: RTContext, scene: Scene, device: Int32 = 0) {
+    /// `devices`: the GPUs the scene is made resident on.  nil = every GPU of the box (rt_device_count): the BVHs are
+    /// built once, the other GPUs get device-to-device copies, and rt_render deals the frame's 8-row chunks to all of
+    /// them (rt_scene_create_multi); one entry = that GPU alone (rt_scene_create).
+    public init(ctx: RTContext, scene: Scene, devices: [Int32]? = nil) {
+        let gpus: [Int32] = devices ?? (0..<max(1, rt_device_count())).map { Int32($0) }
         self.ctx = ctx
         var triV = [Double](); triV.reserveCapacity(ctx.triangles.count * 9)
         var triN = [Double](); triN.reserveCapacity(ctx.triangles.count * 9)
@@ -103,7 +107,9 @@ final class Renderer: @unchecked Sendable {
                 desc.spheres = s.baseAddress; desc.planes = p.baseAddress; desc.prims = pr.baseAddress
                 desc.blas = b.baseAddress; desc.instances = i.baseAddress; desc.materials = m.baseAddress
                 desc.pointLights = l.baseAddress
-                return rt_scene_create(&desc, device)          // NULL on failure, never throws (CPly convention)
+                // NULL on failure, never throws (CPly convention)
+                return gpus.count > 1 ? gpus.withUnsafeBufferPointer { rt_scene_create_multi(&desc, $0.baseAddress, Int32(gpus.count)) }
+                                      : rt_scene_create(&desc, gpus[0])
             } } } } } } } } } } }
         if handle == nil { print("❌ CRTCuda: \(String(cString: rt_last_error()))") }
     }
@@ -171,14 +177,24 @@ final class Renderer: @unchecked Sendable {
         var linear = [Double](repeating: 0, count: wantLinear ? width * height * 3 : 0)
         var rgba = [UInt8](repeating: 0, count: wantRGBA ? width * height * 4 : 0)
         var stats = rt_stats()
-        var params = rt_render_params()               // whole frame on this GPU, automatic kernel choice
-        let status = linear.withUnsafeMutableBufferPointer { lp in rgba.withUnsafeMutableBufferPointer { rp in
+        var params = rt_render_params()               // whole frame on the scene's GPU(s), automatic kernel choice
+        // progress / cancellation while the frame is in flight (RayTracer.swift:172-181): the module calls back from this
+        // thread with the rows the finished share of the work amounts to; a cancelled Task stops the frame (RT_ERR_CANCELLED)
+        final class Relay { let row: (@Sendable (Int) -> Void)?; init(_ r: (@Sendable (Int) -> Void)?) { row = r } }
+        let relay = Relay(progressRow)
+        params.progressUser = Unmanaged.passUnretained(relay).toOpaque()
+        params.progress = { rowsDone, _, user in
+            let r = Unmanaged<Relay>.fromOpaque(user!).takeUnretainedValue()
+            r.row?(Int(rowsDone) - 1)
+            return Task.isCancelled ? 1 : 0
+        }
+        let status = withExtendedLifetime(relay) { linear.withUnsafeMutableBufferPointer { lp in rgba.withUnsafeMutableBufferPointer { rp in
             rt_render(handle, &rc, &params, wantRGBA ? rp.baseAddress : nil, wantLinear ? lp.baseAddress : nil, nil, &stats)
-        } }
+        } } }
+        if status == RT_ERR_CANCELLED { throw CancellationError() }      // like `try Task.checkCancellation()` in the reference's chunk loop
         guard status == RT_OK else {
             throw NSError(domain: "Render", code: Int(status), userInfo: [NSLocalizedDescriptionKey: String(cString: rt_last_error())])
         }
-        progressRow?(height - 1)                      // the GPU frame completes at once
         var out = [Vec3](); out.reserveCapacity(width * height)
         if wantLinear { for p in 0..<(width * height) { out.append(Vec3(linear[3 * p], linear[3 * p + 1], linear[3 * p + 2])) } }
         return (out, rgba, stats)
