@@ -167,8 +167,8 @@ typedef struct rt_render_params {
      * records the time spent per tile, and the next frame with the same image size, sample count, shard and kernel
      * draws the longest tiles first, so that it ends on its cheapest work instead of waiting for a few slow packets
      * (rt_stats.tilesScheduled tells whether a cost order was used).  The first frame of a geometry — the reference's
-     * usage: one render per camera, RayTracer.swift:169 — takes its order from one probe ray per tile, traced just before
-     * the frame (a frame of fewer than 256 tiles, or RTCUDA_PROBE=0, runs in the spatial order).
+     * usage: one render per camera, RayTracer.swift:169 — runs in the spatial order (RTCUDA_PROBE=1: it takes its order
+     * from one probe ray per tile traced just before the frame; measured slower than the spatial order).
      * RT_SCHEDULE_SPATIAL (1): always top to bottom.  The image is the same either way. */
     int32_t scheduleMode;
     /* RT_SHARD_ROWS (0): the 8-row chunks c (Object+Extension.swift:75) with c % shardCount == shardIndex.

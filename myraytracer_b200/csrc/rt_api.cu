@@ -64,6 +64,10 @@ double nowMs() {
     return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 
+// RTCUDA_TRACE=1: phase times of rt_scene_create on stderr (diagnostics)
+bool traceOn() { static const bool on = std::getenv("RTCUDA_TRACE") != nullptr; return on; }
+void trace(const char* what, double t0) { if (traceOn()) std::fprintf(stderr, "[rtcuda trace] %-32s %8.2f ms\n", what, nowMs() - t0); }
+
 bool isIdentity34(const double* m16) {
     for (int c = 0; c < 4; c++)
         for (int r = 0; r < 4; r++)
@@ -296,6 +300,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     if (deviceBuild && d->nTriangles > 0) {
         CK(cudaMalloc((void**)&dVerts.p, (size_t)d->nTriangles * 9 * sizeof(double)));
         CK(cudaMemcpy(dVerts.p, d->triVertices, (size_t)d->nTriangles * 9 * sizeof(double), cudaMemcpyHostToDevice));
+        trace("create: vertices -> device", t0);
     }
     int deviceBuilt = 0;
 
@@ -357,6 +362,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
         }
         BlasBuildOutput out;
         bool built = false;
+        const double tBlas = nowMs();
         if ((buildMode == RT_BUILD_DEVICE_SAH && bl.primCount >= 2) || (buildMode == RT_BUILD_SAH && bl.primCount >= RT_BUILD_AUTO_DEVICE_TRIANGLES)) {
             CK(buildBlasDeviceSah(dVerts.p, in, out, renderStackCapacity() - 2, nullptr));
             built = out.maxDepth <= renderStackCapacity() - 2;      // deeper than the stacks: buildBlas reports it below
@@ -367,6 +373,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
             if (built) deviceBuilt++;
         }
         if (!built) buildBlas(in, out);
+        if (bl.primCount >= 4096) trace(built ? "create: BLAS (device builder)" : "create: BLAS (host builder)", tBlas);
         if (out.maxDepth > renderStackCapacity() - 2) return fail(RT_ERR_UNSUPPORTED, "BLAS deeper than the traversal stack");
         bi.kind = bl.primCount == 1 ? INST_TRI : INST_MESH;
         bi.prim = pr[0].primitiveIndex;
@@ -490,6 +497,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     std::vector<double> normals;
     if (d->nTriangles > 0) normals.assign(d->triNormals, d->triNormals + d->nTriangles * 9);
     const double t1 = nowMs();
+    trace("create: build phase total", t0);
 
     // ---- upload
     int64_t bytes = 0;
@@ -563,6 +571,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     if ((rc = allocFrameState(sc, (size_t)d->nInstances))) return rc;
     CK(cudaDeviceSynchronize());
     const double t2 = nowMs();
+    trace("create: upload", t1);
 
     DeviceScene& S = sc->ds;
     bindDeviceScene(sc);

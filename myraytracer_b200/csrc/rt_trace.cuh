@@ -46,15 +46,16 @@ __device__ __forceinline__ bool analyticInstance(const DeviceScene& S, const GIn
 }
 
 // Closest-hit / any-hit test of one instance.  tLow = max(eps, tMin); hit.t = current closest t or tMax.
-template <bool COUNT, bool MOTION = false>
+template <bool COUNT, bool MOTION = false, bool BUDGET = false>
 __device__ __forceinline__ bool enterInstance(const DeviceScene& S, int idx, V3 o, V3 d, double eps, double tMin,
-                                              HitRec& hit, bool anyhit, int32_t* sstack, int sstackN, Counters& C, double time = 0.0) {
+                                              HitRec& hit, bool anyhit, int32_t* sstack, int sstackN, Counters& C, double time = 0.0,
+                                              int* budget = nullptr) {
     const GInstance& I = S.instances[idx];
     V3 oL, dL;
     toLocal<MOTION>(I, o, d, oL, dL, time);
     if (COUNT) C.inst++;
     const double tLow = dmax(eps, tMin);
-    if (I.kind == INST_MESH) return traverseBlas<COUNT, MOTION>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, sstack, sstackN, C, time);
+    if (I.kind == INST_MESH) return traverseBlas<COUNT, MOTION, BUDGET>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, sstack, sstackN, C, time, budget);
     return analyticInstance<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, C);
 }
 
@@ -103,14 +104,14 @@ __device__ __forceinline__ bool traceSceneRef(const DeviceScene& S, V3 o, V3 d, 
 
 // TLAS walk: conservative FP32 boxes (unions of Instance.worldBounds) like the BLAS nodes, near child first; every
 // instance reached is then tested exactly.
-template <bool COUNT, bool MOTION = false>
+template <bool COUNT, bool MOTION = false, bool BUDGET = false>
 __device__ __forceinline__ bool traceScene(const DeviceScene& S, V3 o, V3 d, double tMin, HitRec& hit, bool anyhit,
-                                           int32_t* sstack, int sstackN, Counters& C, double time = 0.0) {
+                                           int32_t* sstack, int sstackN, Counters& C, double time = 0.0, int* budget = nullptr) {
     const double eps = S.eps;
     int32_t cur = S.tlasRootRef;
     if (cur == kEmptyRef) return false;
     if (MOTION && S.refTlasNodes > 0) return traceSceneRef<COUNT>(S, o, d, tMin, hit, anyhit, sstack, sstackN, C, time);
-    if (cur < 0) return enterInstance<COUNT, MOTION>(S, ~cur, o, d, eps, tMin, hit, anyhit, sstack, sstackN, C, time);
+    if (cur < 0) return enterInstance<COUNT, MOTION, BUDGET>(S, ~cur, o, d, eps, tMin, hit, anyhit, sstack, sstackN, C, time, budget);
     const double tLow = dmax(eps, tMin);
     RayF rf = makeRayF(S.tlasLo, S.tlasHi, S.tlasCentre, o, d, refinedInv(d), tLow, hit.t);
     if (COUNT) C.box++;
@@ -135,7 +136,8 @@ __device__ __forceinline__ bool traceScene(const DeviceScene& S, V3 o, V3 d, dou
             } else if (h0) { cur = c0; continue; }
             else if (h1) { cur = c1; continue; }
         } else {
-            if (enterInstance<COUNT, MOTION>(S, ~cur, o, d, eps, tMin, hit, anyhit, sstack, sstackN, C, time)) return true;
+            if (enterInstance<COUNT, MOTION, BUDGET>(S, ~cur, o, d, eps, tMin, hit, anyhit, sstack, sstackN, C, time, budget)) return true;
+            if (BUDGET && *budget < 0) return false;
             rf.tmax = __double2float_ru(hit.t - rf.t0);       // a closer hit prunes the boxes that follow
         }
         if (sp == 0) return false;

@@ -197,10 +197,12 @@ __device__ __forceinline__ void loadTri(const DeviceScene& S, bool f64, int slot
 // motionBlur * ray.time, which the reference applies to the ray origin of the triangle test only
 // (RTContext.swift:480-481,833-834); the node boxes were grown by the motion vector at build time (:283-289) and are
 // tested with the undisplaced ray, like the reference's.
-template <bool COUNT, bool MOTION = false>
+// BUDGET (the tile probe of a first frame only): *budget node visits at most — the walk stops when they are spent and
+// whatever it found stands (a cost estimate needs no more than "this ray is expensive").
+template <bool COUNT, bool MOTION = false, bool BUDGET = false>
 __device__ __forceinline__ bool traverseBlas(const DeviceScene& S, const GInstance& I, int instIdx, V3 oL, V3 dL, double eps,
                                              double tLow, HitRec& hit, bool anyhit, int32_t* sstack, int sstackN, Counters& C,
-                                             double time = 0.0) {
+                                             double time = 0.0, int* budget = nullptr) {
     const V3 oTri = MOTION ? oL - ld3(I.meshMotion) * time : oL;
     // Advance the origin to the BLAS in FP64 so that its FP32 copy is accurate relative to the
     // box size: t0 = entry distance into the (exact) root box, from a widened FP64 slab test.
@@ -233,6 +235,7 @@ __device__ __forceinline__ bool traverseBlas(const DeviceScene& S, const GInstan
     const int tid = threadIdx.x;
     for (;;) {
         while ((uint32_t)cur < 0x7fffffffu) {  // inner node
+            if (BUDGET && --*budget < 0) return false;
             const float4* np = reinterpret_cast<const float4*>(nodes + cur);
             const float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2);
             const int4 ch = __ldg(reinterpret_cast<const int4*>(np + 3));

@@ -1,7 +1,10 @@
 // rt_context.cpp — rthost::RTContext: scene flattening of RTContext.init(scene:)
 // (Models/RTContext.swift:94-418) into the flat arrays of include/rtcuda.h.
 // Compile with -ffp-contract=off (no FMA contraction, like the reference's x86-64 Swift).
+#include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 
@@ -99,7 +102,13 @@ void RTContext::setInstanceTransform(size_t i, const double* m16, bool boundsOnD
     }
 }
 
+// RTCUDA_TRACE=1: phase times of engine creation on stderr (diagnostics)
+static double traceNow() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+static bool traceOn() { static const bool on = std::getenv("RTCUDA_TRACE") != nullptr; return on; }
+static void trace(const char* what, double t0) { if (traceOn()) std::fprintf(stderr, "[rtcuda trace] %-32s %8.2f ms\n", what, traceNow() - t0); }
+
 RTContext::RTContext(const pk::Scene& scene, int ingestDevice) {
+    const double tCtx = traceNow();
     intersectionTestEpsilon = scene.intersectionTestEpsilon;
     shadowRayEpsilon = scene.shadowRayEpsilon;
     for (const pk::Material& m : scene.materials) {
@@ -205,14 +214,20 @@ RTContext::RTContext(const pk::Scene& scene, int ingestDevice) {
             bool fromDevice = false;
             if (fromPLY && ingestDevice >= 0) {
                 PlyBlocks blocks; std::string why;
-                if (loadPlyBlocks(pk::dirOf(scene.path) + object.plyPath, blocks, why)) {
+                const double tRead = traceNow();
+                const bool haveBlocks = loadPlyBlocks(pk::dirOf(scene.path) + object.plyPath, blocks, why);
+                trace("flatten: PLY file -> raw blocks", tRead);
+                if (haveBlocks) {
                     // the kernels' output lands directly behind the triangles flattened so far
                     const int64_t nT = blocks.layout.faceCount * (blocks.layout.verticesPerFace == 4 ? 2 : 1);
                     const size_t old = triVertices.size();
                     triVertices.resize(old + (size_t)nT * 9); triNormals.resize(old + (size_t)nT * 9);
                     rt_ply_stats ps{};
+                    trace("flatten: output arrays resized", tRead);
+                    const double tIng = traceNow();
                     const int rc = rt_ply_ingest(&blocks.layout, blocks.vertexBlock.data(), blocks.faceBlock.data(), isSmooth ? 1 : 0,
                                                  ingestDevice, triVertices.data() + old, triNormals.data() + old, &ps);
+                    trace("flatten: rt_ply_ingest", tIng);
                     if (rc == RT_OK) { fromDevice = true; devTris = nT; deviceIngestedTriangles += nT; deviceIngestMs += ps.deviceMs; }
                     else {
                         triVertices.resize(old); triNormals.resize(old);
@@ -324,6 +339,7 @@ RTContext::RTContext(const pk::Scene& scene, int ingestDevice) {
         addInstance(it->second.blas, it->second.transform, true, it->second.material, D3{0, 0, 0}, meshID);
     }
     if (instances.empty()) warnings.push_back("No instances to build TLAS");  // :416
+    trace("flatten: RTContext(scene:) total", tCtx);
 }
 
 rt_scene_desc RTContext::describe(const pk::Scene& scene) const {

@@ -82,11 +82,14 @@ def test_emulated_kernels_vs_oracle(name, scene_dir, emu):
 
 
 def test_emulated_first_frame_takes_its_tile_order_from_probe_rays(scene_dir, emu, monkeypatch):
-    """First frame of a geometry with >= 256 tiles: one probe ray per tile (tileProbeKernel) estimates the tile costs and
-    the frame already draws expensive tiles first — terrain before sky; the image is the spatial order's."""
+    """RTCUDA_PROBE=1 (opt-in), first frame of a geometry with >= 256 tiles: one probe ray per tile (tileProbeKernel)
+    estimates the tile costs and the frame already draws expensive tiles first; the image is the spatial order's."""
     path = scenegen.config_c2(scene_dir, n=24, width=128, height=64)
     n_tiles = 16 * 16
     ref = RayTracerEngine(path).render(0, schedule=1)
+    off = RayTracerEngine(path).render(0)
+    assert off.stats["tilesScheduled"] == 0 and np.array_equal(off.rgba, ref.rgba)         # default: spatial order
+    monkeypatch.setenv("RTCUDA_PROBE", "1")
     eng = RayTracerEngine(path)
     first = eng.render(0)
     assert first.stats["tilesScheduled"] == n_tiles and first.stats["kernelLaunches"] == 6
@@ -94,9 +97,6 @@ def test_emulated_first_frame_takes_its_tile_order_from_probe_rays(scene_dir, em
     again = eng.render(0)
     assert again.stats["tilesScheduled"] == n_tiles and again.stats["kernelLaunches"] == 3
     assert np.array_equal(again.rgba, ref.rgba)
-    monkeypatch.setenv("RTCUDA_PROBE", "0")
-    off = RayTracerEngine(path).render(0)
-    assert off.stats["tilesScheduled"] == 0 and np.array_equal(off.rgba, ref.rgba)
 
 
 @pytest.mark.parametrize("name", ["c3", "c5", "instances"])

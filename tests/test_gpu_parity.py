@@ -137,8 +137,7 @@ def test_tile_schedule_does_not_change_the_frame(variant, scene_dir):
     ref = eng.render(0, want_linear=True, want_ids=True, variant=variant, schedule=1)
     assert ref.stats["tilesScheduled"] == 0
     first = eng.render(0, want_linear=True, want_ids=True, variant=variant)
-    # nothing learnt yet: the order comes from one probe ray per tile (tileProbeKernel + the two schedule kernels)
-    assert first.stats["tilesScheduled"] == 25 * 30 and first.stats["kernelLaunches"] == 6
+    assert first.stats["tilesScheduled"] == 0               # nothing learnt yet: spatial order
     assert sorted(eng.schedule().tolist()) == list(range(25 * 30))      # a permutation of the tiles
     for _ in range(3):
         again = eng.render(0, want_linear=True, want_ids=True, variant=variant)
@@ -152,7 +151,7 @@ def test_tile_schedule_does_not_change_the_frame(variant, scene_dir):
         assert sorted(eng.schedule().tolist()) == list(range(25 * 30))
     # another shard layout invalidates the order, then learns its own
     part = [eng.render(0, shard_index=1, shard_count=2, variant=variant) for _ in range(2)]
-    assert part[0].stats["tilesScheduled"] == 25 * 2 * 7 and part[1].stats["tilesScheduled"] == 25 * 2 * 7
+    assert part[0].stats["tilesScheduled"] == 0 and part[1].stats["tilesScheduled"] == 25 * 2 * 7
     assert np.array_equal(part[0].rgba, part[1].rgba)
     assert sorted(eng.schedule().tolist()) == list(range(25 * 2 * 7))
     rows = np.zeros(120, bool)
@@ -161,13 +160,19 @@ def test_tile_schedule_does_not_change_the_frame(variant, scene_dir):
     assert np.array_equal(part[1].rgba[rows], ref.rgba[rows]) and (part[1].rgba[~rows] == 0).all()
 
 
-def test_first_frame_probe_can_be_switched_off(scene_dir, monkeypatch):
-    """RTCUDA_PROBE=0: the first frame of a geometry runs in the spatial order, as before the probe existed."""
-    monkeypatch.setenv("RTCUDA_PROBE", "0")
-    eng = RayTracerEngine(scenegen.config_c3(scene_dir, width=200, height=120, samples=4, depth=3, ico_level=2))
+def test_first_frame_probe_orders_the_first_frame(scene_dir, monkeypatch):
+    """RTCUDA_PROBE=1 (opt-in): the first frame of a geometry takes its tile order from one probe ray per tile
+    (tileProbeKernel + the two schedule kernels); same image."""
+    path = scenegen.config_c3(scene_dir, width=200, height=120, samples=4, depth=3, ico_level=2)
+    ref = RayTracerEngine(path).render(0, schedule=1)
+    monkeypatch.setenv("RTCUDA_PROBE", "1")
+    eng = RayTracerEngine(path)
     first = eng.render(0)
-    assert first.stats["tilesScheduled"] == 0 and first.stats["kernelLaunches"] == 3
-    assert eng.render(0).stats["tilesScheduled"] == 25 * 30
+    assert first.stats["tilesScheduled"] == 25 * 30 and first.stats["kernelLaunches"] == 6
+    assert np.array_equal(first.rgba, ref.rgba)
+    again = eng.render(0)
+    assert again.stats["tilesScheduled"] == 25 * 30 and again.stats["kernelLaunches"] == 3
+    assert np.array_equal(again.rgba, ref.rgba)
 
 
 def test_tile_schedule_many_tiles(scene_dir):
@@ -178,7 +183,7 @@ def test_tile_schedule_many_tiles(scene_dir):
     n_tiles = 81 * 51 * 2                                      # 51 chunks of 8 rows, two tile rows each
     for k in range(3):
         out = eng.render(0)
-        assert out.stats["tilesScheduled"] == n_tiles             # first frame: probe order; then the measured one
+        assert out.stats["tilesScheduled"] == (n_tiles if k else 0)
         assert np.array_equal(out.rgba, ref)
         order = eng.schedule()
         assert len(order) == n_tiles and np.array_equal(np.sort(order), np.arange(n_tiles))
