@@ -60,6 +60,17 @@ int upload(const std::vector<T>& v, T** d, int64_t& bytes, std::vector<SceneArra
     return RT_OK;
 }
 
+template <class T>
+int uploadRaw(const T* src, size_t count, T** d, int64_t& bytes, std::vector<SceneArray>* reg, const void* owner) {
+    *d = nullptr;
+    const size_t n = count * sizeof(T);
+    CK(cudaMalloc((void**)d, n ? n : 16));
+    if (n) CK(cudaMemcpy(*d, src, n, cudaMemcpyHostToDevice));
+    bytes += (int64_t)n;
+    if (reg) reg->push_back(SceneArray{(size_t)((const char*)d - (const char*)owner), n ? n : 16});
+    return RT_OK;
+}
+
 double nowMs() {
     return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
@@ -163,6 +174,7 @@ struct rt_scene {
     bool glossy = false;               // some material has roughness != 0: RNG draws inside trace
     int64_t bigBlasTriangles = kBigBlasTriangles;   // meshes above this size are walked per lane by incoherent packets (RTCUDA_BIG_BLAS overrides: tests)
     bool recurse = false;              // maxRecursionDepth > 0 and a mirror / dielectric / conductor material: child rays exist
+    bool smallGeometry = false;        // no mesh above kBigBlasTriangles: analytic primitives and small meshes (rt_render_kernel.cuh: BLOCKS)
     bool nonFinite = false;            // a light / material / ambient constant is inf or NaN: the non-finite guard of `trace` can fire
     int pendingVariant = 0;
     bool pending = false; bool pendingCounters = false;
@@ -411,9 +423,9 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
         }
         for (GNode& g : out.nodes) { g.child0 = rebase(g.child0); g.child1 = rebase(g.child1); }
         bi.rootRef = rebase(out.rootRef);
-        nodes.insert(nodes.end(), out.nodes.begin(), out.nodes.end());
-        if (out.f64) trisD.insert(trisD.end(), out.trisD.begin(), out.trisD.end());
-        else tris.insert(tris.end(), out.tris.begin(), out.tris.end());
+        if (nodes.empty()) nodes = std::move(out.nodes); else nodes.insert(nodes.end(), out.nodes.begin(), out.nodes.end());
+        if (out.f64) { if (trisD.empty()) trisD = std::move(out.trisD); else trisD.insert(trisD.end(), out.trisD.begin(), out.trisD.end()); }
+        else { if (tris.empty()) tris = std::move(out.tris); else tris.insert(tris.end(), out.tris.begin(), out.tris.end()); }
         if (out.maxDepth > maxDepth) maxDepth = out.maxDepth;
         if (out.maxLeaf > maxLeaf) maxLeaf = out.maxLeaf;
         if (bi.kind == INST_MESH) sc->meshes++;
@@ -432,6 +444,9 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
         sc->instBlas.push_back(in.blas);
         std::memcpy(&wb[i * 6], in.worldBounds, 48);
     }
+    sc->smallGeometry = true;
+    for (const BlasInfo& bi : blasInfo) if (bi.kind == INST_MESH && bi.triCount > kBigBlasTriangles) sc->smallGeometry = false;
+    if (const char* e = std::getenv("RTCUDA_SMALL_GEOMETRY")) sc->smallGeometry = std::atoi(e) != 0;      // measurements / tests
     TlasBuildOutput tl;
     buildTlas(wb.data(), d->nInstances, tl);
     if (tl.maxDepth > 38) return fail(RT_ERR_UNSUPPORTED, "TLAS deeper than the TLAS stack");
@@ -494,8 +509,6 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
                 jitter[100 + k] = (double)gy + (double)next() * 2.3283064365386963e-10;
             }
     }
-    std::vector<double> normals;
-    if (d->nTriangles > 0) normals.assign(d->triNormals, d->triNormals + d->nTriangles * 9);
     const double t1 = nowMs();
     trace("create: build phase total", t0);
 
@@ -506,7 +519,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     if ((rc = upload(wnodes, &sc->dWNodes, bytes, &sc->arrays, sc))) return rc;
     if ((rc = upload(tris, &sc->dTris, bytes, &sc->arrays, sc))) return rc;
     if ((rc = upload(trisD, &sc->dTrisD, bytes, &sc->arrays, sc))) return rc;
-    if ((rc = upload(normals, &sc->dNormals, bytes, &sc->arrays, sc))) return rc;
+    if ((rc = uploadRaw(d->triNormals, (size_t)d->nTriangles * 9, &sc->dNormals, bytes, &sc->arrays, sc))) return rc;     // straight from the caller's array
     // TLAS records: the BLAS node format — FP32 boxes relative to the centre of the scene bounds, padded by
     // M * 2^-19 and rounded outward (conservative: the instance's own exact test decides)
     std::vector<GNode> tlasF(tl.nodes.size());
@@ -663,7 +676,7 @@ static int cloneScene(const rt_scene* src, int device, rt_scene* dst) {
     dst->device = device;
     dst->isReplica = true;
     dst->ds = src->ds; dst->info = src->info; dst->info.device = device; dst->meshes = src->meshes;
-    dst->motion = src->motion; dst->glossy = src->glossy; dst->nonFinite = src->nonFinite; dst->recurse = src->recurse; dst->bigBlasTriangles = src->bigBlasTriangles; dst->instanceMotion = src->instanceMotion;
+    dst->motion = src->motion; dst->glossy = src->glossy; dst->nonFinite = src->nonFinite; dst->recurse = src->recurse; dst->smallGeometry = src->smallGeometry; dst->bigBlasTriangles = src->bigBlasTriangles; dst->instanceMotion = src->instanceMotion;
     dst->blasInfo = src->blasInfo; dst->instBlas = src->instBlas; dst->refitLevelStart = src->refitLevelStart;
     dst->nBoundChunks = src->nBoundChunks;
     dst->arrays = src->arrays;

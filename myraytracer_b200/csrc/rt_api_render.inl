@@ -124,7 +124,7 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     rt.pathStack = sc->dPathStack; rt.counters = sc->dCounters;
     rt.tileCounter = sc->dTileCounter;
     rt.motion = sc->motion ? 1 : 0;
-    rt.recurse = sc->recurse ? 1 : 0;
+    rt.recurse = sc->recurse ? (sc->smallGeometry ? 2 : 1) : 0;
     if (std::getenv("RTCUDA_FORCE_RECURSE")) rt.recurse = 1;       // measurements only: the queue instantiation on a scene without child rays
     // Tile schedule: the frame records its cost per tile, the next frame of the same geometry draws the longest
     // tiles first.

@@ -11,6 +11,7 @@ namespace rtg {
 #if RT_V_FAST
 #define RT_KERNEL(c) renderKernelFast<c, false>
 #define RT_KERNEL_RECURSE(c) renderKernelFast<c, true>
+#define RT_KERNEL_RECURSE_SMALL(c) renderKernelFast<c, true, 16>
 #define RT_NAME(x) x##Fast
 #define RT_THREADS RT_FAST_BLOCK
 #else
@@ -30,6 +31,11 @@ cudaError_t RT_NAME(launchVariant)(const DeviceScene& S, const CameraParams& cam
     }
 #endif
 #ifdef RT_KERNEL_RECURSE
+    if (out.recurse == 2) {                    // ... and no big mesh: 16 resident warps of 128 registers per SM
+        if (counters) RT_LAUNCH(RT_KERNEL_RECURSE_SMALL(true), blocks, RT_THREADS, stream, S, cam, out);
+        else RT_LAUNCH(RT_KERNEL_RECURSE_SMALL(false), blocks, RT_THREADS, stream, S, cam, out);
+        return cudaGetLastError();
+    }
     if (out.recurse) {                         // child rays possible: the instantiation with the warp's ray queue
         if (counters) RT_LAUNCH(RT_KERNEL_RECURSE(true), blocks, RT_THREADS, stream, S, cam, out);
         else RT_LAUNCH(RT_KERNEL_RECURSE(false), blocks, RT_THREADS, stream, S, cam, out);

@@ -148,8 +148,13 @@ __device__ __forceinline__ double shflD(double v, int src) { return __shfl_sync(
 // RT_BATCH_PASSES passes (128 samples) of depth 0 before it drains the queue, so that the secondary rays of a whole
 // 8x4 tile at 4 spp are traced 32 at a time; scenes without recursion run the lean instantiation (no queue code, no
 // colour buffer in shared memory: the packet walk keeps its L1 and its instruction cache).
-template <bool COUNT, bool RECURSE>
-__global__ void __launch_bounds__(RT_FAST_BLOCK, RT_FAST_BLOCKS) renderKernelFast(DeviceScene S, CameraParams cam, RenderTargets out) {
+// BLOCKS: resident one-warp blocks per SM the instantiation is compiled for.  32 (64 registers) is what a scene of big
+// meshes wants — its node walks are dependent chains of cache misses and resident warps hide them (C5: 178 ms at 32,
+// 189 at 24, 209 at 16).  A scene of analytic primitives and small meshes with recursion (C3) spends its time in
+// shading code that streams through the instruction caches, and 16 warps of 128 registers — no spills, half as many
+// warps fetching — run it 8 % faster (6.54 -> 6.03 ms): RenderTargets::recurse == 2 takes that instantiation.
+template <bool COUNT, bool RECURSE, int BLOCKS = RT_FAST_BLOCKS>
+__global__ void __launch_bounds__(RT_FAST_BLOCK, BLOCKS) renderKernelFast(DeviceScene S, CameraParams cam, RenderTargets out) {
     static_assert(RT_FAST_BLOCK == 32, "one warp per block: the packet stack and the colour buffer are the warp's");
     __shared__ int2 wstacks[RT_WARP_STACK_INT2];
     __shared__ double colBuf[RECURSE ? RT_BATCH_PASSES * 96 : 1];     // per-sample sums of the batch in flight
