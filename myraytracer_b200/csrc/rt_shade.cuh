@@ -263,6 +263,12 @@ __device__ __forceinline__ int spawnChildren(const DeviceScene& S, const ShadePo
     return count;
 }
 
+// the general kernel's scene walk: the nested loops of rt_trace.cuh (-DRT_GENERAL_WALK=traceSceneFlat: both levels in
+// one loop — measured and dropped, see the comment there)
+#ifndef RT_GENERAL_WALK
+#define RT_GENERAL_WALK traceScene
+#endif
+
 // Depth-first processing of path entries with the per-lane traversal: `cur` is the entry to start with and
 // `level` the number of entries already waiting on this thread's path stack.  firstIsPrimary: `cur` is the
 // camera ray (tMin = near-plane clip :341-344, hit id recorded).  Returns `color` plus the w * Lo of all
@@ -278,7 +284,7 @@ __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceSc
     for (;;) {
         HitRec hit;
         hit.t = CUDART_INF; hit.u = hit.v = 0; hit.inst = -1; hit.slot = 0;
-        traceScene<COUNT, MOTION>(S, cur.o, cur.d, primary ? tMinPrimary : 0.0, hit, false, T.sstack, T.sstackN, C, time);
+        RT_GENERAL_WALK<COUNT, MOTION>(S, cur.o, cur.d, primary ? tMinPrimary : 0.0, hit, false, T.sstack, T.sstackN, C, time);
         Surface sf;
         if (hit.inst >= 0) {
             resolveHit<MOTION>(S, hit, cur.o, cur.d, sf, time);
@@ -308,7 +314,7 @@ __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceSc
                     HitRec sh;
                     sh.t = dist; sh.u = sh.v = 0; sh.inst = -1; sh.slot = 0;             // tMax = dist (:124)
                     R.shadow++;
-                    const bool occluded = traceScene<COUNT, MOTION>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, C, time);
+                    const bool occluded = RT_GENERAL_WALK<COUNT, MOTION>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, C, time);
                     if (!occluded)
                         Lo = Lo + pointLightTerm(*sp.mat, pl, sp.N, cur.d, wi, dist);
                 }
@@ -326,7 +332,7 @@ __device__ __forceinline__ V3 scalarPathLoop(const DeviceScene& S, const TraceSc
                     sh.t = dist - S.shadowEps; sh.u = sh.v = 0; sh.inst = -1; sh.slot = 0;   // tMax = dist - shadowEps (:173)
                     R.shadow++;
                     const V3 so = sp.p + wi * S.shadowEps;
-                    const bool occluded = traceScene<COUNT, MOTION>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, C, time);
+                    const bool occluded = RT_GENERAL_WALK<COUNT, MOTION>(S, so, wi, 0.0, sh, true, T.sstack, T.sstackN, C, time);
                     if (!occluded) Lo = Lo + areaLightTerm(*sp.mat, al, sp.N, cur.d, wi, dist2, NdotL, Ln);
                 }
             }

@@ -145,6 +145,119 @@ __device__ __forceinline__ bool traceScene(const DeviceScene& S, V3 o, V3 d, dou
     }
 }
 
+// The same query as traceScene with the two levels in ONE loop (the general kernel's walk).  Nested — a TLAS loop whose
+// leaves call a BLAS loop — the lanes of a warp enter a mesh at different iterations of the outer loop and walk it a
+// few at a time: ncu shows 2.3 to 4.2 of 32 lanes active in the node loop of the mesh walk on C3 with glossy materials,
+// half of that kernel's instructions.  TLAS and BLAS nodes share one record format (GNode), so here a lane is simply at
+// "a node": the node step is one piece of code for both levels, every lane that has a ray executes it whatever level
+// it is on, and entering an instance is a leaf action — transform the ray, root test, swap the FP32 ray view and
+// the node array, push a return marker under the BLAS root; popping the marker swaps back.  Same visiting order as
+// the nested loops (an instance is a subtree), so the same hits and the same tie-breaking (every emulated and GPU
+// parity case passes with it).
+// MEASURED AND NOT USED (-DRT_GENERAL_WALK=traceSceneFlat builds it; B200, ms per frame, flat / nested, profiles/r2ac):
+// C3 glossy 11.65 / 12.11, but C3 with area lights 22.86 / 20.03, C3 through the general kernel 10.30 / 9.47, and the
+// mesh scenes forced through the general kernel C4 37.9 / 27.7, C5 410 / 284, C2 0.75 / 0.50.  More lanes are
+// active per instruction, yet every iteration goes through a four-way dispatch (inner node, return marker, triangles,
+// instance entry) and pays for every kind of step some lane is at, where the nested BLAS loop is 35 instructions that
+// stay in the instruction cache; a lane that enters an instance (150 FP64 instructions) stalls 31 node steps.
+static const int32_t kReturnRef = 0x7ffffffe;      // stack marker: the entries above it belonged to an instance's BLAS
+#ifndef RT_FLAT_STACK
+#define RT_FLAT_STACK (RT_STACK + RT_TLAS_STACK + 2)
+#endif
+template <bool COUNT, bool MOTION = false>
+__device__ __forceinline__ bool traceSceneFlat(const DeviceScene& S, V3 o, V3 d, double tMin, HitRec& hit, bool anyhit,
+                                               int32_t* sstack, int sstackN, Counters& C, double time = 0.0) {
+    const double eps = S.eps;
+    int32_t cur = S.tlasRootRef;
+    if (cur == kEmptyRef) return false;
+    if (MOTION && S.refTlasNodes > 0) return traceSceneRef<COUNT>(S, o, d, tMin, hit, anyhit, sstack, sstackN, C, time);
+    const double tLow = dmax(eps, tMin);
+    RayF top;                                   // the ray against the TLAS boxes (unused when the scene is one instance)
+    top.ix = top.iy = top.iz = top.nx = top.ny = top.nz = top.tmin = top.tmax = 0.0f; top.t0 = 0.0; top.hits = true;
+    if (cur >= 0) {
+        top = makeRayF(S.tlasLo, S.tlasHi, S.tlasCentre, o, d, refinedInv(d), tLow, hit.t);
+        if (COUNT) C.box++;
+        if (!top.hits) return false;
+    }
+    RayF a = top;                               // the view the node step uses: `top`, or the current instance's
+    const GNode* base = S.tlas;
+    bool inBlas = false;
+    int instIdx = -1;
+    V3 oL = o, dL = d, oTri = o;
+    int32_t lstack[RT_FLAT_STACK];
+    int sp = 0;
+    const int tid = threadIdx.x;
+#define RT_FLAT_PUSH(v) do { if (sp < sstackN) sstack[sp * RT_BLOCK + tid] = (v); else lstack[sp - sstackN] = (v); sp++; } while (0)
+    for (;;) {
+        if ((uint32_t)cur < (uint32_t)kReturnRef) {            // an inner node of either level
+            float n0, n1;
+            bool h0, h1;
+            int2 ch;
+            twoBoxes(base + cur, a, n0, h0, n1, h1, ch);
+            if (COUNT) C.box += 2;
+            if (h0 && h1) {
+                int32_t nearC = ch.x, farC = ch.y;
+                if (n1 < n0) { nearC = ch.y; farC = ch.x; }
+                RT_FLAT_PUSH(farC);
+                if (COUNT && sp > C.maxStack) C.maxStack = sp;
+                cur = nearC;
+                continue;
+            }
+            if (h0) { cur = ch.x; continue; }
+            if (h1) { cur = ch.y; continue; }
+        } else if (cur == kReturnRef) {                       // the instance is done: back to the TLAS
+            inBlas = false;
+            base = S.tlas;
+            top.tmax = __double2float_ru(hit.t - top.t0);       // a closer hit prunes the boxes that follow
+            a = top;
+        } else if (cur != kEmptyRef) {
+            if (inBlas) {                                       // triangles of a leaf
+                const uint32_t ref = ~(uint32_t)cur;
+                const int first = (int)(ref >> 4), count = (int)(ref & 7u) + 1;
+                const bool f64 = (ref & 8u) != 0;
+                for (int k = 0; k < count; k++) {
+                    V3 v0, v1, v2;
+                    loadTri(S, f64, first + k, v0, v1, v2);
+                    if (COUNT) C.tri++;
+                    double t, u, v;
+                    if (!mtTest(v0, v1, v2, oTri, dL, eps, t, u, v)) continue;
+                    if (!inWindow(t, tLow, hit.t, anyhit)) continue;
+                    if (anyhit) return true;
+                    hit.t = t; hit.u = u; hit.v = v; hit.inst = instIdx; hit.slot = first + k;
+                    a.tmax = __double2float_ru(t - a.t0);
+                }
+            } else {                                            // an instance (RTContext.swift:651-704)
+                const int idx = ~cur;
+                const GInstance& I = S.instances[idx];
+                toLocal<MOTION>(I, o, d, oL, dL, time);
+                if (COUNT) C.inst++;
+                if (I.kind == INST_MESH) {
+                    const RayF b = makeRayF(I.rootLo, I.rootHi, I.centre, oL, dL, refinedInv(dL), tLow, hit.t);
+                    if (COUNT) C.box++;
+                    if (b.hits) {
+                        oTri = MOTION ? oL - ld3(I.meshMotion) * time : oL;
+                        instIdx = idx;
+                        a = b;
+                        base = S.nodes;
+                        inBlas = true;
+                        RT_FLAT_PUSH(kReturnRef);
+                        cur = I.rootRef;
+                        continue;
+                    }
+                } else {
+                    if (analyticInstance<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, C)) return true;
+                    top.tmax = __double2float_ru(hit.t - top.t0);
+                    a = top;
+                }
+            }
+        }
+        if (sp == 0) return false;
+        sp--;
+        cur = sp < sstackN ? sstack[sp * RT_BLOCK + tid] : lstack[sp - sstackN];
+    }
+#undef RT_FLAT_PUSH
+}
+
 #ifdef RT_EMU
 #define RT_NOINLINE __attribute__((noinline))
 #else
