@@ -38,6 +38,18 @@ __device__ __forceinline__ void stsPair(uint32_t addr, int a, int b) {
 }
 __device__ __forceinline__ int2 ldsPair(uint32_t addr) { return *reinterpret_cast<int2*>(rtemu::g_sharedBase + (intptr_t)(int32_t)addr); }
 #endif
+// RT_PREFETCH=1: prefetch.global.L1 of both children before the box tests decide between them; =2: into L2 only
+#if defined(RT_PREFETCH) && !defined(RT_EMU)
+__device__ __forceinline__ void prefetchL1(const void* p) {
+#if RT_PREFETCH == 2
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+#else
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+#endif
+}
+#else
+__device__ __forceinline__ void prefetchL1(const void*) {}
+#endif
 #ifndef RT_WSTACK
 #define RT_WSTACK (RT_BSTACK + 1)   // BLAS entries per warp: the packet walk needs the tree depth (checked against RT_STACK at
 #endif                              // build time, <= 64), the beam walk of the wide tree RT_BSTACK entries + its sentinel
