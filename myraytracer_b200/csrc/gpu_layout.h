@@ -141,7 +141,7 @@ struct DeviceScene {
     const int32_t* refTlasPrim;    // its primitiveIdx array (instance indices in leaf order)
     const WNode* wnodes;           // wide BVHs of the meshes (collapsed from `nodes`), all BLASes concatenated
     int32_t refTlasNodes;          // 0: not used
-    int32_t pad1;
+    int32_t wideMode;              // beam walk (RTCUDA_WIDE): 1 every coherent packet, 2 closest-hit packets only, 3 any-hit packets only
     int32_t tlasRootRef;
     int32_t nInstances, nMaterials, nPointLights;
     int32_t maxDepth;

@@ -593,6 +593,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     S.nInstances = (int32_t)d->nInstances; S.nMaterials = (int32_t)d->nMaterials; S.nPointLights = (int32_t)d->nPointLights;
     S.nAreaLights = (int32_t)d->nAreaLights;
     S.refTlasNodes = (int32_t)refTl.nodes.size();
+    S.wideMode = wantWide ? std::atoi(wideEnv) : 0;
     S.maxDepth = d->maxRecursionDepth;
     std::memcpy(S.ambient, d->ambient, 24); std::memcpy(S.background, d->background, 24);
     // a scene without instances has no TLAS, and `trace` then returns .zero, not the background

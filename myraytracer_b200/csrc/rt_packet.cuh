@@ -229,7 +229,8 @@ __device__ __forceinline__ uint32_t packetInstance(const DeviceScene& S, int idx
             return __ballot_sync(RT_FULL, o1);
         }
         // coherent packet, mesh with a wide tree: the beam walk first
-        const bool tryBeam = !(INCOHERENT && incoherent) && I.wideRoot != kEmptyRef;
+        const bool tryBeam = !(INCOHERENT && incoherent) && I.wideRoot != kEmptyRef &&
+                             (S.wideMode == 1 || (S.wideMode == 2 && !anyhit) || (S.wideMode == 3 && anyhit));
         return packetBlas<COUNT>(S, I, idx, oL, dL, eps, tLow, hit, anyhit, inMask, wstack, C, tryBeam);
     }
     bool occ = false;
