@@ -702,6 +702,20 @@ def test_emulated_beam_walk_vs_oracle(name, scene_dir, emu, monkeypatch):
     assert got.stats["raysPrimary"] == base.stats["raysPrimary"] and got.stats["raysSecondary"] == base.stats["raysSecondary"]
 
 
+@pytest.mark.parametrize("mode", ["2", "3"])
+def test_emulated_beam_walk_by_packet_kind(mode, scene_dir, emu, monkeypatch):
+    """RTCUDA_WIDE=2: only closest-hit packets walk as beams, =3: only any-hit (shadow) packets; the other kind takes the
+    packet walk in the same frame.  Same image, and the box-test counts differ from both pure modes."""
+    path = scenegen.config_c2(scene_dir, n=32, width=64, height=40)
+    runs = {}
+    for m in ("0", "1", mode):
+        monkeypatch.setenv("RTCUDA_WIDE", m)
+        runs[m] = RayTracerEngine(path).render(0, want_ids=True, variant=1, counters=True)
+    assert np.array_equal(runs[mode].rgba, runs["0"].rgba) and np.array_equal(runs["1"].rgba, runs["0"].rgba)
+    assert np.array_equal(runs[mode].ids["prim"], runs["0"].ids["prim"])
+    assert len({runs[m].stats["boxTests"] for m in runs}) == 3
+
+
 def test_emulated_beam_walk_budget_falls_back_to_the_packet_walk(scene_dir, emu, monkeypatch):
     """A low-resolution frame over a fine mesh makes fat beams (an 8x4-pixel packet spans hundreds of triangles): the
     visit budget runs out and the packet walk finishes — same image."""
