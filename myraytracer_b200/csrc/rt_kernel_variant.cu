@@ -11,7 +11,10 @@ namespace rtg {
 #if RT_V_FAST
 #define RT_KERNEL(c) renderKernelFast<c, false>
 #define RT_KERNEL_RECURSE(c) renderKernelFast<c, true>
-#define RT_KERNEL_RECURSE_SMALL(c) renderKernelFast<c, true, 16>
+#ifndef RT_FAST_BLOCKS_SMALL
+#define RT_FAST_BLOCKS_SMALL 12    // B200, C3: 8 warps 6.15 ms, 12 5.71, 16 6.07, 20 6.27, 32 6.49
+#endif
+#define RT_KERNEL_RECURSE_SMALL(c) renderKernelFast<c, true, RT_FAST_BLOCKS_SMALL>
 #define RT_NAME(x) x##Fast
 #define RT_THREADS RT_FAST_BLOCK
 #else
@@ -31,7 +34,7 @@ cudaError_t RT_NAME(launchVariant)(const DeviceScene& S, const CameraParams& cam
     }
 #endif
 #ifdef RT_KERNEL_RECURSE
-    if (out.recurse == 2) {                    // ... and no big mesh: 16 resident warps of 128 registers per SM
+    if (out.recurse == 2) {                    // ... and no big mesh: RT_FAST_BLOCKS_SMALL resident warps per SM
         if (counters) RT_LAUNCH(RT_KERNEL_RECURSE_SMALL(true), blocks, RT_THREADS, stream, S, cam, out);
         else RT_LAUNCH(RT_KERNEL_RECURSE_SMALL(false), blocks, RT_THREADS, stream, S, cam, out);
         return cudaGetLastError();

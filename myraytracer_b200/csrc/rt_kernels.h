@@ -32,7 +32,7 @@ struct RenderTargets {
     int areaPass;
     int motion;                    // 1: the scene has motion blur (general kernel, ray time carried down the path)
     int recurse;                   // 1: child rays are possible (fast kernel: the instantiation with the warp's ray queue);
-                                   // 2: ... and the scene has no big mesh (the same, compiled for 16 warps of 128 registers per SM)
+                                   // 2: ... and the scene has no big mesh (the same, compiled for 12 warps of 168 registers per SM)
 #ifdef RT_WARPTIMES
     unsigned long long* warpTimes; // profiling build only: 4 x u64 per warp (start, first unit done, last draw, exit; ns)
 #endif

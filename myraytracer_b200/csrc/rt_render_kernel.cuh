@@ -151,8 +151,9 @@ __device__ __forceinline__ double shflD(double v, int src) { return __shfl_sync(
 // BLOCKS: resident one-warp blocks per SM the instantiation is compiled for.  32 (64 registers) is what a scene of big
 // meshes wants — its node walks are dependent chains of cache misses and resident warps hide them (C5: 178 ms at 32,
 // 189 at 24, 209 at 16).  A scene of analytic primitives and small meshes with recursion (C3) spends its time in
-// shading code that streams through the instruction caches, and 16 warps of 128 registers — no spills, half as many
-// warps fetching — run it 8 % faster (6.54 -> 6.03 ms): RenderTargets::recurse == 2 takes that instantiation.
+// shading code that streams through the instruction caches, and 12 warps of 168 registers — no spills, a third as many
+// warps fetching — run it 12 % faster (6.49 -> 5.71 ms; rt_kernel_variant.cu: RT_FAST_BLOCKS_SMALL): RenderTargets::recurse
+// == 2 takes that instantiation.
 template <bool COUNT, bool RECURSE, int BLOCKS = RT_FAST_BLOCKS>
 __global__ void __launch_bounds__(RT_FAST_BLOCK, BLOCKS) renderKernelFast(DeviceScene S, CameraParams cam, RenderTargets out) {
     static_assert(RT_FAST_BLOCK == 32, "one warp per block: the packet stack and the colour buffer are the warp's");
