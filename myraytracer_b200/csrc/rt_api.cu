@@ -6,6 +6,7 @@
 // rt_render       : Renderer.render (Extensions/Object+Extension.swift:52-379) + RGBA8 conversion
 //                   (RayTracer.swift:186-195); camera set-up = makeCameraBasis (:382-427) on the host.
 // There is no CPU fallback: without a CUDA device every entry point fails with RT_ERR_CUDA.
+#include <algorithm>
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -130,7 +131,8 @@ struct rt_scene {
     cudaStream_t stream = nullptr, poll = nullptr;
     cudaEvent_t evReset = nullptr;     // the frame's counters have been zeroed: the work counter may be polled
     int* hPoll = nullptr;              // pinned: [0] work counter read back, [1] the value that cancels a frame
-    int64_t pendingUnits = 0, pendingWarps = 0;   // work units of the frame in flight / warps drawing them
+    int64_t pendingUnits = 0;          // work units of the frame in flight: passUnits[0] (counting pass of an area-light frame, else 0) + passUnits[1]
+    int64_t passUnits[2] = {0, 0}, passWarps[2] = {0, 0};   // per pass: units / warps drawing them (a warp's last, failing draw counts too)
     rt_scene_info info{};
     int64_t meshes = 0;
     // device allocations

@@ -116,7 +116,12 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     // general kernel: one depth-first stack of maxDepth + 1 entries per thread; fast kernel: per warp a shared queue of
     // 32 x (maxDepth + 3 + 2 per extra pass of a batch) entries plus maxDepth + 2 private spill-over entries per lane
     // (rt_shade.cuh: WarpQueue)
-    const size_t need = (size_t)(2 * sc->ds.maxDepth + 5 + 2 * (RT_BATCH_PASSES - 1)) * kPathFields * threads * sizeof(double);
+    // an area-light frame of a scene the fast kernel can follow counts its jitter-table draws there (pass 1), then shades
+    // in the general kernel (pass 2): the path stack holds the larger of the two
+    const bool fastCount = area && variant == KV_GENERAL && !sc->glossy && !sc->motion && !std::getenv("RTCUDA_AREA_COUNT_GENERAL");
+    const int blocksCount = sc->blocks[KV_FAST][0];
+    const size_t threadsCount = fastCount ? (size_t)blocksCount * renderBlockSize(KV_FAST) : 0;
+    const size_t need = (size_t)(2 * sc->ds.maxDepth + 5 + 2 * (RT_BATCH_PASSES - 1)) * kPathFields * std::max(threads, threadsCount) * sizeof(double);
     if ((rc = ensure(&sc->dPathStack, &sc->pathStackBytes, need))) return rc;
 
     RenderTargets rt{};
@@ -182,8 +187,12 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     {   // what the work counter counts up to (progress / cancel of rt_render): see the kernels' unit rules
         const int ns = cp.n * cp.n;
         const int unitsPerTile = variant == KV_FAST ? FastUnits(ns, sc->recurse).perTile : 1;
-        sc->pendingUnits = (int64_t)nTiles * unitsPerTile * (area ? 2 : 1);
-        sc->pendingWarps = (int64_t)(threads / 32);
+        sc->passUnits[1] = (int64_t)nTiles * unitsPerTile;
+        sc->passWarps[1] = (int64_t)(threads / 32);
+        // area lights: two passes over the tiles (the work counter is reset in between); pass 0 is the counting pass
+        sc->passUnits[0] = !area ? 0 : fastCount ? (int64_t)nTiles * FastUnits(ns, sc->recurse).perTile : sc->passUnits[1];
+        sc->passWarps[0] = !area ? 0 : fastCount ? (int64_t)(threadsCount / 32) : sc->passWarps[1];
+        sc->pendingUnits = sc->passUnits[0] + sc->passUnits[1];
     }
     if (area) {
         // pass 1 follows every path and counts its jitter-table draws per pixel; the prefix kernel turns the counts
@@ -191,7 +200,8 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
         if ((rc = ensure(&sc->dAreaIndex, &sc->areaIndexBytes, (size_t)cp.width * cp.height * sizeof(unsigned)))) return rc;
         rt.areaIndex = sc->dAreaIndex;
         rt.areaPass = 1;
-        CK(launchRender(variant, sc->ds, cp, rt, blocks, counters, st));
+        if (fastCount) CK(launchRender(KV_FAST, sc->ds, cp, rt, blocksCount, false, st));
+        else CK(launchRender(variant, sc->ds, cp, rt, blocks, counters, st));
         CK(launchAreaPrefix(sc->dAreaIndex, cp.width, cp.height, cp.shardIndex, cp.shardCount, st));
         CK(cudaMemsetAsync(sc->dTileCounter, 0, sizeof(int), st));
         rt.areaPass = 2;
@@ -319,10 +329,11 @@ double pollProgress(rt_scene* rep, bool cancel, int& lastDrawn, int64_t& base) {
     cudaMemcpyAsync(rep->hPoll, rep->dTileCounter, sizeof(int), cudaMemcpyDeviceToHost, rep->poll);
     if (cudaStreamSynchronize(rep->poll) != cudaSuccess) { cudaGetLastError(); return -1; }
     const int drawn = rep->hPoll[0];
-    if (drawn < lastDrawn) base += rep->pendingUnits / 2;        // area lights: the second pass started (counter reset)
+    if (drawn < lastDrawn && base == 0) base = rep->passUnits[0];   // area lights: the second pass started (counter reset)
     lastDrawn = drawn;
-    const int64_t passUnits = rep->ds.nAreaLights > 0 ? rep->pendingUnits / 2 : rep->pendingUnits;
-    int64_t done = (int64_t)drawn - rep->pendingWarps;
+    const int pass = (rep->passUnits[0] > 0 && base == 0) ? 0 : 1;
+    const int64_t passUnits = rep->passUnits[pass];
+    int64_t done = (int64_t)drawn - rep->passWarps[pass];
     if (done < 0) done = 0;
     if (done > passUnits) done = passUnits;
     return rep->pendingUnits > 0 ? (double)(base + done) / (double)rep->pendingUnits : 1.0;

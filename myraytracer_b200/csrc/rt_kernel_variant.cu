@@ -34,6 +34,12 @@ cudaError_t RT_NAME(launchVariant)(const DeviceScene& S, const CameraParams& cam
     }
 #endif
 #ifdef RT_KERNEL_RECURSE
+    if (out.areaPass == 1) {                   // counting pass of an area-light frame (no counters: it reports no rays)
+        if (out.recurse == 2) RT_LAUNCH((renderKernelFast<false, true, RT_FAST_BLOCKS_SMALL, true>), blocks, RT_THREADS, stream, S, cam, out);
+        else if (out.recurse) RT_LAUNCH((renderKernelFast<false, true, RT_FAST_BLOCKS, true>), blocks, RT_THREADS, stream, S, cam, out);
+        else RT_LAUNCH((renderKernelFast<false, false, RT_FAST_BLOCKS, true>), blocks, RT_THREADS, stream, S, cam, out);
+        return cudaGetLastError();
+    }
     if (out.recurse == 2) {                    // ... and no big mesh: RT_FAST_BLOCKS_SMALL resident warps per SM
         if (counters) RT_LAUNCH(RT_KERNEL_RECURSE_SMALL(true), blocks, RT_THREADS, stream, S, cam, out);
         else RT_LAUNCH(RT_KERNEL_RECURSE_SMALL(false), blocks, RT_THREADS, stream, S, cam, out);

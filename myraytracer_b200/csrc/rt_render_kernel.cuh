@@ -100,6 +100,13 @@ __device__ __forceinline__ void writePixel(const RenderTargets& out, size_t pix,
     }
 }
 
+// a finished pixel: its colour — or, in the counting pass of an area-light frame, its number of jitter-table draws
+template <bool AREACOUNT>
+__device__ __forceinline__ void emitPixel(const RenderTargets& out, size_t pix, V3 c) {
+    if (AREACOUNT) out.areaIndex[pix] = (unsigned)c.x;
+    else writePixel(out, pix, c);
+}
+
 template <bool COUNT>
 __device__ __forceinline__ void flushCounters(const RenderTargets& out, Counters& C, RayCounts& R) {
     for (int off = 16; off > 0; off >>= 1) {
@@ -154,7 +161,14 @@ __device__ __forceinline__ double shflD(double v, int src) { return __shfl_sync(
 // shading code that streams through the instruction caches, and 12 warps of 168 registers — no spills, a third as many
 // warps fetching — run it 12 % faster (6.49 -> 5.71 ms; rt_kernel_variant.cu: RT_FAST_BLOCKS_SMALL): RenderTargets::recurse
 // == 2 takes that instantiation.
-template <bool COUNT, bool RECURSE, int BLOCKS = RT_FAST_BLOCKS>
+// AREACOUNT: pass 1 of an area-light frame (RenderTargets::areaPass == 1) for scenes this kernel can follow — no glossy
+// material, no motion blur.  The reference draws an area-light sample for every area light at every shading point that
+// computes direct light (:145-186), through one running index per 8-row chunk; what pass 2 (general kernel) needs is each
+// pixel's number of such draws.  This instantiation walks the same path trees — closest-hit packets, children through
+// the ray queue — without shadow rays or light terms, adds nAreaLights per shading point to the sample's slot (small
+// integers: exact in FP64 in any order) and leaves the pixel's total in areaIndex.  It replaces the general kernel's
+// per-lane counting walk, which cost 40 % of such a frame.
+template <bool COUNT, bool RECURSE, int BLOCKS = RT_FAST_BLOCKS, bool AREACOUNT = false>
 __global__ void __launch_bounds__(RT_FAST_BLOCK, BLOCKS) renderKernelFast(DeviceScene S, CameraParams cam, RenderTargets out) {
     static_assert(RT_FAST_BLOCK == 32, "one warp per block: the packet stack and the colour buffer are the warp's");
     __shared__ int2 wstacks[RT_WARP_STACK_INT2];
@@ -177,7 +191,7 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, BLOCKS) renderKernelFast(Device
     const ShardTiles tiles(cam.width, cam.height, cam.shardIndex, cam.shardCount, cam.shardTiles);
     const int n = cam.n, ns = n * n;                 // samples traced per pixel (:298-306)
     const int drawsPerSample = cam.dof ? 5 : 3;      // xi1, xi2, [lens u, v], time
-    const double samplesD = (double)cam.samples;     // the sum is divided by `samples` (:354)
+    const double samplesD = AREACOUNT ? 1.0 : (double)cam.samples;     // the sum is divided by `samples` (:354); a count is not
     const bool segmented = ns < 32 && (32 % ns) == 0;
     const V3 ambient = ld3(S.ambient), background = ld3(S.background);
     // sample s of a lane is the same in every pass when n*n divides 32: its skip-ahead factors are computed once
@@ -303,10 +317,11 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, BLOCKS) renderKernelFast(Device
                             setupShade(S, sf, cur0, hit.t, sp);
                             if (sp.computeDirect) Lo = ambient * ld3(sp.mat->ambient);
                         }
-                        if (primary && out.ids && active) {
+                        if (!AREACOUNT && primary && out.ids && active) {
                             HitId& h = out.ids[((size_t)idJ * W + idI) * (size_t)ns + (size_t)idS];
                             h.inst = hit.inst; h.kind = sf.kind; h.prim = sf.prim; h.t = hit.t;
                         }
+                        if (AREACOUNT) break;                                       // counting pass: no shadow rays
                         if (__ballot_sync(0xffffffffu, sp.computeDirect) == 0u) break;
                     } else if (rayOn && !occ) {
                         Lo = Lo + pointLightTerm(*sp.mat, S.pointLights[phase - 1], sp.N, cur0.d, wi, dist);
@@ -322,7 +337,8 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, BLOCKS) renderKernelFast(Device
                 // ---- what the rays of this round add to their samples (:345): miss -> background (:101-103), else the
                 //      direct light of the vertex; no non-finite guard here (see WarpQueue)
                 c = mk(0, 0, 0);
-                if (active) c = isHit ? sp.w * Lo : cur0.w * background;
+                if (AREACOUNT) { if (active && isHit && sp.computeDirect) c.x = (double)S.nAreaLights; }
+                else if (active) c = isHit ? sp.w * Lo : cur0.w * background;
                 if (!RECURSE) break;
                 PathEntry c1 = cur0, c2 = cur0;
                 int nc = 0;
@@ -368,7 +384,7 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, BLOCKS) renderKernelFast(Device
                         comp = ddiv(comp, samplesD);
                     }
                     const V3 px3 = mk(shflD(comp, base), shflD(comp, base + 1), shflD(comp, base + 2));
-                    if (active && s == 0) writePixel(out, (size_t)j * W + i, px3);
+                    if (active && s == 0) emitPixel<AREACOUNT>(out, (size_t)j * W + i, px3);
                     __syncwarp();
                 } else if (segmented) {
                     const int base = lane & ~(ns - 1);
@@ -378,7 +394,7 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, BLOCKS) renderKernelFast(Device
                         const V3 ck = mk(shflD(c.x, base + k), shflD(c.y, base + k), shflD(c.z, base + k));
                         sum = sum + ck;
                     }
-                    if (active && s == 0) writePixel(out, (size_t)j * W + i, sum / samplesD);
+                    if (active && s == 0) emitPixel<AREACOUNT>(out, (size_t)j * W + i, sum / samplesD);
                 } else if (units.perPixel) {
                     // 32 divides ns: the 32 samples of this pass are consecutive samples of ONE pixel.  Lanes 0..2 add one
                     // component each, in sample order, carrying their sum from pass to pass (acc.x in all three).
@@ -394,7 +410,7 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, BLOCKS) renderKernelFast(Device
                     if (it == itEnd - 1) {
                         const double comp = ddiv(acc.x, samplesD);
                         const V3 px3 = mk(shflD(comp, 0), shflD(comp, 1), shflD(comp, 2));
-                        if (active && lane == 0) writePixel(out, (size_t)j * W + i, px3);
+                        if (active && lane == 0) emitPixel<AREACOUNT>(out, (size_t)j * W + i, px3);
                     }
                 } else {
 #pragma unroll 1
@@ -404,7 +420,7 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, BLOCKS) renderKernelFast(Device
                         if (pk != openP) {
                             if (openP >= 0 && lane == 0) {
                                 const int qx = (openP & 1) | ((openP >> 1) & 2) | ((openP >> 2) & 4), qy = ((openP >> 1) & 1) | ((openP >> 2) & 2);
-                                if (x0 + qx < W && y0 + qy < H) writePixel(out, (size_t)(y0 + qy) * W + (x0 + qx), acc / samplesD);
+                                if (x0 + qx < W && y0 + qy < H) emitPixel<AREACOUNT>(out, (size_t)(y0 + qy) * W + (x0 + qx), acc / samplesD);
                             }
                             openP = pk;
                             acc = mk(0, 0, 0);
@@ -416,7 +432,7 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, BLOCKS) renderKernelFast(Device
         }
         if (!segmented && !units.perPixel && openP >= 0 && lane == 0) {
             const int qx = (openP & 1) | ((openP >> 1) & 2) | ((openP >> 2) & 4), qy = ((openP >> 1) & 1) | ((openP >> 2) & 2);
-            if (x0 + qx < W && y0 + qy < H) writePixel(out, (size_t)(y0 + qy) * W + (x0 + qx), acc / samplesD);
+            if (x0 + qx < W && y0 + qy < H) emitPixel<AREACOUNT>(out, (size_t)(y0 + qy) * W + (x0 + qx), acc / samplesD);
         }
         if (out.tileCost && lane == 0) {       // cost of the unit in clocks/64, summed per tile for the next frame's schedule
             const uint2 note = unitNote[warpInBlock];
@@ -429,6 +445,7 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, BLOCKS) renderKernelFast(Device
         w[0] = wt0; w[1] = wt1; w[2] = wt2; w[3] = globalTimerNs();
     }
 #endif
+    if (AREACOUNT) return;                     // the counting pass reports no rays: pass 2 traces them all again
     flushCounters<COUNT>(out, C, R);
 }
 

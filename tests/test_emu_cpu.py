@@ -156,6 +156,23 @@ def test_emulated_shards_and_schedule(scene_dir, emu):
         assert np.array_equal(first.rgba, full.rgba) and np.array_equal(again.rgba, full.rgba)
 
 
+@pytest.mark.parametrize("kw", [dict(width=64, height=48, samples=4, depth=3, ico_level=2, area_lights=2),
+                                dict(width=50, height=37, samples=9, depth=4, ico_level=1, area_lights=3),
+                                dict(width=40, height=30, samples=4, depth=3, ico_level=1, area_lights=2, inf_light=True)])
+def test_emulated_area_light_counting_pass_on_the_fast_kernel(kw, scene_dir, emu, monkeypatch):
+    """Pass 1 of an area-light frame (each pixel's number of jitter-table draws) runs on the fast kernel when no material is
+    glossy and nothing moves (renderKernelFast<.., AREACOUNT>: packets + ray queue, no shadow rays); the general kernel's
+    counting walk (RTCUDA_AREA_COUNT_GENERAL=1) must give the same frame bit for bit, and both the oracle's."""
+    path = scenegen.config_c3(scene_dir, **kw)
+    ref = oracle_lib.OracleScene(path).render(want_ids=True, want_linear=True)
+    fast = RayTracerEngine(path).render(0, want_ids=True, want_linear=True)
+    check(fast, ref)
+    monkeypatch.setenv("RTCUDA_AREA_COUNT_GENERAL", "1")
+    gen = RayTracerEngine(path).render(0, want_ids=True, want_linear=True)
+    assert np.array_equal(fast.linear, gen.linear) and np.array_equal(fast.rgba, gen.rgba)
+    assert fast.stats["rays"] == gen.stats["rays"]
+
+
 def test_emulated_area_lights_shard_by_chunks(scene_dir, emu):
     """The jitter index of the area lights runs through an 8-row chunk (Object+Extension.swift:288): shards made of
     whole chunks reproduce the frame bit for bit; tile shards and the fast kernel are refused, not approximated."""
