@@ -155,6 +155,7 @@ struct rt_scene {
     BoundsChunk* dBoundChunks = nullptr; int nBoundChunks = 0;   // (instance, triangle range) work items of launchInstanceBounds
     int32_t* dDerive = nullptr; int32_t* hDerive = nullptr;      // per instance: 1 = derive worldBounds on the device
     unsigned long long* dBoundsEnc = nullptr; unsigned long long* hBoundsEnc = nullptr;
+    int* dDefer = nullptr; size_t deferBytes = 0;                // two-launch frames: [0] number of deferred units, then the units
     unsigned* dAreaIndex = nullptr; size_t areaIndexBytes = 0;   // per-pixel jitter index of an area-light frame
     // render state (re-used across calls)
     int* dTileCounter = nullptr; unsigned long long* dCounters = nullptr;
@@ -634,7 +635,7 @@ void rt_scene_destroy(rt_scene_t* sc) {
     cudaFree(sc->dWNodes);
     cudaFree(sc->dNodes); cudaFree(sc->dTris); cudaFree(sc->dTrisD); cudaFree(sc->dNormals); cudaFree(sc->dTlas);
     cudaFree(sc->dInst); cudaFree(sc->dMat); cudaFree(sc->dLights); cudaFree(sc->dCounters);
-    cudaFree(sc->dAreaLights); cudaFree(sc->dJitter); cudaFree(sc->dAreaIndex);
+    cudaFree(sc->dAreaLights); cudaFree(sc->dJitter); cudaFree(sc->dAreaIndex); cudaFree(sc->dDefer);
     cudaFree(sc->dRefTlas); cudaFree(sc->dRefTlasPrim);
     cudaFree(sc->dTlasD); cudaFree(sc->dRefitOrder); cudaFree(sc->dRefitLevelStart); cudaFree(sc->dInstBounds);
     if (sc->hInst) cudaFreeHost(sc->hInst);

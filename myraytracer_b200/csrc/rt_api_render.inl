@@ -111,6 +111,10 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
         return fail(RT_ERR_UNSUPPORTED, "scenes with area lights shard by 8-row chunks only (RT_SHARD_ROWS)");
     const int blocks = sc->blocks[variant][counters ? 1 : 0];
     cudaStream_t st = (cudaStream_t)cudaStream;
+    // scenes with recursion whose child rays are rare (big meshes, a few reflective objects) render in two launches;
+    // RTCUDA_SPLIT=0|1 overrides the choice (measurements, tests)
+    bool split = variant == KV_FAST && sc->recurse && !area && !sc->smallGeometry;
+    if (const char* e = std::getenv("RTCUDA_SPLIT")) split = variant == KV_FAST && sc->recurse && !area && std::atoi(e) != 0;
 
     const size_t threads = (size_t)blocks * renderBlockSize(variant);
     // general kernel: one depth-first stack of maxDepth + 1 entries per thread; fast kernel: per warp a shared queue of
@@ -192,6 +196,12 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
         // area lights: two passes over the tiles (the work counter is reset in between); pass 0 is the counting pass
         sc->passUnits[0] = !area ? 0 : fastCount ? (int64_t)nTiles * FastUnits(ns, sc->recurse).perTile : sc->passUnits[1];
         sc->passWarps[0] = !area ? 0 : fastCount ? (int64_t)(threadsCount / 32) : sc->passWarps[1];
+        if (split) {        // the first launch draws every unit, the second the deferred ones (their number is known on the device only)
+            sc->passUnits[0] = sc->passUnits[1]; sc->passWarps[0] = sc->passWarps[1];
+            sc->passUnits[1] = sc->passUnits[0] / 16 + 1;
+            if ((rc = ensure(&sc->dDefer, &sc->deferBytes, ((size_t)sc->passUnits[0] + 1) * sizeof(int)))) return rc;
+            CK(cudaMemsetAsync(sc->dDefer, 0, sizeof(int), st));
+        }
         sc->pendingUnits = sc->passUnits[0] + sc->passUnits[1];
     }
     if (area) {
@@ -206,6 +216,15 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
         CK(cudaMemsetAsync(sc->dTileCounter, 0, sizeof(int), st));
         rt.areaPass = 2;
     }
+    if (split) {
+        // two launches (rt_render_kernel.cuh: DEFER): depth 0 of every unit in the lean instantiation, which defers the units
+        // whose primary hits spawn child rays; then the queue instantiation over the deferred units
+        rt.deferCount = sc->dDefer; rt.deferList = sc->dDefer + 1;
+        rt.deferPhase = 1; rt.recurse = 0;
+        CK(launchRender(variant, sc->ds, cp, rt, blocks, counters, st));
+        CK(cudaMemsetAsync(sc->dTileCounter, 0, sizeof(int), st));
+        rt.deferPhase = 2; rt.recurse = sc->smallGeometry ? 2 : 1;
+    }
     CK(launchRender(variant, sc->ds, cp, rt, blocks, counters, st));
     CK(cudaEventRecord(sc->evStop, st));
     CK(cudaStreamWaitEvent(sc->side, sc->evStop, 0));
@@ -217,7 +236,7 @@ int32_t rt_render_device(rt_scene_t* sc, const rt_camera* camera, const rt_rende
     CK(cudaEventRecord(sc->evSide, sc->side));
     sc->sideBusy = true;
     sc->pending = true; sc->pendingCounters = counters; sc->pendingStream = st;
-    sc->launches = (adaptive ? 3 : 1) + (area ? 2 : 0) + (adaptive && sc->pendingProbe ? 3 : 0);
+    sc->launches = (adaptive ? 3 : 1) + (area ? 2 : 0) + (adaptive && sc->pendingProbe ? 3 : 0) + (split ? 1 : 0);
     return RT_OK;
 }
 

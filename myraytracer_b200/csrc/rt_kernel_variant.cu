@@ -40,6 +40,11 @@ cudaError_t RT_NAME(launchVariant)(const DeviceScene& S, const CameraParams& cam
         else RT_LAUNCH((renderKernelFast<false, false, RT_FAST_BLOCKS, true>), blocks, RT_THREADS, stream, S, cam, out);
         return cudaGetLastError();
     }
+    if (out.deferPhase == 1) {                 // first of two launches: depth 0 in the lean code, units with child rays deferred
+        if (counters) RT_LAUNCH((renderKernelFast<true, false, RT_FAST_BLOCKS, false, true>), blocks, RT_THREADS, stream, S, cam, out);
+        else RT_LAUNCH((renderKernelFast<false, false, RT_FAST_BLOCKS, false, true>), blocks, RT_THREADS, stream, S, cam, out);
+        return cudaGetLastError();
+    }
     if (out.recurse == 2) {                    // ... and no big mesh: RT_FAST_BLOCKS_SMALL resident warps per SM
         if (counters) RT_LAUNCH(RT_KERNEL_RECURSE_SMALL(true), blocks, RT_THREADS, stream, S, cam, out);
         else RT_LAUNCH(RT_KERNEL_RECURSE_SMALL(false), blocks, RT_THREADS, stream, S, cam, out);

@@ -33,6 +33,12 @@ struct RenderTargets {
     int motion;                    // 1: the scene has motion blur (general kernel, ray time carried down the path)
     int recurse;                   // 1: child rays are possible (fast kernel: the instantiation with the warp's ray queue);
                                    // 2: ... and the scene has no big mesh (the same, compiled for 12 warps of 168 registers per SM)
+    // Two-launch frames of scenes with rare child rays (rt_render_kernel.cuh: DEFER): 1 = the lean instantiation, which
+    // appends the units (tile * unitsPerTile + pass) whose primary hits spawn children to deferList; 2 = the queue
+    // instantiation drawing its units from that list; 0 = one launch.
+    int deferPhase;
+    int* deferList;
+    int* deferCount;
 #ifdef RT_WARPTIMES
     unsigned long long* warpTimes; // profiling build only: 4 x u64 per warp (start, first unit done, last draw, exit; ns)
 #endif

@@ -168,7 +168,14 @@ __device__ __forceinline__ double shflD(double v, int src) { return __shfl_sync(
 // the ray queue — without shadow rays or light terms, adds nAreaLights per shading point to the sample's slot (small
 // integers: exact in FP64 in any order) and leaves the pixel's total in areaIndex.  It replaces the general kernel's
 // per-lane counting walk, which cost 40 % of such a frame.
-template <bool COUNT, bool RECURSE, int BLOCKS = RT_FAST_BLOCKS, bool AREACOUNT = false>
+// DEFER (with RECURSE = false; RenderTargets::deferPhase == 1): the first of two launches on a scene with recursion whose
+// child rays are rare (big meshes, a few reflective objects: C5 reflects 0.65 % of its rays).  The queue instantiation
+// costs every ray 12 % whether it spawns children or not (C4 forced through it: 12.07 against 10.81 ms), so depth 0
+// runs here, in the lean code, and a unit in which some primary hit lands on a mirror / dielectric / conductor is not
+// finished but appended to RenderTargets::deferList; the second launch — the queue instantiation with deferPhase == 2 —
+// draws its units from that list and traces them whole (depth 0 again, then the queue).  A deferred unit's rays are
+// not counted here and its pixels are written there.
+template <bool COUNT, bool RECURSE, int BLOCKS = RT_FAST_BLOCKS, bool AREACOUNT = false, bool DEFER = false>
 __global__ void __launch_bounds__(RT_FAST_BLOCK, BLOCKS) renderKernelFast(DeviceScene S, CameraParams cam, RenderTargets out) {
     static_assert(RT_FAST_BLOCK == 32, "one warp per block: the packet stack and the colour buffer are the warp's");
     __shared__ int2 wstacks[RT_WARP_STACK_INT2];
@@ -235,11 +242,16 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, BLOCKS) renderKernelFast(Device
         int unit = 0;
         if (lane == 0) unit = atomicAdd(out.tileCounter, 1);
         unit = __shfl_sync(0xffffffffu, unit, 0);
-        if (unit >= totalUnits) break;
+        const bool fromList = RECURSE && out.deferPhase == 2;           // second launch: the units the first one deferred
+        if (unit >= (fromList ? *out.deferCount : totalUnits)) break;
+        if (fromList) unit = out.deferList[unit];                       // (tile, pass) as the first launch resolved it
         // Slot -> tile through the schedule of this frame: tiles in descending order of the cost measured on the
         // previous frame (longest first), so the frame ends on its cheapest units instead of a few slow ones.
         const int slot = unit / unitsPerTile;
-        const int tile = out.tileOrder ? __ldg(out.tileOrder + slot) : slot;
+        const int tile = (out.tileOrder && !fromList) ? __ldg(out.tileOrder + slot) : slot;
+        const RayCounts R0 = R;
+        const Counters C0 = C;
+        bool deferred = false;
         if (lane == 0) unitNote[warpInBlock] = make_uint2((unsigned)clock(), (unsigned)tile);
 #ifdef RT_WARPTIMES
         wtUnit = tile * unitsPerTile + (unit - slot * unitsPerTile);     // records are indexed by (tile, pass)
@@ -322,6 +334,7 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, BLOCKS) renderKernelFast(Device
                             h.inst = hit.inst; h.kind = sf.kind; h.prim = sf.prim; h.t = hit.t;
                         }
                         if (AREACOUNT) break;                                       // counting pass: no shadow rays
+                        if (DEFER && __ballot_sync(0xffffffffu, isHit && sp.mat->type != 0) != 0u) { deferred = true; break; }    // type 0 = plain (rt_shade.cuh: spawnChildren)
                         if (__ballot_sync(0xffffffffu, sp.computeDirect) == 0u) break;
                     } else if (rayOn && !occ) {
                         Lo = Lo + pointLightTerm(*sp.mat, S.pointLights[phase - 1], sp.N, cur0.d, wi, dist);
@@ -356,6 +369,7 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, BLOCKS) renderKernelFast(Device
                 Q.push(out.pathStack, S.maxDepth, nc, c1, c2);
             }
             __syncwarp();
+            if (DEFER && deferred) break;       // a primary hit of this unit spawns child rays: the second launch traces the unit
             // ---- pixelColor += trace(...) in sample order (:345), then / samples (:354), pass by pass
 #pragma unroll 1
             for (int b = 0; b < nb; b++) {
@@ -430,7 +444,10 @@ __global__ void __launch_bounds__(RT_FAST_BLOCK, BLOCKS) renderKernelFast(Device
                 }
             }
         }
-        if (!segmented && !units.perPixel && openP >= 0 && lane == 0) {
+        if (DEFER && deferred) {                // not finished here: its rays are not counted, its unit goes on the list
+            R = R0; C = C0;
+            if (lane == 0) out.deferList[atomicAdd(out.deferCount, 1)] = tile * unitsPerTile + sub;
+        } else if (!segmented && !units.perPixel && openP >= 0 && lane == 0) {
             const int qx = (openP & 1) | ((openP >> 1) & 2) | ((openP >> 2) & 4), qy = ((openP >> 1) & 1) | ((openP >> 2) & 2);
             if (x0 + qx < W && y0 + qy < H) emitPixel<AREACOUNT>(out, (size_t)(y0 + qy) * W + (x0 + qx), acc / samplesD);
         }

@@ -115,6 +115,23 @@ def test_emulated_queue_rounds_walk_big_meshes_per_lane(name, scene_dir, emu, mo
     assert (base.rgba == got.rgba).all(axis=-1).mean() >= 0.9999      # other visiting order inside a mesh: ties only
 
 
+@pytest.mark.parametrize("name", ["c3", "c3x9", "c3x64", "c5", "instances"])
+def test_emulated_two_launch_frames_defer_units_with_child_rays(name, scene_dir, emu, monkeypatch):
+    """RTCUDA_SPLIT=1 (the default for scenes with recursion and big meshes): depth 0 of every unit in the lean instantiation,
+    units whose primary hits spawn child rays deferred to a second launch of the queue instantiation.  Same frame bit for
+    bit, same ray counts (a deferred unit's rays are counted once), one more kernel launch; under every unit rule."""
+    fn, kw, _ = CASES[name]
+    path = fn(scene_dir, **kw)
+    monkeypatch.setenv("RTCUDA_SPLIT", "0")
+    one = RayTracerEngine(path).render(0, want_ids=True, want_linear=True, variant=1, schedule=1)
+    monkeypatch.setenv("RTCUDA_SPLIT", "1")
+    two = RayTracerEngine(path).render(0, want_ids=True, want_linear=True, variant=1, schedule=1)
+    assert np.array_equal(one.rgba, two.rgba) and np.array_equal(one.linear, two.linear) and np.array_equal(one.ids, two.ids)
+    for k in ("raysPrimary", "raysShadow", "raysSecondary"):
+        assert one.stats[k] == two.stats[k], k
+    assert two.stats["kernelLaunches"] == one.stats["kernelLaunches"] + 1
+
+
 def test_emulated_edge_cases(scene_dir, emu):
     """tests/edge_cases.py: empty scene (no TLAS: black, not background), one-instance TLAS, 1x1 / 9x5 / 33x17 images,
     sample counts that are not squares (n = floor(sqrt), sum divided by the count), depth 0 with a mirror — both kernels,
