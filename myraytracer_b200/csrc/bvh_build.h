@@ -21,6 +21,7 @@ struct BlasBuildInput {
     int64_t count;
     double motionBlur[3];           // box growth for Triangle.motionBlur (RTContext.swift:283-289)
     int threads;                    // 0 = hardware concurrency
+    bool keepOnDevice = false;      // buildBlasDeviceSah: leave the node / triangle arrays in device memory (dNodes, dTris)
 };
 
 struct BlasBuildOutput {
@@ -34,6 +35,11 @@ struct BlasBuildOutput {
     double pad = 0;                 // absolute padding applied to every FP32 box
     int maxDepth = 0;
     int maxLeaf = 0;
+    // keepOnDevice: the arrays stay where the builder made them (the caller owns them: cudaFree); nodes / tris / trisD are
+    // then empty.  References inside are BLAS-relative like the host vectors'.
+    void* dNodes = nullptr;         // GNode[nNodesDevice]
+    void* dTris = nullptr;          // GTri[nTrisDevice] or GTriD[nTrisDevice] (f64)
+    int64_t nNodesDevice = 0, nTrisDevice = 0;
 };
 
 void buildBlas(const BlasBuildInput& in, BlasBuildOutput& out);

@@ -573,7 +573,8 @@ cudaError_t buildBlasDeviceSah(const double* dVerts, const BlasBuildInput& in, B
               out.f64 ? dTris.as<GTriD>() : nullptr);
     nl++;
     SCK(cudaGetLastError());
-    if (out.f64) { out.trisD.resize((size_t)n); SCK(cudaMemcpy(out.trisD.data(), dTris.p, (size_t)n * sizeof(GTriD), cudaMemcpyDeviceToHost)); }
+    if (in.keepOnDevice) { out.dTris = dTris.p; out.nTrisDevice = n; dTris.p = nullptr; }       // the caller's from here on
+    else if (out.f64) { out.trisD.resize((size_t)n); SCK(cudaMemcpy(out.trisD.data(), dTris.p, (size_t)n * sizeof(GTriD), cudaMemcpyDeviceToHost)); }
     else { out.tris.resize((size_t)n); SCK(cudaMemcpy(out.tris.data(), dTris.p, (size_t)n * sizeof(GTri), cudaMemcpyDeviceToHost)); }
     if (inner == 0) {                                    // the whole BLAS is one leaf
         out.rootRef = ~(int32_t)((0u << 3) | (unsigned)(n - 1));
@@ -583,8 +584,13 @@ cudaError_t buildBlasDeviceSah(const double* dVerts, const BlasBuildInput& in, B
                   dNodes.as<GNode>());
         nl++;
         SCK(cudaGetLastError());
-        out.nodes.resize((size_t)inner);
-        SCK(cudaMemcpy(out.nodes.data(), dNodes.p, (size_t)inner * sizeof(GNode), cudaMemcpyDeviceToHost));
+        if (in.keepOnDevice) {
+            SCK(cudaDeviceSynchronize());
+            out.dNodes = dNodes.p; out.nNodesDevice = inner; dNodes.p = nullptr;
+        } else {
+            out.nodes.resize((size_t)inner);
+            SCK(cudaMemcpy(out.nodes.data(), dNodes.p, (size_t)inner * sizeof(GNode), cudaMemcpyDeviceToHost));
+        }
         out.rootRef = 0;
     }
     if (launches) *launches = nl;

@@ -72,6 +72,17 @@ int uploadRaw(const T* src, size_t count, T** d, int64_t& bytes, std::vector<Sce
     return RT_OK;
 }
 
+// an empty device array of `count` elements, registered like upload()'s
+template <class T>
+int deviceArray(T** d, size_t count, int64_t& bytes, std::vector<SceneArray>* reg, const void* owner) {
+    *d = nullptr;
+    const size_t n = count * sizeof(T);
+    CK(cudaMalloc((void**)d, n ? n : 16));
+    bytes += (int64_t)n;
+    if (reg) reg->push_back(SceneArray{(size_t)((const char*)d - (const char*)owner), n ? n : 16});
+    return RT_OK;
+}
+
 double nowMs() {
     return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
@@ -322,11 +333,23 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     // ---- BLAS build (one per rt_blas, shared by instances)
     std::vector<BlasInfo>& blasInfo = sc->blasInfo;
     blasInfo.assign((size_t)d->nBlas, BlasInfo());
-    std::vector<GNode> nodes;
+    // The scene-wide node / triangle arrays are assembled ON THE DEVICE from per-BLAS pieces: a piece the device builder
+    // left in device memory (RT_BUILD_SAH / RT_BUILD_DEVICE_SAH) is rebased by a kernel and copied device to device —
+    // it never visits the host; a host-built piece is rebased here and copied up into its slice.
+    struct Piece {
+        int64_t nodeBase = 0, triBase = 0, nNodes = 0, nTris = 0;
+        bool f64 = false;
+        std::vector<GNode> nodes; std::vector<GTri> tris; std::vector<GTriD> trisD;     // host-built
+        void* dNodes = nullptr; void* dTris = nullptr;                                   // device-built, kept on the device
+    };
+    struct Pieces : std::vector<Piece> {
+        ~Pieces() { for (Piece& p : *this) { cudaFree(p.dNodes); cudaFree(p.dTris); } }
+    } pieces;
+    int64_t nNodes = 0, nTris = 0, nTrisD = 0;
     std::vector<WNode> wnodes;
-    std::vector<GTri> tris;
-    std::vector<GTriD> trisD;
     int64_t maxDepth = 0, maxLeaf = 0;
+    const char* residentEnv = std::getenv("RTCUDA_BUILD_RESIDENT");
+    const bool resident = !(residentEnv && std::atoi(residentEnv) == 0);
     // wide BVHs for the beam walk of coherent packets (rt_beam.cuh): RTCUDA_WIDE=1 builds them (first B200 run: C4 12.4 ms
     // against 10.8 ms for the binary packet walk, profiles/r2q — off until it wins)
     const char* wideEnv = std::getenv("RTCUDA_WIDE");
@@ -365,6 +388,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
         }
         BlasBuildInput in{};
         in.triVertices = d->triVertices; in.triIndices = idx.data(); in.count = bl.primCount; in.threads = 0;
+        in.keepOnDevice = resident && !(wantWide && bl.primCount >= wideMinTris);     // the wide collapse reads the nodes on the host
         bool blur = false;
         if (d->triMotionBlur) {            // one motion vector per mesh; the boxes grow by it (RTContext.swift:283-289)
             const double* m0 = d->triMotionBlur + idx[0] * 3;
@@ -387,14 +411,19 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
             built = out.maxDepth <= renderStackCapacity() - 2;      // too deep for the stacks: the SAH builder takes over
             if (built) deviceBuilt++;
         }
-        if (!built) buildBlas(in, out);
+        if (!built) {
+            cudaFree(out.dNodes); cudaFree(out.dTris);          // a device attempt that was given up (tree too deep for the stacks)
+            buildBlas(in, out);
+        }
         if (bl.primCount >= 4096) trace(built ? "create: BLAS (device builder)" : "create: BLAS (host builder)", tBlas);
         if (out.maxDepth > renderStackCapacity() - 2) return fail(RT_ERR_UNSUPPORTED, "BLAS deeper than the traversal stack");
         bi.kind = bl.primCount == 1 ? INST_TRI : INST_MESH;
         bi.prim = pr[0].primitiveIndex;
         bi.f64 = out.f64 ? 1 : 0;
-        bi.nodeBase = (int32_t)nodes.size();
-        bi.triBase = (int32_t)(out.f64 ? trisD.size() : tris.size());
+        bi.nodeBase = (int32_t)nNodes;
+        bi.triBase = (int32_t)(out.f64 ? nTrisD : nTris);
+        const bool onDevice = out.dTris != nullptr;
+        const int64_t pieceNodes = onDevice ? out.nNodesDevice : (int64_t)out.nodes.size();
         bi.triCount = bl.primCount;
         bi.rootRef = out.rootRef;
         std::memcpy(bi.lo, out.rootLo, 24); std::memcpy(bi.hi, out.rootHi, 24); std::memcpy(bi.centre, out.centre, 24);
@@ -405,7 +434,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
             const uint32_t r = ~(uint32_t)ref;
             return ~(int32_t)((((r >> 3) + (uint32_t)bi.triBase) << 4) | (out.f64 ? 8u : 0u) | (r & 7u));
         };
-        if ((int64_t)bi.triBase + bl.primCount >= (int64_t)1 << 27 || (int64_t)nodes.size() + (int64_t)out.nodes.size() >= kEmptyRef)
+        if ((int64_t)bi.triBase + bl.primCount >= (int64_t)1 << 27 || nNodes + pieceNodes >= kEmptyRef)
             return fail(RT_ERR_UNSUPPORTED, "scene exceeds the 2^27 triangles / 2^31 nodes of the device references");
         if (wantWide && bl.primCount >= wideMinTris && out.rootRef >= 0 && out.rootRef != kEmptyRef) {
             WideBuildOutput wide;
@@ -426,9 +455,13 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
         }
         for (GNode& g : out.nodes) { g.child0 = rebase(g.child0); g.child1 = rebase(g.child1); }
         bi.rootRef = rebase(out.rootRef);
-        if (nodes.empty()) nodes = std::move(out.nodes); else nodes.insert(nodes.end(), out.nodes.begin(), out.nodes.end());
-        if (out.f64) { if (trisD.empty()) trisD = std::move(out.trisD); else trisD.insert(trisD.end(), out.trisD.begin(), out.trisD.end()); }
-        else { if (tris.empty()) tris = std::move(out.tris); else tris.insert(tris.end(), out.tris.begin(), out.tris.end()); }
+        pieces.emplace_back();
+        Piece& pc = pieces.back();
+        pc.nodeBase = bi.nodeBase; pc.triBase = bi.triBase; pc.nNodes = pieceNodes; pc.nTris = bl.primCount; pc.f64 = out.f64;
+        if (onDevice) { pc.dNodes = out.dNodes; pc.dTris = out.dTris; out.dNodes = out.dTris = nullptr; }
+        else { pc.nodes = std::move(out.nodes); pc.tris = std::move(out.tris); pc.trisD = std::move(out.trisD); }
+        nNodes += pieceNodes;
+        if (out.f64) nTrisD += bl.primCount; else nTris += bl.primCount;
         if (out.maxDepth > maxDepth) maxDepth = out.maxDepth;
         if (out.maxLeaf > maxLeaf) maxLeaf = out.maxLeaf;
         if (bi.kind == INST_MESH) sc->meshes++;
@@ -518,10 +551,22 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
     // ---- upload
     int64_t bytes = 0;
     int rc;
-    if ((rc = upload(nodes, &sc->dNodes, bytes, &sc->arrays, sc))) return rc;
+    if ((rc = deviceArray(&sc->dNodes, (size_t)nNodes, bytes, &sc->arrays, sc))) return rc;
     if ((rc = upload(wnodes, &sc->dWNodes, bytes, &sc->arrays, sc))) return rc;
-    if ((rc = upload(tris, &sc->dTris, bytes, &sc->arrays, sc))) return rc;
-    if ((rc = upload(trisD, &sc->dTrisD, bytes, &sc->arrays, sc))) return rc;
+    if ((rc = deviceArray(&sc->dTris, (size_t)nTris, bytes, &sc->arrays, sc))) return rc;
+    if ((rc = deviceArray(&sc->dTrisD, (size_t)nTrisD, bytes, &sc->arrays, sc))) return rc;
+    for (Piece& pc : pieces) {
+        const size_t triBytes = (size_t)pc.nTris * (pc.f64 ? sizeof(GTriD) : sizeof(GTri));
+        void* triDst = pc.f64 ? (void*)(sc->dTrisD + pc.triBase) : (void*)(sc->dTris + pc.triBase);
+        if (pc.dTris) {
+            CK(launchRebaseNodes(sc->dNodes + pc.nodeBase, (const GNode*)pc.dNodes, (int)pc.nNodes, (int)pc.nodeBase, (int)pc.triBase, pc.f64 ? 1 : 0, 0));
+            if (triBytes) CK(cudaMemcpyAsync(triDst, pc.dTris, triBytes, cudaMemcpyDeviceToDevice, 0));
+        } else {
+            if (pc.nNodes) CK(cudaMemcpy(sc->dNodes + pc.nodeBase, pc.nodes.data(), (size_t)pc.nNodes * sizeof(GNode), cudaMemcpyHostToDevice));
+            if (triBytes) CK(cudaMemcpy(triDst, pc.f64 ? (const void*)pc.trisD.data() : (const void*)pc.tris.data(), triBytes, cudaMemcpyHostToDevice));
+        }
+    }
+    CK(cudaDeviceSynchronize());          // the pieces are freed when `pieces` goes out of scope
     if ((rc = uploadRaw(d->triNormals, (size_t)d->nTriangles * 9, &sc->dNormals, bytes, &sc->arrays, sc))) return rc;     // straight from the caller's array
     // TLAS records: the BLAS node format — FP32 boxes relative to the centre of the scene bounds, padded by
     // M * 2^-19 and rounded outward (conservative: the instance's own exact test decides)
@@ -615,7 +660,7 @@ static int createImpl(const rt_scene_desc* d, int device, rt_scene* sc) {
 
     rt_scene_info& I = sc->info;
     I.triangles = d->nTriangles; I.spheres = d->nSpheres; I.planes = d->nPlanes; I.instances = d->nInstances; I.blasCount = d->nBlas;
-    I.blasNodes = (int64_t)nodes.size(); I.tlasNodes = (int64_t)tl.nodes.size(); I.maxLeafSize = maxLeaf; I.maxDepth = maxDepth;
+    I.blasNodes = nNodes; I.tlasNodes = (int64_t)tl.nodes.size(); I.maxLeafSize = maxLeaf; I.maxDepth = maxDepth;
     I.deviceBytes = bytes; I.buildMs = t1 - t0; I.uploadMs = t2 - t1; I.device = device; I.deviceBuiltBlas = deviceBuilt; I.deviceCount = 1;
     I.wideNodes = (int32_t)wnodes.size();
     return RT_OK;

@@ -273,6 +273,30 @@ cudaError_t launchSchedule(unsigned* tileCost, int* tileOrder, unsigned* work, i
     return cudaGetLastError();
 }
 
+// ---- scene assembly on the device: a BLAS the device builder left in device memory goes into its slice of the scene-wide
+// node array with its references made absolute (gpu_layout.h), exactly what rt_scene_create's host loop does to a
+// host-built BLAS
+__global__ void __launch_bounds__(256) rebaseNodesKernel(GNode* __restrict__ dst, const GNode* __restrict__ src, int n, int nodeBase,
+                                                         int triBase, int f64) {
+    const int i = (int)(blockIdx.x * blockDim.x + threadIdx.x);
+    if (i >= n) return;
+    GNode g = src[i];
+    int32_t* ref[2] = {&g.child0, &g.child1};
+    for (int c = 0; c < 2; c++) {
+        const int32_t r0 = *ref[c];
+        if (r0 == kEmptyRef) continue;
+        if (r0 >= 0) { *ref[c] = r0 + nodeBase; continue; }
+        const uint32_t r = ~(uint32_t)r0;
+        *ref[c] = ~(int32_t)((((r >> 3) + (uint32_t)triBase) << 4) | (f64 ? 8u : 0u) | (r & 7u));
+    }
+    dst[i] = g;
+}
+
+cudaError_t launchRebaseNodes(GNode* dst, const GNode* src, int n, int nodeBase, int triBase, int f64, cudaStream_t stream) {
+    if (n > 0) RT_LAUNCH(rebaseNodesKernel, (n + 255) / 256, 256, stream, dst, src, n, nodeBase, triBase, f64);
+    return cudaGetLastError();
+}
+
 int renderBlockSize(int variant) { return variant == KV_FAST ? blockSizeVariantFast() : blockSizeVariantGeneral(); }
 int renderStackCapacity() { return RT_STACK; }
 int beamStackCapacity() { return RT_BSTACK; }

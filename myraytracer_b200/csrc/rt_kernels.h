@@ -99,6 +99,8 @@ inline double decodeOrdered(unsigned long long u) {
 }
 cudaError_t launchTlasRefit(TNode* tlasD, GNode* tlasOut, const double* instBounds, const int* order, const int* levelStart,
                             int nLevels, const double* centre, double pad, cudaStream_t stream);
+// a device-built BLAS into its slice of the scene's node array, references made absolute (rt_api.cu: scene assembly)
+cudaError_t launchRebaseNodes(GNode* dst, const GNode* src, int n, int nodeBase, int triBase, int f64, cudaStream_t stream);
 cudaError_t launchSchedule(unsigned* tileCost, int* tileOrder, unsigned* work, int nTiles, cudaStream_t stream);
 // first frame of a geometry: per-tile cost estimates from one probe ray per tile (rt_kernel_variant.cu: tileProbeKernel)
 cudaError_t launchTileProbe(const DeviceScene& S, const CameraParams& cam, unsigned* tileCost, int nTiles, cudaStream_t stream);
