@@ -24,7 +24,11 @@
 // A block whose 256 positions all belong to one node accumulates in shared memory and flushes once (the top levels);
 // mixed blocks go to global memory directly (deep levels, where the addresses are spread out anyway).
 // The arrays come back to the host, where rt_scene_create concatenates a scene's BLASes, as with the other builders.
+#include <algorithm>
+#include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <utility>
 #include <vector>
@@ -415,19 +419,51 @@ __global__ void __launch_bounds__(kT) sahEmitTris(const double* __restrict__ ver
     }
 }
 
+// RTCUDA_TRACE=1 (diagnostics, like rt_api.cu's): where a build's host time goes — allocator calls against the rest
+bool sahTraceOn() { static const bool on = std::getenv("RTCUDA_TRACE") != nullptr; return on; }
+double sahNowMs() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+struct SahTrace { double allocMs = 0, freeMs = 0; int allocs = 0, frees = 0; size_t bytes = 0; } gSahTrace;
+
 struct Buf {
     void* p = nullptr;
     size_t bytes = 0;
-    ~Buf() { cudaFree(p); }
-    cudaError_t alloc(size_t b) { bytes = b; return cudaMalloc(&p, b ? b : 16); }
-    cudaError_t atLeast(size_t b) {                 // grow-only, contents dropped
-        if (b <= bytes) return cudaSuccess;
+    ~Buf() { release(); }
+    void release() {
+        if (!p) return;
+        const double t = sahTraceOn() ? sahNowMs() : 0;
         cudaFree(p);
+        if (sahTraceOn()) { gSahTrace.freeMs += sahNowMs() - t; gSahTrace.frees++; }
         p = nullptr;
-        return alloc(b + b / 2);
+    }
+    cudaError_t alloc(size_t b) {
+        bytes = b;
+        const double t = sahTraceOn() ? sahNowMs() : 0;
+        const cudaError_t e = cudaMalloc(&p, b ? b : 16);
+        if (sahTraceOn()) { gSahTrace.allocMs += sahNowMs() - t; gSahTrace.allocs++; gSahTrace.bytes += b; }
+        return e;
     }
     template <class T> T* as() const { return reinterpret_cast<T*>(p); }
 };
+
+// One allocation carved into 256-byte aligned pieces.  A build used to make ~220 cudaMalloc / ~200 cudaFree calls
+// (every per-level array grown on its own), which was three quarters of its host time (profiles/r2al_build_trace.txt);
+// it now makes at most seven.
+struct Arena {
+    Buf mem;
+    size_t used = 0;
+    static size_t pad(size_t b) { return (b + 255) & ~(size_t)255; }
+    template <class T> T* take(size_t count) {
+        T* r = reinterpret_cast<T*>(static_cast<char*>(mem.p) + used);
+        used += pad(count * sizeof(T));
+        return r;
+    }
+};
+
+// bytes of the per-level arrays for a level of `a` nodes (the take<> calls of the level loop, in its order)
+inline size_t levelBytes(size_t a) {
+    return 2 * Arena::pad(a * 24) + 2 * Arena::pad(a * kSlots * 24) + Arena::pad(a * kSlots * 4) + Arena::pad((a + 1) * 4) +
+           3 * Arena::pad(a * 4) + Arena::pad(a * 96) + Arena::pad(a * 8);
+}
 
 inline int blocksFor(long long n) { return (int)((n + kT - 1) / kT); }
 
@@ -445,34 +481,49 @@ cudaError_t buildBlasDeviceSah(const double* dVerts, const BlasBuildInput& in, B
     const int pool = 2 * n;
     const bool blur = in.motionBlur[0] != 0 || in.motionBlur[1] != 0 || in.motionBlur[2] != 0;
     int64_t nl = 0;
+    const double tBuild = sahTraceOn() ? sahNowMs() : 0;
+    if (sahTraceOn()) gSahTrace = SahTrace();
 
-    Buf idx, triBox, order0, order1, nodeOf0, nodeOf1, nFirst, nCount, nLeft, nBox, small;
-    Buf cbLo, cbHi, binLo, binHi, binCnt, flag, sAxis, sBin, sLc, childBox, cursor, sums;
-    SCK(idx.alloc((size_t)n * 8));
-    SCK(cudaMemcpy(idx.p, in.triIndices, (size_t)n * 8, cudaMemcpyHostToDevice));
-    SCK(triBox.alloc((size_t)n * 48));
-    SCK(order0.alloc((size_t)n * 4)); SCK(order1.alloc((size_t)n * 4));
-    SCK(nodeOf0.alloc((size_t)n * 4)); SCK(nodeOf1.alloc((size_t)n * 4));
-    SCK(nFirst.alloc((size_t)pool * 4)); SCK(nCount.alloc((size_t)pool * 4)); SCK(nLeft.alloc((size_t)pool * 4));
-    SCK(nBox.alloc((size_t)pool * 48));
-    SCK(small.alloc(64));                               // u64 rootLo[3], rootHi[3]; int wide, maxLeaf
+    // everything whose size follows from n, in one allocation (the tree has at most pool = 2n nodes, at most n inner)
+    Arena fixed;
+    const size_t nSums = ((size_t)(pool + 1) / 2048 + 2);
+    SCK(fixed.mem.alloc(Arena::pad((size_t)n * 8) + Arena::pad((size_t)n * 48) + 4 * Arena::pad((size_t)n * 4) +
+                        6 * Arena::pad((size_t)pool * 4) + Arena::pad((size_t)pool * 48) + Arena::pad(64) + Arena::pad(nSums * 4) +
+                        Arena::pad((size_t)(n + 1) * 4)));
+    long long* dIdx = fixed.take<long long>((size_t)n);
+    double* dTriBox = fixed.take<double>((size_t)n * 6);
+    int* dOrder0 = fixed.take<int>((size_t)n);
+    int* dOrder1 = fixed.take<int>((size_t)n);
+    int* dNodeOf0 = fixed.take<int>((size_t)n);
+    int* dNodeOf1 = fixed.take<int>((size_t)n);
+    int* dFirst = fixed.take<int>((size_t)pool);
+    int* dCount = fixed.take<int>((size_t)pool);
+    int* dLeft = fixed.take<int>((size_t)pool);
+    unsigned* dGIndex = fixed.take<unsigned>((size_t)pool);
+    int* dSubCount = fixed.take<int>((size_t)pool);
+    int* dPre = fixed.take<int>((size_t)pool);
+    double* dBox = fixed.take<double>((size_t)pool * 6);
+    unsigned char* dSmall = fixed.take<unsigned char>(64);      // u64 rootLo[3], rootHi[3]; int wide, maxLeaf
+    unsigned* dSums = fixed.take<unsigned>(nSums);
+    unsigned* dKArr = fixed.take<unsigned>((size_t)n + 1);
+    SCK(cudaMemcpy(dIdx, in.triIndices, (size_t)n * 8, cudaMemcpyHostToDevice));
     {
         unsigned char init[64];
         std::memset(init, 0, sizeof init);
         std::memset(init, 0xff, 24);
-        SCK(cudaMemcpy(small.p, init, sizeof init, cudaMemcpyHostToDevice));
+        SCK(cudaMemcpy(dSmall, init, sizeof init, cudaMemcpyHostToDevice));
     }
-    u64* dRootLo = small.as<u64>();
+    u64* dRootLo = reinterpret_cast<u64*>(dSmall);
     u64* dRootHi = dRootLo + 3;
     int* dWide = reinterpret_cast<int*>(dRootLo + 6);
     int* dMaxLeaf = dWide + 1;
 
-    RT_LAUNCH(sahPrep, blocksFor(n), kT, 0, dVerts, idx.as<long long>(), n, in.motionBlur[0], in.motionBlur[1], in.motionBlur[2],
-              blur ? 1 : 0, triBox.as<double>(), dRootLo, dRootHi, dWide, order0.as<int>(), nodeOf0.as<int>());
+    RT_LAUNCH(sahPrep, blocksFor(n), kT, 0, dVerts, dIdx, n, in.motionBlur[0], in.motionBlur[1], in.motionBlur[2],
+              blur ? 1 : 0, dTriBox, dRootLo, dRootHi, dWide, dOrder0, dNodeOf0);
     nl++;
     SCK(cudaGetLastError());
     unsigned char back[64];
-    SCK(cudaMemcpy(back, small.p, sizeof back, cudaMemcpyDeviceToHost));
+    SCK(cudaMemcpy(back, dSmall, sizeof back, cudaMemcpyDeviceToHost));
     u64 enc[6];
     std::memcpy(enc, back, 48);
     int wide = 0;
@@ -489,32 +540,43 @@ cudaError_t buildBlasDeviceSah(const double* dVerts, const BlasBuildInput& in, B
     out.pad = std::fmax(M * std::ldexp(1.0, -19), 1e-30);
     {
         const int first = 0, left = -1;
-        SCK(cudaMemcpy(nFirst.p, &first, 4, cudaMemcpyHostToDevice));
-        SCK(cudaMemcpy(nCount.p, &n, 4, cudaMemcpyHostToDevice));
-        SCK(cudaMemcpy(nLeft.p, &left, 4, cudaMemcpyHostToDevice));
-        SCK(cudaMemcpy(nBox.p, rootBox, 48, cudaMemcpyHostToDevice));
+        SCK(cudaMemcpy(dFirst, &first, 4, cudaMemcpyHostToDevice));
+        SCK(cudaMemcpy(dCount, &n, 4, cudaMemcpyHostToDevice));
+        SCK(cudaMemcpy(dLeft, &left, 4, cudaMemcpyHostToDevice));
+        SCK(cudaMemcpy(dBox, rootBox, 48, cudaMemcpyHostToDevice));
     }
 
     SahState S{};
     S.n = n;
-    S.triBox = triBox.as<double>();
-    S.order[0] = order0.as<int>(); S.order[1] = order1.as<int>();
-    S.nodeOf[0] = nodeOf0.as<int>(); S.nodeOf[1] = nodeOf1.as<int>();
-    S.nFirst = nFirst.as<int>(); S.nCount = nCount.as<int>(); S.nLeft = nLeft.as<int>(); S.nBox = nBox.as<double>();
-    SCK(sums.alloc(((size_t)(pool + 1) / 2048 + 2) * 4));
+    S.triBox = dTriBox;
+    S.order[0] = dOrder0; S.order[1] = dOrder1;
+    S.nodeOf[0] = dNodeOf0; S.nodeOf[1] = dNodeOf1;
+    S.nFirst = dFirst; S.nCount = dCount; S.nLeft = dLeft; S.nBox = dBox;
 
+    // The per-level arrays (centroid boxes, bins, split choices) of a level of A nodes, carved from one allocation that
+    // is re-made 16 times larger when a level outgrows it: a level has at most n nodes (each holds a triangle), so
+    // that is at most ceil(log16 n) + 1 allocations per build — three for a million triangles.  The bins dominate (2.5 KB
+    // a node), so the capacity follows the levels rather than starting at the bound.
+    Arena level;
+    size_t levelCap = 0;
     int levelBase = 0, A = 1, depth = 1, cur = 0, used = 1;
     std::vector<std::pair<int, int>> levels;          // (first pool node, nodes) of every level
     for (;;) {
         levels.emplace_back(levelBase, A);
         const size_t a = (size_t)A;
-        SCK(cbLo.atLeast(a * 24)); SCK(cbHi.atLeast(a * 24));
-        SCK(binLo.atLeast(a * kSlots * 24)); SCK(binHi.atLeast(a * kSlots * 24)); SCK(binCnt.atLeast(a * kSlots * 4));
-        SCK(flag.atLeast((a + 1) * 4)); SCK(sAxis.atLeast(a * 4)); SCK(sBin.atLeast(a * 4)); SCK(sLc.atLeast(a * 4));
-        SCK(childBox.atLeast(a * 96)); SCK(cursor.atLeast(a * 8));
-        S.cbLo = cbLo.as<u64>(); S.cbHi = cbHi.as<u64>(); S.binLo = binLo.as<u64>(); S.binHi = binHi.as<u64>();
-        S.binCnt = binCnt.as<unsigned>(); S.flag = flag.as<unsigned>(); S.sAxis = sAxis.as<int>(); S.sBin = sBin.as<int>();
-        S.sLc = sLc.as<int>(); S.childBox = childBox.as<double>(); S.cursor = cursor.as<unsigned>();
+        if (a > levelCap) {
+            levelCap = std::min(std::max(a * 16, (size_t)4096), std::max((size_t)n, a));
+            level.mem.release();                        // kernels of earlier levels still running: cudaFree waits for them
+            SCK(level.mem.alloc(levelBytes(levelCap)));
+        }
+        level.used = 0;
+        S.cbLo = level.take<u64>(a * 3); S.cbHi = level.take<u64>(a * 3);
+        S.binLo = level.take<u64>(a * kSlots * 3); S.binHi = level.take<u64>(a * kSlots * 3);
+        S.binCnt = level.take<unsigned>(a * kSlots);
+        S.flag = level.take<unsigned>(a + 1);
+        S.sAxis = level.take<int>(a); S.sBin = level.take<int>(a); S.sLc = level.take<int>(a);
+        S.childBox = level.take<double>(a * 12);
+        S.cursor = level.take<unsigned>(a * 2);
         SCK(cudaMemsetAsync(S.cbLo, 0xff, a * 24, 0)); SCK(cudaMemsetAsync(S.cbHi, 0, a * 24, 0));
         SCK(cudaMemsetAsync(S.binLo, 0xff, a * kSlots * 24, 0)); SCK(cudaMemsetAsync(S.binHi, 0, a * kSlots * 24, 0));
         SCK(cudaMemsetAsync(S.binCnt, 0, a * kSlots * 4, 0));
@@ -522,7 +584,7 @@ cudaError_t buildBlasDeviceSah(const double* dVerts, const BlasBuildInput& in, B
         RT_LAUNCH(sahCentroids, blocksFor(n), kT, 0, S, cur, levelBase);
         RT_LAUNCH(sahBin, blocksFor(n), kT, 0, S, cur, levelBase);
         RT_LAUNCH(sahSplit, blocksFor(A), kT, 0, S, levelBase, A);
-        SCK(launchExclusiveScan(S.flag, (long long)A + 1, sums.as<unsigned>(), 0));
+        SCK(launchExclusiveScan(S.flag, (long long)A + 1, dSums, 0));
         nl += 6;
         SCK(cudaGetLastError());
         unsigned splits = 0;
@@ -540,27 +602,30 @@ cudaError_t buildBlasDeviceSah(const double* dVerts, const BlasBuildInput& in, B
         cur ^= 1;
     }
     out.maxDepth = depth;
+    if (sahTraceOn()) {
+        cudaDeviceSynchronize();
+        std::fprintf(stderr, "[rtcuda trace] sah: %d levels                  %8.2f ms (cudaMalloc x%d %.2f ms, %zu MB; cudaFree x%d %.2f ms)\n", depth,
+                     sahNowMs() - tBuild, gSahTrace.allocs, gSahTrace.allocMs, gSahTrace.bytes >> 20, gSahTrace.frees, gSahTrace.freeMs);
+    }
 
     // inner nodes -> GNode slots in the host builder's order (above)
-    Buf gIndex, dNodes, dTris, subCount, pre, kArr;
-    SCK(gIndex.alloc((size_t)used * 4)); SCK(subCount.alloc((size_t)used * 4)); SCK(pre.alloc((size_t)used * 4));
+    Buf dNodes, dTris;
     for (size_t l = levels.size(); l-- > 0;) {
-        RT_LAUNCH(sahSubtreeCounts, blocksFor(levels[l].second), kT, 0, S.nLeft, levels[l].first, levels[l].second, subCount.as<int>());
+        RT_LAUNCH(sahSubtreeCounts, blocksFor(levels[l].second), kT, 0, S.nLeft, levels[l].first, levels[l].second, dSubCount);
         nl++;
     }
     int inner = 0;
-    SCK(cudaMemcpy(&inner, subCount.p, 4, cudaMemcpyDeviceToHost));
+    SCK(cudaMemcpy(&inner, dSubCount, 4, cudaMemcpyDeviceToHost));
+    if (inner > n) return cudaErrorUnknown;             // cannot happen: a binary tree over n triangles has fewer than n inner nodes
     if (inner > 0) {
-        SCK(kArr.alloc((size_t)(inner + 1) * 4));
-        SCK(cudaMemsetAsync(kArr.p, 0, (size_t)(inner + 1) * 4, 0));
-        SCK(cudaMemsetAsync(pre.p, 0, 4, 0));
+        SCK(cudaMemsetAsync(dKArr, 0, (size_t)(inner + 1) * 4, 0));
+        SCK(cudaMemsetAsync(dPre, 0, 4, 0));
         for (size_t l = 0; l < levels.size(); l++) {
-            RT_LAUNCH(sahPreorder, blocksFor(levels[l].second), kT, 0, S.nLeft, levels[l].first, levels[l].second, subCount.as<int>(),
-                      pre.as<int>(), kArr.as<unsigned>());
+            RT_LAUNCH(sahPreorder, blocksFor(levels[l].second), kT, 0, S.nLeft, levels[l].first, levels[l].second, dSubCount, dPre, dKArr);
             nl++;
         }
-        SCK(launchExclusiveScan(kArr.as<unsigned>(), (long long)inner + 1, sums.as<unsigned>(), 0));
-        RT_LAUNCH(sahAssignSlots, blocksFor(used), kT, 0, S.nLeft, used, pre.as<int>(), kArr.as<unsigned>(), gIndex.as<unsigned>());
+        SCK(launchExclusiveScan(dKArr, (long long)inner + 1, dSums, 0));
+        RT_LAUNCH(sahAssignSlots, blocksFor(used), kT, 0, S.nLeft, used, dPre, dKArr, dGIndex);
         nl += 4;
     }
     RT_LAUNCH(sahSortLeaves, blocksFor(used), kT, 0, S, cur, used, dMaxLeaf);
@@ -569,7 +634,7 @@ cudaError_t buildBlasDeviceSah(const double* dVerts, const BlasBuildInput& in, B
     SCK(cudaMemcpy(&out.maxLeaf, dMaxLeaf, 4, cudaMemcpyDeviceToHost));
 
     SCK(dTris.alloc((size_t)n * (out.f64 ? sizeof(GTriD) : sizeof(GTri))));
-    RT_LAUNCH(sahEmitTris, blocksFor(n), kT, 0, dVerts, idx.as<long long>(), S.order[cur], n, out.f64 ? nullptr : dTris.as<GTri>(),
+    RT_LAUNCH(sahEmitTris, blocksFor(n), kT, 0, dVerts, dIdx, S.order[cur], n, out.f64 ? nullptr : dTris.as<GTri>(),
               out.f64 ? dTris.as<GTriD>() : nullptr);
     nl++;
     SCK(cudaGetLastError());
@@ -580,7 +645,7 @@ cudaError_t buildBlasDeviceSah(const double* dVerts, const BlasBuildInput& in, B
         out.rootRef = ~(int32_t)((0u << 3) | (unsigned)(n - 1));
     } else {
         SCK(dNodes.alloc((size_t)inner * sizeof(GNode)));
-        RT_LAUNCH(sahEmitNodes, blocksFor(used), kT, 0, S, used, gIndex.as<unsigned>(), out.centre[0], out.centre[1], out.centre[2], out.pad,
+        RT_LAUNCH(sahEmitNodes, blocksFor(used), kT, 0, S, used, dGIndex, out.centre[0], out.centre[1], out.centre[2], out.pad,
                   dNodes.as<GNode>());
         nl++;
         SCK(cudaGetLastError());
@@ -594,6 +659,11 @@ cudaError_t buildBlasDeviceSah(const double* dVerts, const BlasBuildInput& in, B
         out.rootRef = 0;
     }
     if (launches) *launches = nl;
+    if (sahTraceOn()) {
+        cudaDeviceSynchronize();
+        std::fprintf(stderr, "[rtcuda trace] sah: emitted                    %8.2f ms (cudaMalloc x%d %.2f ms; cudaFree x%d %.2f ms)\n", sahNowMs() - tBuild,
+                     gSahTrace.allocs, gSahTrace.allocMs, gSahTrace.frees, gSahTrace.freeMs);
+    }
     return cudaSuccess;
 #undef SCK
 }
