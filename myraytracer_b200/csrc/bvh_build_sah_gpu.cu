@@ -447,7 +447,7 @@ struct Buf {
 
 // One allocation carved into 256-byte aligned pieces.  A build used to make ~220 cudaMalloc / ~200 cudaFree calls
 // (every per-level array grown on its own), which was three quarters of its host time (profiles/r2al_build_trace.txt);
-// it now makes at most seven.
+// it now makes four of each (two arenas and the two output arrays) for a mesh of up to 2^20 triangles.
 struct Arena {
     Buf mem;
     size_t used = 0;
@@ -553,19 +553,21 @@ cudaError_t buildBlasDeviceSah(const double* dVerts, const BlasBuildInput& in, B
     S.nodeOf[0] = dNodeOf0; S.nodeOf[1] = dNodeOf1;
     S.nFirst = dFirst; S.nCount = dCount; S.nLeft = dLeft; S.nBox = dBox;
 
-    // The per-level arrays (centroid boxes, bins, split choices) of a level of A nodes, carved from one allocation that
-    // is re-made 16 times larger when a level outgrows it: a level has at most n nodes (each holds a triangle), so
-    // that is at most ceil(log16 n) + 1 allocations per build — three for a million triangles.  The bins dominate (2.5 KB
-    // a node), so the capacity follows the levels rather than starting at the bound.
+    // The per-level arrays (centroid boxes, bins, split choices) of a level of A nodes, carved from one allocation.  A
+    // level has at most n nodes (each holds a triangle) and the widest level of a SAH tree with 1-2 triangle leaves is
+    // close to n / 2, so the allocation starts at that bound — up to 2^20 nodes (2.7 GB: the bins are 2.5 KB a node) — and
+    // is re-made 16 times larger if a level of a bigger mesh outgrows it.  Driver memory calls are what stalls a build
+    // (one cudaFree of 1.2 s among 4 ms of them, profiles/r2an_build_trace.txt), so there are as few as possible.
     Arena level;
     size_t levelCap = 0;
+    const size_t levelCap0 = std::min((size_t)n, (size_t)1 << 20);
     int levelBase = 0, A = 1, depth = 1, cur = 0, used = 1;
     std::vector<std::pair<int, int>> levels;          // (first pool node, nodes) of every level
     for (;;) {
         levels.emplace_back(levelBase, A);
         const size_t a = (size_t)A;
         if (a > levelCap) {
-            levelCap = std::min(std::max(a * 16, (size_t)4096), std::max((size_t)n, a));
+            levelCap = std::min(std::max(a * 16, levelCap0), std::max((size_t)n, a));
             level.mem.release();                        // kernels of earlier levels still running: cudaFree waits for them
             SCK(level.mem.alloc(levelBytes(levelCap)));
         }

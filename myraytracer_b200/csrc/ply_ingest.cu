@@ -195,6 +195,12 @@ struct DevBuf {
     template <class T> T* as() const { return reinterpret_cast<T*>(p); }
 };
 
+struct Piece {                       // a slice of the ingest's one allocation
+    void* p = nullptr;
+    size_t off = 0;
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
 // Returns 0, or -1 with `msg` set (CUDA error or malformed data); *launches counts the kernels run.
 int plyIngestDevice(const rt_ply_layout& L, const void* vertexBlock, const void* faceBlock, int smooth, double* triVertsOut,
                     double* triNormalsOut, const char** msg, int64_t* launches, double* deviceMs) {
@@ -208,14 +214,23 @@ int plyIngestDevice(const rt_ply_layout& L, const void* vertexBlock, const void*
     P.L = L;
     P.faceRecord = L.faceLeadBytes + L.faceCountBytes + k * L.faceIndexBytes + L.faceTrailBytes;
     P.trisPerFace = k == 4 ? 2 : 1;
-    DevBuf vb, fb, pos, vnf, idx, fn, cnt, cur, ent, vn, err, sums, tv, tn;
-    PCK(vb.alloc((size_t)nV * L.vertexStride)); PCK(fb.alloc((size_t)nF * P.faceRecord));
-    PCK(pos.alloc((size_t)nV * 24)); PCK(idx.alloc((size_t)nT * 12)); PCK(fn.alloc((size_t)nT * 24));
-    PCK(cnt.alloc((size_t)(nV + 1) * 4)); PCK(cur.alloc((size_t)nV * 4)); PCK(err.alloc(4));
-    PCK(tv.alloc((size_t)nT * 72)); PCK(tn.alloc((size_t)nT * 72));
-    if (fileNormals) PCK(vnf.alloc((size_t)nV * 24));
+    // every array in ONE allocation, carved into 256-byte aligned pieces: a driver memory call costs more than these
+    // kernels do, and now and then a hundred times that (profiles/r2an_build_trace.txt)
     const int scanBlocksN = (int)((nV + 1 + RT_SCAN_BLOCK - 1) / RT_SCAN_BLOCK);
-    if (needSmooth) { PCK(ent.alloc((size_t)nT * 12)); PCK(vn.alloc((size_t)nV * 24)); PCK(sums.alloc((size_t)scanBlocksN * 4)); }
+    Piece vb, fb, pos, vnf, idx, fn, cnt, cur, ent, vn, err, sums, tv, tn;
+    size_t total = 0;
+    auto place = [&](Piece& pc, size_t bytes) { pc.off = total; total += (bytes + 255) & ~(size_t)255; };
+    place(vb, (size_t)nV * L.vertexStride); place(fb, (size_t)nF * P.faceRecord);
+    place(pos, (size_t)nV * 24); place(idx, (size_t)nT * 12); place(fn, (size_t)nT * 24);
+    place(cnt, (size_t)(nV + 1) * 4); place(cur, (size_t)nV * 4); place(err, 4);
+    place(tv, (size_t)nT * 72); place(tn, (size_t)nT * 72);
+    if (fileNormals) place(vnf, (size_t)nV * 24);
+    if (needSmooth) { place(ent, (size_t)nT * 12); place(vn, (size_t)nV * 24); place(sums, (size_t)scanBlocksN * 4); }
+    DevBuf arena;
+    PCK(arena.alloc(total));
+    for (Piece* pc : {&vb, &fb, &pos, &idx, &fn, &cnt, &cur, &err, &tv, &tn}) pc->p = static_cast<char*>(arena.p) + pc->off;
+    if (fileNormals) vnf.p = static_cast<char*>(arena.p) + vnf.off;
+    if (needSmooth) for (Piece* pc : {&ent, &vn, &sums}) pc->p = static_cast<char*>(arena.p) + pc->off;
     struct Ev {                      // destroyed on every return path
         cudaEvent_t e = nullptr;
         ~Ev() { if (e) cudaEventDestroy(e); }

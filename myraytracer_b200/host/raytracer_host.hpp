@@ -16,6 +16,7 @@
 #include <map>
 #include <memory>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/rtcuda.h"
@@ -23,17 +24,31 @@
 
 namespace rthost {
 
+// std::allocator whose construct() default-initialises: resize() of a vector of doubles or of plain records leaves
+// the new elements unwritten instead of zero-filling them on one thread.  The per-triangle arrays of a device-ingested
+// mesh are hundreds of MB that rt_ply_ingest / the flatten's own threads overwrite in full; zero-filling them first
+// was 100 of the 125 ms a 1M-triangle flatten took (page faults on one thread, profiles/r2al_build_trace.txt).
+template <class T>
+struct DefaultInitAllocator : std::allocator<T> {
+    template <class U> struct rebind { using other = DefaultInitAllocator<U>; };
+    DefaultInitAllocator() noexcept {}
+    template <class U> DefaultInitAllocator(const DefaultInitAllocator<U>&) noexcept {}
+    template <class U> void construct(U* p) { ::new (static_cast<void*>(p)) U; }
+    template <class U, class... A> void construct(U* p, A&&... a) { ::new (static_cast<void*>(p)) U(std::forward<A>(a)...); }
+};
+using RawDoubles = std::vector<double, DefaultInitAllocator<double>>;
+
 struct RTContext {
     double intersectionTestEpsilon = 0, shadowRayEpsilon = 0;
     std::vector<rt_material> materials;
     std::vector<rt_sphere> spheres;
     std::vector<rt_plane> planes;
-    std::vector<double> triVertices;   // 9 per triangle
-    std::vector<double> triNormals;    // 9 per triangle
-    std::vector<double> triMotionBlur; // 3 per triangle
+    RawDoubles triVertices;            // 9 per triangle
+    RawDoubles triNormals;             // 9 per triangle
+    RawDoubles triMotionBlur;          // 3 per triangle
     std::vector<rt_point_light> pointLights;
     std::vector<rt_area_light> areaLights;
-    std::vector<rt_prim> prims;
+    std::vector<rt_prim, DefaultInitAllocator<rt_prim>> prims;
     std::vector<rt_blas> blas;
     std::vector<rt_instance> instances;
     std::vector<int32_t> instanceObjectIds;
@@ -41,7 +56,7 @@ struct RTContext {
     bool anyMotionBlur = false;
     // local-space bounds of every prim of a BLAS (6 doubles each): Instance.worldBounds is the union of their
     // transformed boxes (makeInstance :437-447, refitTLAS :891-900)
-    std::vector<std::vector<double>> blasPrimBounds;
+    std::vector<RawDoubles> blasPrimBounds;
 
     RTContext() {}
     // ingestDevice >= 0: PLY meshes are ingested on that CUDA device (rt_ply_ingest) where the file layout allows;

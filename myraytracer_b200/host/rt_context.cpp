@@ -7,6 +7,10 @@
 #include <cstdlib>
 #include <cstring>
 #include <limits>
+#include <thread>
+#ifdef __linux__
+#include <sys/mman.h>
+#endif
 
 #include "ply_loader.hpp"
 #include "raytracer_host.hpp"
@@ -72,18 +76,55 @@ void transformBox(const double* lo, const double* hi, const double* M, double* o
     for (int r = 0; r < 3; r++) { olo[r] = cN[r] - eN[r]; ohi[r] = cN[r] + eN[r]; }
 }
 
+// fn(begin, end, part) over [0, n) in contiguous parts, one thread each: the per-triangle loops of big meshes (every
+// part writes — and so first touches — its own pages).  Small n: one call on this thread.
+template <class F>
+void forParts(int64_t n, F fn, int64_t threadedFrom = 32768) {
+    unsigned hw = std::thread::hardware_concurrency();
+    const int64_t parts = n < threadedFrom ? 1 : (int64_t)(hw < 1 ? 1 : (hw > 16 ? 16 : hw));
+    if (parts == 1) { fn((int64_t)0, n, 0); return; }
+    std::vector<std::thread> th;
+    for (int64_t p = 1; p < parts; p++) th.emplace_back(fn, n * p / parts, n * (p + 1) / parts, (int)p);
+    fn((int64_t)0, n / parts, 0);
+    for (std::thread& t : th) t.join();
+}
+const int kMaxParts = 16;
+
+// first touch of freshly allocated (unwritten) elements [from, to) of a default-initialised vector, on all threads
+void touchPages(double* base, size_t from, size_t to) {
+#ifdef __linux__
+    {   // 2 MB pages where the kernel hands them out on request (transparent_hugepage = madvise): 512 times fewer faults
+        const uintptr_t huge = (uintptr_t)2 << 20;
+        const uintptr_t lo = ((uintptr_t)(base + from) + huge - 1) & ~(huge - 1), hi = (uintptr_t)(base + to) & ~(huge - 1);
+        if (hi > lo) madvise((void*)lo, hi - lo, MADV_HUGEPAGE);
+    }
+#endif
+    const size_t step = 4096 / sizeof(double);
+    forParts((int64_t)((to - from + step - 1) / step), [&](int64_t b, int64_t e, int) {
+        for (int64_t k = b; k < e; k++) base[from + (size_t)k * step] = 0.0;
+    }, 1024);
+}
+
 // localToWorld -> worldToLocal, normalMatrix, worldBounds of an instance (makeInstance :437-456, refitTLAS :889-912)
-void placeInstance(rt_instance& in, const double* m16, const std::vector<double>& pb) {
+void placeInstance(rt_instance& in, const double* m16, const RawDoubles& pb) {
     std::memcpy(in.localToWorld, m16, sizeof in.localToWorld);
     inverse4(m16, in.worldToLocal);
     normalMatrix(m16, in.normalMatrix);
     const double inf = std::numeric_limits<double>::infinity();
+    // the union of the transformed prim boxes; min / max are exact, so the parts combine to the one-thread result
+    double plo[kMaxParts][3], phi[kMaxParts][3];
+    for (int p = 0; p < kMaxParts; p++) for (int a = 0; a < 3; a++) { plo[p][a] = inf; phi[p][a] = -inf; }
+    forParts((int64_t)(pb.size() / 6), [&](int64_t b, int64_t e, int part) {
+        double lo[3] = {inf, inf, inf}, hi[3] = {-inf, -inf, -inf};
+        for (int64_t t = b; t < e; t++) {
+            double tl[3], th[3];
+            transformBox(&pb[(size_t)t * 6], &pb[(size_t)t * 6 + 3], m16, tl, th);
+            for (int a = 0; a < 3; a++) { lo[a] = mn(lo[a], tl[a]); hi[a] = mx(hi[a], th[a]); }
+        }
+        for (int a = 0; a < 3; a++) { plo[part][a] = lo[a]; phi[part][a] = hi[a]; }
+    });
     double lo[3] = {inf, inf, inf}, hi[3] = {-inf, -inf, -inf};
-    for (size_t k = 0; k + 5 < pb.size(); k += 6) {
-        double tl[3], th[3];
-        transformBox(&pb[k], &pb[k + 3], m16, tl, th);
-        for (int a = 0; a < 3; a++) { lo[a] = mn(lo[a], tl[a]); hi[a] = mx(hi[a], th[a]); }
-    }
+    for (int p = 0; p < kMaxParts; p++) for (int a = 0; a < 3; a++) { lo[a] = mn(lo[a], plo[p][a]); hi[a] = mx(hi[a], phi[p][a]); }
     for (int a = 0; a < 3; a++) { in.worldBounds[a] = lo[a]; in.worldBounds[3 + a] = hi[a]; }
 }
 
@@ -91,11 +132,11 @@ void placeInstance(rt_instance& in, const double* m16, const std::vector<double>
 
 void RTContext::setInstanceTransform(size_t i, const double* m16, bool boundsOnDevice) {
     rt_instance& in = instances.at(i);
-    const std::vector<double>& pb = blasPrimBounds.at((size_t)in.blas);
+    const RawDoubles& pb = blasPrimBounds.at((size_t)in.blas);
     if (boundsOnDevice && pb.size() > 6) {
         // a mesh: the union over its triangles is left to rt_scene_update_instances (inverted box = "derive"),
         // which computes the same values on the device and writes them back here
-        static const std::vector<double> none;
+        static const RawDoubles none;
         placeInstance(in, m16, none);
     } else {
         placeInstance(in, m16, pb);
@@ -221,7 +262,8 @@ RTContext::RTContext(const pk::Scene& scene, int ingestDevice) {
                     // the kernels' output lands directly behind the triangles flattened so far
                     const int64_t nT = blocks.layout.faceCount * (blocks.layout.verticesPerFace == 4 ? 2 : 1);
                     const size_t old = triVertices.size();
-                    triVertices.resize(old + (size_t)nT * 9); triNormals.resize(old + (size_t)nT * 9);
+                    triVertices.resize(old + (size_t)nT * 9); triNormals.resize(old + (size_t)nT * 9);      // unwritten (RawDoubles)
+                    touchPages(triVertices.data(), old, triVertices.size()); touchPages(triNormals.data(), old, triNormals.size());
                     rt_ply_stats ps{};
                     trace("flatten: output arrays resized", tRead);
                     const double tIng = traceNow();
@@ -271,8 +313,8 @@ RTContext::RTContext(const pk::Scene& scene, int ingestDevice) {
                 }
             }
             const int64_t firstPrim = (int64_t)prims.size();
-            std::vector<double> pb;
-            pb.reserve((size_t)triCount * 6);
+            RawDoubles pb;
+            if (!fromDevice) pb.reserve((size_t)triCount * 6);
             if (fromDevice) {
                 // vertices and normals are in place; motion vectors, prim records and prim boxes in bulk
                 const int64_t first = triangleCount() - triCount;
@@ -280,18 +322,20 @@ RTContext::RTContext(const pk::Scene& scene, int ingestDevice) {
                 prims.resize((size_t)firstPrim + (size_t)triCount);
                 pb.resize((size_t)triCount * 6);
                 if (blur) anyMotionBlur = true;
-                for (int64_t t = 0; t < triCount; t++) {
-                    double* m = &triMotionBlur[(size_t)(first + t) * 3];
-                    m[0] = mb.x; m[1] = mb.y; m[2] = mb.z;
-                    prims[(size_t)(firstPrim + t)] = rt_prim{RT_GEO_TRIANGLE, isSmooth ? 1 : 0, first + t, matID};
-                    const double* v = &triVertices[(size_t)(first + t) * 9];
-                    double* b = &pb[(size_t)t * 6];
-                    for (int a = 0; a < 3; a++) {
-                        double lo = mn(v[a], mn(v[3 + a], v[6 + a])), hi = mx(v[a], mx(v[3 + a], v[6 + a]));
-                        if (blur) { const double m3 = a == 0 ? mb.x : (a == 1 ? mb.y : mb.z); lo = mn(lo, lo + m3); hi = mx(hi, hi + m3); }
-                        b[a] = lo; b[3 + a] = hi;
+                forParts(triCount, [&](int64_t tb, int64_t te, int) {
+                    for (int64_t t = tb; t < te; t++) {
+                        double* m = &triMotionBlur[(size_t)(first + t) * 3];
+                        m[0] = mb.x; m[1] = mb.y; m[2] = mb.z;
+                        prims[(size_t)(firstPrim + t)] = rt_prim{RT_GEO_TRIANGLE, isSmooth ? 1 : 0, first + t, matID};
+                        const double* v = &triVertices[(size_t)(first + t) * 9];
+                        double* b = &pb[(size_t)t * 6];
+                        for (int a = 0; a < 3; a++) {
+                            double lo = mn(v[a], mn(v[3 + a], v[6 + a])), hi = mx(v[a], mx(v[3 + a], v[6 + a]));
+                            if (blur) { const double m3 = a == 0 ? mb.x : (a == 1 ? mb.y : mb.z); lo = mn(lo, lo + m3); hi = mx(hi, hi + m3); }
+                            b[a] = lo; b[3 + a] = hi;
+                        }
                     }
-                }
+                });
             }
             for (int64_t t = 0; t < triCount && !fromDevice; t++) {
                 const int64_t i0 = faceIdx[3 * t] - offset, i1 = faceIdx[3 * t + 1] - offset, i2 = faceIdx[3 * t + 2] - offset;
