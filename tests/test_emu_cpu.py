@@ -302,6 +302,59 @@ def test_emulated_ply_ingest_equals_host_flatten(tmp_path, emu, monkeypatch):
         assert (ran >= 2) == device, (name, ran)          # the kernels ran / the file was left to the host loader
 
 
+def test_emulated_ingest_flatten_of_a_big_mesh_equals_host_flatten(tmp_path, emu, monkeypatch):
+    """Above 32,768 triangles the flatten of a device-ingested mesh runs on all host threads over unwritten
+    (default-initialised) arrays (rt_context.cpp: forParts, touchPages; raytracer_host.hpp: DefaultInitAllocator):
+    every array of the description — vertices, normals, motion vectors, prim records — and the instance's matrices
+    and world box (a threaded min / max reduction) equal the one-thread host flatten's, bit for bit, with a second
+    mesh flattened on the host before and after it so the ingested block lands in the middle of the arrays."""
+    import os
+    import ctypes as C
+    from myraytracer_b200.engine import FlatContext
+    pos, tris = scenegen.terrain_mesh(131, 5, amp=1.3)                   # 2 * 130^2 = 33,800 triangles
+    assert len(tris) > 32768
+    scenegen.write_ply(os.path.join(str(tmp_path), "big.ply"), pos, tris)
+    sp, st = scenegen.icosphere_mesh(1, radius=0.7)
+    verts = [tuple(map(float, v)) for v in sp]
+    sc = scenegen.Scene(maxRecursionDepth=0)
+    sc.vertexData = verts
+    sc.materials = [scenegen._plain(1, (0.5, 0.5, 0.5)), scenegen._plain(2, (0.2, 0.5, 0.8))]
+    M = scenegen.mat_translate((1.5, -0.25, 3.0)) @ scenegen.mat_rotate((0.3, 1.0, 0.2), 37.0) @ scenegen.mat_scale((1.2, 0.8, 1.1))
+    sc.objects = [
+        scenegen.SceneObject(scenegen.OBJ_MESH, id=1, material=2, smooth=False, faces=(st + 1).astype(np.int32)),
+        scenegen.SceneObject(scenegen.OBJ_MESH, id=2, material=1, smooth=True, plyPath="big.ply", transform=scenegen.colmajor(M),
+                             motionBlur=(0.25, -0.5, 0.125)),
+        scenegen.SceneObject(scenegen.OBJ_MESH, id=3, material=1, smooth=True, faces=(st + 1).astype(np.int32)),
+    ]
+    sc.pointLights = [scenegen.PointLight((8.0, 9.0, 8.0), (1000, 1000, 1000))]
+    sc.cameras = [scenegen.Camera(id=1, imageName="big.png", width=16, height=16, numSamples=1, position=(0.0, 12.0, 19.0),
+                                  gaze=(0.0, -0.68, -1.0), up=(0, 1, 0), nearPlane=(-0.4, 0.4, -0.4, 0.4), nearDistance=1.0)]
+    path = os.path.join(str(tmp_path), "big.rtscene")
+    scenegen.write_rtscene(sc, path)
+
+    def arrays(ctx):
+        d = ctx.desc
+        v, n = ctx.triangles()
+        mb = np.ctypeslib.as_array(d.triMotionBlur, shape=(d.nTriangles, 3)).copy()
+        prims = np.frombuffer(C.string_at(d.prims, d.nPrims * C.sizeof(d.prims._type_)), np.uint8).copy()
+        blas = [(d.blas[b].firstPrim, d.blas[b].primCount) for b in range(d.nBlas)]
+        return v, n, mb, prims, blas, ctx.instances()
+
+    monkeypatch.setenv("RTCUDA_INGEST", "host")
+    hv, hn, hmb, hpr, hbl, hin = arrays(FlatContext(path))
+    before = emu.rtemu_kernel_launches()
+    monkeypatch.setenv("RTCUDA_INGEST", "device")
+    dv, dn, dmb, dpr, dbl, din = arrays(FlatContext(path))
+    assert emu.rtemu_kernel_launches() - before >= 2                     # the ingest kernels ran
+    assert len(hv) == len(tris) + 2 * len(st) and len(dv) == len(hv)
+    assert np.array_equal(hv, dv) and np.array_equal(hn, dn, equal_nan=True)
+    assert np.array_equal(hmb, dmb) and np.array_equal(hpr, dpr) and hbl == dbl
+    assert (dmb[len(st):len(st) + len(tris)] == (0.25, -0.5, 0.125)).all() and (dmb[:len(st)] == 0).all()
+    for k in hin:
+        assert np.array_equal(hin[k], din[k]), k
+    assert np.isfinite(din["bounds"]).all()
+
+
 def test_emulator_is_not_the_product(emu):
     """The product loader never hands out the emulation library, and the emulation build says what it is."""
     import os
