@@ -7,6 +7,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <limits>
+#include <system_error>
 #include <thread>
 #ifdef __linux__
 #include <sys/mman.h>
@@ -84,8 +85,12 @@ void forParts(int64_t n, F fn, int64_t threadedFrom = 32768) {
     const int64_t parts = n < threadedFrom ? 1 : (int64_t)(hw < 1 ? 1 : (hw > 16 ? 16 : hw));
     if (parts == 1) { fn((int64_t)0, n, 0); return; }
     std::vector<std::thread> th;
-    for (int64_t p = 1; p < parts; p++) th.emplace_back(fn, n * p / parts, n * (p + 1) / parts, (int)p);
+    int64_t started = 1;
+    try {
+        for (; started < parts; started++) th.emplace_back(fn, n * started / parts, n * (started + 1) / parts, (int)started);
+    } catch (const std::system_error&) {}          // no more threads to be had: the parts not started run here
     fn((int64_t)0, n / parts, 0);
+    for (int64_t p = started; p < parts; p++) fn(n * p / parts, n * (p + 1) / parts, (int)p);
     for (std::thread& t : th) t.join();
 }
 const int kMaxParts = 16;
